@@ -1,0 +1,185 @@
+/* r2d2_b200 -- C ABI of the B200-native R2D2 learner hot path.
+ *
+ * Drop-in boundary for the hot path of LiXirong/pytorch-r2d2 (reference citations are
+ * file:line into that repo).  The reference has no FFI of its own (it is six Python files);
+ * the entry points below are what a ctypes binding of its hot path binds, one per step of
+ * `Learner.train()` (learner.py:68-104) and of the `ReplayMemory` methods it calls.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative R2D2_E* code on failure, never throws;
+ *     `r2d2_last_error()` returns a thread-local message for the last failure;
+ *   - all tensor arguments are raw DEVICE pointers, borrowed for the duration of the enqueue;
+ *     the caller (PyTorch) owns them;
+ *   - `stream` is a `cudaStream_t` passed as `void*`; calls are asynchronous on it;
+ *   - no entry point allocates device memory; scratch is passed in by the caller and sized
+ *     by the matching `*_scratch_bytes` query;
+ *   - layouts are row-major; "time-major" means row index t*B + b (model.py:59,64-66).
+ */
+#ifndef R2D2_B200_H_
+#define R2D2_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define R2D2_OK 0
+#define R2D2_EINVAL (-1)
+#define R2D2_ECUDA (-2)
+
+#define R2D2_TREE_FAN 32
+#define R2D2_FRAME_BYTES 28224 /* 4*84*84 u8, replay_memory.py:65,77 */
+#define R2D2_FEAT 1568        /* 7*7*32, model.py:24,46 */
+#define R2D2_ACTIONS 6        /* model.py:35 */
+
+int r2d2_version(void);
+const char* r2d2_last_error(void);
+/* number of SMs of the current device (grid sizing for callers / bench) */
+int r2d2_sm_count(void);
+
+/* ------------------------------------------------------------------ sum-tree (K1, K8)
+ * Replaces the O(M) mask + normalise + torch.multinomial of replay_memory.py:225-232.
+ * Leaves are implicit: leaf(slot) = is_seq_start[slot]==1 ? sequence_priority[slot] : 0 (f32).
+ * Internal nodes are f64, fan-out 32; level k+1 node j = last element of a Hillis-Steele
+ * warp scan over its 32 children.  `nodes` holds all internal levels bottom-up, back to back;
+ * r2d2_tree_layout gives sizes/offsets. */
+int r2d2_tree_layout(int64_t M, int max_levels, int64_t* level_sizes, int64_t* level_offsets,
+                     int* n_levels, int64_t* total_nodes);
+int r2d2_tree_build(const float* seq_prio, const uint8_t* is_start, int64_t M, double* nodes,
+                    void* stream);
+/* out_slot[i] = slot drawn for the f64 uniform u[i] in [0,1): target = u*root, descend by
+ * "first child with value>0 and inclusive prefix >= target".  Same draws as multinomial
+ * (replay_memory.py:227-232) given the same uniforms; see DESIGN.md for the contract. */
+int r2d2_tree_sample(const float* seq_prio, const uint8_t* is_start, int64_t M,
+                     const double* nodes, const double* u, int B, int64_t* out_slot,
+                     void* stream);
+/* recompute the ancestors of `n` leaves (slots < 0 are skipped) */
+int r2d2_tree_update(const float* seq_prio, const uint8_t* is_start, int64_t M, double* nodes,
+                     const int64_t* slots, int n, void* stream);
+
+/* ------------------------------------------------------------------ slab gather (K2)
+ * Replaces the Python gather loop of replay_memory.py:233-262 (get_stacked_state :215-222 in
+ * its only used mode, stack_count==1).  One contiguous (T+n)-row u8 slab per sequence:
+ *   slab[b, s]      = state[(seq_index[b]+s) % M]             s < T+n   ([B,T+n,4,84,84] u8)
+ *   state[s]        = slab[:, s], next_state[s] = slab[:, s+n] (replay_memory.py:236-237)
+ *   hs,cs           = hs_cs[seq_index] split at `cell`         (:238-239)
+ *   ths,tcs         = target_hs_cs[(seq_index+n)%M] split      (:240-241)
+ *   action/reward/done[t,b] at (seq_index[b]+burn_in+t) % M    (:242-244) time-major [L,B]
+ *   index[s,b]      = (seq_index[b]+s) % M                     (:245) time-major [T,B]   */
+int r2d2_replay_gather(const uint8_t* state, const float* hs_cs, const float* target_hs_cs,
+                       const int8_t* action, const float* reward, const float* done, int64_t M,
+                       int cell, const int64_t* seq_index, int B, int T, int n_step,
+                       int burn_in, uint8_t* slab, float* hs, float* cs, float* ths, float* tcs,
+                       int64_t* action_out, float* reward_out, float* done_out,
+                       int64_t* index_out, int use_tma, void* stream);
+/* compat path for ReplayMemory.sample(): u8 slab -> f32/255 [T,B,4,84,84] at frame offset s0
+ * (replay_memory.py:255-256) */
+int r2d2_slab_to_f32(const uint8_t* slab, int B, int S, int s0, int T, float* out, void* stream);
+
+/* ------------------------------------------------------------------ ingest (K9)
+ * ReplayMemory.extend (replay_memory.py:107-119): copy `rows` staged rows of all ten keys
+ * into ring slots (write_index + i) % M.  src_* are device staging buffers. */
+int r2d2_replay_ingest(const uint8_t* src_state, const float* src_hs_cs,
+                       const float* src_target_hs_cs, const int8_t* src_action,
+                       const float* src_reward, const float* src_done,
+                       const int8_t* src_stack_count, const float* src_priority,
+                       const float* src_seq_prio, const uint8_t* src_is_start, int64_t rows,
+                       uint8_t* state, float* hs_cs, float* target_hs_cs, int8_t* action,
+                       float* reward, float* done, int8_t* stack_count, float* priority,
+                       float* seq_prio, uint8_t* is_start, int64_t M, int cell,
+                       int64_t write_index, void* stream);
+
+/* ------------------------------------------------------------------ priorities (K8)
+ * update_priority (replay_memory.py:175-176): priority[index[k]] = p[k], last occurrence
+ * wins on duplicate slots (numpy fancy assignment order). */
+int r2d2_update_priority(float* priority, int64_t M, const int64_t* index, const float* p,
+                         int64_t n, void* stream);
+/* The learner's fused form (learner.py:103): index = (seq_index[b]+burn_in+t)%M at flat
+ * position t*B+b; duplicates resolved to the last flat position without scratch. */
+int r2d2_update_priority_seq(float* priority, int64_t M, const int64_t* seq_index, int B,
+                             int burn_in, int L, const float* p, void* stream);
+/* update_sequence_priority (replay_memory.py:184-213) incl. its neighbour quirks; numpy f32
+ * pairwise-sum order for the mean; eta_f32/one_minus_eta_f32 are the f32 roundings of the
+ * Python floats.  touched[3*n] receives the slots written (or -1), for r2d2_tree_update. */
+int r2d2_update_sequence_priority(const float* priority, float* seq_prio,
+                                  const uint8_t* is_start, int64_t M, const int64_t* seq_index,
+                                  int n, int T, float eta_f32, float one_minus_eta_f32,
+                                  int update_pre_next, int64_t* touched, void* stream);
+
+/* ------------------------------------------------------------------ network, forward
+ * conv torso (model.py:13-21,44-46).  Frames come from the u8 slab: output row r = t*B + b
+ * for t < nt reads slab[b, s0 + t]; /255 fused (replay_memory.py:256).  a1 [R,32,20,20],
+ * a2 [R,32,9,9], feat [R,1568] (C-major flatten). */
+int r2d2_torso_fwd_u8(const uint8_t* slab, int B, int S, int s0, int nt, const float* w1,
+                      const float* b1, const float* w2, const float* b2, const float* w3,
+                      const float* b3, float* a1, float* a2, float* feat, void* stream);
+/* same for caller-provided f32 frames [R,4,84,84] (QNet.forward's input, model.py:38-44) */
+int r2d2_torso_fwd_f32(const float* frames, int R, const float* w1, const float* b1,
+                       const float* w2, const float* b2, const float* w3, const float* b3,
+                       float* a1, float* a2, float* feat, void* stream);
+/* y[M,N] = x[M,K] . w[N,K]^T + bias1 + bias2 (either may be NULL), optional ReLU */
+int r2d2_linear_fwd(const float* x, const float* w, const float* bias1, const float* bias2,
+                    float* y, int M, int N, int K, int relu, void* stream);
+/* LSTM unroll (model.py:52-60): xproj [T,B,4H] already holds x.W_ih^T + b_ih + b_hh.
+ * hs_ext/cs_ext are [(T+1),B,H]; slot 0 is the initial state (written by the caller), slot
+ * t+1 receives step t.  gates [T,B,4H] (post-activation i,f,g,o) may be NULL (inference). */
+int r2d2_lstm_seq_fwd(const float* xproj, const float* w_hh, float* hs_ext, float* cs_ext,
+                      float* gates, int T, int B, int H, void* stream);
+/* dueling head (model.py:26-36,62-64): w1 [2H,H] = (val.0.weight; adv.0.weight),
+ * b1 [2H], w2 [7,H] = (val.2.weight; adv.2.weight), b2 [7].  hid [M,2H] scratch/stash. */
+int r2d2_head_fwd(const float* hs, const float* w1, const float* b1, const float* w2,
+                  const float* b2, float* hid, float* q, int M, int H, void* stream);
+
+/* ------------------------------------------------------------------ target / TD (K7)
+ * learner.py:86-102: a* = argmax q_next_online (first max), y = r + gamma_n*Qt[a*]*(1-done)
+ * (optionally h(r + gamma_n*h^-1(Qt)*(1-done)), NOT in the reference, default off),
+ * delta = q[action]-y, loss = mean(0.5 delta^2), dq = dloss/dq_all, prio=(|delta|+eps)^alpha */
+int r2d2_td_target(const float* q_all, const float* q_next_online, const float* q_next_target,
+                   const int64_t* action, const float* reward, const float* done, int n,
+                   float gamma_n, int rescale, float rescale_eps, float prio_eps, float alpha,
+                   const int64_t* next_action_override, int64_t* next_action, float* y,
+                   float* delta, float* dq, float* prio, float* loss, void* stream);
+
+/* ------------------------------------------------------------------ network, backward
+ * (autograd of learner.py:97-99 through model.py:44-66) */
+int r2d2_head_bwd(const float* dq, const float* hid, const float* w2, float* dhid, float* dw2,
+                  float* db2, int M, int H, void* stream);
+/* dx[M,K] (+)= dy[M,N] . w[N,K] */
+int r2d2_linear_dgrad(const float* dy, const float* w, float* dx, int M, int N, int K,
+                      int accumulate, void* stream);
+/* dw[N,K] = dy[M,N]^T . x[M,K]; db[N] = column sums of dy (db may be NULL).
+ * scratch: r2d2_linear_wgrad_scratch_bytes(M,N,K) bytes (split-K partials). */
+int64_t r2d2_linear_wgrad_scratch_bytes(int M, int N, int K);
+int r2d2_linear_wgrad(const float* dy, const float* x, float* dw, float* db, int M, int N,
+                      int K, void* scratch, void* stream);
+/* BPTT over the learn window: dhs [T,B,H] is dL/dh_t from the head; gates/cs_ext from
+ * r2d2_lstm_seq_fwd.  Writes dgates [T,B,4H] (pre-activation grads).  dc_work [B,H] carries
+ * dL/dc between steps (caller-owned, contents undefined on entry). */
+int r2d2_lstm_seq_bwd(const float* dhs, const float* w_hh, const float* gates,
+                      const float* cs_ext, float* dgates, float* dc_work, int T, int B, int H,
+                      void* stream);
+/* conv torso backward for R frames (slab rows as in r2d2_torso_fwd_u8): dfeat [R,1568] is
+ * overwritten; dw*,db* written.  scratch: r2d2_torso_bwd_scratch_bytes(R). */
+int64_t r2d2_torso_bwd_scratch_bytes(int R);
+int r2d2_torso_bwd_u8(const uint8_t* slab, int B, int S, int s0, int nt, const float* a1,
+                      const float* a2, const float* feat, float* dfeat, const float* w2,
+                      const float* w3, float* dw1, float* db1, float* dw2, float* db2,
+                      float* dw3, float* db3, void* scratch, void* stream);
+/* same for caller-provided f32 frames [R,4,84,84] (autograd of QNet.forward) */
+int r2d2_torso_bwd_f32(const float* frames, int R, const float* a1, const float* a2,
+                       const float* feat, float* dfeat, const float* w2, const float* w3,
+                       float* dw1, float* db1, float* dw2, float* db2, float* dw3, float* db3,
+                       void* scratch, void* stream);
+
+/* ------------------------------------------------------------------ optimiser (K10)
+ * torch.optim.RMSprop(centered=True) of learner.py:51 over a flat f32 buffer:
+ * g *= grad_scale; v = a v + (1-a) g^2; m = a m + (1-a) g; p -= lr*g/(sqrt(v-m^2)+eps) */
+int r2d2_rmsprop_centered(float* param, const float* grad, float* square_avg, float* grad_avg,
+                          int64_t n, double lr, double alpha, double eps, double grad_scale,
+                          void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* R2D2_B200_H_ */

@@ -1,0 +1,104 @@
+"""ctypes binding of libr2d2_b200.so (the C ABI declared in include/r2d2_b200.h).
+
+The library is the product path; there is NO fallback.  If the shared object is missing or a
+call fails, a RuntimeError carrying ``r2d2_last_error()`` is raised.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libr2d2_b200.so")
+
+_P, _I, _L, _F, _D = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_float, ctypes.c_double
+
+# name -> (restype, argtypes); mirrors include/r2d2_b200.h one to one
+PROTOTYPES = {
+    "r2d2_version": (_I, []),
+    "r2d2_last_error": (ctypes.c_char_p, []),
+    "r2d2_sm_count": (_I, []),
+    "r2d2_tree_layout": (_I, [_L, _I, _P, _P, _P, _P]),
+    "r2d2_tree_build": (_I, [_P, _P, _L, _P, _P]),
+    "r2d2_tree_sample": (_I, [_P, _P, _L, _P, _P, _I, _P, _P]),
+    "r2d2_tree_update": (_I, [_P, _P, _L, _P, _P, _I, _P]),
+    "r2d2_replay_gather": (_I, [_P] * 6 + [_L, _I, _P, _I, _I, _I, _I] + [_P] * 9 + [_I, _P]),
+    "r2d2_slab_to_f32": (_I, [_P, _I, _I, _I, _I, _P, _P]),
+    "r2d2_replay_ingest": (_I, [_P] * 10 + [_L] + [_P] * 10 + [_L, _I, _L, _P]),
+    "r2d2_update_priority": (_I, [_P, _L, _P, _P, _L, _P]),
+    "r2d2_update_priority_seq": (_I, [_P, _L, _P, _I, _I, _I, _P, _P]),
+    "r2d2_update_sequence_priority": (_I, [_P, _P, _P, _L, _P, _I, _I, _F, _F, _I, _P, _P]),
+    "r2d2_torso_fwd_u8": (_I, [_P, _I, _I, _I, _I] + [_P] * 9 + [_P]),
+    "r2d2_torso_fwd_f32": (_I, [_P, _I] + [_P] * 9 + [_P]),
+    "r2d2_linear_fwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
+    "r2d2_lstm_seq_fwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _P]),
+    "r2d2_head_fwd": (_I, [_P] * 7 + [_I, _I, _P]),
+    "r2d2_td_target": (_I, [_P] * 6 + [_I, _F, _I, _F, _F, _F] + [_P] * 7 + [_P]),
+    "r2d2_head_bwd": (_I, [_P] * 6 + [_I, _I, _P]),
+    "r2d2_linear_dgrad": (_I, [_P, _P, _P, _I, _I, _I, _I, _P]),
+    "r2d2_linear_wgrad_scratch_bytes": (_L, [_I, _I, _I]),
+    "r2d2_linear_wgrad": (_I, [_P, _P, _P, _P, _I, _I, _I, _P, _P]),
+    "r2d2_lstm_seq_bwd": (_I, [_P] * 6 + [_I, _I, _I, _P]),
+    "r2d2_torso_bwd_scratch_bytes": (_L, [_I]),
+    "r2d2_torso_bwd_u8": (_I, [_P, _I, _I, _I, _I] + [_P] * 13 + [_P]),
+    "r2d2_torso_bwd_f32": (_I, [_P, _I] + [_P] * 13 + [_P]),
+    "r2d2_rmsprop_centered": (_I, [_P, _P, _P, _P, _L, _D, _D, _D, _D, _P]),
+}
+
+_lib = None
+
+
+def load():
+    """Load the shared library (once).  Raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: build it with `python -m pytorch_r2d2_b200.build` "
+            "(or __graft_entry__.build()).  There is no CPU or PyTorch fallback.")
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (res, args) in PROTOTYPES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is not exported
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def last_error() -> str:
+    return load().r2d2_last_error().decode("utf-8", "replace")
+
+
+def check(rc: int, what: str = "") -> None:
+    if rc != 0:
+        raise RuntimeError(f"r2d2_b200 {what} failed (code {rc}): {last_error()}")
+
+
+def stream_ptr() -> ctypes.c_void_p:
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+_DT = {"f32": torch.float32, "f64": torch.float64, "u8": torch.uint8, "i8": torch.int8,
+       "i64": torch.int64}
+
+
+def ptr(t, dtype: str | None = None, allow_none: bool = False) -> ctypes.c_void_p:
+    """Device pointer of a contiguous CUDA tensor (with dtype check)."""
+    if t is None:
+        if allow_none:
+            return ctypes.c_void_p(0)
+        raise ValueError("null tensor passed to r2d2_b200")
+    if not t.is_cuda:
+        raise ValueError("r2d2_b200 kernels take CUDA tensors only (no CPU fallback)")
+    if not t.is_contiguous():
+        raise ValueError("r2d2_b200 kernels take contiguous tensors")
+    if dtype is not None and t.dtype != _DT[dtype]:
+        raise TypeError(f"expected {dtype} tensor, got {t.dtype}")
+    return ctypes.c_void_p(t.data_ptr())
+
+
+def call(name: str, *args) -> None:
+    check(getattr(load(), name)(*args), name)

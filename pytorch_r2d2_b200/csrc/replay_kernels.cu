@@ -1,0 +1,702 @@
+// GPU-resident prioritized sequence replay: sum-tree (K1/K8), slab gather (K2), ingest (K9),
+// priority scatter and sequence-priority refresh (K8).  Integer/byte work: HBM- or
+// latency-bound; no tensor cores.  Reference semantics: replay_memory.py:93-119,175-262.
+#include "common.cuh"
+
+namespace r2d2 {
+
+static thread_local char g_err[512] = "";
+char* err_buf() { return g_err; }
+int set_err(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+int sm_count() {
+    int dev = 0, n = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess)
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    return n;
+}
+
+// ======================================================================== sum-tree
+constexpr int FAN = R2D2_TREE_FAN;
+constexpr int MAX_LEVELS = 8;
+
+struct TreeLayout {
+    int n_levels;
+    int64_t size[MAX_LEVELS];
+    int64_t off[MAX_LEVELS];
+    int64_t total;
+};
+
+static TreeLayout make_layout(int64_t M) {
+    TreeLayout L{};
+    int64_t n = M, off = 0;
+    int l = 0;
+    while (l < MAX_LEVELS) {
+        n = (n + FAN - 1) / FAN;
+        L.size[l] = n;
+        L.off[l] = off;
+        off += n;
+        ++l;
+        if (n <= FAN) break;
+    }
+    L.n_levels = l;
+    L.total = off;
+    return L;
+}
+
+// Inclusive Hillis-Steele scan across the warp, f64.  The association (own + lower, d =
+// 1,2,4,8,16) is part of the parity contract: oracle/replay_oracle.py:_hs_scan mirrors it.
+__device__ __forceinline__ double hs_scan(double v, int lane) {
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        double o = __shfl_up_sync(FULL, v, d);
+        if (lane >= d) v = __dadd_rn(v, o);
+    }
+    return v;
+}
+
+__device__ __forceinline__ double leaf_value(const float* __restrict__ sp,
+                                             const uint8_t* __restrict__ st, int64_t slot,
+                                             int64_t M) {
+    if (slot >= M) return 0.0;
+    return st[slot] == 1 ? (double)sp[slot] : 0.0;
+}
+
+// one warp per parent node of level `lvl` (0 = parents of leaves)
+__global__ void tree_build_level(const float* __restrict__ sp, const uint8_t* __restrict__ st,
+                                 int64_t M, double* __restrict__ nodes, int lvl,
+                                 int64_t child_off, int64_t child_size, int64_t out_off,
+                                 int64_t out_size) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t j = warp; j < out_size; j += nwarps) {
+        const int64_t c = j * FAN + lane;
+        double v;
+        if (lvl == 0) v = leaf_value(sp, st, c, M);
+        else v = c < child_size ? nodes[child_off + c] : 0.0;
+        v = hs_scan(v, lane);
+        if (lane == 31) nodes[out_off + j] = v;
+    }
+}
+
+// Descent rule (shared with oracle SumTree._pick): first lane with value>0 and inclusive
+// prefix >= target; else the last lane with value>0; lane 0 if the node is empty.
+__device__ __forceinline__ int pick_child(double v, double pre, double& target, int lane) {
+    unsigned hit = __ballot_sync(FULL, v > 0.0 && pre >= target);
+    int sel;
+    if (hit) sel = __ffs(hit) - 1;
+    else {
+        unsigned pos = __ballot_sync(FULL, v > 0.0);
+        sel = pos ? 31 - __clz(pos) : 0;
+    }
+    double excl = __shfl_sync(FULL, pre, sel > 0 ? sel - 1 : 0);
+    if (sel == 0) excl = 0.0;
+    target = __dsub_rn(target, excl);
+    return sel;
+}
+
+__global__ void tree_sample_kernel(const float* __restrict__ sp, const uint8_t* __restrict__ st,
+                                   int64_t M, const double* __restrict__ nodes, TreeLayout L,
+                                   const double* __restrict__ u, int B,
+                                   int64_t* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const int draw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (draw >= B) return;
+    const int top = L.n_levels - 1;
+    double v = lane < L.size[top] ? nodes[L.off[top] + lane] : 0.0;
+    double pre = hs_scan(v, lane);
+    const double root = __shfl_sync(FULL, pre, 31);
+    double target = __dmul_rn(u[draw], root);
+    int64_t node = pick_child(v, pre, target, lane);
+    for (int lvl = top; lvl >= 0; --lvl) {
+        const int64_t c = node * FAN + lane;
+        if (lvl == 0) v = leaf_value(sp, st, c, M);
+        else v = c < L.size[lvl - 1] ? nodes[L.off[lvl - 1] + c] : 0.0;
+        pre = hs_scan(v, lane);
+        node = node * FAN + pick_child(v, pre, target, lane);
+    }
+    if (lane == 0) out[draw] = node;
+}
+
+// single CTA; level-synchronous recompute of the ancestors of `n` leaves
+__global__ void tree_update_kernel(const float* __restrict__ sp, const uint8_t* __restrict__ st,
+                                   int64_t M, double* __restrict__ nodes, TreeLayout L,
+                                   const int64_t* __restrict__ slots, int n) {
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int nwarps = blockDim.x >> 5;
+    for (int lvl = 0; lvl < L.n_levels; ++lvl) {
+        for (int i = warp; i < n; i += nwarps) {
+            int64_t s = slots[i];
+            if (s < 0 || s >= M) continue;  // warp-uniform
+            int64_t node = s;
+            for (int k = 0; k <= lvl; ++k) node /= FAN;
+            const int64_t c = node * FAN + lane;
+            double v;
+            if (lvl == 0) v = leaf_value(sp, st, c, M);
+            else v = c < L.size[lvl - 1] ? nodes[L.off[lvl - 1] + c] : 0.0;
+            v = hs_scan(v, lane);
+            if (lane == 31) nodes[L.off[lvl] + node] = v;
+        }
+        __threadfence_block();
+        __syncthreads();
+    }
+}
+
+// ======================================================================== gather
+constexpr int FRAME_U4 = R2D2_FRAME_BYTES / 16;  // 1764 x 16 B per transition row
+
+// one CTA per (sequence, row): a 28 224-byte contiguous row copy, 16 B per lane per access
+__global__ void __launch_bounds__(256)
+gather_rows_kernel(const uint4* __restrict__ state, int64_t M,
+                   const int64_t* __restrict__ seq_index, int S, uint4* __restrict__ slab) {
+    const int b = blockIdx.y, s = blockIdx.x;
+    const int64_t src = (seq_index[b] + s) % M;
+    const uint4* in = state + src * FRAME_U4;
+    uint4* out = slab + ((int64_t)b * S + s) * FRAME_U4;
+    uint4 v[7];
+#pragma unroll
+    for (int j = 0; j < 7; ++j) {
+        int i = threadIdx.x + j * 256;
+        if (i < FRAME_U4) v[j] = ld_stream(in + i);
+    }
+#pragma unroll
+    for (int j = 0; j < 7; ++j) {
+        int i = threadIdx.x + j * 256;
+        if (i < FRAME_U4) st_stream(out + i, v[j]);
+    }
+}
+
+// ---- TMA (bulk async copy) variant: global -> smem -> global, one elected thread drives a
+// 4-deep ring of 28 224-byte row buffers per CTA; persistent grid.
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    // bounded: a lost transaction traps instead of hanging the GPU
+    for (uint32_t it = 0; it < (1u << 28); ++it)
+        if (mbar_try_wait(bar, parity)) return;
+    __trap();
+}
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32_t bytes,
+                                         uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+        ::"r"(smem_u32(dst_smem)), "l"(src), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void* dst, const void* src_smem, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst),
+                 "r"(smem_u32(src_smem)), "r"(bytes)
+                 : "memory");
+}
+
+constexpr int TMA_STAGES = 4;
+
+__global__ void __launch_bounds__(32)
+gather_rows_tma_kernel(const uint8_t* __restrict__ state, int64_t M,
+                       const int64_t* __restrict__ seq_index, int B, int S,
+                       uint8_t* __restrict__ slab) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ uint64_t full[TMA_STAGES];
+    if (threadIdx.x != 0) return;
+    for (int i = 0; i < TMA_STAGES; ++i) mbar_init(&full[i], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    const int64_t total = (int64_t)B * S;
+    const int64_t per = (total + gridDim.x - 1) / gridDim.x;
+    const int64_t lo = blockIdx.x * per;
+    const int64_t hi = lo + per < total ? lo + per : total;
+    const int64_t cnt = hi > lo ? hi - lo : 0;
+    // prologue: fill the ring
+    for (int64_t i = 0; i < cnt && i < TMA_STAGES; ++i) {
+        const int64_t r = lo + i;
+        const int64_t src = (seq_index[r / S] + (r % S)) % M;
+        mbar_expect_tx(&full[i], R2D2_FRAME_BYTES);
+        bulk_g2s(smem + i * R2D2_FRAME_BYTES, state + src * R2D2_FRAME_BYTES, R2D2_FRAME_BYTES,
+                 &full[i]);
+    }
+    for (int64_t i = 0; i < cnt; ++i) {
+        const int st = (int)(i % TMA_STAGES);
+        const uint32_t parity = (uint32_t)((i / TMA_STAGES) & 1);
+        mbar_wait(&full[st], parity);
+        bulk_s2g(slab + (lo + i) * R2D2_FRAME_BYTES, smem + st * R2D2_FRAME_BYTES,
+                 R2D2_FRAME_BYTES);
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        const int64_t nx = i + TMA_STAGES;
+        if (nx < cnt) {
+            // the buffer may be refilled once its store has finished READING smem
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            const int64_t r = lo + nx;
+            const int64_t src = (seq_index[r / S] + (r % S)) % M;
+            mbar_expect_tx(&full[st], R2D2_FRAME_BYTES);
+            bulk_g2s(smem + st * R2D2_FRAME_BYTES, state + src * R2D2_FRAME_BYTES,
+                     R2D2_FRAME_BYTES, &full[st]);
+        }
+    }
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
+// hidden rows, action/reward/done over the learn window, index matrix
+__global__ void gather_small_kernel(const float* __restrict__ hs_cs,
+                                    const float* __restrict__ ths_cs,
+                                    const int8_t* __restrict__ action,
+                                    const float* __restrict__ reward,
+                                    const float* __restrict__ done, int64_t M, int cell,
+                                    const int64_t* __restrict__ seq_index, int B, int T,
+                                    int n_step, int burn_in, float* __restrict__ hs,
+                                    float* __restrict__ cs, float* __restrict__ ths,
+                                    float* __restrict__ tcs, int64_t* __restrict__ action_out,
+                                    float* __restrict__ reward_out, float* __restrict__ done_out,
+                                    int64_t* __restrict__ index_out) {
+    const int L = T - burn_in;
+    const int64_t n_hidden = (int64_t)B * cell;
+    const int64_t n_learn = (int64_t)L * B;
+    const int64_t n_index = (int64_t)T * B;
+    const int64_t total = n_hidden + n_learn + n_index;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        if (i < n_hidden) {
+            const int b = (int)(i / cell), j = (int)(i % cell);
+            const int64_t s0 = seq_index[b], s1 = (s0 + n_step) % M;
+            hs[i] = hs_cs[s0 * 2 * cell + j];
+            cs[i] = hs_cs[s0 * 2 * cell + cell + j];
+            ths[i] = ths_cs[s1 * 2 * cell + j];
+            tcs[i] = ths_cs[s1 * 2 * cell + cell + j];
+        } else if (i < n_hidden + n_learn) {
+            const int64_t k = i - n_hidden;
+            const int t = (int)(k / B), b = (int)(k % B);
+            const int64_t slot = (seq_index[b] + burn_in + t) % M;
+            action_out[k] = (int64_t)action[slot];
+            reward_out[k] = reward[slot];
+            done_out[k] = done[slot];
+        } else {
+            const int64_t k = i - n_hidden - n_learn;
+            const int s = (int)(k / B), b = (int)(k % B);
+            index_out[k] = (seq_index[b] + s) % M;
+        }
+    }
+}
+
+// slab u8 [B,S,frame] -> f32/255 [T,B,frame] starting at frame offset s0
+__global__ void slab_to_f32_kernel(const uint8_t* __restrict__ slab, int B, int S, int s0,
+                                   int T, float* __restrict__ out) {
+    const int64_t row = blockIdx.x;  // t*B + b
+    const int t = (int)(row / B), b = (int)(row % B);
+    const uchar4* in =
+        reinterpret_cast<const uchar4*>(slab + ((int64_t)b * S + s0 + t) * R2D2_FRAME_BYTES);
+    float4* o = reinterpret_cast<float4*>(out + row * R2D2_FRAME_BYTES);
+    for (int i = threadIdx.x; i < R2D2_FRAME_BYTES / 4; i += blockDim.x) {
+        uchar4 v = in[i];
+        o[i] = make_float4(__fdiv_rn((float)v.x, 255.f), __fdiv_rn((float)v.y, 255.f),
+                           __fdiv_rn((float)v.z, 255.f), __fdiv_rn((float)v.w, 255.f));
+    }
+}
+
+// ======================================================================== ingest
+__global__ void __launch_bounds__(256)
+ingest_rows_kernel(const uint4* __restrict__ src, uint4* __restrict__ state, int64_t M,
+                   int64_t write_index) {
+    const int64_t i = blockIdx.x;
+    const int64_t slot = (write_index + i) % M;
+    const uint4* in = src + i * FRAME_U4;
+    uint4* out = state + slot * FRAME_U4;
+    uint4 v[7];
+#pragma unroll
+    for (int j = 0; j < 7; ++j) {
+        int k = threadIdx.x + j * 256;
+        if (k < FRAME_U4) v[j] = ld_stream(in + k);
+    }
+#pragma unroll
+    for (int j = 0; j < 7; ++j) {
+        int k = threadIdx.x + j * 256;
+        if (k < FRAME_U4) st_stream(out + k, v[j]);
+    }
+}
+
+__global__ void ingest_small_kernel(const float* __restrict__ s_hs, const float* __restrict__ s_ths,
+                                    const int8_t* __restrict__ s_action,
+                                    const float* __restrict__ s_reward,
+                                    const float* __restrict__ s_done,
+                                    const int8_t* __restrict__ s_stack,
+                                    const float* __restrict__ s_prio,
+                                    const float* __restrict__ s_sp,
+                                    const uint8_t* __restrict__ s_start, int64_t rows,
+                                    float* hs_cs, float* ths_cs, int8_t* action, float* reward,
+                                    float* done, int8_t* stack, float* prio, float* sp,
+                                    uint8_t* start, int64_t M, int cell, int64_t write_index) {
+    const int w = 2 * cell;
+    const int64_t total = rows * w;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / w;
+        const int j = (int)(i % w);
+        const int64_t slot = (write_index + r) % M;
+        hs_cs[slot * w + j] = s_hs[i];
+        ths_cs[slot * w + j] = s_ths[i];
+        if (j == 0) {
+            action[slot] = s_action[r];
+            reward[slot] = s_reward[r];
+            done[slot] = s_done[r];
+            stack[slot] = s_stack[r];
+            prio[slot] = s_prio[r];
+            sp[slot] = s_sp[r];
+            start[slot] = s_start[r];
+        }
+    }
+}
+
+// ======================================================================== priorities
+// generic scatter with numpy's last-occurrence-wins on duplicates
+__global__ void update_priority_kernel(float* __restrict__ priority, int64_t M,
+                                       const int64_t* __restrict__ index,
+                                       const float* __restrict__ p, int64_t n) {
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n;
+         k += (int64_t)gridDim.x * blockDim.x) {
+        int64_t s = index[k];
+        if (s < 0) s += M;  // numpy negative index
+        if (s < 0 || s >= M) continue;
+        bool later = false;
+        for (int64_t k2 = k + 1; k2 < n && !later; ++k2) {
+            int64_t s2 = index[k2];
+            if (s2 < 0) s2 += M;
+            later = (s2 == s);
+        }
+        if (!later) priority[s] = p[k];
+    }
+}
+
+// learner form: flat position k = t*B+b writes slot (seq_index[b]+burn_in+t)%M
+__global__ void update_priority_seq_kernel(float* __restrict__ priority, int64_t M,
+                                           const int64_t* __restrict__ seq_index, int B,
+                                           int burn_in, int L, const float* __restrict__ p) {
+    extern __shared__ int64_t s_seq[];
+    for (int i = threadIdx.x; i < B; i += blockDim.x) s_seq[i] = seq_index[i];
+    __syncthreads();
+    const int64_t n = (int64_t)L * B;
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n;
+         k += (int64_t)gridDim.x * blockDim.x) {
+        const int t = (int)(k / B), b = (int)(k % B);
+        const int64_t slot = (s_seq[b] + burn_in + t) % M;
+        bool later = false;
+        for (int b2 = 0; b2 < B && !later; ++b2) {
+            // smallest t2 >= 0 with (seq[b2]+burn_in+t2) % M == slot; further solutions are
+            // t2 + j*M, all checked while < L (only matters when M < L)
+            for (int64_t t2 = mod_pos(slot - s_seq[b2] - burn_in, M); t2 < L; t2 += M)
+                if (t2 * B + b2 > k) { later = true; break; }
+        }
+        if (!later) priority[slot] = p[k];
+    }
+}
+
+// numpy float32 pairwise sum over a window of `n` priorities starting at `start`
+// (wrap: element i is priority[(start+i) mod M]); association as numpy's add.reduce.
+__device__ float pw_sum(const float* __restrict__ pr, int64_t start, int n, int64_t M,
+                        bool wrap) {
+    auto at = [&](int i) -> float {
+        int64_t s = start + i;
+        if (wrap) s = mod_pos(s, M);
+        return pr[s];
+    };
+    if (n < 8) {
+        float res = 0.f;
+        for (int i = 0; i < n; ++i) res = __fadd_rn(res, at(i));
+        return res;
+    }
+    if (n <= 128) {
+        float r[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) r[j] = at(j);
+        int i = 8;
+        for (; i < n - (n % 8); i += 8) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) r[j] = __fadd_rn(r[j], at(i + j));
+        }
+        float res = __fadd_rn(__fadd_rn(__fadd_rn(r[0], r[1]), __fadd_rn(r[2], r[3])),
+                              __fadd_rn(__fadd_rn(r[4], r[5]), __fadd_rn(r[6], r[7])));
+        for (; i < n; ++i) res = __fadd_rn(res, at(i));
+        return res;
+    }
+    int n2 = n / 2;
+    n2 -= n2 % 8;
+    return __fadd_rn(pw_sum(pr, start, n2, M, wrap), pw_sum(pr, start + n2, n - n2, M, wrap));
+}
+
+__device__ float seq_priority_value(const float* __restrict__ pr, int64_t start, int n,
+                                    int64_t M, bool wrap, float eta, float ometa) {
+    float mx = -INFINITY;
+    for (int i = 0; i < n; ++i) {
+        int64_t s = start + i;
+        if (wrap) s = mod_pos(s, M);
+        mx = fmaxf(mx, pr[s]);
+    }
+    const float mean = __fdiv_rn(pw_sum(pr, start, n, M, wrap), (float)n);
+    return __fadd_rn(__fmul_rn(eta, mx), __fmul_rn(ometa, mean));
+}
+
+// Single CTA.  op = 3*i + j: j=0 own slot (non-wrapping, truncated window), j=1 "previous",
+// j=2 "next" (both write slot idx-i from a wrapping window) -- replay_memory.py:184-213.
+// All values depend only on `priority`/`is_start`, which this kernel does not modify, so the
+// sequential loop of the reference reduces to "last op targeting a slot wins"; the two
+// formulas only differ for slots within T of the array end, so only those need the check.
+__global__ void update_seq_priority_kernel(const float* __restrict__ pr, float* __restrict__ sp,
+                                           const uint8_t* __restrict__ st, int64_t M,
+                                           const int64_t* __restrict__ seq_index, int n, int T,
+                                           float eta, float ometa, int flag,
+                                           int64_t* __restrict__ touched) {
+    const int nops = 3 * n;
+    // phase 1: target slot (hit may be negative: numpy wraps it) or -1
+    for (int op = threadIdx.x; op < nops; op += blockDim.x) {
+        const int i = op / 3, j = op % 3;
+        const int64_t idx = seq_index[i];
+        int64_t hit = -1;
+        bool valid = false;
+        if (j == 0) { hit = idx; valid = true; }
+        else if (flag) {
+            const int dir = j == 1 ? -1 : 1;
+            for (int k = 1; k <= T; ++k) {
+                if (st[mod_pos(idx + (int64_t)dir * k, M)] == 1) { hit = idx - k; valid = true; break; }
+            }
+        }
+        touched[op] = valid ? mod_pos(hit, M) : -1;
+    }
+    __threadfence_block();
+    __syncthreads();
+    // phase 2: value + write unless a later op owns the slot
+    for (int op = threadIdx.x; op < nops; op += blockDim.x) {
+        const int64_t slot = touched[op];
+        if (slot < 0) continue;
+        const int i = op / 3, j = op % 3;
+        if (slot + T > M) {
+            bool later = false;
+            for (int o2 = op + 1; o2 < nops && !later; ++o2) later = (touched[o2] == slot);
+            if (later) continue;
+        }
+        float v;
+        if (j == 0) {
+            const int64_t idx = seq_index[i];
+            const int len = (int)((idx + T <= M) ? T : (M - idx));
+            v = seq_priority_value(pr, idx, len, M, false, eta, ometa);
+        } else {
+            // wrapping window starting at the (possibly negative) hit == slot mod M
+            v = seq_priority_value(pr, slot, T, M, true, eta, ometa);
+        }
+        sp[slot] = v;
+    }
+}
+
+}  // namespace r2d2
+
+using namespace r2d2;
+
+// ======================================================================== C ABI
+extern "C" {
+
+int r2d2_version(void) { return 100; }
+const char* r2d2_last_error(void) { return r2d2::err_buf(); }
+int r2d2_sm_count(void) { return r2d2::sm_count(); }
+
+int r2d2_tree_layout(int64_t M, int max_levels, int64_t* level_sizes, int64_t* level_offsets,
+                     int* n_levels, int64_t* total_nodes) {
+    R2D2_REQUIRE(M > 0, "tree_layout: M must be positive");
+    TreeLayout L = make_layout(M);
+    R2D2_REQUIRE(L.size[L.n_levels - 1] <= FAN, "tree_layout: M=%lld needs more than %d levels",
+                 (long long)M, MAX_LEVELS);
+    R2D2_REQUIRE(max_levels >= L.n_levels, "tree_layout: need room for %d levels", L.n_levels);
+    for (int i = 0; i < L.n_levels; ++i) {
+        if (level_sizes) level_sizes[i] = L.size[i];
+        if (level_offsets) level_offsets[i] = L.off[i];
+    }
+    if (n_levels) *n_levels = L.n_levels;
+    if (total_nodes) *total_nodes = L.total;
+    return R2D2_OK;
+}
+
+int r2d2_tree_build(const float* seq_prio, const uint8_t* is_start, int64_t M, double* nodes,
+                    void* stream) {
+    R2D2_REQUIRE(seq_prio && is_start && nodes && M > 0, "tree_build: null pointer or M<=0");
+    TreeLayout L = make_layout(M);
+    R2D2_REQUIRE(L.size[L.n_levels - 1] <= FAN, "tree_build: M too large");
+    const int sms = sm_count();
+    for (int l = 0; l < L.n_levels; ++l) {
+        const int64_t warps = L.size[l];
+        int64_t blocks = (warps + 7) / 8;  // 8 warps per CTA
+        if (blocks > (int64_t)sms * 16) blocks = (int64_t)sms * 16;
+        tree_build_level<<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(
+            seq_prio, is_start, M, nodes, l, l ? L.off[l - 1] : 0, l ? L.size[l - 1] : M, L.off[l],
+            L.size[l]);
+        R2D2_LAUNCH_OK();
+    }
+    return R2D2_OK;
+}
+
+int r2d2_tree_sample(const float* seq_prio, const uint8_t* is_start, int64_t M,
+                     const double* nodes, const double* u, int B, int64_t* out_slot,
+                     void* stream) {
+    R2D2_REQUIRE(seq_prio && is_start && nodes && u && out_slot, "tree_sample: null pointer");
+    R2D2_REQUIRE(M > 0 && B >= 0, "tree_sample: bad sizes");
+    if (B == 0) return R2D2_OK;
+    TreeLayout L = make_layout(M);
+    const int warps_per_cta = 4;
+    tree_sample_kernel<<<(B + warps_per_cta - 1) / warps_per_cta, warps_per_cta * 32, 0,
+                         as_stream(stream)>>>(seq_prio, is_start, M, nodes, L, u, B, out_slot);
+    R2D2_LAUNCH_OK();
+    return R2D2_OK;
+}
+
+int r2d2_tree_update(const float* seq_prio, const uint8_t* is_start, int64_t M, double* nodes,
+                     const int64_t* slots, int n, void* stream) {
+    R2D2_REQUIRE(seq_prio && is_start && nodes && slots, "tree_update: null pointer");
+    if (n <= 0) return R2D2_OK;
+    TreeLayout L = make_layout(M);
+    tree_update_kernel<<<1, 1024, 0, as_stream(stream)>>>(seq_prio, is_start, M, nodes, L, slots,
+                                                           n);
+    R2D2_LAUNCH_OK();
+    return R2D2_OK;
+}
+
+int r2d2_replay_gather(const uint8_t* state, const float* hs_cs, const float* target_hs_cs,
+                       const int8_t* action, const float* reward, const float* done, int64_t M,
+                       int cell, const int64_t* seq_index, int B, int T, int n_step,
+                       int burn_in, uint8_t* slab, float* hs, float* cs, float* ths, float* tcs,
+                       int64_t* action_out, float* reward_out, float* done_out,
+                       int64_t* index_out, int use_tma, void* stream) {
+    R2D2_REQUIRE(state && hs_cs && target_hs_cs && action && reward && done && seq_index && slab &&
+                     hs && cs && ths && tcs && action_out && reward_out && done_out && index_out,
+                 "replay_gather: null pointer");
+    R2D2_REQUIRE(B > 0 && T > 0 && n_step >= 0 && burn_in >= 0 && burn_in < T && cell > 0 && M > 0,
+                 "replay_gather: bad sizes B=%d T=%d n=%d burn_in=%d", B, T, n_step, burn_in);
+    R2D2_REQUIRE(((uintptr_t)state % 16) == 0 && ((uintptr_t)slab % 16) == 0,
+                 "replay_gather: state/slab must be 16-byte aligned");
+    const int S = T + n_step;
+    if (use_tma) {
+        const int smem = TMA_STAGES * R2D2_FRAME_BYTES;
+        R2D2_CUDA_OK(cudaFuncSetAttribute(gather_rows_tma_kernel,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        int64_t total = (int64_t)B * S;
+        int grid = sm_count();
+        if (grid > total) grid = (int)total;
+        gather_rows_tma_kernel<<<grid, 32, smem, as_stream(stream)>>>(state, M, seq_index, B, S,
+                                                                     slab);
+    } else {
+        gather_rows_kernel<<<dim3(S, B), 256, 0, as_stream(stream)>>>(
+            reinterpret_cast<const uint4*>(state), M, seq_index, S, reinterpret_cast<uint4*>(slab));
+    }
+    R2D2_LAUNCH_OK();
+    const int64_t total = (int64_t)B * cell + (int64_t)(T - burn_in) * B + (int64_t)T * B;
+    gather_small_kernel<<<(unsigned)((total + 255) / 256), 256, 0, as_stream(stream)>>>(
+        hs_cs, target_hs_cs, action, reward, done, M, cell, seq_index, B, T, n_step, burn_in, hs,
+        cs, ths, tcs, action_out, reward_out, done_out, index_out);
+    R2D2_LAUNCH_OK();
+    return R2D2_OK;
+}
+
+int r2d2_slab_to_f32(const uint8_t* slab, int B, int S, int s0, int T, float* out, void* stream) {
+    R2D2_REQUIRE(slab && out && B > 0 && T > 0 && s0 >= 0 && s0 + T <= S, "slab_to_f32: bad args");
+    slab_to_f32_kernel<<<(unsigned)((int64_t)T * B), 256, 0, as_stream(stream)>>>(slab, B, S, s0,
+                                                                                   T, out);
+    R2D2_LAUNCH_OK();
+    return R2D2_OK;
+}
+
+int r2d2_replay_ingest(const uint8_t* src_state, const float* src_hs_cs,
+                       const float* src_target_hs_cs, const int8_t* src_action,
+                       const float* src_reward, const float* src_done,
+                       const int8_t* src_stack_count, const float* src_priority,
+                       const float* src_seq_prio, const uint8_t* src_is_start, int64_t rows,
+                       uint8_t* state, float* hs_cs, float* target_hs_cs, int8_t* action,
+                       float* reward, float* done, int8_t* stack_count, float* priority,
+                       float* seq_prio, uint8_t* is_start, int64_t M, int cell,
+                       int64_t write_index, void* stream) {
+    R2D2_REQUIRE(rows >= 0 && rows <= M, "replay_ingest: rows=%lld exceeds ring size %lld",
+                 (long long)rows, (long long)M);
+    if (rows == 0) return R2D2_OK;
+    R2D2_REQUIRE(src_state && src_hs_cs && src_target_hs_cs && src_action && src_reward &&
+                     src_done && src_stack_count && src_priority && src_seq_prio && src_is_start &&
+                     state && hs_cs && target_hs_cs && action && reward && done && stack_count &&
+                     priority && seq_prio && is_start,
+                 "replay_ingest: null pointer");
+    R2D2_REQUIRE(((uintptr_t)state % 16) == 0 && ((uintptr_t)src_state % 16) == 0,
+                 "replay_ingest: state buffers must be 16-byte aligned");
+    ingest_rows_kernel<<<(unsigned)rows, 256, 0, as_stream(stream)>>>(
+        reinterpret_cast<const uint4*>(src_state), reinterpret_cast<uint4*>(state), M,
+        write_index % M);
+    R2D2_LAUNCH_OK();
+    const int64_t total = rows * 2 * cell;
+    int64_t blocks = (total + 255) / 256;
+    if (blocks > 148 * 32) blocks = 148 * 32;
+    ingest_small_kernel<<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(
+        src_hs_cs, src_target_hs_cs, src_action, src_reward, src_done, src_stack_count,
+        src_priority, src_seq_prio, src_is_start, rows, hs_cs, target_hs_cs, action, reward, done,
+        stack_count, priority, seq_prio, is_start, M, cell, write_index % M);
+    R2D2_LAUNCH_OK();
+    return R2D2_OK;
+}
+
+int r2d2_update_priority(float* priority, int64_t M, const int64_t* index, const float* p,
+                         int64_t n, void* stream) {
+    R2D2_REQUIRE(priority && index && p && M > 0, "update_priority: bad args");
+    if (n <= 0) return R2D2_OK;
+    int64_t blocks = (n + 127) / 128;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    update_priority_kernel<<<(unsigned)blocks, 128, 0, as_stream(stream)>>>(priority, M, index, p,
+                                                                            n);
+    R2D2_LAUNCH_OK();
+    return R2D2_OK;
+}
+
+int r2d2_update_priority_seq(float* priority, int64_t M, const int64_t* seq_index, int B,
+                             int burn_in, int L, const float* p, void* stream) {
+    R2D2_REQUIRE(priority && seq_index && p && M > 0 && B > 0 && L > 0 && burn_in >= 0,
+                 "update_priority_seq: bad args");
+    R2D2_REQUIRE(B <= 4096, "update_priority_seq: B=%d exceeds 4096", B);
+    const int64_t n = (int64_t)L * B;
+    int64_t blocks = (n + 127) / 128;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    update_priority_seq_kernel<<<(unsigned)blocks, 128, B * sizeof(int64_t), as_stream(stream)>>>(
+        priority, M, seq_index, B, burn_in, L, p);
+    R2D2_LAUNCH_OK();
+    return R2D2_OK;
+}
+
+int r2d2_update_sequence_priority(const float* priority, float* seq_prio,
+                                  const uint8_t* is_start, int64_t M, const int64_t* seq_index,
+                                  int n, int T, float eta_f32, float one_minus_eta_f32,
+                                  int update_pre_next, int64_t* touched, void* stream) {
+    R2D2_REQUIRE(priority && seq_prio && is_start && seq_index && touched,
+                 "update_sequence_priority: null pointer");
+    R2D2_REQUIRE(M > 0 && T > 0 && T <= M, "update_sequence_priority: need 0 < T <= M");
+    if (n <= 0) return R2D2_OK;
+    update_seq_priority_kernel<<<1, 1024, 0, as_stream(stream)>>>(
+        priority, seq_prio, is_start, M, seq_index, n, T, eta_f32, one_minus_eta_f32,
+        update_pre_next, touched);
+    R2D2_LAUNCH_OK();
+    return R2D2_OK;
+}
+
+}  // extern "C"

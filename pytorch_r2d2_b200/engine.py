@@ -1,0 +1,135 @@
+"""Thin tensor-level wrappers over the C ABI (one Python function per entry point) and the
+forward/backward compositions shared by ``QNet`` and ``Learner``.  No math happens here:
+every function validates tensors and enqueues CUDA kernels on torch's current stream.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+from .params import FEAT, N_ACTIONS
+
+P = _lib.ptr
+S = _lib.stream_ptr
+
+
+class Weights:
+    """Pointers to the tensors of one network inside its flat buffer (see params.py)."""
+
+    def __init__(self, flat: torch.Tensor, layout):
+        v = lambda k: layout.view(flat, k)  # noqa: E731
+        self.H = layout.cell
+        self.w1, self.b1 = v("vis_layers.0.weight"), v("vis_layers.0.bias")
+        self.w2, self.b2 = v("vis_layers.2.weight"), v("vis_layers.2.bias")
+        self.w3, self.b3 = v("vis_layers.4.weight"), v("vis_layers.4.bias")
+        self.w_ih, self.w_hh = v("lstm.weight_ih"), v("lstm.weight_hh")
+        self.b_ih, self.b_hh = v("lstm.bias_ih"), v("lstm.bias_hh")
+        H = self.H
+        o, n = layout.span("val.0.weight", "adv.0.weight")
+        self.head_w1 = flat[o:o + n].view(2 * H, H)
+        o, n = layout.span("val.0.bias", "adv.0.bias")
+        self.head_b1 = flat[o:o + n]
+        o, n = layout.span("val.2.weight", "adv.2.weight")
+        self.head_w2 = flat[o:o + n].view(1 + N_ACTIONS, H)
+        o, n = layout.span("val.2.bias", "adv.2.bias")
+        self.head_b2 = flat[o:o + n]
+
+
+# ---------------------------------------------------------------------------- forward ops
+def torso_fwd_u8(slab, s0, nt, w: Weights, a1, a2, feat):
+    B, Sfr = slab.shape[0], slab.shape[1]
+    _lib.call("r2d2_torso_fwd_u8", P(slab, "u8"), B, Sfr, s0, nt, P(w.w1), P(w.b1), P(w.w2), P(w.b2),
+              P(w.w3), P(w.b3), P(a1, "f32"), P(a2, "f32"), P(feat, "f32"), S())
+
+
+def torso_fwd_f32(frames, w: Weights, a1, a2, feat):
+    R = frames.shape[0]
+    _lib.call("r2d2_torso_fwd_f32", P(frames, "f32"), R, P(w.w1), P(w.b1), P(w.w2), P(w.b2), P(w.w3),
+              P(w.b3), P(a1, "f32"), P(a2, "f32"), P(feat, "f32"), S())
+
+
+def linear_fwd(x, w, b1, b2, y, relu=False):
+    M, K = x.shape
+    N = w.shape[0]
+    assert w.shape[1] == K and y.shape == (M, N)
+    _lib.call("r2d2_linear_fwd", P(x, "f32"), P(w, "f32"), P(b1, "f32", True), P(b2, "f32", True),
+              P(y, "f32"), M, N, K, int(relu), S())
+
+
+def lstm_seq_fwd(xproj, w_hh, hs_ext, cs_ext, gates, T, B, H):
+    _lib.call("r2d2_lstm_seq_fwd", P(xproj, "f32"), P(w_hh, "f32"), P(hs_ext, "f32"), P(cs_ext, "f32"),
+              P(gates, "f32", True), T, B, H, S())
+
+
+def head_fwd(hs, w: Weights, hid, q):
+    M, H = hs.shape
+    _lib.call("r2d2_head_fwd", P(hs, "f32"), P(w.head_w1), P(w.head_b1), P(w.head_w2), P(w.head_b2),
+              P(hid, "f32"), P(q, "f32"), M, H, S())
+
+
+def td_target(q_all, qn_on, qn_tg, action, reward, done, gamma_n, out, *, rescale=False,
+              rescale_eps=1e-3, prio_eps=1e-6, alpha=0.6, next_action_override=None):
+    n = q_all.shape[0]
+    _lib.call("r2d2_td_target", P(q_all, "f32"), P(qn_on, "f32"), P(qn_tg, "f32"), P(action, "i64"),
+              P(reward, "f32"), P(done, "f32"), n, float(gamma_n), int(rescale), float(rescale_eps),
+              float(prio_eps), float(alpha), P(next_action_override, "i64", True),
+              P(out["next_action"], "i64"), P(out["y"], "f32"), P(out["delta"], "f32"),
+              P(out["dq"], "f32"), P(out["prio"], "f32"), P(out["loss"], "f32"), S())
+
+
+# ---------------------------------------------------------------------------- backward ops
+def head_bwd(dq, hid, w: Weights, dhid, dw2, db2):
+    M, H2 = hid.shape
+    _lib.call("r2d2_head_bwd", P(dq, "f32"), P(hid, "f32"), P(w.head_w2), P(dhid, "f32"), P(dw2, "f32"),
+              P(db2, "f32"), M, H2 // 2, S())
+
+
+def linear_dgrad(dy, w, dx, accumulate=False):
+    M, N = dy.shape
+    K = w.shape[1]
+    _lib.call("r2d2_linear_dgrad", P(dy, "f32"), P(w, "f32"), P(dx, "f32"), M, N, K, int(accumulate), S())
+
+
+def linear_wgrad_scratch_bytes(M, N, K):
+    return int(_lib.load().r2d2_linear_wgrad_scratch_bytes(M, N, K))
+
+
+def linear_wgrad(dy, x, dw, db, scratch):
+    M, N = dy.shape
+    K = x.shape[1]
+    _lib.call("r2d2_linear_wgrad", P(dy, "f32"), P(x, "f32"), P(dw, "f32"), P(db, "f32", True), M, N, K,
+              P(scratch, None, True), S())
+
+
+def lstm_seq_bwd(dhs, w_hh, gates, cs_ext, dgates, dc_work, T, B, H):
+    _lib.call("r2d2_lstm_seq_bwd", P(dhs, "f32"), P(w_hh, "f32"), P(gates, "f32"), P(cs_ext, "f32"),
+              P(dgates, "f32"), P(dc_work, "f32"), T, B, H, S())
+
+
+def torso_bwd_scratch_bytes(R):
+    return int(_lib.load().r2d2_torso_bwd_scratch_bytes(R))
+
+
+def torso_bwd_u8(slab, s0, nt, a1, a2, feat, dfeat, w: Weights, g: Weights, scratch):
+    B, Sfr = slab.shape[0], slab.shape[1]
+    _lib.call("r2d2_torso_bwd_u8", P(slab, "u8"), B, Sfr, s0, nt, P(a1, "f32"), P(a2, "f32"),
+              P(feat, "f32"), P(dfeat, "f32"), P(w.w2), P(w.w3), P(g.w1), P(g.b1), P(g.w2), P(g.b2),
+              P(g.w3), P(g.b3), P(scratch), S())
+
+
+def torso_bwd_f32(frames, a1, a2, feat, dfeat, w: Weights, g: Weights, scratch):
+    R = frames.shape[0]
+    _lib.call("r2d2_torso_bwd_f32", P(frames, "f32"), R, P(a1, "f32"), P(a2, "f32"), P(feat, "f32"),
+              P(dfeat, "f32"), P(w.w2), P(w.w3), P(g.w1), P(g.b1), P(g.w2), P(g.b2), P(g.w3), P(g.b3),
+              P(scratch), S())
+
+
+def rmsprop_centered(param, grad, sq, ga, lr, alpha, eps, grad_scale=1.0):
+    _lib.call("r2d2_rmsprop_centered", P(param, "f32"), P(grad, "f32"), P(sq, "f32"), P(ga, "f32"),
+              param.numel(), float(lr), float(alpha), float(eps), float(grad_scale), S())
+
+
+# ---------------------------------------------------------------------------- compositions
+def alloc_torso(R, device):
+    return (torch.empty((R, 32, 20, 20), device=device), torch.empty((R, 32, 9, 9), device=device),
+            torch.empty((R, FEAT), device=device))

@@ -1,0 +1,254 @@
+"""``Learner`` behind the reference's interface (/root/reference learner.py:18-124).
+
+``train()`` is the hot path (learner.py:68-104): PER sample -> burn-in + learn + double-Q
+unrolls of the online net, burn-in + evaluation of the target net -> n-step double-Q target,
+TD error, loss -> backward -> centered RMSprop -> per-step and per-sequence priority update.
+Every stage is a CUDA kernel enqueued through the C ABI on torch's current stream; nothing
+crosses to the host inside a step except the B float64 uniforms going in.
+
+Same attribute names and defaults as the reference (``batch_size=8``, 10+10 steps, n=3, ...);
+they are plain attributes and can be changed after construction, exactly like tests of the
+reference have to do.  Extra, opt-in (defaults reproduce the reference): ``cell_size``,
+``rescale`` (invertible value rescaling, absent from the reference), ``world_size``/``rank`` for
+the data-parallel gradient allreduce.
+"""
+from __future__ import annotations
+
+import os
+from copy import deepcopy
+
+import numpy as np
+import torch
+
+from . import engine
+from .engine import Weights
+from .model import QNet
+from .params import FEAT, N_ACTIONS
+from .replay_memory import ReplayMemory
+
+
+def learner_process(n_actors, shared_dict):
+    Learner(n_actors, shared_dict).run()
+
+
+class FusedCenteredRMSprop:
+    """torch.optim.RMSprop(lr, alpha, eps, centered=True) (learner.py:51) as ONE kernel over the
+    flat parameter buffer."""
+
+    def __init__(self, net: QNet, lr=0.00025 / 4.0, alpha=0.95, eps=1.5e-7):
+        self.net, self.lr, self.alpha, self.eps = net, lr, alpha, eps
+        flat = net.flat_parameters()
+        self.grad = torch.zeros_like(flat)
+        self.square_avg = torch.zeros_like(flat)
+        self.grad_avg = torch.zeros_like(flat)
+        self.grad_scale = 1.0
+
+    def zero_grad(self):
+        self.grad.zero_()
+
+    def step(self):
+        engine.rmsprop_centered(self.net.flat_parameters(), self.grad, self.square_avg,
+                                self.grad_avg, self.lr, self.alpha, self.eps, self.grad_scale)
+
+    def state_dict(self):
+        return {"square_avg": self.square_avg.clone(), "grad_avg": self.grad_avg.clone(),
+                "lr": self.lr, "alpha": self.alpha, "eps": self.eps}
+
+    def load_state_dict(self, sd):
+        self.square_avg.copy_(sd["square_avg"])
+        self.grad_avg.copy_(sd["grad_avg"])
+        self.lr, self.alpha, self.eps = sd["lr"], sd["alpha"], sd["eps"]
+
+
+class Learner:
+    def __init__(self, n_actors, shared_dict, device="cuda:0", *, cell_size=256, memory_size=500000,
+                 rescale=False, process_group=None):
+        # params (learner.py:20-28)
+        self.gamma = 0.99
+        self.alpha = 0.6
+        self.bootstrap_steps = 3
+        self.initial_exploration = 50000
+        self.priority_epsilon = 1e-6
+        self.device = device
+        self.n_epochs = 0
+        self.n_actors = n_actors
+        self.rescale = rescale
+        self.rescale_eps = 1e-3
+        self.memory_path = os.path.join("./", "logs", "memory")
+        # memory (learner.py:34-41)
+        self.burn_in_length = 10
+        self.learning_length = 10
+        self.sequence_length = self.burn_in_length + self.learning_length
+        self.memory_size = memory_size
+        self.batch_size = 8
+        self.memory_load_interval = 20
+        self.cell_size = cell_size
+        self.replay_memory = ReplayMemory(self.memory_size, self.batch_size, self.bootstrap_steps,
+                                          cell_size=cell_size, device=device)
+        # net (learner.py:44-51)
+        self.shared_dict = shared_dict
+        self.net_save_interval = 100
+        self.target_update_interval = 1000
+        self.net = QNet(self.device, cell_size).to(self.device)
+        self.target_net = QNet(self.device, cell_size).to(self.device)
+        self.target_net.load_state_dict(self.net.state_dict())
+        self.save_model()
+        self.optim = FusedCenteredRMSprop(self.net)
+        self.process_group = process_group
+        self._ws = None
+        self.last = None  # tensors of the last step (q, y, delta, loss, ...) for inspection
+
+    # ------------------------------------------------------------------ control loop
+    def run(self):
+        while True:
+            if self.replay_memory.size > self.initial_exploration:
+                self.train()
+                self.n_epochs += 1
+                if self.n_epochs % 100 == 0:
+                    print("trained", self.n_epochs, "epochs")
+                self.interval()
+            else:
+                self._ingest()
+
+    def _ingest(self):
+        for i in range(self.n_actors):
+            try:
+                self.replay_memory.load(self.memory_path, i)
+            except Exception:  # the reference ignores hand-off errors (learner.py:63-66)
+                pass
+
+    def interval(self):
+        if self.n_epochs % self.target_update_interval == 0:
+            self.sync_target()
+        if self.n_epochs % self.net_save_interval == 0:
+            self.save_model()
+        if self.n_epochs % self.memory_load_interval == 0:
+            self._ingest()
+        if self.n_epochs % 10000 == 0:
+            os.makedirs("save", exist_ok=True)
+            torch.save(self.net.cpu().state_dict(), "save/" + str(self.n_epochs) + "_save.pt")
+
+    def sync_target(self):
+        """target_net.load_state_dict(net.state_dict()) (learner.py:108) = one D2D copy."""
+        self.target_net.flat_parameters().copy_(self.net.flat_parameters())
+
+    def save_model(self):
+        self.shared_dict["net_state"] = self.net.cpu().state_dict()
+        self.shared_dict["target_net_state"] = self.target_net.cpu().state_dict()
+
+    # ------------------------------------------------------------------ workspace
+    def _workspace(self):
+        B, BI, L, n, H = (self.batch_size, self.burn_in_length, self.learning_length,
+                          self.bootstrap_steps, self.cell_size)
+        key = (B, BI, L, n, H)
+        if self._ws is not None and self._ws["key"] == key:
+            return self._ws
+        dev = self.net.flat_parameters().device
+        T, S = BI + L, BI + L + n
+        f = lambda *shape: torch.empty(shape, dtype=torch.float32, device=dev)  # noqa: E731
+        M = L * B
+        ws = dict(key=key)
+        ws["a1_on"], ws["a2_on"], ws["feat_on"] = f(S * B, 32, 20, 20), f(S * B, 32, 9, 9), f(S * B, FEAT)
+        ws["a1_tg"], ws["a2_tg"], ws["feat_tg"] = f(T * B, 32, 20, 20), f(T * B, 32, 9, 9), f(T * B, FEAT)
+        ws["xp_on"], ws["xp_tg"] = f(S * B, 4 * H), f(T * B, 4 * H)
+        ws["hs_on"], ws["cs_on"] = f(T + 1, B, H), f(T + 1, B, H)
+        ws["hs_dq"], ws["cs_dq"] = f(L + 1, B, H), f(L + 1, B, H)
+        ws["hs_tg"], ws["cs_tg"] = f(T + 1, B, H), f(T + 1, B, H)
+        ws["gates"] = f(T, B, 4 * H)
+        ws["hid_on"], ws["hid_tmp"] = f(M, 2 * H), f(M, 2 * H)
+        ws["q_all"], ws["qn_on"], ws["qn_tg"] = f(M, N_ACTIONS), f(M, N_ACTIONS), f(M, N_ACTIONS)
+        ws["td"] = dict(next_action=torch.empty(M, dtype=torch.int64, device=dev), y=f(M), delta=f(M),
+                        dq=f(M, N_ACTIONS), prio=f(M), loss=f(1))
+        ws["dhid"], ws["dhs"], ws["dgates"] = f(M, 2 * H), f(M, H), f(M, 4 * H)
+        ws["dc_work"], ws["dfeat"] = f(B, H), f(M, FEAT)
+        nbytes = max(engine.linear_wgrad_scratch_bytes(M, 2 * H, H),
+                     engine.linear_wgrad_scratch_bytes(M, 4 * H, H),
+                     engine.linear_wgrad_scratch_bytes(M, 4 * H, FEAT),
+                     engine.torso_bwd_scratch_bytes(M))
+        ws["scratch"] = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        self._ws = ws
+        return ws
+
+    # ------------------------------------------------------------------ the hot path
+    def train(self, u=None, seq_index=None, next_action_override=None):
+        """One learner step (learner.py:68-104).  `u` optionally supplies the B float64
+        uniforms (default: drawn from torch's global CPU generator like the reference's
+        multinomial); `seq_index` bypasses the draw (parity tests)."""
+        rm = self.replay_memory
+        B, BI, L, n, H = (self.batch_size, self.burn_in_length, self.learning_length,
+                          self.bootstrap_steps, self.cell_size)
+        T = BI + L
+        rm.batch_size, rm.n_step = B, n
+        rm.burn_in_length, rm.learning_length, rm.sequence_length = BI, L, T
+        ws = self._workspace()
+        batch = rm.sample_slab(u=u, seq_index=seq_index)
+        slab = batch["slab"]
+        w, wt = self.net._weights(), self.target_net._weights()
+        g = Weights(self.optim.grad, self.net.layout)
+        M = L * B
+
+        # ---- conv torso + input projection: online on all T+n frames, target on frames n..T+n
+        engine.torso_fwd_u8(slab, 0, T + n, w, ws["a1_on"], ws["a2_on"], ws["feat_on"])
+        engine.torso_fwd_u8(slab, n, T, wt, ws["a1_tg"], ws["a2_tg"], ws["feat_tg"])
+        engine.linear_fwd(ws["feat_on"], w.w_ih, w.b_ih, w.b_hh, ws["xp_on"])
+        engine.linear_fwd(ws["feat_tg"], wt.w_ih, wt.b_ih, wt.b_hh, ws["xp_tg"])
+
+        # ---- online net: burn-in + learn over state[0:T] (hidden state carries through)
+        ws["hs_on"][0].copy_(batch["hs"])
+        ws["cs_on"][0].copy_(batch["cs"])
+        engine.lstm_seq_fwd(ws["xp_on"], w.w_hh, ws["hs_on"], ws["cs_on"], ws["gates"], T, B, H)
+        # ---- online net again on next_state[BI:T] = frames BI+n.., starting from the state left
+        #      after state[T-1] (the reference never resets it: learner.py:86,91)
+        ws["hs_dq"][0].copy_(ws["hs_on"][T])
+        ws["cs_dq"][0].copy_(ws["cs_on"][T])
+        engine.lstm_seq_fwd(ws["xp_on"][(BI + n) * B:], w.w_hh, ws["hs_dq"], ws["cs_dq"], None, L, B, H)
+        # ---- target net: burn-in on next_state[0:BI], then next_state[BI:T]
+        ws["hs_tg"][0].copy_(batch["target_hs"])
+        ws["cs_tg"][0].copy_(batch["target_cs"])
+        engine.lstm_seq_fwd(ws["xp_tg"], wt.w_hh, ws["hs_tg"], ws["cs_tg"], None, T, B, H)
+
+        # ---- dueling heads on the learn window only
+        hs_learn = ws["hs_on"][1 + BI:].reshape(M, H)
+        engine.head_fwd(hs_learn, w, ws["hid_on"], ws["q_all"])
+        engine.head_fwd(ws["hs_dq"][1:].reshape(M, H), w, ws["hid_tmp"], ws["qn_on"])
+        engine.head_fwd(ws["hs_tg"][1 + BI:].reshape(M, H), wt, ws["hid_tmp"], ws["qn_tg"])
+
+        # ---- n-step double-Q target, TD error, loss gradient, per-step priorities
+        td = ws["td"]
+        engine.td_target(ws["q_all"], ws["qn_on"], ws["qn_tg"], batch["action"].reshape(M),
+                         batch["reward"].reshape(M), batch["done"].reshape(M),
+                         self.gamma ** self.bootstrap_steps, td, rescale=self.rescale,
+                         rescale_eps=self.rescale_eps, prio_eps=self.priority_epsilon,
+                         alpha=self.alpha, next_action_override=next_action_override)
+
+        # ---- backward (learn window only; BPTT truncated at the burn-in boundary)
+        scratch = ws["scratch"]
+        engine.head_bwd(td["dq"], ws["hid_on"], w, ws["dhid"], g.head_w2, g.head_b2)
+        engine.linear_wgrad(ws["dhid"], hs_learn, g.head_w1, g.head_b1, scratch)
+        engine.linear_dgrad(ws["dhid"], w.head_w1, ws["dhs"])
+        engine.lstm_seq_bwd(ws["dhs"], w.w_hh, ws["gates"][BI:], ws["cs_on"][BI:], ws["dgates"],
+                            ws["dc_work"], L, B, H)
+        engine.linear_wgrad(ws["dgates"], ws["hs_on"][BI:BI + L].reshape(M, H), g.w_hh, g.b_hh, scratch)
+        g.b_ih.copy_(g.b_hh)
+        feat_l = ws["feat_on"][BI * B: T * B]
+        engine.linear_wgrad(ws["dgates"], feat_l, g.w_ih, None, scratch)
+        engine.linear_dgrad(ws["dgates"], w.w_ih, ws["dfeat"])
+        engine.torso_bwd_u8(slab, BI, L, ws["a1_on"][BI * B: T * B], ws["a2_on"][BI * B: T * B], feat_l,
+                            ws["dfeat"], w, g, scratch)
+
+        # ---- optimiser (data-parallel: sum gradients over ranks, scale by 1/world in K10)
+        if self.process_group is not None or (torch.distributed.is_available()
+                                              and torch.distributed.is_initialized()
+                                              and torch.distributed.get_world_size() > 1):
+            torch.distributed.all_reduce(self.optim.grad, group=self.process_group)
+            self.optim.grad_scale = 1.0 / torch.distributed.get_world_size(self.process_group)
+        self.optim.step()
+
+        # ---- priorities (learner.py:102-104)
+        rm.update_priority_learn_window(batch["seq_index"], td["prio"])
+        rm.update_sequence_priority(batch["seq_index"], True)
+        self.last = dict(loss=td["loss"], q_all=ws["q_all"], q_next_online=ws["qn_on"],
+                         q_next_target=ws["qn_tg"], next_action=td["next_action"], y=td["y"],
+                         delta=td["delta"], priority=td["prio"], seq_index=batch["seq_index"],
+                         index=batch["index"])
+        return td["loss"]

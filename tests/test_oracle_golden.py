@@ -1,0 +1,158 @@
+"""CPU: the oracle restatement against the golden vectors produced by the unmodified
+reference (oracle/make_golden.py)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import net_oracle as NO
+from oracle import replay_oracle as RO
+from util import make_oracle_replay, rel_err
+
+
+@pytest.fixture(scope="module")
+def gold(golden_dir):
+    return {n: np.load(os.path.join(golden_dir, n + ".npz")) for n in ("sampling", "priority", "network")}
+
+
+def _case_names(npz):
+    return sorted({k.split("/")[0] for k in npz.files})
+
+
+def sampling_inputs(g, name):
+    N, stride = int(g[f"{name}/N"]), int(g[f"{name}/stride"])
+    rng = np.random.RandomState(int(g[f"{name}/seed_prio"]))
+    if int(g[f"{name}/exact"]):
+        p = rng.randint(1, 4, N).astype(np.int64)
+        diff, i = int(2 * N - p.sum()), 0
+        while diff != 0:
+            step = 1 if diff > 0 else -1
+            if 1 <= p[i] + step <= 3:
+                p[i] += step
+                diff -= step
+            i = (i + 1) % N
+        p = p.astype(np.float32)
+    else:
+        p = ((rng.rand(N).astype(np.float32) + np.float32(1e-3)) ** np.float32(0.6)).astype(np.float32)
+    leaves = np.zeros(N * stride, np.float32)
+    mask = np.zeros(N * stride, np.uint8)
+    leaves[np.arange(N) * stride] = p
+    mask[np.arange(N) * stride] = 1
+    return leaves, mask
+
+
+@pytest.mark.parametrize("name", ["n37", "n1000", "n100000", "x1024", "x65536"])
+def test_reference_cdf_restatement(gold, name):
+    g = gold["sampling"]
+    leaves, mask = sampling_inputs(g, name)
+    idx = RO.ref_sample_indices(leaves, mask, g[f"{name}/u"])
+    assert np.array_equal(idx, g[f"{name}/seq_index"])
+
+
+@pytest.mark.parametrize("name", ["n37", "n1000", "x1024", "x65536"])
+def test_tree_oracle_matches_reference(gold, name):
+    g = gold["sampling"]
+    leaves, mask = sampling_inputs(g, name)
+    tree = RO.SumTree(RO.masked_leaves(leaves, mask))
+    idx = tree.sample(g[f"{name}/u"][:256])
+    want = g[f"{name}/seq_index"][:256]
+    assert int((idx == want).sum()) == len(want)
+    assert np.all(mask[idx] == 1)
+
+
+def test_tree_update_equals_rebuild():
+    rng = np.random.RandomState(0)
+    leaves = rng.rand(5000).astype(np.float32)
+    leaves[rng.rand(5000) < 0.5] = 0
+    t = RO.SumTree(leaves)
+    for s in rng.randint(0, 5000, 50):
+        t.update_leaf(int(s), rng.rand())
+    t2 = RO.SumTree(t.leaves.copy())
+    for a, b in zip(t.levels, t2.levels):
+        assert np.array_equal(a, b)
+    assert t.root == t2.root
+
+
+def test_zero_weight_never_drawn():
+    leaves = np.zeros(1000, np.float32)
+    leaves[[3, 500, 999]] = [1.0, 2.0, 1e-6]
+    t = RO.SumTree(leaves)
+    u = np.concatenate([np.random.RandomState(1).rand(500), [0.0, 1.0 - 2 ** -53]])
+    idx = t.sample(u)
+    assert set(idx.tolist()) <= {3, 500, 999}
+
+
+@pytest.mark.parametrize("name", ["regular", "irregular", "near_end", "noflag", "dense"])
+def test_priority_update_restatement(gold, name):
+    g = gold["priority"]
+    M, T = int(g[f"{name}/M"]), int(g[f"{name}/T"])
+    pr = g[f"{name}/priority0"].copy()
+    RO.update_priority(pr, g[f"{name}/scatter_idx"], g[f"{name}/scatter_val"])
+    assert np.array_equal(pr, g[f"{name}/priority1"])
+    sp = g[f"{name}/seqprio0"].copy()
+    mask = np.zeros(M, np.uint8)
+    mask[g[f"{name}/starts"]] = 1
+    RO.update_sequence_priority(pr, sp, mask, g[f"{name}/seq_index"], T, 0.9, bool(g[f"{name}/flag"]))
+    assert np.array_equal(sp.view(np.uint32), g[f"{name}/seqprio1"].view(np.uint32))
+
+
+def test_pairwise_sum_matches_numpy():
+    rng = np.random.RandomState(5)
+    for n in list(range(1, 40)) + [80, 85, 128, 129, 300]:
+        a = rng.rand(n).astype(np.float32)
+        assert RO.np_pairwise_sum_f32(a).view(np.uint32) == np.sum(a).view(np.uint32)
+
+
+def test_forward_restatement(gold):
+    g = gold["network"]
+    p = NO.init_params(0, 256)
+    rng = np.random.RandomState(int(g["fwd/seed_x"]))
+    x5 = torch.from_numpy(rng.randint(0, 256, (3, 2, 4, 84, 84)).astype(np.float32) / np.float32(255))
+    x4 = x5[0].clone()
+    h0 = torch.from_numpy((rng.randn(2, 256) * 0.1).astype(np.float32))
+    c0 = torch.from_numpy((rng.randn(2, 256) * 0.1).astype(np.float32))
+    with torch.no_grad():
+        q5, hs5, cs5, _ = NO.qnet_forward(p, x5, None, None)
+        q4, hs4, cs4, st = NO.qnet_forward(p, x4, h0, c0)
+        q4b, _, cs4b, _ = NO.qnet_forward(p, x4, *st)
+    assert rel_err(q5, g["fwd/q5"]) < 1e-5 and rel_err(hs5, g["fwd/hs5"]) < 1e-5
+    assert rel_err(q4, g["fwd/q4"]) < 1e-5 and rel_err(cs4, g["fwd/cs4"]) < 1e-5
+    assert rel_err(q4b, g["fwd/q4b"]) < 1e-5 and rel_err(cs4b, g["fwd/cs4b"]) < 1e-5
+
+
+def test_train_step_restatement(gold):
+    g = gold["network"]
+    M, B, BI, LN, NS, H = [int(v) for v in g["train/config"]]
+    rep, _ = make_oracle_replay(M, H, NS, BI, LN, seed=21)
+    p = NO.init_params(0, H)
+    pt = {k: v.clone() for k, v in p.items()}
+    si = rep.sample_indices(g["train/u"])
+    assert np.array_equal(si, g["train/seq_index"])
+    gb = rep.gather(si)
+    res = NO.train_step(p, pt, NO.to_torch_batch(gb["batch"]), burn_in=BI, n_step=NS)
+    assert rel_err(res["q_all"], g["train/q_all"]) < 1e-5
+    assert rel_err(res["q_next_online"], g["train/q_next_online"]) < 1e-5
+    assert rel_err(res["q_next_target"], g["train/q_next_target"]) < 1e-5
+    for k in NO.PARAM_KEYS:
+        f = res["grads"][k].reshape(-1)
+        step = max(1, f.numel() // 2048)
+        mine = f[::step][:2048]
+        assert float((mine - torch.from_numpy(g[f"train/grad_sub/{k}"])).abs().max()
+                     / float(g[f"train/grad_absmax/{k}"])) < 1e-5, k
+    sq = {k: torch.zeros_like(v) for k, v in p.items()}
+    ga = {k: torch.zeros_like(v) for k, v in p.items()}
+    for k in NO.PARAM_KEYS:
+        NO.rmsprop_centered(p[k], res["grads"][k], sq[k], ga[k])
+        f = p[k].reshape(-1)
+        step = max(1, f.numel() // 2048)
+        assert rel_err(f[::step][:2048], g[f"train/param1_sub/{k}"]) < 1e-5, k
+    rep.update_priority(gb["index"][BI:].reshape(-1), res["priority"])
+    rep.update_sequence_priority(si, True)
+    assert np.allclose(rep.memory["priority"], g["train/priority_after"], rtol=1e-4, atol=1e-7)
+    assert np.allclose(rep.memory["sequence_priority"], g["train/seqprio_after"], rtol=1e-4, atol=1e-7)
+
+
+def test_value_rescale_inverse():
+    x = torch.linspace(-50, 50, 1001)
+    assert torch.allclose(NO.value_rescale_inv(NO.value_rescale(x)), x, atol=2e-3)
