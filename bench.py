@@ -1,0 +1,418 @@
+#!/usr/bin/env python
+"""Benchmark of the R2D2 learner hot path (BASELINE.json metric: learner sequences/sec at
+B=64, T=80 = burn-in 40 + learn 40, n=5, LSTM 512, synthetic 84x84 frames).
+
+    python bench.py --gpus N --steps K --warmup W            # this repo, one rank per GPU
+    python bench.py --impl reference --steps K --warmup W    # the reference path on host cores
+
+One "step" = one full ``Learner.train()``: PER draw -> slab gather -> conv torso + LSTM burn-in /
+learn / double-Q unrolls of both nets -> n-step double-Q target + TD + loss -> backward ->
+centered RMSprop -> per-step + per-sequence priority update + tree refresh.  Nothing is
+skipped or cached.  Rank 0 prints ONE JSON line.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FRAME = 4 * 84 * 84
+FEAT = 1568
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--burn-in", type=int, default=40)
+    ap.add_argument("--learn", type=int, default=40)
+    ap.add_argument("--n-step", type=int, default=5)
+    ap.add_argument("--cell", type=int, default=512)
+    ap.add_argument("--memory-size", type=int, default=500000)
+    ap.add_argument("--ingest-rows", type=int, default=640,
+                    help="e2e leg: fresh transitions uploaded from pinned host memory per step")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--tma-gather", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._pump, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = float(r[1])
+            except (ValueError, IndexError):
+                continue
+            for n, v in zip(names, r[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------ work model
+def work_model(B, BI, L, n, H):
+    """Algorithmic FLOPs per launch of the named kernels."""
+    T, S = BI + L, BI + L + n
+    M = L * B
+    conv = {"conv1": 6553600, "conv2": 2654208, "conv3": 903168}
+    per_step_frames_fwd = (S + T) * B
+    lin_fwd = 2 * ((S * B) * 4 * H * FEAT + (T * B) * 4 * H * FEAT + 3 * M * 2 * H * H)
+    lin_dgrad = 2 * (M * 2 * H * H + M * 4 * H * FEAT)
+    lin_wgrad = 2 * (M * 2 * H * H + M * 4 * H * H + M * 4 * H * FEAT)
+    steps_fwd = T + L + T
+    w = {
+        "conv1_fwd": (conv["conv1"] * per_step_frames_fwd, 2),
+        "conv2_fwd": (conv["conv2"] * per_step_frames_fwd, 2),
+        "conv3_fwd": (conv["conv3"] * per_step_frames_fwd, 2),
+        "linear_fwd": (lin_fwd, 5),
+        "linear_dgrad": (lin_dgrad, 2),
+        "linear_wgrad": (lin_wgrad, 3),
+        "lstm_step_fwd_kernel": (2 * B * 4 * H * H * steps_fwd, steps_fwd),
+        "lstm_step_bwd_kernel": (2 * B * 4 * H * H * (L - 1), L),
+        "conv1_wgrad": (conv["conv1"] * M, 1), "conv2_wgrad": (conv["conv2"] * M, 1),
+        "conv3_wgrad": (conv["conv3"] * M, 1),
+        "conv_dgrad_kernel<4,20,9,2>": (conv["conv2"] * M, 1),
+        "conv_dgrad_kernel<3,9,7,1>": (conv["conv3"] * M, 1),
+    }
+    total = (S + T) * B * (sum(conv.values()) + 2 * 4 * H * FEAT) + steps_fwd * B * 2 * 4 * H * H \
+        + 3 * M * 2 * (2 * H * H + 7 * H) \
+        + M * (2 * (sum(conv.values()) + 2 * 4 * H * FEAT + 2 * 4 * H * H + 2 * (2 * H * H + 7 * H))
+               - conv["conv1"])
+    bytes_model = {
+        "gather_rows_kernel": 2 * B * S * FRAME, "gather_rows_tma_kernel": 2 * B * S * FRAME,
+        "rmsprop_kernel": 28,  # x n_params, filled by the caller
+    }
+    return w, total, bytes_model
+
+
+# ------------------------------------------------------------------------------ reference arm
+def cpu_reference_step_factory(args, M=20000):
+    """The reference path on host cores: the oracle port (oracle/) of ReplayMemory.sample +
+    Learner.train (itself pinned to the unmodified reference in oracle/make_golden.py), at the
+    bench's full shapes.  /root/reference does not exist on the GPU box and the reference has no
+    installable package, hence kind='port'."""
+    import numpy as np
+    import torch
+    from oracle import net_oracle as NO
+    from oracle import replay_oracle as RO
+
+    torch.set_num_threads(os.cpu_count() or 1)
+    B, BI, L, n, H = args.batch, args.burn_in, args.learn, args.n_step, args.cell
+    rep = RO.ReplayOracle(M, H, n, BI, L)
+    RO.synth_fill(rep, seed=1, stride=40)
+    p = NO.init_params(0, H)
+    pt = {k: v.clone() for k, v in p.items()}
+    sq = {k: torch.zeros_like(v) for k, v in p.items()}
+    ga = {k: torch.zeros_like(v) for k, v in p.items()}
+    state = {"i": 0}
+
+    def step():
+        torch.manual_seed(1000 + state["i"])
+        state["i"] += 1
+        u = torch.rand(B, dtype=torch.float64).numpy()
+        si = rep.sample_indices(u)
+        g = rep.gather(si)
+        res = NO.train_step(p, pt, NO.to_torch_batch(g["batch"]), burn_in=BI, n_step=n)
+        for k in NO.PARAM_KEYS:
+            NO.rmsprop_centered(p[k], res["grads"][k], sq[k], ga[k])
+        rep.update_priority(g["index"][BI:].reshape(-1), res["priority"])
+        rep.update_sequence_priority(si, True)
+        return float(res["loss"])
+
+    return step
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    step = cpu_reference_step_factory(args)
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = (time.perf_counter() - t0) / max(args.steps, 1)
+    B = args.batch
+    val = B / dt
+    cores = os.cpu_count() or 1
+    line = {
+        "impl": "reference", "metric": "learner_sequences_per_sec", "value": val, "unit": "seq/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": workload_config(args, extra={"replay_slots": 20000}),
+        "cpu_baseline": {"value": val, "unit": "seq/s", "cores": cores, "kind": "port",
+                         "sample": f"{args.steps} full steps (B={B}) after {args.warmup} warm-up, "
+                                   f"torch CPU fp32 with {cores} threads, 20000-slot replay"},
+        "e2e": {"value": val, "unit": "seq/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, extra=None):
+    c = {"workload": "configs[1]: synthetic Atari 84x84 R2D2 learner step "
+                     "(PER sample -> LSTM unroll -> n-step TD -> priority update)",
+         "batch_per_gpu": args.batch, "seq_len": args.burn_in + args.learn, "burn_in": args.burn_in,
+         "n_step": args.n_step, "lstm": args.cell, "frame": "4x84x84 u8"}
+    if extra:
+        c.update(extra)
+    return c
+
+
+# ------------------------------------------------------------------------------ our arm
+def fill_synthetic(L, args, rank):
+    """SYN-R2D2 generated on the device: M slots, 80 % filled, sequence
+    starts every 40 slots, done every 997th row."""
+    import torch
+    rm = L.replay_memory
+    M = rm.memory_size
+    N = int(0.8 * M)
+    gen = torch.Generator(device=rm.device).manual_seed(1 + rank)
+    raw = lambda k: dict.__getitem__(rm.memory, k)  # noqa: E731
+    raw("state")[:N].random_(0, 256, generator=gen)
+    raw("hs_cs")[:N].normal_(0, 0.1, generator=gen)
+    raw("target_hs_cs")[:N].normal_(0, 0.1, generator=gen)
+    raw("action")[:N].random_(0, 6, generator=gen)
+    raw("reward")[:N].normal_(0, 1, generator=gen)
+    raw("done")[:N, 0] = (torch.arange(N, device=rm.device) % 997 == 996).float()
+    raw("stack_count")[:N] = 1
+    raw("priority")[:N].uniform_(0.01, 1.01, generator=gen)
+    rm.index = N
+    rm.burn_in_length, rm.learning_length = args.burn_in, args.learn
+    rm.sequence_length = args.burn_in + args.learn
+    starts = torch.arange(0, N - rm.sequence_length - args.n_step, 40, device=rm.device)
+    for i in range(0, starts.numel(), 4096):
+        rm.update_sequence_priority(starts[i:i + 4096])
+    rm.memory["is_seq_start"][starts] = 1
+    rm.rebuild_tree()
+
+
+def make_host_dump(rows, H):
+    import torch
+    g = torch.Generator().manual_seed(3)
+    pin = lambda t: t.pin_memory()  # noqa: E731
+    return {
+        "state": pin(torch.randint(0, 256, (rows, 4, 84, 84), dtype=torch.uint8, generator=g)),
+        "hs_cs": pin(torch.randn(rows, 2 * H, generator=g) * 0.1),
+        "target_hs_cs": pin(torch.randn(rows, 2 * H, generator=g) * 0.1),
+        "action": pin(torch.randint(0, 6, (rows, 1), generator=g).to(torch.int8)),
+        "reward": pin(torch.randn(rows, 1, generator=g)),
+        "done": pin(torch.zeros(rows, 1)),
+        "stack_count": pin(torch.ones(rows, dtype=torch.int8)),
+        "priority": pin(torch.rand(rows, generator=g) + 0.01),
+        "sequence_priority": pin(torch.rand(rows, generator=g) + 0.01),
+        "is_seq_start": pin((torch.arange(rows) % 40 == 0).to(torch.uint8)),
+    }
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from pytorch_r2d2_b200 import Learner, _lib
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+    _lib.load()
+    B, BI, Ln, n, H = args.batch, args.burn_in, args.learn, args.n_step, args.cell
+
+    torch.manual_seed(0)
+    L = Learner(1, {}, device=f"cuda:{local}", cell_size=H, memory_size=args.memory_size)
+    L.batch_size, L.burn_in_length, L.learning_length, L.bootstrap_steps = B, BI, Ln, n
+    L.sequence_length = BI + Ln
+    L.replay_memory.use_tma_gather = args.tma_gather
+    fill_synthetic(L, args, rank)
+    torch.manual_seed(1234 + rank)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        L.train()
+    barrier()
+
+    # ---- timed region: K steps, device time, inputs resident in HBM ----------------------
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    _lib.prof_report(reset=True)
+    _lib.prof_enable(True)
+    launches0 = _lib.launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    for _ in range(args.steps):
+        L.train()
+    ev1.record()
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    launches = _lib.launch_count() - launches0
+    _lib.prof_enable(False)
+    prof = _lib.prof_report(reset=True)
+    clk = clocks.stop() if rank == 0 else None
+    t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    ms_per_step = ms / args.steps
+    value = world * B / (ms_per_step * 1e-3)
+
+    # ---- e2e: the public API with host buffers ---------------------------------------------
+    rows = args.ingest_rows
+    dump = make_host_dump(rows, H)
+    h2d = sum(v.numel() * v.element_size() for v in dump.values()) + B * 8
+    for _ in range(2):
+        L.replay_memory.extend(dump)
+        float(L.train().item())
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        L.replay_memory.extend(dump)        # fresh experience from pinned host memory (H2D)
+        loss_host = float(L.train().item())  # uniforms H2D inside; loss read back (D2H, sync)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = world * B * args.steps / float(t.item())
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel -----------------------------------------------------
+    peaks = {"hbm_gbs": 6650.0, "bf16_tflops_sustained": 1400.0, "src": "fallback"}
+    pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(pk):
+        d = json.load(open(pk))
+        peaks = {"hbm_gbs": d["hbm_gbs"], "bf16_tflops_sustained": d["bf16_tflops_sustained"],
+                 "src": "measured"}
+    work, total_flops, bytes_model = work_model(B, BI, Ln, n, H)
+    top = sorted(prof.items(), key=lambda kv: -kv[1][1])
+    kernel_ms_per_step = sum(v[1] for v in prof.values()) / args.steps
+    dom_name, (dom_cnt, dom_ms) = top[0]
+    avg_ms = dom_ms / dom_cnt
+    roof = {"kernel": dom_name, "launches_per_step": dom_cnt / args.steps, "avg_ms": avg_ms,
+            "share_of_step": dom_ms / args.steps / ms_per_step, "traffic": None,
+            "peak_source": peaks["src"]}
+    if dom_name in work:
+        flops, nl = work[dom_name]
+        ach = flops / nl / (avg_ms * 1e-3) / 1e12
+        roof.update({"bound": "tensor", "achieved": ach, "peak": peaks["bf16_tflops_sustained"],
+                     "unit": "TFLOP/s", "frac": ach / peaks["bf16_tflops_sustained"],
+                     "algorithmic_flops_per_launch": flops / nl})
+    else:
+        nbytes = bytes_model.get(dom_name, 0)
+        ach = nbytes / (avg_ms * 1e-3) / 1e9
+        roof.update({"bound": "hbm", "achieved": ach, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                     "frac": ach / peaks["hbm_gbs"], "algorithmic_bytes_per_launch": nbytes})
+    kernels = {k: {"launches_per_step": c / args.steps, "ms_per_step": m / args.steps}
+               for k, (c, m) in top[:12]}
+    if "gather_rows_kernel" in prof or "gather_rows_tma_kernel" in prof:
+        gk = "gather_rows_tma_kernel" if "gather_rows_tma_kernel" in prof else "gather_rows_kernel"
+        c, m = prof[gk]
+        kernels[gk] = {"launches_per_step": c / args.steps, "ms_per_step": m / args.steps,
+                       "GBps": bytes_model[gk] / (m / c * 1e-3) / 1e9}
+
+    # ---- CPU baseline (bounded sample of the same workload, rank 0, N=1 only) --------------
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        step = cpu_reference_step_factory(args)
+        step()
+        t0 = time.perf_counter()
+        ncpu = 2
+        for _ in range(ncpu):
+            step()
+        dt = (time.perf_counter() - t0) / ncpu
+        cores = os.cpu_count() or 1
+        cpu = {"value": B / dt, "unit": "seq/s", "cores": cores, "kind": "port",
+               "sample": f"{ncpu} full B={B} steps after 1 warm-up, torch CPU fp32, {cores} threads"}
+
+    line = {
+        "metric": "learner_sequences_per_sec", "value": value, "unit": "seq/s", "n_gpus": world,
+        "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": workload_config(args, extra={
+            "replay_slots_per_gpu": args.memory_size, "l2_policy": "inputs larger than L2 "
+            "(replay ring >> 126 MB; each step gathers a fresh 154 MB slab)",
+            "parallelism": f"dp{world}", "global_batch": world * B,
+            "algorithmic_gflop_per_step_per_gpu": total_flops / 1e9,
+            "e2e_ingest_rows_per_step": rows}),
+        "e2e": {"value": e2e_value, "unit": "seq/s", "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": 4, "last_loss": loss_host},
+        "gpu_launches": launches, "clocks": clk, "roofline": roof,
+        "kernel_ms_per_step": kernel_ms_per_step, "kernels": kernels,
+        "achieved_tflops_whole_step": total_flops / (ms_per_step * 1e-3) / 1e12,
+    }
+    if cpu:
+        line["cpu_baseline"] = cpu
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -37,6 +37,13 @@ int r2d2_version(void);
 const char* r2d2_last_error(void);
 /* number of SMs of the current device (grid sizing for callers / bench) */
 int r2d2_sm_count(void);
+/* kernels launched by this library since it was loaded (bench.py's gpu_launches) */
+long long r2d2_launch_count(void);
+/* optional per-kernel CUDA-event timing on the launch stream (bench.py's roofline leg; not for
+ * use under stream capture).  r2d2_prof_report synchronises the device and writes one
+ * "name count total_ms" line per kernel into buf. */
+int r2d2_prof_enable(int on);
+int r2d2_prof_report(char* buf, int buflen, int reset);
 
 /* ------------------------------------------------------------------ sum-tree (K1, K8)
  * Replaces the O(M) mask + normalise + torch.multinomial of replay_memory.py:225-232.

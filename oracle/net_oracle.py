@@ -53,6 +53,16 @@ def torso(p: dict, frames: torch.Tensor) -> torch.Tensor:
     return x.reshape(x.shape[0], FEAT)
 
 
+def torso_kink_margin(p: dict, frames: torch.Tensor) -> float:
+    """min |pre-activation| over the three conv layers: distance of the batch from a ReLU kink
+    (tests use it to avoid comparing gradients across a discontinuity)."""
+    with torch.no_grad():
+        z1 = F.conv2d(frames, p["vis_layers.0.weight"], p["vis_layers.0.bias"], stride=4)
+        z2 = F.conv2d(F.relu(z1), p["vis_layers.2.weight"], p["vis_layers.2.bias"], stride=2)
+        z3 = F.conv2d(F.relu(z2), p["vis_layers.4.weight"], p["vis_layers.4.bias"], stride=1)
+    return float(min(z1.abs().min(), z2.abs().min(), z3.abs().min()))
+
+
 def lstm_step(p: dict, x, h, c):
     """One LSTMCell step, gate order i,f,g,o (model.py:24,55)."""
     g = F.linear(x, p["lstm.weight_ih"], p["lstm.bias_ih"]) + \

@@ -20,6 +20,9 @@ PROTOTYPES = {
     "r2d2_version": (_I, []),
     "r2d2_last_error": (ctypes.c_char_p, []),
     "r2d2_sm_count": (_I, []),
+    "r2d2_launch_count": (ctypes.c_longlong, []),
+    "r2d2_prof_enable": (_I, [_I]),
+    "r2d2_prof_report": (_I, [ctypes.c_char_p, _I, _I]),
     "r2d2_tree_layout": (_I, [_L, _I, _P, _P, _P, _P]),
     "r2d2_tree_build": (_I, [_P, _P, _L, _P, _P]),
     "r2d2_tree_sample": (_I, [_P, _P, _L, _P, _P, _I, _P, _P]),
@@ -102,3 +105,22 @@ def ptr(t, dtype: str | None = None, allow_none: bool = False) -> ctypes.c_void_
 
 def call(name: str, *args) -> None:
     check(getattr(load(), name)(*args), name)
+
+
+def launch_count() -> int:
+    return int(load().r2d2_launch_count())
+
+
+def prof_enable(on: bool) -> None:
+    call("r2d2_prof_enable", int(on))
+
+
+def prof_report(reset: bool = True) -> dict:
+    """{kernel name: (launches, total_ms)} measured with CUDA events on the launch stream."""
+    buf = ctypes.create_string_buffer(1 << 16)
+    call("r2d2_prof_report", buf, len(buf), int(reset))
+    out = {}
+    for line in buf.value.decode().splitlines():
+        name, cnt, ms = line.rsplit(" ", 2)
+        out[name] = (int(cnt), float(ms))
+    return out

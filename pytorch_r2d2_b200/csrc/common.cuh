@@ -28,6 +28,17 @@ int set_err(int code, const char* fmt, ...);
 
 #define R2D2_LAUNCH_OK() R2D2_CUDA_OK(cudaGetLastError())
 
+// Every kernel launch of the library goes through this: counts the launch and, when the
+// profiler is enabled (bench.py's roofline leg), brackets it with CUDA events on its stream.
+#define R2D2_LAUNCH(name, st, ...)                \
+    do {                                          \
+        {                                         \
+            r2d2::ProfScope ps__(name, st);       \
+            __VA_ARGS__;                          \
+        }                                         \
+        R2D2_LAUNCH_OK();                         \
+    } while (0)
+
 static inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
 constexpr unsigned FULL = 0xffffffffu;
@@ -52,5 +63,15 @@ __device__ __forceinline__ void st_stream(uint4* p, const uint4& v) {
 }
 
 int sm_count();
+
+struct ProfScope {
+    ProfScope(const char* name, cudaStream_t st);
+    ~ProfScope();
+    const char* name_;
+    cudaStream_t st_;
+    bool on_;
+    void* a_ = nullptr;
+    void* b_ = nullptr;
+};
 
 }  // namespace r2d2

@@ -271,13 +271,16 @@ struct EpiConv {
 };
 
 template <int BM, int BN, int TM, int TN, class AL, class BL, class EP>
-static inline cudaError_t launch_gemm(const AL& al, const BL& bl, const EP& ep, int M, int N,
-                                      int K, int splits, cudaStream_t st) {
+static inline cudaError_t launch_gemm(const char* name, const AL& al, const BL& bl, const EP& ep,
+                                      int M, int N, int K, int splits, cudaStream_t st) {
     constexpr int NT = (BM / TM) * (BN / TN);
     int kps = (K + splits - 1) / splits;
     kps = (kps + 15) / 16 * 16;
     dim3 grid((M + BM - 1) / BM, (N + BN - 1) / BN, splits);
-    gemm_kernel<BM, BN, TM, TN, AL, BL, EP><<<grid, NT, 0, st>>>(al, bl, ep, M, N, K, kps);
+    {
+        ProfScope ps(name, st);
+        gemm_kernel<BM, BN, TM, TN, AL, BL, EP><<<grid, NT, 0, st>>>(al, bl, ep, M, N, K, kps);
+    }
     return cudaGetLastError();
 }
 

@@ -501,19 +501,19 @@ static int torso_fwd_impl(const T* frames, FrameMap fm, int R, const float* w1, 
         ConvPatchRows<T, 4, 8, 84, 20, 4> al{frames, fm};
         W bl{w1, 256, 1};
         EpiConv<32, 400> ep{a1, b1};
-        R2D2_CUDA_OK((launch_gemm<128, 32, 8, 4>(al, bl, ep, R * 400, 32, 256, 1, st)));
+        R2D2_CUDA_OK((launch_gemm<128, 32, 8, 4>("conv1_fwd", al, bl, ep, R * 400, 32, 256, 1, st)));
     }
     {
         ConvPatchRows<float, 32, 4, 20, 9, 2> al{a1, FrameMap{0, 0, 0, 12800}};
         W bl{w2, 512, 1};
         EpiConv<32, 81> ep{a2, b2};
-        R2D2_CUDA_OK((launch_gemm<128, 32, 8, 4>(al, bl, ep, R * 81, 32, 512, 1, st)));
+        R2D2_CUDA_OK((launch_gemm<128, 32, 8, 4>("conv2_fwd", al, bl, ep, R * 81, 32, 512, 1, st)));
     }
     {
         ConvPatchRows<float, 32, 3, 9, 7, 1> al{a2, FrameMap{0, 0, 0, 2592}};
         W bl{w3, 288, 1};
         EpiConv<32, 49> ep{feat, b3};
-        R2D2_CUDA_OK((launch_gemm<128, 32, 8, 4>(al, bl, ep, R * 49, 32, 288, 1, st)));
+        R2D2_CUDA_OK((launch_gemm<128, 32, 8, 4>("conv3_fwd", al, bl, ep, R * 49, 32, 288, 1, st)));
     }
     return R2D2_OK;
 }
@@ -529,15 +529,14 @@ static int pick_splits(int tiles, int K) {
 
 // conv weight gradient: dW[32, KP] = sum over (frame, out pixel)
 template <class AL, class BL>
-static int conv_wgrad(const AL& al, const BL& bl, int KP, int Kred, float* dw, float* part,
+static int conv_wgrad(const char* name, const AL& al, const BL& bl, int KP, int Kred, float* dw, float* part,
                       cudaStream_t st) {
     const int tiles = (KP + 63) / 64;
     const int splits = pick_splits(tiles, Kred);
     EpiPartial ep{part, KP, (long long)32 * KP};
-    R2D2_CUDA_OK((launch_gemm<32, 64, 4, 8>(al, bl, ep, 32, KP, Kred, splits, st)));
+    R2D2_CUDA_OK((launch_gemm<32, 64, 4, 8>(name, al, bl, ep, 32, KP, Kred, splits, st)));
     const int64_t n = (int64_t)32 * KP;
-    reduce_partials_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(part, dw, n, splits);
-    R2D2_LAUNCH_OK();
+    R2D2_LAUNCH("reduce_partials_kernel", st, reduce_partials_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(part, dw, n, splits));
     return R2D2_OK;
 }
 
@@ -556,46 +555,40 @@ static int torso_bwd_impl(const T* frames, FrameMap fm, int R, const float* a1, 
         const int64_t n = (int64_t)R * R2D2_FEAT;
         int64_t blocks = (n + 255) / 256;
         if (blocks > 148 * 16) blocks = 148 * 16;
-        relu_mask_kernel<<<(unsigned)blocks, 256, 0, st>>>(dfeat, feat, n);
-        R2D2_LAUNCH_OK();
+        R2D2_LAUNCH("relu_mask_kernel", st, relu_mask_kernel<<<(unsigned)blocks, 256, 0, st>>>(dfeat, feat, n));
     }
     {
         GradRowsT<32, 7> al{dfeat};
         ConvPatchCols<float, 32, 3, 9, 7, 1> bl{a2, FrameMap{0, 0, 0, 2592}};
-        int rc = conv_wgrad(al, bl, 288, R * 49, dw3, part, st);
+        int rc = conv_wgrad("conv3_wgrad", al, bl, 288, R * 49, dw3, part, st);
         if (rc) return rc;
-        chansum_kernel<<<32, 1024, 0, st>>>(dfeat, db3, R, 32, 49);
-        R2D2_LAUNCH_OK();
+        R2D2_LAUNCH("chansum_kernel", st, chansum_kernel<<<32, 1024, 0, st>>>(dfeat, db3, R, 32, 49));
     }
     {
         constexpr int smem = (32 * 3 * 3 * 32 + 32 * 49) * 4;
         R2D2_CUDA_OK(cudaFuncSetAttribute(conv_dgrad_kernel<3, 9, 7, 1>,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        conv_dgrad_kernel<3, 9, 7, 1><<<R, 256, smem, st>>>(dfeat, w3, a2, dz2);
-        R2D2_LAUNCH_OK();
+        R2D2_LAUNCH("conv_dgrad_kernel<3,9,7,1>", st, conv_dgrad_kernel<3, 9, 7, 1><<<R, 256, smem, st>>>(dfeat, w3, a2, dz2));
     }
     {   // layer 2
         GradRowsT<32, 9> al{dz2};
         ConvPatchCols<float, 32, 4, 20, 9, 2> bl{a1, FrameMap{0, 0, 0, 12800}};
-        int rc = conv_wgrad(al, bl, 512, R * 81, dw2, part, st);
+        int rc = conv_wgrad("conv2_wgrad", al, bl, 512, R * 81, dw2, part, st);
         if (rc) return rc;
-        chansum_kernel<<<32, 1024, 0, st>>>(dz2, db2, R, 32, 81);
-        R2D2_LAUNCH_OK();
+        R2D2_LAUNCH("chansum_kernel", st, chansum_kernel<<<32, 1024, 0, st>>>(dz2, db2, R, 32, 81));
     }
     {
         constexpr int smem = (32 * 4 * 4 * 32 + 32 * 81) * 4;
         R2D2_CUDA_OK(cudaFuncSetAttribute(conv_dgrad_kernel<4, 20, 9, 2>,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        conv_dgrad_kernel<4, 20, 9, 2><<<R, 256, smem, st>>>(dz2, w2, a1, dz1);
-        R2D2_LAUNCH_OK();
+        R2D2_LAUNCH("conv_dgrad_kernel<4,20,9,2>", st, conv_dgrad_kernel<4, 20, 9, 2><<<R, 256, smem, st>>>(dz2, w2, a1, dz1));
     }
     {   // layer 1 (no data gradient: frames are inputs)
         GradRowsT<32, 20> al{dz1};
         ConvPatchCols<T, 4, 8, 84, 20, 4> bl{frames, fm};
-        int rc = conv_wgrad(al, bl, 256, R * 400, dw1, part, st);
+        int rc = conv_wgrad("conv1_wgrad", al, bl, 256, R * 400, dw1, part, st);
         if (rc) return rc;
-        chansum_kernel<<<32, 1024, 0, st>>>(dz1, db1, R, 32, 400);
-        R2D2_LAUNCH_OK();
+        R2D2_LAUNCH("chansum_kernel", st, chansum_kernel<<<32, 1024, 0, st>>>(dz1, db1, R, 32, 400));
     }
     return R2D2_OK;
 }
@@ -630,8 +623,8 @@ int r2d2_linear_fwd(const float* x, const float* w, const float* bias1, const fl
     R2D2_REQUIRE(x && w && y && M > 0 && N > 0 && K > 0, "linear_fwd: bad args");
     DenseLoad<true> al{x, K, 1}, bl{w, K, 1};
     EpiDense ep{y, N, bias1, bias2, relu, 0};
-    if (M >= 512) R2D2_CUDA_OK((launch_gemm<128, 128, 8, 8>(al, bl, ep, M, N, K, 1, as_stream(stream))));
-    else R2D2_CUDA_OK((launch_gemm<64, 64, 4, 4>(al, bl, ep, M, N, K, 1, as_stream(stream))));
+    if (M >= 512) R2D2_CUDA_OK((launch_gemm<128, 128, 8, 8>("linear_fwd", al, bl, ep, M, N, K, 1, as_stream(stream))));
+    else R2D2_CUDA_OK((launch_gemm<64, 64, 4, 4>("linear_fwd_small", al, bl, ep, M, N, K, 1, as_stream(stream))));
     return R2D2_OK;
 }
 
@@ -641,8 +634,8 @@ int r2d2_linear_dgrad(const float* dy, const float* w, float* dx, int M, int N, 
     DenseLoad<true> al{dy, N, 1};
     DenseLoad<false> bl{w, 1, K};
     EpiDense ep{dx, K, nullptr, nullptr, 0, accumulate};
-    if (M >= 512) R2D2_CUDA_OK((launch_gemm<128, 128, 8, 8>(al, bl, ep, M, K, N, 1, as_stream(stream))));
-    else R2D2_CUDA_OK((launch_gemm<64, 64, 4, 4>(al, bl, ep, M, K, N, 1, as_stream(stream))));
+    if (M >= 512) R2D2_CUDA_OK((launch_gemm<128, 128, 8, 8>("linear_dgrad", al, bl, ep, M, K, N, 1, as_stream(stream))));
+    else R2D2_CUDA_OK((launch_gemm<64, 64, 4, 4>("linear_dgrad_small", al, bl, ep, M, K, N, 1, as_stream(stream))));
     return R2D2_OK;
 }
 
@@ -670,18 +663,16 @@ int r2d2_linear_wgrad(const float* dy, const float* x, float* dw, float* db, int
         R2D2_REQUIRE(scratch, "linear_wgrad: scratch required (%lld bytes)",
                      (long long)r2d2_linear_wgrad_scratch_bytes(M, N, K));
         EpiPartial ep{(float*)scratch, K, (long long)N * K};
-        R2D2_CUDA_OK((launch_gemm<128, 128, 8, 8>(al, bl, ep, N, K, M, splits, st)));
+        R2D2_CUDA_OK((launch_gemm<128, 128, 8, 8>("linear_wgrad", al, bl, ep, N, K, M, splits, st)));
         const int64_t n = (int64_t)N * K;
-        reduce_partials_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const float*)scratch,
-                                                                            dw, n, splits);
-        R2D2_LAUNCH_OK();
+        R2D2_LAUNCH("reduce_partials_kernel", st, reduce_partials_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const float*)scratch,
+                                                                            dw, n, splits));
     } else {
         EpiDense ep{dw, K, nullptr, nullptr, 0, 0};
-        R2D2_CUDA_OK((launch_gemm<128, 128, 8, 8>(al, bl, ep, N, K, M, 1, st)));
+        R2D2_CUDA_OK((launch_gemm<128, 128, 8, 8>("linear_wgrad", al, bl, ep, N, K, M, 1, st)));
     }
     if (db) {
-        colsum_kernel<<<(N + 31) / 32, 1024, 0, st>>>(dy, db, M, N);
-        R2D2_LAUNCH_OK();
+        R2D2_LAUNCH("colsum_kernel", st, colsum_kernel<<<(N + 31) / 32, 1024, 0, st>>>(dy, db, M, N));
     }
     return R2D2_OK;
 }
@@ -693,11 +684,10 @@ int r2d2_lstm_seq_fwd(const float* xproj, const float* w_hh, float* hs_ext, floa
     const int64_t bh = (int64_t)B * H;
     dim3 grid(H / LSTM_UPB, (B + LSTM_BT - 1) / LSTM_BT);
     for (int t = 0; t < T; ++t) {
-        lstm_step_fwd_kernel<<<grid, 256, 0, as_stream(stream)>>>(
+        R2D2_LAUNCH("lstm_step_fwd_kernel", as_stream(stream), lstm_step_fwd_kernel<<<grid, 256, 0, as_stream(stream)>>>(
             xproj + (int64_t)t * 4 * bh, w_hh, hs_ext + t * bh, cs_ext + t * bh,
             hs_ext + (t + 1) * bh, cs_ext + (t + 1) * bh, gates ? gates + (int64_t)t * 4 * bh : nullptr,
-            B, H);
-        R2D2_LAUNCH_OK();
+            B, H));
     }
     return R2D2_OK;
 }
@@ -711,11 +701,10 @@ int r2d2_lstm_seq_bwd(const float* dhs, const float* w_hh, const float* gates,
     const int64_t bh = (int64_t)B * H;
     dim3 grid(H / LSTM_UPB, (B + LSTM_BT - 1) / LSTM_BT);
     for (int t = T - 1; t >= 0; --t) {
-        lstm_step_bwd_kernel<<<grid, 256, 0, as_stream(stream)>>>(
+        R2D2_LAUNCH("lstm_step_bwd_kernel", as_stream(stream), lstm_step_bwd_kernel<<<grid, 256, 0, as_stream(stream)>>>(
             dhs + t * bh, t == T - 1 ? nullptr : dgates + (int64_t)(t + 1) * 4 * bh, w_hh,
             gates + (int64_t)t * 4 * bh, cs_ext + (t + 1) * bh, cs_ext + t * bh, dc_work,
-            dgates + (int64_t)t * 4 * bh, t == T - 1 ? 1 : 0, B, H);
-        R2D2_LAUNCH_OK();
+            dgates + (int64_t)t * 4 * bh, t == T - 1 ? 1 : 0, B, H));
     }
     return R2D2_OK;
 }
@@ -725,8 +714,7 @@ int r2d2_head_fwd(const float* hs, const float* w1, const float* b1, const float
     R2D2_REQUIRE(hs && w1 && b1 && w2 && b2 && hid && q && M > 0 && H > 0, "head_fwd: bad args");
     int rc = r2d2_linear_fwd(hs, w1, b1, nullptr, hid, M, 2 * H, H, 1, stream);
     if (rc) return rc;
-    head_out_kernel<<<(M + 7) / 8, 256, 0, as_stream(stream)>>>(hid, w2, b2, q, M, H);
-    R2D2_LAUNCH_OK();
+    R2D2_LAUNCH("head_out_kernel", as_stream(stream), head_out_kernel<<<(M + 7) / 8, 256, 0, as_stream(stream)>>>(hid, w2, b2, q, M, H));
     return R2D2_OK;
 }
 
@@ -734,10 +722,8 @@ int r2d2_head_bwd(const float* dq, const float* hid, const float* w2, float* dhi
                   float* db2, int M, int H, void* stream) {
     R2D2_REQUIRE(dq && hid && w2 && dhid && dw2 && db2 && M > 0 && H > 0 && H % 32 == 0,
                  "head_bwd: bad args (H must be a multiple of 32)");
-    head_bwd_dhid_kernel<<<M, 256, 0, as_stream(stream)>>>(dq, hid, w2, dhid, M, H);
-    R2D2_LAUNCH_OK();
-    head_bwd_dw2_kernel<<<H / 32 + 1, 1024, 0, as_stream(stream)>>>(dq, hid, dw2, db2, M, H);
-    R2D2_LAUNCH_OK();
+    R2D2_LAUNCH("head_bwd_dhid_kernel", as_stream(stream), head_bwd_dhid_kernel<<<M, 256, 0, as_stream(stream)>>>(dq, hid, w2, dhid, M, H));
+    R2D2_LAUNCH("head_bwd_dw2_kernel", as_stream(stream), head_bwd_dw2_kernel<<<H / 32 + 1, 1024, 0, as_stream(stream)>>>(dq, hid, dw2, db2, M, H));
     return R2D2_OK;
 }
 
@@ -749,10 +735,9 @@ int r2d2_td_target(const float* q_all, const float* q_next_online, const float* 
     R2D2_REQUIRE(q_all && q_next_online && q_next_target && action && reward && done &&
                      next_action && y && delta && dq && prio && loss && n > 0,
                  "td_target: bad args");
-    td_target_kernel<<<1, 1024, 0, as_stream(stream)>>>(
+    R2D2_LAUNCH("td_target_kernel", as_stream(stream), td_target_kernel<<<1, 1024, 0, as_stream(stream)>>>(
         q_all, q_next_online, q_next_target, action, reward, done, n, gamma_n, rescale, rescale_eps,
-        prio_eps, alpha, next_action_override, next_action, y, delta, dq, prio, loss);
-    R2D2_LAUNCH_OK();
+        prio_eps, alpha, next_action_override, next_action, y, delta, dq, prio, loss));
     return R2D2_OK;
 }
 
@@ -793,11 +778,10 @@ int r2d2_rmsprop_centered(float* param, const float* grad, float* square_avg, fl
     int64_t blocks = (n / 4 + 255) / 256;
     if (blocks > 148 * 8) blocks = 148 * 8;
     if (blocks < 1) blocks = 1;
-    rmsprop_kernel<<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(param, grad, square_avg,
+    R2D2_LAUNCH("rmsprop_kernel", as_stream(stream), rmsprop_kernel<<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(param, grad, square_avg,
                                                                     grad_avg, n, (float)lr,
                                                                     (float)alpha, (float)(1.0 - alpha),
-                                                                    (float)eps, (float)grad_scale);
-    R2D2_LAUNCH_OK();
+                                                                    (float)eps, (float)grad_scale));
     return R2D2_OK;
 }
 

@@ -3,6 +3,12 @@
 // latency-bound; no tensor cores.  Reference semantics: replay_memory.py:93-119,175-262.
 #include "common.cuh"
 
+#include <atomic>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
 namespace r2d2 {
 
 static thread_local char g_err[512] = "";
@@ -14,6 +20,37 @@ int set_err(int code, const char* fmt, ...) {
     va_end(ap);
     return code;
 }
+// ---- launch counter and optional per-kernel CUDA-event profiler (bench.py's roofline leg)
+static std::atomic<long long> g_launches{0};
+static bool g_prof_on = false;
+struct ProfRec { const char* name; cudaEvent_t a, b; };
+static std::vector<ProfRec> g_recs;
+static std::vector<cudaEvent_t> g_pool;
+static std::mutex g_prof_mu;
+
+static cudaEvent_t prof_event() {
+    if (!g_pool.empty()) { cudaEvent_t e = g_pool.back(); g_pool.pop_back(); return e; }
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    return e;
+}
+ProfScope::ProfScope(const char* name, cudaStream_t st) : name_(name), st_(st), on_(g_prof_on) {
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    if (on_) {
+        std::lock_guard<std::mutex> lk(g_prof_mu);
+        a_ = prof_event();
+        b_ = prof_event();
+        cudaEventRecord((cudaEvent_t)a_, st_);
+    }
+}
+ProfScope::~ProfScope() {
+    if (on_) {
+        cudaEventRecord((cudaEvent_t)b_, st_);
+        std::lock_guard<std::mutex> lk(g_prof_mu);
+        g_recs.push_back(ProfRec{name_, (cudaEvent_t)a_, (cudaEvent_t)b_});
+    }
+}
+
 int sm_count() {
     int dev = 0, n = 148;
     if (cudaGetDevice(&dev) == cudaSuccess)
@@ -520,6 +557,38 @@ extern "C" {
 int r2d2_version(void) { return 100; }
 const char* r2d2_last_error(void) { return r2d2::err_buf(); }
 int r2d2_sm_count(void) { return r2d2::sm_count(); }
+long long r2d2_launch_count(void) { return r2d2::g_launches.load(); }
+int r2d2_prof_enable(int on) {
+    r2d2::g_prof_on = on != 0;
+    return R2D2_OK;
+}
+int r2d2_prof_report(char* buf, int buflen, int reset) {
+    // synchronises, then writes one "name count total_ms" line per kernel name
+    R2D2_CUDA_OK(cudaDeviceSynchronize());
+    std::lock_guard<std::mutex> lk(r2d2::g_prof_mu);
+    std::map<std::string, std::pair<long long, double>> agg;
+    for (auto& r : r2d2::g_recs) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess) {
+            auto& e = agg[r.name];
+            e.first += 1;
+            e.second += ms;
+        }
+    }
+    int pos = 0;
+    if (buf && buflen > 0) buf[0] = 0;
+    for (auto& kv : agg) {
+        int w = snprintf(buf + pos, pos < buflen ? buflen - pos : 0, "%s %lld %.6f\n",
+                         kv.first.c_str(), kv.second.first, kv.second.second);
+        if (w < 0 || pos + w >= buflen) break;
+        pos += w;
+    }
+    if (reset) {
+        for (auto& r : r2d2::g_recs) { r2d2::g_pool.push_back(r.a); r2d2::g_pool.push_back(r.b); }
+        r2d2::g_recs.clear();
+    }
+    return R2D2_OK;
+}
 
 int r2d2_tree_layout(int64_t M, int max_levels, int64_t* level_sizes, int64_t* level_offsets,
                      int* n_levels, int64_t* total_nodes) {
@@ -547,10 +616,9 @@ int r2d2_tree_build(const float* seq_prio, const uint8_t* is_start, int64_t M, d
         const int64_t warps = L.size[l];
         int64_t blocks = (warps + 7) / 8;  // 8 warps per CTA
         if (blocks > (int64_t)sms * 16) blocks = (int64_t)sms * 16;
-        tree_build_level<<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(
+        R2D2_LAUNCH("tree_build_level", as_stream(stream), tree_build_level<<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(
             seq_prio, is_start, M, nodes, l, l ? L.off[l - 1] : 0, l ? L.size[l - 1] : M, L.off[l],
-            L.size[l]);
-        R2D2_LAUNCH_OK();
+            L.size[l]));
     }
     return R2D2_OK;
 }
@@ -563,9 +631,8 @@ int r2d2_tree_sample(const float* seq_prio, const uint8_t* is_start, int64_t M,
     if (B == 0) return R2D2_OK;
     TreeLayout L = make_layout(M);
     const int warps_per_cta = 4;
-    tree_sample_kernel<<<(B + warps_per_cta - 1) / warps_per_cta, warps_per_cta * 32, 0,
-                         as_stream(stream)>>>(seq_prio, is_start, M, nodes, L, u, B, out_slot);
-    R2D2_LAUNCH_OK();
+    R2D2_LAUNCH("tree_sample_kernel", as_stream(stream), tree_sample_kernel<<<(B + warps_per_cta - 1) / warps_per_cta, warps_per_cta * 32, 0,
+                         as_stream(stream)>>>(seq_prio, is_start, M, nodes, L, u, B, out_slot));
     return R2D2_OK;
 }
 
@@ -574,9 +641,8 @@ int r2d2_tree_update(const float* seq_prio, const uint8_t* is_start, int64_t M, 
     R2D2_REQUIRE(seq_prio && is_start && nodes && slots, "tree_update: null pointer");
     if (n <= 0) return R2D2_OK;
     TreeLayout L = make_layout(M);
-    tree_update_kernel<<<1, 1024, 0, as_stream(stream)>>>(seq_prio, is_start, M, nodes, L, slots,
-                                                           n);
-    R2D2_LAUNCH_OK();
+    R2D2_LAUNCH("tree_update_kernel", as_stream(stream), tree_update_kernel<<<1, 1024, 0, as_stream(stream)>>>(seq_prio, is_start, M, nodes, L, slots,
+                                                           n));
     return R2D2_OK;
 }
 
@@ -601,26 +667,27 @@ int r2d2_replay_gather(const uint8_t* state, const float* hs_cs, const float* ta
         int64_t total = (int64_t)B * S;
         int grid = sm_count();
         if (grid > total) grid = (int)total;
-        gather_rows_tma_kernel<<<grid, 32, smem, as_stream(stream)>>>(state, M, seq_index, B, S,
-                                                                     slab);
+        R2D2_LAUNCH("gather_rows_tma_kernel", as_stream(stream),
+                    gather_rows_tma_kernel<<<grid, 32, smem, as_stream(stream)>>>(state, M, seq_index,
+                                                                                 B, S, slab));
     } else {
-        gather_rows_kernel<<<dim3(S, B), 256, 0, as_stream(stream)>>>(
-            reinterpret_cast<const uint4*>(state), M, seq_index, S, reinterpret_cast<uint4*>(slab));
+        R2D2_LAUNCH("gather_rows_kernel", as_stream(stream),
+                    gather_rows_kernel<<<dim3(S, B), 256, 0, as_stream(stream)>>>(
+                        reinterpret_cast<const uint4*>(state), M, seq_index, S,
+                        reinterpret_cast<uint4*>(slab)));
     }
-    R2D2_LAUNCH_OK();
     const int64_t total = (int64_t)B * cell + (int64_t)(T - burn_in) * B + (int64_t)T * B;
-    gather_small_kernel<<<(unsigned)((total + 255) / 256), 256, 0, as_stream(stream)>>>(
-        hs_cs, target_hs_cs, action, reward, done, M, cell, seq_index, B, T, n_step, burn_in, hs,
-        cs, ths, tcs, action_out, reward_out, done_out, index_out);
-    R2D2_LAUNCH_OK();
+    R2D2_LAUNCH("gather_small_kernel", as_stream(stream),
+                gather_small_kernel<<<(unsigned)((total + 255) / 256), 256, 0, as_stream(stream)>>>(
+                    hs_cs, target_hs_cs, action, reward, done, M, cell, seq_index, B, T, n_step,
+                    burn_in, hs, cs, ths, tcs, action_out, reward_out, done_out, index_out));
     return R2D2_OK;
 }
 
 int r2d2_slab_to_f32(const uint8_t* slab, int B, int S, int s0, int T, float* out, void* stream) {
     R2D2_REQUIRE(slab && out && B > 0 && T > 0 && s0 >= 0 && s0 + T <= S, "slab_to_f32: bad args");
-    slab_to_f32_kernel<<<(unsigned)((int64_t)T * B), 256, 0, as_stream(stream)>>>(slab, B, S, s0,
-                                                                                   T, out);
-    R2D2_LAUNCH_OK();
+    R2D2_LAUNCH("slab_to_f32_kernel", as_stream(stream), slab_to_f32_kernel<<<(unsigned)((int64_t)T * B), 256, 0, as_stream(stream)>>>(slab, B, S, s0,
+                                                                                   T, out));
     return R2D2_OK;
 }
 
@@ -643,18 +710,16 @@ int r2d2_replay_ingest(const uint8_t* src_state, const float* src_hs_cs,
                  "replay_ingest: null pointer");
     R2D2_REQUIRE(((uintptr_t)state % 16) == 0 && ((uintptr_t)src_state % 16) == 0,
                  "replay_ingest: state buffers must be 16-byte aligned");
-    ingest_rows_kernel<<<(unsigned)rows, 256, 0, as_stream(stream)>>>(
+    R2D2_LAUNCH("ingest_rows_kernel", as_stream(stream), ingest_rows_kernel<<<(unsigned)rows, 256, 0, as_stream(stream)>>>(
         reinterpret_cast<const uint4*>(src_state), reinterpret_cast<uint4*>(state), M,
-        write_index % M);
-    R2D2_LAUNCH_OK();
+        write_index % M));
     const int64_t total = rows * 2 * cell;
     int64_t blocks = (total + 255) / 256;
     if (blocks > 148 * 32) blocks = 148 * 32;
-    ingest_small_kernel<<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(
+    R2D2_LAUNCH("ingest_small_kernel", as_stream(stream), ingest_small_kernel<<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(
         src_hs_cs, src_target_hs_cs, src_action, src_reward, src_done, src_stack_count,
         src_priority, src_seq_prio, src_is_start, rows, hs_cs, target_hs_cs, action, reward, done,
-        stack_count, priority, seq_prio, is_start, M, cell, write_index % M);
-    R2D2_LAUNCH_OK();
+        stack_count, priority, seq_prio, is_start, M, cell, write_index % M));
     return R2D2_OK;
 }
 
@@ -664,9 +729,8 @@ int r2d2_update_priority(float* priority, int64_t M, const int64_t* index, const
     if (n <= 0) return R2D2_OK;
     int64_t blocks = (n + 127) / 128;
     if (blocks > 148 * 16) blocks = 148 * 16;
-    update_priority_kernel<<<(unsigned)blocks, 128, 0, as_stream(stream)>>>(priority, M, index, p,
-                                                                            n);
-    R2D2_LAUNCH_OK();
+    R2D2_LAUNCH("update_priority_kernel", as_stream(stream), update_priority_kernel<<<(unsigned)blocks, 128, 0, as_stream(stream)>>>(priority, M, index, p,
+                                                                            n));
     return R2D2_OK;
 }
 
@@ -678,9 +742,8 @@ int r2d2_update_priority_seq(float* priority, int64_t M, const int64_t* seq_inde
     const int64_t n = (int64_t)L * B;
     int64_t blocks = (n + 127) / 128;
     if (blocks > 148 * 16) blocks = 148 * 16;
-    update_priority_seq_kernel<<<(unsigned)blocks, 128, B * sizeof(int64_t), as_stream(stream)>>>(
-        priority, M, seq_index, B, burn_in, L, p);
-    R2D2_LAUNCH_OK();
+    R2D2_LAUNCH("update_priority_seq_kernel", as_stream(stream), update_priority_seq_kernel<<<(unsigned)blocks, 128, B * sizeof(int64_t), as_stream(stream)>>>(
+        priority, M, seq_index, B, burn_in, L, p));
     return R2D2_OK;
 }
 
@@ -692,10 +755,9 @@ int r2d2_update_sequence_priority(const float* priority, float* seq_prio,
                  "update_sequence_priority: null pointer");
     R2D2_REQUIRE(M > 0 && T > 0 && T <= M, "update_sequence_priority: need 0 < T <= M");
     if (n <= 0) return R2D2_OK;
-    update_seq_priority_kernel<<<1, 1024, 0, as_stream(stream)>>>(
+    R2D2_LAUNCH("update_seq_priority_kernel", as_stream(stream), update_seq_priority_kernel<<<1, 1024, 0, as_stream(stream)>>>(
         priority, seq_prio, is_start, M, seq_index, n, T, eta_f32, one_minus_eta_f32,
-        update_pre_next, touched);
-    R2D2_LAUNCH_OK();
+        update_pre_next, touched));
     return R2D2_OK;
 }
 

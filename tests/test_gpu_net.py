@@ -282,9 +282,17 @@ def test_train_step_vs_oracle(cuda_device, H, B, BI, LN, NS):
     L.replay_memory = mirror_to_gpu(rep, B)
     p = {k: v.cpu().clone() for k, v in L.net.state_dict().items()}
     pt = {k: v.cpu().clone() for k, v in L.target_net.state_dict().items()}
-    u = np.random.RandomState(H).rand(B)
-    si = rep.sample_indices(u)
-    res = NO.train_step(p, pt, NO.to_torch_batch(rep.gather(si)["batch"]), burn_in=BI, n_step=NS)
+    # ReLU' is discontinuous: a conv pre-activation within rounding distance of 0 (seen: 4e-8)
+    # legitimately flips one mask bit between two fp32 implementations and changes that
+    # channel's gradient by O(1e-3).  Draw the batch so that no learn-window pre-activation of
+    # the torso sits closer than 1e-6 to the kink (deterministic search over seeds).
+    for attempt in range(20):
+        u = np.random.RandomState(H + 1000 * attempt).rand(B)
+        si = rep.sample_indices(u)
+        tb = NO.to_torch_batch(rep.gather(si)["batch"])
+        if NO.torso_kink_margin(p, tb["state"][BI:].reshape(-1, 4, 84, 84)) > 1e-6:
+            break
+    res = NO.train_step(p, pt, tb, burn_in=BI, n_step=NS)
     L.train(u=torch.from_numpy(u), next_action_override=res["next_action"].cuda())
     out = L.last
     assert np.array_equal(out["seq_index"].cpu().numpy(), si)

@@ -7,10 +7,10 @@ from oracle import replay_oracle as RO
 
 
 def rel_err(a, b):
-    a = torch.as_tensor(a, dtype=torch.float64).cpu().reshape(-1)
-    b = torch.as_tensor(b, dtype=torch.float64).cpu().reshape(-1)
+    a = torch.as_tensor(a).detach().to(torch.float64).cpu().reshape(-1)
+    b = torch.as_tensor(b).detach().to(torch.float64).cpu().reshape(-1)
     den = b.abs().max().clamp_min(1e-30)
-    return float((a - b).abs().max() / den)
+    return float(((a - b).abs().max() / den).detach())
 
 
 def fill_small(mem, M, H, seed):
