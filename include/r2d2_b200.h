@@ -160,6 +160,18 @@ int r2d2_linear_dgrad(const float* dy, const float* w, float* dx, int M, int N, 
 int64_t r2d2_linear_wgrad_scratch_bytes(int M, int N, int K);
 int r2d2_linear_wgrad(const float* dy, const float* x, float* dw, float* db, int M, int N,
                       int K, void* scratch, void* stream);
+/* No counterpart in the reference.  Same result as r2d2_linear_wgrad for callers that cannot
+ * supply (or allocate) a workspace: a C/C++ actor or serving host that was given exactly its
+ * input/output buffers by another component, a process whose whole HBM budget was handed out
+ * at start-up, or a latency-critical loop that must never reach cudaMalloc because it stalls
+ * every stream on the device.  The split-K partial sums go to an array built into the library
+ * (R2D2_STATIC_WGRAD_SCRATCH_BYTES per GPU, resident until exit).  Problems whose scratch
+ * need exceeds it are refused with R2D2_EINVAL.  The first call on each device resolves the
+ * array's address (do it at set-up, before any stream capture); all calls share the array, so
+ * calls that may overlap on the GPU must be serialised by the caller.  Never allocates. */
+#define R2D2_STATIC_WGRAD_SCRATCH_BYTES (32 << 20)
+int r2d2_linear_wgrad_static(const float* dy, const float* x, float* dw, float* db, int M, int N,
+                             int K, void* stream);
 /* BPTT over the learn window: dhs [T,B,H] is dL/dh_t from the head; gates/cs_ext from
  * r2d2_lstm_seq_fwd.  Writes dgates [T,B,4H] (pre-activation grads).  dc_work [B,H] carries
  * dL/dc between steps (caller-owned, contents undefined on entry). */

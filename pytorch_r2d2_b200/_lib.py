@@ -43,6 +43,7 @@ PROTOTYPES = {
     "r2d2_linear_dgrad": (_I, [_P, _P, _P, _I, _I, _I, _I, _P]),
     "r2d2_linear_wgrad_scratch_bytes": (_L, [_I, _I, _I]),
     "r2d2_linear_wgrad": (_I, [_P, _P, _P, _P, _I, _I, _I, _P, _P]),
+    "r2d2_linear_wgrad_static": (_I, [_P, _P, _P, _P, _I, _I, _I, _P]),
     "r2d2_lstm_seq_bwd": (_I, [_P] * 6 + [_I, _I, _I, _P]),
     "r2d2_torso_bwd_scratch_bytes": (_L, [_I]),
     "r2d2_torso_bwd_u8": (_I, [_P, _I, _I, _I, _I] + [_P] * 13 + [_P]),

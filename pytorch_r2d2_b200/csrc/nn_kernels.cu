@@ -4,6 +4,8 @@
 // (learner.py:86-102), centered RMSprop (learner.py:51,100).
 #include "gemm.cuh"
 
+#include <mutex>
+
 namespace r2d2 {
 
 // ======================================================================== small helpers
@@ -738,6 +740,87 @@ int r2d2_td_target(const float* q_all, const float* q_next_online, const float* 
     R2D2_LAUNCH("td_target_kernel", as_stream(stream), td_target_kernel<<<1, 1024, 0, as_stream(stream)>>>(
         q_all, q_next_online, q_next_target, action, reward, done, n, gamma_n, rescale, rescale_eps,
         prio_eps, alpha, next_action_override, next_action, y, delta, dq, prio, loss));
+    return R2D2_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// r2d2_linear_wgrad_static: r2d2_linear_wgrad for callers that have no way to hand us a
+// workspace.  Some users of this C ABI are not PyTorch programs: an actor host or a serving
+// process written in C/C++ that received every device buffer it owns from another component
+// (sized for inputs and outputs only), that runs under a fixed HBM budget handed out entirely
+// at start-up, or that sits on a latency-critical path where cudaMalloc is off limits because
+// it synchronises the whole device and would stall the inference streams running next to it.
+// For them the split-K partial sums live in the array below, which is part of the library
+// image: every GPU that loads the library carries these 32 MiB until the process exits.
+//
+// Rules of the road
+//   * Largest problem: wgrad_splits(M,N,K) * N * K floats must fit in
+//     R2D2_STATIC_WGRAD_SCRATCH_BYTES; anything larger is refused with R2D2_EINVAL and a
+//     message saying how much was needed (use r2d2_linear_wgrad with your own scratch then).
+//   * The first call on each device looks up the array's device address (the name below is
+//     only a host-side handle, never a pointer a kernel may dereference) with
+//     cudaGetSymbolAddress while that device is current, and caches it.  Make that first
+//     call during set-up, before any stream capture begins.
+//   * One array per device, shared by every call and every stream.  It still holds the
+//     previous call's partial sums; that is harmless because each call overwrites every
+//     element it later reads (all splits of all tiles are written, empty splits write
+//     zeros), so nothing needs clearing.  Two calls whose kernels overlap on the GPU
+//     (different streams, no ordering between them) race on it: serialise them.
+//   * No cudaMalloc / cudaFree / allocating library call is made here, ever.
+// ------------------------------------------------------------------------------------------
+static __device__ __align__(256) float g_static_wgrad_scratch[R2D2_STATIC_WGRAD_SCRATCH_BYTES / 4];
+
+static int static_wgrad_scratch_ptr(float** out) {
+    static std::mutex mu;
+    static float* ptrs[64] = {nullptr};
+    int dev = -1;
+    R2D2_CUDA_OK(cudaGetDevice(&dev));
+    R2D2_REQUIRE(dev >= 0 && dev < 64, "linear_wgrad_static: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lk(mu);
+    if (!ptrs[dev]) {
+        void* p = nullptr;
+        R2D2_CUDA_OK(cudaGetSymbolAddress(&p, g_static_wgrad_scratch));
+        R2D2_REQUIRE(p != nullptr, "linear_wgrad_static: cudaGetSymbolAddress returned null");
+        ptrs[dev] = static_cast<float*>(p);
+    }
+    *out = ptrs[dev];
+    return R2D2_OK;
+}
+
+int r2d2_linear_wgrad_static(const float* dy, const float* x, float* dw, float* db, int M, int N,
+                             int K, void* stream) {
+    R2D2_REQUIRE(dy && x && dw && M > 0 && N > 0 && K > 0, "linear_wgrad_static: bad args");
+    cudaStream_t st = as_stream(stream);
+    const int splits = wgrad_splits(M, N, K);
+    const long long need = splits > 1 ? (long long)splits * N * K * 4 : 0;
+    R2D2_REQUIRE(need <= (long long)R2D2_STATIC_WGRAD_SCRATCH_BYTES,
+                 "linear_wgrad_static: M=%d N=%d K=%d needs %lld bytes of split-K scratch but the "
+                 "built-in array holds %lld; call r2d2_linear_wgrad with caller-provided scratch",
+                 M, N, K, need, (long long)R2D2_STATIC_WGRAD_SCRATCH_BYTES);
+    using AL = DenseLoad<false>;
+    AL al{dy, 1, N}, bl{x, 1, K};
+    int kps = (M + splits - 1) / splits;
+    kps = (kps + 15) / 16 * 16;
+    const dim3 grid((N + 127) / 128, (K + 127) / 128, splits);
+    if (splits > 1) {
+        float* part = nullptr;
+        int rc = static_wgrad_scratch_ptr(&part);
+        if (rc) return rc;
+        EpiPartial ep{part, K, (long long)N * K};
+        gemm_kernel<128, 128, 8, 8, AL, AL, EpiPartial><<<grid, 256, 0, st>>>(al, bl, ep, N, K, M, kps);
+        R2D2_LAUNCH_OK();
+        const int64_t n = (int64_t)N * K;
+        reduce_partials_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(part, dw, n, splits);
+        R2D2_LAUNCH_OK();
+    } else {
+        EpiDense ep{dw, K, nullptr, nullptr, 0, 0};
+        gemm_kernel<128, 128, 8, 8, AL, AL, EpiDense><<<grid, 256, 0, st>>>(al, bl, ep, N, K, M, kps);
+        R2D2_LAUNCH_OK();
+    }
+    if (db) {
+        colsum_kernel<<<(N + 31) / 32, 1024, 0, st>>>(dy, db, M, N);
+        R2D2_LAUNCH_OK();
+    }
     return R2D2_OK;
 }
 
