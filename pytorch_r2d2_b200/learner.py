@@ -20,7 +20,7 @@ from copy import deepcopy
 import numpy as np
 import torch
 
-from . import engine
+from . import engine, parallel
 from .engine import Weights
 from .model import QNet
 from .params import FEAT, N_ACTIONS
@@ -93,8 +93,10 @@ class Learner:
         self.target_net = QNet(self.device, cell_size).to(self.device)
         self.target_net.load_state_dict(self.net.state_dict())
         self.save_model()
-        self.optim = FusedCenteredRMSprop(self.net)
         self.process_group = process_group
+        parallel.broadcast_flat_params(self.net.flat_parameters(), 0, process_group)
+        parallel.broadcast_flat_params(self.target_net.flat_parameters(), 0, process_group)
+        self.optim = FusedCenteredRMSprop(self.net)
         self._ws = None
         self.last = None  # tensors of the last step (q, y, delta, loss, ...) for inspection
 
@@ -236,12 +238,8 @@ class Learner:
         engine.torso_bwd_u8(slab, BI, L, ws["a1_on"][BI * B: T * B], ws["a2_on"][BI * B: T * B], feat_l,
                             ws["dfeat"], w, g, scratch)
 
-        # ---- optimiser (data-parallel: sum gradients over ranks, scale by 1/world in K10)
-        if self.process_group is not None or (torch.distributed.is_available()
-                                              and torch.distributed.is_initialized()
-                                              and torch.distributed.get_world_size() > 1):
-            torch.distributed.all_reduce(self.optim.grad, group=self.process_group)
-            self.optim.grad_scale = 1.0 / torch.distributed.get_world_size(self.process_group)
+        # ---- optimiser (data-parallel: sum gradients over ranks, 1/world folded into K10)
+        self.optim.grad_scale = parallel.allreduce_flat_grad(self.optim.grad, self.process_group)
         self.optim.step()
 
         # ---- priorities (learner.py:102-104)
