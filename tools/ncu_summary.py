@@ -1,0 +1,24 @@
+"""Key metrics of an `ncu --set full` report, one block per profiled launch (read with no GPU)."""
+import csv, subprocess, sys
+WANT = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+        "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+        "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+        "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
+        "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
+        "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread",
+        "launch__grid_size", "launch__block_size", "launch__shared_mem_per_block_dynamic",
+        "launch__shared_mem_per_block_static", "launch__occupancy_limit_registers",
+        "launch__occupancy_limit_shared_mem", "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum",
+        "lts__t_bytes.sum", "lts__t_sector_hit_rate.pct"]
+out = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+rows = list(csv.reader(out.splitlines()))
+hdr, units = rows[0], rows[1]
+for row in rows[2:]:
+    d = dict(zip(hdr, zip(units, row)))
+    print("kernel:", d["Kernel Name"][1][:160])
+    for w in WANT:
+        if w in d:
+            print(f"  {w:72s} {d[w][1]:>16s} {d[w][0]}")
+    rd, wr = d.get("dram__bytes_read.sum"), d.get("dram__bytes_write.sum")
+    print()
