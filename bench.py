@@ -43,6 +43,8 @@ def parse():
                     help="e2e leg: fresh transitions uploaded from pinned host memory per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--tma-gather", action="store_true")
+    ap.add_argument("--precision", default="bf16", choices=["fp32", "bf16"],
+                    help="bf16: tcgen05 tensor-core contractions (2e-2 class); fp32: FFMA (1e-5 class)")
     return ap.parse_args()
 
 
@@ -110,6 +112,7 @@ def work_model(B, BI, L, n, H):
         "conv2_fwd": (conv["conv2"] * per_step_frames_fwd, 2),
         "conv3_fwd": (conv["conv3"] * per_step_frames_fwd, 2),
         "linear_fwd": (lin_fwd, 5),
+        "tc_gemm_kernel": (lin_fwd + lin_dgrad + lin_wgrad, 10),
         "linear_dgrad": (lin_dgrad, 2),
         "linear_wgrad": (lin_wgrad, 3),
         "lstm_step_fwd_kernel": (2 * B * 4 * H * H * steps_fwd, steps_fwd),
@@ -268,7 +271,8 @@ def run_ours(args):
     B, BI, Ln, n, H = args.batch, args.burn_in, args.learn, args.n_step, args.cell
 
     torch.manual_seed(0)
-    L = Learner(1, {}, device=f"cuda:{local}", cell_size=H, memory_size=args.memory_size)
+    L = Learner(1, {}, device=f"cuda:{local}", cell_size=H, memory_size=args.memory_size,
+                precision=args.precision)
     L.batch_size, L.burn_in_length, L.learning_length, L.bootstrap_steps = B, BI, Ln, n
     L.sequence_length = BI + Ln
     L.replay_memory.use_tma_gather = args.tma_gather
@@ -390,9 +394,11 @@ def run_ours(args):
     line = {
         "metric": "learner_sequences_per_sec", "value": value, "unit": "seq/s", "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "bf16" if args.precision == "bf16" else "f32",
         "data": "synthetic",
         "config": workload_config(args, extra={
+            "precision": args.precision,
             "replay_slots_per_gpu": args.memory_size, "l2_policy": "inputs larger than L2 "
             "(replay ring >> 126 MB; each step gathers a fresh 154 MB slab)",
             "parallelism": f"dp{world}", "global_batch": world * B,

@@ -138,6 +138,11 @@ int r2d2_lstm_seq_fwd(const float* xproj, const float* w_hh, float* hs_ext, floa
 int r2d2_head_fwd(const float* hs, const float* w1, const float* b1, const float* w2,
                   const float* b2, float* hid, float* q, int M, int H, void* stream);
 
+/* second half of r2d2_head_fwd alone (val/adv output layers + dueling combine) for callers that
+ * computed hid = relu(hs.w1^T + b1) themselves (bf16 tensor-core path) */
+int r2d2_head_out(const float* hid, const float* w2, const float* b2, float* q, int M, int H,
+                  void* stream);
+
 /* ------------------------------------------------------------------ target / TD (K7)
  * learner.py:86-102: a* = argmax q_next_online (first max), y = r + gamma_n*Qt[a*]*(1-done)
  * (optionally h(r + gamma_n*h^-1(Qt)*(1-done)), NOT in the reference, default off),
@@ -172,6 +177,8 @@ int r2d2_linear_wgrad(const float* dy, const float* x, float* dw, float* db, int
 #define R2D2_STATIC_WGRAD_SCRATCH_BYTES (32 << 20)
 int r2d2_linear_wgrad_static(const float* dy, const float* x, float* dw, float* db, int M, int N,
                              int K, void* stream);
+/* db[N] = column sums of dy[M,N] (bias gradients when the weight gradient runs on tensor cores) */
+int r2d2_colsum(const float* dy, float* db, int M, int N, void* stream);
 /* BPTT over the learn window: dhs [T,B,H] is dL/dh_t from the head; gates/cs_ext from
  * r2d2_lstm_seq_fwd.  Writes dgates [T,B,4H] (pre-activation grads).  dc_work [B,H] carries
  * dL/dc between steps (caller-owned, contents undefined on entry). */
@@ -190,6 +197,26 @@ int r2d2_torso_bwd_f32(const float* frames, int R, const float* a1, const float*
                        const float* feat, float* dfeat, const float* w2, const float* w3,
                        float* dw1, float* db1, float* dw2, float* db2, float* dw3, float* db3,
                        void* scratch, void* stream);
+
+/* ------------------------------------------------------------------ bf16 tensor-core path
+ * (north-star 2e-2 precision class; tcgen05.mma + TMEM accumulators + TMA operand staging)
+ * y[M,N] = x[M,K] . w[N,K]^T + bias1 + bias2 (ReLU optional); x, w bf16 row-major with K
+ * contiguous (K % 8 == 0, N % 4 == 0); either or both outputs (f32 / bf16) may be given.
+ * The same entry point serves model.py:55 (x.W_ih^T), the dueling hidden layer (model.py:26-36)
+ * and - on transposed bf16 copies - the data and weight gradients of both. */
+int r2d2_tc_linear(const void* x_bf16, const void* w_bf16, const float* bias1, const float* bias2,
+                   float* y_f32, void* y_bf16, int M, int N, int K, int relu, void* stream);
+/* Error-compensated variant ("bf16x3"): x = x_hi + x_lo, w = w_hi + w_lo (r2d2_split_bf16) and
+ * y = x_hi.w_hi^T + x_hi.w_lo^T + x_lo.w_hi^T, fp32 accumulation in TMEM -- operand error 2^-16
+ * instead of 2^-9.  Used for FORWARD contractions: a 1e-3 forward perturbation flips ReLU masks
+ * and moves the (heavily cancelling) gradient sums by several percent, see DESIGN.md section 2. */
+int r2d2_tc_linear_x3(const void* x_hi, const void* x_lo, const void* w_hi, const void* w_lo,
+                      const float* bias1, const float* bias2, float* y_f32, void* y_bf16, int M,
+                      int N, int K, int relu, void* stream);
+int r2d2_split_bf16(const float* in, void* hi_bf16, void* lo_bf16, int64_t n, void* stream);
+/* f32 -> bf16 copies feeding r2d2_tc_linear: flat cast, and out[c,r] = in[r,c] */
+int r2d2_cast_bf16(const float* in, void* out_bf16, int64_t n, void* stream);
+int r2d2_transpose_cast_bf16(const float* in, void* out_bf16, int R, int C, void* stream);
 
 /* ------------------------------------------------------------------ optimiser (K10)
  * torch.optim.RMSprop(centered=True) of learner.py:51 over a flat f32 buffer:

@@ -63,9 +63,37 @@ def torso_kink_margin(p: dict, frames: torch.Tensor) -> float:
     return float(min(z1.abs().min(), z2.abs().min(), z3.abs().min()))
 
 
+class _Bf16Linear(torch.autograd.Function):
+    """x @ w.T with both operands rounded to bf16 and fp32 accumulation, in forward AND in both
+    backward contractions -- the arithmetic of the tensor-core path (tc_gemm.cu), so that the
+    bf16 kernels can be checked tightly against a same-precision restatement."""
+
+    @staticmethod
+    def forward(ctx, x, w):
+        ctx.save_for_backward(x, w)
+        return x.bfloat16().float() @ w.bfloat16().float().T
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w = ctx.saved_tensors
+        d = dy.bfloat16().float()
+        return d @ w.bfloat16().float(), d.T @ x.bfloat16().float()
+
+
+# which contractions are emulated in bf16 (set by train_step(..., tc_emulation=...))
+_TC = {"proj": False, "head": False}
+
+
+def _linear(x, w, b, kind):
+    if _TC.get(kind):
+        y = _Bf16Linear.apply(x, w)
+        return y + b if b is not None else y
+    return F.linear(x, w, b)
+
+
 def lstm_step(p: dict, x, h, c):
     """One LSTMCell step, gate order i,f,g,o (model.py:24,55)."""
-    g = F.linear(x, p["lstm.weight_ih"], p["lstm.bias_ih"]) + \
+    g = _linear(x, p["lstm.weight_ih"], p["lstm.bias_ih"], "proj") + \
         F.linear(h, p["lstm.weight_hh"], p["lstm.bias_hh"])
     i, f, gg, o = g.chunk(4, dim=1)
     c2 = torch.sigmoid(f) * c + torch.sigmoid(i) * torch.tanh(gg)
@@ -75,9 +103,9 @@ def lstm_step(p: dict, x, h, c):
 
 def head(p: dict, hs: torch.Tensor) -> torch.Tensor:
     """Dueling head: val + adv - mean_a(adv) (model.py:26-36,62-64)."""
-    val = F.linear(F.relu(F.linear(hs, p["val.0.weight"], p["val.0.bias"])),
+    val = F.linear(F.relu(_linear(hs, p["val.0.weight"], p["val.0.bias"], "head")),
                    p["val.2.weight"], p["val.2.bias"])
-    adv = F.linear(F.relu(F.linear(hs, p["adv.0.weight"], p["adv.0.bias"])),
+    adv = F.linear(F.relu(_linear(hs, p["adv.0.weight"], p["adv.0.bias"], "head")),
                    p["adv.2.weight"], p["adv.2.bias"])
     return val + adv - adv.mean(1, keepdim=True)
 
@@ -131,7 +159,7 @@ def rmsprop_centered(param, grad, square_avg, grad_avg, lr=0.00025 / 4.0, alpha=
 
 def train_step(p_online: dict, p_target: dict, batch: dict, *, burn_in: int, n_step: int,
                gamma: float = 0.99, alpha: float = 0.6, prio_eps: float = 1e-6,
-               rescale: bool = False, next_action_override=None) -> dict:
+               rescale: bool = False, next_action_override=None, tc_emulation=()) -> dict:
     """``Learner.train`` from the sampled batch to the per-step priorities
     (learner.py:71-102), without the optimiser step (see ``rmsprop_centered``).
 
@@ -139,6 +167,18 @@ def train_step(p_online: dict, p_target: dict, batch: dict, *, burn_in: int, n_s
     double-Q action pass) exactly as the reference's stateful module does.
     `batch` holds torch f32 tensors in the reference's layouts; `action` is int64.
     """
+    for k in _TC:
+        _TC[k] = k in tc_emulation
+    try:
+        return _train_step(p_online, p_target, batch, burn_in, n_step, gamma, alpha, prio_eps,
+                           rescale, next_action_override)
+    finally:
+        for k in _TC:
+            _TC[k] = False
+
+
+def _train_step(p_online, p_target, batch, burn_in, n_step, gamma, alpha, prio_eps, rescale,
+                next_action_override):
     po = {k: v.detach().clone().requires_grad_(True) for k, v in p_online.items()}
     BI = burn_in
     state, next_state = batch["state"], batch["next_state"]

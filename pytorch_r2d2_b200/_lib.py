@@ -38,6 +38,8 @@ PROTOTYPES = {
     "r2d2_linear_fwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "r2d2_lstm_seq_fwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _P]),
     "r2d2_head_fwd": (_I, [_P] * 7 + [_I, _I, _P]),
+    "r2d2_head_out": (_I, [_P, _P, _P, _P, _I, _I, _P]),
+    "r2d2_colsum": (_I, [_P, _P, _I, _I, _P]),
     "r2d2_td_target": (_I, [_P] * 6 + [_I, _F, _I, _F, _F, _F] + [_P] * 7 + [_P]),
     "r2d2_head_bwd": (_I, [_P] * 6 + [_I, _I, _P]),
     "r2d2_linear_dgrad": (_I, [_P, _P, _P, _I, _I, _I, _I, _P]),
@@ -48,6 +50,11 @@ PROTOTYPES = {
     "r2d2_torso_bwd_scratch_bytes": (_L, [_I]),
     "r2d2_torso_bwd_u8": (_I, [_P, _I, _I, _I, _I] + [_P] * 13 + [_P]),
     "r2d2_torso_bwd_f32": (_I, [_P, _I] + [_P] * 13 + [_P]),
+    "r2d2_tc_linear": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
+    "r2d2_tc_linear_x3": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
+    "r2d2_split_bf16": (_I, [_P, _P, _P, _L, _P]),
+    "r2d2_cast_bf16": (_I, [_P, _P, _L, _P]),
+    "r2d2_transpose_cast_bf16": (_I, [_P, _P, _I, _I, _P]),
     "r2d2_rmsprop_centered": (_I, [_P, _P, _P, _P, _L, _D, _D, _D, _D, _P]),
 }
 
@@ -85,7 +92,7 @@ def stream_ptr() -> ctypes.c_void_p:
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
-_DT = {"f32": torch.float32, "f64": torch.float64, "u8": torch.uint8, "i8": torch.int8,
+_DT = {"bf16": torch.bfloat16, "f32": torch.float32, "f64": torch.float64, "u8": torch.uint8, "i8": torch.int8,
        "i64": torch.int64}
 
 

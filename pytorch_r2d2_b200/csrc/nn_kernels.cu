@@ -720,6 +720,19 @@ int r2d2_head_fwd(const float* hs, const float* w1, const float* b1, const float
     return R2D2_OK;
 }
 
+int r2d2_head_out(const float* hid, const float* w2, const float* b2, float* q, int M, int H,
+                  void* stream) {
+    R2D2_REQUIRE(hid && w2 && b2 && q && M > 0 && H > 0, "head_out: bad args");
+    R2D2_LAUNCH("head_out_kernel", as_stream(stream), head_out_kernel<<<(M + 7) / 8, 256, 0, as_stream(stream)>>>(hid, w2, b2, q, M, H));
+    return R2D2_OK;
+}
+
+int r2d2_colsum(const float* dy, float* db, int M, int N, void* stream) {
+    R2D2_REQUIRE(dy && db && M > 0 && N > 0, "colsum: bad args");
+    R2D2_LAUNCH("colsum_kernel", as_stream(stream), colsum_kernel<<<(N + 31) / 32, 1024, 0, as_stream(stream)>>>(dy, db, M, N));
+    return R2D2_OK;
+}
+
 int r2d2_head_bwd(const float* dq, const float* hid, const float* w2, float* dhid, float* dw2,
                   float* db2, int M, int H, void* stream) {
     R2D2_REQUIRE(dq && hid && w2 && dhid && dw2 && db2 && M > 0 && H > 0 && H % 32 == 0,

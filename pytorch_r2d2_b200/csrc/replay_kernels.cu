@@ -2,6 +2,7 @@
 // priority scatter and sequence-priority refresh (K8).  Integer/byte work: HBM- or
 // latency-bound; no tensor cores.  Reference semantics: replay_memory.py:93-119,175-262.
 #include "common.cuh"
+#include "ptx.cuh"
 
 #include <atomic>
 #include <map>
@@ -212,47 +213,6 @@ gather_rows_kernel(const uint4* __restrict__ state, int64_t M,
 
 // ---- TMA (bulk async copy) variant: global -> smem -> global, one elected thread drives a
 // 4-deep ring of 28 224-byte row buffers per CTA; persistent grid.
-__device__ __forceinline__ uint32_t smem_u32(const void* p) {
-    return (uint32_t)__cvta_generic_to_shared(p);
-}
-__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
-                 "r"(bytes)
-                 : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
-    uint32_t ok;
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok)
-        : "r"(smem_u32(bar)), "r"(parity)
-        : "memory");
-    return ok != 0;
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    // bounded: a lost transaction traps instead of hanging the GPU
-    for (uint32_t it = 0; it < (1u << 28); ++it)
-        if (mbar_try_wait(bar, parity)) return;
-    __trap();
-}
-__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32_t bytes,
-                                         uint64_t* bar) {
-    asm volatile(
-        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-        ::"r"(smem_u32(dst_smem)), "l"(src), "r"(bytes), "r"(smem_u32(bar))
-        : "memory");
-}
-__device__ __forceinline__ void bulk_s2g(void* dst, const void* src_smem, uint32_t bytes) {
-    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst),
-                 "r"(smem_u32(src_smem)), "r"(bytes)
-                 : "memory");
-}
-
 constexpr int TMA_STAGES = 4;
 
 __global__ void __launch_bounds__(32)
@@ -263,8 +223,7 @@ gather_rows_tma_kernel(const uint8_t* __restrict__ state, int64_t M,
     __shared__ uint64_t full[TMA_STAGES];
     if (threadIdx.x != 0) return;
     for (int i = 0; i < TMA_STAGES; ++i) mbar_init(&full[i], 1);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    mbar_fence_init();
     const int64_t total = (int64_t)B * S;
     const int64_t per = (total + gridDim.x - 1) / gridDim.x;
     const int64_t lo = blockIdx.x * per;

@@ -1,0 +1,312 @@
+// bf16 tensor-core path (north-star "2e-2" precision class): tcgen05.mma with TMEM accumulators,
+// operands staged by TMA into 128B-swizzled shared memory through an mbarrier ring.
+//
+//   C[M,N] = A[M,K] . B[N,K]^T  (+ bias1[n] + bias2[n]) (ReLU)     A, B bf16 K-major; C f32/bf16
+//
+// One 128 x BN output tile per CTA.  192 threads: warp 0 = TMA producer (one elected lane),
+// warp 1 = TMEM allocator + MMA issuer (one elected lane), warps 2-5 = epilogue (each owns the
+// TMEM lane quarter warp_idx % 4; tcgen05.ld 32x32b -> registers -> global).
+// Used for: LSTM input projection x.W_ih^T (model.py:55), dueling hidden layer (model.py:26-36),
+// and, with transposed bf16 copies of the operands, their data/weight gradients.
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace r2d2 {
+
+constexpr int TC_BM = 128, TC_BK = 64, TC_STAGES = 6;
+
+struct TcEpilogue {
+    float* c32;             // may be null
+    __nv_bfloat16* c16;     // may be null
+    long long ldc;
+    const float* bias1;     // per output column, may be null
+    const float* bias2;
+    int relu;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(192, 1)
+tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+               const __grid_constant__ CUtensorMap tma_a_lo,
+               const __grid_constant__ CUtensorMap tma_b_lo, const int nseg, const TcEpilogue ep,
+               const int M, const int N, const int K) {
+    constexpr uint32_t A_BYTES = TC_BM * TC_BK * 2, B_BYTES = BN * TC_BK * 2;
+    constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t full_bar[TC_STAGES], empty_bar[TC_STAGES], acc_bar;
+    __shared__ uint32_t tmem_slot;
+
+    // SWIZZLE_128B atoms must start on 1024-byte boundaries
+    const uint32_t raw = smem_u32(smem_raw);
+    uint8_t* tiles = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = blockIdx.x * TC_BM, n0 = blockIdx.y * BN;
+    // nseg == 1: C = A.B^T in plain bf16.  nseg == 3: error-compensated "bf16x3" -- A = A_hi+A_lo,
+    // B = B_hi+B_lo (each the bf16 rounding of the remainder) and C = A_hi.B_hi + A_hi.B_lo +
+    // A_lo.B_hi accumulated in fp32 in TMEM: ~2^-16 relative operand error instead of 2^-9.
+    const int kb_per_seg = (K + TC_BK - 1) / TC_BK;
+    const int num_kb = kb_per_seg * nseg;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tma_a);
+        tma_prefetch_desc(&tma_b);
+        for (int s = 0; s < TC_STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(&acc_bar, 1);
+        mbar_fence_init();
+    }
+    if (warp == 1) tmem_alloc(&tmem_slot, BN);   // BN fp32 accumulator columns x 128 lanes
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % TC_STAGES;
+                const uint32_t ph = (kb / TC_STAGES) & 1;
+                mbar_wait(&empty_bar[s], ph ^ 1);            // slot free (first pass: immediate)
+                mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+                uint8_t* a_dst = tiles + (size_t)s * STAGE_BYTES;
+                const int seg = kb / kb_per_seg, kk = (kb - seg * kb_per_seg) * TC_BK;
+                tma_load_2d(a_dst, seg == 2 ? &tma_a_lo : &tma_a, kk, m0, &full_bar[s]);
+                tma_load_2d(a_dst + A_BYTES, seg == 1 ? &tma_b_lo : &tma_b, kk, n0, &full_bar[s]);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(TC_BM, BN);
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % TC_STAGES;
+                const uint32_t ph = (kb / TC_STAGES) & 1;
+                mbar_wait(&full_bar[s], ph);                 // TMA bytes have landed
+                tc_fence_after();
+                const uint32_t a_addr = smem_u32(tiles + (size_t)s * STAGE_BYTES);
+                const uint32_t b_addr = a_addr + A_BYTES;
+#pragma unroll
+                for (int k = 0; k < TC_BK / 16; ++k)         // UMMA_K = 16 bf16 = 32 bytes
+                    umma_f16(tmem_base, umma_desc_k_sw128(a_addr + k * 32),
+                             umma_desc_k_sw128(b_addr + k * 32), idesc, (kb | k) != 0);
+                umma_commit(&empty_bar[s]);                  // frees the slot when the MMAs finish
+            }
+            umma_commit(&acc_bar);                           // accumulator complete
+        }
+    } else {
+        // ---- epilogue: TMEM -> registers -> global, one output row per thread
+        mbar_wait(&acc_bar, 0);
+        tc_fence_after();
+        const int q = warp & 3;                              // TMEM lane quarter of this warp
+        const int m = m0 + q * 32 + lane;
+#pragma unroll 1
+        for (int c = 0; c < BN; c += 32) {
+            uint32_t r[32];
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c, r);
+            tmem_ld_wait();
+            if (m < M) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) {
+                    const int n = n0 + c + j;
+                    if (n >= N) break;
+                    float v[4];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        float x = __uint_as_float(r[j + e]);
+                        if (ep.bias1) x += __ldg(ep.bias1 + n + e);
+                        if (ep.bias2) x += __ldg(ep.bias2 + n + e);
+                        if (ep.relu) x = fmaxf(x, 0.f);
+                        v[e] = x;
+                    }
+                    if (ep.c32)
+                        *reinterpret_cast<float4*>(ep.c32 + (long long)m * ep.ldc + n) =
+                            make_float4(v[0], v[1], v[2], v[3]);
+                    if (ep.c16) {
+                        __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]);
+                        __nv_bfloat162 hi = __floats2bfloat162_rn(v[2], v[3]);
+                        uint2 pk;
+                        pk.x = *reinterpret_cast<uint32_t*>(&lo);
+                        pk.y = *reinterpret_cast<uint32_t*>(&hi);
+                        *reinterpret_cast<uint2*>(ep.c16 + (long long)m * ep.ldc + n) = pk;
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, BN);
+}
+
+// ---------------------------------------------------------------- host: tensor maps
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) ==
+                cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+// row-major bf16 [rows, cols] (cols contiguous); box = [box_rows, 64 cols], 128B swizzle,
+// out-of-bounds elements read as zero
+static int make_tmap(CUtensorMap* tm, const void* base, long long rows, long long cols,
+                     int box_rows) {
+    EncodeTiledFn fn = encode_fn();
+    R2D2_REQUIRE(fn, "tc_gemm: cuTensorMapEncodeTiled is unavailable in this driver");
+    R2D2_REQUIRE(((uintptr_t)base % 16) == 0 && (cols * 2) % 16 == 0,
+                 "tc_gemm: operand base must be 16-byte aligned and K a multiple of 8 (K=%lld)", cols);
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
+    cuuint32_t box[2] = {(cuuint32_t)TC_BK, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides,
+                    box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    R2D2_REQUIRE(r == CUDA_SUCCESS, "tc_gemm: cuTensorMapEncodeTiled failed with %d", (int)r);
+    return R2D2_OK;
+}
+
+// ---------------------------------------------------------------- casts / transposes
+__global__ void cast_bf16_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out,
+                                 int64_t n) {
+    const int64_t n4 = n / 4;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const float4 v = reinterpret_cast<const float4*>(in)[i];
+        __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+        uint2 pk;
+        pk.x = *reinterpret_cast<uint32_t*>(&lo);
+        pk.y = *reinterpret_cast<uint32_t*>(&hi);
+        reinterpret_cast<uint2*>(out)[i] = pk;
+    }
+    if (blockIdx.x == 0)
+        for (int64_t i = n4 * 4 + threadIdx.x; i < n; i += blockDim.x) out[i] = __float2bfloat16_rn(in[i]);
+}
+
+// hi = bf16(x), lo = bf16(x - hi): x ~= hi + lo to ~2^-17 relative
+__global__ void split_bf16_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ hi,
+                                  __nv_bfloat16* __restrict__ lo, int64_t n) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const float x = in[i];
+        const __nv_bfloat16 h = __float2bfloat16_rn(x);
+        hi[i] = h;
+        lo[i] = __float2bfloat16_rn(x - __bfloat162float(h));
+    }
+}
+
+// out[c, r] = bf16(in[r, c]); 32x32 tiles through shared memory
+__global__ void transpose_cast_bf16_kernel(const float* __restrict__ in,
+                                           __nv_bfloat16* __restrict__ out, int R, int C) {
+    __shared__ float t[32][33];
+    const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int r = r0 + i, c = c0 + threadIdx.x;
+        t[i][threadIdx.x] = (r < R && c < C) ? in[(int64_t)r * C + c] : 0.f;
+    }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int c = c0 + i, r = r0 + threadIdx.x;
+        if (c < C && r < R) out[(int64_t)c * R + r] = __float2bfloat16_rn(t[threadIdx.x][i]);
+    }
+}
+
+}  // namespace r2d2
+
+using namespace r2d2;
+
+extern "C" {
+
+static int tc_linear_impl(const void* x_hi, const void* x_lo, const void* w_hi, const void* w_lo,
+                          const float* bias1, const float* bias2, float* y_f32, void* y_bf16, int M,
+                          int N, int K, int relu, void* stream) {
+    R2D2_REQUIRE(x_hi && w_hi && (y_f32 || y_bf16) && M > 0 && N > 0 && K > 0, "tc_linear: bad args");
+    R2D2_REQUIRE((x_lo == nullptr) == (w_lo == nullptr), "tc_linear: give both lo parts or neither");
+    R2D2_REQUIRE(N % 4 == 0, "tc_linear: N must be a multiple of 4 (N=%d)", N);
+    R2D2_REQUIRE(!y_f32 || ((uintptr_t)y_f32 % 16) == 0, "tc_linear: y_f32 must be 16-byte aligned");
+    R2D2_REQUIRE(!y_bf16 || ((uintptr_t)y_bf16 % 8) == 0, "tc_linear: y_bf16 must be 8-byte aligned");
+    constexpr int BN = 128;
+    CUtensorMap ta, tb, ta_lo, tb_lo;
+    int rc = make_tmap(&ta, x_hi, M, K, TC_BM);
+    if (rc) return rc;
+    rc = make_tmap(&tb, w_hi, N, K, BN);
+    if (rc) return rc;
+    rc = make_tmap(&ta_lo, x_lo ? x_lo : x_hi, M, K, TC_BM);
+    if (rc) return rc;
+    rc = make_tmap(&tb_lo, w_lo ? w_lo : w_hi, N, K, BN);
+    if (rc) return rc;
+    const int smem = TC_STAGES * (TC_BM * TC_BK * 2 + BN * TC_BK * 2) + 1024;
+    static bool attr_set = false;
+    if (!attr_set) {
+        R2D2_CUDA_OK(cudaFuncSetAttribute(tc_gemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr_set = true;
+    }
+    TcEpilogue ep{y_f32, reinterpret_cast<__nv_bfloat16*>(y_bf16), N, bias1, bias2, relu};
+    dim3 grid((M + TC_BM - 1) / TC_BM, (N + BN - 1) / BN);
+    const int nseg = x_lo ? 3 : 1;
+    R2D2_LAUNCH(nseg == 3 ? "tc_gemm_kernel_x3" : "tc_gemm_kernel", as_stream(stream),
+                tc_gemm_kernel<BN><<<grid, 192, smem, as_stream(stream)>>>(ta, tb, ta_lo, tb_lo, nseg,
+                                                                         ep, M, N, K));
+    return R2D2_OK;
+}
+
+int r2d2_tc_linear(const void* x_bf16, const void* w_bf16, const float* bias1, const float* bias2,
+                   float* y_f32, void* y_bf16, int M, int N, int K, int relu, void* stream) {
+    return tc_linear_impl(x_bf16, nullptr, w_bf16, nullptr, bias1, bias2, y_f32, y_bf16, M, N, K, relu,
+                          stream);
+}
+
+int r2d2_tc_linear_x3(const void* x_hi, const void* x_lo, const void* w_hi, const void* w_lo,
+                      const float* bias1, const float* bias2, float* y_f32, void* y_bf16, int M,
+                      int N, int K, int relu, void* stream) {
+    R2D2_REQUIRE(x_lo && w_lo, "tc_linear_x3: lo parts required");
+    return tc_linear_impl(x_hi, x_lo, w_hi, w_lo, bias1, bias2, y_f32, y_bf16, M, N, K, relu, stream);
+}
+
+int r2d2_split_bf16(const float* in, void* hi_bf16, void* lo_bf16, int64_t n, void* stream) {
+    R2D2_REQUIRE(in && hi_bf16 && lo_bf16 && n > 0, "split_bf16: bad args");
+    int64_t blocks = (n + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    R2D2_LAUNCH("split_bf16_kernel", as_stream(stream),
+                split_bf16_kernel<<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(
+                    in, reinterpret_cast<__nv_bfloat16*>(hi_bf16),
+                    reinterpret_cast<__nv_bfloat16*>(lo_bf16), n));
+    return R2D2_OK;
+}
+
+int r2d2_cast_bf16(const float* in, void* out_bf16, int64_t n, void* stream) {
+    R2D2_REQUIRE(in && out_bf16 && n > 0, "cast_bf16: bad args");
+    R2D2_REQUIRE(((uintptr_t)in % 16) == 0 && ((uintptr_t)out_bf16 % 8) == 0, "cast_bf16: misaligned");
+    int64_t blocks = (n / 4 + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    if (blocks < 1) blocks = 1;
+    R2D2_LAUNCH("cast_bf16_kernel", as_stream(stream),
+                cast_bf16_kernel<<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(
+                    in, reinterpret_cast<__nv_bfloat16*>(out_bf16), n));
+    return R2D2_OK;
+}
+
+int r2d2_transpose_cast_bf16(const float* in, void* out_bf16, int R, int C, void* stream) {
+    R2D2_REQUIRE(in && out_bf16 && R > 0 && C > 0, "transpose_cast_bf16: bad args");
+    dim3 grid((C + 31) / 32, (R + 31) / 32), block(32, 8);
+    R2D2_LAUNCH("transpose_cast_bf16_kernel", as_stream(stream),
+                transpose_cast_bf16_kernel<<<grid, block, 0, as_stream(stream)>>>(
+                    in, reinterpret_cast<__nv_bfloat16*>(out_bf16), R, C));
+    return R2D2_OK;
+}
+
+}  // extern "C"

@@ -67,6 +67,16 @@ def head_fwd(hs, w: Weights, hid, q):
               P(hid, "f32"), P(q, "f32"), M, H, S())
 
 
+def head_out(hid, w: Weights, q):
+    M, H2 = hid.shape
+    _lib.call("r2d2_head_out", P(hid, "f32"), P(w.head_w2), P(w.head_b2), P(q, "f32"), M, H2 // 2, S())
+
+
+def colsum(dy, db):
+    M, N = dy.shape
+    _lib.call("r2d2_colsum", P(dy, "f32"), P(db, "f32"), M, N, S())
+
+
 def td_target(q_all, qn_on, qn_tg, action, reward, done, gamma_n, out, *, rescale=False,
               rescale_eps=1e-3, prio_eps=1e-6, alpha=0.6, next_action_override=None):
     n = q_all.shape[0]
@@ -127,6 +137,37 @@ def torso_bwd_f32(frames, a1, a2, feat, dfeat, w: Weights, g: Weights, scratch):
 def rmsprop_centered(param, grad, sq, ga, lr, alpha, eps, grad_scale=1.0):
     _lib.call("r2d2_rmsprop_centered", P(param, "f32"), P(grad, "f32"), P(sq, "f32"), P(ga, "f32"),
               param.numel(), float(lr), float(alpha), float(eps), float(grad_scale), S())
+
+
+# ---------------------------------------------------------------------------- bf16 tensor-core ops
+def tc_linear(x16, w16, b1, b2, y32=None, y16=None, relu=False):
+    M, K = x16.shape
+    N = w16.shape[0]
+    assert w16.shape[1] == K
+    _lib.call("r2d2_tc_linear", P(x16, "bf16"), P(w16, "bf16"), P(b1, "f32", True), P(b2, "f32", True),
+              P(y32, "f32", True), P(y16, "bf16", True), M, N, K, int(relu), S())
+
+
+def tc_linear_x3(x_hi, x_lo, w_hi, w_lo, b1, b2, y32=None, y16=None, relu=False):
+    M, K = x_hi.shape
+    N = w_hi.shape[0]
+    _lib.call("r2d2_tc_linear_x3", P(x_hi, "bf16"), P(x_lo, "bf16"), P(w_hi, "bf16"), P(w_lo, "bf16"),
+              P(b1, "f32", True), P(b2, "f32", True), P(y32, "f32", True), P(y16, "bf16", True),
+              M, N, K, int(relu), S())
+
+
+def split_bf16(x, hi, lo):
+    _lib.call("r2d2_split_bf16", P(x, "f32"), P(hi, "bf16"), P(lo, "bf16"), x.numel(), S())
+
+
+def cast_bf16(x, out):
+    _lib.call("r2d2_cast_bf16", P(x, "f32"), P(out, "bf16"), x.numel(), S())
+
+
+def transpose_cast_bf16(x, out):
+    R, C = x.shape
+    assert out.shape == (C, R)
+    _lib.call("r2d2_transpose_cast_bf16", P(x, "f32"), P(out, "bf16"), R, C, S())
 
 
 # ---------------------------------------------------------------------------- compositions

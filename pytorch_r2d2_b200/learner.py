@@ -62,7 +62,7 @@ class FusedCenteredRMSprop:
 
 class Learner:
     def __init__(self, n_actors, shared_dict, device="cuda:0", *, cell_size=256, memory_size=500000,
-                 rescale=False, process_group=None):
+                 rescale=False, process_group=None, precision="fp32"):
         # params (learner.py:20-28)
         self.gamma = 0.99
         self.alpha = 0.6
@@ -74,6 +74,12 @@ class Learner:
         self.n_actors = n_actors
         self.rescale = rescale
         self.rescale_eps = 1e-3
+        # "fp32": every contraction in fp32 FFMA (1e-5 class vs the reference);
+        # "bf16": dense contractions on tcgen05 tensor cores, bf16 operands / fp32 accumulate
+        #         (2e-2 class, BASELINE.json north_star)
+        if precision not in ("fp32", "bf16"):
+            raise ValueError("precision must be 'fp32' or 'bf16'")
+        self.precision = precision
         self.memory_path = os.path.join("./", "logs", "memory")
         # memory (learner.py:34-41)
         self.burn_in_length = 10
@@ -142,7 +148,7 @@ class Learner:
     def _workspace(self):
         B, BI, L, n, H = (self.batch_size, self.burn_in_length, self.learning_length,
                           self.bootstrap_steps, self.cell_size)
-        key = (B, BI, L, n, H)
+        key = (B, BI, L, n, H, self.precision)
         if self._ws is not None and self._ws["key"] == key:
             return self._ws
         dev = self.net.flat_parameters().device
@@ -168,6 +174,18 @@ class Learner:
                      engine.linear_wgrad_scratch_bytes(M, 4 * H, FEAT),
                      engine.torso_bwd_scratch_bytes(M))
         ws["scratch"] = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        if self.precision == "bf16":
+            if M % 8 != 0:
+                raise ValueError("bf16 mode needs learning_length*batch_size to be a multiple of 8 "
+                                 "(TMA row pitch of the transposed gradient operands)")
+            h = lambda *shape: torch.empty(shape, dtype=torch.bfloat16, device=dev)  # noqa: E731
+            # forward operands as bf16 (hi, lo) pairs, stacked on a leading axis of 2
+            ws["feat16_on"], ws["feat16_tg"] = h(2, S * B, FEAT), h(2, T * B, FEAT)
+            ws["w_ih16"], ws["w_ih16_t"], ws["w_ihT16"] = h(2, 4 * H, FEAT), h(2, 4 * H, FEAT), h(FEAT, 4 * H)
+            ws["hw1_16"], ws["hw1_16_t"], ws["hw1T16"] = h(2, 2 * H, H), h(2, 2 * H, H), h(H, 2 * H)
+            ws["hs16"] = h(2, M, H)
+            ws["dhid16"], ws["dhidT16"], ws["hsT16"] = h(M, 2 * H), h(2 * H, M), h(H, M)
+            ws["dg16"], ws["dgT16"], ws["hprevT16"], ws["featT16"] = h(M, 4 * H), h(4 * H, M), h(H, M), h(FEAT, M)
         self._ws = ws
         return ws
 
@@ -192,8 +210,25 @@ class Learner:
         # ---- conv torso + input projection: online on all T+n frames, target on frames n..T+n
         engine.torso_fwd_u8(slab, 0, T + n, w, ws["a1_on"], ws["a2_on"], ws["feat_on"])
         engine.torso_fwd_u8(slab, n, T, wt, ws["a1_tg"], ws["a2_tg"], ws["feat_tg"])
-        engine.linear_fwd(ws["feat_on"], w.w_ih, w.b_ih, w.b_hh, ws["xp_on"])
-        engine.linear_fwd(ws["feat_tg"], wt.w_ih, wt.b_ih, wt.b_hh, ws["xp_tg"])
+        bf16 = self.precision == "bf16"
+        if bf16:   # dense contractions on tcgen05: bf16 copies of this step's operands
+            def split(x, pair):
+                engine.split_bf16(x, pair[0], pair[1])
+
+            split(w.w_ih, ws["w_ih16"])
+            split(wt.w_ih, ws["w_ih16_t"])
+            split(w.head_w1, ws["hw1_16"])
+            split(wt.head_w1, ws["hw1_16_t"])
+            split(ws["feat_on"], ws["feat16_on"])
+            split(ws["feat_tg"], ws["feat16_tg"])
+            # forward contractions: error-compensated bf16x3
+            engine.tc_linear_x3(ws["feat16_on"][0], ws["feat16_on"][1], ws["w_ih16"][0], ws["w_ih16"][1],
+                                w.b_ih, w.b_hh, y32=ws["xp_on"])
+            engine.tc_linear_x3(ws["feat16_tg"][0], ws["feat16_tg"][1], ws["w_ih16_t"][0],
+                                ws["w_ih16_t"][1], wt.b_ih, wt.b_hh, y32=ws["xp_tg"])
+        else:
+            engine.linear_fwd(ws["feat_on"], w.w_ih, w.b_ih, w.b_hh, ws["xp_on"])
+            engine.linear_fwd(ws["feat_tg"], wt.w_ih, wt.b_ih, wt.b_hh, ws["xp_tg"])
 
         # ---- online net: burn-in + learn over state[0:T] (hidden state carries through)
         ws["hs_on"][0].copy_(batch["hs"])
@@ -211,9 +246,18 @@ class Learner:
 
         # ---- dueling heads on the learn window only
         hs_learn = ws["hs_on"][1 + BI:].reshape(M, H)
-        engine.head_fwd(hs_learn, w, ws["hid_on"], ws["q_all"])
-        engine.head_fwd(ws["hs_dq"][1:].reshape(M, H), w, ws["hid_tmp"], ws["qn_on"])
-        engine.head_fwd(ws["hs_tg"][1 + BI:].reshape(M, H), wt, ws["hid_tmp"], ws["qn_tg"])
+        def head(hs, wts, w1_16, hid, q):
+            if bf16:
+                engine.split_bf16(hs, ws["hs16"][0], ws["hs16"][1])
+                engine.tc_linear_x3(ws["hs16"][0], ws["hs16"][1], w1_16[0], w1_16[1], wts.head_b1, None,
+                                    y32=hid, relu=True)
+                engine.head_out(hid, wts, q)
+            else:
+                engine.head_fwd(hs, wts, hid, q)
+
+        head(ws["hs_dq"][1:].reshape(M, H), w, ws.get("hw1_16"), ws["hid_tmp"], ws["qn_on"])
+        head(ws["hs_tg"][1 + BI:].reshape(M, H), wt, ws.get("hw1_16_t"), ws["hid_tmp"], ws["qn_tg"])
+        head(hs_learn, w, ws.get("hw1_16"), ws["hid_on"], ws["q_all"])   # last: hs16 = learn window
 
         # ---- n-step double-Q target, TD error, loss gradient, per-step priorities
         td = ws["td"]
@@ -226,15 +270,39 @@ class Learner:
         # ---- backward (learn window only; BPTT truncated at the burn-in boundary)
         scratch = ws["scratch"]
         engine.head_bwd(td["dq"], ws["hid_on"], w, ws["dhid"], g.head_w2, g.head_b2)
-        engine.linear_wgrad(ws["dhid"], hs_learn, g.head_w1, g.head_b1, scratch)
-        engine.linear_dgrad(ws["dhid"], w.head_w1, ws["dhs"])
+        hprev = ws["hs_on"][BI:BI + L].reshape(M, H)
+        feat_l = ws["feat_on"][BI * B: T * B]
+        if bf16:
+            # weight gradients: dW = dY^T . X with both operands transposed to [*, M] bf16;
+            # data gradients: dX = dY . W with W transposed to [K_out, N] bf16
+            engine.transpose_cast_bf16(ws["dhid"], ws["dhidT16"])
+            engine.transpose_cast_bf16(hs_learn, ws["hsT16"])
+            engine.tc_linear(ws["dhidT16"], ws["hsT16"], None, None, y32=g.head_w1)
+            engine.colsum(ws["dhid"], g.head_b1)
+            engine.cast_bf16(ws["dhid"], ws["dhid16"])
+            engine.transpose_cast_bf16(w.head_w1, ws["hw1T16"])
+            engine.tc_linear(ws["dhid16"], ws["hw1T16"], None, None, y32=ws["dhs"])
+        else:
+            engine.linear_wgrad(ws["dhid"], hs_learn, g.head_w1, g.head_b1, scratch)
+            engine.linear_dgrad(ws["dhid"], w.head_w1, ws["dhs"])
         engine.lstm_seq_bwd(ws["dhs"], w.w_hh, ws["gates"][BI:], ws["cs_on"][BI:], ws["dgates"],
                             ws["dc_work"], L, B, H)
-        engine.linear_wgrad(ws["dgates"], ws["hs_on"][BI:BI + L].reshape(M, H), g.w_hh, g.b_hh, scratch)
-        g.b_ih.copy_(g.b_hh)
-        feat_l = ws["feat_on"][BI * B: T * B]
-        engine.linear_wgrad(ws["dgates"], feat_l, g.w_ih, None, scratch)
-        engine.linear_dgrad(ws["dgates"], w.w_ih, ws["dfeat"])
+        if bf16:
+            engine.transpose_cast_bf16(ws["dgates"], ws["dgT16"])
+            engine.transpose_cast_bf16(hprev, ws["hprevT16"])
+            engine.tc_linear(ws["dgT16"], ws["hprevT16"], None, None, y32=g.w_hh)
+            engine.colsum(ws["dgates"], g.b_hh)
+            g.b_ih.copy_(g.b_hh)
+            engine.transpose_cast_bf16(feat_l, ws["featT16"])
+            engine.tc_linear(ws["dgT16"], ws["featT16"], None, None, y32=g.w_ih)
+            engine.cast_bf16(ws["dgates"], ws["dg16"])
+            engine.transpose_cast_bf16(w.w_ih, ws["w_ihT16"])
+            engine.tc_linear(ws["dg16"], ws["w_ihT16"], None, None, y32=ws["dfeat"])
+        else:
+            engine.linear_wgrad(ws["dgates"], hprev, g.w_hh, g.b_hh, scratch)
+            g.b_ih.copy_(g.b_hh)
+            engine.linear_wgrad(ws["dgates"], feat_l, g.w_ih, None, scratch)
+            engine.linear_dgrad(ws["dgates"], w.w_ih, ws["dfeat"])
         engine.torso_bwd_u8(slab, BI, L, ws["a1_on"][BI * B: T * B], ws["a2_on"][BI * B: T * B], feat_l,
                             ws["dfeat"], w, g, scratch)
 
