@@ -206,6 +206,15 @@ int r2d2_torso_bwd_f32(const float* frames, int R, const float* a1, const float*
  * and - on transposed bf16 copies - the data and weight gradients of both. */
 int r2d2_tc_linear(const void* x_bf16, const void* w_bf16, const float* bias1, const float* bias2,
                    float* y_f32, void* y_bf16, int M, int N, int K, int relu, void* stream);
+/* conv torso forward on tensor cores (same contract as r2d2_torso_fwd_{u8,f32}): implicit GEMM,
+ * patches gathered by producer warps into swizzled shared memory, bf16x3 compensation, weights
+ * resident, two TMEM accumulators */
+int r2d2_tc_torso_fwd_u8(const uint8_t* slab, int B, int S, int s0, int nt, const float* w1,
+                         const float* b1, const float* w2, const float* b2, const float* w3,
+                         const float* b3, float* a1, float* a2, float* feat, void* stream);
+int r2d2_tc_torso_fwd_f32(const float* frames, int R, const float* w1, const float* b1,
+                          const float* w2, const float* b2, const float* w3, const float* b3,
+                          float* a1, float* a2, float* feat, void* stream);
 /* Error-compensated variant ("bf16x3"): x = x_hi + x_lo, w = w_hi + w_lo (r2d2_split_bf16) and
  * y = x_hi.w_hi^T + x_hi.w_lo^T + x_lo.w_hi^T, fp32 accumulation in TMEM -- operand error 2^-16
  * instead of 2^-9.  Used for FORWARD contractions: a 1e-3 forward perturbation flips ReLU masks

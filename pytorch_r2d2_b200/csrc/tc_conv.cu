@@ -1,0 +1,306 @@
+// Conv torso forward (model.py:13-21,44-46) as an implicit GEMM on tcgen05 tensor cores.
+//
+//   out[r, co, p] = relu(bias[co] + sum_k patch[(r,p), k] * W[co, k]),  k = (ci, ky, kx)
+//
+// M = 128 output pixels per tile (one TMEM lane each), N = 32 output channels, K = Cin*Kh*Kw in
+// blocks of 64.  Persistent CTAs, 416 threads:
+//   warps 0-7  producers: two threads per row of the A tile (the pixel's receptive field), four
+//              16-byte chunks each, all patch offsets compile-time constants; they gather
+//              straight from the u8 slab / fp32 NCHW activations, splits it into bf16 (hi, lo)
+//              and stores it into shared memory in the 128-byte-swizzled K-major layout the UMMA
+//              descriptor expects (what TMA would have produced for a dense matrix);
+//   warp 8     TMEM allocator + MMA issuer (one lane): error-compensated bf16x3
+//              (A_hi.W_hi + A_hi.W_lo + A_lo.W_hi, fp32 accumulate in TMEM); for conv1 the u8
+//              pixels are exact in bf16, so A has no lo part and 1/255 is applied in the epilogue;
+//   warps 9-12 epilogue: tcgen05.ld -> bias + ReLU -> NCHW fp32 (coalesced along pixels).
+// The weights (both halves, all K) stay resident in shared memory; two TMEM accumulator
+// buffers let the epilogue of tile i overlap the MMAs of tile i+1.
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+#include "gemm.cuh"   // FrameMap
+#include "ptx.cuh"
+
+namespace r2d2 {
+
+constexpr int CV_STAGES = 4;
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ float bf16_round(float x) {
+    return __bfloat162float(__float2bfloat16_rn(x));
+}
+// byte offset of (row, 16-byte chunk) inside a K-major SWIZZLE_128B tile of 128-byte rows
+__device__ __forceinline__ uint32_t sw128_off(int row, int chunk) {
+    return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((chunk ^ (row & 7)) << 4));
+}
+
+// Four 8-element chunks (chunks 4*HALF .. 4*HALF+3 of k-block kb) of one patch row.
+template <class T, int CIN, int KH, int HIN, int HALF>
+__device__ __forceinline__ void gather_chunks(const T* __restrict__ src, const int kb,
+                                              const bool valid, float (&v)[4][8]) {
+    constexpr int K = CIN * KH * KH;
+#pragma unroll
+    for (int cc = 0; cc < 4; ++cc) {
+        constexpr int dummy = 0;
+        (void)dummy;
+        const int c = HALF * 4 + cc;
+        if constexpr (sizeof(T) == 1 && KH == 8) {
+            // conv1 on the u8 slab: k-block = one input channel, chunk = one 8-pixel patch row
+            const uint32_t* q = reinterpret_cast<const uint32_t*>(src + kb * (HIN * HIN) + c * HIN);
+            const uint32_t lo4 = valid ? __ldg(q) : 0u, hi4 = valid ? __ldg(q + 1) : 0u;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                v[cc][e] = (float)((lo4 >> (8 * e)) & 0xffu);
+                v[cc][4 + e] = (float)((hi4 >> (8 * e)) & 0xffu);
+            }
+        } else if constexpr (KH == 4) {
+            // conv2: chunk = (ci = 4kb + c/2, ky = 2(c%2) .. +1, kx = 0..3): two rows of 4 floats
+            const T* q = src + (kb * 4 + (c >> 1)) * (HIN * HIN) + ((c & 1) * 2) * HIN;
+#pragma unroll
+            for (int rr = 0; rr < 2; ++rr) {
+                const float2* q2 = reinterpret_cast<const float2*>(q + rr * HIN);
+                const float2 x0 = valid ? __ldg(q2) : make_float2(0.f, 0.f);
+                const float2 x1 = valid ? __ldg(q2 + 1) : make_float2(0.f, 0.f);
+                v[cc][rr * 4 + 0] = x0.x; v[cc][rr * 4 + 1] = x0.y;
+                v[cc][rr * 4 + 2] = x1.x; v[cc][rr * 4 + 3] = x1.y;
+            }
+        } else {
+            // generic (conv3, f32-frame conv1): scalar loads; kb is unrolled by the caller, so k
+            // and the (ci,ky,kx) decode are compile-time constants
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const int k = kb * 64 + c * 8 + e;
+                const int ci = k / (KH * KH), rem = k - ci * (KH * KH);
+                const int ky = rem / KH, kx = rem - ky * KH;
+                float x = 0.f;
+                if (k < K && valid) x = (float)__ldg(src + ci * HIN * HIN + ky * HIN + kx);
+                v[cc][e] = x;
+            }
+        }
+    }
+}
+
+template <class T, int CIN, int KH, int HIN, int HOUT, int STRIDE>
+__global__ void __launch_bounds__(416, 1)
+tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __restrict__ w,
+                   const float* __restrict__ bias, float* __restrict__ out, const int R,
+                   const float in_scale) {
+    constexpr int K = CIN * KH * KH, NKB = (K + 63) / 64, KP = NKB * 64;
+    constexpr int P = HOUT * HOUT, COUT = 32;
+    constexpr bool NEED_LO = sizeof(T) != 1;                 // u8 pixels are exact in bf16
+    constexpr uint32_t A_TILE = 128 * 128;                   // 128 rows x 64 bf16
+    constexpr uint32_t STAGE_BYTES = NEED_LO ? 2 * A_TILE : A_TILE;
+    constexpr uint32_t W_KB = COUT * 128;                    // 32 rows x 64 bf16 per k-block
+    constexpr uint32_t W_BYTES = 2 * NKB * W_KB;             // hi then lo
+    constexpr int MMA_WARP = 8;
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t full_bar[CV_STAGES], empty_bar[CV_STAGES], acc_full[2], acc_empty[2];
+    __shared__ uint32_t tmem_slot;
+
+    const uint32_t raw = smem_u32(smem_raw);
+    uint8_t* base = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
+    uint8_t* w_s = base;                                     // [hi|lo][NKB][32 x 128 B]
+    uint8_t* a_s = base + W_BYTES;                           // CV_STAGES x STAGE_BYTES
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const long long Mtot = (long long)R * P;
+    const int ntiles = (int)((Mtot + 127) / 128);
+
+    // ---- one-time set-up: barriers, k-offset table, resident weights (hi/lo, swizzled)
+    if (tid == 0) {
+        for (int s = 0; s < CV_STAGES; ++s) {
+            mbar_init(&full_bar[s], 256);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&acc_full[b], 1);
+            mbar_init(&acc_empty[b], 128);
+        }
+        mbar_fence_init();
+    }
+    for (int i = tid; i < COUT * (KP / 8); i += blockDim.x) {
+        const int co = i / (KP / 8), ch = i - co * (KP / 8);  // chunk of 8 k's
+        const int kb = ch >> 3, c = ch & 7;
+        float v[8], l[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const int k = ch * 8 + e;
+            const float x = k < K ? __ldg(w + (long long)co * K + k) : 0.f;
+            v[e] = x;
+            l[e] = x - bf16_round(x);
+        }
+        const uint32_t off = (uint32_t)kb * W_KB + sw128_off(co, c);
+        *reinterpret_cast<uint4*>(w_s + off) = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
+                                                         pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+        *reinterpret_cast<uint4*>(w_s + NKB * W_KB + off) =
+            make_uint4(pack_bf16x2(l[0], l[1]), pack_bf16x2(l[2], l[3]), pack_bf16x2(l[4], l[5]),
+                       pack_bf16x2(l[6], l[7]));
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // weights -> tensor-core proxy
+    if (warp == MMA_WARP) tmem_alloc(&tmem_slot, 64);                      // 2 accumulators x 32 columns
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+
+    if (warp < MMA_WARP) {
+        // ================= producers: thread t -> row (t & 127), chunks 4*(t>>7) .. +3
+        const int row = tid & 127, half = tid >> 7;
+        uint32_t it = 0;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+            const long long m = (long long)tile * 128 + row;
+            const bool valid = m < Mtot;
+            const T* src = in;                                // any valid address when !valid
+            if (valid) {
+                const int r = (int)(m / P), p = (int)(m - (long long)r * P);
+                const int oy = p / HOUT, ox = p - oy * HOUT;
+                src = in + fm.base(r) + (long long)(oy * STRIDE) * HIN + ox * STRIDE;
+            }
+#pragma unroll
+            for (int kb = 0; kb < NKB; ++kb, ++it) {
+                const int s = it % CV_STAGES;
+                mbar_wait(&empty_bar[s], ((it / CV_STAGES) & 1) ^ 1);
+                uint8_t* a_hi = a_s + (size_t)s * STAGE_BYTES;
+                float v[4][8];
+                // ---- issue all loads of this thread's four chunks first (memory-level
+                //      parallelism); `half` is dispatched at compile time so that every patch
+                //      offset folds to an immediate
+                if (half == 0) gather_chunks<T, CIN, KH, HIN, 0>(src, kb, valid, v);
+                else gather_chunks<T, CIN, KH, HIN, 1>(src, kb, valid, v);
+#pragma unroll
+                for (int cc = 0; cc < 4; ++cc) {
+                    const uint32_t off = sw128_off(row, half * 4 + cc);
+                    *reinterpret_cast<uint4*>(a_hi + off) =
+                        make_uint4(pack_bf16x2(v[cc][0], v[cc][1]), pack_bf16x2(v[cc][2], v[cc][3]),
+                                   pack_bf16x2(v[cc][4], v[cc][5]), pack_bf16x2(v[cc][6], v[cc][7]));
+                    if constexpr (NEED_LO) {
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) v[cc][e] -= bf16_round(v[cc][e]);
+                        *reinterpret_cast<uint4*>(a_hi + A_TILE + off) =
+                            make_uint4(pack_bf16x2(v[cc][0], v[cc][1]), pack_bf16x2(v[cc][2], v[cc][3]),
+                                       pack_bf16x2(v[cc][4], v[cc][5]), pack_bf16x2(v[cc][6], v[cc][7]));
+                    }
+                }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                mbar_arrive(&full_bar[s]);
+            }
+        }
+    } else if (warp == MMA_WARP) {
+        // ================= MMA issuer
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(128, COUT);
+            const uint32_t w_hi = smem_u32(w_s), w_lo = w_hi + NKB * W_KB;
+            uint32_t it = 0, tcount = 0;
+            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++tcount) {
+                const uint32_t buf = tcount & 1, use = tcount >> 1;
+                mbar_wait(&acc_empty[buf], (use & 1) ^ 1);           // epilogue drained this buffer
+                tc_fence_after();
+                const uint32_t d = tmem_base + buf * COUT;
+                for (int kb = 0; kb < NKB; ++kb, ++it) {
+                    const int s = it % CV_STAGES;
+                    mbar_wait(&full_bar[s], (it / CV_STAGES) & 1);
+                    tc_fence_after();
+                    const uint32_t a_hi = smem_u32(a_s + (size_t)s * STAGE_BYTES), a_lo = a_hi + A_TILE;
+                    const uint32_t b_hi = w_hi + kb * W_KB, b_lo = w_lo + kb * W_KB;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        umma_f16(d, umma_desc_k_sw128(a_hi + k * 32), umma_desc_k_sw128(b_hi + k * 32),
+                                 idesc, (kb | k) != 0);
+                        umma_f16(d, umma_desc_k_sw128(a_hi + k * 32), umma_desc_k_sw128(b_lo + k * 32),
+                                 idesc, 1);
+                        if (NEED_LO)
+                            umma_f16(d, umma_desc_k_sw128(a_lo + k * 32),
+                                     umma_desc_k_sw128(b_hi + k * 32), idesc, 1);
+                    }
+                    umma_commit(&empty_bar[s]);
+                }
+                umma_commit(&acc_full[buf]);
+            }
+        }
+    } else {
+        // ================= epilogue: one pixel (TMEM lane) per thread, 32 channels
+        const int q = warp & 3;
+        uint32_t tcount = 0;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++tcount) {
+            const uint32_t buf = tcount & 1, use = tcount >> 1;
+            mbar_wait(&acc_full[buf], use & 1);
+            tc_fence_after();
+            uint32_t r[32];
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + buf * COUT, r);
+            tmem_ld_wait();
+            tc_fence_before();
+            mbar_arrive(&acc_empty[buf]);
+            const long long m = (long long)tile * 128 + q * 32 + lane;
+            if (m < Mtot) {
+                const int fr = (int)(m / P), p = (int)(m - (long long)fr * P);
+                float* o = out + (long long)fr * COUT * P + p;
+#pragma unroll
+                for (int co = 0; co < COUT; ++co)
+                    o[(long long)co * P] = fmaxf(fmaf(__uint_as_float(r[co]), in_scale, __ldg(bias + co)), 0.f);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == MMA_WARP) tmem_dealloc(tmem_base, 64);
+}
+
+template <class T, int CIN, int KH, int HIN, int HOUT, int STRIDE>
+static int launch_tc_conv(const char* name, const T* in, FrameMap fm, const float* w, const float* b,
+                          float* out, int R, float in_scale, cudaStream_t st) {
+    constexpr int K = CIN * KH * KH, NKB = (K + 63) / 64;
+    constexpr bool NEED_LO = sizeof(T) != 1;
+    const int smem = 2 * NKB * 32 * 128 + CV_STAGES * (NEED_LO ? 2 : 1) * 128 * 128 + 1024;
+    auto kern = tc_conv_fwd_kernel<T, CIN, KH, HIN, HOUT, STRIDE>;
+    R2D2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    const long long Mtot = (long long)R * HOUT * HOUT;
+    const int ntiles = (int)((Mtot + 127) / 128);
+    int grid = sm_count();
+    if (grid > ntiles) grid = ntiles;
+    R2D2_LAUNCH(name, st, kern<<<grid, 416, smem, st>>>(in, fm, w, b, out, R, in_scale));
+    return R2D2_OK;
+}
+
+template <class T>
+static int tc_torso_fwd_impl(const T* frames, FrameMap fm, int R, const float* w1, const float* b1,
+                             const float* w2, const float* b2, const float* w3, const float* b3,
+                             float* a1, float* a2, float* feat, cudaStream_t st) {
+    R2D2_REQUIRE((long long)R * 400 < (1ll << 31), "tc_torso_fwd: too many frames");
+    const float s1 = sizeof(T) == 1 ? 1.f / 255.f : 1.f;
+    int rc = launch_tc_conv<T, 4, 8, 84, 20, 4>("tc_conv1_fwd", frames, fm, w1, b1, a1, R, s1, st);
+    if (rc) return rc;
+    rc = launch_tc_conv<float, 32, 4, 20, 9, 2>("tc_conv2_fwd", a1, FrameMap{0, 0, 0, 12800}, w2, b2, a2,
+                                                R, 1.f, st);
+    if (rc) return rc;
+    return launch_tc_conv<float, 32, 3, 9, 7, 1>("tc_conv3_fwd", a2, FrameMap{0, 0, 0, 2592}, w3, b3, feat,
+                                                 R, 1.f, st);
+}
+
+}  // namespace r2d2
+
+using namespace r2d2;
+
+extern "C" {
+
+int r2d2_tc_torso_fwd_u8(const uint8_t* slab, int B, int S, int s0, int nt, const float* w1,
+                         const float* b1, const float* w2, const float* b2, const float* w3,
+                         const float* b3, float* a1, float* a2, float* feat, void* stream) {
+    R2D2_REQUIRE(slab && w1 && b1 && w2 && b2 && w3 && b3 && a1 && a2 && feat, "tc_torso_fwd: null pointer");
+    R2D2_REQUIRE(B > 0 && nt > 0 && s0 >= 0 && s0 + nt <= S, "tc_torso_fwd: bad frame window");
+    return tc_torso_fwd_impl<uint8_t>(slab, FrameMap{B, S, s0, R2D2_FRAME_BYTES}, B * nt, w1, b1, w2, b2,
+                                      w3, b3, a1, a2, feat, as_stream(stream));
+}
+
+int r2d2_tc_torso_fwd_f32(const float* frames, int R, const float* w1, const float* b1,
+                          const float* w2, const float* b2, const float* w3, const float* b3,
+                          float* a1, float* a2, float* feat, void* stream) {
+    R2D2_REQUIRE(frames && w1 && b1 && w2 && b2 && w3 && b3 && a1 && a2 && feat, "tc_torso_fwd: null pointer");
+    R2D2_REQUIRE(R > 0, "tc_torso_fwd: bad frame count");
+    return tc_torso_fwd_impl<float>(frames, FrameMap{0, 0, 0, R2D2_FRAME_BYTES}, R, w1, b1, w2, b2, w3, b3,
+                                    a1, a2, feat, as_stream(stream));
+}
+
+}  // extern "C"

@@ -36,15 +36,15 @@ class Weights:
 
 
 # ---------------------------------------------------------------------------- forward ops
-def torso_fwd_u8(slab, s0, nt, w: Weights, a1, a2, feat):
+def torso_fwd_u8(slab, s0, nt, w: Weights, a1, a2, feat, tc=False):
     B, Sfr = slab.shape[0], slab.shape[1]
-    _lib.call("r2d2_torso_fwd_u8", P(slab, "u8"), B, Sfr, s0, nt, P(w.w1), P(w.b1), P(w.w2), P(w.b2),
+    _lib.call("r2d2_tc_torso_fwd_u8" if tc else "r2d2_torso_fwd_u8", P(slab, "u8"), B, Sfr, s0, nt, P(w.w1), P(w.b1), P(w.w2), P(w.b2),
               P(w.w3), P(w.b3), P(a1, "f32"), P(a2, "f32"), P(feat, "f32"), S())
 
 
-def torso_fwd_f32(frames, w: Weights, a1, a2, feat):
+def torso_fwd_f32(frames, w: Weights, a1, a2, feat, tc=False):
     R = frames.shape[0]
-    _lib.call("r2d2_torso_fwd_f32", P(frames, "f32"), R, P(w.w1), P(w.b1), P(w.w2), P(w.b2), P(w.w3),
+    _lib.call("r2d2_tc_torso_fwd_f32" if tc else "r2d2_torso_fwd_f32", P(frames, "f32"), R, P(w.w1), P(w.b1), P(w.w2), P(w.b2), P(w.w3),
               P(w.b3), P(a1, "f32"), P(a2, "f32"), P(feat, "f32"), S())
 
 

@@ -208,8 +208,9 @@ class Learner:
         M = L * B
 
         # ---- conv torso + input projection: online on all T+n frames, target on frames n..T+n
-        engine.torso_fwd_u8(slab, 0, T + n, w, ws["a1_on"], ws["a2_on"], ws["feat_on"])
-        engine.torso_fwd_u8(slab, n, T, wt, ws["a1_tg"], ws["a2_tg"], ws["feat_tg"])
+        tc = self.precision == "bf16"
+        engine.torso_fwd_u8(slab, 0, T + n, w, ws["a1_on"], ws["a2_on"], ws["feat_on"], tc=tc)
+        engine.torso_fwd_u8(slab, n, T, wt, ws["a1_tg"], ws["a2_tg"], ws["feat_tg"], tc=tc)
         bf16 = self.precision == "bf16"
         if bf16:   # dense contractions on tcgen05: bf16 copies of this step's operands
             def split(x, pair):

@@ -64,3 +64,37 @@ def test_cast_and_transpose(cuda_device):
     o2 = torch.empty(130, 77, device="cuda", dtype=torch.bfloat16)
     engine.transpose_cast_bf16(x2, o2)
     assert torch.equal(o2, x2.T.contiguous().bfloat16())
+
+
+def test_tc_torso_vs_torch(cuda_device):
+    """Tensor-core conv torso (bf16x3 implicit GEMM) == fp32 torch convs to 1e-5, u8 slab and
+    f32 entry points, incl. a partial last tile and the time-major frame mapping."""
+    import numpy as np
+    from oracle import net_oracle as NO
+    from pytorch_r2d2_b200 import QNet, engine
+    torch.manual_seed(2)
+    net = QNet("cuda:0", 256)
+    w = net._weights()
+    p = {k: v.cpu() for k, v in net.state_dict().items()}
+    rng = np.random.RandomState(1)
+    B, S = 3, 5
+    slab = torch.from_numpy(rng.randint(0, 256, (B, S, 4, 84, 84)).astype(np.uint8)).cuda()
+    a1, a2, feat = engine.alloc_torso(B * 3, "cuda")
+    engine.torso_fwd_u8(slab, 1, 3, w, a1, a2, feat, tc=True)
+    frames = slab[:, 1:4].permute(1, 0, 2, 3, 4).reshape(-1, 4, 84, 84).cpu().float() / 255.
+    x1 = torch.relu(torch.nn.functional.conv2d(frames, p["vis_layers.0.weight"], p["vis_layers.0.bias"], stride=4))
+    x2 = torch.relu(torch.nn.functional.conv2d(x1, p["vis_layers.2.weight"], p["vis_layers.2.bias"], stride=2))
+    want = NO.torso(p, frames)
+    assert rel_err(a1, x1) < 1e-5, rel_err(a1, x1)
+    assert rel_err(a2, x2) < 1e-5, rel_err(a2, x2)
+    assert rel_err(feat, want) < 1e-5, rel_err(feat, want)
+    b1, b2, featb = engine.alloc_torso(B * 3, "cuda")
+    engine.torso_fwd_f32(frames.cuda().contiguous(), w, b1, b2, featb, tc=True)
+    assert rel_err(featb, want) < 1e-5
+    # many tiles per CTA (exercises the ring / TMEM double buffering across > 148*2 tiles)
+    slab2 = torch.from_numpy(rng.randint(0, 256, (16, 8, 4, 84, 84)).astype(np.uint8)).cuda()
+    c1, c2, f2 = engine.alloc_torso(16 * 8, "cuda")
+    d1, d2, g2 = engine.alloc_torso(16 * 8, "cuda")
+    engine.torso_fwd_u8(slab2, 0, 8, w, c1, c2, f2, tc=True)
+    engine.torso_fwd_u8(slab2, 0, 8, w, d1, d2, g2, tc=False)
+    assert rel_err(c1, d1) < 1e-5 and rel_err(c2, d2) < 1e-5 and rel_err(f2, g2) < 1e-5
