@@ -202,6 +202,8 @@ int r2d2_torso_bwd_f32(const float* frames, int R, const float* a1, const float*
  * (north-star 2e-2 precision class; tcgen05.mma + TMEM accumulators + TMA operand staging)
  * y[M,N] = x[M,K] . w[N,K]^T + bias1 + bias2 (ReLU optional); x, w bf16 row-major with K
  * contiguous (K % 8 == 0, N % 4 == 0); either or both outputs (f32 / bf16) may be given.
+ * `relu` is a flag word: bit 0 = ReLU, bit 1 = biases are per output ROW (used to produce the
+ * transposed input projection W_ih.x^T that the persistent LSTM kernel consumes).
  * The same entry point serves model.py:55 (x.W_ih^T), the dueling hidden layer (model.py:26-36)
  * and - on transposed bf16 copies - the data and weight gradients of both. */
 int r2d2_tc_linear(const void* x_bf16, const void* w_bf16, const float* bias1, const float* bias2,
@@ -215,6 +217,16 @@ int r2d2_tc_torso_fwd_u8(const uint8_t* slab, int B, int S, int s0, int nt, cons
 int r2d2_tc_torso_fwd_f32(const float* frames, int R, const float* w1, const float* b1,
                           const float* w2, const float* b2, const float* w3, const float* b3,
                           float* a1, float* a2, float* feat, void* stream);
+/* Persistent LSTM unroll on tensor cores (model.py:52-60): one cooperative launch runs all T
+ * steps; W_hh stays resident in shared memory (bf16 hi/lo), the cell state in registers, h_t is
+ * exchanged between the CTAs through a ping-pong buffer + grid-wide counter in `scratch`
+ * (r2d2_tc_lstm_scratch_bytes, 256-byte aligned).  xprojT is the TRANSPOSED input projection
+ * [4H, ldx] (column col0 + t*B + b), biases included.  Outputs as r2d2_lstm_seq_fwd.
+ * H % 64 == 0, H <= 512; H/16 * ceil(B/64) CTAs must be co-resident. */
+int64_t r2d2_tc_lstm_scratch_bytes(int B, int H);
+int r2d2_tc_lstm_seq_fwd(const float* xprojT, int64_t ldx, int64_t col0, const float* w_hh,
+                         float* hs_ext, float* cs_ext, float* gates, int T, int B, int H,
+                         void* scratch, void* stream);
 /* Error-compensated variant ("bf16x3"): x = x_hi + x_lo, w = w_hi + w_lo (r2d2_split_bf16) and
  * y = x_hi.w_hi^T + x_hi.w_lo^T + x_lo.w_hi^T, fp32 accumulation in TMEM -- operand error 2^-16
  * instead of 2^-9.  Used for FORWARD contractions: a 1e-3 forward perturbation flips ReLU masks

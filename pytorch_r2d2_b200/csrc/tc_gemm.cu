@@ -25,6 +25,7 @@ struct TcEpilogue {
     const float* bias1;     // per output column, may be null
     const float* bias2;
     int relu;
+    int bias_row;           // biases indexed by output row m instead of column n
 };
 
 template <int BN>
@@ -118,8 +119,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
                         float x = __uint_as_float(r[j + e]);
-                        if (ep.bias1) x += __ldg(ep.bias1 + n + e);
-                        if (ep.bias2) x += __ldg(ep.bias2 + n + e);
+                        if (ep.bias1) x += __ldg(ep.bias1 + (ep.bias_row ? m : n + e));
+                        if (ep.bias2) x += __ldg(ep.bias2 + (ep.bias_row ? m : n + e));
                         if (ep.relu) x = fmaxf(x, 0.f);
                         v[e] = x;
                     }
@@ -255,7 +256,8 @@ static int tc_linear_impl(const void* x_hi, const void* x_lo, const void* w_hi, 
         R2D2_CUDA_OK(cudaFuncSetAttribute(tc_gemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         attr_set = true;
     }
-    TcEpilogue ep{y_f32, reinterpret_cast<__nv_bfloat16*>(y_bf16), N, bias1, bias2, relu};
+    TcEpilogue ep{y_f32, reinterpret_cast<__nv_bfloat16*>(y_bf16), N, bias1, bias2, relu & 1,
+                  (relu >> 1) & 1};
     dim3 grid((M + TC_BM - 1) / TC_BM, (N + BN - 1) / BN);
     const int nseg = x_lo ? 3 : 1;
     R2D2_LAUNCH(nseg == 3 ? "tc_gemm_kernel_x3" : "tc_gemm_kernel", as_stream(stream),

@@ -1,0 +1,344 @@
+// Persistent LSTM unroll on tcgen05 tensor cores (model.py:52-60), one cooperative launch for all
+// T steps of a chain.
+//
+// Swap-AB: per step  G^T[4H, B] = W_hh[4H, H] . h_{t-1}^T[H, B]  (+ xproj^T).  CTA c owns 16 hidden
+// units and all four of their gates = 64 rows of W_hh (UMMA M = 64, N = 64 batch columns); its
+// W_hh slice stays resident in shared memory for the whole unroll as bf16 (hi, lo) pairs, the
+// cell state c lives in registers, and only h_{t-1} travels: every CTA writes its 16 units of
+// h_t (bf16 hi/lo, K-major) to a ping-pong buffer in global memory, a grid-wide arrive/wait
+// counter publishes it, and TMA streams it back in as the B operand of the next step.
+// Forward contractions are error-compensated bf16x3 (W_hi.h_hi + W_lo.h_hi + W_hi.h_lo, fp32
+// accumulation in TMEM) -- see DESIGN.md section 2 for why the forward pass needs this.
+//
+// 320 threads: warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2-5 = TMEM
+// readers (gate q = warp % 4 sits in lanes 32q..32q+15 of the M=64 accumulator layout),
+// warps 2-9 = pointwise cell update (thread -> batch row b, 4 hidden units).
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace r2d2 {
+
+constexpr int LS_UNITS = 16, LS_ROWS = 64, LS_NB = 64, LS_STAGES = 4;
+
+__device__ __forceinline__ uint32_t ls_pack(float a, float b) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ float ls_round(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
+__device__ __forceinline__ uint32_t ls_sw128(int row, int chunk) {
+    return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((chunk ^ (row & 7)) << 4));
+}
+__device__ __forceinline__ float ls_sigmoid(float x) { return 1.f / (1.f + expf(-x)); }
+
+__device__ __forceinline__ int ld_acquire(const int* p) {
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+struct LstmArgs {
+    const float* xprojT;   // [4H, ldx]: column col0 + t*B + b holds step t, batch b
+    long long ldx, col0;
+    const float* w_hh;     // [4H, H] fp32
+    float* hs_ext;         // [(T+1), B, H]; slot 0 = h0 (read), slot t+1 written
+    float* cs_ext;         // same for c
+    float* gates;          // [T, B, 4H] post-activation i,f,g,o or null
+    __nv_bfloat16* h16_hi; // [2, B, H] ping-pong, K-major B operand
+    __nv_bfloat16* h16_lo;
+    int* counter;          // [gridDim.y] grid barrier counters, zero on entry
+    int T, B, H;
+};
+
+__global__ void __launch_bounds__(320, 1)
+tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_constant__ CUtensorMap tma_lo,
+                   const LstmArgs a) {
+    const int H = a.H, B = a.B, NKB = H / 64;
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t full_bar[LS_STAGES], empty_bar[LS_STAGES], acc_full, acc_empty;
+    __shared__ uint32_t tmem_slot;
+    __shared__ __align__(16) float G[4][LS_UNITS][LS_NB + 4];   // raw gate pre-activations (no xproj)
+
+    const uint32_t raw = smem_u32(smem_raw);
+    uint8_t* base = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
+    const uint32_t W_KB = LS_ROWS * 128;                        // 64 rows x 64 bf16
+    uint8_t* w_s = base;                                        // [hi|lo][NKB][8 KB]
+    uint8_t* h_s = base + 2 * NKB * W_KB;                       // LS_STAGES x (hi 8 KB | lo 8 KB)
+    const uint32_t H_TILE = LS_NB * 128, STAGE = 2 * H_TILE;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int u0 = blockIdx.x * LS_UNITS, b0 = blockIdx.y * LS_NB;
+    const int ncta = gridDim.x;
+    int* counter = a.counter + blockIdx.y;
+    const long long BH = (long long)B * H;
+
+    if (tid == 0) {
+        tma_prefetch_desc(&tma_hi);
+        tma_prefetch_desc(&tma_lo);
+        for (int s = 0; s < LS_STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(&acc_full, 1);
+        mbar_init(&acc_empty, 128);
+        mbar_fence_init();
+    }
+    // resident W_hh slice: row = gate*16 + u  <->  W_hh[gate*H + u0 + u, :], split into hi/lo
+    for (int i = tid; i < LS_ROWS * (H / 8); i += blockDim.x) {
+        const int row = i / (H / 8), ch = i - row * (H / 8);
+        const int kb = ch >> 3, c = ch & 7;
+        const float* src = a.w_hh + (long long)((row >> 4) * H + u0 + (row & 15)) * H + ch * 8;
+        const float4 x0 = __ldg(reinterpret_cast<const float4*>(src));
+        const float4 x1 = __ldg(reinterpret_cast<const float4*>(src) + 1);
+        const float v[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+        float l[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) l[e] = v[e] - ls_round(v[e]);
+        const uint32_t off = (uint32_t)kb * W_KB + ls_sw128(row, c);
+        *reinterpret_cast<uint4*>(w_s + off) =
+            make_uint4(ls_pack(v[0], v[1]), ls_pack(v[2], v[3]), ls_pack(v[4], v[5]), ls_pack(v[6], v[7]));
+        *reinterpret_cast<uint4*>(w_s + NKB * W_KB + off) =
+            make_uint4(ls_pack(l[0], l[1]), ls_pack(l[2], l[3]), ls_pack(l[4], l[5]), ls_pack(l[6], l[7]));
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    if (warp == 1) tmem_alloc(&tmem_slot, 64);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+
+    // pointwise mapping (warps 2..9): batch row b and 4 consecutive hidden units
+    const int pt = tid - 64;                    // 0..255 for pointwise threads
+    const int pb = pt & 63, pu = (pt >> 6) * 4; // local batch row, first local unit
+    const bool pw = warp >= 2;
+    const bool pvalid = pw && (b0 + pb) < B;
+    float c_reg[4] = {0.f, 0.f, 0.f, 0.f};
+
+    // ---- prologue: publish h0 as bf16 (hi, lo) into ping-pong buffer 0; load c0
+    if (pvalid) {
+        const long long o = (long long)(b0 + pb) * H + u0 + pu;
+        const float4 h0 = *reinterpret_cast<const float4*>(a.hs_ext + o);
+        const float4 c0 = *reinterpret_cast<const float4*>(a.cs_ext + o);
+        c_reg[0] = c0.x; c_reg[1] = c0.y; c_reg[2] = c0.z; c_reg[3] = c0.w;
+        const float hv[4] = {h0.x, h0.y, h0.z, h0.w};
+        uint2 hi, lo;
+        hi.x = ls_pack(hv[0], hv[1]); hi.y = ls_pack(hv[2], hv[3]);
+        lo.x = ls_pack(hv[0] - ls_round(hv[0]), hv[1] - ls_round(hv[1]));
+        lo.y = ls_pack(hv[2] - ls_round(hv[2]), hv[3] - ls_round(hv[3]));
+        *reinterpret_cast<uint2*>(a.h16_hi + o) = hi;
+        *reinterpret_cast<uint2*>(a.h16_lo + o) = lo;
+    }
+    if (pw) {
+        __threadfence();
+        named_bar_sync(1, 256);
+        if (pt == 0) atomicAdd(counter, 1);
+    }
+
+    uint32_t it = 0;   // ring iteration counter (producer and MMA warps keep identical copies)
+    for (int t = 0; t < a.T; ++t) {
+        const int p = t & 1;
+        if (warp == 0) {
+            if (lane == 0) {
+                // wait until every CTA of this batch group has published h_{t-1}
+                const int target = ncta * (t + 1);
+                uint32_t spins = 0;
+                while (ld_acquire(counter) < target)
+                    if (++spins > (1u << 28)) __trap();
+                asm volatile("fence.proxy.async;" ::: "memory");   // generic writes -> TMA reads
+                for (int kb = 0; kb < NKB; ++kb, ++it) {
+                    const int s = it % LS_STAGES;
+                    mbar_wait(&empty_bar[s], ((it / LS_STAGES) & 1) ^ 1);
+                    mbar_expect_tx(&full_bar[s], STAGE);
+                    uint8_t* dst = h_s + (size_t)s * STAGE;
+                    tma_load_2d(dst, &tma_hi, kb * 64, p * B + b0, &full_bar[s]);
+                    tma_load_2d(dst + H_TILE, &tma_lo, kb * 64, p * B + b0, &full_bar[s]);
+                }
+            }
+        } else if (warp == 1) {
+            if (lane == 0) {
+                constexpr uint32_t idesc = umma_idesc_bf16(LS_ROWS, LS_NB);
+                mbar_wait(&acc_empty, (t & 1) ^ 1);                // readers drained step t-1
+                tc_fence_after();
+                const uint32_t w_hi = smem_u32(w_s), w_lo = w_hi + NKB * W_KB;
+                for (int kb = 0; kb < NKB; ++kb, ++it) {
+                    const int s = it % LS_STAGES;
+                    mbar_wait(&full_bar[s], (it / LS_STAGES) & 1);
+                    tc_fence_after();
+                    const uint32_t hhi = smem_u32(h_s + (size_t)s * STAGE), hlo = hhi + H_TILE;
+                    const uint32_t whi = w_hi + kb * W_KB, wlo = w_lo + kb * W_KB;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        umma_f16(tmem_base, umma_desc_k_sw128(whi + k * 32), umma_desc_k_sw128(hhi + k * 32),
+                                 idesc, (kb | k) != 0);
+                        umma_f16(tmem_base, umma_desc_k_sw128(wlo + k * 32), umma_desc_k_sw128(hhi + k * 32),
+                                 idesc, 1);
+                        umma_f16(tmem_base, umma_desc_k_sw128(whi + k * 32), umma_desc_k_sw128(hlo + k * 32),
+                                 idesc, 1);
+                    }
+                    umma_commit(&empty_bar[s]);
+                }
+                umma_commit(&acc_full);
+            }
+        } else {
+            // ---- pointwise threads: prefetch this step's input projection (independent of the MMA)
+            float xp[4][4];
+            if (pvalid) {
+                const float* xc = a.xprojT + a.col0 + (long long)t * B + b0 + pb;
+#pragma unroll
+                for (int g = 0; g < 4; ++g)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        xp[g][j] = __ldg(xc + (long long)(g * H + u0 + pu + j) * a.ldx);
+            }
+            if (warp < 6) {
+                // ---- TMEM readers: gate q = warp % 4, unit = lane (< 16), 64 batch columns
+                const int q = warp & 3;
+                mbar_wait(&acc_full, t & 1);
+                tc_fence_after();
+                uint32_t r0[32], r1[32];
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16), r0);
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + 32, r1);
+                tmem_ld_wait();
+                tc_fence_before();
+                mbar_arrive(&acc_empty);
+                if (lane < LS_UNITS) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) {
+                        *reinterpret_cast<float4*>(&G[q][lane][j]) =
+                            make_float4(__uint_as_float(r0[j]), __uint_as_float(r0[j + 1]),
+                                        __uint_as_float(r0[j + 2]), __uint_as_float(r0[j + 3]));
+                        *reinterpret_cast<float4*>(&G[q][lane][32 + j]) =
+                            make_float4(__uint_as_float(r1[j]), __uint_as_float(r1[j + 1]),
+                                        __uint_as_float(r1[j + 2]), __uint_as_float(r1[j + 3]));
+                    }
+                }
+            }
+            named_bar_sync(1, 256);                                 // G complete
+            if (pvalid) {
+                float hv[4], cv[4], gi[4], gf[4], gg[4], go[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    gi[j] = ls_sigmoid(G[0][pu + j][pb] + xp[0][j]);
+                    gf[j] = ls_sigmoid(G[1][pu + j][pb] + xp[1][j]);
+                    gg[j] = tanhf(G[2][pu + j][pb] + xp[2][j]);
+                    go[j] = ls_sigmoid(G[3][pu + j][pb] + xp[3][j]);
+                    cv[j] = gf[j] * c_reg[j] + gi[j] * gg[j];
+                    hv[j] = go[j] * tanhf(cv[j]);
+                    c_reg[j] = cv[j];
+                }
+                const long long o = (long long)(b0 + pb) * H + u0 + pu;
+                *reinterpret_cast<float4*>(a.hs_ext + (long long)(t + 1) * BH + o) = make_float4(hv[0], hv[1], hv[2], hv[3]);
+                *reinterpret_cast<float4*>(a.cs_ext + (long long)(t + 1) * BH + o) = make_float4(cv[0], cv[1], cv[2], cv[3]);
+                uint2 hi, lo;
+                hi.x = ls_pack(hv[0], hv[1]); hi.y = ls_pack(hv[2], hv[3]);
+                lo.x = ls_pack(hv[0] - ls_round(hv[0]), hv[1] - ls_round(hv[1]));
+                lo.y = ls_pack(hv[2] - ls_round(hv[2]), hv[3] - ls_round(hv[3]));
+                const long long o16 = (long long)((t + 1) & 1) * BH + o;
+                *reinterpret_cast<uint2*>(a.h16_hi + o16) = hi;
+                *reinterpret_cast<uint2*>(a.h16_lo + o16) = lo;
+                if (a.gates) {
+                    float* gp = a.gates + ((long long)t * B + b0 + pb) * 4 * H + u0 + pu;
+                    *reinterpret_cast<float4*>(gp) = make_float4(gi[0], gi[1], gi[2], gi[3]);
+                    *reinterpret_cast<float4*>(gp + H) = make_float4(gf[0], gf[1], gf[2], gf[3]);
+                    *reinterpret_cast<float4*>(gp + 2 * H) = make_float4(gg[0], gg[1], gg[2], gg[3]);
+                    *reinterpret_cast<float4*>(gp + 3 * H) = make_float4(go[0], go[1], go[2], go[3]);
+                }
+            }
+            __threadfence();
+            named_bar_sync(2, 256);                                 // all of this CTA's h_t is out
+            if (pt == 0) atomicAdd(counter, 1);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, 64);
+}
+
+typedef CUresult (*EncodeTiledFn2)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static int make_h_tmap(CUtensorMap* tm, const void* base, long long rows, long long cols) {
+    static EncodeTiledFn2 fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn2>(p);
+    }
+    R2D2_REQUIRE(fn, "tc_lstm: cuTensorMapEncodeTiled is unavailable in this driver");
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
+    cuuint32_t box[2] = {64, (cuuint32_t)LS_NB};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box,
+                    estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    R2D2_REQUIRE(r == CUDA_SUCCESS, "tc_lstm: cuTensorMapEncodeTiled failed with %d", (int)r);
+    return R2D2_OK;
+}
+
+}  // namespace r2d2
+
+using namespace r2d2;
+
+extern "C" {
+
+int64_t r2d2_tc_lstm_scratch_bytes(int B, int H) {
+    // h16 hi + lo ping-pong [2,B,H] bf16 each, + barrier counters (256 B, kept 256-byte aligned)
+    const int64_t h16 = (int64_t)2 * B * H * 2;
+    return 2 * ((h16 + 255) / 256 * 256) + 256;
+}
+
+int r2d2_tc_lstm_seq_fwd(const float* xprojT, int64_t ldx, int64_t col0, const float* w_hh,
+                         float* hs_ext, float* cs_ext, float* gates, int T, int B, int H,
+                         void* scratch, void* stream) {
+    R2D2_REQUIRE(xprojT && w_hh && hs_ext && cs_ext && scratch, "tc_lstm_seq_fwd: null pointer");
+    R2D2_REQUIRE(T > 0 && B > 0 && H > 0 && H % 64 == 0 && H <= 512,
+                 "tc_lstm_seq_fwd: H must be a multiple of 64 and <= 512 (H=%d)", H);
+    R2D2_REQUIRE(((uintptr_t)w_hh % 16) == 0 && ((uintptr_t)hs_ext % 16) == 0 &&
+                     ((uintptr_t)cs_ext % 16) == 0 && ((uintptr_t)scratch % 256) == 0 &&
+                     (!gates || ((uintptr_t)gates % 16) == 0),
+                 "tc_lstm_seq_fwd: misaligned buffer");
+    cudaStream_t st = as_stream(stream);
+    const int64_t h16 = ((int64_t)2 * B * H * 2 + 255) / 256 * 256;
+    uint8_t* sc = static_cast<uint8_t*>(scratch);
+    LstmArgs a;
+    a.xprojT = xprojT; a.ldx = ldx; a.col0 = col0; a.w_hh = w_hh;
+    a.hs_ext = hs_ext; a.cs_ext = cs_ext; a.gates = gates;
+    a.h16_hi = reinterpret_cast<__nv_bfloat16*>(sc);
+    a.h16_lo = reinterpret_cast<__nv_bfloat16*>(sc + h16);
+    a.counter = reinterpret_cast<int*>(sc + 2 * h16);
+    a.T = T; a.B = B; a.H = H;
+    const int groups = (B + LS_NB - 1) / LS_NB;
+    R2D2_REQUIRE(groups <= 64, "tc_lstm_seq_fwd: batch too large");
+    R2D2_CUDA_OK(cudaMemsetAsync(a.counter, 0, 256, st));
+    CUtensorMap thi, tlo;
+    int rc = make_h_tmap(&thi, a.h16_hi, 2ll * B, H);
+    if (rc) return rc;
+    rc = make_h_tmap(&tlo, a.h16_lo, 2ll * B, H);
+    if (rc) return rc;
+    const int NKB = H / 64;
+    const int smem = 2 * NKB * LS_ROWS * 128 + LS_STAGES * 2 * LS_NB * 128 + 1024;
+    R2D2_CUDA_OK(cudaFuncSetAttribute(tc_lstm_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    dim3 grid(H / LS_UNITS, groups);
+    R2D2_REQUIRE((int)(grid.x * grid.y) <= sm_count(),
+                 "tc_lstm_seq_fwd: %d CTAs must be co-resident but the device has %d SMs",
+                 grid.x * grid.y, sm_count());
+    void* params[] = {&thi, &tlo, &a};
+    {
+        ProfScope ps("tc_lstm_fwd_kernel", st);
+        R2D2_CUDA_OK(cudaLaunchCooperativeKernel((void*)tc_lstm_fwd_kernel, grid, dim3(320), params,
+                                                 (size_t)smem, st));
+    }
+    return R2D2_OK;
+}
+
+}  // extern "C"

@@ -148,12 +148,22 @@ def tc_linear(x16, w16, b1, b2, y32=None, y16=None, relu=False):
               P(y32, "f32", True), P(y16, "bf16", True), M, N, K, int(relu), S())
 
 
-def tc_linear_x3(x_hi, x_lo, w_hi, w_lo, b1, b2, y32=None, y16=None, relu=False):
+def tc_linear_x3(x_hi, x_lo, w_hi, w_lo, b1, b2, y32=None, y16=None, relu=False, bias_row=False):
     M, K = x_hi.shape
     N = w_hi.shape[0]
     _lib.call("r2d2_tc_linear_x3", P(x_hi, "bf16"), P(x_lo, "bf16"), P(w_hi, "bf16"), P(w_lo, "bf16"),
               P(b1, "f32", True), P(b2, "f32", True), P(y32, "f32", True), P(y16, "bf16", True),
-              M, N, K, int(relu), S())
+              M, N, K, int(relu) | (2 if bias_row else 0), S())
+
+
+def tc_lstm_scratch_bytes(B, H):
+    return int(_lib.load().r2d2_tc_lstm_scratch_bytes(B, H))
+
+
+def tc_lstm_seq_fwd(xprojT, col0, w_hh, hs_ext, cs_ext, gates, T, B, H, scratch):
+    """xprojT: [4H, ldx] f32 (transposed input projection, biases included)."""
+    _lib.call("r2d2_tc_lstm_seq_fwd", P(xprojT, "f32"), xprojT.shape[1], col0, P(w_hh, "f32"),
+              P(hs_ext, "f32"), P(cs_ext, "f32"), P(gates, "f32", True), T, B, H, P(scratch), S())
 
 
 def split_bf16(x, hi, lo):

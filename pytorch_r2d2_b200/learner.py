@@ -184,6 +184,9 @@ class Learner:
             ws["w_ih16"], ws["w_ih16_t"], ws["w_ihT16"] = h(2, 4 * H, FEAT), h(2, 4 * H, FEAT), h(FEAT, 4 * H)
             ws["hw1_16"], ws["hw1_16_t"], ws["hw1T16"] = h(2, 2 * H, H), h(2, 2 * H, H), h(H, 2 * H)
             ws["hs16"] = h(2, M, H)
+            # transposed input projections [4H, frames*B] for the persistent LSTM kernel
+            ws["xpT_on"], ws["xpT_tg"] = f(4 * H, S * B), f(4 * H, T * B)
+            ws["lstm_scratch"] = torch.empty(engine.tc_lstm_scratch_bytes(B, H), dtype=torch.uint8, device=dev)
             ws["dhid16"], ws["dhidT16"], ws["hsT16"] = h(M, 2 * H), h(2 * H, M), h(H, M)
             ws["dg16"], ws["dgT16"], ws["hprevT16"], ws["featT16"] = h(M, 4 * H), h(4 * H, M), h(H, M), h(FEAT, M)
         self._ws = ws
@@ -223,27 +226,36 @@ class Learner:
             split(ws["feat_on"], ws["feat16_on"])
             split(ws["feat_tg"], ws["feat16_tg"])
             # forward contractions: error-compensated bf16x3
-            engine.tc_linear_x3(ws["feat16_on"][0], ws["feat16_on"][1], ws["w_ih16"][0], ws["w_ih16"][1],
-                                w.b_ih, w.b_hh, y32=ws["xp_on"])
-            engine.tc_linear_x3(ws["feat16_tg"][0], ws["feat16_tg"][1], ws["w_ih16_t"][0],
-                                ws["w_ih16_t"][1], wt.b_ih, wt.b_hh, y32=ws["xp_tg"])
+            # xproj^T[4H, frames*B] = W_ih . feat^T + (b_ih + b_hh) per row
+            engine.tc_linear_x3(ws["w_ih16"][0], ws["w_ih16"][1], ws["feat16_on"][0], ws["feat16_on"][1],
+                                w.b_ih, w.b_hh, y32=ws["xpT_on"], bias_row=True)
+            engine.tc_linear_x3(ws["w_ih16_t"][0], ws["w_ih16_t"][1], ws["feat16_tg"][0],
+                                ws["feat16_tg"][1], wt.b_ih, wt.b_hh, y32=ws["xpT_tg"], bias_row=True)
         else:
             engine.linear_fwd(ws["feat_on"], w.w_ih, w.b_ih, w.b_hh, ws["xp_on"])
             engine.linear_fwd(ws["feat_tg"], wt.w_ih, wt.b_ih, wt.b_hh, ws["xp_tg"])
 
-        # ---- online net: burn-in + learn over state[0:T] (hidden state carries through)
+        # ---- online net: burn-in + learn over state[0:T] (hidden state carries through); then
+        #      again on next_state[BI:T] = frames BI+n.., starting from the state left after
+        #      state[T-1] (the reference never resets it: learner.py:86,91); target net: burn-in
+        #      on next_state[0:BI], then next_state[BI:T]
         ws["hs_on"][0].copy_(batch["hs"])
         ws["cs_on"][0].copy_(batch["cs"])
-        engine.lstm_seq_fwd(ws["xp_on"], w.w_hh, ws["hs_on"], ws["cs_on"], ws["gates"], T, B, H)
-        # ---- online net again on next_state[BI:T] = frames BI+n.., starting from the state left
-        #      after state[T-1] (the reference never resets it: learner.py:86,91)
-        ws["hs_dq"][0].copy_(ws["hs_on"][T])
-        ws["cs_dq"][0].copy_(ws["cs_on"][T])
-        engine.lstm_seq_fwd(ws["xp_on"][(BI + n) * B:], w.w_hh, ws["hs_dq"], ws["cs_dq"], None, L, B, H)
-        # ---- target net: burn-in on next_state[0:BI], then next_state[BI:T]
         ws["hs_tg"][0].copy_(batch["target_hs"])
         ws["cs_tg"][0].copy_(batch["target_cs"])
-        engine.lstm_seq_fwd(ws["xp_tg"], wt.w_hh, ws["hs_tg"], ws["cs_tg"], None, T, B, H)
+        if bf16:
+            sc = ws["lstm_scratch"]
+            engine.tc_lstm_seq_fwd(ws["xpT_on"], 0, w.w_hh, ws["hs_on"], ws["cs_on"], ws["gates"], T, B, H, sc)
+            ws["hs_dq"][0].copy_(ws["hs_on"][T])
+            ws["cs_dq"][0].copy_(ws["cs_on"][T])
+            engine.tc_lstm_seq_fwd(ws["xpT_on"], (BI + n) * B, w.w_hh, ws["hs_dq"], ws["cs_dq"], None, L, B, H, sc)
+            engine.tc_lstm_seq_fwd(ws["xpT_tg"], 0, wt.w_hh, ws["hs_tg"], ws["cs_tg"], None, T, B, H, sc)
+        else:
+            engine.lstm_seq_fwd(ws["xp_on"], w.w_hh, ws["hs_on"], ws["cs_on"], ws["gates"], T, B, H)
+            ws["hs_dq"][0].copy_(ws["hs_on"][T])
+            ws["cs_dq"][0].copy_(ws["cs_on"][T])
+            engine.lstm_seq_fwd(ws["xp_on"][(BI + n) * B:], w.w_hh, ws["hs_dq"], ws["cs_dq"], None, L, B, H)
+            engine.lstm_seq_fwd(ws["xp_tg"], wt.w_hh, ws["hs_tg"], ws["cs_tg"], None, T, B, H)
 
         # ---- dueling heads on the learn window only
         hs_learn = ws["hs_on"][1 + BI:].reshape(M, H)

@@ -98,3 +98,35 @@ def test_tc_torso_vs_torch(cuda_device):
     engine.torso_fwd_u8(slab2, 0, 8, w, c1, c2, f2, tc=True)
     engine.torso_fwd_u8(slab2, 0, 8, w, d1, d2, g2, tc=False)
     assert rel_err(c1, d1) < 1e-5 and rel_err(c2, d2) < 1e-5 and rel_err(f2, g2) < 1e-5
+
+
+@pytest.mark.parametrize("H,B,T", [(256, 4, 5), (512, 64, 6), (512, 8, 3), (256, 100, 2)])
+def test_tc_lstm_vs_torch(cuda_device, H, B, T):
+    """Persistent tensor-core LSTM unroll == fp32 recurrence to 1e-5 (bf16x3 compensation),
+    incl. batches that are not a multiple of the 64-column tile and > 1 batch group."""
+    from pytorch_r2d2_b200 import engine
+    g = torch.Generator().manual_seed(H + B + T)
+    xproj = torch.randn(T, B, 4 * H, generator=g) * 0.5
+    w_hh = torch.randn(4 * H, H, generator=g) * 0.05
+    h0, c0 = torch.randn(B, H, generator=g) * 0.1, torch.randn(B, H, generator=g) * 0.1
+    h, c, hs, cs, gs = h0, c0, [], [], []
+    for t in range(T):
+        gates = xproj[t] + h @ w_hh.T
+        i, f, gg, o = gates.chunk(4, 1)
+        i, f, gg, o = torch.sigmoid(i), torch.sigmoid(f), torch.tanh(gg), torch.sigmoid(o)
+        c = f * c + i * gg
+        h = o * torch.tanh(c)
+        hs.append(h); cs.append(c); gs.append(torch.cat([i, f, gg, o], 1))
+    xprojT = xproj.reshape(T * B, 4 * H).T.contiguous().cuda()          # [4H, T*B]
+    pad = torch.zeros(4 * H, 3 * B, device="cuda")                        # exercise col0 != 0
+    xprojT = torch.cat([pad, xprojT], 1).contiguous()
+    hs_ext = torch.empty(T + 1, B, H, device="cuda"); cs_ext = torch.empty(T + 1, B, H, device="cuda")
+    hs_ext[0], cs_ext[0] = h0.cuda(), c0.cuda()
+    gates_d = torch.empty(T, B, 4 * H, device="cuda")
+    scratch = torch.empty(engine.tc_lstm_scratch_bytes(B, H), dtype=torch.uint8, device="cuda")
+    for _ in range(2):                                                    # twice: scratch reuse
+        engine.tc_lstm_seq_fwd(xprojT, 3 * B, w_hh.cuda(), hs_ext, cs_ext, gates_d, T, B, H, scratch)
+    torch.cuda.synchronize()
+    assert rel_err(hs_ext[1:], torch.stack(hs)) < 1e-5, rel_err(hs_ext[1:], torch.stack(hs))
+    assert rel_err(cs_ext[1:], torch.stack(cs)) < 1e-5
+    assert rel_err(gates_d, torch.stack(gs)) < 1e-5
