@@ -60,20 +60,28 @@ colsum_kernel(const float* __restrict__ dy, float* __restrict__ db, int M, int N
     }
 }
 
-// per-channel sum over frames and pixels of an NCHW gradient: db[c] = sum_{r,p} dz[r,c,p]
-__global__ void __launch_bounds__(1024)
-chansum_kernel(const float* __restrict__ dz, float* __restrict__ db, int R, int C, int PIX) {
+// per-channel sum over frames and pixels of an NCHW gradient: db[c] = sum_{r,p} dz[r,c,p].
+// grid (C, CS_SPLITS): block (c, z) sums frames z, z+CS_SPLITS, ... into part[z*C + c]; the
+// partials are then added in fixed order (deterministic, no atomics).
+constexpr int CS_SPLITS = 37;   // 32 channels x 37 = 1184 CTAs = 8 per SM
+__global__ void __launch_bounds__(256)
+chansum_partial_kernel(const float* __restrict__ dz, float* __restrict__ part, int R, int C, int PIX) {
     __shared__ float red[32];
-    const int c = blockIdx.x;
-    const int64_t total = (int64_t)R * PIX;
+    const int c = blockIdx.x, z = blockIdx.y;
     float s = 0.f;
-    for (int64_t e = threadIdx.x; e < total; e += blockDim.x) {
-        const int64_t r = e / PIX;
-        const int p = (int)(e - r * PIX);
-        s += dz[(r * C + c) * PIX + p];
+    for (int r = z; r < R; r += CS_SPLITS) {
+        const float* p = dz + ((int64_t)r * C + c) * PIX;
+        for (int i = threadIdx.x; i < PIX; i += blockDim.x) s += p[i];
     }
     s = block_sum(s, red);
-    if (threadIdx.x == 0) db[c] = s;
+    if (threadIdx.x == 0) part[z * C + c] = s;
+}
+__global__ void chansum_final_kernel(const float* __restrict__ part, float* __restrict__ db, int C) {
+    const int c = threadIdx.x;
+    if (c >= C) return;
+    float s = 0.f;
+    for (int z = 0; z < CS_SPLITS; ++z) s += part[z * C + c];
+    db[c] = s;
 }
 
 // d[i] = a[i] > 0 ? d[i] : 0
@@ -564,7 +572,8 @@ static int torso_bwd_impl(const T* frames, FrameMap fm, int R, const float* a1, 
         ConvPatchCols<float, 32, 3, 9, 7, 1> bl{a2, FrameMap{0, 0, 0, 2592}};
         int rc = conv_wgrad("conv3_wgrad", al, bl, 288, R * 49, dw3, part, st);
         if (rc) return rc;
-        R2D2_LAUNCH("chansum_kernel", st, chansum_kernel<<<32, 1024, 0, st>>>(dfeat, db3, R, 32, 49));
+        R2D2_LAUNCH("chansum_partial_kernel", st, chansum_partial_kernel<<<dim3(32, CS_SPLITS), 256, 0, st>>>(dfeat, part, R, 32, 49));
+        R2D2_LAUNCH("chansum_final_kernel", st, chansum_final_kernel<<<1, 32, 0, st>>>(part, db3, 32));
     }
     {
         constexpr int smem = (32 * 3 * 3 * 32 + 32 * 49) * 4;
@@ -577,7 +586,8 @@ static int torso_bwd_impl(const T* frames, FrameMap fm, int R, const float* a1, 
         ConvPatchCols<float, 32, 4, 20, 9, 2> bl{a1, FrameMap{0, 0, 0, 12800}};
         int rc = conv_wgrad("conv2_wgrad", al, bl, 512, R * 81, dw2, part, st);
         if (rc) return rc;
-        R2D2_LAUNCH("chansum_kernel", st, chansum_kernel<<<32, 1024, 0, st>>>(dz2, db2, R, 32, 81));
+        R2D2_LAUNCH("chansum_partial_kernel", st, chansum_partial_kernel<<<dim3(32, CS_SPLITS), 256, 0, st>>>(dz2, part, R, 32, 81));
+        R2D2_LAUNCH("chansum_final_kernel", st, chansum_final_kernel<<<1, 32, 0, st>>>(part, db2, 32));
     }
     {
         constexpr int smem = (32 * 4 * 4 * 32 + 32 * 81) * 4;
@@ -590,7 +600,8 @@ static int torso_bwd_impl(const T* frames, FrameMap fm, int R, const float* a1, 
         ConvPatchCols<T, 4, 8, 84, 20, 4> bl{frames, fm};
         int rc = conv_wgrad("conv1_wgrad", al, bl, 256, R * 400, dw1, part, st);
         if (rc) return rc;
-        R2D2_LAUNCH("chansum_kernel", st, chansum_kernel<<<32, 1024, 0, st>>>(dz1, db1, R, 32, 400));
+        R2D2_LAUNCH("chansum_partial_kernel", st, chansum_partial_kernel<<<dim3(32, CS_SPLITS), 256, 0, st>>>(dz1, part, R, 32, 400));
+        R2D2_LAUNCH("chansum_final_kernel", st, chansum_final_kernel<<<1, 32, 0, st>>>(part, db1, 32));
     }
     return R2D2_OK;
 }

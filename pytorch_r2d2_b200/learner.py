@@ -187,6 +187,9 @@ class Learner:
             # transposed input projections [4H, frames*B] for the persistent LSTM kernel
             ws["xpT_on"], ws["xpT_tg"] = f(4 * H, S * B), f(4 * H, T * B)
             ws["lstm_scratch"] = torch.empty(engine.tc_lstm_scratch_bytes(B, H), dtype=torch.uint8, device=dev)
+            ws["lstm_scratch_tg"] = torch.empty_like(ws["lstm_scratch"])
+            ws["side_stream"] = torch.cuda.Stream(device=dev)
+            ws["ev_fork"], ws["ev_join"] = torch.cuda.Event(), torch.cuda.Event()
             ws["dhid16"], ws["dhidT16"], ws["hsT16"] = h(M, 2 * H), h(2 * H, M), h(H, M)
             ws["dg16"], ws["dgT16"], ws["hprevT16"], ws["featT16"] = h(M, 4 * H), h(4 * H, M), h(H, M), h(FEAT, M)
         self._ws = ws
@@ -244,12 +247,21 @@ class Learner:
         ws["hs_tg"][0].copy_(batch["target_hs"])
         ws["cs_tg"][0].copy_(batch["target_cs"])
         if bf16:
+            # the two chains are independent and latency-bound on H/16 SMs each: run the target
+            # net's unroll on a side stream next to the online net's
+            main, side = torch.cuda.current_stream(), ws["side_stream"]
+            ws["ev_fork"].record(main)
+            side.wait_event(ws["ev_fork"])
+            with torch.cuda.stream(side):
+                engine.tc_lstm_seq_fwd(ws["xpT_tg"], 0, wt.w_hh, ws["hs_tg"], ws["cs_tg"], None, T, B, H,
+                                       ws["lstm_scratch_tg"])
+                ws["ev_join"].record(side)
             sc = ws["lstm_scratch"]
             engine.tc_lstm_seq_fwd(ws["xpT_on"], 0, w.w_hh, ws["hs_on"], ws["cs_on"], ws["gates"], T, B, H, sc)
             ws["hs_dq"][0].copy_(ws["hs_on"][T])
             ws["cs_dq"][0].copy_(ws["cs_on"][T])
             engine.tc_lstm_seq_fwd(ws["xpT_on"], (BI + n) * B, w.w_hh, ws["hs_dq"], ws["cs_dq"], None, L, B, H, sc)
-            engine.tc_lstm_seq_fwd(ws["xpT_tg"], 0, wt.w_hh, ws["hs_tg"], ws["cs_tg"], None, T, B, H, sc)
+            main.wait_event(ws["ev_join"])
         else:
             engine.lstm_seq_fwd(ws["xp_on"], w.w_hh, ws["hs_on"], ws["cs_on"], ws["gates"], T, B, H)
             ws["hs_dq"][0].copy_(ws["hs_on"][T])
