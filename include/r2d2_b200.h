@@ -227,6 +227,12 @@ int64_t r2d2_tc_lstm_scratch_bytes(int B, int H);
 int r2d2_tc_lstm_seq_fwd(const float* xprojT, int64_t ldx, int64_t col0, const float* w_hh,
                          float* hs_ext, float* cs_ext, float* gates, int T, int B, int H,
                          void* scratch, void* stream);
+/* Persistent BPTT on tensor cores (same contract as r2d2_lstm_seq_bwd, plain bf16 operands):
+ * dG_{t+1} streamed by TMA, W_hh^T slice resident, dL/dc in registers, grid-wide counter. */
+int64_t r2d2_tc_lstm_bwd_scratch_bytes(int B, int H);
+int r2d2_tc_lstm_seq_bwd(const float* dhs, const float* w_hh, const float* gates,
+                         const float* cs_ext, float* dgates, int T, int B, int H, void* scratch,
+                         void* stream);
 /* Error-compensated variant ("bf16x3"): x = x_hi + x_lo, w = w_hi + w_lo (r2d2_split_bf16) and
  * y = x_hi.w_hi^T + x_hi.w_lo^T + x_lo.w_hi^T, fp32 accumulation in TMEM -- operand error 2^-16
  * instead of 2^-9.  Used for FORWARD contractions: a 1e-3 forward perturbation flips ReLU masks

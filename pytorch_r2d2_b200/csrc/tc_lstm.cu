@@ -259,11 +259,192 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
     if (warp == 1) tmem_dealloc(tmem_base, 64);
 }
 
+// ------------------------------------------------------------------------------------------
+// BPTT over the learn window, persistent, plain bf16 operands (backward contractions do not
+// need the compensation).  Per step (t descending)
+//   dh[B, u] = dhs_t[B, u] + dG_{t+1}[B, 4H] . W_hh[4H, u]
+// with CTA c owning 16 hidden units u: A = dG_{t+1} (M = 64 batch rows, streamed by TMA from a
+// bf16 ping-pong buffer every CTA writes its columns of), B = its W_hh^T slice [16, 4H] resident
+// in shared memory, D[64, 16] in TMEM.  In the M=64 accumulator layout batch row m sits in lane
+// (m%16) + 32*(m/16), so reader thread (warp q, lane < 16) owns batch row 16q+lane and all 16
+// units: the gate-gradient math runs right there, dL/dc stays in registers across steps.
+struct LstmBwdArgs {
+    const float* dhs;      // [T, B, H] dL/dh_t from the head
+    const float* w_hh;     // [4H, H]
+    const float* gates;    // [T, B, 4H] post-activation i,f,g,o
+    const float* cs_ext;   // [(T+1), B, H], slot t = c_{t-1}, slot t+1 = c_t
+    float* dgates;         // [T, B, 4H] out: pre-activation gradients
+    __nv_bfloat16* dg16;   // [2, B, 4H] ping-pong
+    int* counter;
+    int T, B, H;
+};
+constexpr int LB_STAGES = 16;
+
+__global__ void __launch_bounds__(192, 1)
+tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs a) {
+    const int H = a.H, B = a.B, K4 = 4 * a.H, NKB = K4 / 64;
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t full_bar[LB_STAGES], empty_bar[LB_STAGES], acc_full, acc_empty;
+    __shared__ uint32_t tmem_slot;
+    const uint32_t raw = smem_u32(smem_raw);
+    uint8_t* base = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
+    const uint32_t W_KB = LS_UNITS * 128;                       // 16 rows x 64 bf16 = 2 KB
+    uint8_t* w_s = base;                                        // [NKB][2 KB]
+    const uint32_t A_TILE = LS_NB * 128;                        // 64 rows x 64 bf16 = 8 KB
+    uint8_t* a_s = base + (size_t)NKB * W_KB;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int u0 = blockIdx.x * LS_UNITS, b0 = blockIdx.y * LS_NB;
+    const int ncta = gridDim.x;
+    int* counter = a.counter + blockIdx.y;
+    const long long BH = (long long)B * H, BG = (long long)B * K4;
+
+    if (tid == 0) {
+        tma_prefetch_desc(&tma_dg);
+        for (int s = 0; s < LB_STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(&acc_full, 1);
+        mbar_init(&acc_empty, 128);
+        mbar_fence_init();
+    }
+    // resident B operand: row = unit u, K = gate index j: W_hh[j, u0+u]
+    for (int i = tid; i < LS_UNITS * (K4 / 8); i += blockDim.x) {
+        const int u = i % LS_UNITS, ch = i / LS_UNITS;          // consecutive threads -> consecutive u
+        const int kb = ch >> 3, c = ch & 7;
+        float v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] = __ldg(a.w_hh + (long long)(ch * 8 + e) * H + u0 + u);
+        *reinterpret_cast<uint4*>(w_s + (uint32_t)kb * W_KB + ls_sw128(u, c)) =
+            make_uint4(ls_pack(v[0], v[1]), ls_pack(v[2], v[3]), ls_pack(v[4], v[5]), ls_pack(v[6], v[7]));
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    if (warp == 1) tmem_alloc(&tmem_slot, 32);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+
+    const int q = warp & 3;                                     // readers: warps 2..5
+    const int rb = b0 + q * 16 + lane;                          // batch row of this reader thread
+    const bool rvalid = warp >= 2 && lane < 16 && rb < B;
+    float dc_reg[LS_UNITS];
+#pragma unroll
+    for (int j = 0; j < LS_UNITS; ++j) dc_reg[j] = 0.f;
+
+    uint32_t it = 0;
+    for (int s = 0; s < a.T; ++s) {
+        const int t = a.T - 1 - s;
+        if (warp == 0) {
+            if (lane == 0 && s > 0) {
+                const int target = ncta * s;                    // every CTA finished iteration s-1
+                uint32_t spins = 0;
+                while (ld_acquire(counter) < target)
+                    if (++spins > (1u << 28)) __trap();
+                asm volatile("fence.proxy.async;" ::: "memory");
+                const int p = (s - 1) & 1;
+                for (int kb = 0; kb < NKB; ++kb, ++it) {
+                    const int st = it % LB_STAGES;
+                    mbar_wait(&empty_bar[st], ((it / LB_STAGES) & 1) ^ 1);
+                    mbar_expect_tx(&full_bar[st], A_TILE);
+                    tma_load_2d(a_s + (size_t)st * A_TILE, &tma_dg, kb * 64, p * B + b0, &full_bar[st]);
+                }
+            }
+        } else if (warp == 1) {
+            if (lane == 0 && s > 0) {
+                constexpr uint32_t idesc = umma_idesc_bf16(LS_NB, LS_UNITS);
+                mbar_wait(&acc_empty, s & 1);   // readers drained iteration s-1 (s=1: passes at once)
+                tc_fence_after();
+                const uint32_t wb = smem_u32(w_s);
+                for (int kb = 0; kb < NKB; ++kb, ++it) {
+                    const int st = it % LB_STAGES;
+                    mbar_wait(&full_bar[st], (it / LB_STAGES) & 1);
+                    tc_fence_after();
+                    const uint32_t aa = smem_u32(a_s + (size_t)st * A_TILE), bb = wb + kb * W_KB;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        umma_f16(tmem_base, umma_desc_k_sw128(aa + k * 32), umma_desc_k_sw128(bb + k * 32),
+                                 idesc, (kb | k) != 0);
+                    umma_commit(&empty_bar[st]);
+                }
+                umma_commit(&acc_full);
+            }
+        } else {
+            // ---- readers + gate-gradient math (64 active threads per CTA)
+            float rec[LS_UNITS];
+#pragma unroll
+            for (int j = 0; j < LS_UNITS; ++j) rec[j] = 0.f;
+            if (s > 0) {
+                mbar_wait(&acc_full, (s - 1) & 1);
+                tc_fence_after();
+                uint32_t r[32];
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16), r);
+                tmem_ld_wait();
+                tc_fence_before();
+                mbar_arrive(&acc_empty);
+#pragma unroll
+                for (int j = 0; j < LS_UNITS; ++j) rec[j] = __uint_as_float(r[j]);
+            }
+            if (rvalid) {
+                const long long o = (long long)rb * H + u0;
+                const float* gp = a.gates + ((long long)t * B + rb) * K4 + u0;
+                float* dgp = a.dgates + ((long long)t * B + rb) * K4 + u0;
+                __nv_bfloat16* d16 = a.dg16 + (long long)(s & 1) * BG + (long long)rb * K4 + u0;
+                float gi[16], gf[16], gg[16], go[16], ct[16], cp[16], dh[16];
+#pragma unroll
+                for (int j = 0; j < 16; j += 4) {
+                    *reinterpret_cast<float4*>(gi + j) = *reinterpret_cast<const float4*>(gp + j);
+                    *reinterpret_cast<float4*>(gf + j) = *reinterpret_cast<const float4*>(gp + H + j);
+                    *reinterpret_cast<float4*>(gg + j) = *reinterpret_cast<const float4*>(gp + 2 * H + j);
+                    *reinterpret_cast<float4*>(go + j) = *reinterpret_cast<const float4*>(gp + 3 * H + j);
+                    *reinterpret_cast<float4*>(ct + j) = *reinterpret_cast<const float4*>(a.cs_ext + (long long)(t + 1) * BH + o + j);
+                    *reinterpret_cast<float4*>(cp + j) = *reinterpret_cast<const float4*>(a.cs_ext + (long long)t * BH + o + j);
+                    *reinterpret_cast<float4*>(dh + j) = *reinterpret_cast<const float4*>(a.dhs + (long long)t * BH + o + j);
+                }
+                float di[16], df[16], dg[16], dov[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const float d = dh[j] + rec[j];
+                    const float tc = tanhf(ct[j]);
+                    const float dc = dc_reg[j] + d * go[j] * (1.f - tc * tc);
+                    di[j] = dc * gg[j] * gi[j] * (1.f - gi[j]);
+                    df[j] = dc * cp[j] * gf[j] * (1.f - gf[j]);
+                    dg[j] = dc * gi[j] * (1.f - gg[j] * gg[j]);
+                    dov[j] = d * tc * go[j] * (1.f - go[j]);
+                    dc_reg[j] = dc * gf[j];
+                }
+#pragma unroll
+                for (int j = 0; j < 16; j += 4) {
+                    *reinterpret_cast<float4*>(dgp + j) = make_float4(di[j], di[j + 1], di[j + 2], di[j + 3]);
+                    *reinterpret_cast<float4*>(dgp + H + j) = make_float4(df[j], df[j + 1], df[j + 2], df[j + 3]);
+                    *reinterpret_cast<float4*>(dgp + 2 * H + j) = make_float4(dg[j], dg[j + 1], dg[j + 2], dg[j + 3]);
+                    *reinterpret_cast<float4*>(dgp + 3 * H + j) = make_float4(dov[j], dov[j + 1], dov[j + 2], dov[j + 3]);
+                }
+#pragma unroll
+                for (int j = 0; j < 16; j += 8) {
+                    *reinterpret_cast<uint4*>(d16 + j) = make_uint4(ls_pack(di[j], di[j + 1]), ls_pack(di[j + 2], di[j + 3]), ls_pack(di[j + 4], di[j + 5]), ls_pack(di[j + 6], di[j + 7]));
+                    *reinterpret_cast<uint4*>(d16 + H + j) = make_uint4(ls_pack(df[j], df[j + 1]), ls_pack(df[j + 2], df[j + 3]), ls_pack(df[j + 4], df[j + 5]), ls_pack(df[j + 6], df[j + 7]));
+                    *reinterpret_cast<uint4*>(d16 + 2 * H + j) = make_uint4(ls_pack(dg[j], dg[j + 1]), ls_pack(dg[j + 2], dg[j + 3]), ls_pack(dg[j + 4], dg[j + 5]), ls_pack(dg[j + 6], dg[j + 7]));
+                    *reinterpret_cast<uint4*>(d16 + 3 * H + j) = make_uint4(ls_pack(dov[j], dov[j + 1]), ls_pack(dov[j + 2], dov[j + 3]), ls_pack(dov[j + 4], dov[j + 5]), ls_pack(dov[j + 6], dov[j + 7]));
+                }
+            }
+            __threadfence();
+            named_bar_sync(1, 128);
+            if (tid == 64) atomicAdd(counter, 1);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, 32);
+}
+
 typedef CUresult (*EncodeTiledFn2)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
                                    const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
                                    const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
+static int make_h_tmap(CUtensorMap* tm, const void* base, long long rows, long long cols);
 static int make_h_tmap(CUtensorMap* tm, const void* base, long long rows, long long cols) {
     static EncodeTiledFn2 fn = nullptr;
     if (!fn) {
@@ -336,6 +517,52 @@ int r2d2_tc_lstm_seq_fwd(const float* xprojT, int64_t ldx, int64_t col0, const f
     {
         ProfScope ps("tc_lstm_fwd_kernel", st);
         R2D2_CUDA_OK(cudaLaunchCooperativeKernel((void*)tc_lstm_fwd_kernel, grid, dim3(320), params,
+                                                 (size_t)smem, st));
+    }
+    return R2D2_OK;
+}
+
+}  // extern "C"
+
+extern "C" {
+
+int64_t r2d2_tc_lstm_bwd_scratch_bytes(int B, int H) {
+    const int64_t dg16 = ((int64_t)2 * B * 4 * H * 2 + 255) / 256 * 256;
+    return dg16 + 256;
+}
+
+int r2d2_tc_lstm_seq_bwd(const float* dhs, const float* w_hh, const float* gates,
+                         const float* cs_ext, float* dgates, int T, int B, int H, void* scratch,
+                         void* stream) {
+    R2D2_REQUIRE(dhs && w_hh && gates && cs_ext && dgates && scratch, "tc_lstm_seq_bwd: null pointer");
+    R2D2_REQUIRE(T > 0 && B > 0 && H > 0 && H % 64 == 0 && H <= 512,
+                 "tc_lstm_seq_bwd: H must be a multiple of 64 and <= 512 (H=%d)", H);
+    R2D2_REQUIRE(((uintptr_t)dhs % 16) == 0 && ((uintptr_t)gates % 16) == 0 && ((uintptr_t)cs_ext % 16) == 0 &&
+                     ((uintptr_t)dgates % 16) == 0 && ((uintptr_t)scratch % 256) == 0,
+                 "tc_lstm_seq_bwd: misaligned buffer");
+    cudaStream_t st = as_stream(stream);
+    const int64_t dg16 = ((int64_t)2 * B * 4 * H * 2 + 255) / 256 * 256;
+    uint8_t* sc = static_cast<uint8_t*>(scratch);
+    LstmBwdArgs a;
+    a.dhs = dhs; a.w_hh = w_hh; a.gates = gates; a.cs_ext = cs_ext; a.dgates = dgates;
+    a.dg16 = reinterpret_cast<__nv_bfloat16*>(sc);
+    a.counter = reinterpret_cast<int*>(sc + dg16);
+    a.T = T; a.B = B; a.H = H;
+    const int groups = (B + LS_NB - 1) / LS_NB;
+    R2D2_REQUIRE(groups <= 64, "tc_lstm_seq_bwd: batch too large");
+    R2D2_CUDA_OK(cudaMemsetAsync(a.counter, 0, 256, st));
+    CUtensorMap tdg;
+    int rc = make_h_tmap(&tdg, a.dg16, 2ll * B, 4ll * H);
+    if (rc) return rc;
+    const int NKB = 4 * H / 64;
+    const int smem = NKB * LS_UNITS * 128 + LB_STAGES * LS_NB * 128 + 1024;
+    R2D2_CUDA_OK(cudaFuncSetAttribute(tc_lstm_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    dim3 grid(H / LS_UNITS, groups);
+    R2D2_REQUIRE((int)(grid.x * grid.y) <= sm_count(), "tc_lstm_seq_bwd: %d CTAs must be co-resident", grid.x * grid.y);
+    void* params[] = {&tdg, &a};
+    {
+        ProfScope ps("tc_lstm_bwd_kernel", st);
+        R2D2_CUDA_OK(cudaLaunchCooperativeKernel((void*)tc_lstm_bwd_kernel, grid, dim3(192), params,
                                                  (size_t)smem, st));
     }
     return R2D2_OK;

@@ -156,6 +156,15 @@ def tc_linear_x3(x_hi, x_lo, w_hi, w_lo, b1, b2, y32=None, y16=None, relu=False,
               M, N, K, int(relu) | (2 if bias_row else 0), S())
 
 
+def tc_lstm_bwd_scratch_bytes(B, H):
+    return int(_lib.load().r2d2_tc_lstm_bwd_scratch_bytes(B, H))
+
+
+def tc_lstm_seq_bwd(dhs, w_hh, gates, cs_ext, dgates, T, B, H, scratch):
+    _lib.call("r2d2_tc_lstm_seq_bwd", P(dhs, "f32"), P(w_hh, "f32"), P(gates, "f32"), P(cs_ext, "f32"),
+              P(dgates, "f32"), T, B, H, P(scratch), S())
+
+
 def tc_lstm_scratch_bytes(B, H):
     return int(_lib.load().r2d2_tc_lstm_scratch_bytes(B, H))
 

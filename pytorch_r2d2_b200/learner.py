@@ -188,6 +188,7 @@ class Learner:
             ws["xpT_on"], ws["xpT_tg"] = f(4 * H, S * B), f(4 * H, T * B)
             ws["lstm_scratch"] = torch.empty(engine.tc_lstm_scratch_bytes(B, H), dtype=torch.uint8, device=dev)
             ws["lstm_scratch_tg"] = torch.empty_like(ws["lstm_scratch"])
+            ws["lstm_bwd_scratch"] = torch.empty(engine.tc_lstm_bwd_scratch_bytes(B, H), dtype=torch.uint8, device=dev)
             ws["side_stream"] = torch.cuda.Stream(device=dev)
             ws["ev_fork"], ws["ev_join"] = torch.cuda.Event(), torch.cuda.Event()
             ws["dhid16"], ws["dhidT16"], ws["hsT16"] = h(M, 2 * H), h(2 * H, M), h(H, M)
@@ -310,8 +311,12 @@ class Learner:
         else:
             engine.linear_wgrad(ws["dhid"], hs_learn, g.head_w1, g.head_b1, scratch)
             engine.linear_dgrad(ws["dhid"], w.head_w1, ws["dhs"])
-        engine.lstm_seq_bwd(ws["dhs"], w.w_hh, ws["gates"][BI:], ws["cs_on"][BI:], ws["dgates"],
-                            ws["dc_work"], L, B, H)
+        if bf16:
+            engine.tc_lstm_seq_bwd(ws["dhs"], w.w_hh, ws["gates"][BI:], ws["cs_on"][BI:], ws["dgates"],
+                                   L, B, H, ws["lstm_bwd_scratch"])
+        else:
+            engine.lstm_seq_bwd(ws["dhs"], w.w_hh, ws["gates"][BI:], ws["cs_on"][BI:], ws["dgates"],
+                                ws["dc_work"], L, B, H)
         if bf16:
             engine.transpose_cast_bf16(ws["dgates"], ws["dgT16"])
             engine.transpose_cast_bf16(hprev, ws["hprevT16"])

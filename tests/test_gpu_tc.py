@@ -130,3 +130,34 @@ def test_tc_lstm_vs_torch(cuda_device, H, B, T):
     assert rel_err(hs_ext[1:], torch.stack(hs)) < 1e-5, rel_err(hs_ext[1:], torch.stack(hs))
     assert rel_err(cs_ext[1:], torch.stack(cs)) < 1e-5
     assert rel_err(gates_d, torch.stack(gs)) < 1e-5
+
+
+@pytest.mark.parametrize("H,B,T", [(256, 4, 5), (512, 64, 6), (256, 100, 3)])
+def test_tc_lstm_bwd_vs_autograd(cuda_device, H, B, T):
+    """Persistent tensor-core BPTT == autograd of the fp32 recurrence within the bf16 class
+    (plain bf16 operands in the backward contraction): 1e-2 relative to max|grad|."""
+    from pytorch_r2d2_b200 import engine
+    g = torch.Generator().manual_seed(H * 3 + B + T)
+    xproj = (torch.randn(T, B, 4 * H, generator=g) * 0.5).requires_grad_(True)
+    w_hh = torch.randn(4 * H, H, generator=g) * 0.05
+    h0, c0 = torch.randn(B, H, generator=g) * 0.1, torch.randn(B, H, generator=g) * 0.1
+    dhs = torch.randn(T, B, H, generator=g)
+    h, c, hs, cs, gs = h0, c0, [], [c0], []
+    for t in range(T):
+        gates = xproj[t] + h @ w_hh.T
+        i, f, gg, o = gates.chunk(4, 1)
+        i, f, gg, o = torch.sigmoid(i), torch.sigmoid(f), torch.tanh(gg), torch.sigmoid(o)
+        c = f * c + i * gg
+        h = o * torch.tanh(c)
+        hs.append(h); cs.append(c); gs.append(torch.cat([i, f, gg, o], 1))
+    (torch.stack(hs) * dhs).sum().backward()
+    gates_d = torch.stack(gs).detach().cuda().contiguous()
+    cs_ext = torch.stack(cs).detach().cuda().contiguous()
+    dgates = torch.full((T, B, 4 * H), float("nan"), device="cuda")
+    scratch = torch.empty(engine.tc_lstm_bwd_scratch_bytes(B, H), dtype=torch.uint8, device="cuda")
+    for _ in range(2):
+        engine.tc_lstm_seq_bwd(dhs.cuda(), w_hh.cuda(), gates_d, cs_ext, dgates, T, B, H, scratch)
+    torch.cuda.synchronize()
+    err = rel_err(dgates, xproj.grad)
+    assert err < 1e-2, err
+    assert rel_err(dgates[-1], xproj.grad[-1]) < 1e-5        # last step has no recurrent term
