@@ -233,6 +233,18 @@ int64_t r2d2_tc_lstm_bwd_scratch_bytes(int B, int H);
 int r2d2_tc_lstm_seq_bwd(const float* dhs, const float* w_hh, const float* gates,
                          const float* cs_ext, float* dgates, int T, int B, int H, void* scratch,
                          void* stream);
+/* conv torso backward split for the tensor-core path: r2d2_torso_bwd_dgrad_u8 runs the ReLU
+ * masks, data gradients and bias gradients (scratch as r2d2_torso_bwd_u8: [dz2 | dz1 | partials])
+ * and r2d2_tc_torso_wgrad_u8 the three weight gradients on tcgen05 (plain bf16, the forward's
+ * patch tile reused as an MN-major operand; per-CTA partials summed in fixed order). */
+int r2d2_torso_bwd_dgrad_u8(const uint8_t* slab, int B, int S, int s0, int nt, const float* a1,
+                            const float* a2, const float* feat, float* dfeat, const float* w2,
+                            const float* w3, float* db1, float* db2, float* db3, void* scratch,
+                            void* stream);
+int r2d2_tc_torso_wgrad_u8(const uint8_t* slab, int B, int S, int s0, int nt, const float* a1,
+                           const float* a2, const float* dz1, const float* dz2, const float* dz3,
+                           float* dw1, float* dw2, float* dw3, void* scratch, void* stream);
+int r2d2_reduce_partials(const float* part, float* out, int64_t n, int splits, void* stream);
 /* Error-compensated variant ("bf16x3"): x = x_hi + x_lo, w = w_hi + w_lo (r2d2_split_bf16) and
  * y = x_hi.w_hi^T + x_hi.w_lo^T + x_lo.w_hi^T, fp32 accumulation in TMEM -- operand error 2^-16
  * instead of 2^-9.  Used for FORWARD contractions: a 1e-3 forward perturbation flips ReLU masks

@@ -556,7 +556,7 @@ template <class T>
 static int torso_bwd_impl(const T* frames, FrameMap fm, int R, const float* a1, const float* a2,
                           const float* feat, float* dfeat, const float* w2, const float* w3,
                           float* dw1, float* db1, float* dw2, float* db2, float* dw3, float* db3,
-                          void* scratch, cudaStream_t st) {
+                          void* scratch, cudaStream_t st, bool skip_wgrad = false) {
     R2D2_REQUIRE((int64_t)R * 400 < (1ll << 31), "torso_bwd: too many frames");
     float* dz2 = (float*)scratch;                   // [R,32,9,9]
     float* dz1 = dz2 + (int64_t)R * 2592;           // [R,32,20,20]
@@ -570,7 +570,7 @@ static int torso_bwd_impl(const T* frames, FrameMap fm, int R, const float* a1, 
     {
         GradRowsT<32, 7> al{dfeat};
         ConvPatchCols<float, 32, 3, 9, 7, 1> bl{a2, FrameMap{0, 0, 0, 2592}};
-        int rc = conv_wgrad("conv3_wgrad", al, bl, 288, R * 49, dw3, part, st);
+        int rc = skip_wgrad ? 0 : conv_wgrad("conv3_wgrad", al, bl, 288, R * 49, dw3, part, st);
         if (rc) return rc;
         R2D2_LAUNCH("chansum_partial_kernel", st, chansum_partial_kernel<<<dim3(32, CS_SPLITS), 256, 0, st>>>(dfeat, part, R, 32, 49));
         R2D2_LAUNCH("chansum_final_kernel", st, chansum_final_kernel<<<1, 32, 0, st>>>(part, db3, 32));
@@ -584,7 +584,7 @@ static int torso_bwd_impl(const T* frames, FrameMap fm, int R, const float* a1, 
     {   // layer 2
         GradRowsT<32, 9> al{dz2};
         ConvPatchCols<float, 32, 4, 20, 9, 2> bl{a1, FrameMap{0, 0, 0, 12800}};
-        int rc = conv_wgrad("conv2_wgrad", al, bl, 512, R * 81, dw2, part, st);
+        int rc = skip_wgrad ? 0 : conv_wgrad("conv2_wgrad", al, bl, 512, R * 81, dw2, part, st);
         if (rc) return rc;
         R2D2_LAUNCH("chansum_partial_kernel", st, chansum_partial_kernel<<<dim3(32, CS_SPLITS), 256, 0, st>>>(dz2, part, R, 32, 81));
         R2D2_LAUNCH("chansum_final_kernel", st, chansum_final_kernel<<<1, 32, 0, st>>>(part, db2, 32));
@@ -598,7 +598,7 @@ static int torso_bwd_impl(const T* frames, FrameMap fm, int R, const float* a1, 
     {   // layer 1 (no data gradient: frames are inputs)
         GradRowsT<32, 20> al{dz1};
         ConvPatchCols<T, 4, 8, 84, 20, 4> bl{frames, fm};
-        int rc = conv_wgrad("conv1_wgrad", al, bl, 256, R * 400, dw1, part, st);
+        int rc = skip_wgrad ? 0 : conv_wgrad("conv1_wgrad", al, bl, 256, R * 400, dw1, part, st);
         if (rc) return rc;
         R2D2_LAUNCH("chansum_partial_kernel", st, chansum_partial_kernel<<<dim3(32, CS_SPLITS), 256, 0, st>>>(dz1, part, R, 32, 400));
         R2D2_LAUNCH("chansum_final_kernel", st, chansum_final_kernel<<<1, 32, 0, st>>>(part, db1, 32));
@@ -728,6 +728,13 @@ int r2d2_head_fwd(const float* hs, const float* w1, const float* b1, const float
     int rc = r2d2_linear_fwd(hs, w1, b1, nullptr, hid, M, 2 * H, H, 1, stream);
     if (rc) return rc;
     R2D2_LAUNCH("head_out_kernel", as_stream(stream), head_out_kernel<<<(M + 7) / 8, 256, 0, as_stream(stream)>>>(hid, w2, b2, q, M, H));
+    return R2D2_OK;
+}
+
+int r2d2_reduce_partials(const float* part, float* out, int64_t n, int splits, void* stream) {
+    R2D2_REQUIRE(part && out && n > 0 && splits > 0, "reduce_partials: bad args");
+    R2D2_LAUNCH("reduce_partials_kernel", as_stream(stream),
+                reduce_partials_kernel<<<(unsigned)((n + 255) / 256), 256, 0, as_stream(stream)>>>(part, out, n, splits));
     return R2D2_OK;
 }
 
@@ -862,6 +869,20 @@ int r2d2_torso_bwd_u8(const uint8_t* slab, int B, int S, int s0, int nt, const f
     return torso_bwd_impl<uint8_t>(slab, FrameMap{B, S, s0, R2D2_FRAME_BYTES}, B * nt, a1, a2, feat,
                                    dfeat, w2, w3, dw1, db1, dw2, db2, dw3, db3, scratch,
                                    as_stream(stream));
+}
+
+// data gradients + bias gradients only (dz2/dz1 left in scratch for the tensor-core weight
+// gradients, r2d2_tc_torso_wgrad_u8): scratch layout [dz2 | dz1 | partials] as r2d2_torso_bwd_u8
+int r2d2_torso_bwd_dgrad_u8(const uint8_t* slab, int B, int S, int s0, int nt, const float* a1,
+                            const float* a2, const float* feat, float* dfeat, const float* w2,
+                            const float* w3, float* db1, float* db2, float* db3, void* scratch,
+                            void* stream) {
+    R2D2_REQUIRE(slab && a1 && a2 && feat && dfeat && w2 && w3 && db1 && db2 && db3 && scratch,
+                 "torso_bwd_dgrad: null pointer");
+    R2D2_REQUIRE(B > 0 && nt > 0 && s0 >= 0 && s0 + nt <= S, "torso_bwd_dgrad: bad frame window");
+    return torso_bwd_impl<uint8_t>(slab, FrameMap{B, S, s0, R2D2_FRAME_BYTES}, B * nt, a1, a2, feat,
+                                   dfeat, w2, w3, nullptr, db1, nullptr, db2, nullptr, db3, scratch,
+                                   as_stream(stream), true);
 }
 
 int r2d2_torso_bwd_f32(const float* frames, int R, const float* a1, const float* a2,

@@ -264,6 +264,199 @@ static int launch_tc_conv(const char* name, const T* in, FrameMap fm, const floa
     return R2D2_OK;
 }
 
+// ------------------------------------------------------------------------------------------
+// Conv weight gradient on tensor cores (plain bf16; backward contractions need no compensation):
+//   dW[co, k] = sum_{pixels} dZ[pix, co] * patch[pix, k]
+// computed as D[k (M), co (N=32)] = sum_pix A[k, pix] * B[co, pix].  The A tile is the SAME
+// shared-memory image the forward producer builds (64 pixel rows x 128-byte rows of 64 patch
+// elements, 128B-swizzled) -- consumed here as an MN-major operand (M = patch element, K = pixel);
+// B is a K-major [32 co x 64 pixels] tile of dZ.  Each persistent CTA owns a contiguous range of
+// 64-pixel blocks, accumulates its partial dW in TMEM (KP/128 accumulators of 32 columns) and
+// writes it out once; the partials are then summed in fixed order (reduce_partials_kernel).
+__host__ __device__ constexpr uint32_t umma_idesc_bf16_amn(int M, int N) {
+    return umma_idesc_bf16(M, N) | (1u << 15);               // A operand MN-major
+}
+// MN-major SWIZZLE_128B operand: 64-element (128 B) MN groups `lbo` bytes apart, 8-row K groups
+// 1024 bytes apart
+__device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t smem_addr, uint32_t lbo_bytes) {
+    return (uint64_t)((smem_addr & 0x3FFFF) >> 4) | ((uint64_t)(lbo_bytes >> 4) << 16) |
+           (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+
+template <class T, int CIN, int KH, int HIN, int SUB>
+__device__ __forceinline__ void wgrad_gather(const T* __restrict__ src, const bool valid, const int prow,
+                                             uint8_t* __restrict__ a_stage) {
+    constexpr int K = CIN * KH * KH, NKB = (K + 63) / 64;
+    // half-k-blocks SUB, SUB+4, ... of this pixel's patch row (compile-time indices)
+#pragma unroll
+    for (int hk = SUB; hk < 2 * NKB; hk += 4) {
+        constexpr int HALF = SUB & 1;
+        const int kb = hk >> 1;
+        float v[4][8];
+        gather_chunks<T, CIN, KH, HIN, HALF>(src, kb, valid, v);
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc)
+            *reinterpret_cast<uint4*>(a_stage + kb * 8192 + sw128_off(prow, HALF * 4 + cc)) =
+                make_uint4(pack_bf16x2(v[cc][0], v[cc][1]), pack_bf16x2(v[cc][2], v[cc][3]),
+                           pack_bf16x2(v[cc][4], v[cc][5]), pack_bf16x2(v[cc][6], v[cc][7]));
+    }
+}
+
+template <class T, int CIN, int KH, int HIN, int HOUT, int STRIDE, int STAGES>
+__global__ void __launch_bounds__(416, 1)
+tc_conv_wgrad_kernel(const T* __restrict__ in, const FrameMap fm, const float* __restrict__ dz,
+                     float* __restrict__ part, const int R, const float in_scale) {
+    constexpr int K = CIN * KH * KH, NKB = (K + 63) / 64;
+    constexpr int MT = (NKB + 1) / 2, KPM = MT * 128;           // M tiles of 128 patch elements
+    constexpr int P = HOUT * HOUT, COUT = 32;
+    constexpr uint32_t A_STAGE = 2 * MT * 8192, B_TILE = COUT * 128, STAGE_BYTES = A_STAGE + B_TILE;
+    constexpr int MMA_WARP = 8;
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], acc_full;
+    __shared__ uint32_t tmem_slot;
+    const uint32_t raw = smem_u32(smem_raw);
+    uint8_t* base = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const long long Mtot = (long long)R * P;
+    const int nblk = (int)((Mtot + 63) / 64);
+    const int per = (nblk + gridDim.x - 1) / gridDim.x;
+    const int blk_lo = min(nblk, (int)blockIdx.x * per), blk_hi = min(nblk, blk_lo + per);
+
+    if (tid == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full_bar[s], 256);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(&acc_full, 1);
+        mbar_fence_init();
+    }
+    if (NKB < 2 * MT) {   // odd number of 64-wide groups: the padding group must hold finite values
+        for (int i = tid; i < STAGES * 8192 / 16; i += blockDim.x) {
+            const int s = i / (8192 / 16), o = i - s * (8192 / 16);
+            *reinterpret_cast<uint4*>(base + (size_t)s * STAGE_BYTES + (2 * MT - 1) * 8192 + o * 16) =
+                make_uint4(0u, 0u, 0u, 0u);
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (warp == MMA_WARP) tmem_alloc(&tmem_slot, 128);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+
+    if (warp < MMA_WARP) {
+        // ================= producers: A: pixel = tid & 63, quarter = tid >> 6; B: (co, chunk) = tid
+        const int prow = tid & 63, sub = tid >> 6;
+        const int bco = tid >> 3, bch = tid & 7;
+        uint32_t it = 0;
+        for (int blk = blk_lo; blk < blk_hi; ++blk, ++it) {
+            const int s = it % STAGES;
+            mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
+            uint8_t* a_stage = base + (size_t)s * STAGE_BYTES;
+            // ---- A: this pixel's patch row
+            const long long m = (long long)blk * 64 + prow;
+            const bool valid = m < Mtot;
+            const T* src = in;
+            if (valid) {
+                const int r = (int)(m / P), p = (int)(m - (long long)r * P);
+                const int oy = p / HOUT, ox = p - oy * HOUT;
+                src = in + fm.base(r) + (long long)(oy * STRIDE) * HIN + ox * STRIDE;
+            }
+            switch (sub) {
+                case 0: wgrad_gather<T, CIN, KH, HIN, 0>(src, valid, prow, a_stage); break;
+                case 1: wgrad_gather<T, CIN, KH, HIN, 1>(src, valid, prow, a_stage); break;
+                case 2: wgrad_gather<T, CIN, KH, HIN, 2>(src, valid, prow, a_stage); break;
+                default: wgrad_gather<T, CIN, KH, HIN, 3>(src, valid, prow, a_stage); break;
+            }
+            // ---- B: dZ[., co, 8 consecutive pixels]
+            {
+                float v[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    const long long mm = (long long)blk * 64 + bch * 8 + e;
+                    float x = 0.f;
+                    if (mm < Mtot) {
+                        const int r = (int)(mm / P), p = (int)(mm - (long long)r * P);
+                        x = __ldg(dz + ((long long)r * COUT + bco) * P + p);
+                    }
+                    v[e] = x;
+                }
+                *reinterpret_cast<uint4*>(a_stage + A_STAGE + sw128_off(bco, bch)) =
+                    make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
+                               pack_bf16x2(v[6], v[7]));
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            mbar_arrive(&full_bar[s]);
+        }
+    } else if (warp == MMA_WARP) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16_amn(128, COUT);
+            uint32_t it = 0;
+            for (int blk = blk_lo; blk < blk_hi; ++blk, ++it) {
+                const int s = it % STAGES;
+                mbar_wait(&full_bar[s], (it / STAGES) & 1);
+                tc_fence_after();
+                const uint32_t a0 = smem_u32(base + (size_t)s * STAGE_BYTES), b0 = a0 + A_STAGE;
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks)                      // 16 pixels per MMA
+#pragma unroll
+                    for (int mt = 0; mt < MT; ++mt)
+                        umma_f16(tmem_base + mt * COUT,
+                                 umma_desc_mn_sw128(a0 + mt * 16384 + ks * 2048, 8192),
+                                 umma_desc_k_sw128(b0 + ks * 32), idesc, (it | ks) != 0);
+                umma_commit(&empty_bar[s]);
+            }
+            umma_commit(&acc_full);
+        }
+    } else {
+        // ================= epilogue (once): lane = patch element, 32 columns = co
+        const int q = warp & 3;
+        if (blk_hi > blk_lo) {
+            mbar_wait(&acc_full, 0);
+            tc_fence_after();
+        }
+        float* out = part + (long long)blockIdx.x * COUT * K;
+#pragma unroll 1
+        for (int mt = 0; mt < MT; ++mt) {
+            uint32_t r[32];
+            if (blk_hi > blk_lo) {
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + mt * COUT, r);
+                tmem_ld_wait();
+            } else {
+#pragma unroll
+                for (int co = 0; co < COUT; ++co) r[co] = 0u;
+            }
+            const int k = mt * 128 + q * 32 + lane;
+            if (k < K) {
+#pragma unroll
+                for (int co = 0; co < COUT; ++co)
+                    out[(long long)co * K + k] = __uint_as_float(r[co]) * in_scale;
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == MMA_WARP) tmem_dealloc(tmem_base, 128);
+    (void)KPM;
+}
+
+template <class T, int CIN, int KH, int HIN, int HOUT, int STRIDE, int STAGES>
+static int launch_tc_wgrad(const char* name, const T* in, FrameMap fm, const float* dz, float* part,
+                           int R, float in_scale, int* grid_out, cudaStream_t st) {
+    constexpr int K = CIN * KH * KH, NKB = (K + 63) / 64, MT = (NKB + 1) / 2;
+    const int smem = STAGES * (2 * MT * 8192 + 32 * 128) + 1024;
+    auto kern = tc_conv_wgrad_kernel<T, CIN, KH, HIN, HOUT, STRIDE, STAGES>;
+    R2D2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    const long long Mtot = (long long)R * HOUT * HOUT;
+    const int nblk = (int)((Mtot + 63) / 64);
+    int grid = sm_count();
+    if (grid > nblk) grid = nblk;
+    *grid_out = grid;
+    R2D2_LAUNCH(name, st, kern<<<grid, 416, smem, st>>>(in, fm, dz, part, R, in_scale));
+    return R2D2_OK;
+}
+
 template <class T>
 static int tc_torso_fwd_impl(const T* frames, FrameMap fm, int R, const float* w1, const float* b1,
                              const float* w2, const float* b2, const float* w3, const float* b3,
@@ -292,6 +485,38 @@ int r2d2_tc_torso_fwd_u8(const uint8_t* slab, int B, int S, int s0, int nt, cons
     R2D2_REQUIRE(B > 0 && nt > 0 && s0 >= 0 && s0 + nt <= S, "tc_torso_fwd: bad frame window");
     return tc_torso_fwd_impl<uint8_t>(slab, FrameMap{B, S, s0, R2D2_FRAME_BYTES}, B * nt, w1, b1, w2, b2,
                                       w3, b3, a1, a2, feat, as_stream(stream));
+}
+
+// partial-sum reduction shared with the fp32 path (nn_kernels.cu)
+int r2d2_reduce_partials(const float* part, float* out, int64_t n, int splits, void* stream);
+
+// weight gradients of the three conv layers on tensor cores; dz1/dz2/dz3 are the NCHW
+// pre-activation gradients produced by the data-gradient kernels (dz3 = masked dfeat)
+int r2d2_tc_torso_wgrad_u8(const uint8_t* slab, int B, int S, int s0, int nt, const float* a1,
+                           const float* a2, const float* dz1, const float* dz2, const float* dz3,
+                           float* dw1, float* dw2, float* dw3, void* scratch, void* stream) {
+    R2D2_REQUIRE(slab && a1 && a2 && dz1 && dz2 && dz3 && dw1 && dw2 && dw3 && scratch,
+                 "tc_torso_wgrad: null pointer");
+    R2D2_REQUIRE(B > 0 && nt > 0 && s0 >= 0 && s0 + nt <= S, "tc_torso_wgrad: bad frame window");
+    cudaStream_t st = as_stream(stream);
+    const int R = B * nt;
+    float* part = static_cast<float*>(scratch);
+    int grid = 0;
+    int rc = launch_tc_wgrad<float, 32, 3, 9, 7, 1, 3>("tc_conv3_wgrad", a2, FrameMap{0, 0, 0, 2592}, dz3,
+                                                       part, R, 1.f, &grid, st);
+    if (rc) return rc;
+    rc = r2d2_reduce_partials(part, dw3, 32 * 288, grid, stream);
+    if (rc) return rc;
+    rc = launch_tc_wgrad<float, 32, 4, 20, 9, 2, 3>("tc_conv2_wgrad", a1, FrameMap{0, 0, 0, 12800}, dz2,
+                                                    part, R, 1.f, &grid, st);
+    if (rc) return rc;
+    rc = r2d2_reduce_partials(part, dw2, 32 * 512, grid, stream);
+    if (rc) return rc;
+    rc = launch_tc_wgrad<uint8_t, 4, 8, 84, 20, 4, 4>("tc_conv1_wgrad", slab,
+                                                      FrameMap{B, S, s0, R2D2_FRAME_BYTES}, dz1, part, R,
+                                                      1.f / 255.f, &grid, st);
+    if (rc) return rc;
+    return r2d2_reduce_partials(part, dw1, 32 * 256, grid, stream);
 }
 
 int r2d2_tc_torso_fwd_f32(const float* frames, int R, const float* w1, const float* b1,

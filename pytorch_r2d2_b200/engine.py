@@ -127,6 +127,19 @@ def torso_bwd_u8(slab, s0, nt, a1, a2, feat, dfeat, w: Weights, g: Weights, scra
               P(g.w3), P(g.b3), P(scratch), S())
 
 
+def torso_bwd_tc_u8(slab, s0, nt, a1, a2, feat, dfeat, w: Weights, g: Weights, scratch):
+    """Tensor-core variant: fp32 data/bias gradients, then the weight gradients on tcgen05."""
+    B, Sfr = slab.shape[0], slab.shape[1]
+    R = B * nt
+    _lib.call("r2d2_torso_bwd_dgrad_u8", P(slab, "u8"), B, Sfr, s0, nt, P(a1, "f32"), P(a2, "f32"),
+              P(feat, "f32"), P(dfeat, "f32"), P(w.w2), P(w.w3), P(g.b1), P(g.b2), P(g.b3), P(scratch), S())
+    sc = scratch.view(torch.float32)
+    dz2, dz1 = sc[:R * 2592], sc[R * 2592: R * (2592 + 12800)]
+    part = sc[R * (2592 + 12800):]
+    _lib.call("r2d2_tc_torso_wgrad_u8", P(slab, "u8"), B, Sfr, s0, nt, P(a1, "f32"), P(a2, "f32"),
+              P(dz1, "f32"), P(dz2, "f32"), P(dfeat, "f32"), P(g.w1), P(g.w2), P(g.w3), P(part, "f32"), S())
+
+
 def torso_bwd_f32(frames, a1, a2, feat, dfeat, w: Weights, g: Weights, scratch):
     R = frames.shape[0]
     _lib.call("r2d2_torso_bwd_f32", P(frames, "f32"), R, P(a1, "f32"), P(a2, "f32"), P(feat, "f32"),

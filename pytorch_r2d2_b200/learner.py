@@ -333,8 +333,9 @@ class Learner:
             g.b_ih.copy_(g.b_hh)
             engine.linear_wgrad(ws["dgates"], feat_l, g.w_ih, None, scratch)
             engine.linear_dgrad(ws["dgates"], w.w_ih, ws["dfeat"])
-        engine.torso_bwd_u8(slab, BI, L, ws["a1_on"][BI * B: T * B], ws["a2_on"][BI * B: T * B], feat_l,
-                            ws["dfeat"], w, g, scratch)
+        (engine.torso_bwd_tc_u8 if bf16 else engine.torso_bwd_u8)(
+            slab, BI, L, ws["a1_on"][BI * B: T * B], ws["a2_on"][BI * B: T * B], feat_l, ws["dfeat"], w, g,
+            scratch)
 
         # ---- optimiser (data-parallel: sum gradients over ranks, 1/world folded into K10)
         self.optim.grad_scale = parallel.allreduce_flat_grad(self.optim.grad, self.process_group)

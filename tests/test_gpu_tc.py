@@ -161,3 +161,33 @@ def test_tc_lstm_bwd_vs_autograd(cuda_device, H, B, T):
     err = rel_err(dgates, xproj.grad)
     assert err < 1e-2, err
     assert rel_err(dgates[-1], xproj.grad[-1]) < 1e-5        # last step has no recurrent term
+
+
+def test_tc_conv_wgrad_vs_fp32(cuda_device):
+    """Tensor-core conv weight gradients (plain bf16) vs the fp32 kernels on the same inputs:
+    1e-2 relative to max|dW| (bf16 operand rounding), bias/data gradients identical."""
+    import numpy as np
+    from pytorch_r2d2_b200 import QNet, engine
+    torch.manual_seed(4)
+    net = QNet("cuda:0", 256)
+    w = net._weights()
+    rng = np.random.RandomState(8)
+    B, S, s0, nt = 5, 7, 2, 4
+    slab = torch.from_numpy(rng.randint(0, 256, (B, S, 4, 84, 84)).astype(np.uint8)).cuda()
+    R = B * nt
+    a1, a2, feat = engine.alloc_torso(R, "cuda")
+    engine.torso_fwd_u8(slab, s0, nt, w, a1, a2, feat)
+    dfeat = torch.randn(R, 1568, generator=torch.Generator().manual_seed(1)).cuda()
+    outs = []
+    for fn in (engine.torso_bwd_u8, engine.torso_bwd_tc_u8):
+        gflat = torch.full_like(net.flat_parameters(), float("nan"))
+        gw = engine.Weights(gflat, net.layout)
+        scratch = torch.empty(engine.torso_bwd_scratch_bytes(R), dtype=torch.uint8, device="cuda")
+        fn(slab, s0, nt, a1, a2, feat, dfeat.clone(), w, gw, scratch)
+        outs.append(gw)
+    ref, tc = outs
+    for name in ("w1", "w2", "w3"):
+        err = rel_err(getattr(tc, name), getattr(ref, name))
+        assert err < 1e-2, (name, err)
+    for name in ("b1", "b2", "b3"):
+        assert torch.equal(getattr(tc, name), getattr(ref, name)), name
