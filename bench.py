@@ -266,6 +266,9 @@ def run_ours(args):
         raise RuntimeError("bench.py needs a CUDA device: the product path has no CPU fallback")
     torch.cuda.set_device(local)
     if world > 1:
+        # keep stdout to the single JSON line (NCCL_DEBUG=VERSION/INFO would print there)
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "INFO", "TRACE"):
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
     _lib.load()
     B, BI, Ln, n, H = args.batch, args.burn_in, args.learn, args.n_step, args.cell
