@@ -195,7 +195,7 @@ def run_reference(args):
                                    f"torch CPU fp32 with {cores} threads, 20000-slot replay"},
         "e2e": {"value": val, "unit": "seq/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_config(args, extra=None):
@@ -415,17 +415,43 @@ def run_ours(args):
     }
     if cpu:
         line["cpu_baseline"] = cpu
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+class _StdoutToStderr:
+    """Route everything written to fd 1 (NCCL banners, library chatter) to stderr while the
+    benchmark runs, so that stdout carries exactly ONE line: the JSON result."""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        os.dup2(2, 1)
+        return self
+
+    def __exit__(self, *exc):
+        sys.stdout.flush()
+        os.dup2(self.saved, 1)
+        os.close(self.saved)
+
+
+_RESULT = []
+
+
+def emit(line: dict):
+    _RESULT.append(json.dumps(line))
+
+
 def main():
     args = parse()
-    if args.impl == "reference":
-        run_reference(args)
-    else:
-        run_ours(args)
+    with _StdoutToStderr():
+        if args.impl == "reference":
+            run_reference(args)
+        else:
+            run_ours(args)
+    for r in _RESULT:
+        print(r, flush=True)
 
 
 if __name__ == "__main__":
