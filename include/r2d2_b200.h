@@ -245,6 +245,16 @@ int r2d2_tc_torso_wgrad_u8(const uint8_t* slab, int B, int S, int s0, int nt, co
                            const float* a2, const float* dz1, const float* dz2, const float* dz3,
                            float* dw1, float* dw2, float* dw3, void* scratch, void* stream);
 int r2d2_reduce_partials(const float* part, float* out, int64_t n, int splits, void* stream);
+/* conv data gradients on tcgen05 (plain bf16, ReLU' of the layer input fused): dz3 [R,32,7,7]
+ * -> dz2 [R,32,9,9] (a2 = that layer's activations), dz2 -> dz1 [R,32,20,20]; the stride-2 layer
+ * runs as four output-parity classes.  Plus the two small pieces of the conv backward that stay
+ * elementwise: d[i] = a[i] > 0 ? d[i] : 0, and per-channel sums (part: >= 37*32 floats). */
+int r2d2_tc_conv_dgrad3(const float* dz3, const float* w3, const float* a2, float* dz2, int R,
+                        void* stream);
+int r2d2_tc_conv_dgrad2(const float* dz2, const float* w2, const float* a1, float* dz1, int R,
+                        void* stream);
+int r2d2_relu_mask(float* d, const float* a, int64_t n, void* stream);
+int r2d2_chansum(const float* dz, float* db, int R, int PIX, float* part, void* stream);
 /* Error-compensated variant ("bf16x3"): x = x_hi + x_lo, w = w_hi + w_lo (r2d2_split_bf16) and
  * y = x_hi.w_hi^T + x_hi.w_lo^T + x_lo.w_hi^T, fp32 accumulation in TMEM -- operand error 2^-16
  * instead of 2^-9.  Used for FORWARD contractions: a 1e-3 forward perturbation flips ReLU masks

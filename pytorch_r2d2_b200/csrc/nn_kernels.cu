@@ -871,6 +871,23 @@ int r2d2_torso_bwd_u8(const uint8_t* slab, int B, int S, int s0, int nt, const f
                                    as_stream(stream));
 }
 
+// pieces of the conv backward the tensor-core path still takes from this file
+int r2d2_relu_mask(float* d, const float* a, int64_t n, void* stream) {
+    R2D2_REQUIRE(d && a && n > 0, "relu_mask: bad args");
+    int64_t blocks = (n + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    R2D2_LAUNCH("relu_mask_kernel", as_stream(stream), relu_mask_kernel<<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(d, a, n));
+    return R2D2_OK;
+}
+// db[c] = sum over frames and pixels of dz[R, C=32, PIX]; part: CS_SPLITS*32 floats of scratch
+int r2d2_chansum(const float* dz, float* db, int R, int PIX, float* part, void* stream) {
+    R2D2_REQUIRE(dz && db && part && R > 0 && PIX > 0, "chansum: bad args");
+    cudaStream_t st = as_stream(stream);
+    R2D2_LAUNCH("chansum_partial_kernel", st, chansum_partial_kernel<<<dim3(32, CS_SPLITS), 256, 0, st>>>(dz, part, R, 32, PIX));
+    R2D2_LAUNCH("chansum_final_kernel", st, chansum_final_kernel<<<1, 32, 0, st>>>(part, db, 32));
+    return R2D2_OK;
+}
+
 // data gradients + bias gradients only (dz2/dz1 left in scratch for the tensor-core weight
 // gradients, r2d2_tc_torso_wgrad_u8): scratch layout [dz2 | dz1 | partials] as r2d2_torso_bwd_u8
 int r2d2_torso_bwd_dgrad_u8(const uint8_t* slab, int B, int S, int s0, int nt, const float* a1,

@@ -457,6 +457,191 @@ static int launch_tc_wgrad(const char* name, const T* in, FrameMap fm, const flo
     return R2D2_OK;
 }
 
+// ------------------------------------------------------------------------------------------
+// Conv data gradient on tensor cores (plain bf16), ReLU' of the layer input fused:
+//   dIn[r,ci,y,x] = relu'(act[r,ci,y,x]) * sum_{co,ky,kx} dZ[r,co,(y-ky)/S,(x-kx)/S] W[co,ci,ky,kx]
+// Output pixels are split by parity class (PY,PX) = (y%S, x%S): within a class only the taps
+// ky = PY + S*jy, kx = PX + S*jx contribute, so each class is a dense implicit GEMM with
+// M = (frame, yy, xx), N = 32 input channels, K = 32 * (KH/S)^2 -- no zero-insertion.
+// Same pipeline as the forward kernel (producer warps -> swizzled smem -> UMMA -> TMEM x2).
+template <int KH, int HIN, int HOUT, int STRIDE, int PY, int PX>
+__global__ void __launch_bounds__(416, 1)
+tc_conv_dgrad_kernel(const float* __restrict__ dz, const float* __restrict__ w,
+                     const float* __restrict__ act, float* __restrict__ din, const int R) {
+    constexpr int TAPS = KH / STRIDE, C = 32;
+    constexpr int K = C * TAPS * TAPS, NKB = (K + 63) / 64, KP = NKB * 64;
+    constexpr int GY = (HIN - PY + STRIDE - 1) / STRIDE, GX = (HIN - PX + STRIDE - 1) / STRIDE;
+    constexpr int P = GY * GX;                                   // output pixels of this class per frame
+    constexpr uint32_t A_TILE = 128 * 128, W_KB = C * 128;
+    constexpr int MMA_WARP = 8;
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t full_bar[CV_STAGES], empty_bar[CV_STAGES], acc_full[2], acc_empty[2];
+    __shared__ uint32_t tmem_slot;
+    const uint32_t raw = smem_u32(smem_raw);
+    uint8_t* base = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
+    uint8_t* w_s = base;                                         // [NKB][32 x 128 B]
+    uint8_t* a_s = base + NKB * W_KB;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const long long Mtot = (long long)R * P;
+    const int ntiles = (int)((Mtot + 127) / 128);
+
+    if (tid == 0) {
+        for (int s = 0; s < CV_STAGES; ++s) {
+            mbar_init(&full_bar[s], 256);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&acc_full[b], 1);
+            mbar_init(&acc_empty[b], 128);
+        }
+        mbar_fence_init();
+    }
+    // resident B: row = ci, k = (co, jy, jx) -> W[co, ci, PY + S*jy, PX + S*jx]
+    for (int i = tid; i < C * (KP / 8); i += blockDim.x) {
+        const int ci = i / (KP / 8), ch = i - ci * (KP / 8);
+        float v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const int k = ch * 8 + e;
+            float x = 0.f;
+            if (k < K) {
+                const int co = k / (TAPS * TAPS), rem = k - co * (TAPS * TAPS);
+                const int jy = rem / TAPS, jx = rem - jy * TAPS;
+                x = __ldg(w + ((long long)(co * C + ci) * KH + PY + STRIDE * jy) * KH + PX + STRIDE * jx);
+            }
+            v[e] = x;
+        }
+        *reinterpret_cast<uint4*>(w_s + (uint32_t)(ch >> 3) * W_KB + sw128_off(ci, ch & 7)) =
+            make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
+                       pack_bf16x2(v[6], v[7]));
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    if (warp == MMA_WARP) tmem_alloc(&tmem_slot, 64);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+
+    if (warp < MMA_WARP) {
+        const int row = tid & 127, half = tid >> 7;
+        uint32_t it = 0;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+            const long long m = (long long)tile * 128 + row;
+            const bool valid = m < Mtot;
+            int yy = 0, xx = 0;
+            const float* src = dz;
+            if (valid) {
+                const int r = (int)(m / P), p = (int)(m - (long long)r * P);
+                yy = p / GX;
+                xx = p - yy * GX;
+                src = dz + (long long)r * C * HOUT * HOUT;
+            }
+#pragma unroll
+            for (int kb = 0; kb < NKB; ++kb, ++it) {
+                const int s = it % CV_STAGES;
+                mbar_wait(&empty_bar[s], ((it / CV_STAGES) & 1) ^ 1);
+                uint8_t* a_t = a_s + (size_t)s * A_TILE;
+                float v[4][8];
+#pragma unroll
+                for (int cc = 0; cc < 4; ++cc)
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) {
+                        // `half` only shifts k by 32: keep the decode compile-time per branch
+                        const int kbase = kb * 64 + cc * 8 + e;
+                        float x = 0.f;
+#pragma unroll
+                        for (int hsel = 0; hsel < 2; ++hsel) {
+                            if (half == hsel) {
+                                const int k = kbase + hsel * 32;
+                                const int co = k / (TAPS * TAPS), rem = k - co * (TAPS * TAPS);
+                                const int jy = rem / TAPS, jx = rem - jy * TAPS;
+                                const int oy = yy - jy, ox = xx - jx;
+                                if (k < K && valid && oy >= 0 && oy < HOUT && ox >= 0 && ox < HOUT)
+                                    x = __ldg(src + (co * HOUT + oy) * HOUT + ox);
+                            }
+                        }
+                        v[cc][e] = x;
+                    }
+#pragma unroll
+                for (int cc = 0; cc < 4; ++cc)
+                    *reinterpret_cast<uint4*>(a_t + sw128_off(row, half * 4 + cc)) =
+                        make_uint4(pack_bf16x2(v[cc][0], v[cc][1]), pack_bf16x2(v[cc][2], v[cc][3]),
+                                   pack_bf16x2(v[cc][4], v[cc][5]), pack_bf16x2(v[cc][6], v[cc][7]));
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                mbar_arrive(&full_bar[s]);
+            }
+        }
+    } else if (warp == MMA_WARP) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(128, C);
+            const uint32_t wb = smem_u32(w_s);
+            uint32_t it = 0, tcount = 0;
+            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++tcount) {
+                const uint32_t buf = tcount & 1, use = tcount >> 1;
+                mbar_wait(&acc_empty[buf], (use & 1) ^ 1);
+                tc_fence_after();
+                const uint32_t d = tmem_base + buf * C;
+                for (int kb = 0; kb < NKB; ++kb, ++it) {
+                    const int s = it % CV_STAGES;
+                    mbar_wait(&full_bar[s], (it / CV_STAGES) & 1);
+                    tc_fence_after();
+                    const uint32_t aa = smem_u32(a_s + (size_t)s * A_TILE), bb = wb + kb * W_KB;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        umma_f16(d, umma_desc_k_sw128(aa + k * 32), umma_desc_k_sw128(bb + k * 32), idesc,
+                                 (kb | k) != 0);
+                    umma_commit(&empty_bar[s]);
+                }
+                umma_commit(&acc_full[buf]);
+            }
+        }
+    } else {
+        const int q = warp & 3;
+        uint32_t tcount = 0;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++tcount) {
+            const uint32_t buf = tcount & 1, use = tcount >> 1;
+            mbar_wait(&acc_full[buf], use & 1);
+            tc_fence_after();
+            uint32_t r[32];
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + buf * C, r);
+            tmem_ld_wait();
+            tc_fence_before();
+            mbar_arrive(&acc_empty[buf]);
+            const long long m = (long long)tile * 128 + q * 32 + lane;
+            if (m < Mtot) {
+                const int fr = (int)(m / P), p = (int)(m - (long long)fr * P);
+                const int yy = p / GX, xx = p - yy * GX;
+                const long long o = (long long)fr * C * HIN * HIN + (STRIDE * yy + PY) * HIN + STRIDE * xx + PX;
+#pragma unroll
+                for (int ci = 0; ci < C; ++ci) {
+                    const long long oo = o + (long long)ci * HIN * HIN;
+                    din[oo] = act[oo] > 0.f ? __uint_as_float(r[ci]) : 0.f;
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == MMA_WARP) tmem_dealloc(tmem_base, 64);
+}
+
+template <int KH, int HIN, int HOUT, int STRIDE, int PY, int PX>
+static int launch_tc_dgrad(const char* name, const float* dz, const float* w, const float* act,
+                           float* din, int R, cudaStream_t st) {
+    constexpr int TAPS = KH / STRIDE, K = 32 * TAPS * TAPS, NKB = (K + 63) / 64;
+    constexpr int GY = (HIN - PY + STRIDE - 1) / STRIDE, GX = (HIN - PX + STRIDE - 1) / STRIDE;
+    const int smem = NKB * 32 * 128 + CV_STAGES * 128 * 128 + 1024;
+    auto kern = tc_conv_dgrad_kernel<KH, HIN, HOUT, STRIDE, PY, PX>;
+    R2D2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    const long long Mtot = (long long)R * GY * GX;
+    const int ntiles = (int)((Mtot + 127) / 128);
+    int grid = sm_count();
+    if (grid > ntiles) grid = ntiles;
+    R2D2_LAUNCH(name, st, kern<<<grid, 416, smem, st>>>(dz, w, act, din, R));
+    return R2D2_OK;
+}
+
 template <class T>
 static int tc_torso_fwd_impl(const T* frames, FrameMap fm, int R, const float* w1, const float* b1,
                              const float* w2, const float* b2, const float* w3, const float* b3,
@@ -485,6 +670,25 @@ int r2d2_tc_torso_fwd_u8(const uint8_t* slab, int B, int S, int s0, int nt, cons
     R2D2_REQUIRE(B > 0 && nt > 0 && s0 >= 0 && s0 + nt <= S, "tc_torso_fwd: bad frame window");
     return tc_torso_fwd_impl<uint8_t>(slab, FrameMap{B, S, s0, R2D2_FRAME_BYTES}, B * nt, w1, b1, w2, b2,
                                       w3, b3, a1, a2, feat, as_stream(stream));
+}
+
+// data gradients of conv3 (into the 9x9 layer) and conv2 (into the 20x20 layer), ReLU' fused
+int r2d2_tc_conv_dgrad3(const float* dz3, const float* w3, const float* a2, float* dz2, int R,
+                        void* stream) {
+    R2D2_REQUIRE(dz3 && w3 && a2 && dz2 && R > 0, "tc_conv_dgrad3: bad args");
+    return launch_tc_dgrad<3, 9, 7, 1, 0, 0>("tc_conv3_dgrad", dz3, w3, a2, dz2, R, as_stream(stream));
+}
+int r2d2_tc_conv_dgrad2(const float* dz2, const float* w2, const float* a1, float* dz1, int R,
+                        void* stream) {
+    R2D2_REQUIRE(dz2 && w2 && a1 && dz1 && R > 0, "tc_conv_dgrad2: bad args");
+    cudaStream_t st = as_stream(stream);
+    int rc = launch_tc_dgrad<4, 20, 9, 2, 0, 0>("tc_conv2_dgrad", dz2, w2, a1, dz1, R, st);
+    if (rc) return rc;
+    rc = launch_tc_dgrad<4, 20, 9, 2, 0, 1>("tc_conv2_dgrad", dz2, w2, a1, dz1, R, st);
+    if (rc) return rc;
+    rc = launch_tc_dgrad<4, 20, 9, 2, 1, 0>("tc_conv2_dgrad", dz2, w2, a1, dz1, R, st);
+    if (rc) return rc;
+    return launch_tc_dgrad<4, 20, 9, 2, 1, 1>("tc_conv2_dgrad", dz2, w2, a1, dz1, R, st);
 }
 
 // partial-sum reduction shared with the fp32 path (nn_kernels.cu)

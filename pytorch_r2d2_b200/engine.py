@@ -128,16 +128,22 @@ def torso_bwd_u8(slab, s0, nt, a1, a2, feat, dfeat, w: Weights, g: Weights, scra
 
 
 def torso_bwd_tc_u8(slab, s0, nt, a1, a2, feat, dfeat, w: Weights, g: Weights, scratch):
-    """Tensor-core variant: fp32 data/bias gradients, then the weight gradients on tcgen05."""
+    """Tensor-core conv backward: ReLU mask, data gradients (tcgen05, ReLU' fused), bias sums,
+    then the three weight gradients (tcgen05).  scratch layout [dz2 | dz1 | partials]."""
     B, Sfr = slab.shape[0], slab.shape[1]
     R = B * nt
-    _lib.call("r2d2_torso_bwd_dgrad_u8", P(slab, "u8"), B, Sfr, s0, nt, P(a1, "f32"), P(a2, "f32"),
-              P(feat, "f32"), P(dfeat, "f32"), P(w.w2), P(w.w3), P(g.b1), P(g.b2), P(g.b3), P(scratch), S())
     sc = scratch.view(torch.float32)
     dz2, dz1 = sc[:R * 2592], sc[R * 2592: R * (2592 + 12800)]
     part = sc[R * (2592 + 12800):]
+    st = S()
+    _lib.call("r2d2_relu_mask", P(dfeat, "f32"), P(feat, "f32"), dfeat.numel(), st)
+    _lib.call("r2d2_tc_conv_dgrad3", P(dfeat, "f32"), P(w.w3), P(a2, "f32"), P(dz2, "f32"), R, st)
+    _lib.call("r2d2_tc_conv_dgrad2", P(dz2, "f32"), P(w.w2), P(a1, "f32"), P(dz1, "f32"), R, st)
+    _lib.call("r2d2_chansum", P(dfeat, "f32"), P(g.b3), R, 49, P(part, "f32"), st)
+    _lib.call("r2d2_chansum", P(dz2, "f32"), P(g.b2), R, 81, P(part, "f32"), st)
+    _lib.call("r2d2_chansum", P(dz1, "f32"), P(g.b1), R, 400, P(part, "f32"), st)
     _lib.call("r2d2_tc_torso_wgrad_u8", P(slab, "u8"), B, Sfr, s0, nt, P(a1, "f32"), P(a2, "f32"),
-              P(dz1, "f32"), P(dz2, "f32"), P(dfeat, "f32"), P(g.w1), P(g.w2), P(g.w3), P(part, "f32"), S())
+              P(dz1, "f32"), P(dz2, "f32"), P(dfeat, "f32"), P(g.w1), P(g.w2), P(g.w3), P(part, "f32"), st)
 
 
 def torso_bwd_f32(frames, a1, a2, feat, dfeat, w: Weights, g: Weights, scratch):

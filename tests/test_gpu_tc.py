@@ -163,9 +163,9 @@ def test_tc_lstm_bwd_vs_autograd(cuda_device, H, B, T):
     assert rel_err(dgates[-1], xproj.grad[-1]) < 1e-5        # last step has no recurrent term
 
 
-def test_tc_conv_wgrad_vs_fp32(cuda_device):
-    """Tensor-core conv weight gradients (plain bf16) vs the fp32 kernels on the same inputs:
-    1e-2 relative to max|dW| (bf16 operand rounding), bias/data gradients identical."""
+def test_tc_conv_backward_vs_fp32(cuda_device):
+    """Tensor-core conv backward (data + weight gradients in plain bf16) vs the fp32 kernels on
+    the same inputs: 1e-2 relative to max|grad| (bf16 operand rounding)."""
     import numpy as np
     from pytorch_r2d2_b200 import QNet, engine
     torch.manual_seed(4)
@@ -189,5 +189,5 @@ def test_tc_conv_wgrad_vs_fp32(cuda_device):
     for name in ("w1", "w2", "w3"):
         err = rel_err(getattr(tc, name), getattr(ref, name))
         assert err < 1e-2, (name, err)
-    for name in ("b1", "b2", "b3"):
-        assert torch.equal(getattr(tc, name), getattr(ref, name)), name
+    for name in ("b1", "b2", "b3"):   # data gradients now also run in bf16 on tensor cores
+        assert rel_err(getattr(tc, name), getattr(ref, name)) < 1e-2, name
