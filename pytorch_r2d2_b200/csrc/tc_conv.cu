@@ -51,10 +51,12 @@ __device__ __forceinline__ void gather_chunks(const T* __restrict__ src, const i
             // conv1 on the u8 slab: k-block = one input channel, chunk = one 8-pixel patch row
             const uint32_t* q = reinterpret_cast<const uint32_t*>(src + kb * (HIN * HIN) + c * HIN);
             const uint32_t lo4 = valid ? __ldg(q) : 0u, hi4 = valid ? __ldg(q + 1) : 0u;
+            // u8 -> float without the (quarter-rate) I2F pipe: splice the byte into the mantissa
+            // of 2^23 with one PRMT, subtract 2^23 with one FADD (exact for 0..255)
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
-                v[cc][e] = (float)((lo4 >> (8 * e)) & 0xffu);
-                v[cc][4 + e] = (float)((hi4 >> (8 * e)) & 0xffu);
+                v[cc][e] = __uint_as_float(__byte_perm(lo4, 0x4B000000u, 0x7650u | e)) - 8388608.f;
+                v[cc][4 + e] = __uint_as_float(__byte_perm(hi4, 0x4B000000u, 0x7650u | e)) - 8388608.f;
             }
         } else if constexpr (KH == 4) {
             // conv2: chunk = (ci = 4kb + c/2, ky = 2(c%2) .. +1, kx = 0..3): two rows of 4 floats

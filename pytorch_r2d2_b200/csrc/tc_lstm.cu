@@ -21,7 +21,7 @@
 
 namespace r2d2 {
 
-constexpr int LS_UNITS = 16, LS_ROWS = 64, LS_NB = 64, LS_STAGES = 4;
+constexpr int LS_UNITS = 16, LS_ROWS = 64, LS_NB = 64, LS_STAGES = 4;   // LS_NB: backward batch tile
 
 __device__ __forceinline__ uint32_t ls_pack(float a, float b) {
     __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
@@ -55,24 +55,54 @@ struct LstmArgs {
     int T, B, H;
 };
 
+template <int N> __device__ __forceinline__ void st_f32(float* p, const float* v) {
+    if constexpr (N == 4) *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+    else if constexpr (N == 2) *reinterpret_cast<float2*>(p) = make_float2(v[0], v[1]);
+    else *p = v[0];
+}
+template <int N> __device__ __forceinline__ void st_bf16_hilo(__nv_bfloat16* hi, __nv_bfloat16* lo,
+                                                              const float* v) {
+    if constexpr (N == 4) {
+        uint2 a, b;
+        a.x = ls_pack(v[0], v[1]); a.y = ls_pack(v[2], v[3]);
+        b.x = ls_pack(v[0] - ls_round(v[0]), v[1] - ls_round(v[1]));
+        b.y = ls_pack(v[2] - ls_round(v[2]), v[3] - ls_round(v[3]));
+        *reinterpret_cast<uint2*>(hi) = a;
+        *reinterpret_cast<uint2*>(lo) = b;
+    } else if constexpr (N == 2) {
+        *reinterpret_cast<uint32_t*>(hi) = ls_pack(v[0], v[1]);
+        *reinterpret_cast<uint32_t*>(lo) = ls_pack(v[0] - ls_round(v[0]), v[1] - ls_round(v[1]));
+    } else {
+        *hi = __float2bfloat16_rn(v[0]);
+        *lo = __float2bfloat16_rn(v[0] - ls_round(v[0]));
+    }
+}
+
+// NB = batch columns per CTA (UMMA N).  Batch rows never interact, so the B/NB batch groups are
+// independent chains with their own arrive counter: a smaller NB spreads one chain over more SMs
+// (less h traffic, MMA time and pointwise work per CTA per step).
+template <int NB>
 __global__ void __launch_bounds__(320, 1)
 tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_constant__ CUtensorMap tma_lo,
                    const LstmArgs a) {
+    constexpr int STAGES = 256 / NB;                            // 64 -> 4, 32 -> 8 (whole h in flight)
+    constexpr int UPT = LS_UNITS * NB / 256;                    // hidden units per pointwise thread
+    static_assert(NB == 64 || NB == 32, "batch tile must be 32 or 64");
     const int H = a.H, B = a.B, NKB = H / 64;
     extern __shared__ uint8_t smem_raw[];
-    __shared__ uint64_t full_bar[LS_STAGES], empty_bar[LS_STAGES], acc_full, acc_empty;
+    __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], acc_full, acc_empty;
     __shared__ uint32_t tmem_slot;
-    __shared__ __align__(16) float G[4][LS_UNITS][LS_NB + 4];   // raw gate pre-activations (no xproj)
+    __shared__ __align__(16) float G[4][LS_UNITS][NB + 4];      // raw gate pre-activations (no xproj)
 
     const uint32_t raw = smem_u32(smem_raw);
     uint8_t* base = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
     const uint32_t W_KB = LS_ROWS * 128;                        // 64 rows x 64 bf16
     uint8_t* w_s = base;                                        // [hi|lo][NKB][8 KB]
-    uint8_t* h_s = base + 2 * NKB * W_KB;                       // LS_STAGES x (hi 8 KB | lo 8 KB)
-    const uint32_t H_TILE = LS_NB * 128, STAGE = 2 * H_TILE;
+    uint8_t* h_s = base + 2 * NKB * W_KB;                       // STAGES x (hi | lo)
+    constexpr uint32_t H_TILE = NB * 128, STAGE = 2 * H_TILE;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int u0 = blockIdx.x * LS_UNITS, b0 = blockIdx.y * LS_NB;
+    const int u0 = blockIdx.x * LS_UNITS, b0 = blockIdx.y * NB;
     const int ncta = gridDim.x;
     int* counter = a.counter + blockIdx.y;
     const long long BH = (long long)B * H;
@@ -80,7 +110,7 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
     if (tid == 0) {
         tma_prefetch_desc(&tma_hi);
         tma_prefetch_desc(&tma_lo);
-        for (int s = 0; s < LS_STAGES; ++s) {
+        for (int s = 0; s < STAGES; ++s) {
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
         }
@@ -112,26 +142,25 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
     tc_fence_after();
     const uint32_t tmem_base = tmem_slot;
 
-    // pointwise mapping (warps 2..9): batch row b and 4 consecutive hidden units
-    const int pt = tid - 64;                    // 0..255 for pointwise threads
-    const int pb = pt & 63, pu = (pt >> 6) * 4; // local batch row, first local unit
+    // pointwise mapping (warps 2..9): batch row pb and UPT consecutive hidden units
+    const int pt = tid - 64;                      // 0..255 for pointwise threads
+    const int pb = pt % NB, pu = (pt / NB) * UPT;
     const bool pw = warp >= 2;
     const bool pvalid = pw && (b0 + pb) < B;
-    float c_reg[4] = {0.f, 0.f, 0.f, 0.f};
+    float c_reg[UPT];
+#pragma unroll
+    for (int j = 0; j < UPT; ++j) c_reg[j] = 0.f;
 
     // ---- prologue: publish h0 as bf16 (hi, lo) into ping-pong buffer 0; load c0
     if (pvalid) {
         const long long o = (long long)(b0 + pb) * H + u0 + pu;
-        const float4 h0 = *reinterpret_cast<const float4*>(a.hs_ext + o);
-        const float4 c0 = *reinterpret_cast<const float4*>(a.cs_ext + o);
-        c_reg[0] = c0.x; c_reg[1] = c0.y; c_reg[2] = c0.z; c_reg[3] = c0.w;
-        const float hv[4] = {h0.x, h0.y, h0.z, h0.w};
-        uint2 hi, lo;
-        hi.x = ls_pack(hv[0], hv[1]); hi.y = ls_pack(hv[2], hv[3]);
-        lo.x = ls_pack(hv[0] - ls_round(hv[0]), hv[1] - ls_round(hv[1]));
-        lo.y = ls_pack(hv[2] - ls_round(hv[2]), hv[3] - ls_round(hv[3]));
-        *reinterpret_cast<uint2*>(a.h16_hi + o) = hi;
-        *reinterpret_cast<uint2*>(a.h16_lo + o) = lo;
+        float hv[UPT];
+#pragma unroll
+        for (int j = 0; j < UPT; ++j) {
+            hv[j] = a.hs_ext[o + j];
+            c_reg[j] = a.cs_ext[o + j];
+        }
+        st_bf16_hilo<UPT>(a.h16_hi + o, a.h16_lo + o, hv);
     }
     if (pw) {
         __threadfence();
@@ -151,8 +180,8 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
                     if (++spins > (1u << 28)) __trap();
                 asm volatile("fence.proxy.async;" ::: "memory");   // generic writes -> TMA reads
                 for (int kb = 0; kb < NKB; ++kb, ++it) {
-                    const int s = it % LS_STAGES;
-                    mbar_wait(&empty_bar[s], ((it / LS_STAGES) & 1) ^ 1);
+                    const int s = it % STAGES;
+                    mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
                     mbar_expect_tx(&full_bar[s], STAGE);
                     uint8_t* dst = h_s + (size_t)s * STAGE;
                     tma_load_2d(dst, &tma_hi, kb * 64, p * B + b0, &full_bar[s]);
@@ -161,13 +190,13 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
             }
         } else if (warp == 1) {
             if (lane == 0) {
-                constexpr uint32_t idesc = umma_idesc_bf16(LS_ROWS, LS_NB);
+                constexpr uint32_t idesc = umma_idesc_bf16(LS_ROWS, NB);
                 mbar_wait(&acc_empty, (t & 1) ^ 1);                // readers drained step t-1
                 tc_fence_after();
                 const uint32_t w_hi = smem_u32(w_s), w_lo = w_hi + NKB * W_KB;
                 for (int kb = 0; kb < NKB; ++kb, ++it) {
-                    const int s = it % LS_STAGES;
-                    mbar_wait(&full_bar[s], (it / LS_STAGES) & 1);
+                    const int s = it % STAGES;
+                    mbar_wait(&full_bar[s], (it / STAGES) & 1);
                     tc_fence_after();
                     const uint32_t hhi = smem_u32(h_s + (size_t)s * STAGE), hlo = hhi + H_TILE;
                     const uint32_t whi = w_hi + kb * W_KB, wlo = w_lo + kb * W_KB;
@@ -186,23 +215,23 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
             }
         } else {
             // ---- pointwise threads: prefetch this step's input projection (independent of the MMA)
-            float xp[4][4];
+            float xp[4][UPT];
             if (pvalid) {
                 const float* xc = a.xprojT + a.col0 + (long long)t * B + b0 + pb;
 #pragma unroll
                 for (int g = 0; g < 4; ++g)
 #pragma unroll
-                    for (int j = 0; j < 4; ++j)
+                    for (int j = 0; j < UPT; ++j)
                         xp[g][j] = __ldg(xc + (long long)(g * H + u0 + pu + j) * a.ldx);
             }
             if (warp < 6) {
-                // ---- TMEM readers: gate q = warp % 4, unit = lane (< 16), 64 batch columns
+                // ---- TMEM readers: gate q = warp % 4, unit = lane (< 16), NB batch columns
                 const int q = warp & 3;
                 mbar_wait(&acc_full, t & 1);
                 tc_fence_after();
                 uint32_t r0[32], r1[32];
                 tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16), r0);
-                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + 32, r1);
+                if constexpr (NB == 64) tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + 32, r1);
                 tmem_ld_wait();
                 tc_fence_before();
                 mbar_arrive(&acc_empty);
@@ -212,17 +241,18 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
                         *reinterpret_cast<float4*>(&G[q][lane][j]) =
                             make_float4(__uint_as_float(r0[j]), __uint_as_float(r0[j + 1]),
                                         __uint_as_float(r0[j + 2]), __uint_as_float(r0[j + 3]));
-                        *reinterpret_cast<float4*>(&G[q][lane][32 + j]) =
-                            make_float4(__uint_as_float(r1[j]), __uint_as_float(r1[j + 1]),
-                                        __uint_as_float(r1[j + 2]), __uint_as_float(r1[j + 3]));
+                        if constexpr (NB == 64)
+                            *reinterpret_cast<float4*>(&G[q][lane][32 + j]) =
+                                make_float4(__uint_as_float(r1[j]), __uint_as_float(r1[j + 1]),
+                                            __uint_as_float(r1[j + 2]), __uint_as_float(r1[j + 3]));
                     }
                 }
             }
             named_bar_sync(1, 256);                                 // G complete
             if (pvalid) {
-                float hv[4], cv[4], gi[4], gf[4], gg[4], go[4];
+                float hv[UPT], cv[UPT], gi[UPT], gf[UPT], gg[UPT], go[UPT];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
+                for (int j = 0; j < UPT; ++j) {
                     gi[j] = ls_sigmoid(G[0][pu + j][pb] + xp[0][j]);
                     gf[j] = ls_sigmoid(G[1][pu + j][pb] + xp[1][j]);
                     gg[j] = tanhf(G[2][pu + j][pb] + xp[2][j]);
@@ -232,21 +262,16 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
                     c_reg[j] = cv[j];
                 }
                 const long long o = (long long)(b0 + pb) * H + u0 + pu;
-                *reinterpret_cast<float4*>(a.hs_ext + (long long)(t + 1) * BH + o) = make_float4(hv[0], hv[1], hv[2], hv[3]);
-                *reinterpret_cast<float4*>(a.cs_ext + (long long)(t + 1) * BH + o) = make_float4(cv[0], cv[1], cv[2], cv[3]);
-                uint2 hi, lo;
-                hi.x = ls_pack(hv[0], hv[1]); hi.y = ls_pack(hv[2], hv[3]);
-                lo.x = ls_pack(hv[0] - ls_round(hv[0]), hv[1] - ls_round(hv[1]));
-                lo.y = ls_pack(hv[2] - ls_round(hv[2]), hv[3] - ls_round(hv[3]));
+                st_f32<UPT>(a.hs_ext + (long long)(t + 1) * BH + o, hv);
+                st_f32<UPT>(a.cs_ext + (long long)(t + 1) * BH + o, cv);
                 const long long o16 = (long long)((t + 1) & 1) * BH + o;
-                *reinterpret_cast<uint2*>(a.h16_hi + o16) = hi;
-                *reinterpret_cast<uint2*>(a.h16_lo + o16) = lo;
+                st_bf16_hilo<UPT>(a.h16_hi + o16, a.h16_lo + o16, hv);
                 if (a.gates) {
                     float* gp = a.gates + ((long long)t * B + b0 + pb) * 4 * H + u0 + pu;
-                    *reinterpret_cast<float4*>(gp) = make_float4(gi[0], gi[1], gi[2], gi[3]);
-                    *reinterpret_cast<float4*>(gp + H) = make_float4(gf[0], gf[1], gf[2], gf[3]);
-                    *reinterpret_cast<float4*>(gp + 2 * H) = make_float4(gg[0], gg[1], gg[2], gg[3]);
-                    *reinterpret_cast<float4*>(gp + 3 * H) = make_float4(go[0], go[1], go[2], go[3]);
+                    st_f32<UPT>(gp, gi);
+                    st_f32<UPT>(gp + H, gf);
+                    st_f32<UPT>(gp + 2 * H, gg);
+                    st_f32<UPT>(gp + 3 * H, go);
                 }
             }
             __threadfence();
@@ -444,8 +469,8 @@ typedef CUresult (*EncodeTiledFn2)(CUtensorMap*, CUtensorMapDataType, cuuint32_t
                                    const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-static int make_h_tmap(CUtensorMap* tm, const void* base, long long rows, long long cols);
-static int make_h_tmap(CUtensorMap* tm, const void* base, long long rows, long long cols) {
+static int make_h_tmap(CUtensorMap* tm, const void* base, long long rows, long long cols,
+                       int box_rows = LS_NB) {
     static EncodeTiledFn2 fn = nullptr;
     if (!fn) {
         void* p = nullptr;
@@ -457,7 +482,7 @@ static int make_h_tmap(CUtensorMap* tm, const void* base, long long rows, long l
     R2D2_REQUIRE(fn, "tc_lstm: cuTensorMapEncodeTiled is unavailable in this driver");
     cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
     cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
-    cuuint32_t box[2] = {64, (cuuint32_t)LS_NB};
+    cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box,
                     estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
@@ -498,17 +523,22 @@ int r2d2_tc_lstm_seq_fwd(const float* xprojT, int64_t ldx, int64_t col0, const f
     a.h16_lo = reinterpret_cast<__nv_bfloat16*>(sc + h16);
     a.counter = reinterpret_cast<int*>(sc + 2 * h16);
     a.T = T; a.B = B; a.H = H;
-    const int groups = (B + LS_NB - 1) / LS_NB;
+    // batch tile: 32 columns spreads a chain over twice the SMs; fall back to 64 when that many
+    // CTAs (two chains may run side by side) would not be co-resident
+    const int NKB = H / 64;
+    int nb = 32;
+    if ((H / LS_UNITS) * ((B + 31) / 32) * 2 > sm_count()) nb = 64;
+    const int groups = (B + nb - 1) / nb;
     R2D2_REQUIRE(groups <= 64, "tc_lstm_seq_fwd: batch too large");
     R2D2_CUDA_OK(cudaMemsetAsync(a.counter, 0, 256, st));
     CUtensorMap thi, tlo;
-    int rc = make_h_tmap(&thi, a.h16_hi, 2ll * B, H);
+    int rc = make_h_tmap(&thi, a.h16_hi, 2ll * B, H, nb);
     if (rc) return rc;
-    rc = make_h_tmap(&tlo, a.h16_lo, 2ll * B, H);
+    rc = make_h_tmap(&tlo, a.h16_lo, 2ll * B, H, nb);
     if (rc) return rc;
-    const int NKB = H / 64;
-    const int smem = 2 * NKB * LS_ROWS * 128 + LS_STAGES * 2 * LS_NB * 128 + 1024;
-    R2D2_CUDA_OK(cudaFuncSetAttribute(tc_lstm_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    const int smem = 2 * NKB * LS_ROWS * 128 + (256 / nb) * 2 * nb * 128 + 1024;
+    void* kern = nb == 32 ? (void*)tc_lstm_fwd_kernel<32> : (void*)tc_lstm_fwd_kernel<64>;
+    R2D2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     dim3 grid(H / LS_UNITS, groups);
     R2D2_REQUIRE((int)(grid.x * grid.y) <= sm_count(),
                  "tc_lstm_seq_fwd: %d CTAs must be co-resident but the device has %d SMs",
@@ -516,8 +546,7 @@ int r2d2_tc_lstm_seq_fwd(const float* xprojT, int64_t ldx, int64_t col0, const f
     void* params[] = {&thi, &tlo, &a};
     {
         ProfScope ps("tc_lstm_fwd_kernel", st);
-        R2D2_CUDA_OK(cudaLaunchCooperativeKernel((void*)tc_lstm_fwd_kernel, grid, dim3(320), params,
-                                                 (size_t)smem, st));
+        R2D2_CUDA_OK(cudaLaunchCooperativeKernel(kern, grid, dim3(320), params, (size_t)smem, st));
     }
     return R2D2_OK;
 }

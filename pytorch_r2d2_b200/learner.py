@@ -163,7 +163,7 @@ class Learner:
         ws["hs_dq"], ws["cs_dq"] = f(L + 1, B, H), f(L + 1, B, H)
         ws["hs_tg"], ws["cs_tg"] = f(T + 1, B, H), f(T + 1, B, H)
         ws["gates"] = f(T, B, 4 * H)
-        ws["hid_on"], ws["hid_tmp"] = f(M, 2 * H), f(M, 2 * H)
+        ws["hid_on"], ws["hid_tmp"], ws["hid_tg"] = f(M, 2 * H), f(M, 2 * H), f(M, 2 * H)
         ws["q_all"], ws["qn_on"], ws["qn_tg"] = f(M, N_ACTIONS), f(M, N_ACTIONS), f(M, N_ACTIONS)
         ws["td"] = dict(next_action=torch.empty(M, dtype=torch.int64, device=dev), y=f(M), delta=f(M),
                         dq=f(M, N_ACTIONS), prio=f(M), loss=f(1))
@@ -183,7 +183,7 @@ class Learner:
             ws["feat16_on"], ws["feat16_tg"] = h(2, S * B, FEAT), h(2, T * B, FEAT)
             ws["w_ih16"], ws["w_ih16_t"], ws["w_ihT16"] = h(2, 4 * H, FEAT), h(2, 4 * H, FEAT), h(FEAT, 4 * H)
             ws["hw1_16"], ws["hw1_16_t"], ws["hw1T16"] = h(2, 2 * H, H), h(2, 2 * H, H), h(H, 2 * H)
-            ws["hs16"] = h(2, M, H)
+            ws["hs16"], ws["hs16_t"] = h(2, M, H), h(2, M, H)
             # transposed input projections [4H, frames*B] for the persistent LSTM kernel
             ws["xpT_on"], ws["xpT_tg"] = f(4 * H, S * B), f(4 * H, T * B)
             ws["lstm_scratch"] = torch.empty(engine.tc_lstm_scratch_bytes(B, H), dtype=torch.uint8, device=dev)
@@ -214,76 +214,85 @@ class Learner:
         g = Weights(self.optim.grad, self.net.layout)
         M = L * B
 
-        # ---- conv torso + input projection: online on all T+n frames, target on frames n..T+n
-        tc = self.precision == "bf16"
-        engine.torso_fwd_u8(slab, 0, T + n, w, ws["a1_on"], ws["a2_on"], ws["feat_on"], tc=tc)
-        engine.torso_fwd_u8(slab, n, T, wt, ws["a1_tg"], ws["a2_tg"], ws["feat_tg"], tc=tc)
         bf16 = self.precision == "bf16"
-        if bf16:   # dense contractions on tcgen05: bf16 copies of this step's operands
-            def split(x, pair):
-                engine.split_bf16(x, pair[0], pair[1])
+        hs_learn = ws["hs_on"][1 + BI:].reshape(M, H)
 
-            split(w.w_ih, ws["w_ih16"])
-            split(wt.w_ih, ws["w_ih16_t"])
-            split(w.head_w1, ws["hw1_16"])
-            split(wt.head_w1, ws["hw1_16_t"])
-            split(ws["feat_on"], ws["feat16_on"])
-            split(ws["feat_tg"], ws["feat16_tg"])
-            # forward contractions: error-compensated bf16x3
-            # xproj^T[4H, frames*B] = W_ih . feat^T + (b_ih + b_hh) per row
-            engine.tc_linear_x3(ws["w_ih16"][0], ws["w_ih16"][1], ws["feat16_on"][0], ws["feat16_on"][1],
-                                w.b_ih, w.b_hh, y32=ws["xpT_on"], bias_row=True)
-            engine.tc_linear_x3(ws["w_ih16_t"][0], ws["w_ih16_t"][1], ws["feat16_tg"][0],
-                                ws["feat16_tg"][1], wt.b_ih, wt.b_hh, y32=ws["xpT_tg"], bias_row=True)
-        else:
-            engine.linear_fwd(ws["feat_on"], w.w_ih, w.b_ih, w.b_hh, ws["xp_on"])
-            engine.linear_fwd(ws["feat_tg"], wt.w_ih, wt.b_ih, wt.b_hh, ws["xp_tg"])
+        def split(x, pair):
+            engine.split_bf16(x, pair[0], pair[1])
 
-        # ---- online net: burn-in + learn over state[0:T] (hidden state carries through); then
-        #      again on next_state[BI:T] = frames BI+n.., starting from the state left after
-        #      state[T-1] (the reference never resets it: learner.py:86,91); target net: burn-in
-        #      on next_state[0:BI], then next_state[BI:T]
-        ws["hs_on"][0].copy_(batch["hs"])
-        ws["cs_on"][0].copy_(batch["cs"])
-        ws["hs_tg"][0].copy_(batch["target_hs"])
-        ws["cs_tg"][0].copy_(batch["target_cs"])
+        def head(hs, wts, w1_16, hs16, hid, q):
+            """Dueling head on [M,H] hidden states (bf16: compensated tcgen05 hidden layer)."""
+            if bf16:
+                split(hs, hs16)
+                engine.tc_linear_x3(hs16[0], hs16[1], w1_16[0], w1_16[1], wts.head_b1, None, y32=hid,
+                                    relu=True)
+                engine.head_out(hid, wts, q)
+            else:
+                engine.head_fwd(hs, wts, hid, q)
+
+        def target_branch():
+            """Target net (learner.py:72,79,92): torso on frames n..T+n, burn-in on
+            next_state[0:BI], evaluation on next_state[BI:T].  Independent of the online net
+            until the TD target, so in bf16 mode it runs on the side stream."""
+            engine.torso_fwd_u8(slab, n, T, wt, ws["a1_tg"], ws["a2_tg"], ws["feat_tg"], tc=bf16)
+            ws["hs_tg"][0].copy_(batch["target_hs"])
+            ws["cs_tg"][0].copy_(batch["target_cs"])
+            if bf16:
+                split(wt.w_ih, ws["w_ih16_t"])
+                split(wt.head_w1, ws["hw1_16_t"])
+                split(ws["feat_tg"], ws["feat16_tg"])
+                engine.tc_linear_x3(ws["w_ih16_t"][0], ws["w_ih16_t"][1], ws["feat16_tg"][0],
+                                    ws["feat16_tg"][1], wt.b_ih, wt.b_hh, y32=ws["xpT_tg"], bias_row=True)
+                engine.tc_lstm_seq_fwd(ws["xpT_tg"], 0, wt.w_hh, ws["hs_tg"], ws["cs_tg"], None, T, B, H,
+                                       ws["lstm_scratch_tg"])
+            else:
+                engine.linear_fwd(ws["feat_tg"], wt.w_ih, wt.b_ih, wt.b_hh, ws["xp_tg"])
+                engine.lstm_seq_fwd(ws["xp_tg"], wt.w_hh, ws["hs_tg"], ws["cs_tg"], None, T, B, H)
+            head(ws["hs_tg"][1 + BI:].reshape(M, H), wt, ws.get("hw1_16_t"), ws.get("hs16_t"),
+                 ws["hid_tg"], ws["qn_tg"])
+
         if bf16:
-            # the two chains are independent and latency-bound on H/16 SMs each: run the target
-            # net's unroll on a side stream next to the online net's
             main, side = torch.cuda.current_stream(), ws["side_stream"]
             ws["ev_fork"].record(main)
             side.wait_event(ws["ev_fork"])
             with torch.cuda.stream(side):
-                engine.tc_lstm_seq_fwd(ws["xpT_tg"], 0, wt.w_hh, ws["hs_tg"], ws["cs_tg"], None, T, B, H,
-                                       ws["lstm_scratch_tg"])
+                target_branch()
                 ws["ev_join"].record(side)
+        else:
+            target_branch()
+
+        # ---- online net: torso on all T+n frames; burn-in + learn over state[0:T] (the hidden
+        #      state carries through); then again on next_state[BI:T] = frames BI+n.., starting
+        #      from the state left after state[T-1] (the reference never resets it:
+        #      learner.py:86,91)
+        engine.torso_fwd_u8(slab, 0, T + n, w, ws["a1_on"], ws["a2_on"], ws["feat_on"], tc=bf16)
+        ws["hs_on"][0].copy_(batch["hs"])
+        ws["cs_on"][0].copy_(batch["cs"])
+        if bf16:
+            # forward contractions: error-compensated bf16x3 (DESIGN.md section 4b);
+            # xproj^T[4H, frames*B] = W_ih . feat^T + (b_ih + b_hh) per row
+            split(w.w_ih, ws["w_ih16"])
+            split(w.head_w1, ws["hw1_16"])
+            split(ws["feat_on"], ws["feat16_on"])
+            engine.tc_linear_x3(ws["w_ih16"][0], ws["w_ih16"][1], ws["feat16_on"][0], ws["feat16_on"][1],
+                                w.b_ih, w.b_hh, y32=ws["xpT_on"], bias_row=True)
             sc = ws["lstm_scratch"]
             engine.tc_lstm_seq_fwd(ws["xpT_on"], 0, w.w_hh, ws["hs_on"], ws["cs_on"], ws["gates"], T, B, H, sc)
             ws["hs_dq"][0].copy_(ws["hs_on"][T])
             ws["cs_dq"][0].copy_(ws["cs_on"][T])
             engine.tc_lstm_seq_fwd(ws["xpT_on"], (BI + n) * B, w.w_hh, ws["hs_dq"], ws["cs_dq"], None, L, B, H, sc)
-            main.wait_event(ws["ev_join"])
         else:
+            engine.linear_fwd(ws["feat_on"], w.w_ih, w.b_ih, w.b_hh, ws["xp_on"])
             engine.lstm_seq_fwd(ws["xp_on"], w.w_hh, ws["hs_on"], ws["cs_on"], ws["gates"], T, B, H)
             ws["hs_dq"][0].copy_(ws["hs_on"][T])
             ws["cs_dq"][0].copy_(ws["cs_on"][T])
             engine.lstm_seq_fwd(ws["xp_on"][(BI + n) * B:], w.w_hh, ws["hs_dq"], ws["cs_dq"], None, L, B, H)
-            engine.lstm_seq_fwd(ws["xp_tg"], wt.w_hh, ws["hs_tg"], ws["cs_tg"], None, T, B, H)
 
         # ---- dueling heads on the learn window only
-        hs_learn = ws["hs_on"][1 + BI:].reshape(M, H)
-        def head(hs, wts, w1_16, hid, q):
-            if bf16:
-                engine.split_bf16(hs, ws["hs16"][0], ws["hs16"][1])
-                engine.tc_linear_x3(ws["hs16"][0], ws["hs16"][1], w1_16[0], w1_16[1], wts.head_b1, None,
-                                    y32=hid, relu=True)
-                engine.head_out(hid, wts, q)
-            else:
-                engine.head_fwd(hs, wts, hid, q)
-
-        head(ws["hs_dq"][1:].reshape(M, H), w, ws.get("hw1_16"), ws["hid_tmp"], ws["qn_on"])
-        head(ws["hs_tg"][1 + BI:].reshape(M, H), wt, ws.get("hw1_16_t"), ws["hid_tmp"], ws["qn_tg"])
-        head(hs_learn, w, ws.get("hw1_16"), ws["hid_on"], ws["q_all"])   # last: hs16 = learn window
+        head(ws["hs_dq"][1:].reshape(M, H), w, ws.get("hw1_16"), ws.get("hs16"), ws["hid_tmp"], ws["qn_on"])
+        head(hs_learn, w, ws.get("hw1_16"), ws.get("hs16"), ws["hid_on"], ws["q_all"])
+        if bf16:
+            main.wait_event(ws["ev_join"])
 
         # ---- n-step double-Q target, TD error, loss gradient, per-step priorities
         td = ws["td"]
