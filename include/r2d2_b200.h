@@ -224,6 +224,10 @@ int r2d2_tc_torso_fwd_f32(const float* frames, int R, const float* w1, const flo
  * [4H, ldx] (column col0 + t*B + b), biases included.  Outputs as r2d2_lstm_seq_fwd.
  * H % 64 == 0, H <= 512; H/16 * ceil(B/64) CTAs must be co-resident. */
 int64_t r2d2_tc_lstm_scratch_bytes(int B, int H);
+/* diagnostics: [T,32] int64 device buffer receiving globaltimer stamps of CTA (0,0) per step
+ * (barrier passed, proxy fence, MMAs issued, accumulator ready, gates staged, stores issued,
+ * fence done, arrive done); null switches it off */
+int r2d2_tc_lstm_set_trace(void* trace);
 int r2d2_tc_lstm_seq_fwd(const float* xprojT, int64_t ldx, int64_t col0, const float* w_hh,
                          float* hs_ext, float* cs_ext, float* gates, int T, int B, int H,
                          void* scratch, void* stream);

@@ -21,7 +21,7 @@
 
 namespace r2d2 {
 
-constexpr int LS_UNITS = 16, LS_ROWS = 64, LS_NB = 64, LS_STAGES = 4;   // LS_NB: backward batch tile
+constexpr int LS_UNITS = 16, LS_ROWS = 64, LS_NB = 64;   // LS_NB: backward batch tile
 
 __device__ __forceinline__ uint32_t ls_pack(float a, float b) {
     __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
@@ -31,7 +31,13 @@ __device__ __forceinline__ float ls_round(float x) { return __bfloat162float(__f
 __device__ __forceinline__ uint32_t ls_sw128(int row, int chunk) {
     return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((chunk ^ (row & 7)) << 4));
 }
-__device__ __forceinline__ float ls_sigmoid(float x) { return 1.f / (1.f + expf(-x)); }
+// sigmoid / tanh through ex2.approx + rcp.approx: absolute error ~1e-7 (inside the 1e-5 class),
+// a fraction of the instructions of the libm-accurate versions on the per-step critical path
+__device__ __forceinline__ float ls_sigmoid(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
+__device__ __forceinline__ float ls_tanh(float x) { return 1.f - __fdividef(2.f, __expf(2.f * x) + 1.f); }
+__device__ __forceinline__ void red_release_add(int* p, int v) {
+    asm volatile("red.release.gpu.global.add.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 
 __device__ __forceinline__ int ld_acquire(const int* p) {
     int v;
@@ -53,7 +59,18 @@ struct LstmArgs {
     __nv_bfloat16* h16_lo;
     int* counter;          // [gridDim.y] grid barrier counters, zero on entry
     int T, B, H;
+    long long* trace;      // optional [T, 8] globaltimer stamps of CTA (0,0) (diagnostics), or null
 };
+
+__device__ __forceinline__ long long gtimer() {
+    long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+#define LS_STAMP(slot)                                                        \
+    do {                                                                      \
+        if (a.trace && blockIdx.x == 0 && blockIdx.y == 0) a.trace[t * 32 + (slot)] = gtimer(); \
+    } while (0)
 
 template <int N> __device__ __forceinline__ void st_f32(float* p, const float* v) {
     if constexpr (N == 4) *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
@@ -81,8 +98,10 @@ template <int N> __device__ __forceinline__ void st_bf16_hilo(__nv_bfloat16* hi,
 // NB = batch columns per CTA (UMMA N).  Batch rows never interact, so the B/NB batch groups are
 // independent chains with their own arrive counter: a smaller NB spreads one chain over more SMs
 // (less h traffic, MMA time and pointwise work per CTA per step).
+constexpr int LS_ISSUERS = 4;   // MMA-issuing warps: 1, 10, 11, 12 (k-blocks kb % 4 == i)
+
 template <int NB>
-__global__ void __launch_bounds__(320, 1)
+__global__ void __launch_bounds__(416, 1)
 tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_constant__ CUtensorMap tma_lo,
                    const LstmArgs a) {
     constexpr int STAGES = 256 / NB;                            // 64 -> 4, 32 -> 8 (whole h in flight)
@@ -114,7 +133,7 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
         }
-        mbar_init(&acc_full, 1);
+        mbar_init(&acc_full, LS_ISSUERS);
         mbar_init(&acc_empty, 128);
         mbar_fence_init();
     }
@@ -136,16 +155,17 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
             make_uint4(ls_pack(l[0], l[1]), ls_pack(l[2], l[3]), ls_pack(l[4], l[5]), ls_pack(l[6], l[7]));
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    if (warp == 1) tmem_alloc(&tmem_slot, 64);
+    if (warp == 1) tmem_alloc(&tmem_slot, LS_ISSUERS * NB);   // one accumulator slice per issuer
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_slot;
+    const int issuer = warp == 1 ? 0 : (warp >= 10 ? warp - 9 : -1);
 
     // pointwise mapping (warps 2..9): batch row pb and UPT consecutive hidden units
     const int pt = tid - 64;                      // 0..255 for pointwise threads
     const int pb = pt % NB, pu = (pt / NB) * UPT;
-    const bool pw = warp >= 2;
+    const bool pw = warp >= 2 && warp < 10;
     const bool pvalid = pw && (b0 + pb) < B;
     float c_reg[UPT];
 #pragma unroll
@@ -163,9 +183,10 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
         st_bf16_hilo<UPT>(a.h16_hi + o, a.h16_lo + o, hv);
     }
     if (pw) {
-        __threadfence();
+        // CTA barrier orders every thread's stores before thread 0's gpu-scope RELEASE, which is
+        // cumulative: one releasing arrive per CTA instead of 256 thread fences
         named_bar_sync(1, 256);
-        if (pt == 0) atomicAdd(counter, 1);
+        if (pt == 0) red_release_add(counter, 1);
     }
 
     uint32_t it = 0;   // ring iteration counter (producer and MMA warps keep identical copies)
@@ -178,7 +199,9 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
                 uint32_t spins = 0;
                 while (ld_acquire(counter) < target)
                     if (++spins > (1u << 28)) __trap();
+                LS_STAMP(0);                                        // barrier passed
                 asm volatile("fence.proxy.async;" ::: "memory");   // generic writes -> TMA reads
+                LS_STAMP(1);
                 for (int kb = 0; kb < NKB; ++kb, ++it) {
                     const int s = it % STAGES;
                     mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
@@ -188,30 +211,38 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
                     tma_load_2d(dst + H_TILE, &tma_lo, kb * 64, p * B + b0, &full_bar[s]);
                 }
             }
-        } else if (warp == 1) {
+        } else if (issuer >= 0) {
             if (lane == 0) {
+                // Four issuing warps, k-blocks kb % 4 == issuer, each accumulating into its own
+                // TMEM slice (the readers add the slices): issuing the 12*NKB small MMAs of a step
+                // from one thread was the critical path (37 ns per MMA, tools/diag_lstm.py).
                 constexpr uint32_t idesc = umma_idesc_bf16(LS_ROWS, NB);
                 mbar_wait(&acc_empty, (t & 1) ^ 1);                // readers drained step t-1
                 tc_fence_after();
-                const uint32_t w_hi = smem_u32(w_s), w_lo = w_hi + NKB * W_KB;
-                for (int kb = 0; kb < NKB; ++kb, ++it) {
-                    const int s = it % STAGES;
-                    mbar_wait(&full_bar[s], (it / STAGES) & 1);
+                const uint64_t dw_hi = umma_desc_k_sw128(smem_u32(w_s));
+                const uint64_t dw_lo = dw_hi + (uint64_t)((NKB * W_KB) >> 4);
+                const uint64_t dh0 = umma_desc_k_sw128(smem_u32(h_s));
+                const uint32_t d = tmem_base + issuer * NB;
+                const uint32_t it0 = (uint32_t)t * NKB;             // ring position of k-block 0
+                for (int kb = issuer; kb < NKB; kb += LS_ISSUERS) {
+                    const uint32_t itk = it0 + kb;
+                    const int s = itk % STAGES;
+                    mbar_wait(&full_bar[s], (itk / STAGES) & 1);
                     tc_fence_after();
-                    const uint32_t hhi = smem_u32(h_s + (size_t)s * STAGE), hlo = hhi + H_TILE;
-                    const uint32_t whi = w_hi + kb * W_KB, wlo = w_lo + kb * W_KB;
+                    const uint64_t hhi = dh0 + (uint64_t)((s * STAGE) >> 4), hlo = hhi + (H_TILE >> 4);
+                    const uint64_t whi = dw_hi + (uint64_t)((kb * W_KB) >> 4);
+                    const uint64_t wlo = dw_lo + (uint64_t)((kb * W_KB) >> 4);
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {
-                        umma_f16(tmem_base, umma_desc_k_sw128(whi + k * 32), umma_desc_k_sw128(hhi + k * 32),
-                                 idesc, (kb | k) != 0);
-                        umma_f16(tmem_base, umma_desc_k_sw128(wlo + k * 32), umma_desc_k_sw128(hhi + k * 32),
-                                 idesc, 1);
-                        umma_f16(tmem_base, umma_desc_k_sw128(whi + k * 32), umma_desc_k_sw128(hlo + k * 32),
-                                 idesc, 1);
+                        umma_f16(d, whi + 2 * k, hhi + 2 * k, idesc, (kb >= LS_ISSUERS) | (k != 0));
+                        umma_f16(d, wlo + 2 * k, hhi + 2 * k, idesc, 1);
+                        umma_f16(d, whi + 2 * k, hlo + 2 * k, idesc, 1);
                     }
                     umma_commit(&empty_bar[s]);
+                    if (issuer == 0) LS_STAMP(16 + kb);
                 }
-                umma_commit(&acc_full);
+                if (issuer == 0) LS_STAMP(2);
+                umma_commit(&acc_full);                             // LS_ISSUERS arrivals complete it
             }
         } else {
             // ---- pointwise threads: prefetch this step's input projection (independent of the MMA)
@@ -228,37 +259,46 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
                 // ---- TMEM readers: gate q = warp % 4, unit = lane (< 16), NB batch columns
                 const int q = warp & 3;
                 mbar_wait(&acc_full, t & 1);
+                if (tid == 64) LS_STAMP(3);                         // accumulator complete
                 tc_fence_after();
-                uint32_t r0[32], r1[32];
-                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16), r0);
-                if constexpr (NB == 64) tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + 32, r1);
-                tmem_ld_wait();
+                const int nslices = NKB < LS_ISSUERS ? NKB : LS_ISSUERS;   // issuers that ran MMAs
+                float acc[NB];
+#pragma unroll
+                for (int j = 0; j < NB; ++j) acc[j] = 0.f;
+#pragma unroll
+                for (int i = 0; i < LS_ISSUERS; ++i) {
+                    if (i < nslices) {
+#pragma unroll
+                        for (int c = 0; c < NB; c += 32) {
+                            uint32_t r[32];
+                            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + i * NB + c, r);
+                            tmem_ld_wait();
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) acc[c + j] += __uint_as_float(r[j]);
+                        }
+                    }
+                }
                 tc_fence_before();
                 mbar_arrive(&acc_empty);
                 if (lane < LS_UNITS) {
 #pragma unroll
-                    for (int j = 0; j < 32; j += 4) {
+                    for (int j = 0; j < NB; j += 4)
                         *reinterpret_cast<float4*>(&G[q][lane][j]) =
-                            make_float4(__uint_as_float(r0[j]), __uint_as_float(r0[j + 1]),
-                                        __uint_as_float(r0[j + 2]), __uint_as_float(r0[j + 3]));
-                        if constexpr (NB == 64)
-                            *reinterpret_cast<float4*>(&G[q][lane][32 + j]) =
-                                make_float4(__uint_as_float(r1[j]), __uint_as_float(r1[j + 1]),
-                                            __uint_as_float(r1[j + 2]), __uint_as_float(r1[j + 3]));
-                    }
+                            make_float4(acc[j], acc[j + 1], acc[j + 2], acc[j + 3]);
                 }
             }
             named_bar_sync(1, 256);                                 // G complete
+            if (pt == 0) LS_STAMP(4);
             if (pvalid) {
                 float hv[UPT], cv[UPT], gi[UPT], gf[UPT], gg[UPT], go[UPT];
 #pragma unroll
                 for (int j = 0; j < UPT; ++j) {
                     gi[j] = ls_sigmoid(G[0][pu + j][pb] + xp[0][j]);
                     gf[j] = ls_sigmoid(G[1][pu + j][pb] + xp[1][j]);
-                    gg[j] = tanhf(G[2][pu + j][pb] + xp[2][j]);
+                    gg[j] = ls_tanh(G[2][pu + j][pb] + xp[2][j]);
                     go[j] = ls_sigmoid(G[3][pu + j][pb] + xp[3][j]);
                     cv[j] = gf[j] * c_reg[j] + gi[j] * gg[j];
-                    hv[j] = go[j] * tanhf(cv[j]);
+                    hv[j] = go[j] * ls_tanh(cv[j]);
                     c_reg[j] = cv[j];
                 }
                 const long long o = (long long)(b0 + pb) * H + u0 + pu;
@@ -274,14 +314,18 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
                     st_f32<UPT>(gp + 3 * H, go);
                 }
             }
-            __threadfence();
+            if (pt == 0) LS_STAMP(5);                               // pointwise + stores issued
             named_bar_sync(2, 256);                                 // all of this CTA's h_t is out
-            if (pt == 0) atomicAdd(counter, 1);
+            if (pt == 0) {
+                LS_STAMP(6);
+                red_release_add(counter, 1);
+                LS_STAMP(7);
+            }
         }
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 1) tmem_dealloc(tmem_base, 64);
+    if (warp == 1) tmem_dealloc(tmem_base, LS_ISSUERS * NB);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -381,16 +425,16 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
                 constexpr uint32_t idesc = umma_idesc_bf16(LS_NB, LS_UNITS);
                 mbar_wait(&acc_empty, s & 1);   // readers drained iteration s-1 (s=1: passes at once)
                 tc_fence_after();
-                const uint32_t wb = smem_u32(w_s);
+                const uint64_t db0 = umma_desc_k_sw128(smem_u32(w_s));
+                const uint64_t da0 = umma_desc_k_sw128(smem_u32(a_s));
                 for (int kb = 0; kb < NKB; ++kb, ++it) {
                     const int st = it % LB_STAGES;
                     mbar_wait(&full_bar[st], (it / LB_STAGES) & 1);
                     tc_fence_after();
-                    const uint32_t aa = smem_u32(a_s + (size_t)st * A_TILE), bb = wb + kb * W_KB;
+                    const uint64_t aa = da0 + (uint64_t)((st * A_TILE) >> 4);
+                    const uint64_t bb = db0 + (uint64_t)((kb * W_KB) >> 4);
 #pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        umma_f16(tmem_base, umma_desc_k_sw128(aa + k * 32), umma_desc_k_sw128(bb + k * 32),
-                                 idesc, (kb | k) != 0);
+                    for (int k = 0; k < 4; ++k) umma_f16(tmem_base, aa + 2 * k, bb + 2 * k, idesc, (kb | k) != 0);
                     umma_commit(&empty_bar[st]);
                 }
                 umma_commit(&acc_full);
@@ -431,7 +475,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
 #pragma unroll
                 for (int j = 0; j < 16; ++j) {
                     const float d = dh[j] + rec[j];
-                    const float tc = tanhf(ct[j]);
+                    const float tc = ls_tanh(ct[j]);
                     const float dc = dc_reg[j] + d * go[j] * (1.f - tc * tc);
                     di[j] = dc * gg[j] * gi[j] * (1.f - gi[j]);
                     df[j] = dc * cp[j] * gf[j] * (1.f - gf[j]);
@@ -454,9 +498,8 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
                     *reinterpret_cast<uint4*>(d16 + 3 * H + j) = make_uint4(ls_pack(dov[j], dov[j + 1]), ls_pack(dov[j + 2], dov[j + 3]), ls_pack(dov[j + 4], dov[j + 5]), ls_pack(dov[j + 6], dov[j + 7]));
                 }
             }
-            __threadfence();
             named_bar_sync(1, 128);
-            if (tid == 64) atomicAdd(counter, 1);
+            if (tid == 64) red_release_add(counter, 1);
         }
     }
     tc_fence_before();
@@ -495,7 +538,16 @@ static int make_h_tmap(CUtensorMap* tm, const void* base, long long rows, long l
 
 using namespace r2d2;
 
+static long long* g_lstm_trace = nullptr;
+
 extern "C" {
+
+// diagnostics: device buffer [T,32] of globaltimer stamps written by CTA (0,0) of the next forward
+// unrolls (null switches it off)
+int r2d2_tc_lstm_set_trace(void* trace) {
+    g_lstm_trace = static_cast<long long*>(trace);
+    return R2D2_OK;
+}
 
 int64_t r2d2_tc_lstm_scratch_bytes(int B, int H) {
     // h16 hi + lo ping-pong [2,B,H] bf16 each, + barrier counters (256 B, kept 256-byte aligned)
@@ -523,6 +575,7 @@ int r2d2_tc_lstm_seq_fwd(const float* xprojT, int64_t ldx, int64_t col0, const f
     a.h16_lo = reinterpret_cast<__nv_bfloat16*>(sc + h16);
     a.counter = reinterpret_cast<int*>(sc + 2 * h16);
     a.T = T; a.B = B; a.H = H;
+    a.trace = g_lstm_trace;
     // batch tile: 32 columns spreads a chain over twice the SMs; fall back to 64 when that many
     // CTAs (two chains may run side by side) would not be co-resident
     const int NKB = H / 64;
@@ -546,7 +599,7 @@ int r2d2_tc_lstm_seq_fwd(const float* xprojT, int64_t ldx, int64_t col0, const f
     void* params[] = {&thi, &tlo, &a};
     {
         ProfScope ps("tc_lstm_fwd_kernel", st);
-        R2D2_CUDA_OK(cudaLaunchCooperativeKernel(kern, grid, dim3(320), params, (size_t)smem, st));
+        R2D2_CUDA_OK(cudaLaunchCooperativeKernel(kern, grid, dim3(416), params, (size_t)smem, st));
     }
     return R2D2_OK;
 }
