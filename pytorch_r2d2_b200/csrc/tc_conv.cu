@@ -161,6 +161,41 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
                 const int oy = p / HOUT, ox = p - oy * HOUT;
                 src = in + fm.base(r) + (long long)(oy * STRIDE) * HIN + ox * STRIDE;
             }
+            if constexpr (sizeof(T) == 1 && KH == 8) {
+                // conv1 on the u8 slab: the gather is memory-latency bound, so issue the loads of
+                // the WHOLE tile row (4 input channels x 4 patch rows of this thread = 32 x 4 B)
+                // before touching the ring, then convert + store k-block by k-block
+                uint32_t rawv[NKB][4][2];
+#pragma unroll
+                for (int kb = 0; kb < NKB; ++kb)
+#pragma unroll
+                    for (int cc = 0; cc < 4; ++cc) {
+                        const uint32_t* q = reinterpret_cast<const uint32_t*>(
+                            src + kb * (HIN * HIN) + (half * 4 + cc) * HIN);
+                        rawv[kb][cc][0] = valid ? __ldg(q) : 0u;
+                        rawv[kb][cc][1] = valid ? __ldg(q + 1) : 0u;
+                    }
+#pragma unroll
+                for (int kb = 0; kb < NKB; ++kb, ++it) {
+                    const int s = it % CV_STAGES;
+                    mbar_wait(&empty_bar[s], ((it / CV_STAGES) & 1) ^ 1);
+                    uint8_t* a_hi = a_s + (size_t)s * STAGE_BYTES;
+#pragma unroll
+                    for (int cc = 0; cc < 4; ++cc) {
+                        float v[8];
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            v[e] = __uint_as_float(__byte_perm(rawv[kb][cc][0], 0x4B000000u, 0x7650u | e)) - 8388608.f;
+                            v[4 + e] = __uint_as_float(__byte_perm(rawv[kb][cc][1], 0x4B000000u, 0x7650u | e)) - 8388608.f;
+                        }
+                        *reinterpret_cast<uint4*>(a_hi + sw128_off(row, half * 4 + cc)) =
+                            make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
+                                       pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+                    }
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    mbar_arrive(&full_bar[s]);
+                }
+            } else {
 #pragma unroll
             for (int kb = 0; kb < NKB; ++kb, ++it) {
                 const int s = it % CV_STAGES;
@@ -188,6 +223,7 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
                 }
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 mbar_arrive(&full_bar[s]);
+            }
             }
         }
     } else if (warp == MMA_WARP) {
