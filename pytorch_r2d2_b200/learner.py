@@ -80,6 +80,9 @@ class Learner:
         if precision not in ("fp32", "bf16"):
             raise ValueError("precision must be 'fp32' or 'bf16'")
         self.precision = precision
+        # bf16 mode: run the target net's branch on a side stream next to the online net's
+        # (False = one stream, e.g. to time kernels in isolation)
+        self.overlap_streams = True
         self.memory_path = os.path.join("./", "logs", "memory")
         # memory (learner.py:34-41)
         self.burn_in_length = 10
@@ -251,7 +254,8 @@ class Learner:
             head(ws["hs_tg"][1 + BI:].reshape(M, H), wt, ws.get("hw1_16_t"), ws.get("hs16_t"),
                  ws["hid_tg"], ws["qn_tg"])
 
-        if bf16:
+        overlap = bf16 and self.overlap_streams
+        if overlap:
             main, side = torch.cuda.current_stream(), ws["side_stream"]
             ws["ev_fork"].record(main)
             side.wait_event(ws["ev_fork"])
@@ -291,7 +295,7 @@ class Learner:
         # ---- dueling heads on the learn window only
         head(ws["hs_dq"][1:].reshape(M, H), w, ws.get("hw1_16"), ws.get("hs16"), ws["hid_tmp"], ws["qn_on"])
         head(hs_learn, w, ws.get("hw1_16"), ws.get("hs16"), ws["hid_on"], ws["q_all"])
-        if bf16:
+        if overlap:
             main.wait_event(ws["ev_join"])
 
         # ---- n-step double-Q target, TD error, loss gradient, per-step priorities

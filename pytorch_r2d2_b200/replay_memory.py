@@ -94,6 +94,7 @@ class ReplayMemory:
         _, _, total = tree_layout(M)
         self._nodes = torch.zeros(total, dtype=torch.float64, device=dev)
         self._tree_dirty = True
+        self._ingest_stream, self._ingest_event, self._ingest_pending = None, None, False
         self._u_host = None      # pinned staging for the uniforms
         self._ws = {}            # sample workspaces keyed by shape
         self._touched = None
@@ -107,6 +108,7 @@ class ReplayMemory:
         return min(self.index, self.memory_size)
 
     def _ensure_tree(self):
+        self._wait_ingest()
         if self._tree_dirty:
             _lib.call("r2d2_tree_build", _lib.ptr(self._raw("sequence_priority"), "f32"),
                       _lib.ptr(self._raw("is_seq_start"), "u8"), self.memory_size,
@@ -122,13 +124,38 @@ class ReplayMemory:
         return t.to(device=self.device, dtype=dtype, non_blocking=True).contiguous()
 
     # ------------------------------------------------------------------ write path
-    def extend(self, memory):
-        """Bulk-append an actor dump (replay_memory.py:107-119): all ten keys, ring wrap."""
+    def extend(self, memory, overlap=False):
+        """Bulk-append an actor dump (replay_memory.py:107-119): all ten keys, ring wrap.
+
+        overlap=True enqueues the host->device copies and the scatter kernel on a dedicated
+        ingest stream so that they run next to the learner's kernels; the next draw waits for
+        them (an event), so a step always sees every dump appended before it was called."""
         rows = int(memory["state"].shape[0])
         if rows == 0:
             return
         if rows > self.memory_size:
             raise ValueError("dump larger than the ring")
+        if overlap:
+            if self._ingest_stream is None:
+                self._ingest_stream = torch.cuda.Stream(device=self.device)
+                self._ingest_event = torch.cuda.Event()
+            main = torch.cuda.current_stream()
+            fence = torch.cuda.Event()
+            fence.record(main)                       # rows about to be overwritten may be in use
+            self._ingest_stream.wait_event(fence)
+            with torch.cuda.stream(self._ingest_stream):
+                self._extend_now(memory, rows)
+                self._ingest_event.record(self._ingest_stream)
+            self._ingest_pending = True
+        else:
+            self._extend_now(memory, rows)
+
+    def _wait_ingest(self):
+        if self._ingest_pending:
+            torch.cuda.current_stream().wait_event(self._ingest_event)
+            self._ingest_pending = False
+
+    def _extend_now(self, memory, rows):
         H = self.cell_size
         src = {
             "state": self._dev(memory["state"], torch.uint8).reshape(rows, -1),
@@ -299,6 +326,7 @@ class ReplayMemory:
         reused by the next call)."""
         B, T, n, H = self.batch_size, self.sequence_length, self.n_step, self.cell_size
         ws = self._workspace(B, T, n, H)
+        self._wait_ingest()
         if seq_index is None:
             if u is None:
                 u = self.draw_uniforms(B)

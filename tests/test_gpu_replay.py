@@ -247,3 +247,29 @@ def test_full_size_gather_roundtrip(cuda_device):
         ws = r.sample_slab(seq_index=seq)
         rows = (seq[:, None] + torch.arange(T + n, device="cuda")[None]) % M
         assert torch.equal(ws["slab"], st[rows]), tma
+
+
+def test_overlapped_extend_is_visible_to_next_draw(cuda_device):
+    """extend(overlap=True) runs on the ingest stream; the following draw/gather must see it."""
+    from pytorch_r2d2_b200 import ReplayMemory
+    M, H = 64, 256
+    rep = RO.ReplayOracle(M, H, 2, 3, 4)
+    g = ReplayMemory(M, 4, 2, cell_size=H)
+    g.burn_in_length, g.learning_length, g.sequence_length = 3, 4, 7
+    rng = np.random.RandomState(3)
+    for rows in (30, 30, 20):
+        dump = RO.alloc_memory(rows, H)
+        dump["state"][:] = rng.randint(0, 256, dump["state"].shape)
+        for k in ("hs_cs", "target_hs_cs", "reward", "priority"):
+            dump[k][:] = rng.randn(*dump[k].shape)
+        dump["sequence_priority"][:] = rng.rand(rows) + 0.1
+        dump["is_seq_start"][:] = (np.arange(rows) % 5 == 0)
+        rep.extend(dump)
+        pinned = {k: torch.from_numpy(v).pin_memory() for k, v in dump.items()}
+        g.extend(pinned, overlap=True)
+        u = rng.rand(4)
+        ws = g.sample_slab(u=torch.from_numpy(u))
+        si = rep.sample_indices(u)
+        assert np.array_equal(ws["seq_index"].cpu().numpy(), si)
+        rows_idx = (si[:, None] + np.arange(9)[None]) % M
+        assert np.array_equal(ws["slab"].cpu().numpy(), rep.memory["state"][rows_idx])
