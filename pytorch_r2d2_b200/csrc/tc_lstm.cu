@@ -349,7 +349,7 @@ struct LstmBwdArgs {
 };
 constexpr int LB_STAGES = 16;
 
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(288, 1)
 tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs a) {
     const int H = a.H, B = a.B, K4 = 4 * a.H, NKB = K4 / 64;
     extern __shared__ uint8_t smem_raw[];
@@ -374,7 +374,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
         }
-        mbar_init(&acc_full, 1);
+        mbar_init(&acc_full, LS_ISSUERS);
         mbar_init(&acc_empty, 128);
         mbar_fence_init();
     }
@@ -389,7 +389,8 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
             make_uint4(ls_pack(v[0], v[1]), ls_pack(v[2], v[3]), ls_pack(v[4], v[5]), ls_pack(v[6], v[7]));
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    if (warp == 1) tmem_alloc(&tmem_slot, 32);
+    if (warp == 1) tmem_alloc(&tmem_slot, 64);                   // LS_ISSUERS slices of 16 columns
+    const int issuer = warp == 1 ? 0 : (warp >= 6 ? warp - 5 : -1);   // MMA warps 1, 6, 7, 8
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -397,7 +398,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
 
     const int q = warp & 3;                                     // readers: warps 2..5
     const int rb = b0 + q * 16 + lane;                          // batch row of this reader thread
-    const bool rvalid = warp >= 2 && lane < 16 && rb < B;
+    const bool rvalid = warp >= 2 && warp < 6 && lane < 16 && rb < B;
     float dc_reg[LS_UNITS];
 #pragma unroll
     for (int j = 0; j < LS_UNITS; ++j) dc_reg[j] = 0.f;
@@ -420,26 +421,31 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
                     tma_load_2d(a_s + (size_t)st * A_TILE, &tma_dg, kb * 64, p * B + b0, &full_bar[st]);
                 }
             }
-        } else if (warp == 1) {
+        } else if (issuer >= 0) {
             if (lane == 0 && s > 0) {
+                // four issuing warps (k-blocks kb % 4 == issuer), private 16-column TMEM slices
                 constexpr uint32_t idesc = umma_idesc_bf16(LS_NB, LS_UNITS);
                 mbar_wait(&acc_empty, s & 1);   // readers drained iteration s-1 (s=1: passes at once)
                 tc_fence_after();
                 const uint64_t db0 = umma_desc_k_sw128(smem_u32(w_s));
                 const uint64_t da0 = umma_desc_k_sw128(smem_u32(a_s));
-                for (int kb = 0; kb < NKB; ++kb, ++it) {
-                    const int st = it % LB_STAGES;
-                    mbar_wait(&full_bar[st], (it / LB_STAGES) & 1);
+                const uint32_t d = tmem_base + issuer * LS_UNITS;
+                const uint32_t it0 = (uint32_t)(s - 1) * NKB;
+                for (int kb = issuer; kb < NKB; kb += LS_ISSUERS) {
+                    const uint32_t itk = it0 + kb;
+                    const int st = itk % LB_STAGES;
+                    mbar_wait(&full_bar[st], (itk / LB_STAGES) & 1);
                     tc_fence_after();
                     const uint64_t aa = da0 + (uint64_t)((st * A_TILE) >> 4);
                     const uint64_t bb = db0 + (uint64_t)((kb * W_KB) >> 4);
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) umma_f16(tmem_base, aa + 2 * k, bb + 2 * k, idesc, (kb | k) != 0);
+                    for (int k = 0; k < 4; ++k)
+                        umma_f16(d, aa + 2 * k, bb + 2 * k, idesc, (kb >= LS_ISSUERS) | (k != 0));
                     umma_commit(&empty_bar[st]);
                 }
                 umma_commit(&acc_full);
             }
-        } else {
+        } else if (warp >= 2 && warp < 6) {
             // ---- readers + gate-gradient math (64 active threads per CTA)
             float rec[LS_UNITS];
 #pragma unroll
@@ -447,13 +453,16 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
             if (s > 0) {
                 mbar_wait(&acc_full, (s - 1) & 1);
                 tc_fence_after();
-                uint32_t r[32];
-                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16), r);
+                uint32_t ra[32], rb2[32];
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16), ra);
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + 32, rb2);
                 tmem_ld_wait();
                 tc_fence_before();
                 mbar_arrive(&acc_empty);
 #pragma unroll
-                for (int j = 0; j < LS_UNITS; ++j) rec[j] = __uint_as_float(r[j]);
+                for (int j = 0; j < LS_UNITS; ++j)
+                    rec[j] = (__uint_as_float(ra[j]) + __uint_as_float(ra[16 + j])) +
+                             (__uint_as_float(rb2[j]) + __uint_as_float(rb2[16 + j]));
             }
             if (rvalid) {
                 const long long o = (long long)rb * H + u0;
@@ -504,7 +513,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 1) tmem_dealloc(tmem_base, 32);
+    if (warp == 1) tmem_dealloc(tmem_base, 64);
 }
 
 typedef CUresult (*EncodeTiledFn2)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
@@ -644,7 +653,7 @@ int r2d2_tc_lstm_seq_bwd(const float* dhs, const float* w_hh, const float* gates
     void* params[] = {&tdg, &a};
     {
         ProfScope ps("tc_lstm_bwd_kernel", st);
-        R2D2_CUDA_OK(cudaLaunchCooperativeKernel((void*)tc_lstm_bwd_kernel, grid, dim3(192), params,
+        R2D2_CUDA_OK(cudaLaunchCooperativeKernel((void*)tc_lstm_bwd_kernel, grid, dim3(288), params,
                                                  (size_t)smem, st));
     }
     return R2D2_OK;
