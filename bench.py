@@ -43,6 +43,8 @@ def parse():
                     help="e2e leg: fresh transitions uploaded from pinned host memory per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--tma-gather", action="store_true")
+    ap.add_argument("--no-cuda-graph", action="store_true",
+                    help="enqueue every kernel from Python instead of replaying the captured step")
     ap.add_argument("--precision", default="bf16", choices=["fp32", "bf16"],
                     help="bf16: tcgen05 tensor-core contractions (2e-2 class); fp32: FFMA (1e-5 class)")
     return ap.parse_args()
@@ -282,6 +284,7 @@ def run_ours(args):
     L.batch_size, L.burn_in_length, L.learning_length, L.bootstrap_steps = B, BI, Ln, n
     L.sequence_length = BI + Ln
     L.replay_memory.use_tma_gather = args.tma_gather
+    L.use_cuda_graph = not args.no_cuda_graph and world == 1
     fill_synthetic(L, args, rank)
     torch.manual_seed(1234 + rank)
 
@@ -312,6 +315,7 @@ def run_ours(args):
     #      (per-kernel durations for the roofline; kept out of `value` because the ~600 event
     #      records per step cost a few percent)
     L.overlap_streams = False            # one stream: per-kernel durations free of co-runners
+    graphed, L.use_cuda_graph = L.use_cuda_graph, False   # eager, so that launches can be bracketed
     L.train()
     torch.cuda.synchronize()
     _lib.prof_report(reset=True)
@@ -320,7 +324,7 @@ def run_ours(args):
         L.train()
     _lib.prof_enable(False)
     prof = _lib.prof_report(reset=True)
-    L.overlap_streams = True
+    L.overlap_streams, L.use_cuda_graph = True, graphed
     clk = clocks.stop() if rank == 0 else None
     t = torch.tensor([ms], device="cuda", dtype=torch.float64)
     if world > 1:
@@ -384,9 +388,18 @@ def run_ours(args):
                           "frac": ach / peaks["hbm_gbs"], "algorithmic_bytes_per_launch": per_launch})
         return r
 
+    # DRAM traffic per launch from the committed `ncu --set full` capture of the same workload
+    traffic = {}
+    tfiles = sorted(f for f in os.listdir(os.path.join(ROOT, "profiles")) if f.endswith("_ncu_traffic.json")) \
+        if os.path.isdir(os.path.join(ROOT, "profiles")) else []
+    if tfiles:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", tfiles[-1])))
     dom_name, (dom_cnt, dom_ms) = top[0]
     roof = roof_of(dom_name, dom_cnt, dom_ms)
-    roof.update({"share_of_serial_step": dom_ms / args.steps / kernel_ms_per_step, "traffic": None,
+    tkey = dom_name if dom_name in traffic else ("tc_gemm_kernel*" if dom_name.startswith("tc_gemm") else None)
+    roof.update({"share_of_serial_step": dom_ms / args.steps / kernel_ms_per_step,
+                 "traffic": traffic[tkey]["dram_bytes_per_launch"] if tkey else None,
+                 "traffic_source": (tfiles[-1] if tkey else None),
                  "peak_source": peaks["src"],
                  "timing": "CUDA events around every launch, single-stream pass of the same K steps"})
     kernels = {k: roof_of(k, c, m) for k, (c, m) in top[:16]}
@@ -415,7 +428,7 @@ def run_ours(args):
         "dtype": "bf16" if args.precision == "bf16" else "f32",
         "data": "synthetic",
         "config": workload_config(args, extra={
-            "precision": args.precision,
+            "precision": args.precision, "cuda_graph": bool(L.use_cuda_graph),
             "replay_slots_per_gpu": args.memory_size, "l2_policy": "inputs larger than L2 "
             "(replay ring >> 126 MB; each step gathers a fresh 154 MB slab)",
             "parallelism": f"dp{world}", "global_batch": world * B,

@@ -196,34 +196,39 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
                     mbar_arrive(&full_bar[s]);
                 }
             } else {
+                // software pipeline: the loads of k-block kb+1 are in flight while k-block kb is
+                // converted and stored (the gather is memory-latency bound)
+                float v[2][4][8];
+                if (half == 0) gather_chunks<T, CIN, KH, HIN, 0>(src, 0, valid, v[0]);
+                else gather_chunks<T, CIN, KH, HIN, 1>(src, 0, valid, v[0]);
 #pragma unroll
-            for (int kb = 0; kb < NKB; ++kb, ++it) {
-                const int s = it % CV_STAGES;
-                mbar_wait(&empty_bar[s], ((it / CV_STAGES) & 1) ^ 1);
-                uint8_t* a_hi = a_s + (size_t)s * STAGE_BYTES;
-                float v[4][8];
-                // ---- issue all loads of this thread's four chunks first (memory-level
-                //      parallelism); `half` is dispatched at compile time so that every patch
-                //      offset folds to an immediate
-                if (half == 0) gather_chunks<T, CIN, KH, HIN, 0>(src, kb, valid, v);
-                else gather_chunks<T, CIN, KH, HIN, 1>(src, kb, valid, v);
-#pragma unroll
-                for (int cc = 0; cc < 4; ++cc) {
-                    const uint32_t off = sw128_off(row, half * 4 + cc);
-                    *reinterpret_cast<uint4*>(a_hi + off) =
-                        make_uint4(pack_bf16x2(v[cc][0], v[cc][1]), pack_bf16x2(v[cc][2], v[cc][3]),
-                                   pack_bf16x2(v[cc][4], v[cc][5]), pack_bf16x2(v[cc][6], v[cc][7]));
-                    if constexpr (NEED_LO) {
-#pragma unroll
-                        for (int e = 0; e < 8; ++e) v[cc][e] -= bf16_round(v[cc][e]);
-                        *reinterpret_cast<uint4*>(a_hi + A_TILE + off) =
-                            make_uint4(pack_bf16x2(v[cc][0], v[cc][1]), pack_bf16x2(v[cc][2], v[cc][3]),
-                                       pack_bf16x2(v[cc][4], v[cc][5]), pack_bf16x2(v[cc][6], v[cc][7]));
+                for (int kb = 0; kb < NKB; ++kb, ++it) {
+                    if (kb + 1 < NKB) {
+                        if (half == 0) gather_chunks<T, CIN, KH, HIN, 0>(src, kb + 1, valid, v[(kb + 1) & 1]);
+                        else gather_chunks<T, CIN, KH, HIN, 1>(src, kb + 1, valid, v[(kb + 1) & 1]);
                     }
+                    const int s = it % CV_STAGES;
+                    mbar_wait(&empty_bar[s], ((it / CV_STAGES) & 1) ^ 1);
+                    uint8_t* a_hi = a_s + (size_t)s * STAGE_BYTES;
+                    float(&vv)[4][8] = v[kb & 1];
+#pragma unroll
+                    for (int cc = 0; cc < 4; ++cc) {
+                        const uint32_t off = sw128_off(row, half * 4 + cc);
+                        *reinterpret_cast<uint4*>(a_hi + off) =
+                            make_uint4(pack_bf16x2(vv[cc][0], vv[cc][1]), pack_bf16x2(vv[cc][2], vv[cc][3]),
+                                       pack_bf16x2(vv[cc][4], vv[cc][5]), pack_bf16x2(vv[cc][6], vv[cc][7]));
+                        if constexpr (NEED_LO) {
+                            float l[8];
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) l[e] = vv[cc][e] - bf16_round(vv[cc][e]);
+                            *reinterpret_cast<uint4*>(a_hi + A_TILE + off) =
+                                make_uint4(pack_bf16x2(l[0], l[1]), pack_bf16x2(l[2], l[3]),
+                                           pack_bf16x2(l[4], l[5]), pack_bf16x2(l[6], l[7]));
+                        }
+                    }
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    mbar_arrive(&full_bar[s]);
                 }
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                mbar_arrive(&full_bar[s]);
-            }
             }
         }
     } else if (warp == MMA_WARP) {
@@ -664,6 +669,176 @@ tc_conv_dgrad_kernel(const float* __restrict__ dz, const float* __restrict__ w,
     if (warp == MMA_WARP) tmem_dealloc(tmem_base, 64);
 }
 
+// Stride-2 layer (conv2: 4x4 kernel, 20x20 <- 9x9), all four output-parity classes in ONE GEMM:
+// the A tile (dZ gathered at (yy-jy, xx-jx), k = (co, jy, jx), K = 128) does not depend on the
+// class, only the weights do, so the classes are concatenated along N: D[(r,yy,xx), (py,px,ci)],
+// N = 128.  One pass over dZ and over the layer's activations (ReLU'), 2x2 output blocks written
+// as float2 -- the per-class version re-read the activations four times (ncu: 226 MB per class).
+__global__ void __launch_bounds__(416, 1)
+tc_conv_dgrad2_kernel(const float* __restrict__ dz, const float* __restrict__ w,
+                      const float* __restrict__ act, float* __restrict__ din, const int R) {
+    constexpr int KH = 4, HIN = 20, HOUT = 9, TAPS = 2, C = 32, NCOL = 128;
+    constexpr int K = C * TAPS * TAPS, NKB = K / 64;             // 128, 2
+    constexpr int G = 10, P = G * G;                              // (yy, xx) grid per frame
+    constexpr uint32_t A_TILE = 128 * 128, W_KB = NCOL * 128;     // B k-block: 128 rows x 128 B
+    constexpr int MMA_WARP = 8;
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t full_bar[CV_STAGES], empty_bar[CV_STAGES], acc_full[2], acc_empty[2];
+    __shared__ uint32_t tmem_slot;
+    const uint32_t raw = smem_u32(smem_raw);
+    uint8_t* base = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
+    uint8_t* w_s = base;
+    uint8_t* a_s = base + NKB * W_KB;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const long long Mtot = (long long)R * P;
+    const int ntiles = (int)((Mtot + 127) / 128);
+
+    if (tid == 0) {
+        for (int s = 0; s < CV_STAGES; ++s) {
+            mbar_init(&full_bar[s], 256);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&acc_full[b], 1);
+            mbar_init(&acc_empty[b], 128);
+        }
+        mbar_fence_init();
+    }
+    // resident B: row n = (py*2+px)*32 + ci, k = (co, jy, jx) -> W[co, ci, py + 2 jy, px + 2 jx]
+    for (int i = tid; i < NCOL * (K / 8); i += blockDim.x) {
+        const int n = i / (K / 8), ch = i - n * (K / 8);
+        const int cls = n >> 5, ci = n & 31, py = cls >> 1, px = cls & 1;
+        float v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const int k = ch * 8 + e;
+            const int co = k >> 2, jy = (k >> 1) & 1, jx = k & 1;
+            v[e] = __ldg(w + ((long long)(co * C + ci) * KH + py + 2 * jy) * KH + px + 2 * jx);
+        }
+        *reinterpret_cast<uint4*>(w_s + (uint32_t)(ch >> 3) * W_KB + sw128_off(n, ch & 7)) =
+            make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
+                       pack_bf16x2(v[6], v[7]));
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    if (warp == MMA_WARP) tmem_alloc(&tmem_slot, 256);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+
+    if (warp < MMA_WARP) {
+        const int row = tid & 127, half = tid >> 7;
+        uint32_t it = 0;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+            const long long m = (long long)tile * 128 + row;
+            const bool valid = m < Mtot;
+            int yy = 0, xx = 0;
+            const float* src = dz;
+            if (valid) {
+                const int r = (int)(m / P), p = (int)(m - (long long)r * P);
+                yy = p / G;
+                xx = p - yy * G;
+                src = dz + (long long)r * C * HOUT * HOUT;
+            }
+            // the four taps of this pixel: validity and offsets once per row
+            int off[4];
+            bool ok[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int oy = yy - (j >> 1), ox = xx - (j & 1);
+                ok[j] = valid && oy >= 0 && oy < HOUT && ox >= 0 && ox < HOUT;
+                off[j] = oy * HOUT + ox;
+            }
+#pragma unroll
+            for (int kb = 0; kb < NKB; ++kb, ++it) {
+                const int s = it % CV_STAGES;
+                mbar_wait(&empty_bar[s], ((it / CV_STAGES) & 1) ^ 1);
+                uint8_t* a_t = a_s + (size_t)s * A_TILE;
+                float v[4][8];
+#pragma unroll
+                for (int cc = 0; cc < 4; ++cc)
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) {
+                        const int co = kb * 16 + half * 8 + cc * 2 + (e >> 2);   // k = co*4 + tap
+                        v[cc][e] = ok[e & 3] ? __ldg(src + co * (HOUT * HOUT) + off[e & 3]) : 0.f;
+                    }
+#pragma unroll
+                for (int cc = 0; cc < 4; ++cc)
+                    *reinterpret_cast<uint4*>(a_t + sw128_off(row, half * 4 + cc)) =
+                        make_uint4(pack_bf16x2(v[cc][0], v[cc][1]), pack_bf16x2(v[cc][2], v[cc][3]),
+                                   pack_bf16x2(v[cc][4], v[cc][5]), pack_bf16x2(v[cc][6], v[cc][7]));
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                mbar_arrive(&full_bar[s]);
+            }
+        }
+    } else if (warp == MMA_WARP) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(128, NCOL);
+            const uint32_t wb = smem_u32(w_s);
+            uint32_t it = 0, tcount = 0;
+            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++tcount) {
+                const uint32_t buf = tcount & 1, use = tcount >> 1;
+                mbar_wait(&acc_empty[buf], (use & 1) ^ 1);
+                tc_fence_after();
+                const uint32_t d = tmem_base + buf * NCOL;
+                for (int kb = 0; kb < NKB; ++kb, ++it) {
+                    const int s = it % CV_STAGES;
+                    mbar_wait(&full_bar[s], (it / CV_STAGES) & 1);
+                    tc_fence_after();
+                    const uint32_t aa = smem_u32(a_s + (size_t)s * A_TILE), bb = wb + kb * W_KB;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        umma_f16(d, umma_desc_k_sw128(aa + k * 32), umma_desc_k_sw128(bb + k * 32), idesc,
+                                 (kb | k) != 0);
+                    umma_commit(&empty_bar[s]);
+                }
+                umma_commit(&acc_full[buf]);
+            }
+        }
+    } else {
+        const int q = warp & 3;
+        uint32_t tcount = 0;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++tcount) {
+            const uint32_t buf = tcount & 1, use = tcount >> 1;
+            mbar_wait(&acc_full[buf], use & 1);
+            tc_fence_after();
+            const long long m = (long long)tile * 128 + q * 32 + lane;
+            const bool valid = m < Mtot;
+            long long o = 0;
+            if (valid) {
+                const int fr = (int)(m / P), p = (int)(m - (long long)fr * P);
+                const int yy = p / G, xx = p - yy * G;
+                o = (long long)fr * C * HIN * HIN + (2 * yy) * HIN + 2 * xx;
+            }
+#pragma unroll
+            for (int py = 0; py < 2; ++py) {
+                uint32_t r0[32], r1[32];                       // px = 0, 1
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + buf * NCOL + (py * 2) * C, r0);
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + buf * NCOL + (py * 2 + 1) * C, r1);
+                tmem_ld_wait();
+                if (py == 1) {
+                    tc_fence_before();
+                    mbar_arrive(&acc_empty[buf]);
+                }
+                if (valid) {
+#pragma unroll
+                    for (int ci = 0; ci < C; ++ci) {
+                        const long long oo = o + (long long)ci * HIN * HIN + py * HIN;
+                        const float2 a = *reinterpret_cast<const float2*>(act + oo);
+                        *reinterpret_cast<float2*>(din + oo) =
+                            make_float2(a.x > 0.f ? __uint_as_float(r0[ci]) : 0.f,
+                                        a.y > 0.f ? __uint_as_float(r1[ci]) : 0.f);
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == MMA_WARP) tmem_dealloc(tmem_base, 256);
+}
+
 template <int KH, int HIN, int HOUT, int STRIDE, int PY, int PX>
 static int launch_tc_dgrad(const char* name, const float* dz, const float* w, const float* act,
                            float* din, int R, cudaStream_t st) {
@@ -720,13 +895,13 @@ int r2d2_tc_conv_dgrad2(const float* dz2, const float* w2, const float* a1, floa
                         void* stream) {
     R2D2_REQUIRE(dz2 && w2 && a1 && dz1 && R > 0, "tc_conv_dgrad2: bad args");
     cudaStream_t st = as_stream(stream);
-    int rc = launch_tc_dgrad<4, 20, 9, 2, 0, 0>("tc_conv2_dgrad", dz2, w2, a1, dz1, R, st);
-    if (rc) return rc;
-    rc = launch_tc_dgrad<4, 20, 9, 2, 0, 1>("tc_conv2_dgrad", dz2, w2, a1, dz1, R, st);
-    if (rc) return rc;
-    rc = launch_tc_dgrad<4, 20, 9, 2, 1, 0>("tc_conv2_dgrad", dz2, w2, a1, dz1, R, st);
-    if (rc) return rc;
-    return launch_tc_dgrad<4, 20, 9, 2, 1, 1>("tc_conv2_dgrad", dz2, w2, a1, dz1, R, st);
+    const int smem = 2 * 128 * 128 + CV_STAGES * 128 * 128 + 1024;
+    R2D2_CUDA_OK(cudaFuncSetAttribute(tc_conv_dgrad2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    const int ntiles = (int)(((long long)R * 100 + 127) / 128);
+    int grid = sm_count();
+    if (grid > ntiles) grid = ntiles;
+    R2D2_LAUNCH("tc_conv2_dgrad", st, tc_conv_dgrad2_kernel<<<grid, 416, smem, st>>>(dz2, w2, a1, dz1, R));
+    return R2D2_OK;
 }
 
 // partial-sum reduction shared with the fp32 path (nn_kernels.cu)

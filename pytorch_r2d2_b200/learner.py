@@ -83,6 +83,11 @@ class Learner:
         # bf16 mode: run the target net's branch on a side stream next to the online net's
         # (False = one stream, e.g. to time kernels in isolation)
         self.overlap_streams = True
+        # capture the whole step (both streams) in a CUDA graph and replay it: removes ~110
+        # launches worth of host work per step.  Only the default path (u drawn from the global
+        # CPU generator, no overrides) is graphed; anything else runs eagerly.
+        self.use_cuda_graph = False
+        self._graph, self._graph_key = None, None
         self.memory_path = os.path.join("./", "logs", "memory")
         # memory (learner.py:34-41)
         self.burn_in_length = 10
@@ -204,6 +209,35 @@ class Learner:
         """One learner step (learner.py:68-104).  `u` optionally supplies the B float64
         uniforms (default: drawn from torch's global CPU generator like the reference's
         multinomial); `seq_index` bypasses the draw (parity tests)."""
+        if (self.use_cuda_graph and u is None and seq_index is None and next_action_override is None
+                and parallel.active_world(self.process_group) == 1):
+            return self._train_graphed()
+        return self._train_eager(u, seq_index, next_action_override)
+
+    def _train_graphed(self):
+        rm = self.replay_memory
+        key = (self.batch_size, self.burn_in_length, self.learning_length, self.bootstrap_steps,
+               self.cell_size, self.precision, self.overlap_streams, id(rm))
+        u_host = rm.draw_uniforms(self.batch_size)          # host RNG + pinned buffer, every step
+        rm._wait_ingest()                                    # cross-stream waits stay outside the graph
+        if self._graph is None or self._graph_key != key:
+            # the captured step always rebuilds the sum-tree first (cheap: M*5 bytes), so that
+            # replays are valid whether or not rows were ingested / poked since the last step
+            rm._tree_dirty = True
+            self._train_eager(u_host, None, None)            # warm-up: allocates every workspace
+            torch.cuda.synchronize()
+            rm._tree_dirty = True
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                loss = self._train_eager(u_host, None, None)
+            self._graph, self._graph_key, self._graph_loss = g, key, loss
+            rm._tree_dirty = False
+            return loss      # the capture pass does not execute; the warm-up step above did
+        self._graph.replay()
+        rm._tree_dirty = False
+        return self._graph_loss
+
+    def _train_eager(self, u=None, seq_index=None, next_action_override=None):
         rm = self.replay_memory
         B, BI, L, n, H = (self.batch_size, self.burn_in_length, self.learning_length,
                           self.bootstrap_steps, self.cell_size)

@@ -371,3 +371,25 @@ def test_full_size_step_properties(cuda_device):
                      raw("sequence_priority").clone()))
     for a, b in zip(outs[0], outs[1]):
         assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_cuda_graph_step_equals_eager(cuda_device, precision):
+    """Replaying the captured step gives the same weights / priorities as enqueueing it."""
+    M, B, BI, LN, NS, H = 96, 8, 3, 4, 2, 256
+    outs = []
+    for graphed in (False, True):
+        rep, _ = make_oracle_replay(M, H, NS, BI, LN, seed=5)
+        from pytorch_r2d2_b200 import Learner
+        torch.manual_seed(3)
+        L = Learner(1, {}, device="cuda:0", cell_size=H, memory_size=M, precision=precision)
+        L.batch_size, L.burn_in_length, L.learning_length, L.bootstrap_steps = B, BI, LN, NS
+        L.replay_memory = mirror_to_gpu(rep, B)
+        L.use_cuda_graph = graphed
+        torch.manual_seed(77)
+        losses = [float(L.train()) for _ in range(4)]
+        torch.cuda.synchronize()
+        outs.append((losses, L.net.flat_parameters().clone(), gpu_mem_np(L.replay_memory, "sequence_priority")))
+    assert outs[0][0] == outs[1][0]
+    assert torch.equal(outs[0][1], outs[1][1])
+    assert np.array_equal(outs[0][2], outs[1][2])
