@@ -15,7 +15,8 @@ from .model import QNet
 
 
 class BatchedActor:
-    def __init__(self, n_actors, device="cuda:0", cell_size=256, net=None, target_net=None):
+    def __init__(self, n_actors, device="cuda:0", cell_size=256, net=None, target_net=None,
+                 precision="fp32"):
         self.gamma = 0.99
         self.bootstrap_steps = 3
         self.alpha = 0.6
@@ -25,8 +26,8 @@ class BatchedActor:
         # epsilon_i = 0.4 ** (1 + 7 i / (N-1))  (actor.py:22; N=1 divides by zero there)
         i = np.arange(n_actors)
         self.epsilon = 0.4 ** (1 + i * 7 / max(n_actors - 1, 1))
-        self.net = net if net is not None else QNet(device, cell_size)
-        self.target_net = target_net if target_net is not None else QNet(device, cell_size)
+        self.net = net if net is not None else QNet(device, cell_size, precision)
+        self.target_net = target_net if target_net is not None else QNet(device, cell_size, precision)
         if target_net is None:
             self.target_net.load_state_dict(self.net.state_dict())
 

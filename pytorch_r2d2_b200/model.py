@@ -48,33 +48,56 @@ class NetStash:
                  "cs_ext", "gates", "hid", "q")
 
 
+def _split(x):
+    pair = torch.empty((2, *x.shape), dtype=torch.bfloat16, device=x.device)
+    engine.split_bf16(x, pair[0], pair[1])
+    return pair
+
+
 def net_forward(w: Weights, T, B, h0, c0, *, slab=None, s0=0, frames=None, want_gates=True,
-                head_from=0, ws=None):
+                head_from=0, ws=None, tc=False):
     """Torso -> input projection -> LSTM unroll -> head on steps [head_from, T).
 
     Frames come either from a u8 slab [B,S,4,84,84] (steps s0..s0+T, /255 fused) or from an f32
-    tensor [T*B,4,84,84].  Returns a NetStash; q covers rows head_from*B .. T*B."""
+    tensor [T*B,4,84,84].  tc=True runs every contraction on tcgen05 tensor cores (compensated
+    bf16x3, fp32-accurate forward).  Returns a NetStash; q covers rows head_from*B .. T*B."""
     dev, H = h0.device, w.H
     R = T * B
     st = NetStash()
     st.frames_u8, st.frames_f32, st.s0, st.T, st.B = slab, frames, s0, T, B
     st.a1, st.a2, st.feat = engine.alloc_torso(R, dev)
     if slab is not None:
-        engine.torso_fwd_u8(slab, s0, T, w, st.a1, st.a2, st.feat)
+        engine.torso_fwd_u8(slab, s0, T, w, st.a1, st.a2, st.feat, tc=tc)
     else:
-        engine.torso_fwd_f32(frames, w, st.a1, st.a2, st.feat)
-    st.xproj = torch.empty((R, 4 * H), device=dev)
-    engine.linear_fwd(st.feat, w.w_ih, w.b_ih, w.b_hh, st.xproj)
+        engine.torso_fwd_f32(frames, w, st.a1, st.a2, st.feat, tc=tc)
     st.hs_ext = torch.empty((T + 1, B, H), device=dev)
     st.cs_ext = torch.empty((T + 1, B, H), device=dev)
     st.hs_ext[0].copy_(h0)
     st.cs_ext[0].copy_(c0)
     st.gates = torch.empty((T, B, 4 * H), device=dev) if want_gates else None
-    engine.lstm_seq_fwd(st.xproj, w.w_hh, st.hs_ext, st.cs_ext, st.gates, T, B, H)
     Mh = (T - head_from) * B
     st.hid = torch.empty((Mh, 2 * H), device=dev)
     st.q = torch.empty((Mh, N_ACTIONS), device=dev)
-    engine.head_fwd(st.hs_ext[1 + head_from:].reshape(Mh, H), w, st.hid, st.q)
+    hs_head = st.hs_ext[1 + head_from:].reshape(Mh, H)
+    if tc:
+        Rp = (R + 3) // 4 * 4                      # tc_linear needs N % 4 == 0 (N = frames here)
+        w16, f16 = _split(w.w_ih), _split(st.feat)
+        st.xproj = torch.empty((4 * H, Rp), device=dev)          # transposed projection
+        if Rp != R:
+            fpad = torch.zeros((2, Rp, f16.shape[2]), dtype=torch.bfloat16, device=dev)
+            fpad[:, :R] = f16
+            f16 = fpad
+        engine.tc_linear_x3(w16[0], w16[1], f16[0], f16[1], w.b_ih, w.b_hh, y32=st.xproj, bias_row=True)
+        scratch = torch.empty(engine.tc_lstm_scratch_bytes(B, H), dtype=torch.uint8, device=dev)
+        engine.tc_lstm_seq_fwd(st.xproj, 0, w.w_hh, st.hs_ext, st.cs_ext, st.gates, T, B, H, scratch)
+        h16, hw16 = _split(hs_head), _split(w.head_w1)
+        engine.tc_linear_x3(h16[0], h16[1], hw16[0], hw16[1], w.head_b1, None, y32=st.hid, relu=True)
+        engine.head_out(st.hid, w, st.q)
+    else:
+        st.xproj = torch.empty((R, 4 * H), device=dev)
+        engine.linear_fwd(st.feat, w.w_ih, w.b_ih, w.b_hh, st.xproj)
+        engine.lstm_seq_fwd(st.xproj, w.w_hh, st.hs_ext, st.cs_ext, st.gates, T, B, H)
+        engine.head_fwd(hs_head, w, st.hid, st.q)
     return st
 
 
@@ -135,8 +158,13 @@ class _QNetFunction(torch.autograd.Function):
 
 
 class QNet(nn.Module):
-    def __init__(self, device="cuda:0", cell_size=256):
+    def __init__(self, device="cuda:0", cell_size=256, precision="fp32"):
         super().__init__()
+        if precision not in ("fp32", "bf16"):
+            raise ValueError("precision must be 'fp32' or 'bf16'")
+        # "bf16": no-grad forwards (actors, target evaluation) run on tensor cores with the
+        # compensated bf16x3 contractions; forwards that need autograd use the fp32 kernels
+        self.precision = precision
         if not torch.cuda.is_available():
             raise RuntimeError("pytorch_r2d2_b200.QNet needs a CUDA device (no CPU fallback)")
         _lib.load()
@@ -207,6 +235,7 @@ class QNet(nn.Module):
         nn.Module.__init__(new)
         src_flat = self.flat_parameters()
         new.device, new.cell_size, new.layout = self.device, self.cell_size, self.layout
+        new.precision = self.precision
         new.hs, new.cs, new._w = None, None, None
         new._flat = src_flat.clone()
         groups = {top: nn.ModuleDict() for top in ("vis_layers", "val", "adv")}
@@ -260,7 +289,8 @@ class QNet(nn.Module):
         if need_grad:
             q, hs_ext, cs_ext = _QNetFunction.apply(self, frames, T, B, h0, c0, *self._named())
         else:
-            st = net_forward(w, T, B, h0, c0, frames=frames, want_gates=False)
+            st = net_forward(w, T, B, h0, c0, frames=frames, want_gates=False,
+                             tc=self.precision == "bf16")
             q, hs_ext, cs_ext = st.q, st.hs_ext, st.cs_ext
         self.hs, self.cs = hs_ext[T], cs_ext[T]
         q_val = q.view(-1, N_ACTIONS) if T > 1 else q

@@ -393,3 +393,30 @@ def test_cuda_graph_step_equals_eager(cuda_device, precision):
     assert outs[0][0] == outs[1][0]
     assert torch.equal(outs[0][1], outs[1][1])
     assert np.array_equal(outs[0][2], outs[1][2])
+
+
+@pytest.mark.parametrize("precision,tol", [("fp32", 1e-5), ("bf16", 1e-5)])
+def test_batched_actor_inference_vs_oracle(cuda_device, precision, tol):
+    """BASELINE config 5 shape in miniature: N actors stepped together (T=1), both nets, hidden
+    state carried per actor across steps == the reference's per-actor batch-1 loop
+    (actor.py:96-106).  The bf16 mode (tensor cores, compensated) stays inside 1e-5 too."""
+    from pytorch_r2d2_b200 import BatchedActor
+    N, H = 37, 256
+    torch.manual_seed(11)
+    act = BatchedActor(N, "cuda:0", H, precision=precision)
+    p = {k: v.cpu().clone() for k, v in act.net.state_dict().items()}
+    rng = np.random.RandomState(4)
+    h = c = th = tc = None
+    for step in range(3):
+        x = torch.from_numpy(rng.randint(0, 256, (N, 4, 84, 84)).astype(np.float32) / np.float32(255))
+        with torch.no_grad():
+            q_ref, _, _, (h, c) = NO.qnet_forward(p, x, h, c)
+            tq_ref, _, _, (th, tc) = NO.qnet_forward(p, x, th, tc)
+        action, q, tq = act.select_action(x.cuda(), rng=np.random.RandomState(step))
+        assert rel_err(q, q_ref) < tol and rel_err(tq, tq_ref) < tol, (step, rel_err(q, q_ref))
+        assert action.shape == (N,) and int(action.min()) >= 0 and int(action.max()) < 6
+    hh, cc = act.net.get_state()
+    assert rel_err(hh, h) < tol and rel_err(cc, c) < tol
+    prio = act.calc_priority(q.cpu().numpy(), action.cpu().numpy(), rng.randn(N).astype(np.float32),
+                             q.cpu().numpy(), tq.cpu().numpy(), rng.rand(N) < 0.2)
+    assert prio.shape == (N,) and np.all(prio > 0)
