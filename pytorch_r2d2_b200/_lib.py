@@ -64,6 +64,7 @@ PROTOTYPES = {
     "r2d2_tc_conv_dgrad2": (_I, [_P, _P, _P, _P, _I, _P]),
     "r2d2_relu_mask": (_I, [_P, _P, _L, _P]),
     "r2d2_chansum": (_I, [_P, _P, _I, _I, _P, _P]),
+    "r2d2_tc_conv_wgrad_layer": (_I, [_I, _P, _I, _I, _I, _I, _P, _P, _P, _P]),
     "r2d2_tc_linear": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "r2d2_tc_linear_x3": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "r2d2_split_bf16": (_I, [_P, _P, _P, _L, _P]),

@@ -936,6 +936,35 @@ int r2d2_tc_torso_wgrad_u8(const uint8_t* slab, int B, int S, int s0, int nt, co
     return r2d2_reduce_partials(part, dw1, 32 * 256, grid, stream);
 }
 
+// one layer at a time (layer = 1, 2, 3), with its own partial buffer, so that the three weight
+// gradients can run on different streams: part needs sm_count * 32 * K floats (K = 256/512/288)
+int r2d2_tc_conv_wgrad_layer(int layer, const void* in, int B, int S, int s0, int nt,
+                             const float* dz, float* dw, float* part, void* stream) {
+    R2D2_REQUIRE(in && dz && dw && part && nt > 0 && B > 0, "tc_conv_wgrad_layer: bad args");
+    cudaStream_t st = as_stream(stream);
+    const int R = B * nt;
+    int grid = 0, rc = 0, K = 0;
+    if (layer == 1) {
+        R2D2_REQUIRE(s0 >= 0 && s0 + nt <= S, "tc_conv_wgrad_layer: bad frame window");
+        K = 256;
+        rc = launch_tc_wgrad<uint8_t, 4, 8, 84, 20, 4, 4>("tc_conv1_wgrad", static_cast<const uint8_t*>(in),
+                                                          FrameMap{B, S, s0, R2D2_FRAME_BYTES}, dz, part, R,
+                                                          1.f / 255.f, &grid, st);
+    } else if (layer == 2) {
+        K = 512;
+        rc = launch_tc_wgrad<float, 32, 4, 20, 9, 2, 3>("tc_conv2_wgrad", static_cast<const float*>(in),
+                                                        FrameMap{0, 0, 0, 12800}, dz, part, R, 1.f, &grid, st);
+    } else if (layer == 3) {
+        K = 288;
+        rc = launch_tc_wgrad<float, 32, 3, 9, 7, 1, 3>("tc_conv3_wgrad", static_cast<const float*>(in),
+                                                       FrameMap{0, 0, 0, 2592}, dz, part, R, 1.f, &grid, st);
+    } else {
+        return set_err(R2D2_EINVAL, "tc_conv_wgrad_layer: layer must be 1, 2 or 3");
+    }
+    if (rc) return rc;
+    return r2d2_reduce_partials(part, dw, 32 * K, grid, stream);
+}
+
 int r2d2_tc_torso_fwd_f32(const float* frames, int R, const float* w1, const float* b1,
                           const float* w2, const float* b2, const float* w3, const float* b3,
                           float* a1, float* a2, float* feat, void* stream) {

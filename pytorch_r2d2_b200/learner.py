@@ -20,7 +20,7 @@ from copy import deepcopy
 import numpy as np
 import torch
 
-from . import engine, parallel
+from . import _lib, engine, parallel
 from .engine import Weights
 from .model import QNet
 from .params import FEAT, N_ACTIONS
@@ -197,7 +197,11 @@ class Learner:
             ws["lstm_scratch"] = torch.empty(engine.tc_lstm_scratch_bytes(B, H), dtype=torch.uint8, device=dev)
             ws["lstm_scratch_tg"] = torch.empty_like(ws["lstm_scratch"])
             ws["lstm_bwd_scratch"] = torch.empty(engine.tc_lstm_bwd_scratch_bytes(B, H), dtype=torch.uint8, device=dev)
+            nsm = int(_lib.load().r2d2_sm_count())
+            ws["wpart"] = [f(nsm * 32 * 256), f(nsm * 32 * 512), f(nsm * 32 * 288)]
+            ws["cpart"] = [f(37 * 32), f(37 * 32), f(37 * 32)]
             ws["side_stream"] = torch.cuda.Stream(device=dev)
+            ws["events"] = [torch.cuda.Event() for _ in range(16)]
             ws["ev_fork"], ws["ev_join"] = torch.cuda.Event(), torch.cuda.Event()
             ws["dhid16"], ws["dhidT16"], ws["hsT16"] = h(M, 2 * H), h(2 * H, M), h(H, M)
             ws["dg16"], ws["dgT16"], ws["hprevT16"], ws["featT16"] = h(M, 4 * H), h(4 * H, M), h(H, M), h(FEAT, M)
@@ -342,55 +346,109 @@ class Learner:
 
         # ---- backward (learn window only; BPTT truncated at the burn-in boundary)
         scratch = ws["scratch"]
-        engine.head_bwd(td["dq"], ws["hid_on"], w, ws["dhid"], g.head_w2, g.head_b2)
         hprev = ws["hs_on"][BI:BI + L].reshape(M, H)
         feat_l = ws["feat_on"][BI * B: T * B]
+        a1_l, a2_l = ws["a1_on"][BI * B: T * B], ws["a2_on"][BI * B: T * B]
         if bf16:
-            # weight gradients: dW = dY^T . X with both operands transposed to [*, M] bf16;
-            # data gradients: dX = dY . W with W transposed to [K_out, N] bf16
-            engine.transpose_cast_bf16(ws["dhid"], ws["dhidT16"])
-            engine.transpose_cast_bf16(hs_learn, ws["hsT16"])
-            engine.tc_linear(ws["dhidT16"], ws["hsT16"], None, None, y32=g.head_w1)
-            engine.colsum(ws["dhid"], g.head_b1)
+            # The data-gradient chain (head -> BPTT -> input projection -> conv) is the critical
+            # path; everything that only CONSUMES a gradient (weight/bias gradients, the priority
+            # update) runs beside it on the side stream.
+            ev = iter(ws["events"])
+            main, side = torch.cuda.current_stream(), ws["side_stream"]
+            overlap_bwd = self.overlap_streams
+
+            def beside(fn):
+                """Run fn() on the side stream after everything enqueued so far on main."""
+                if not overlap_bwd:
+                    return fn()
+                e = next(ev)
+                e.record(main)
+                side.wait_event(e)
+                with torch.cuda.stream(side):
+                    fn()
+
+            def priorities():
+                rm.update_priority_learn_window(batch["seq_index"], td["prio"])
+                rm.update_sequence_priority(batch["seq_index"], True)
+
+            beside(priorities)
+            engine.head_bwd(td["dq"], ws["hid_on"], w, ws["dhid"], g.head_w2, g.head_b2)
+
+            def head_wgrad():     # dW1 = dhid^T . hs  (operands transposed to [*, M] bf16)
+                engine.transpose_cast_bf16(ws["dhid"], ws["dhidT16"])
+                engine.transpose_cast_bf16(hs_learn, ws["hsT16"])
+                engine.tc_linear(ws["dhidT16"], ws["hsT16"], None, None, y32=g.head_w1)
+                engine.colsum(ws["dhid"], g.head_b1)
+
+            beside(head_wgrad)
             engine.cast_bf16(ws["dhid"], ws["dhid16"])
             engine.transpose_cast_bf16(w.head_w1, ws["hw1T16"])
             engine.tc_linear(ws["dhid16"], ws["hw1T16"], None, None, y32=ws["dhs"])
-        else:
-            engine.linear_wgrad(ws["dhid"], hs_learn, g.head_w1, g.head_b1, scratch)
-            engine.linear_dgrad(ws["dhid"], w.head_w1, ws["dhs"])
-        if bf16:
             engine.tc_lstm_seq_bwd(ws["dhs"], w.w_hh, ws["gates"][BI:], ws["cs_on"][BI:], ws["dgates"],
                                    L, B, H, ws["lstm_bwd_scratch"])
-        else:
-            engine.lstm_seq_bwd(ws["dhs"], w.w_hh, ws["gates"][BI:], ws["cs_on"][BI:], ws["dgates"],
-                                ws["dc_work"], L, B, H)
-        if bf16:
-            engine.transpose_cast_bf16(ws["dgates"], ws["dgT16"])
-            engine.transpose_cast_bf16(hprev, ws["hprevT16"])
-            engine.tc_linear(ws["dgT16"], ws["hprevT16"], None, None, y32=g.w_hh)
-            engine.colsum(ws["dgates"], g.b_hh)
-            g.b_ih.copy_(g.b_hh)
-            engine.transpose_cast_bf16(feat_l, ws["featT16"])
-            engine.tc_linear(ws["dgT16"], ws["featT16"], None, None, y32=g.w_ih)
+
+            def lstm_wgrad():
+                engine.transpose_cast_bf16(ws["dgates"], ws["dgT16"])
+                engine.transpose_cast_bf16(hprev, ws["hprevT16"])
+                engine.tc_linear(ws["dgT16"], ws["hprevT16"], None, None, y32=g.w_hh)
+                engine.colsum(ws["dgates"], g.b_hh)
+                g.b_ih.copy_(g.b_hh)
+                engine.transpose_cast_bf16(feat_l, ws["featT16"])
+                engine.tc_linear(ws["dgT16"], ws["featT16"], None, None, y32=g.w_ih)
+
+            beside(lstm_wgrad)
             engine.cast_bf16(ws["dgates"], ws["dg16"])
             engine.transpose_cast_bf16(w.w_ih, ws["w_ihT16"])
             engine.tc_linear(ws["dg16"], ws["w_ihT16"], None, None, y32=ws["dfeat"])
+            # conv torso: scratch = [dz2 | dz1 | ...]; dz3 = dfeat masked in place
+            sc32 = scratch.view(torch.float32)
+            dz2, dz1 = sc32[:M * 2592], sc32[M * 2592: M * (2592 + 12800)]
+            dz3 = ws["dfeat"]
+            P, st = _lib.ptr, _lib.stream_ptr
+            _lib.call("r2d2_relu_mask", P(dz3, "f32"), P(feat_l, "f32"), dz3.numel(), st())
+
+            def conv3_grads():
+                _lib.call("r2d2_chansum", P(dz3, "f32"), P(g.b3), M, 49, P(ws["cpart"][2], "f32"), st())
+                _lib.call("r2d2_tc_conv_wgrad_layer", 3, P(a2_l, "f32"), B, 0, 0, L, P(dz3, "f32"), P(g.w3),
+                          P(ws["wpart"][2], "f32"), st())
+
+            beside(conv3_grads)
+            _lib.call("r2d2_tc_conv_dgrad3", P(dz3, "f32"), P(w.w3), P(a2_l, "f32"), P(dz2, "f32"), M, st())
+
+            def conv2_grads():
+                _lib.call("r2d2_chansum", P(dz2, "f32"), P(g.b2), M, 81, P(ws["cpart"][1], "f32"), st())
+                _lib.call("r2d2_tc_conv_wgrad_layer", 2, P(a1_l, "f32"), B, 0, 0, L, P(dz2, "f32"), P(g.w2),
+                          P(ws["wpart"][1], "f32"), st())
+
+            beside(conv2_grads)
+            _lib.call("r2d2_tc_conv_dgrad2", P(dz2, "f32"), P(w.w2), P(a1_l, "f32"), P(dz1, "f32"), M, st())
+            _lib.call("r2d2_chansum", P(dz1, "f32"), P(g.b1), M, 400, P(ws["cpart"][0], "f32"), st())
+            _lib.call("r2d2_tc_conv_wgrad_layer", 1, P(slab, "u8"), B, T + n, BI, L, P(dz1, "f32"), P(g.w1),
+                      P(ws["wpart"][0], "f32"), st())
+            if overlap_bwd:
+                e = next(ev)
+                e.record(side)
+                main.wait_event(e)
         else:
+            engine.head_bwd(td["dq"], ws["hid_on"], w, ws["dhid"], g.head_w2, g.head_b2)
+            engine.linear_wgrad(ws["dhid"], hs_learn, g.head_w1, g.head_b1, scratch)
+            engine.linear_dgrad(ws["dhid"], w.head_w1, ws["dhs"])
+            engine.lstm_seq_bwd(ws["dhs"], w.w_hh, ws["gates"][BI:], ws["cs_on"][BI:], ws["dgates"],
+                                ws["dc_work"], L, B, H)
             engine.linear_wgrad(ws["dgates"], hprev, g.w_hh, g.b_hh, scratch)
             g.b_ih.copy_(g.b_hh)
             engine.linear_wgrad(ws["dgates"], feat_l, g.w_ih, None, scratch)
             engine.linear_dgrad(ws["dgates"], w.w_ih, ws["dfeat"])
-        (engine.torso_bwd_tc_u8 if bf16 else engine.torso_bwd_u8)(
-            slab, BI, L, ws["a1_on"][BI * B: T * B], ws["a2_on"][BI * B: T * B], feat_l, ws["dfeat"], w, g,
-            scratch)
+            engine.torso_bwd_u8(slab, BI, L, a1_l, a2_l, feat_l, ws["dfeat"], w, g, scratch)
 
         # ---- optimiser (data-parallel: sum gradients over ranks, 1/world folded into K10)
         self.optim.grad_scale = parallel.allreduce_flat_grad(self.optim.grad, self.process_group)
         self.optim.step()
 
-        # ---- priorities (learner.py:102-104)
-        rm.update_priority_learn_window(batch["seq_index"], td["prio"])
-        rm.update_sequence_priority(batch["seq_index"], True)
+        # ---- priorities (learner.py:102-104); the bf16 path already ran them beside the backward
+        if not bf16:
+            rm.update_priority_learn_window(batch["seq_index"], td["prio"])
+            rm.update_sequence_priority(batch["seq_index"], True)
         self.last = dict(loss=td["loss"], q_all=ws["q_all"], q_next_online=ws["qn_on"],
                          q_next_target=ws["qn_tg"], next_action=td["next_action"], y=td["y"],
                          delta=td["delta"], priority=td["prio"], seq_index=batch["seq_index"],
