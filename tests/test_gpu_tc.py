@@ -92,11 +92,14 @@ def test_tc_torso_vs_torch(cuda_device):
     engine.torso_fwd_f32(frames.cuda().contiguous(), w, b1, b2, featb, tc=True)
     assert rel_err(featb, want) < 1e-5
     # many tiles per CTA (exercises the ring / TMEM double buffering across > 148*2 tiles)
-    slab2 = torch.from_numpy(rng.randint(0, 256, (16, 8, 4, 84, 84)).astype(np.uint8)).cuda()
-    c1, c2, f2 = engine.alloc_torso(16 * 8, "cuda")
-    d1, d2, g2 = engine.alloc_torso(16 * 8, "cuda")
-    engine.torso_fwd_u8(slab2, 0, 8, w, c1, c2, f2, tc=True)
-    engine.torso_fwd_u8(slab2, 0, 8, w, d1, d2, g2, tc=False)
+    # (960 frames: every conv layer has several tiles per persistent CTA, which is what exposes
+    #  ring-phase hazards between the four MMA-issuing warps)
+    slab2 = torch.from_numpy(rng.randint(0, 256, (32, 30, 4, 84, 84)).astype(np.uint8)).cuda()
+    c1, c2, f2 = engine.alloc_torso(32 * 30, "cuda")
+    d1, d2, g2 = engine.alloc_torso(32 * 30, "cuda")
+    for _ in range(3):
+        engine.torso_fwd_u8(slab2, 0, 30, w, c1, c2, f2, tc=True)
+    engine.torso_fwd_u8(slab2, 0, 30, w, d1, d2, g2, tc=False)
     assert rel_err(c1, d1) < 1e-5 and rel_err(c2, d2) < 1e-5 and rel_err(f2, g2) < 1e-5
 
 
