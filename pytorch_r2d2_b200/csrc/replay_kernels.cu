@@ -400,10 +400,16 @@ __global__ void update_priority_seq_kernel(float* __restrict__ priority, int64_t
         const int t = (int)(k / B), b = (int)(k % B);
         const int64_t slot = (s_seq[b] + burn_in + t) % M;
         bool later = false;
+        const int64_t base = slot - burn_in % M;        // in (-M, M)
         for (int b2 = 0; b2 < B && !later; ++b2) {
             // smallest t2 >= 0 with (seq[b2]+burn_in+t2) % M == slot; further solutions are
-            // t2 + j*M, all checked while < L (only matters when M < L)
-            for (int64_t t2 = mod_pos(slot - s_seq[b2] - burn_in, M); t2 < L; t2 += M)
+            // t2 + j*M, all checked while < L (only matters when M < L).  All terms are in
+            // [0, M), so the modulo is two conditional adds (a 64-bit % per pair made this
+            // kernel take milliseconds at B = 4096).
+            int64_t t2 = base - s_seq[b2];               // in (-2M, M)
+            if (t2 < 0) t2 += M;
+            if (t2 < 0) t2 += M;
+            for (; t2 < L; t2 += M)
                 if (t2 * B + b2 > k) { later = true; break; }
         }
         if (!later) priority[slot] = p[k];
