@@ -95,8 +95,8 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
     constexpr bool NEED_LO = sizeof(T) != 1;                 // u8 pixels are exact in bf16
     constexpr uint32_t A_TILE = 128 * 128;                   // 128 rows x 64 bf16
     constexpr uint32_t STAGE_BYTES = NEED_LO ? 2 * A_TILE : A_TILE;
-    constexpr uint32_t W_KB = COUT * 128;                    // 32 rows x 64 bf16 per k-block
-    constexpr uint32_t W_BYTES = 2 * NKB * W_KB;             // hi then lo
+    constexpr uint32_t W_KB = COUT * 128;                    // 32 rows x 64 bf16 per k-block and half
+    constexpr uint32_t W_BYTES = 2 * NKB * W_KB;             // per k-block: [hi rows | lo rows]
     constexpr int MMA_WARP = 8;
     extern __shared__ uint8_t smem_raw[];
     __shared__ uint64_t full_bar[CV_STAGES], empty_bar[CV_STAGES], acc_full[2], acc_empty[2];
@@ -104,7 +104,7 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
 
     const uint32_t raw = smem_u32(smem_raw);
     uint8_t* base = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
-    uint8_t* w_s = base;                                     // [hi|lo][NKB][32 x 128 B]
+    uint8_t* w_s = base;                                     // [NKB][hi|lo][32 x 128 B]
     uint8_t* a_s = base + W_BYTES;                           // CV_STAGES x STAGE_BYTES
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -134,15 +134,16 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
             v[e] = x;
             l[e] = x - bf16_round(x);
         }
-        const uint32_t off = (uint32_t)kb * W_KB + sw128_off(co, c);
+        // rows 0..31 of the k-block tile = W_hi, rows 32..63 = W_lo: ONE 64-row K-major operand
+        const uint32_t off = (uint32_t)kb * 2 * W_KB + sw128_off(co, c);
         *reinterpret_cast<uint4*>(w_s + off) = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
                                                          pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
-        *reinterpret_cast<uint4*>(w_s + NKB * W_KB + off) =
+        *reinterpret_cast<uint4*>(w_s + off + W_KB) =
             make_uint4(pack_bf16x2(l[0], l[1]), pack_bf16x2(l[2], l[3]), pack_bf16x2(l[4], l[5]),
                        pack_bf16x2(l[6], l[7]));
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // weights -> tensor-core proxy
-    if (warp == MMA_WARP) tmem_alloc(&tmem_slot, 64);                      // 2 accumulators x 32 columns
+    if (warp == MMA_WARP) tmem_alloc(&tmem_slot, 128);                     // 2 buffers x (32 + 32) columns
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -152,29 +153,34 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
         // ================= producers: thread t -> row (t & 127), chunks 4*(t>>7) .. +3
         const int row = tid & 127, half = tid >> 7;
         uint32_t it = 0;
-        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-            const long long m = (long long)tile * 128 + row;
-            const bool valid = m < Mtot;
-            const T* src = in;                                // any valid address when !valid
-            if (valid) {
-                const int r = (int)(m / P), p = (int)(m - (long long)r * P);
-                const int oy = p / HOUT, ox = p - oy * HOUT;
-                src = in + fm.base(r) + (long long)(oy * STRIDE) * HIN + ox * STRIDE;
-            }
-            if constexpr (sizeof(T) == 1 && KH == 8) {
-                // conv1 on the u8 slab: the gather is memory-latency bound, so issue the loads of
-                // the WHOLE tile row (4 input channels x 4 patch rows of this thread = 32 x 4 B)
-                // before touching the ring, then convert + store k-block by k-block
-                uint32_t rawv[NKB][4][2];
+        if constexpr (sizeof(T) == 1 && KH == 8) {
+            // conv1 on the u8 slab.  The gather is memory-latency bound: all 32 four-byte loads of
+            // a tile row (4 input channels x this thread's 4 patch rows x 8 pixels) are issued
+            // together, and the NEXT tile's loads are issued before the current tile is converted
+            // and stored, so that DRAM latency overlaps the ring traffic of the current tile.
+            auto issue = [&](int tile, uint32_t (&dst)[NKB][4][2]) {
+                const long long m = (long long)tile * 128 + row;
+                const bool valid = tile < ntiles && m < Mtot;
+                const T* src = in;
+                if (valid) {
+                    const int r = (int)(m / P), p = (int)(m - (long long)r * P);
+                    const int oy = p / HOUT, ox = p - oy * HOUT;
+                    src = in + fm.base(r) + (long long)(oy * STRIDE) * HIN + ox * STRIDE;
+                }
 #pragma unroll
                 for (int kb = 0; kb < NKB; ++kb)
 #pragma unroll
                     for (int cc = 0; cc < 4; ++cc) {
                         const uint32_t* q = reinterpret_cast<const uint32_t*>(
                             src + kb * (HIN * HIN) + (half * 4 + cc) * HIN);
-                        rawv[kb][cc][0] = valid ? __ldg(q) : 0u;
-                        rawv[kb][cc][1] = valid ? __ldg(q + 1) : 0u;
+                        dst[kb][cc][0] = valid ? __ldg(q) : 0u;
+                        dst[kb][cc][1] = valid ? __ldg(q + 1) : 0u;
                     }
+            };
+            uint32_t cur[NKB][4][2], nxt[NKB][4][2];
+            issue(blockIdx.x, cur);
+            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+                issue(tile + gridDim.x, nxt);
 #pragma unroll
                 for (int kb = 0; kb < NKB; ++kb, ++it) {
                     const int s = it % CV_STAGES;
@@ -185,8 +191,8 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
                         float v[8];
 #pragma unroll
                         for (int e = 0; e < 4; ++e) {
-                            v[e] = __uint_as_float(__byte_perm(rawv[kb][cc][0], 0x4B000000u, 0x7650u | e)) - 8388608.f;
-                            v[4 + e] = __uint_as_float(__byte_perm(rawv[kb][cc][1], 0x4B000000u, 0x7650u | e)) - 8388608.f;
+                            v[e] = __uint_as_float(__byte_perm(cur[kb][cc][0], 0x4B000000u, 0x7650u | e)) - 8388608.f;
+                            v[4 + e] = __uint_as_float(__byte_perm(cur[kb][cc][1], 0x4B000000u, 0x7650u | e)) - 8388608.f;
                         }
                         *reinterpret_cast<uint4*>(a_hi + sw128_off(row, half * 4 + cc)) =
                             make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
@@ -195,7 +201,25 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
                     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                     mbar_arrive(&full_bar[s]);
                 }
-            } else {
+#pragma unroll
+                for (int kb = 0; kb < NKB; ++kb)
+#pragma unroll
+                    for (int cc = 0; cc < 4; ++cc) {
+                        cur[kb][cc][0] = nxt[kb][cc][0];
+                        cur[kb][cc][1] = nxt[kb][cc][1];
+                    }
+            }
+        } else {
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+            const long long m = (long long)tile * 128 + row;
+            const bool valid = m < Mtot;
+            const T* src = in;                                // any valid address when !valid
+            if (valid) {
+                const int r = (int)(m / P), p = (int)(m - (long long)r * P);
+                const int oy = p / HOUT, ox = p - oy * HOUT;
+                src = in + fm.base(r) + (long long)(oy * STRIDE) * HIN + ox * STRIDE;
+            }
+            {
                 // software pipeline: the loads of k-block kb+1 are in flight while k-block kb is
                 // converted and stored (the gather is memory-latency bound)
                 float v[2][4][8];
@@ -231,32 +255,35 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
                 }
             }
         }
+        }
     } else if (warp == MMA_WARP) {
         // ================= MMA issuer
         if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_bf16(128, COUT);
-            const uint32_t w_hi = smem_u32(w_s), w_lo = w_hi + NKB * W_KB;
+            // The tensor pipe spends ~44 cycles on an MMA this small whatever its N, and one thread
+            // issues one every ~37 ns, so the count matters: A_hi multiplies both W_hi and W_lo,
+            // hence ONE MMA with N = 64 against the stacked [W_hi ; W_lo] rows (columns 0-31 and
+            // 32-63 of the accumulator, added in the epilogue) instead of two with N = 32.
+            constexpr uint32_t idesc64 = umma_idesc_bf16(128, 2 * COUT), idesc32 = umma_idesc_bf16(128, COUT);
+            const uint32_t wb = smem_u32(w_s);
             uint32_t it = 0, tcount = 0;
             for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++tcount) {
                 const uint32_t buf = tcount & 1, use = tcount >> 1;
                 mbar_wait(&acc_empty[buf], (use & 1) ^ 1);           // epilogue drained this buffer
                 tc_fence_after();
-                const uint32_t d = tmem_base + buf * COUT;
+                const uint32_t d = tmem_base + buf * 2 * COUT;
                 for (int kb = 0; kb < NKB; ++kb, ++it) {
                     const int s = it % CV_STAGES;
                     mbar_wait(&full_bar[s], (it / CV_STAGES) & 1);
                     tc_fence_after();
                     const uint32_t a_hi = smem_u32(a_s + (size_t)s * STAGE_BYTES), a_lo = a_hi + A_TILE;
-                    const uint32_t b_hi = w_hi + kb * W_KB, b_lo = w_lo + kb * W_KB;
+                    const uint32_t b_hl = wb + kb * 2 * W_KB;        // [W_hi ; W_lo] of this k-block
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {
-                        umma_f16(d, umma_desc_k_sw128(a_hi + k * 32), umma_desc_k_sw128(b_hi + k * 32),
-                                 idesc, (kb | k) != 0);
-                        umma_f16(d, umma_desc_k_sw128(a_hi + k * 32), umma_desc_k_sw128(b_lo + k * 32),
-                                 idesc, 1);
+                        umma_f16(d, umma_desc_k_sw128(a_hi + k * 32), umma_desc_k_sw128(b_hl + k * 32),
+                                 idesc64, (kb | k) != 0);
                         if (NEED_LO)
                             umma_f16(d, umma_desc_k_sw128(a_lo + k * 32),
-                                     umma_desc_k_sw128(b_hi + k * 32), idesc, 1);
+                                     umma_desc_k_sw128(b_hl + k * 32), idesc32, 1);
                     }
                     umma_commit(&empty_bar[s]);
                 }
@@ -271,9 +298,12 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
             const uint32_t buf = tcount & 1, use = tcount >> 1;
             mbar_wait(&acc_full[buf], use & 1);
             tc_fence_after();
-            uint32_t r[32];
-            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + buf * COUT, r);
+            uint32_t r[32], r2[32];
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + buf * 2 * COUT, r);
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + buf * 2 * COUT + COUT, r2);
             tmem_ld_wait();
+#pragma unroll
+            for (int c = 0; c < 32; ++c) r[c] = __float_as_uint(__uint_as_float(r[c]) + __uint_as_float(r2[c]));
             tc_fence_before();
             mbar_arrive(&acc_empty[buf]);
             const long long m = (long long)tile * 128 + q * 32 + lane;
@@ -288,7 +318,7 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == MMA_WARP) tmem_dealloc(tmem_base, 64);
+    if (warp == MMA_WARP) tmem_dealloc(tmem_base, 128);
 }
 
 template <class T, int CIN, int KH, int HIN, int HOUT, int STRIDE>

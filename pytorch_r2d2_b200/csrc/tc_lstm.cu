@@ -106,6 +106,11 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
                    const LstmArgs a) {
     constexpr int STAGES = 256 / NB;                            // 64 -> 4, 32 -> 8 (whole h in flight)
     constexpr int UPT = LS_UNITS * NB / 256;                    // hidden units per pointwise thread
+    // W_hi multiplies both h_hi and h_lo: with NB = 32 they are ONE MMA of N = 64 against the
+    // adjacent [h_hi ; h_lo] tiles of a stage (2 MMAs per k-step instead of 3; the tensor pipe and
+    // the issuing thread pay per instruction at these sizes).  Slice = SW accumulator columns.
+    constexpr bool CAT = NB == 32;
+    constexpr int SW = CAT ? 2 * NB : NB;
     static_assert(NB == 64 || NB == 32, "batch tile must be 32 or 64");
     const int H = a.H, B = a.B, NKB = H / 64;
     extern __shared__ uint8_t smem_raw[];
@@ -155,7 +160,7 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
             make_uint4(ls_pack(l[0], l[1]), ls_pack(l[2], l[3]), ls_pack(l[4], l[5]), ls_pack(l[6], l[7]));
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    if (warp == 1) tmem_alloc(&tmem_slot, LS_ISSUERS * NB);   // one accumulator slice per issuer
+    if (warp == 1) tmem_alloc(&tmem_slot, LS_ISSUERS * SW);   // one accumulator slice per issuer
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -216,13 +221,13 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
                 // Four issuing warps, k-blocks kb % 4 == issuer, each accumulating into its own
                 // TMEM slice (the readers add the slices): issuing the 12*NKB small MMAs of a step
                 // from one thread was the critical path (37 ns per MMA, tools/diag_lstm.py).
-                constexpr uint32_t idesc = umma_idesc_bf16(LS_ROWS, NB);
+                constexpr uint32_t idesc = umma_idesc_bf16(LS_ROWS, NB), idesc2 = umma_idesc_bf16(LS_ROWS, 2 * NB);
                 mbar_wait(&acc_empty, (t & 1) ^ 1);                // readers drained step t-1
                 tc_fence_after();
                 const uint64_t dw_hi = umma_desc_k_sw128(smem_u32(w_s));
                 const uint64_t dw_lo = dw_hi + (uint64_t)((NKB * W_KB) >> 4);
                 const uint64_t dh0 = umma_desc_k_sw128(smem_u32(h_s));
-                const uint32_t d = tmem_base + issuer * NB;
+                const uint32_t d = tmem_base + issuer * SW;
                 const uint32_t it0 = (uint32_t)t * NKB;             // ring position of k-block 0
                 for (int kb = issuer; kb < NKB; kb += LS_ISSUERS) {
                     const uint32_t itk = it0 + kb;
@@ -234,9 +239,14 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
                     const uint64_t wlo = dw_lo + (uint64_t)((kb * W_KB) >> 4);
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {
-                        umma_f16(d, whi + 2 * k, hhi + 2 * k, idesc, (kb >= LS_ISSUERS) | (k != 0));
-                        umma_f16(d, wlo + 2 * k, hhi + 2 * k, idesc, 1);
-                        umma_f16(d, whi + 2 * k, hlo + 2 * k, idesc, 1);
+                        if constexpr (CAT) {
+                            umma_f16(d, whi + 2 * k, hhi + 2 * k, idesc2, (kb >= LS_ISSUERS) | (k != 0));
+                            umma_f16(d, wlo + 2 * k, hhi + 2 * k, idesc, 1);
+                        } else {
+                            umma_f16(d, whi + 2 * k, hhi + 2 * k, idesc, (kb >= LS_ISSUERS) | (k != 0));
+                            umma_f16(d, wlo + 2 * k, hhi + 2 * k, idesc, 1);
+                            umma_f16(d, whi + 2 * k, hlo + 2 * k, idesc, 1);
+                        }
                     }
                     umma_commit(&empty_bar[s]);
                     if (issuer == 0) LS_STAMP(16 + kb);
@@ -269,12 +279,12 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
                 for (int i = 0; i < LS_ISSUERS; ++i) {
                     if (i < nslices) {
 #pragma unroll
-                        for (int c = 0; c < NB; c += 32) {
+                        for (int c = 0; c < SW; c += 32) {
                             uint32_t r[32];
-                            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + i * NB + c, r);
+                            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + i * SW + c, r);
                             tmem_ld_wait();
 #pragma unroll
-                            for (int j = 0; j < 32; ++j) acc[c + j] += __uint_as_float(r[j]);
+                            for (int j = 0; j < 32; ++j) acc[(c + j) % NB] += __uint_as_float(r[j]);
                         }
                     }
                 }
@@ -325,7 +335,7 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 1) tmem_dealloc(tmem_base, LS_ISSUERS * NB);
+    if (warp == 1) tmem_dealloc(tmem_base, LS_ISSUERS * SW);
 }
 
 // ------------------------------------------------------------------------------------------
