@@ -284,6 +284,8 @@ def run_ours(args):
     L.batch_size, L.burn_in_length, L.learning_length, L.bootstrap_steps = B, BI, Ln, n
     L.sequence_length = BI + Ln
     L.replay_memory.use_tma_gather = args.tma_gather
+    # world > 1: the step is enqueued eagerly (capturing the NCCL all-reduce together with the
+    # cooperative LSTM launches hung in testing; the eager step time is the same)
     L.use_cuda_graph = not args.no_cuda_graph and world == 1
     fill_synthetic(L, args, rank)
     torch.manual_seed(1234 + rank)

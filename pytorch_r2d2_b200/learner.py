@@ -87,6 +87,9 @@ class Learner:
         # launches worth of host work per step.  Only the default path (u drawn from the global
         # CPU generator, no overrides) is graphed; anything else runs eagerly.
         self.use_cuda_graph = False
+        # also capture the NCCL gradient all-reduce (world > 1).  EXPERIMENTAL and off: capturing it
+        # next to the cooperative LSTM launches hung on 2 GPUs; multi-GPU steps run eagerly.
+        self.graph_collectives = False
         self._graph, self._graph_key = None, None
         self.memory_path = os.path.join("./", "logs", "memory")
         # memory (learner.py:34-41)
@@ -214,7 +217,7 @@ class Learner:
         uniforms (default: drawn from torch's global CPU generator like the reference's
         multinomial); `seq_index` bypasses the draw (parity tests)."""
         if (self.use_cuda_graph and u is None and seq_index is None and next_action_override is None
-                and parallel.active_world(self.process_group) == 1):
+                and (parallel.active_world(self.process_group) == 1 or self.graph_collectives)):
             return self._train_graphed()
         return self._train_eager(u, seq_index, next_action_override)
 
