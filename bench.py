@@ -340,8 +340,8 @@ def run_ours(args):
     dump = make_host_dump(rows, H)
     h2d = sum(v.numel() * v.element_size() for v in dump.values()) + B * 8
     for _ in range(2):
-        L.replay_memory.extend(dump, overlap=True)
         float(L.train().item())
+        L.replay_memory.extend(dump, overlap=True)
     barrier()
     # every step: upload fresh experience from pinned host memory (ingest stream), run the step,
     # copy its loss to pinned host memory (D2H) -- the host READS loss k-1 while step k runs, the
@@ -351,8 +351,8 @@ def run_ours(args):
     losses = []
     t0 = time.perf_counter()
     for i in range(args.steps):
-        L.replay_memory.extend(dump, overlap=True)
-        loss = L.train()
+        loss = L.train()                                  # lands the dump staged during step i-1
+        L.replay_memory.extend(dump, overlap=True)        # H2D of the next dump overlaps step i
         loss_pin[i & 1].copy_(loss, non_blocking=True)
         loss_ev[i & 1].record()
         if i > 0:

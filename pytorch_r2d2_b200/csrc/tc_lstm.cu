@@ -359,6 +359,9 @@ struct LstmBwdArgs {
 };
 constexpr int LB_STAGES = 16;
 
+// NB = batch rows per CTA (32 or 64); the UMMA is always M = 64, with NB = 32 the upper half of
+// the A tile is never filled and its accumulator rows are ignored (rows are independent).
+template <int NB>
 __global__ void __launch_bounds__(288, 1)
 tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs a) {
     const int H = a.H, B = a.B, K4 = 4 * a.H, NKB = K4 / 64;
@@ -373,7 +376,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
     uint8_t* a_s = base + (size_t)NKB * W_KB;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int u0 = blockIdx.x * LS_UNITS, b0 = blockIdx.y * LS_NB;
+    const int u0 = blockIdx.x * LS_UNITS, b0 = blockIdx.y * NB;
     const int ncta = gridDim.x;
     int* counter = a.counter + blockIdx.y;
     const long long BH = (long long)B * H, BG = (long long)B * K4;
@@ -408,7 +411,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
 
     const int q = warp & 3;                                     // readers: warps 2..5
     const int rb = b0 + q * 16 + lane;                          // batch row of this reader thread
-    const bool rvalid = warp >= 2 && warp < 6 && lane < 16 && rb < B;
+    const bool rvalid = warp >= 2 && warp < 6 && lane < 16 && q * 16 < NB && rb < B;
     float dc_reg[LS_UNITS];
 #pragma unroll
     for (int j = 0; j < LS_UNITS; ++j) dc_reg[j] = 0.f;
@@ -427,7 +430,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
                 for (int kb = 0; kb < NKB; ++kb, ++it) {
                     const int st = it % LB_STAGES;
                     mbar_wait(&empty_bar[st], ((it / LB_STAGES) & 1) ^ 1);
-                    mbar_expect_tx(&full_bar[st], A_TILE);
+                    mbar_expect_tx(&full_bar[st], NB * 128);
                     tma_load_2d(a_s + (size_t)st * A_TILE, &tma_dg, kb * 64, p * B + b0, &full_bar[st]);
                 }
             }
@@ -456,7 +459,23 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
                 umma_commit(&acc_full);
             }
         } else if (warp >= 2 && warp < 6) {
-            // ---- readers + gate-gradient math (64 active threads per CTA)
+            // ---- readers + gate-gradient math (64 active threads per CTA).  Everything that does
+            //      not depend on the recurrent term is loaded BEFORE waiting for the accumulator.
+            float gi[16], gf[16], gg[16], go[16], ct[16], cp[16], dh[16];
+            const long long o = (long long)rb * H + u0;
+            if (rvalid) {
+                const float* gp = a.gates + ((long long)t * B + rb) * K4 + u0;
+#pragma unroll
+                for (int j = 0; j < 16; j += 4) {
+                    *reinterpret_cast<float4*>(gi + j) = __ldg(reinterpret_cast<const float4*>(gp + j));
+                    *reinterpret_cast<float4*>(gf + j) = __ldg(reinterpret_cast<const float4*>(gp + H + j));
+                    *reinterpret_cast<float4*>(gg + j) = __ldg(reinterpret_cast<const float4*>(gp + 2 * H + j));
+                    *reinterpret_cast<float4*>(go + j) = __ldg(reinterpret_cast<const float4*>(gp + 3 * H + j));
+                    *reinterpret_cast<float4*>(ct + j) = __ldg(reinterpret_cast<const float4*>(a.cs_ext + (long long)(t + 1) * BH + o + j));
+                    *reinterpret_cast<float4*>(cp + j) = __ldg(reinterpret_cast<const float4*>(a.cs_ext + (long long)t * BH + o + j));
+                    *reinterpret_cast<float4*>(dh + j) = __ldg(reinterpret_cast<const float4*>(a.dhs + (long long)t * BH + o + j));
+                }
+            }
             float rec[LS_UNITS];
 #pragma unroll
             for (int j = 0; j < LS_UNITS; ++j) rec[j] = 0.f;
@@ -475,21 +494,8 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
                              (__uint_as_float(rb2[j]) + __uint_as_float(rb2[16 + j]));
             }
             if (rvalid) {
-                const long long o = (long long)rb * H + u0;
-                const float* gp = a.gates + ((long long)t * B + rb) * K4 + u0;
                 float* dgp = a.dgates + ((long long)t * B + rb) * K4 + u0;
                 __nv_bfloat16* d16 = a.dg16 + (long long)(s & 1) * BG + (long long)rb * K4 + u0;
-                float gi[16], gf[16], gg[16], go[16], ct[16], cp[16], dh[16];
-#pragma unroll
-                for (int j = 0; j < 16; j += 4) {
-                    *reinterpret_cast<float4*>(gi + j) = *reinterpret_cast<const float4*>(gp + j);
-                    *reinterpret_cast<float4*>(gf + j) = *reinterpret_cast<const float4*>(gp + H + j);
-                    *reinterpret_cast<float4*>(gg + j) = *reinterpret_cast<const float4*>(gp + 2 * H + j);
-                    *reinterpret_cast<float4*>(go + j) = *reinterpret_cast<const float4*>(gp + 3 * H + j);
-                    *reinterpret_cast<float4*>(ct + j) = *reinterpret_cast<const float4*>(a.cs_ext + (long long)(t + 1) * BH + o + j);
-                    *reinterpret_cast<float4*>(cp + j) = *reinterpret_cast<const float4*>(a.cs_ext + (long long)t * BH + o + j);
-                    *reinterpret_cast<float4*>(dh + j) = *reinterpret_cast<const float4*>(a.dhs + (long long)t * BH + o + j);
-                }
                 float di[16], df[16], dg[16], dov[16];
 #pragma unroll
                 for (int j = 0; j < 16; ++j) {
@@ -649,22 +655,24 @@ int r2d2_tc_lstm_seq_bwd(const float* dhs, const float* w_hh, const float* gates
     a.dg16 = reinterpret_cast<__nv_bfloat16*>(sc);
     a.counter = reinterpret_cast<int*>(sc + dg16);
     a.T = T; a.B = B; a.H = H;
-    const int groups = (B + LS_NB - 1) / LS_NB;
+    int nb = 32;
+    if ((H / LS_UNITS) * ((B + 31) / 32) > sm_count()) nb = 64;
+    const int groups = (B + nb - 1) / nb;
     R2D2_REQUIRE(groups <= 64, "tc_lstm_seq_bwd: batch too large");
     R2D2_CUDA_OK(cudaMemsetAsync(a.counter, 0, 256, st));
     CUtensorMap tdg;
-    int rc = make_h_tmap(&tdg, a.dg16, 2ll * B, 4ll * H);
+    int rc = make_h_tmap(&tdg, a.dg16, 2ll * B, 4ll * H, nb);
     if (rc) return rc;
     const int NKB = 4 * H / 64;
     const int smem = NKB * LS_UNITS * 128 + LB_STAGES * LS_NB * 128 + 1024;
-    R2D2_CUDA_OK(cudaFuncSetAttribute(tc_lstm_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    void* kern = nb == 32 ? (void*)tc_lstm_bwd_kernel<32> : (void*)tc_lstm_bwd_kernel<64>;
+    R2D2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     dim3 grid(H / LS_UNITS, groups);
     R2D2_REQUIRE((int)(grid.x * grid.y) <= sm_count(), "tc_lstm_seq_bwd: %d CTAs must be co-resident", grid.x * grid.y);
     void* params[] = {&tdg, &a};
     {
         ProfScope ps("tc_lstm_bwd_kernel", st);
-        R2D2_CUDA_OK(cudaLaunchCooperativeKernel((void*)tc_lstm_bwd_kernel, grid, dim3(288), params,
-                                                 (size_t)smem, st));
+        R2D2_CUDA_OK(cudaLaunchCooperativeKernel(kern, grid, dim3(288), params, (size_t)smem, st));
     }
     return R2D2_OK;
 }

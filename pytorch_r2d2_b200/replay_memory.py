@@ -94,7 +94,7 @@ class ReplayMemory:
         _, _, total = tree_layout(M)
         self._nodes = torch.zeros(total, dtype=torch.float64, device=dev)
         self._tree_dirty = True
-        self._ingest_stream, self._ingest_event, self._ingest_pending = None, None, False
+        self._ingest_stream, self._pending, self._stage, self._stage_turn = None, [], {}, 0
         self._u_host = None      # pinned staging for the uniforms
         self._ws = {}            # sample workspaces keyed by shape
         self._touched = None
@@ -124,60 +124,82 @@ class ReplayMemory:
         return t.to(device=self.device, dtype=dtype, non_blocking=True).contiguous()
 
     # ------------------------------------------------------------------ write path
+    _DT = {"state": "u8", "hs_cs": "f32", "target_hs_cs": "f32", "action": "i8", "reward": "f32",
+           "done": "f32", "stack_count": "i8", "priority": "f32", "sequence_priority": "f32",
+           "is_seq_start": "u8"}
+
+    def _staging(self, rows, slot):
+        """Persistent device staging buffers (two sets, ping-pong) for overlapped ingest."""
+        key = (rows, slot)
+        st = self._stage.get(key)
+        if st is None:
+            H, dev = self.cell_size, self.device
+            st = {
+                "state": torch.empty((rows, 28224), dtype=torch.uint8, device=dev),
+                "hs_cs": torch.empty((rows, 2 * H), device=dev),
+                "target_hs_cs": torch.empty((rows, 2 * H), device=dev),
+                "action": torch.empty(rows, dtype=torch.int8, device=dev),
+                "reward": torch.empty(rows, device=dev), "done": torch.empty(rows, device=dev),
+                "stack_count": torch.empty(rows, dtype=torch.int8, device=dev),
+                "priority": torch.empty(rows, device=dev),
+                "sequence_priority": torch.empty(rows, device=dev),
+                "is_seq_start": torch.empty(rows, dtype=torch.uint8, device=dev),
+                "free": torch.cuda.Event(), "ready": torch.cuda.Event(),
+            }
+            st["free"].record(torch.cuda.current_stream())
+            self._stage[key] = st
+        return st
+
     def extend(self, memory, overlap=False):
         """Bulk-append an actor dump (replay_memory.py:107-119): all ten keys, ring wrap.
 
-        overlap=True enqueues the host->device copies and the scatter kernel on a dedicated
-        ingest stream so that they run next to the learner's kernels; the next draw waits for
-        them (an event), so a step always sees every dump appended before it was called."""
+        overlap=True splits the append in two: the host->device copies go to a private staging
+        buffer on a dedicated ingest stream (they overlap whatever the learner is running and
+        touch nothing it reads); the scatter from staging into the ring (an HBM-speed kernel) is
+        enqueued on the caller's stream right before the next draw.  A draw therefore always
+        sees every dump appended before it, and rows are never overwritten under a running
+        gather."""
         rows = int(memory["state"].shape[0])
         if rows == 0:
             return
         if rows > self.memory_size:
             raise ValueError("dump larger than the ring")
-        if overlap:
+        if not overlap:
+            self._wait_ingest()
+            src = {k: self._dev(memory[k], _lib._DT[self._DT[k]]).reshape(rows, -1) if k in
+                   ("state", "hs_cs", "target_hs_cs") else self._dev(memory[k], _lib._DT[self._DT[k]]).reshape(rows)
+                   for k in KEYS}
+            self._scatter(src, rows, self.index % self.memory_size)
+        else:
             if self._ingest_stream is None:
                 self._ingest_stream = torch.cuda.Stream(device=self.device)
-                self._ingest_event = torch.cuda.Event()
-            main = torch.cuda.current_stream()
-            fence = torch.cuda.Event()
-            fence.record(main)                       # rows about to be overwritten may be in use
-            self._ingest_stream.wait_event(fence)
+            st = self._staging(rows, self._stage_turn)
+            self._stage_turn ^= 1
             with torch.cuda.stream(self._ingest_stream):
-                self._extend_now(memory, rows)
-                self._ingest_event.record(self._ingest_stream)
-            self._ingest_pending = True
-        else:
-            self._extend_now(memory, rows)
-
-    def _wait_ingest(self):
-        if self._ingest_pending:
-            torch.cuda.current_stream().wait_event(self._ingest_event)
-            self._ingest_pending = False
-
-    def _extend_now(self, memory, rows):
-        H = self.cell_size
-        src = {
-            "state": self._dev(memory["state"], torch.uint8).reshape(rows, -1),
-            "hs_cs": self._dev(memory["hs_cs"], torch.float32).reshape(rows, 2 * H),
-            "target_hs_cs": self._dev(memory["target_hs_cs"], torch.float32).reshape(rows, 2 * H),
-            "action": self._dev(memory["action"], torch.int8).reshape(rows),
-            "reward": self._dev(memory["reward"], torch.float32).reshape(rows),
-            "done": self._dev(memory["done"], torch.float32).reshape(rows),
-            "stack_count": self._dev(memory["stack_count"], torch.int8).reshape(rows),
-            "priority": self._dev(memory["priority"], torch.float32).reshape(rows),
-            "sequence_priority": self._dev(memory["sequence_priority"], torch.float32).reshape(rows),
-            "is_seq_start": self._dev(memory["is_seq_start"], torch.uint8).reshape(rows),
-        }
-        dt = {"state": "u8", "hs_cs": "f32", "target_hs_cs": "f32", "action": "i8", "reward": "f32",
-              "done": "f32", "stack_count": "i8", "priority": "f32", "sequence_priority": "f32",
-              "is_seq_start": "u8"}
-        args = [_lib.ptr(src[k], dt[k]) for k in KEYS] + [rows] + \
-               [_lib.ptr(self._raw(k), dt[k]) for k in KEYS] + \
-               [self.memory_size, H, self.index % self.memory_size, _lib.stream_ptr()]
-        _lib.call("r2d2_replay_ingest", *args)
+                self._ingest_stream.wait_event(st["free"])     # previous scatter out of this set done
+                for k in KEYS:
+                    srcv = memory[k] if torch.is_tensor(memory[k]) else torch.as_tensor(np.asarray(memory[k]))
+                    st[k].copy_(srcv.reshape(st[k].shape), non_blocking=True)
+                st["ready"].record(self._ingest_stream)
+            self._pending.append((st, rows, self.index % self.memory_size))
         self.index += rows
         self._tree_dirty = True
+
+    def _scatter(self, src, rows, write_index):
+        args = [_lib.ptr(src[k], self._DT[k]) for k in KEYS] + [rows] + \
+               [_lib.ptr(self._raw(k), self._DT[k]) for k in KEYS] + \
+               [self.memory_size, self.cell_size, write_index, _lib.stream_ptr()]
+        _lib.call("r2d2_replay_ingest", *args)
+
+    def _wait_ingest(self):
+        """Land every staged dump in the ring (on the current stream, in append order)."""
+        if self._pending:
+            cur = torch.cuda.current_stream()
+            for st, rows, widx in self._pending:
+                cur.wait_event(st["ready"])
+                self._scatter(st, rows, widx)
+                st["free"].record(cur)
+            self._pending = []
 
     def add(self, state, hs, cs, target_hs, target_cs, action, reward, done, stack_count, priority):
         """One transition (replay_memory.py:93-105).  `state` is a float frame block in [0,1];
