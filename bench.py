@@ -303,7 +303,7 @@ def run_ours(args):
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
-    launches0 = _lib.launch_count()
+    launches0, replays0 = _lib.launch_count(), L.graph_replays
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     ev0.record()
@@ -312,7 +312,9 @@ def run_ours(args):
     ev1.record()
     barrier()
     ms = ev0.elapsed_time(ev1)
-    launches = _lib.launch_count() - launches0
+    # kernels of this library launched inside the timed region: the ones that went through the
+    # C entry points plus, for CUDA-graph replays, the kernel nodes counted at capture
+    launches = (_lib.launch_count() - launches0) + (L.graph_replays - replays0) * L.graph_kernel_nodes
     # ---- same K steps again with every kernel launch bracketed by CUDA events on its stream
     #      (per-kernel durations for the roofline; kept out of `value` because the ~600 event
     #      records per step cost a few percent)

@@ -44,6 +44,10 @@ long long r2d2_launch_count(void);
  * "name count total_ms" line per kernel into buf. */
 int r2d2_prof_enable(int on);
 int r2d2_prof_report(char* buf, int buflen, int reset);
+/* one "name stream_id start_ms end_ms" line per recorded launch, in launch order, relative to the
+ * first recorded launch: the timeline of a multi-stream step (tools/timeline.py).  Call before
+ * r2d2_prof_report(reset=1). */
+int r2d2_prof_trace(char* buf, int buflen);
 
 /* ------------------------------------------------------------------ sum-tree (K1, K8)
  * Replaces the O(M) mask + normalise + torch.multinomial of replay_memory.py:225-232.
@@ -154,7 +158,9 @@ int r2d2_td_target(const float* q_all, const float* q_next_online, const float* 
                    float* delta, float* dq, float* prio, float* loss, void* stream);
 
 /* ------------------------------------------------------------------ network, backward
- * (autograd of learner.py:97-99 through model.py:44-66) */
+ * (autograd of learner.py:97-99 through model.py:44-66).  head_bwd: gradient of the dueling
+ * output layers w.r.t. the hidden layer (dhid, ReLU' applied) and w.r.t. their weights (dw2, db2);
+ * either half may be skipped by passing NULL (dhid, or dw2 and db2 together). */
 int r2d2_head_bwd(const float* dq, const float* hid, const float* w2, float* dhid, float* dw2,
                   float* db2, int M, int H, void* stream);
 /* dx[M,K] (+)= dy[M,N] . w[N,K] */
@@ -257,7 +263,9 @@ int r2d2_tc_conv_wgrad_layer(int layer, const void* in, int B, int S, int s0, in
 /* conv data gradients on tcgen05 (plain bf16, ReLU' of the layer input fused): dz3 [R,32,7,7]
  * -> dz2 [R,32,9,9] (a2 = that layer's activations), dz2 -> dz1 [R,32,20,20]; the stride-2 layer
  * runs as four output-parity classes.  Plus the two small pieces of the conv backward that stay
- * elementwise: d[i] = a[i] > 0 ? d[i] : 0, and per-channel sums (part: >= 37*32 floats). */
+ * elementwise: d[i] = a[i] > 0 ? d[i] : 0, and per-channel sums of a [R,32,PIX] gradient, PIX in {49,81,400}
+ * (part: >= R2D2_CHANSUM_PART_FLOATS floats of scratch). */
+#define R2D2_CHANSUM_PART_FLOATS (296 * 32)
 int r2d2_tc_conv_dgrad3(const float* dz3, const float* w3, const float* a2, float* dz2, int R,
                         void* stream);
 int r2d2_tc_conv_dgrad2(const float* dz2, const float* w2, const float* a1, float* dz1, int R,

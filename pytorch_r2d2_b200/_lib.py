@@ -23,6 +23,7 @@ PROTOTYPES = {
     "r2d2_launch_count": (ctypes.c_longlong, []),
     "r2d2_prof_enable": (_I, [_I]),
     "r2d2_prof_report": (_I, [ctypes.c_char_p, _I, _I]),
+    "r2d2_prof_trace": (_I, [ctypes.c_char_p, _I]),
     "r2d2_tree_layout": (_I, [_L, _I, _P, _P, _P, _P]),
     "r2d2_tree_build": (_I, [_P, _P, _L, _P, _P]),
     "r2d2_tree_sample": (_I, [_P, _P, _L, _P, _P, _I, _P, _P]),
@@ -136,6 +137,17 @@ def launch_count() -> int:
 
 def prof_enable(on: bool) -> None:
     call("r2d2_prof_enable", int(on))
+
+
+def prof_trace() -> list:
+    """[(kernel name, stream id, start_ms, end_ms)] of every launch recorded since the last reset."""
+    buf = ctypes.create_string_buffer(1 << 20)
+    call("r2d2_prof_trace", buf, len(buf))
+    out = []
+    for line in buf.value.decode().splitlines():
+        name, sid, t0, t1 = line.rsplit(" ", 3)
+        out.append((name, int(sid), float(t0), float(t1)))
+    return out
 
 
 def prof_report(reset: bool = True) -> dict:

@@ -42,46 +42,106 @@ __global__ void reduce_partials_kernel(const float* __restrict__ part, float* __
     }
 }
 
-// db[n] = sum_m dy[m*N + n]: 32 columns per CTA, 32 warps stride over rows
+// db[n] = sum_m dy[m*N + n]: 8 columns (one 32-byte sector per row) per CTA, 128 row lanes
+// stride over the rows with four independent accumulators, then a fixed-order reduction
 __global__ void __launch_bounds__(1024)
 colsum_kernel(const float* __restrict__ dy, float* __restrict__ db, int M, int N) {
-    __shared__ float red[32][33];
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const int n = blockIdx.x * 32 + lane;
-    float s = 0.f;
-    if (n < N)
-        for (int m = w; m < M; m += 32) s += dy[(int64_t)m * N + n];
-    red[w][lane] = s;
-    __syncthreads();
-    if (w == 0 && n < N) {
-        float t = 0.f;
-        for (int i = 0; i < 32; ++i) t += red[i][lane];
-        db[n] = t;
+    __shared__ float red[128][9];
+    const int col = threadIdx.x & 7, rl = threadIdx.x >> 3;
+    const int n = blockIdx.x * 8 + col;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    if (n < N) {
+        const float* p = dy + n;
+        int m = rl;
+        for (; m + 384 < M; m += 512) {
+            s0 += p[(int64_t)m * N];
+            s1 += p[(int64_t)(m + 128) * N];
+            s2 += p[(int64_t)(m + 256) * N];
+            s3 += p[(int64_t)(m + 384) * N];
+        }
+        for (; m < M; m += 128) s0 += p[(int64_t)m * N];
     }
+    red[rl][col] = (s0 + s1) + (s2 + s3);
+    __syncthreads();
+    for (int h = 64; h >= 1; h >>= 1) {
+        if (rl < h) red[rl][col] += red[rl + h][col];
+        __syncthreads();
+    }
+    if (rl == 0 && n < N) db[n] = red[0][col];
 }
 
-// per-channel sum over frames and pixels of an NCHW gradient: db[c] = sum_{r,p} dz[r,c,p].
-// grid (C, CS_SPLITS): block (c, z) sums frames z, z+CS_SPLITS, ... into part[z*C + c]; the
-// partials are then added in fixed order (deterministic, no atomics).
-constexpr int CS_SPLITS = 37;   // 32 channels x 37 = 1184 CTAs = 8 per SM
+// per-channel sum over frames and pixels of an NCHW gradient: db[c] = sum_{r,p} dz[r,c,p], C = 32.
+// CTA z walks frames z, z+Z, ...; thread t keeps the float4s t, t+256, ... of a frame in
+// registers (the same channel/pixel every frame), so the frame loop is pure coalesced 16-byte
+// loads + adds.  The register image is then laid out in shared memory and each warp sums four
+// channels in a fixed order -> part[z*32 + c]; chansum_final adds the Z partials in fixed order
+// (deterministic, no atomics).
+constexpr int CS_Z = R2D2_CHANSUM_PART_FLOATS / 32;   // 296 CTAs = 2 per SM
+template <int PIX>
 __global__ void __launch_bounds__(256)
-chansum_partial_kernel(const float* __restrict__ dz, float* __restrict__ part, int R, int C, int PIX) {
-    __shared__ float red[32];
-    const int c = blockIdx.x, z = blockIdx.y;
-    float s = 0.f;
-    for (int r = z; r < R; r += CS_SPLITS) {
-        const float* p = dz + ((int64_t)r * C + c) * PIX;
-        for (int i = threadIdx.x; i < PIX; i += blockDim.x) s += p[i];
+chansum_partial_kernel(const float* __restrict__ dz, float* __restrict__ part, int R) {
+    constexpr int Q = 32 * PIX / 4;              // float4s per frame
+    constexpr int NQ = (Q + 255) / 256;
+    extern __shared__ float4 img[];              // [Q]
+    float4 acc[NQ];
+#pragma unroll
+    for (int j = 0; j < NQ; ++j) acc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int r = blockIdx.x; r < R; r += gridDim.x) {
+        const float4* f = reinterpret_cast<const float4*>(dz + (int64_t)r * 32 * PIX);
+#pragma unroll
+        for (int j = 0; j < NQ; ++j) {
+            const int q = threadIdx.x + 256 * j;
+            if (q < Q) {
+                const float4 v = __ldg(f + q);
+                acc[j].x += v.x; acc[j].y += v.y; acc[j].z += v.z; acc[j].w += v.w;
+            }
+        }
     }
-    s = block_sum(s, red);
-    if (threadIdx.x == 0) part[z * C + c] = s;
+#pragma unroll
+    for (int j = 0; j < NQ; ++j) {
+        const int q = threadIdx.x + 256 * j;
+        if (q < Q) img[q] = acc[j];
+    }
+    __syncthreads();
+    const float* flat = reinterpret_cast<const float*>(img);
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (int c = w; c < 32; c += 8) {
+        float s = 0.f;
+        for (int i = lane; i < PIX; i += 32) s += flat[c * PIX + i];
+        s = warp_sum(s);
+        if (lane == 0) part[blockIdx.x * 32 + c] = s;
+    }
 }
-__global__ void chansum_final_kernel(const float* __restrict__ part, float* __restrict__ db, int C) {
-    const int c = threadIdx.x;
-    if (c >= C) return;
+// one warp per channel: lanes stride over the Z partials, fixed-order shuffle tree
+__global__ void __launch_bounds__(1024)
+chansum_final_kernel(const float* __restrict__ part, float* __restrict__ db, int Z) {
+    const int lane = threadIdx.x & 31, c = threadIdx.x >> 5;
     float s = 0.f;
-    for (int z = 0; z < CS_SPLITS; ++z) s += part[z * C + c];
-    db[c] = s;
+    for (int z = lane; z < Z; z += 32) s += part[z * 32 + c];
+    s = warp_sum(s);
+    if (lane == 0) db[c] = s;
+}
+template <int PIX>
+static int chansum_launch(const float* dz, float* db, int R, float* part, cudaStream_t st) {
+    constexpr int smem = 32 * PIX * 4;
+    static bool attr_set = false;
+    if (!attr_set) {
+        R2D2_CUDA_OK(cudaFuncSetAttribute(chansum_partial_kernel<PIX>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr_set = true;
+    }
+    const int Z = R < CS_Z ? R : CS_Z;
+    R2D2_LAUNCH("chansum_partial_kernel", st, chansum_partial_kernel<PIX><<<Z, 256, smem, st>>>(dz, part, R));
+    R2D2_LAUNCH("chansum_final_kernel", st, chansum_final_kernel<<<1, 1024, 0, st>>>(part, db, Z));
+    return R2D2_OK;
+}
+static int chansum_dispatch(const float* dz, float* db, int R, int PIX, float* part, cudaStream_t st) {
+    switch (PIX) {
+        case 49: return chansum_launch<49>(dz, db, R, part, st);
+        case 81: return chansum_launch<81>(dz, db, R, part, st);
+        case 400: return chansum_launch<400>(dz, db, R, part, st);
+    }
+    return r2d2::set_err(R2D2_EINVAL, "chansum: PIX must be 49, 81 or 400 (the three conv layers), got %d", PIX);
 }
 
 // d[i] = a[i] > 0 ? d[i] : 0
@@ -572,8 +632,8 @@ static int torso_bwd_impl(const T* frames, FrameMap fm, int R, const float* a1, 
         ConvPatchCols<float, 32, 3, 9, 7, 1> bl{a2, FrameMap{0, 0, 0, 2592}};
         int rc = skip_wgrad ? 0 : conv_wgrad("conv3_wgrad", al, bl, 288, R * 49, dw3, part, st);
         if (rc) return rc;
-        R2D2_LAUNCH("chansum_partial_kernel", st, chansum_partial_kernel<<<dim3(32, CS_SPLITS), 256, 0, st>>>(dfeat, part, R, 32, 49));
-        R2D2_LAUNCH("chansum_final_kernel", st, chansum_final_kernel<<<1, 32, 0, st>>>(part, db3, 32));
+        rc = chansum_dispatch(dfeat, db3, R, 49, part, st);
+        if (rc) return rc;
     }
     {
         constexpr int smem = (32 * 3 * 3 * 32 + 32 * 49) * 4;
@@ -586,8 +646,8 @@ static int torso_bwd_impl(const T* frames, FrameMap fm, int R, const float* a1, 
         ConvPatchCols<float, 32, 4, 20, 9, 2> bl{a1, FrameMap{0, 0, 0, 12800}};
         int rc = skip_wgrad ? 0 : conv_wgrad("conv2_wgrad", al, bl, 512, R * 81, dw2, part, st);
         if (rc) return rc;
-        R2D2_LAUNCH("chansum_partial_kernel", st, chansum_partial_kernel<<<dim3(32, CS_SPLITS), 256, 0, st>>>(dz2, part, R, 32, 81));
-        R2D2_LAUNCH("chansum_final_kernel", st, chansum_final_kernel<<<1, 32, 0, st>>>(part, db2, 32));
+        rc = chansum_dispatch(dz2, db2, R, 81, part, st);
+        if (rc) return rc;
     }
     {
         constexpr int smem = (32 * 4 * 4 * 32 + 32 * 81) * 4;
@@ -600,8 +660,8 @@ static int torso_bwd_impl(const T* frames, FrameMap fm, int R, const float* a1, 
         ConvPatchCols<T, 4, 8, 84, 20, 4> bl{frames, fm};
         int rc = skip_wgrad ? 0 : conv_wgrad("conv1_wgrad", al, bl, 256, R * 400, dw1, part, st);
         if (rc) return rc;
-        R2D2_LAUNCH("chansum_partial_kernel", st, chansum_partial_kernel<<<dim3(32, CS_SPLITS), 256, 0, st>>>(dz1, part, R, 32, 400));
-        R2D2_LAUNCH("chansum_final_kernel", st, chansum_final_kernel<<<1, 32, 0, st>>>(part, db1, 32));
+        rc = chansum_dispatch(dz1, db1, R, 400, part, st);
+        if (rc) return rc;
     }
     return R2D2_OK;
 }
@@ -685,7 +745,7 @@ int r2d2_linear_wgrad(const float* dy, const float* x, float* dw, float* db, int
         R2D2_CUDA_OK((launch_gemm<128, 128, 8, 8>("linear_wgrad", al, bl, ep, N, K, M, 1, st)));
     }
     if (db) {
-        R2D2_LAUNCH("colsum_kernel", st, colsum_kernel<<<(N + 31) / 32, 1024, 0, st>>>(dy, db, M, N));
+        R2D2_LAUNCH("colsum_kernel", st, colsum_kernel<<<(N + 7) / 8, 1024, 0, st>>>(dy, db, M, N));
     }
     return R2D2_OK;
 }
@@ -747,16 +807,22 @@ int r2d2_head_out(const float* hid, const float* w2, const float* b2, float* q, 
 
 int r2d2_colsum(const float* dy, float* db, int M, int N, void* stream) {
     R2D2_REQUIRE(dy && db && M > 0 && N > 0, "colsum: bad args");
-    R2D2_LAUNCH("colsum_kernel", as_stream(stream), colsum_kernel<<<(N + 31) / 32, 1024, 0, as_stream(stream)>>>(dy, db, M, N));
+    R2D2_LAUNCH("colsum_kernel", as_stream(stream), colsum_kernel<<<(N + 7) / 8, 1024, 0, as_stream(stream)>>>(dy, db, M, N));
     return R2D2_OK;
 }
 
 int r2d2_head_bwd(const float* dq, const float* hid, const float* w2, float* dhid, float* dw2,
                   float* db2, int M, int H, void* stream) {
-    R2D2_REQUIRE(dq && hid && w2 && dhid && dw2 && db2 && M > 0 && H > 0 && H % 32 == 0,
+    R2D2_REQUIRE(dq && hid && w2 && M > 0 && H > 0 && H % 32 == 0,
                  "head_bwd: bad args (H must be a multiple of 32)");
-    R2D2_LAUNCH("head_bwd_dhid_kernel", as_stream(stream), head_bwd_dhid_kernel<<<M, 256, 0, as_stream(stream)>>>(dq, hid, w2, dhid, M, H));
-    R2D2_LAUNCH("head_bwd_dw2_kernel", as_stream(stream), head_bwd_dw2_kernel<<<H / 32 + 1, 1024, 0, as_stream(stream)>>>(dq, hid, dw2, db2, M, H));
+    R2D2_REQUIRE(dhid || (dw2 && db2), "head_bwd: nothing to compute (dhid and dw2/db2 are NULL)");
+    R2D2_REQUIRE((dw2 == nullptr) == (db2 == nullptr), "head_bwd: dw2 and db2 go together");
+    // the two halves are independent: a caller may ask for one of them per call (dhid = NULL or
+    // dw2 = db2 = NULL) to run them on different streams
+    if (dhid)
+        R2D2_LAUNCH("head_bwd_dhid_kernel", as_stream(stream), head_bwd_dhid_kernel<<<M, 256, 0, as_stream(stream)>>>(dq, hid, w2, dhid, M, H));
+    if (dw2)
+        R2D2_LAUNCH("head_bwd_dw2_kernel", as_stream(stream), head_bwd_dw2_kernel<<<H / 32 + 1, 1024, 0, as_stream(stream)>>>(dq, hid, dw2, db2, M, H));
     return R2D2_OK;
 }
 
@@ -849,7 +915,7 @@ int r2d2_linear_wgrad_static(const float* dy, const float* x, float* dw, float* 
         R2D2_LAUNCH_OK();
     }
     if (db) {
-        colsum_kernel<<<(N + 31) / 32, 1024, 0, st>>>(dy, db, M, N);
+        colsum_kernel<<<(N + 7) / 8, 1024, 0, st>>>(dy, db, M, N);
         R2D2_LAUNCH_OK();
     }
     return R2D2_OK;
@@ -879,13 +945,10 @@ int r2d2_relu_mask(float* d, const float* a, int64_t n, void* stream) {
     R2D2_LAUNCH("relu_mask_kernel", as_stream(stream), relu_mask_kernel<<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(d, a, n));
     return R2D2_OK;
 }
-// db[c] = sum over frames and pixels of dz[R, C=32, PIX]; part: CS_SPLITS*32 floats of scratch
+// db[c] = sum over frames and pixels of dz[R, C=32, PIX]; part: R2D2_CHANSUM_PART_FLOATS of scratch
 int r2d2_chansum(const float* dz, float* db, int R, int PIX, float* part, void* stream) {
     R2D2_REQUIRE(dz && db && part && R > 0 && PIX > 0, "chansum: bad args");
-    cudaStream_t st = as_stream(stream);
-    R2D2_LAUNCH("chansum_partial_kernel", st, chansum_partial_kernel<<<dim3(32, CS_SPLITS), 256, 0, st>>>(dz, part, R, 32, PIX));
-    R2D2_LAUNCH("chansum_final_kernel", st, chansum_final_kernel<<<1, 32, 0, st>>>(part, db, 32));
-    return R2D2_OK;
+    return chansum_dispatch(dz, db, R, PIX, part, as_stream(stream));
 }
 
 // data gradients + bias gradients only (dz2/dz1 left in scratch for the tensor-core weight

@@ -42,6 +42,16 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     __trap();
 }
 
+// long waits: poll with a pause in between -- a warp spinning on try_wait competes for the same
+// issue slots and memory-pipe queue as the thread issuing the TMA loads it is waiting for
+__device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity, uint32_t ns) {
+    for (uint32_t it = 0; it < (1u << 26); ++it) {
+        if (mbar_try_wait(bar, parity)) return;
+        __nanosleep(ns);
+    }
+    __trap();
+}
+
 // ---------------------------------------------------------------- bulk copies (TMA, 1-D)
 __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32_t bytes,
                                          uint64_t* bar) {

@@ -24,7 +24,7 @@ int set_err(int code, const char* fmt, ...) {
 // ---- launch counter and optional per-kernel CUDA-event profiler (bench.py's roofline leg)
 static std::atomic<long long> g_launches{0};
 static bool g_prof_on = false;
-struct ProfRec { const char* name; cudaEvent_t a, b; };
+struct ProfRec { const char* name; cudaEvent_t a, b; cudaStream_t st; };
 static std::vector<ProfRec> g_recs;
 static std::vector<cudaEvent_t> g_pool;
 static std::mutex g_prof_mu;
@@ -48,7 +48,7 @@ ProfScope::~ProfScope() {
     if (on_) {
         cudaEventRecord((cudaEvent_t)b_, st_);
         std::lock_guard<std::mutex> lk(g_prof_mu);
-        g_recs.push_back(ProfRec{name_, (cudaEvent_t)a_, (cudaEvent_t)b_});
+        g_recs.push_back(ProfRec{name_, (cudaEvent_t)a_, (cudaEvent_t)b_, st_});
     }
 }
 
@@ -551,6 +551,29 @@ int r2d2_prof_report(char* buf, int buflen, int reset) {
     if (reset) {
         for (auto& r : r2d2::g_recs) { r2d2::g_pool.push_back(r.a); r2d2::g_pool.push_back(r.b); }
         r2d2::g_recs.clear();
+    }
+    return R2D2_OK;
+}
+
+int r2d2_prof_trace(char* buf, int buflen) {
+    // synchronises, then writes one "name stream_id start_ms end_ms" line per recorded launch, in
+    // launch order, times relative to the first recorded launch (events of different streams
+    // share one device clock)
+    R2D2_CUDA_OK(cudaDeviceSynchronize());
+    std::lock_guard<std::mutex> lk(r2d2::g_prof_mu);
+    int pos = 0;
+    if (buf && buflen > 0) buf[0] = 0;
+    std::map<cudaStream_t, int> ids;
+    for (auto& r : r2d2::g_recs) {
+        float t0 = 0.f, t1 = 0.f;
+        if (cudaEventElapsedTime(&t0, r2d2::g_recs[0].a, r.a) != cudaSuccess ||
+            cudaEventElapsedTime(&t1, r2d2::g_recs[0].a, r.b) != cudaSuccess)
+            continue;
+        int id = ids.emplace(r.st, (int)ids.size()).first->second;
+        int w = snprintf(buf + pos, pos < buflen ? buflen - pos : 0, "%s %d %.6f %.6f\n", r.name, id,
+                         t0, t1);
+        if (w < 0 || pos + w >= buflen) break;
+        pos += w;
     }
     return R2D2_OK;
 }

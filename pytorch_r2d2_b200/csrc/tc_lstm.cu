@@ -55,8 +55,9 @@ struct LstmArgs {
     float* hs_ext;         // [(T+1), B, H]; slot 0 = h0 (read), slot t+1 written
     float* cs_ext;         // same for c
     float* gates;          // [T, B, 4H] post-activation i,f,g,o or null
-    __nv_bfloat16* h16_hi; // [2, B, H] ping-pong, K-major B operand
-    __nv_bfloat16* h16_lo;
+    __nv_bfloat16* h16;    // [2, H/64, groups, hi|lo, NB, 64] ping-pong, K-major B operand laid out
+                           // so that the (hi, lo) tiles of one k-block and batch group are ONE
+                           // contiguous 2*NB*128-byte run = one TMA box = one pipeline stage
     int* counter;          // [gridDim.y] grid barrier counters, zero on entry
     int T, B, H;
     long long* trace;      // optional [T, 8] globaltimer stamps of CTA (0,0) (diagnostics), or null
@@ -102,8 +103,7 @@ constexpr int LS_ISSUERS = 4;   // MMA-issuing warps: 1, 10, 11, 12 (k-blocks kb
 
 template <int NB>
 __global__ void __launch_bounds__(416, 1)
-tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_constant__ CUtensorMap tma_lo,
-                   const LstmArgs a) {
+tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_h, const LstmArgs a) {
     constexpr int STAGES = 256 / NB;                            // 64 -> 4, 32 -> 8 (whole h in flight)
     constexpr int UPT = LS_UNITS * NB / 256;                    // hidden units per pointwise thread
     // W_hi multiplies both h_hi and h_lo: with NB = 32 they are ONE MMA of N = 64 against the
@@ -132,8 +132,7 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
     const long long BH = (long long)B * H;
 
     if (tid == 0) {
-        tma_prefetch_desc(&tma_hi);
-        tma_prefetch_desc(&tma_lo);
+        tma_prefetch_desc(&tma_h);
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
@@ -167,9 +166,16 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
     const uint32_t tmem_base = tmem_slot;
     const int issuer = warp == 1 ? 0 : (warp >= 10 ? warp - 9 : -1);
 
-    // pointwise mapping (warps 2..9): batch row pb and UPT consecutive hidden units
+    // pointwise mapping (warps 2..9): batch row pb and UPT consecutive hidden units; the
+    // LS_UNITS/UPT threads of a batch row are neighbours, so a warp's store covers whole 64-byte
+    // runs (16 units of one row) instead of 32 different rows
     const int pt = tid - 64;                      // 0..255 for pointwise threads
-    const int pb = pt % NB, pu = (pt / NB) * UPT;
+    constexpr int TPR = LS_UNITS / UPT;           // threads per batch row
+    const int pb = pt / TPR, pu = (pt % TPR) * UPT;
+    // offset of (row b0+pb, units u0+pu.., hi) inside one [H/64, groups, 2, NB, 64] bf16 image
+    const long long o16r = (((long long)(u0 >> 6) * gridDim.y + blockIdx.y) * 2 * NB + pb) * 64 + (u0 & 63) + pu;
+    const long long IMG = (long long)NKB * gridDim.y * 2 * NB * 64;
+    __nv_bfloat16* const h16_lo = a.h16 + NB * 64;
     const bool pw = warp >= 2 && warp < 10;
     const bool pvalid = pw && (b0 + pb) < B;
     float c_reg[UPT];
@@ -185,7 +191,7 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
             hv[j] = a.hs_ext[o + j];
             c_reg[j] = a.cs_ext[o + j];
         }
-        st_bf16_hilo<UPT>(a.h16_hi + o, a.h16_lo + o, hv);
+        st_bf16_hilo<UPT>(a.h16 + o16r, h16_lo + o16r, hv);
     }
     if (pw) {
         // CTA barrier orders every thread's stores before thread 0's gpu-scope RELEASE, which is
@@ -212,8 +218,7 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
                     mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
                     mbar_expect_tx(&full_bar[s], STAGE);
                     uint8_t* dst = h_s + (size_t)s * STAGE;
-                    tma_load_2d(dst, &tma_hi, kb * 64, p * B + b0, &full_bar[s]);
-                    tma_load_2d(dst + H_TILE, &tma_lo, kb * 64, p * B + b0, &full_bar[s]);
+                    tma_load_2d(dst, &tma_h, 0, ((p * NKB + kb) * (int)gridDim.y + (int)blockIdx.y) * 2 * NB, &full_bar[s]);
                 }
             }
         } else if (issuer >= 0) {
@@ -268,8 +273,13 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
             if (warp < 6) {
                 // ---- TMEM readers: gate q = warp % 4, unit = lane (< 16), NB batch columns
                 const int q = warp & 3;
-                mbar_wait(&acc_full, t & 1);
-                if (tid == 64) LS_STAMP(3);                         // accumulator complete
+                // one thread polls the accumulator barrier, the other readers sleep on a hardware
+                // barrier: pollers take issue slots from the TMA and MMA issuing threads
+                if (tid == 64) {
+                    mbar_wait_sleep(&acc_full, t & 1, 32);
+                    LS_STAMP(3);                                    // accumulator complete
+                }
+                named_bar_sync(3, 128);
                 tc_fence_after();
                 const int nslices = NKB < LS_ISSUERS ? NKB : LS_ISSUERS;   // issuers that ran MMAs
                 float acc[NB];
@@ -299,8 +309,8 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
             }
             named_bar_sync(1, 256);                                 // G complete
             if (pt == 0) LS_STAMP(4);
+            float hv[UPT], cv[UPT], gi[UPT], gf[UPT], gg[UPT], go[UPT];
             if (pvalid) {
-                float hv[UPT], cv[UPT], gi[UPT], gf[UPT], gg[UPT], go[UPT];
 #pragma unroll
                 for (int j = 0; j < UPT; ++j) {
                     gi[j] = ls_sigmoid(G[0][pu + j][pb] + xp[0][j]);
@@ -311,11 +321,23 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
                     hv[j] = go[j] * ls_tanh(cv[j]);
                     c_reg[j] = cv[j];
                 }
+                // what the next step waits for goes out first and alone: the releasing arrive
+                // below has to wait for every store issued before it
+                const long long o16 = (long long)((t + 1) & 1) * IMG + o16r;
+                st_bf16_hilo<UPT>(a.h16 + o16, h16_lo + o16, hv);
+            }
+            if (pt == 0) LS_STAMP(5);                               // pointwise + h stores issued
+            named_bar_sync(2, 256);                                 // all of this CTA's h_t is out
+            if (pt == 0) {
+                LS_STAMP(6);
+                red_release_add(counter, 1);
+                LS_STAMP(7);
+            }
+            // fp32 history for the kernels after the unroll (nobody inside it reads these)
+            if (pvalid) {
                 const long long o = (long long)(b0 + pb) * H + u0 + pu;
                 st_f32<UPT>(a.hs_ext + (long long)(t + 1) * BH + o, hv);
                 st_f32<UPT>(a.cs_ext + (long long)(t + 1) * BH + o, cv);
-                const long long o16 = (long long)((t + 1) & 1) * BH + o;
-                st_bf16_hilo<UPT>(a.h16_hi + o16, a.h16_lo + o16, hv);
                 if (a.gates) {
                     float* gp = a.gates + ((long long)t * B + b0 + pb) * 4 * H + u0 + pu;
                     st_f32<UPT>(gp, gi);
@@ -323,13 +345,6 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_hi, const __grid_cons
                     st_f32<UPT>(gp + 2 * H, gg);
                     st_f32<UPT>(gp + 3 * H, go);
                 }
-            }
-            if (pt == 0) LS_STAMP(5);                               // pointwise + stores issued
-            named_bar_sync(2, 256);                                 // all of this CTA's h_t is out
-            if (pt == 0) {
-                LS_STAMP(6);
-                red_release_add(counter, 1);
-                LS_STAMP(7);
             }
         }
     }
@@ -353,17 +368,25 @@ struct LstmBwdArgs {
     const float* gates;    // [T, B, 4H] post-activation i,f,g,o
     const float* cs_ext;   // [(T+1), B, H], slot t = c_{t-1}, slot t+1 = c_t
     float* dgates;         // [T, B, 4H] out: pre-activation gradients
-    __nv_bfloat16* dg16;   // [2, B, 4H] ping-pong
+    __nv_bfloat16* dg16;   // [2, 4H/64, B, 64] ping-pong, k-block-major (contiguous TMA boxes)
     int* counter;
     int T, B, H;
+    long long* trace;      // optional [T, 32] globaltimer stamps of CTA (0,0), or null
 };
-constexpr int LB_STAGES = 16;
+#define LB_STAMP(slot)                                                        \
+    do {                                                                      \
+        if (a.trace && blockIdx.x == 0 && blockIdx.y == 0) a.trace[s * 32 + (slot)] = gtimer(); \
+    } while (0)
+constexpr int LB_RING_BYTES = 128 * 1024;   // A-tile ring: with NB = 32 a whole step's dG (32 tiles of 4 KB)
 
 // NB = batch rows per CTA (32 or 64); the UMMA is always M = 64, with NB = 32 the upper half of
 // the A tile is never filled and its accumulator rows are ignored (rows are independent).
 template <int NB>
 __global__ void __launch_bounds__(288, 1)
 tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs a) {
+    // ring stage = NB rows x 128 B.  The UMMA reads 64 rows: with NB = 32 the upper half of a tile
+    // aliases the next stage (or the pad behind the ring) and only feeds ignored accumulator rows.
+    constexpr int LB_STAGES = LB_RING_BYTES / (NB * 128);
     const int H = a.H, B = a.B, K4 = 4 * a.H, NKB = K4 / 64;
     extern __shared__ uint8_t smem_raw[];
     __shared__ uint64_t full_bar[LB_STAGES], empty_bar[LB_STAGES], acc_full, acc_empty;
@@ -372,7 +395,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
     uint8_t* base = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
     const uint32_t W_KB = LS_UNITS * 128;                       // 16 rows x 64 bf16 = 2 KB
     uint8_t* w_s = base;                                        // [NKB][2 KB]
-    const uint32_t A_TILE = LS_NB * 128;                        // 64 rows x 64 bf16 = 8 KB
+    constexpr uint32_t A_TILE = NB * 128;                       // NB rows x 64 bf16
     uint8_t* a_s = base + (size_t)NKB * W_KB;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -425,14 +448,17 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
                 uint32_t spins = 0;
                 while (ld_acquire(counter) < target)
                     if (++spins > (1u << 28)) __trap();
+                LB_STAMP(0);                                    // barrier passed
                 asm volatile("fence.proxy.async;" ::: "memory");
                 const int p = (s - 1) & 1;
                 for (int kb = 0; kb < NKB; ++kb, ++it) {
                     const int st = it % LB_STAGES;
                     mbar_wait(&empty_bar[st], ((it / LB_STAGES) & 1) ^ 1);
                     mbar_expect_tx(&full_bar[st], NB * 128);
-                    tma_load_2d(a_s + (size_t)st * A_TILE, &tma_dg, kb * 64, p * B + b0, &full_bar[st]);
+                    tma_load_2d(a_s + (size_t)st * A_TILE, &tma_dg, 0, (p * NKB + kb) * B + b0, &full_bar[st]);
+                    if (kb == LB_STAGES - 1) LB_STAMP(8);       // first ring fill issued
                 }
+                LB_STAMP(1);                                    // all loads issued
             }
         } else if (issuer >= 0) {
             if (lane == 0 && s > 0) {
@@ -449,6 +475,8 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
                     const int st = itk % LB_STAGES;
                     mbar_wait(&full_bar[st], (itk / LB_STAGES) & 1);
                     tc_fence_after();
+                    if (issuer == 0 && kb == 0) LB_STAMP(9);    // first tile landed
+                    if (issuer == 3 && kb == NKB - 1) LB_STAMP(10);   // last tile landed
                     const uint64_t aa = da0 + (uint64_t)((st * A_TILE) >> 4);
                     const uint64_t bb = db0 + (uint64_t)((kb * W_KB) >> 4);
 #pragma unroll
@@ -457,6 +485,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
                     umma_commit(&empty_bar[st]);
                 }
                 umma_commit(&acc_full);
+                if (issuer == 3) LB_STAMP(2);                   // last MMA issued
             }
         } else if (warp >= 2 && warp < 6) {
             // ---- readers + gate-gradient math (64 active threads per CTA).  Everything that does
@@ -480,7 +509,11 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
 #pragma unroll
             for (int j = 0; j < LS_UNITS; ++j) rec[j] = 0.f;
             if (s > 0) {
-                mbar_wait(&acc_full, (s - 1) & 1);
+                if (tid == 64) {
+                    mbar_wait_sleep(&acc_full, (s - 1) & 1, 32);
+                    LB_STAMP(3);                                // accumulators complete
+                }
+                named_bar_sync(3, 128);
                 tc_fence_after();
                 uint32_t ra[32], rb2[32];
                 tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16), ra);
@@ -488,15 +521,14 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
                 tmem_ld_wait();
                 tc_fence_before();
                 mbar_arrive(&acc_empty);
+                if (tid == 64) LB_STAMP(4);                     // TMEM read
 #pragma unroll
                 for (int j = 0; j < LS_UNITS; ++j)
                     rec[j] = (__uint_as_float(ra[j]) + __uint_as_float(ra[16 + j])) +
                              (__uint_as_float(rb2[j]) + __uint_as_float(rb2[16 + j]));
             }
+            float di[16], df[16], dg[16], dov[16];
             if (rvalid) {
-                float* dgp = a.dgates + ((long long)t * B + rb) * K4 + u0;
-                __nv_bfloat16* d16 = a.dg16 + (long long)(s & 1) * BG + (long long)rb * K4 + u0;
-                float di[16], df[16], dg[16], dov[16];
 #pragma unroll
                 for (int j = 0; j < 16; ++j) {
                     const float d = dh[j] + rec[j];
@@ -508,6 +540,27 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
                     dov[j] = d * tc * go[j] * (1.f - go[j]);
                     dc_reg[j] = dc * gf[j];
                 }
+                // bf16 image the next step's TMA reads: gate g, units u0.. = k-block g*H/64 + u0/64
+                __nv_bfloat16* d16 = a.dg16 + (long long)(s & 1) * BG + ((long long)(u0 >> 6) * B + rb) * 64 + (u0 & 63);
+                const long long gstep = (long long)(H >> 6) * B * 64;
+#pragma unroll
+                for (int j = 0; j < 16; j += 8) {
+                    *reinterpret_cast<uint4*>(d16 + j) = make_uint4(ls_pack(di[j], di[j + 1]), ls_pack(di[j + 2], di[j + 3]), ls_pack(di[j + 4], di[j + 5]), ls_pack(di[j + 6], di[j + 7]));
+                    *reinterpret_cast<uint4*>(d16 + gstep + j) = make_uint4(ls_pack(df[j], df[j + 1]), ls_pack(df[j + 2], df[j + 3]), ls_pack(df[j + 4], df[j + 5]), ls_pack(df[j + 6], df[j + 7]));
+                    *reinterpret_cast<uint4*>(d16 + 2 * gstep + j) = make_uint4(ls_pack(dg[j], dg[j + 1]), ls_pack(dg[j + 2], dg[j + 3]), ls_pack(dg[j + 4], dg[j + 5]), ls_pack(dg[j + 6], dg[j + 7]));
+                    *reinterpret_cast<uint4*>(d16 + 3 * gstep + j) = make_uint4(ls_pack(dov[j], dov[j + 1]), ls_pack(dov[j + 2], dov[j + 3]), ls_pack(dov[j + 4], dov[j + 5]), ls_pack(dov[j + 6], dov[j + 7]));
+                }
+            }
+            if (tid == 64) LB_STAMP(5);                         // gate math + bf16 stores issued
+            named_bar_sync(1, 128);
+            if (tid == 64) {
+                LB_STAMP(6);
+                red_release_add(counter, 1);
+                LB_STAMP(7);
+            }
+            // fp32 gradients for the kernels after the unroll, behind the releasing arrive
+            if (rvalid) {
+                float* dgp = a.dgates + ((long long)t * B + rb) * K4 + u0;
 #pragma unroll
                 for (int j = 0; j < 16; j += 4) {
                     *reinterpret_cast<float4*>(dgp + j) = make_float4(di[j], di[j + 1], di[j + 2], di[j + 3]);
@@ -515,16 +568,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
                     *reinterpret_cast<float4*>(dgp + 2 * H + j) = make_float4(dg[j], dg[j + 1], dg[j + 2], dg[j + 3]);
                     *reinterpret_cast<float4*>(dgp + 3 * H + j) = make_float4(dov[j], dov[j + 1], dov[j + 2], dov[j + 3]);
                 }
-#pragma unroll
-                for (int j = 0; j < 16; j += 8) {
-                    *reinterpret_cast<uint4*>(d16 + j) = make_uint4(ls_pack(di[j], di[j + 1]), ls_pack(di[j + 2], di[j + 3]), ls_pack(di[j + 4], di[j + 5]), ls_pack(di[j + 6], di[j + 7]));
-                    *reinterpret_cast<uint4*>(d16 + H + j) = make_uint4(ls_pack(df[j], df[j + 1]), ls_pack(df[j + 2], df[j + 3]), ls_pack(df[j + 4], df[j + 5]), ls_pack(df[j + 6], df[j + 7]));
-                    *reinterpret_cast<uint4*>(d16 + 2 * H + j) = make_uint4(ls_pack(dg[j], dg[j + 1]), ls_pack(dg[j + 2], dg[j + 3]), ls_pack(dg[j + 4], dg[j + 5]), ls_pack(dg[j + 6], dg[j + 7]));
-                    *reinterpret_cast<uint4*>(d16 + 3 * H + j) = make_uint4(ls_pack(dov[j], dov[j + 1]), ls_pack(dov[j + 2], dov[j + 3]), ls_pack(dov[j + 4], dov[j + 5]), ls_pack(dov[j + 6], dov[j + 7]));
-                }
             }
-            named_bar_sync(1, 128);
-            if (tid == 64) red_release_add(counter, 1);
         }
     }
     tc_fence_before();
@@ -575,9 +619,10 @@ int r2d2_tc_lstm_set_trace(void* trace) {
 }
 
 int64_t r2d2_tc_lstm_scratch_bytes(int B, int H) {
-    // h16 hi + lo ping-pong [2,B,H] bf16 each, + barrier counters (256 B, kept 256-byte aligned)
-    const int64_t h16 = (int64_t)2 * B * H * 2;
-    return 2 * ((h16 + 255) / 256 * 256) + 256;
+    // h ping-pong [2, H/64, groups, hi|lo, NB, 64] bf16 (batch padded to whole 64-row groups),
+    // + barrier counters (256 B, kept 256-byte aligned)
+    const int64_t Bp = ((int64_t)B + 63) / 64 * 64;
+    return 2 * 2 * Bp * H * 2 + 256;
 }
 
 int r2d2_tc_lstm_seq_fwd(const float* xprojT, int64_t ldx, int64_t col0, const float* w_hh,
@@ -591,14 +636,13 @@ int r2d2_tc_lstm_seq_fwd(const float* xprojT, int64_t ldx, int64_t col0, const f
                      (!gates || ((uintptr_t)gates % 16) == 0),
                  "tc_lstm_seq_fwd: misaligned buffer");
     cudaStream_t st = as_stream(stream);
-    const int64_t h16 = ((int64_t)2 * B * H * 2 + 255) / 256 * 256;
+    const int64_t h16 = r2d2_tc_lstm_scratch_bytes(B, H) - 256;
     uint8_t* sc = static_cast<uint8_t*>(scratch);
     LstmArgs a;
     a.xprojT = xprojT; a.ldx = ldx; a.col0 = col0; a.w_hh = w_hh;
     a.hs_ext = hs_ext; a.cs_ext = cs_ext; a.gates = gates;
-    a.h16_hi = reinterpret_cast<__nv_bfloat16*>(sc);
-    a.h16_lo = reinterpret_cast<__nv_bfloat16*>(sc + h16);
-    a.counter = reinterpret_cast<int*>(sc + 2 * h16);
+    a.h16 = reinterpret_cast<__nv_bfloat16*>(sc);
+    a.counter = reinterpret_cast<int*>(sc + h16);
     a.T = T; a.B = B; a.H = H;
     a.trace = g_lstm_trace;
     // batch tile: 32 columns spreads a chain over twice the SMs; fall back to 64 when that many
@@ -609,10 +653,8 @@ int r2d2_tc_lstm_seq_fwd(const float* xprojT, int64_t ldx, int64_t col0, const f
     const int groups = (B + nb - 1) / nb;
     R2D2_REQUIRE(groups <= 64, "tc_lstm_seq_fwd: batch too large");
     R2D2_CUDA_OK(cudaMemsetAsync(a.counter, 0, 256, st));
-    CUtensorMap thi, tlo;
-    int rc = make_h_tmap(&thi, a.h16_hi, 2ll * B, H, nb);
-    if (rc) return rc;
-    rc = make_h_tmap(&tlo, a.h16_lo, 2ll * B, H, nb);
+    CUtensorMap th;
+    int rc = make_h_tmap(&th, a.h16, 2ll * (H / 64) * groups * 2 * nb, 64, 2 * nb);
     if (rc) return rc;
     const int smem = 2 * NKB * LS_ROWS * 128 + (256 / nb) * 2 * nb * 128 + 1024;
     void* kern = nb == 32 ? (void*)tc_lstm_fwd_kernel<32> : (void*)tc_lstm_fwd_kernel<64>;
@@ -621,7 +663,7 @@ int r2d2_tc_lstm_seq_fwd(const float* xprojT, int64_t ldx, int64_t col0, const f
     R2D2_REQUIRE((int)(grid.x * grid.y) <= sm_count(),
                  "tc_lstm_seq_fwd: %d CTAs must be co-resident but the device has %d SMs",
                  grid.x * grid.y, sm_count());
-    void* params[] = {&thi, &tlo, &a};
+    void* params[] = {&th, &a};
     {
         ProfScope ps("tc_lstm_fwd_kernel", st);
         R2D2_CUDA_OK(cudaLaunchCooperativeKernel(kern, grid, dim3(416), params, (size_t)smem, st));
@@ -655,16 +697,17 @@ int r2d2_tc_lstm_seq_bwd(const float* dhs, const float* w_hh, const float* gates
     a.dg16 = reinterpret_cast<__nv_bfloat16*>(sc);
     a.counter = reinterpret_cast<int*>(sc + dg16);
     a.T = T; a.B = B; a.H = H;
+    a.trace = g_lstm_trace;
     int nb = 32;
     if ((H / LS_UNITS) * ((B + 31) / 32) > sm_count()) nb = 64;
     const int groups = (B + nb - 1) / nb;
     R2D2_REQUIRE(groups <= 64, "tc_lstm_seq_bwd: batch too large");
     R2D2_CUDA_OK(cudaMemsetAsync(a.counter, 0, 256, st));
     CUtensorMap tdg;
-    int rc = make_h_tmap(&tdg, a.dg16, 2ll * B, 4ll * H, nb);
+    int rc = make_h_tmap(&tdg, a.dg16, 2ll * (4 * H / 64) * B, 64, nb);
     if (rc) return rc;
     const int NKB = 4 * H / 64;
-    const int smem = NKB * LS_UNITS * 128 + LB_STAGES * LS_NB * 128 + 1024;
+    const int smem = NKB * LS_UNITS * 128 + LB_RING_BYTES + 4096 + 1024;
     void* kern = nb == 32 ? (void*)tc_lstm_bwd_kernel<32> : (void*)tc_lstm_bwd_kernel<64>;
     R2D2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     dim3 grid(H / LS_UNITS, groups);

@@ -90,8 +90,9 @@ def td_target(q_all, qn_on, qn_tg, action, reward, done, gamma_n, out, *, rescal
 # ---------------------------------------------------------------------------- backward ops
 def head_bwd(dq, hid, w: Weights, dhid, dw2, db2):
     M, H2 = hid.shape
-    _lib.call("r2d2_head_bwd", P(dq, "f32"), P(hid, "f32"), P(w.head_w2), P(dhid, "f32"), P(dw2, "f32"),
-              P(db2, "f32"), M, H2 // 2, S())
+    opt = lambda t: P(t, "f32") if t is not None else None  # noqa: E731
+    _lib.call("r2d2_head_bwd", P(dq, "f32"), P(hid, "f32"), P(w.head_w2), opt(dhid), opt(dw2),
+              opt(db2), M, H2 // 2, S())
 
 
 def linear_dgrad(dy, w, dx, accumulate=False):

@@ -91,6 +91,9 @@ class Learner:
         # next to the cooperative LSTM launches hung on 2 GPUs; multi-GPU steps run eagerly.
         self.graph_collectives = False
         self._graph, self._graph_key = None, None
+        # kernels of this library inside the captured step / replays so far (a replay launches
+        # them without passing through the C entry points, so r2d2_launch_count() cannot see them)
+        self.graph_kernel_nodes, self.graph_replays = 0, 0
         self.memory_path = os.path.join("./", "logs", "memory")
         # memory (learner.py:34-41)
         self.burn_in_length = 10
@@ -194,7 +197,7 @@ class Learner:
             ws["feat16_on"], ws["feat16_tg"] = h(2, S * B, FEAT), h(2, T * B, FEAT)
             ws["w_ih16"], ws["w_ih16_t"], ws["w_ihT16"] = h(2, 4 * H, FEAT), h(2, 4 * H, FEAT), h(FEAT, 4 * H)
             ws["hw1_16"], ws["hw1_16_t"], ws["hw1T16"] = h(2, 2 * H, H), h(2, 2 * H, H), h(H, 2 * H)
-            ws["hs16"], ws["hs16_t"] = h(2, M, H), h(2, M, H)
+            ws["hs16"], ws["hs16_t"], ws["hs16_l"] = h(2, M, H), h(2, M, H), h(2, M, H)
             # transposed input projections [4H, frames*B] for the persistent LSTM kernel
             ws["xpT_on"], ws["xpT_tg"] = f(4 * H, S * B), f(4 * H, T * B)
             ws["lstm_scratch"] = torch.empty(engine.tc_lstm_scratch_bytes(B, H), dtype=torch.uint8, device=dev)
@@ -202,8 +205,10 @@ class Learner:
             ws["lstm_bwd_scratch"] = torch.empty(engine.tc_lstm_bwd_scratch_bytes(B, H), dtype=torch.uint8, device=dev)
             nsm = int(_lib.load().r2d2_sm_count())
             ws["wpart"] = [f(nsm * 32 * 256), f(nsm * 32 * 512), f(nsm * 32 * 288)]
-            ws["cpart"] = [f(37 * 32), f(37 * 32), f(37 * 32)]
+            ws["cpart"] = [f(296 * 32), f(296 * 32), f(296 * 32)]   # R2D2_CHANSUM_PART_FLOATS
             ws["side_stream"] = torch.cuda.Stream(device=dev)
+            ws["aux_stream"] = torch.cuda.Stream(device=dev)
+            ws["ev_aux"] = [torch.cuda.Event() for _ in range(2)]
             ws["events"] = [torch.cuda.Event() for _ in range(16)]
             ws["ev_fork"], ws["ev_join"] = torch.cuda.Event(), torch.cuda.Event()
             ws["dhid16"], ws["dhidT16"], ws["hsT16"] = h(M, 2 * H), h(2 * H, M), h(H, M)
@@ -235,12 +240,15 @@ class Learner:
             torch.cuda.synchronize()
             rm._tree_dirty = True
             g = torch.cuda.CUDAGraph()
+            n0 = _lib.launch_count()
             with torch.cuda.graph(g):
                 loss = self._train_eager(u_host, None, None)
+            self.graph_kernel_nodes = _lib.launch_count() - n0
             self._graph, self._graph_key, self._graph_loss = g, key, loss
             rm._tree_dirty = False
             return loss      # the capture pass does not execute; the warm-up step above did
         self._graph.replay()
+        self.graph_replays += 1
         rm._tree_dirty = False
         return self._graph_loss
 
@@ -323,6 +331,14 @@ class Learner:
                                 w.b_ih, w.b_hh, y32=ws["xpT_on"], bias_row=True)
             sc = ws["lstm_scratch"]
             engine.tc_lstm_seq_fwd(ws["xpT_on"], 0, w.w_hh, ws["hs_on"], ws["cs_on"], ws["gates"], T, B, H, sc)
+            if overlap:
+                # the learn-window head only needs hs_on: it runs on a third stream beside the
+                # double-Q pass of the recurrence (which occupies 64 of the 148 SMs)
+                ws["ev_aux"][0].record(main)
+                ws["aux_stream"].wait_event(ws["ev_aux"][0])
+                with torch.cuda.stream(ws["aux_stream"]):
+                    head(hs_learn, w, ws["hw1_16"], ws["hs16_l"], ws["hid_on"], ws["q_all"])
+                    ws["ev_aux"][1].record(ws["aux_stream"])
             ws["hs_dq"][0].copy_(ws["hs_on"][T])
             ws["cs_dq"][0].copy_(ws["cs_on"][T])
             engine.tc_lstm_seq_fwd(ws["xpT_on"], (BI + n) * B, w.w_hh, ws["hs_dq"], ws["cs_dq"], None, L, B, H, sc)
@@ -335,9 +351,11 @@ class Learner:
 
         # ---- dueling heads on the learn window only
         head(ws["hs_dq"][1:].reshape(M, H), w, ws.get("hw1_16"), ws.get("hs16"), ws["hid_tmp"], ws["qn_on"])
-        head(hs_learn, w, ws.get("hw1_16"), ws.get("hs16"), ws["hid_on"], ws["q_all"])
         if overlap:
+            main.wait_event(ws["ev_aux"][1])
             main.wait_event(ws["ev_join"])
+        else:
+            head(hs_learn, w, ws.get("hw1_16"), ws.get("hs16"), ws["hid_on"], ws["q_all"])
 
         # ---- n-step double-Q target, TD error, loss gradient, per-step priorities
         td = ws["td"]
@@ -375,9 +393,10 @@ class Learner:
                 rm.update_sequence_priority(batch["seq_index"], True)
 
             beside(priorities)
-            engine.head_bwd(td["dq"], ws["hid_on"], w, ws["dhid"], g.head_w2, g.head_b2)
+            engine.head_bwd(td["dq"], ws["hid_on"], w, ws["dhid"], None, None)
 
-            def head_wgrad():     # dW1 = dhid^T . hs  (operands transposed to [*, M] bf16)
+            def head_wgrad():     # dW2, db2; dW1 = dhid^T . hs  (operands transposed to [*, M] bf16)
+                engine.head_bwd(td["dq"], ws["hid_on"], w, None, g.head_w2, g.head_b2)
                 engine.transpose_cast_bf16(ws["dhid"], ws["dhidT16"])
                 engine.transpose_cast_bf16(hs_learn, ws["hsT16"])
                 engine.tc_linear(ws["dhidT16"], ws["hsT16"], None, None, y32=g.head_w1)
