@@ -10,9 +10,9 @@
 // Forward contractions are error-compensated bf16x3 (W_hi.h_hi + W_lo.h_hi + W_hi.h_lo, fp32
 // accumulation in TMEM) -- see DESIGN.md section 2 for why the forward pass needs this.
 //
-// 320 threads: warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2-5 = TMEM
-// readers (gate q = warp % 4 sits in lanes 32q..32q+15 of the M=64 accumulator layout),
-// warps 2-9 = pointwise cell update (thread -> batch row b, 4 hidden units).
+// 416 threads: warp 0 = bulk-copy producer, warps 1,10,11,12 = MMA issuers (warp 1 also owns the
+// TMEM allocation), warps 2-5 = TMEM readers (gate q = warp % 4 sits in lanes 32q..32q+15 of the
+// M=64 accumulator layout), warps 2-9 = pointwise cell update (thread -> batch row, 2-4 units).
 #include <cuda.h>
 #include <cuda_bf16.h>
 
@@ -99,12 +99,19 @@ template <int N> __device__ __forceinline__ void st_bf16_hilo(__nv_bfloat16* hi,
 // NB = batch columns per CTA (UMMA N).  Batch rows never interact, so the B/NB batch groups are
 // independent chains with their own arrive counter: a smaller NB spreads one chain over more SMs
 // (less h traffic, MMA time and pointwise work per CTA per step).
-constexpr int LS_ISSUERS = 4;   // MMA-issuing warps: 1, 10, 11, 12 (k-blocks kb % 4 == i)
+constexpr int LS_ISSUERS = 4;   // MMA-issuing warps: 1, 10, 11, 12 (load groups g % 4 == i)
 
 template <int NB>
 __global__ void __launch_bounds__(416, 1)
-tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_h, const LstmArgs a) {
-    constexpr int STAGES = 256 / NB;                            // 64 -> 4, 32 -> 8 (whole h in flight)
+tc_lstm_fwd_kernel(const LstmArgs a) {
+    // h ring: 64 KB = 4 slots of 16 KB.  A slot is a LOAD GROUP of KBG consecutive k-blocks
+    // ((hi|lo) tiles, NB rows x 128 B each), contiguous and already swizzled in global memory, so
+    // it arrives with ONE 1-D bulk copy on ONE mbarrier: every mbarrier operation of the
+    // producer thread costs 30-250 ns on this critical path (tools/ubench/tma_fanin.cu).
+    // NB = 32: the ring holds the whole h of a step (H <= 512), so a slot is never reused within
+    // a step and the grid barrier already proves it free: no "slot empty" barriers at all.
+    constexpr int KBG = NB == 32 ? 2 : 1, STAGES = 4;
+    constexpr bool WHOLE = NB == 32;
     constexpr int UPT = LS_UNITS * NB / 256;                    // hidden units per pointwise thread
     // W_hi multiplies both h_hi and h_lo: with NB = 32 they are ONE MMA of N = 64 against the
     // adjacent [h_hi ; h_lo] tiles of a stage (2 MMAs per k-step instead of 3; the tensor pipe and
@@ -132,7 +139,6 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_h, const LstmArgs a) 
     const long long BH = (long long)B * H;
 
     if (tid == 0) {
-        tma_prefetch_desc(&tma_h);
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
@@ -172,9 +178,14 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_h, const LstmArgs a) 
     const int pt = tid - 64;                      // 0..255 for pointwise threads
     constexpr int TPR = LS_UNITS / UPT;           // threads per batch row
     const int pb = pt / TPR, pu = (pt % TPR) * UPT;
-    // offset of (row b0+pb, units u0+pu.., hi) inside one [H/64, groups, 2, NB, 64] bf16 image
-    const long long o16r = (((long long)(u0 >> 6) * gridDim.y + blockIdx.y) * 2 * NB + pb) * 64 + (u0 & 63) + pu;
-    const long long IMG = (long long)NKB * gridDim.y * 2 * NB * 64;
+    // offset of (row b0+pb, units u0+pu.., hi) inside one [groups, H/64, hi|lo, NB, 64] bf16
+    // image; the 16-byte chunks of a 128-byte row are stored in SWIZZLE_128B order (chunk ^ row%8)
+    // so that a linear bulk copy lands the tile exactly as the UMMA descriptor expects it
+    const int col16 = (u0 & 63) + pu;
+    const long long GRP = (long long)NKB * 2 * NB * 64;          // elements per batch group
+    const long long o16r = (long long)blockIdx.y * GRP + ((long long)(u0 >> 6) * 2 * NB + pb) * 64 +
+                           ((((col16 >> 3) ^ (pb & 7)) << 3) | (col16 & 7));
+    const long long IMG = GRP * gridDim.y;
     __nv_bfloat16* const h16_lo = a.h16 + NB * 64;
     const bool pw = warp >= 2 && warp < 10;
     const bool pvalid = pw && (b0 + pb) < B;
@@ -213,17 +224,18 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_h, const LstmArgs a) 
                 LS_STAMP(0);                                        // barrier passed
                 asm volatile("fence.proxy.async;" ::: "memory");   // generic writes -> TMA reads
                 LS_STAMP(1);
-                for (int kb = 0; kb < NKB; ++kb, ++it) {
+                const uint8_t* img = reinterpret_cast<const uint8_t*>(a.h16 + (long long)p * IMG + (long long)blockIdx.y * GRP);
+                for (int kb = 0; kb < NKB; kb += KBG, ++it) {
                     const int s = it % STAGES;
-                    mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
-                    mbar_expect_tx(&full_bar[s], STAGE);
-                    uint8_t* dst = h_s + (size_t)s * STAGE;
-                    tma_load_2d(dst, &tma_h, 0, ((p * NKB + kb) * (int)gridDim.y + (int)blockIdx.y) * 2 * NB, &full_bar[s]);
+                    const int nk = NKB - kb < KBG ? NKB - kb : KBG;
+                    if constexpr (!WHOLE) mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
+                    mbar_expect_tx(&full_bar[s], nk * STAGE);
+                    bulk_g2s(h_s + (size_t)s * (KBG * STAGE), img + (size_t)kb * STAGE, nk * STAGE, &full_bar[s]);
                 }
             }
         } else if (issuer >= 0) {
             if (lane == 0) {
-                // Four issuing warps, k-blocks kb % 4 == issuer, each accumulating into its own
+                // Four issuing warps, load groups g % 4 == issuer, each accumulating into its own
                 // TMEM slice (the readers add the slices): issuing the 12*NKB small MMAs of a step
                 // from one thread was the critical path (37 ns per MMA, tools/diag_lstm.py).
                 constexpr uint32_t idesc = umma_idesc_bf16(LS_ROWS, NB), idesc2 = umma_idesc_bf16(LS_ROWS, 2 * NB);
@@ -233,28 +245,36 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_h, const LstmArgs a) 
                 const uint64_t dw_lo = dw_hi + (uint64_t)((NKB * W_KB) >> 4);
                 const uint64_t dh0 = umma_desc_k_sw128(smem_u32(h_s));
                 const uint32_t d = tmem_base + issuer * SW;
-                const uint32_t it0 = (uint32_t)t * NKB;             // ring position of k-block 0
-                for (int kb = issuer; kb < NKB; kb += LS_ISSUERS) {
-                    const uint32_t itk = it0 + kb;
+                const int ngrp = (NKB + KBG - 1) / KBG;             // load groups per step
+                const uint32_t it0 = (uint32_t)t * ngrp;            // ring position of group 0
+                for (int g = issuer; g < ngrp; g += LS_ISSUERS) {
+                    const uint32_t itk = it0 + g;
                     const int s = itk % STAGES;
                     mbar_wait(&full_bar[s], (itk / STAGES) & 1);
                     tc_fence_after();
-                    const uint64_t hhi = dh0 + (uint64_t)((s * STAGE) >> 4), hlo = hhi + (H_TILE >> 4);
-                    const uint64_t whi = dw_hi + (uint64_t)((kb * W_KB) >> 4);
-                    const uint64_t wlo = dw_lo + (uint64_t)((kb * W_KB) >> 4);
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        if constexpr (CAT) {
-                            umma_f16(d, whi + 2 * k, hhi + 2 * k, idesc2, (kb >= LS_ISSUERS) | (k != 0));
-                            umma_f16(d, wlo + 2 * k, hhi + 2 * k, idesc, 1);
-                        } else {
-                            umma_f16(d, whi + 2 * k, hhi + 2 * k, idesc, (kb >= LS_ISSUERS) | (k != 0));
-                            umma_f16(d, wlo + 2 * k, hhi + 2 * k, idesc, 1);
-                            umma_f16(d, whi + 2 * k, hlo + 2 * k, idesc, 1);
+                    for (int j = 0; j < KBG; ++j) {
+                        const int kb = g * KBG + j;
+                        if (kb < NKB) {
+                            const uint64_t hhi = dh0 + (uint64_t)(((s * KBG + j) * STAGE) >> 4), hlo = hhi + (H_TILE >> 4);
+                            const uint64_t whi = dw_hi + (uint64_t)((kb * W_KB) >> 4);
+                            const uint64_t wlo = dw_lo + (uint64_t)((kb * W_KB) >> 4);
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) {
+                                const uint32_t acc = (g >= LS_ISSUERS) | (j != 0) | (k != 0);
+                                if constexpr (CAT) {
+                                    umma_f16(d, whi + 2 * k, hhi + 2 * k, idesc2, acc);
+                                    umma_f16(d, wlo + 2 * k, hhi + 2 * k, idesc, 1);
+                                } else {
+                                    umma_f16(d, whi + 2 * k, hhi + 2 * k, idesc, acc);
+                                    umma_f16(d, wlo + 2 * k, hhi + 2 * k, idesc, 1);
+                                    umma_f16(d, whi + 2 * k, hlo + 2 * k, idesc, 1);
+                                }
+                            }
                         }
                     }
-                    umma_commit(&empty_bar[s]);
-                    if (issuer == 0) LS_STAMP(16 + kb);
+                    if constexpr (!WHOLE) umma_commit(&empty_bar[s]);
+                    if (issuer == 0) LS_STAMP(16 + g);
                 }
                 if (issuer == 0) LS_STAMP(2);
                 umma_commit(&acc_full);                             // LS_ISSUERS arrivals complete it
@@ -281,7 +301,8 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_h, const LstmArgs a) 
                 }
                 named_bar_sync(3, 128);
                 tc_fence_after();
-                const int nslices = NKB < LS_ISSUERS ? NKB : LS_ISSUERS;   // issuers that ran MMAs
+                const int ngrp_r = (NKB + KBG - 1) / KBG;
+                const int nslices = ngrp_r < LS_ISSUERS ? ngrp_r : LS_ISSUERS;   // issuers that ran MMAs
                 float acc[NB];
 #pragma unroll
                 for (int j = 0; j < NB; ++j) acc[j] = 0.f;
@@ -357,11 +378,12 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tma_h, const LstmArgs a) 
 // BPTT over the learn window, persistent, plain bf16 operands (backward contractions do not
 // need the compensation).  Per step (t descending)
 //   dh[B, u] = dhs_t[B, u] + dG_{t+1}[B, 4H] . W_hh[4H, u]
-// with CTA c owning 16 hidden units u: A = dG_{t+1} (M = 64 batch rows, streamed by TMA from a
-// bf16 ping-pong buffer every CTA writes its columns of), B = its W_hh^T slice [16, 4H] resident
-// in shared memory, D[64, 16] in TMEM.  In the M=64 accumulator layout batch row m sits in lane
-// (m%16) + 32*(m/16), so reader thread (warp q, lane < 16) owns batch row 16q+lane and all 16
-// units: the gate-gradient math runs right there, dL/dc stays in registers across steps.
+// with CTA c owning 16 hidden units u: A = dG_{t+1} (M = 64 batch rows, pulled in by four bulk
+// copies per step from a bf16 ping-pong image every CTA writes its columns of), B = its W_hh^T
+// slice [16, 4H] resident in shared memory, D[64, 16] in TMEM.  In the M=64 accumulator layout
+// batch row m sits in lane (m%16) + 32*(m/16): those lanes read the recurrent term and hand it
+// over through shared memory, then all 128 reader threads do the gate-gradient math (thread ->
+// batch row, 4 or 8 units; dL/dc stays in registers across steps).
 struct LstmBwdArgs {
     const float* dhs;      // [T, B, H] dL/dh_t from the head
     const float* w_hh;     // [4H, H]
@@ -383,14 +405,22 @@ constexpr int LB_RING_BYTES = 128 * 1024;   // A-tile ring: with NB = 32 a whole
 // the A tile is never filled and its accumulator rows are ignored (rows are independent).
 template <int NB>
 __global__ void __launch_bounds__(288, 1)
-tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs a) {
-    // ring stage = NB rows x 128 B.  The UMMA reads 64 rows: with NB = 32 the upper half of a tile
-    // aliases the next stage (or the pad behind the ring) and only feeds ignored accumulator rows.
-    constexpr int LB_STAGES = LB_RING_BYTES / (NB * 128);
+tc_lstm_bwd_kernel(const LstmBwdArgs a) {
+    // A tile = NB rows x 128 B.  The UMMA reads 64 rows: with NB = 32 the upper half of a tile
+    // aliases the next tile (or the pad behind the ring) and only feeds ignored accumulator rows.
+    // Ring = 4 slots of 32 KB; a slot is a LOAD GROUP of kpg consecutive k-block tiles, contiguous
+    // and pre-swizzled in global memory: one bulk copy and one mbarrier per group (see the forward
+    // kernel).  NB = 32: 4 groups = the whole dG of a step (H <= 512), no "slot empty" barriers.
+    constexpr int LB_STAGES = 4;
+    constexpr uint32_t SLOT = LB_RING_BYTES / LB_STAGES;
+    constexpr bool WHOLE = NB == 32;
     const int H = a.H, B = a.B, K4 = 4 * a.H, NKB = K4 / 64;
+    const int kpg = WHOLE ? NKB / 4 : (NKB >= 8 ? NKB / 8 : 1);   // tiles per load group (<= 32 KB)
+    const int ngrp = NKB / kpg;
     extern __shared__ uint8_t smem_raw[];
     __shared__ uint64_t full_bar[LB_STAGES], empty_bar[LB_STAGES], acc_full, acc_empty;
     __shared__ uint32_t tmem_slot;
+    __shared__ __align__(16) float R[64][20];                   // recurrent term, row stride 20: conflict-free float4
     const uint32_t raw = smem_u32(smem_raw);
     uint8_t* base = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
     const uint32_t W_KB = LS_UNITS * 128;                       // 16 rows x 64 bf16 = 2 KB
@@ -402,10 +432,11 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
     const int u0 = blockIdx.x * LS_UNITS, b0 = blockIdx.y * NB;
     const int ncta = gridDim.x;
     int* counter = a.counter + blockIdx.y;
-    const long long BH = (long long)B * H, BG = (long long)B * K4;
+    const long long BH = (long long)B * H;
+    const long long GRP = (long long)NKB * NB * 64;             // dg16 image: [groups][NKB][NB][64]
+    const long long IMG = GRP * gridDim.y;
 
     if (tid == 0) {
-        tma_prefetch_desc(&tma_dg);
         for (int s = 0; s < LB_STAGES; ++s) {
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
@@ -432,12 +463,19 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
     tc_fence_after();
     const uint32_t tmem_base = tmem_slot;
 
-    const int q = warp & 3;                                     // readers: warps 2..5
-    const int rb = b0 + q * 16 + lane;                          // batch row of this reader thread
-    const bool rvalid = warp >= 2 && warp < 6 && lane < 16 && q * 16 < NB && rb < B;
-    float dc_reg[LS_UNITS];
+    // warps 2..5: TMEM readers (lane < 16 of warp q = warp % 4 owns accumulator row 16q + lane)
+    // hand the recurrent term over through shared memory, then all 128 threads do the gate-gradient
+    // math: thread -> batch row mr and EPT consecutive hidden units (dL/dc stays in registers)
+    const int q = warp & 3;
+    const bool treader = warp >= 2 && warp < 6 && q * 16 < NB;   // warp-uniform: tcgen05.ld is warp-wide
+    constexpr int EPT = NB / 8, TPR = LS_UNITS / EPT;           // 4 or 8 units per thread
+    const int mi = tid - 64;
+    const int mr = mi / TPR, mu = (mi % TPR) * EPT;
+    const int rb = b0 + mr;
+    const bool rvalid = warp >= 2 && warp < 6 && rb < B;
+    float dc_reg[EPT];
 #pragma unroll
-    for (int j = 0; j < LS_UNITS; ++j) dc_reg[j] = 0.f;
+    for (int j = 0; j < EPT; ++j) dc_reg[j] = 0.f;
 
     uint32_t it = 0;
     for (int s = 0; s < a.T; ++s) {
@@ -451,12 +489,12 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
                 LB_STAMP(0);                                    // barrier passed
                 asm volatile("fence.proxy.async;" ::: "memory");
                 const int p = (s - 1) & 1;
-                for (int kb = 0; kb < NKB; ++kb, ++it) {
+                const uint8_t* img = reinterpret_cast<const uint8_t*>(a.dg16 + (long long)p * IMG + (long long)blockIdx.y * GRP);
+                for (int g = 0; g < ngrp; ++g, ++it) {
                     const int st = it % LB_STAGES;
-                    mbar_wait(&empty_bar[st], ((it / LB_STAGES) & 1) ^ 1);
-                    mbar_expect_tx(&full_bar[st], NB * 128);
-                    tma_load_2d(a_s + (size_t)st * A_TILE, &tma_dg, 0, (p * NKB + kb) * B + b0, &full_bar[st]);
-                    if (kb == LB_STAGES - 1) LB_STAMP(8);       // first ring fill issued
+                    if constexpr (!WHOLE) mbar_wait(&empty_bar[st], ((it / LB_STAGES) & 1) ^ 1);
+                    mbar_expect_tx(&full_bar[st], kpg * A_TILE);
+                    bulk_g2s(a_s + (size_t)st * SLOT, img + (size_t)g * kpg * A_TILE, kpg * A_TILE, &full_bar[st]);
                 }
                 LB_STAMP(1);                                    // all loads issued
             }
@@ -469,33 +507,36 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
                 const uint64_t db0 = umma_desc_k_sw128(smem_u32(w_s));
                 const uint64_t da0 = umma_desc_k_sw128(smem_u32(a_s));
                 const uint32_t d = tmem_base + issuer * LS_UNITS;
-                const uint32_t it0 = (uint32_t)(s - 1) * NKB;
-                for (int kb = issuer; kb < NKB; kb += LS_ISSUERS) {
-                    const uint32_t itk = it0 + kb;
+                const uint32_t it0 = (uint32_t)(s - 1) * ngrp;
+                for (int g = issuer; g < ngrp; g += LS_ISSUERS) {
+                    const uint32_t itk = it0 + g;
                     const int st = itk % LB_STAGES;
                     mbar_wait(&full_bar[st], (itk / LB_STAGES) & 1);
                     tc_fence_after();
-                    if (issuer == 0 && kb == 0) LB_STAMP(9);    // first tile landed
-                    if (issuer == 3 && kb == NKB - 1) LB_STAMP(10);   // last tile landed
-                    const uint64_t aa = da0 + (uint64_t)((st * A_TILE) >> 4);
-                    const uint64_t bb = db0 + (uint64_t)((kb * W_KB) >> 4);
+                    if (g == 0) LB_STAMP(9);                    // first group landed
+                    if (g == ngrp - 1) LB_STAMP(10);            // last group landed
+                    for (int j = 0; j < kpg; ++j) {
+                        const int kb = g * kpg + j;
+                        const uint64_t aa = da0 + (uint64_t)((st * SLOT + j * A_TILE) >> 4);
+                        const uint64_t bb = db0 + (uint64_t)((kb * W_KB) >> 4);
 #pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        umma_f16(d, aa + 2 * k, bb + 2 * k, idesc, (kb >= LS_ISSUERS) | (k != 0));
-                    umma_commit(&empty_bar[st]);
+                        for (int k = 0; k < 4; ++k)
+                            umma_f16(d, aa + 2 * k, bb + 2 * k, idesc, (g >= LS_ISSUERS) | (j != 0) | (k != 0));
+                    }
+                    if constexpr (!WHOLE) umma_commit(&empty_bar[st]);
                 }
                 umma_commit(&acc_full);
-                if (issuer == 3) LB_STAMP(2);                   // last MMA issued
+                if (issuer == (ngrp - 1) % LS_ISSUERS) LB_STAMP(2);   // last MMA issued
             }
         } else if (warp >= 2 && warp < 6) {
-            // ---- readers + gate-gradient math (64 active threads per CTA).  Everything that does
-            //      not depend on the recurrent term is loaded BEFORE waiting for the accumulator.
-            float gi[16], gf[16], gg[16], go[16], ct[16], cp[16], dh[16];
-            const long long o = (long long)rb * H + u0;
+            // ---- everything that does not depend on the recurrent term is loaded BEFORE waiting
+            //      for the accumulator
+            float gi[EPT], gf[EPT], gg[EPT], go[EPT], ct[EPT], cp[EPT], dh[EPT];
+            const long long o = (long long)rb * H + u0 + mu;
             if (rvalid) {
-                const float* gp = a.gates + ((long long)t * B + rb) * K4 + u0;
+                const float* gp = a.gates + ((long long)t * B + rb) * K4 + u0 + mu;
 #pragma unroll
-                for (int j = 0; j < 16; j += 4) {
+                for (int j = 0; j < EPT; j += 4) {
                     *reinterpret_cast<float4*>(gi + j) = __ldg(reinterpret_cast<const float4*>(gp + j));
                     *reinterpret_cast<float4*>(gf + j) = __ldg(reinterpret_cast<const float4*>(gp + H + j));
                     *reinterpret_cast<float4*>(gg + j) = __ldg(reinterpret_cast<const float4*>(gp + 2 * H + j));
@@ -505,9 +546,9 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
                     *reinterpret_cast<float4*>(dh + j) = __ldg(reinterpret_cast<const float4*>(a.dhs + (long long)t * BH + o + j));
                 }
             }
-            float rec[LS_UNITS];
+            float rec[EPT];
 #pragma unroll
-            for (int j = 0; j < LS_UNITS; ++j) rec[j] = 0.f;
+            for (int j = 0; j < EPT; ++j) rec[j] = 0.f;
             if (s > 0) {
                 if (tid == 64) {
                     mbar_wait_sleep(&acc_full, (s - 1) & 1, 32);
@@ -515,22 +556,33 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
                 }
                 named_bar_sync(3, 128);
                 tc_fence_after();
-                uint32_t ra[32], rb2[32];
-                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16), ra);
-                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + 32, rb2);
-                tmem_ld_wait();
+                if (treader) {
+                    uint32_t ra[32], rb2[32];
+                    tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16), ra);
+                    tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + 32, rb2);
+                    tmem_ld_wait();
+                    float* dst = &R[q * 16 + (lane & 15)][0];
+                    if (lane < 16)
+#pragma unroll
+                    for (int j = 0; j < LS_UNITS; j += 4)
+                        *reinterpret_cast<float4*>(dst + j) = make_float4(
+                            (__uint_as_float(ra[j]) + __uint_as_float(ra[16 + j])) + (__uint_as_float(rb2[j]) + __uint_as_float(rb2[16 + j])),
+                            (__uint_as_float(ra[j + 1]) + __uint_as_float(ra[17 + j])) + (__uint_as_float(rb2[j + 1]) + __uint_as_float(rb2[17 + j])),
+                            (__uint_as_float(ra[j + 2]) + __uint_as_float(ra[18 + j])) + (__uint_as_float(rb2[j + 2]) + __uint_as_float(rb2[18 + j])),
+                            (__uint_as_float(ra[j + 3]) + __uint_as_float(ra[19 + j])) + (__uint_as_float(rb2[j + 3]) + __uint_as_float(rb2[19 + j])));
+                }
                 tc_fence_before();
                 mbar_arrive(&acc_empty);
-                if (tid == 64) LB_STAMP(4);                     // TMEM read
+                named_bar_sync(4, 128);                          // R complete
+                if (tid == 64) LB_STAMP(4);                     // TMEM read + hand-over
 #pragma unroll
-                for (int j = 0; j < LS_UNITS; ++j)
-                    rec[j] = (__uint_as_float(ra[j]) + __uint_as_float(ra[16 + j])) +
-                             (__uint_as_float(rb2[j]) + __uint_as_float(rb2[16 + j]));
+                for (int j = 0; j < EPT; j += 4)
+                    *reinterpret_cast<float4*>(rec + j) = *reinterpret_cast<const float4*>(&R[mr][mu + j]);
             }
-            float di[16], df[16], dg[16], dov[16];
+            float di[EPT], df[EPT], dg[EPT], dov[EPT];
             if (rvalid) {
 #pragma unroll
-                for (int j = 0; j < 16; ++j) {
+                for (int j = 0; j < EPT; ++j) {
                     const float d = dh[j] + rec[j];
                     const float tc = ls_tanh(ct[j]);
                     const float dc = dc_reg[j] + d * go[j] * (1.f - tc * tc);
@@ -540,15 +592,22 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
                     dov[j] = d * tc * go[j] * (1.f - go[j]);
                     dc_reg[j] = dc * gf[j];
                 }
-                // bf16 image the next step's TMA reads: gate g, units u0.. = k-block g*H/64 + u0/64
-                __nv_bfloat16* d16 = a.dg16 + (long long)(s & 1) * BG + ((long long)(u0 >> 6) * B + rb) * 64 + (u0 & 63);
-                const long long gstep = (long long)(H >> 6) * B * 64;
-#pragma unroll
-                for (int j = 0; j < 16; j += 8) {
-                    *reinterpret_cast<uint4*>(d16 + j) = make_uint4(ls_pack(di[j], di[j + 1]), ls_pack(di[j + 2], di[j + 3]), ls_pack(di[j + 4], di[j + 5]), ls_pack(di[j + 6], di[j + 7]));
-                    *reinterpret_cast<uint4*>(d16 + gstep + j) = make_uint4(ls_pack(df[j], df[j + 1]), ls_pack(df[j + 2], df[j + 3]), ls_pack(df[j + 4], df[j + 5]), ls_pack(df[j + 6], df[j + 7]));
-                    *reinterpret_cast<uint4*>(d16 + 2 * gstep + j) = make_uint4(ls_pack(dg[j], dg[j + 1]), ls_pack(dg[j + 2], dg[j + 3]), ls_pack(dg[j + 4], dg[j + 5]), ls_pack(dg[j + 6], dg[j + 7]));
-                    *reinterpret_cast<uint4*>(d16 + 3 * gstep + j) = make_uint4(ls_pack(dov[j], dov[j + 1]), ls_pack(dov[j + 2], dov[j + 3]), ls_pack(dov[j + 4], dov[j + 5]), ls_pack(dov[j + 6], dov[j + 7]));
+                // bf16 image the next step's bulk copies read: gate g, units u0.. = k-block
+                // g*H/64 + u0/64; 16-byte chunks in SWIZZLE_128B order (chunk ^ row%8)
+                const int col = (u0 & 63) + mu;
+                __nv_bfloat16* d16 = a.dg16 + (long long)(s & 1) * IMG + (long long)blockIdx.y * GRP +
+                                     ((long long)(u0 >> 6) * NB + mr) * 64 + ((((col >> 3) ^ (mr & 7)) << 3) | (col & 7));
+                const long long gstep = (long long)(H >> 6) * NB * 64;
+                if constexpr (EPT == 4) {
+                    *reinterpret_cast<uint2*>(d16) = make_uint2(ls_pack(di[0], di[1]), ls_pack(di[2], di[3]));
+                    *reinterpret_cast<uint2*>(d16 + gstep) = make_uint2(ls_pack(df[0], df[1]), ls_pack(df[2], df[3]));
+                    *reinterpret_cast<uint2*>(d16 + 2 * gstep) = make_uint2(ls_pack(dg[0], dg[1]), ls_pack(dg[2], dg[3]));
+                    *reinterpret_cast<uint2*>(d16 + 3 * gstep) = make_uint2(ls_pack(dov[0], dov[1]), ls_pack(dov[2], dov[3]));
+                } else {
+                    *reinterpret_cast<uint4*>(d16) = make_uint4(ls_pack(di[0], di[1]), ls_pack(di[2], di[3]), ls_pack(di[4], di[5]), ls_pack(di[6], di[7]));
+                    *reinterpret_cast<uint4*>(d16 + gstep) = make_uint4(ls_pack(df[0], df[1]), ls_pack(df[2], df[3]), ls_pack(df[4], df[5]), ls_pack(df[6], df[7]));
+                    *reinterpret_cast<uint4*>(d16 + 2 * gstep) = make_uint4(ls_pack(dg[0], dg[1]), ls_pack(dg[2], dg[3]), ls_pack(dg[4], dg[5]), ls_pack(dg[6], dg[7]));
+                    *reinterpret_cast<uint4*>(d16 + 3 * gstep) = make_uint4(ls_pack(dov[0], dov[1]), ls_pack(dov[2], dov[3]), ls_pack(dov[4], dov[5]), ls_pack(dov[6], dov[7]));
                 }
             }
             if (tid == 64) LB_STAMP(5);                         // gate math + bf16 stores issued
@@ -560,9 +619,9 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
             }
             // fp32 gradients for the kernels after the unroll, behind the releasing arrive
             if (rvalid) {
-                float* dgp = a.dgates + ((long long)t * B + rb) * K4 + u0;
+                float* dgp = a.dgates + ((long long)t * B + rb) * K4 + u0 + mu;
 #pragma unroll
-                for (int j = 0; j < 16; j += 4) {
+                for (int j = 0; j < EPT; j += 4) {
                     *reinterpret_cast<float4*>(dgp + j) = make_float4(di[j], di[j + 1], di[j + 2], di[j + 3]);
                     *reinterpret_cast<float4*>(dgp + H + j) = make_float4(df[j], df[j + 1], df[j + 2], df[j + 3]);
                     *reinterpret_cast<float4*>(dgp + 2 * H + j) = make_float4(dg[j], dg[j + 1], dg[j + 2], dg[j + 3]);
@@ -574,33 +633,6 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tma_dg, const LstmBwdArgs
     tc_fence_before();
     __syncthreads();
     if (warp == 1) tmem_dealloc(tmem_base, 64);
-}
-
-typedef CUresult (*EncodeTiledFn2)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
-                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
-                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static int make_h_tmap(CUtensorMap* tm, const void* base, long long rows, long long cols,
-                       int box_rows = LS_NB) {
-    static EncodeTiledFn2 fn = nullptr;
-    if (!fn) {
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
-            q == cudaDriverEntryPointSuccess)
-            fn = reinterpret_cast<EncodeTiledFn2>(p);
-    }
-    R2D2_REQUIRE(fn, "tc_lstm: cuTensorMapEncodeTiled is unavailable in this driver");
-    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-    cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
-    cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
-    cuuint32_t estr[2] = {1, 1};
-    CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box,
-                    estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    R2D2_REQUIRE(r == CUDA_SUCCESS, "tc_lstm: cuTensorMapEncodeTiled failed with %d", (int)r);
-    return R2D2_OK;
 }
 
 }  // namespace r2d2
@@ -653,9 +685,6 @@ int r2d2_tc_lstm_seq_fwd(const float* xprojT, int64_t ldx, int64_t col0, const f
     const int groups = (B + nb - 1) / nb;
     R2D2_REQUIRE(groups <= 64, "tc_lstm_seq_fwd: batch too large");
     R2D2_CUDA_OK(cudaMemsetAsync(a.counter, 0, 256, st));
-    CUtensorMap th;
-    int rc = make_h_tmap(&th, a.h16, 2ll * (H / 64) * groups * 2 * nb, 64, 2 * nb);
-    if (rc) return rc;
     const int smem = 2 * NKB * LS_ROWS * 128 + (256 / nb) * 2 * nb * 128 + 1024;
     void* kern = nb == 32 ? (void*)tc_lstm_fwd_kernel<32> : (void*)tc_lstm_fwd_kernel<64>;
     R2D2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -663,7 +692,7 @@ int r2d2_tc_lstm_seq_fwd(const float* xprojT, int64_t ldx, int64_t col0, const f
     R2D2_REQUIRE((int)(grid.x * grid.y) <= sm_count(),
                  "tc_lstm_seq_fwd: %d CTAs must be co-resident but the device has %d SMs",
                  grid.x * grid.y, sm_count());
-    void* params[] = {&th, &a};
+    void* params[] = {&a};
     {
         ProfScope ps("tc_lstm_fwd_kernel", st);
         R2D2_CUDA_OK(cudaLaunchCooperativeKernel(kern, grid, dim3(416), params, (size_t)smem, st));
@@ -676,8 +705,9 @@ int r2d2_tc_lstm_seq_fwd(const float* xprojT, int64_t ldx, int64_t col0, const f
 extern "C" {
 
 int64_t r2d2_tc_lstm_bwd_scratch_bytes(int B, int H) {
-    const int64_t dg16 = ((int64_t)2 * B * 4 * H * 2 + 255) / 256 * 256;
-    return dg16 + 256;
+    // dG ping-pong [2, groups, 4H/64, NB, 64] bf16 (batch padded to whole 64-row groups) + counters
+    const int64_t Bp = ((int64_t)B + 63) / 64 * 64;
+    return 2 * Bp * 4 * H * 2 + 256;
 }
 
 int r2d2_tc_lstm_seq_bwd(const float* dhs, const float* w_hh, const float* gates,
@@ -690,7 +720,7 @@ int r2d2_tc_lstm_seq_bwd(const float* dhs, const float* w_hh, const float* gates
                      ((uintptr_t)dgates % 16) == 0 && ((uintptr_t)scratch % 256) == 0,
                  "tc_lstm_seq_bwd: misaligned buffer");
     cudaStream_t st = as_stream(stream);
-    const int64_t dg16 = ((int64_t)2 * B * 4 * H * 2 + 255) / 256 * 256;
+    const int64_t dg16 = r2d2_tc_lstm_bwd_scratch_bytes(B, H) - 256;
     uint8_t* sc = static_cast<uint8_t*>(scratch);
     LstmBwdArgs a;
     a.dhs = dhs; a.w_hh = w_hh; a.gates = gates; a.cs_ext = cs_ext; a.dgates = dgates;
@@ -703,16 +733,13 @@ int r2d2_tc_lstm_seq_bwd(const float* dhs, const float* w_hh, const float* gates
     const int groups = (B + nb - 1) / nb;
     R2D2_REQUIRE(groups <= 64, "tc_lstm_seq_bwd: batch too large");
     R2D2_CUDA_OK(cudaMemsetAsync(a.counter, 0, 256, st));
-    CUtensorMap tdg;
-    int rc = make_h_tmap(&tdg, a.dg16, 2ll * (4 * H / 64) * B, 64, nb);
-    if (rc) return rc;
     const int NKB = 4 * H / 64;
     const int smem = NKB * LS_UNITS * 128 + LB_RING_BYTES + 4096 + 1024;
     void* kern = nb == 32 ? (void*)tc_lstm_bwd_kernel<32> : (void*)tc_lstm_bwd_kernel<64>;
     R2D2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     dim3 grid(H / LS_UNITS, groups);
     R2D2_REQUIRE((int)(grid.x * grid.y) <= sm_count(), "tc_lstm_seq_bwd: %d CTAs must be co-resident", grid.x * grid.y);
-    void* params[] = {&tdg, &a};
+    void* params[] = {&a};
     {
         ProfScope ps("tc_lstm_bwd_kernel", st);
         R2D2_CUDA_OK(cudaLaunchCooperativeKernel(kern, grid, dim3(288), params, (size_t)smem, st));

@@ -29,10 +29,10 @@ torch.cuda.synchronize()
 _lib.call("r2d2_tc_lstm_set_trace", None)
 tr = trace.cpu().double()[5:35]
 print(f"steady-state step period {float((tr[1:, 0] - tr[:-1, 0]).mean()):.0f} ns")
-names = {0: "barrier passed", 8: "first ring fill issued", 1: "all loads issued", 9: "first tile landed",
-         10: "last tile landed", 2: "last MMA issued", 3: "accumulators complete", 4: "TMEM read",
+names = {0: "barrier passed", 1: "all loads issued", 9: "first group landed",
+         10: "last group landed", 2: "last MMA issued", 3: "accumulators complete", 4: "TMEM read",
          5: "gate math + stores issued", 6: "CTA barrier", 7: "arrive issued"}
 # stamps 3..7 of iteration s belong to the recurrent term loaded in iteration s (same s)
-for k in (8, 1, 9, 10, 2, 3, 4, 5, 6, 7):
+for k in (1, 9, 10, 2, 3, 4, 5, 6, 7):
     print(f"  {names[k]:>28s}  +{float((tr[:, k] - tr[:, 0]).mean()):8.0f} ns after the barrier")
 print(f"  {'next barrier passed':>28s}  +{float((tr[1:, 0] - tr[:-1, 0]).mean()):8.0f} ns")
