@@ -85,18 +85,26 @@ __device__ __forceinline__ void gather_chunks(const T* __restrict__ src, const i
     }
 }
 
-template <class T, int CIN, int KH, int HIN, int HOUT, int STRIDE>
+// NW = 2 (conv1 on the u8 slab only): TWO networks' first layers in one pass.  The online and the
+// target net read the same frames, and the kernel is bound by the producers' gather, so the A
+// tile is built once and multiplied against both weight sets stacked along N (one N = 128 MMA per
+// k-step); net 1 skips the first `skip1` frames (its window starts later) and writes out1.
+template <class T, int CIN, int KH, int HIN, int HOUT, int STRIDE, int NW = 1>
 __global__ void __launch_bounds__(416, 1)
 tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __restrict__ w,
                    const float* __restrict__ bias, float* __restrict__ out, const int R,
-                   const float in_scale) {
+                   const float in_scale, const float* __restrict__ w1 = nullptr,
+                   const float* __restrict__ bias1 = nullptr, float* __restrict__ out1 = nullptr,
+                   const int skip1 = 0) {
     constexpr int K = CIN * KH * KH, NKB = (K + 63) / 64, KP = NKB * 64;
     constexpr int P = HOUT * HOUT, COUT = 32;
     constexpr bool NEED_LO = sizeof(T) != 1;                 // u8 pixels are exact in bf16
+    static_assert(NW == 1 || !NEED_LO, "the two-network pass is for the u8 first layer");
     constexpr uint32_t A_TILE = 128 * 128;                   // 128 rows x 64 bf16
     constexpr uint32_t STAGE_BYTES = NEED_LO ? 2 * A_TILE : A_TILE;
     constexpr uint32_t W_KB = COUT * 128;                    // 32 rows x 64 bf16 per k-block and half
-    constexpr uint32_t W_BYTES = 2 * NKB * W_KB;             // per k-block: [hi rows | lo rows]
+    constexpr uint32_t W_BYTES = NW * 2 * NKB * W_KB;        // per k-block: NW x [hi rows | lo rows]
+    constexpr uint32_t ACC_COLS = NW * 2 * COUT;             // accumulator columns per buffer
     constexpr int MMA_WARP = 8;
     extern __shared__ uint8_t smem_raw[];
     __shared__ uint64_t full_bar[CV_STAGES], empty_bar[CV_STAGES], acc_full[2], acc_empty[2];
@@ -123,19 +131,22 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
         }
         mbar_fence_init();
     }
-    for (int i = tid; i < COUT * (KP / 8); i += blockDim.x) {
-        const int co = i / (KP / 8), ch = i - co * (KP / 8);  // chunk of 8 k's
+    for (int i = tid; i < NW * COUT * (KP / 8); i += blockDim.x) {
+        const int net = i / (COUT * (KP / 8)), i2 = i - net * (COUT * (KP / 8));
+        const int co = i2 / (KP / 8), ch = i2 - co * (KP / 8);  // chunk of 8 k's
         const int kb = ch >> 3, c = ch & 7;
+        const float* wsrc = net == 0 ? w : w1;
         float v[8], l[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
             const int k = ch * 8 + e;
-            const float x = k < K ? __ldg(w + (long long)co * K + k) : 0.f;
+            const float x = k < K ? __ldg(wsrc + (long long)co * K + k) : 0.f;
             v[e] = x;
             l[e] = x - bf16_round(x);
         }
-        // rows 0..31 of the k-block tile = W_hi, rows 32..63 = W_lo: ONE 64-row K-major operand
-        const uint32_t off = (uint32_t)kb * 2 * W_KB + sw128_off(co, c);
+        // rows 0..31 of a net's k-block tile = W_hi, rows 32..63 = W_lo: ONE K-major operand of
+        // 64*NW rows (1 KB swizzle atoms of 8 rows, so the per-net 8 KB offset keeps the pattern)
+        const uint32_t off = (uint32_t)(kb * NW + net) * 2 * W_KB + sw128_off(co, c);
         *reinterpret_cast<uint4*>(w_s + off) = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
                                                          pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
         *reinterpret_cast<uint4*>(w_s + off + W_KB) =
@@ -143,7 +154,7 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
                        pack_bf16x2(l[6], l[7]));
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // weights -> tensor-core proxy
-    if (warp == MMA_WARP) tmem_alloc(&tmem_slot, 128);                     // 2 buffers x (32 + 32) columns
+    if (warp == MMA_WARP) tmem_alloc(&tmem_slot, 2 * ACC_COLS);            // 2 buffers x NW x (32 + 32) columns
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -263,20 +274,20 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
             // issues one every ~37 ns, so the count matters: A_hi multiplies both W_hi and W_lo,
             // hence ONE MMA with N = 64 against the stacked [W_hi ; W_lo] rows (columns 0-31 and
             // 32-63 of the accumulator, added in the epilogue) instead of two with N = 32.
-            constexpr uint32_t idesc64 = umma_idesc_bf16(128, 2 * COUT), idesc32 = umma_idesc_bf16(128, COUT);
+            constexpr uint32_t idesc64 = umma_idesc_bf16(128, ACC_COLS), idesc32 = umma_idesc_bf16(128, COUT);
             const uint32_t wb = smem_u32(w_s);
             uint32_t it = 0, tcount = 0;
             for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++tcount) {
                 const uint32_t buf = tcount & 1, use = tcount >> 1;
                 mbar_wait(&acc_empty[buf], (use & 1) ^ 1);           // epilogue drained this buffer
                 tc_fence_after();
-                const uint32_t d = tmem_base + buf * 2 * COUT;
+                const uint32_t d = tmem_base + buf * ACC_COLS;
                 for (int kb = 0; kb < NKB; ++kb, ++it) {
                     const int s = it % CV_STAGES;
                     mbar_wait(&full_bar[s], (it / CV_STAGES) & 1);
                     tc_fence_after();
                     const uint32_t a_hi = smem_u32(a_s + (size_t)s * STAGE_BYTES), a_lo = a_hi + A_TILE;
-                    const uint32_t b_hl = wb + kb * 2 * W_KB;        // [W_hi ; W_lo] of this k-block
+                    const uint32_t b_hl = wb + kb * NW * 2 * W_KB;   // [W_hi ; W_lo] (x NW) of this k-block
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {
                         umma_f16(d, umma_desc_k_sw128(a_hi + k * 32), umma_desc_k_sw128(b_hl + k * 32),
@@ -298,27 +309,34 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
             const uint32_t buf = tcount & 1, use = tcount >> 1;
             mbar_wait(&acc_full[buf], use & 1);
             tc_fence_after();
-            uint32_t r[32], r2[32];
-            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + buf * 2 * COUT, r);
-            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + buf * 2 * COUT + COUT, r2);
-            tmem_ld_wait();
-#pragma unroll
-            for (int c = 0; c < 32; ++c) r[c] = __float_as_uint(__uint_as_float(r[c]) + __uint_as_float(r2[c]));
-            tc_fence_before();
-            mbar_arrive(&acc_empty[buf]);
             const long long m = (long long)tile * 128 + q * 32 + lane;
-            if (m < Mtot) {
-                const int fr = (int)(m / P), p = (int)(m - (long long)fr * P);
-                float* o = out + (long long)fr * COUT * P + p;
+            const int fr = (int)(m / P), p = (int)(m - (long long)fr * P);
 #pragma unroll
-                for (int co = 0; co < COUT; ++co)
-                    o[(long long)co * P] = fmaxf(fmaf(__uint_as_float(r[co]), in_scale, __ldg(bias + co)), 0.f);
+            for (int net = 0; net < NW; ++net) {
+                uint32_t r[32], r2[32];
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + buf * ACC_COLS + net * 2 * COUT, r);
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + buf * ACC_COLS + net * 2 * COUT + COUT, r2);
+                tmem_ld_wait();
+#pragma unroll
+                for (int c = 0; c < 32; ++c) r[c] = __float_as_uint(__uint_as_float(r[c]) + __uint_as_float(r2[c]));
+                if (net == NW - 1) {
+                    tc_fence_before();
+                    mbar_arrive(&acc_empty[buf]);
+                }
+                const int fo = net == 0 ? fr : fr - skip1;         // net 1 starts skip1 frames later
+                if (m < Mtot && fo >= 0) {
+                    float* o = (net == 0 ? out : out1) + (long long)fo * COUT * P + p;
+                    const float* bs = net == 0 ? bias : bias1;
+#pragma unroll
+                    for (int co = 0; co < COUT; ++co)
+                        o[(long long)co * P] = fmaxf(fmaf(__uint_as_float(r[co]), in_scale, __ldg(bs + co)), 0.f);
+                }
             }
         }
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == MMA_WARP) tmem_dealloc(tmem_base, 128);
+    if (warp == MMA_WARP) tmem_dealloc(tmem_base, 2 * ACC_COLS);
 }
 
 template <class T, int CIN, int KH, int HIN, int HOUT, int STRIDE>
@@ -333,7 +351,23 @@ static int launch_tc_conv(const char* name, const T* in, FrameMap fm, const floa
     const int ntiles = (int)((Mtot + 127) / 128);
     int grid = sm_count();
     if (grid > ntiles) grid = ntiles;
-    R2D2_LAUNCH(name, st, kern<<<grid, 416, smem, st>>>(in, fm, w, b, out, R, in_scale));
+    R2D2_LAUNCH(name, st, kern<<<grid, 416, smem, st>>>(in, fm, w, b, out, R, in_scale, nullptr, nullptr, nullptr, 0));
+    return R2D2_OK;
+}
+
+// first conv layer of two networks over the same u8 frames (see the kernel's NW parameter)
+static int launch_tc_conv1_dual(const uint8_t* in, FrameMap fm, const float* wa, const float* ba, float* outa,
+                                const float* wb, const float* bb, float* outb, int R, int skip_b,
+                                cudaStream_t st) {
+    constexpr int NKB = 4;
+    const int smem = 2 * 2 * NKB * 32 * 128 + CV_STAGES * 128 * 128 + 1024;
+    auto kern = tc_conv_fwd_kernel<uint8_t, 4, 8, 84, 20, 4, 2>;
+    R2D2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    const long long Mtot = (long long)R * 400;
+    const int ntiles = (int)((Mtot + 127) / 128);
+    int grid = sm_count();
+    if (grid > ntiles) grid = ntiles;
+    R2D2_LAUNCH("tc_conv1_fwd_dual", st, kern<<<grid, 416, smem, st>>>(in, fm, wa, ba, outa, R, 1.f / 255.f, wb, bb, outb, skip_b));
     return R2D2_OK;
 }
 
@@ -913,6 +947,26 @@ int r2d2_tc_torso_fwd_u8(const uint8_t* slab, int B, int S, int s0, int nt, cons
     R2D2_REQUIRE(B > 0 && nt > 0 && s0 >= 0 && s0 + nt <= S, "tc_torso_fwd: bad frame window");
     return tc_torso_fwd_impl<uint8_t>(slab, FrameMap{B, S, s0, R2D2_FRAME_BYTES}, B * nt, w1, b1, w2, b2,
                                       w3, b3, a1, a2, feat, as_stream(stream));
+}
+
+int r2d2_tc_conv1_fwd_dual_u8(const uint8_t* slab, int B, int S, int nt, const float* w1_a,
+                              const float* b1_a, float* a1_a, const float* w1_b, const float* b1_b,
+                              float* a1_b, int s0_b, void* stream) {
+    R2D2_REQUIRE(slab && w1_a && b1_a && a1_a && w1_b && b1_b && a1_b, "tc_conv1_fwd_dual: null pointer");
+    R2D2_REQUIRE(B > 0 && nt > 0 && nt <= S && s0_b >= 0 && s0_b < nt, "tc_conv1_fwd_dual: bad frame window");
+    R2D2_REQUIRE((long long)B * nt * 400 < (1ll << 31), "tc_conv1_fwd_dual: too many frames");
+    return launch_tc_conv1_dual(slab, FrameMap{B, S, 0, R2D2_FRAME_BYTES}, w1_a, b1_a, a1_a, w1_b, b1_b, a1_b,
+                                B * nt, s0_b * B, as_stream(stream));
+}
+
+int r2d2_tc_torso_fwd_tail(const float* a1, int R, const float* w2, const float* b2, const float* w3,
+                           const float* b3, float* a2, float* feat, void* stream) {
+    R2D2_REQUIRE(a1 && w2 && b2 && w3 && b3 && a2 && feat && R > 0, "tc_torso_fwd_tail: bad args");
+    int rc = launch_tc_conv<float, 32, 4, 20, 9, 2>("tc_conv2_fwd", a1, FrameMap{0, 0, 0, 12800}, w2, b2, a2,
+                                                    R, 1.f, as_stream(stream));
+    if (rc) return rc;
+    return launch_tc_conv<float, 32, 3, 9, 7, 1>("tc_conv3_fwd", a2, FrameMap{0, 0, 0, 2592}, w3, b3, feat,
+                                                 R, 1.f, as_stream(stream));
 }
 
 // data gradients of conv3 (into the 9x9 layer) and conv2 (into the 20x20 layer), ReLU' fused

@@ -42,6 +42,19 @@ def torso_fwd_u8(slab, s0, nt, w: Weights, a1, a2, feat, tc=False):
               P(w.w3), P(w.b3), P(a1, "f32"), P(a2, "f32"), P(feat, "f32"), S())
 
 
+def conv1_fwd_dual_u8(slab, nt, wa: Weights, a1_a, wb: Weights, a1_b, s0_b):
+    """First conv layer of two nets over the same frames: net a on frames 0..nt, net b on s0_b..nt."""
+    B, Sfr = slab.shape[0], slab.shape[1]
+    _lib.call("r2d2_tc_conv1_fwd_dual_u8", P(slab, "u8"), B, Sfr, nt, P(wa.w1), P(wa.b1), P(a1_a, "f32"),
+              P(wb.w1), P(wb.b1), P(a1_b, "f32"), s0_b, S())
+
+
+def torso_fwd_tail(a1, w: Weights, a2, feat):
+    """conv2 + conv3 of one net from its first-layer activations."""
+    _lib.call("r2d2_tc_torso_fwd_tail", P(a1, "f32"), a1.shape[0], P(w.w2), P(w.b2), P(w.w3), P(w.b3),
+              P(a2, "f32"), P(feat, "f32"), S())
+
+
 def torso_fwd_f32(frames, w: Weights, a1, a2, feat, tc=False):
     R = frames.shape[0]
     _lib.call("r2d2_tc_torso_fwd_f32" if tc else "r2d2_torso_fwd_f32", P(frames, "f32"), R, P(w.w1), P(w.b1), P(w.w2), P(w.b2), P(w.w3),

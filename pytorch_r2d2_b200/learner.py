@@ -286,7 +286,10 @@ class Learner:
             """Target net (learner.py:72,79,92): torso on frames n..T+n, burn-in on
             next_state[0:BI], evaluation on next_state[BI:T].  Independent of the online net
             until the TD target, so in bf16 mode it runs on the side stream."""
-            engine.torso_fwd_u8(slab, n, T, wt, ws["a1_tg"], ws["a2_tg"], ws["feat_tg"], tc=bf16)
+            if fused_conv1:
+                engine.torso_fwd_tail(ws["a1_tg"], wt, ws["a2_tg"], ws["feat_tg"])
+            else:
+                engine.torso_fwd_u8(slab, n, T, wt, ws["a1_tg"], ws["a2_tg"], ws["feat_tg"], tc=bf16)
             ws["hs_tg"][0].copy_(batch["target_hs"])
             ws["cs_tg"][0].copy_(batch["target_cs"])
             if bf16:
@@ -304,6 +307,11 @@ class Learner:
                  ws["hid_tg"], ws["qn_tg"])
 
         overlap = bf16 and self.overlap_streams
+        # both nets read the same frames and the first layer is bound by gathering them: one pass
+        # builds each receptive field once and multiplies it against both nets' filters
+        fused_conv1 = bf16
+        if fused_conv1:
+            engine.conv1_fwd_dual_u8(slab, T + n, w, ws["a1_on"], wt, ws["a1_tg"], n)
         if overlap:
             main, side = torch.cuda.current_stream(), ws["side_stream"]
             ws["ev_fork"].record(main)
@@ -318,7 +326,10 @@ class Learner:
         #      state carries through); then again on next_state[BI:T] = frames BI+n.., starting
         #      from the state left after state[T-1] (the reference never resets it:
         #      learner.py:86,91)
-        engine.torso_fwd_u8(slab, 0, T + n, w, ws["a1_on"], ws["a2_on"], ws["feat_on"], tc=bf16)
+        if fused_conv1:
+            engine.torso_fwd_tail(ws["a1_on"], w, ws["a2_on"], ws["feat_on"])
+        else:
+            engine.torso_fwd_u8(slab, 0, T + n, w, ws["a1_on"], ws["a2_on"], ws["feat_on"], tc=bf16)
         ws["hs_on"][0].copy_(batch["hs"])
         ws["cs_on"][0].copy_(batch["cs"])
         if bf16:

@@ -103,6 +103,31 @@ def test_tc_torso_vs_torch(cuda_device):
     assert rel_err(c1, d1) < 1e-5 and rel_err(c2, d2) < 1e-5 and rel_err(f2, g2) < 1e-5
 
 
+def test_tc_conv1_dual_matches_single(cuda_device):
+    """One pass of the first conv layer for two nets (online: frames 0..S, target: frames s0..S)
+    == the two single-net passes, bit for bit, plus the tail entry point (conv2 + conv3)."""
+    import numpy as np
+    from pytorch_r2d2_b200 import QNet, engine
+    torch.manual_seed(5)
+    na, nb = QNet("cuda:0", 256), QNet("cuda:0", 256)
+    wa, wb = na._weights(), nb._weights()
+    rng = np.random.RandomState(4)
+    for B, S, s0 in ((3, 6, 2), (32, 30, 5)):
+        slab = torch.from_numpy(rng.randint(0, 256, (B, S, 4, 84, 84)).astype(np.uint8)).cuda()
+        a1, a2, fa = engine.alloc_torso(B * S, "cuda")
+        b1, b2, fb = engine.alloc_torso(B * (S - s0), "cuda")
+        engine.torso_fwd_u8(slab, 0, S, wa, a1, a2, fa, tc=True)
+        engine.torso_fwd_u8(slab, s0, S - s0, wb, b1, b2, fb, tc=True)
+        c1, c2, fc = engine.alloc_torso(B * S, "cuda")
+        d1, d2, fd = engine.alloc_torso(B * (S - s0), "cuda")
+        d1.fill_(float("nan"))
+        engine.conv1_fwd_dual_u8(slab, S, wa, c1, wb, d1, s0)
+        assert torch.equal(c1, a1) and torch.equal(d1, b1)
+        engine.torso_fwd_tail(c1, wa, c2, fc)
+        engine.torso_fwd_tail(d1, wb, d2, fd)
+        assert torch.equal(fc, fa) and torch.equal(fd, fb)
+
+
 @pytest.mark.parametrize("H,B,T", [(256, 4, 5), (512, 64, 6), (512, 8, 3), (256, 100, 2)])
 def test_tc_lstm_vs_torch(cuda_device, H, B, T):
     """Persistent tensor-core LSTM unroll == fp32 recurrence to 1e-5 (bf16x3 compensation),
