@@ -37,16 +37,14 @@ __device__ __forceinline__ uint32_t sw128_off(int row, int chunk) {
     return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((chunk ^ (row & 7)) << 4));
 }
 
-// Four 8-element chunks (chunks 4*HALF .. 4*HALF+3 of k-block kb) of one patch row.
-template <class T, int CIN, int KH, int HIN, int HALF>
+// NCH 8-element chunks (chunks NCH*PART .. NCH*PART+NCH-1 of k-block kb) of one patch row.
+template <class T, int CIN, int KH, int HIN, int PART, int NCH = 4>
 __device__ __forceinline__ void gather_chunks(const T* __restrict__ src, const int kb,
-                                              const bool valid, float (&v)[4][8]) {
+                                              const bool valid, float (&v)[NCH][8]) {
     constexpr int K = CIN * KH * KH;
 #pragma unroll
-    for (int cc = 0; cc < 4; ++cc) {
-        constexpr int dummy = 0;
-        (void)dummy;
-        const int c = HALF * 4 + cc;
+    for (int cc = 0; cc < NCH; ++cc) {
+        const int c = PART * NCH + cc;
         if constexpr (sizeof(T) == 1 && KH == 8) {
             // conv1 on the u8 slab: k-block = one input channel, chunk = one 8-pixel patch row
             const uint32_t* q = reinterpret_cast<const uint32_t*>(src + kb * (HIN * HIN) + c * HIN);
@@ -89,8 +87,10 @@ __device__ __forceinline__ void gather_chunks(const T* __restrict__ src, const i
 // target net read the same frames, and the kernel is bound by the producers' gather, so the A
 // tile is built once and multiplied against both weight sets stacked along N (one N = 128 MMA per
 // k-step); net 1 skips the first `skip1` frames (its window starts later) and writes out1.
-template <class T, int CIN, int KH, int HIN, int HOUT, int STRIDE, int NW = 1>
-__global__ void __launch_bounds__(416, 1)
+// NPW = producer warps (8 or 16): the gather is bound by memory latency, so the fp32 layers run 16
+// (two chunks per thread, twice the loads in flight per SM at half the registers per thread).
+template <class T, int CIN, int KH, int HIN, int HOUT, int STRIDE, int NW = 1, int NPW = 8>
+__global__ void __launch_bounds__(NPW * 32 + 160, 1)
 tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __restrict__ w,
                    const float* __restrict__ bias, float* __restrict__ out, const int R,
                    const float in_scale, const float* __restrict__ w1 = nullptr,
@@ -105,7 +105,10 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
     constexpr uint32_t W_KB = COUT * 128;                    // 32 rows x 64 bf16 per k-block and half
     constexpr uint32_t W_BYTES = NW * 2 * NKB * W_KB;        // per k-block: NW x [hi rows | lo rows]
     constexpr uint32_t ACC_COLS = NW * 2 * COUT;             // accumulator columns per buffer
-    constexpr int MMA_WARP = 8;
+    constexpr int MMA_WARP = NPW;
+    constexpr int NCH = 32 / NPW;                            // 16-byte chunks of a row per producer thread
+    static_assert(NPW == 8 || NPW == 16, "8 or 16 producer warps");
+    static_assert(NPW == 8 || !(sizeof(T) == 1 && KH == 8), "the u8 first-layer path is written for 8 producer warps");
     extern __shared__ uint8_t smem_raw[];
     __shared__ uint64_t full_bar[CV_STAGES], empty_bar[CV_STAGES], acc_full[2], acc_empty[2];
     __shared__ uint32_t tmem_slot;
@@ -122,7 +125,7 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
     // ---- one-time set-up: barriers, k-offset table, resident weights (hi/lo, swizzled)
     if (tid == 0) {
         for (int s = 0; s < CV_STAGES; ++s) {
-            mbar_init(&full_bar[s], 256);
+            mbar_init(&full_bar[s], NPW * 32);
             mbar_init(&empty_bar[s], 1);
         }
         for (int b = 0; b < 2; ++b) {
@@ -231,34 +234,43 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
                 src = in + fm.base(r) + (long long)(oy * STRIDE) * HIN + ox * STRIDE;
             }
             {
-                // software pipeline: the loads of k-block kb+1 are in flight while k-block kb is
-                // converted and stored (the gather is memory-latency bound)
-                float v[2][4][8];
-                if (half == 0) gather_chunks<T, CIN, KH, HIN, 0>(src, 0, valid, v[0]);
-                else gather_chunks<T, CIN, KH, HIN, 1>(src, 0, valid, v[0]);
+                // software pipeline: the loads of the next PF k-blocks are in flight while k-block kb
+                // is converted and stored (the gather is memory-latency bound)
+                constexpr int PF = NPW == 16 ? 2 : 1;             // k-blocks of loads in flight ahead
+                float v[PF + 1][NCH][8];
+                auto gather = [&](int kb, float (&dst)[NCH][8]) {
+                    // `half` (= which group of NCH chunks) selects a compile-time instantiation
+                    if (half == 0) gather_chunks<T, CIN, KH, HIN, 0, NCH>(src, kb, valid, dst);
+                    else if (half == 1) gather_chunks<T, CIN, KH, HIN, 1, NCH>(src, kb, valid, dst);
+                    else if constexpr (NPW == 16) {
+                        if (half == 2) gather_chunks<T, CIN, KH, HIN, 2, NCH>(src, kb, valid, dst);
+                        else gather_chunks<T, CIN, KH, HIN, 3, NCH>(src, kb, valid, dst);
+                    }
+                };
+#pragma unroll
+                for (int kb = 0; kb < PF && kb < NKB; ++kb) gather(kb, v[kb]);
 #pragma unroll
                 for (int kb = 0; kb < NKB; ++kb, ++it) {
-                    if (kb + 1 < NKB) {
-                        if (half == 0) gather_chunks<T, CIN, KH, HIN, 0>(src, kb + 1, valid, v[(kb + 1) & 1]);
-                        else gather_chunks<T, CIN, KH, HIN, 1>(src, kb + 1, valid, v[(kb + 1) & 1]);
-                    }
+                    if (kb + PF < NKB) gather(kb + PF, v[(kb + PF) % (PF + 1)]);
                     const int s = it % CV_STAGES;
                     mbar_wait(&empty_bar[s], ((it / CV_STAGES) & 1) ^ 1);
                     uint8_t* a_hi = a_s + (size_t)s * STAGE_BYTES;
-                    float(&vv)[4][8] = v[kb & 1];
+                    float(&vv)[NCH][8] = v[kb % (PF + 1)];
 #pragma unroll
-                    for (int cc = 0; cc < 4; ++cc) {
-                        const uint32_t off = sw128_off(row, half * 4 + cc);
-                        *reinterpret_cast<uint4*>(a_hi + off) =
-                            make_uint4(pack_bf16x2(vv[cc][0], vv[cc][1]), pack_bf16x2(vv[cc][2], vv[cc][3]),
-                                       pack_bf16x2(vv[cc][4], vv[cc][5]), pack_bf16x2(vv[cc][6], vv[cc][7]));
+                    for (int cc = 0; cc < NCH; ++cc) {
+                        const uint32_t off = sw128_off(row, half * NCH + cc);
                         if constexpr (NEED_LO) {
-                            float l[8];
-#pragma unroll
-                            for (int e = 0; e < 8; ++e) l[e] = vv[cc][e] - bf16_round(vv[cc][e]);
-                            *reinterpret_cast<uint4*>(a_hi + A_TILE + off) =
-                                make_uint4(pack_bf16x2(l[0], l[1]), pack_bf16x2(l[2], l[3]),
-                                           pack_bf16x2(l[4], l[5]), pack_bf16x2(l[6], l[7]));
+                            uint4 h, l;
+                            split_bf16x2(vv[cc][0], vv[cc][1], h.x, l.x);
+                            split_bf16x2(vv[cc][2], vv[cc][3], h.y, l.y);
+                            split_bf16x2(vv[cc][4], vv[cc][5], h.z, l.z);
+                            split_bf16x2(vv[cc][6], vv[cc][7], h.w, l.w);
+                            *reinterpret_cast<uint4*>(a_hi + off) = h;
+                            *reinterpret_cast<uint4*>(a_hi + A_TILE + off) = l;
+                        } else {
+                            *reinterpret_cast<uint4*>(a_hi + off) =
+                                make_uint4(pack_bf16x2(vv[cc][0], vv[cc][1]), pack_bf16x2(vv[cc][2], vv[cc][3]),
+                                           pack_bf16x2(vv[cc][4], vv[cc][5]), pack_bf16x2(vv[cc][6], vv[cc][7]));
                         }
                     }
                     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -344,14 +356,15 @@ static int launch_tc_conv(const char* name, const T* in, FrameMap fm, const floa
                           float* out, int R, float in_scale, cudaStream_t st) {
     constexpr int K = CIN * KH * KH, NKB = (K + 63) / 64;
     constexpr bool NEED_LO = sizeof(T) != 1;
+    constexpr int NPW = (sizeof(T) == 1 && KH == 8) ? 8 : 16;
     const int smem = 2 * NKB * 32 * 128 + CV_STAGES * (NEED_LO ? 2 : 1) * 128 * 128 + 1024;
-    auto kern = tc_conv_fwd_kernel<T, CIN, KH, HIN, HOUT, STRIDE>;
+    auto kern = tc_conv_fwd_kernel<T, CIN, KH, HIN, HOUT, STRIDE, 1, NPW>;
     R2D2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     const long long Mtot = (long long)R * HOUT * HOUT;
     const int ntiles = (int)((Mtot + 127) / 128);
     int grid = sm_count();
     if (grid > ntiles) grid = ntiles;
-    R2D2_LAUNCH(name, st, kern<<<grid, 416, smem, st>>>(in, fm, w, b, out, R, in_scale, nullptr, nullptr, nullptr, 0));
+    R2D2_LAUNCH(name, st, kern<<<grid, NPW * 32 + 160, smem, st>>>(in, fm, w, b, out, R, in_scale, nullptr, nullptr, nullptr, 0));
     return R2D2_OK;
 }
 

@@ -82,14 +82,15 @@ template <int N> __device__ __forceinline__ void st_bf16_hilo(__nv_bfloat16* hi,
                                                               const float* v) {
     if constexpr (N == 4) {
         uint2 a, b;
-        a.x = ls_pack(v[0], v[1]); a.y = ls_pack(v[2], v[3]);
-        b.x = ls_pack(v[0] - ls_round(v[0]), v[1] - ls_round(v[1]));
-        b.y = ls_pack(v[2] - ls_round(v[2]), v[3] - ls_round(v[3]));
+        split_bf16x2(v[0], v[1], a.x, b.x);
+        split_bf16x2(v[2], v[3], a.y, b.y);
         *reinterpret_cast<uint2*>(hi) = a;
         *reinterpret_cast<uint2*>(lo) = b;
     } else if constexpr (N == 2) {
-        *reinterpret_cast<uint32_t*>(hi) = ls_pack(v[0], v[1]);
-        *reinterpret_cast<uint32_t*>(lo) = ls_pack(v[0] - ls_round(v[0]), v[1] - ls_round(v[1]));
+        uint32_t a, b;
+        split_bf16x2(v[0], v[1], a, b);
+        *reinterpret_cast<uint32_t*>(hi) = a;
+        *reinterpret_cast<uint32_t*>(lo) = b;
     } else {
         *hi = __float2bfloat16_rn(v[0]);
         *lo = __float2bfloat16_rn(v[0] - ls_round(v[0]));
