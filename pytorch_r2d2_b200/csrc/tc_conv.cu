@@ -470,6 +470,78 @@ tc_conv_wgrad_kernel(const T* __restrict__ in, const FrameMap fm, const float* _
         const int prow = tid & 63, sub = tid >> 6;
         const int bco = tid >> 3, bch = tid & 7;
         uint32_t it = 0;
+        if constexpr (sizeof(T) == 1 && KH == 8 && P % 8 == 0) {
+            // first layer on the u8 slab: the gather is memory-latency bound, so the loads of block
+            // blk+1 (16 words of patch + 8 gradient values per thread) are issued before block blk
+            // is converted and stored.  Thread (pixel prow, sub) owns half-k-blocks sub and sub+4:
+            // input channel ci = sub/2 (+2), patch rows 4*(sub%2) .. +3, eight pixels each.
+            static_assert(NKB == 4, "u8 first layer: K = 256");
+            auto issue = [&](int blk, uint32_t (&raw)[2][4][2], float4 (&g)[2]) {
+                const long long m = (long long)blk * 64 + prow;
+                const bool valid = blk < blk_hi && m < Mtot;
+                const T* src = in;
+                if (valid) {
+                    const int r = (int)(m / P), p = (int)(m - (long long)r * P);
+                    const int oy = p / HOUT, ox = p - oy * HOUT;
+                    src = in + fm.base(r) + (long long)(oy * STRIDE) * HIN + ox * STRIDE;
+                }
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+#pragma unroll
+                    for (int cc = 0; cc < 4; ++cc) {
+                        const int kb = (sub >> 1) + 2 * h, c = (sub & 1) * 4 + cc;
+                        const uint32_t* q = reinterpret_cast<const uint32_t*>(src + kb * (HIN * HIN) + c * HIN);
+                        raw[h][cc][0] = valid ? __ldg(q) : 0u;
+                        raw[h][cc][1] = valid ? __ldg(q + 1) : 0u;
+                    }
+                const long long mm = (long long)blk * 64 + bch * 8;
+                g[0] = g[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (blk < blk_hi && mm < Mtot) {      // P % 8 == 0: the 8 pixels share a frame, 32-byte aligned
+                    const int r = (int)(mm / P), p = (int)(mm - (long long)r * P);
+                    const float4* gp = reinterpret_cast<const float4*>(dz + ((long long)r * COUT + bco) * P + p);
+                    g[0] = __ldg(gp);
+                    g[1] = __ldg(gp + 1);
+                }
+            };
+            uint32_t cur[2][4][2], nxt[2][4][2];
+            float4 gcur[2], gnxt[2];
+            issue(blk_lo, cur, gcur);
+            for (int blk = blk_lo; blk < blk_hi; ++blk, ++it) {
+                issue(blk + 1, nxt, gnxt);
+                const int s = it % STAGES;
+                mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
+                uint8_t* a_stage = base + (size_t)s * STAGE_BYTES;
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+#pragma unroll
+                    for (int cc = 0; cc < 4; ++cc) {
+                        float v[8];
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            v[e] = __uint_as_float(__byte_perm(cur[h][cc][0], 0x4B000000u, 0x7650u | e)) - 8388608.f;
+                            v[4 + e] = __uint_as_float(__byte_perm(cur[h][cc][1], 0x4B000000u, 0x7650u | e)) - 8388608.f;
+                        }
+                        const int kb = (sub >> 1) + 2 * h;
+                        *reinterpret_cast<uint4*>(a_stage + kb * 8192 + sw128_off(prow, (sub & 1) * 4 + cc)) =
+                            make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
+                                       pack_bf16x2(v[6], v[7]));
+                    }
+                *reinterpret_cast<uint4*>(a_stage + A_STAGE + sw128_off(bco, bch)) =
+                    make_uint4(pack_bf16x2(gcur[0].x, gcur[0].y), pack_bf16x2(gcur[0].z, gcur[0].w),
+                               pack_bf16x2(gcur[1].x, gcur[1].y), pack_bf16x2(gcur[1].z, gcur[1].w));
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                mbar_arrive(&full_bar[s]);
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+#pragma unroll
+                    for (int cc = 0; cc < 4; ++cc) {
+                        cur[h][cc][0] = nxt[h][cc][0];
+                        cur[h][cc][1] = nxt[h][cc][1];
+                    }
+                gcur[0] = gnxt[0];
+                gcur[1] = gnxt[1];
+            }
+        } else {
         for (int blk = blk_lo; blk < blk_hi; ++blk, ++it) {
             const int s = it % STAGES;
             mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
@@ -508,6 +580,7 @@ tc_conv_wgrad_kernel(const T* __restrict__ in, const FrameMap fm, const float* _
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             mbar_arrive(&full_bar[s]);
+        }
         }
     } else if (warp == MMA_WARP) {
         if (lane == 0) {
