@@ -28,6 +28,11 @@ struct TcEpilogue {
     int bias_row;           // biases indexed by output row m instead of column n
 };
 
+__device__ __forceinline__ uint32_t pack2_bf16(float a, float b) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&v);
+}
+
 template <int BN>
 __global__ void __launch_bounds__(192, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
@@ -144,6 +149,140 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     if (warp == 1) tmem_dealloc(tmem_base, BN);
 }
 
+// ---------------------------------------------------------------- bf16x3 GEMM
+// C = A_hi.B_hi^T + A_hi.B_lo^T + A_lo.B_hi^T with all four operand tiles of a k-block in ONE
+// pipeline stage, so every tile crosses L2 -> shared memory once per k-block (the three-pass form
+// above re-reads A_hi and B_hi and is bound by exactly that traffic).
+//   BN = 128: [B_hi ; B_lo] are adjacent in the stage = one 256-row K-major operand: A_hi multiplies
+//             both in ONE N = 256 MMA (accumulator columns 0-127 and 128-255, added in the epilogue),
+//             A_lo.B_hi is a second N = 128 MMA into columns 0-127.
+//   BN = 256: three N = 256 MMAs into the same 256 columns; twice the output per byte loaded.
+template <int BN>
+__global__ void __launch_bounds__(192, 1)
+tc_gemm_x3_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                  const __grid_constant__ CUtensorMap tma_a_lo,
+                  const __grid_constant__ CUtensorMap tma_b_lo, const TcEpilogue ep, const int M,
+                  const int N, const int K) {
+    constexpr uint32_t A_BYTES = TC_BM * TC_BK * 2, B_BYTES = BN * TC_BK * 2;
+    constexpr uint32_t STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;
+    constexpr int STAGES = BN == 128 ? 3 : 2;
+    constexpr bool CAT = BN == 128;
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], acc_bar;
+    __shared__ uint32_t tmem_slot;
+    const uint32_t raw = smem_u32(smem_raw);
+    uint8_t* tiles = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = blockIdx.x * TC_BM, n0 = blockIdx.y * BN;
+    const int num_kb = (K + TC_BK - 1) / TC_BK;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tma_a);
+        tma_prefetch_desc(&tma_b);
+        tma_prefetch_desc(&tma_a_lo);
+        tma_prefetch_desc(&tma_b_lo);
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(&acc_bar, 1);
+        mbar_fence_init();
+    }
+    if (warp == 1) tmem_alloc(&tmem_slot, 256);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % STAGES;
+                mbar_wait(&empty_bar[s], ((kb / STAGES) & 1) ^ 1);
+                mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+                uint8_t* dst = tiles + (size_t)s * STAGE_BYTES;
+                const int kk = kb * TC_BK;
+                tma_load_2d(dst, &tma_a, kk, m0, &full_bar[s]);
+                tma_load_2d(dst + A_BYTES, &tma_a_lo, kk, m0, &full_bar[s]);
+                tma_load_2d(dst + 2 * A_BYTES, &tma_b, kk, n0, &full_bar[s]);
+                tma_load_2d(dst + 2 * A_BYTES + B_BYTES, &tma_b_lo, kk, n0, &full_bar[s]);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(TC_BM, BN), idesc_cat = umma_idesc_bf16(TC_BM, 256);
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % STAGES;
+                mbar_wait(&full_bar[s], (kb / STAGES) & 1);
+                tc_fence_after();
+                const uint32_t a_hi = smem_u32(tiles + (size_t)s * STAGE_BYTES), a_lo = a_hi + A_BYTES;
+                const uint32_t b_hi = a_hi + 2 * A_BYTES, b_lo = b_hi + B_BYTES;
+#pragma unroll
+                for (int k = 0; k < TC_BK / 16; ++k) {
+                    const uint32_t acc = (kb | k) != 0;
+                    if constexpr (CAT) {
+                        umma_f16(tmem_base, umma_desc_k_sw128(a_hi + k * 32), umma_desc_k_sw128(b_hi + k * 32), idesc_cat, acc);
+                        umma_f16(tmem_base, umma_desc_k_sw128(a_lo + k * 32), umma_desc_k_sw128(b_hi + k * 32), idesc, 1);
+                    } else {
+                        umma_f16(tmem_base, umma_desc_k_sw128(a_hi + k * 32), umma_desc_k_sw128(b_hi + k * 32), idesc, acc);
+                        umma_f16(tmem_base, umma_desc_k_sw128(a_hi + k * 32), umma_desc_k_sw128(b_lo + k * 32), idesc, 1);
+                        umma_f16(tmem_base, umma_desc_k_sw128(a_lo + k * 32), umma_desc_k_sw128(b_hi + k * 32), idesc, 1);
+                    }
+                }
+                umma_commit(&empty_bar[s]);
+            }
+            umma_commit(&acc_bar);
+        }
+    } else {
+        mbar_wait(&acc_bar, 0);
+        tc_fence_after();
+        const int q = warp & 3;
+        const int m = m0 + q * 32 + lane;
+#pragma unroll 1
+        for (int c = 0; c < BN; c += 32) {
+            uint32_t r[32];
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c, r);
+            if constexpr (CAT) {
+                uint32_t r2[32];
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(128 + c), r2);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(__uint_as_float(r[j]) + __uint_as_float(r2[j]));
+            } else {
+                tmem_ld_wait();
+            }
+            if (m < M) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) {
+                    const int n = n0 + c + j;
+                    if (n >= N) break;
+                    float v[4];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        float x = __uint_as_float(r[j + e]);
+                        if (ep.bias1) x += __ldg(ep.bias1 + (ep.bias_row ? m : n + e));
+                        if (ep.bias2) x += __ldg(ep.bias2 + (ep.bias_row ? m : n + e));
+                        if (ep.relu) x = fmaxf(x, 0.f);
+                        v[e] = x;
+                    }
+                    if (ep.c32)
+                        *reinterpret_cast<float4*>(ep.c32 + (long long)m * ep.ldc + n) =
+                            make_float4(v[0], v[1], v[2], v[3]);
+                    if (ep.c16) {
+                        uint2 pk;
+                        pk.x = pack2_bf16(v[0], v[1]);
+                        pk.y = pack2_bf16(v[2], v[3]);
+                        *reinterpret_cast<uint2*>(ep.c16 + (long long)m * ep.ldc + n) = pk;
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, 256);
+}
+
 // ---------------------------------------------------------------- host: tensor maps
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
@@ -256,6 +395,35 @@ static int tc_linear_impl(const void* x_hi, const void* x_lo, const void* w_hi, 
     R2D2_REQUIRE(N % 4 == 0, "tc_linear: N must be a multiple of 4 (N=%d)", N);
     R2D2_REQUIRE(!y_f32 || ((uintptr_t)y_f32 % 16) == 0, "tc_linear: y_f32 must be 16-byte aligned");
     R2D2_REQUIRE(!y_bf16 || ((uintptr_t)y_bf16 % 8) == 0, "tc_linear: y_bf16 must be 8-byte aligned");
+    if (x_lo) {
+        // bf16x3: BN = 256 halves the operand traffic per output; the small problems (heads) keep
+        // 128-wide tiles so that they still spread over the SMs
+        const bool wide = (long long)((M + TC_BM - 1) / TC_BM) * ((N + 255) / 256) >= 2 * sm_count();
+        const int BNx = wide ? 256 : 128;
+        CUtensorMap ta, tb, ta_lo, tb_lo;
+        int rc = make_tmap(&ta, x_hi, M, K, TC_BM);
+        if (rc) return rc;
+        rc = make_tmap(&ta_lo, x_lo, M, K, TC_BM);
+        if (rc) return rc;
+        rc = make_tmap(&tb, w_hi, N, K, BNx);
+        if (rc) return rc;
+        rc = make_tmap(&tb_lo, w_lo, N, K, BNx);
+        if (rc) return rc;
+        TcEpilogue ep{y_f32, reinterpret_cast<__nv_bfloat16*>(y_bf16), N, bias1, bias2, relu & 1, (relu >> 1) & 1};
+        dim3 grid((M + TC_BM - 1) / TC_BM, (N + BNx - 1) / BNx);
+        if (wide) {
+            const int smem = 2 * (2 * TC_BM * TC_BK * 2 + 2 * 256 * TC_BK * 2) + 1024;
+            R2D2_CUDA_OK(cudaFuncSetAttribute(tc_gemm_x3_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            R2D2_LAUNCH("tc_gemm_kernel_x3", as_stream(stream),
+                        tc_gemm_x3_kernel<256><<<grid, 192, smem, as_stream(stream)>>>(ta, tb, ta_lo, tb_lo, ep, M, N, K));
+        } else {
+            const int smem = 3 * (2 * TC_BM * TC_BK * 2 + 2 * 128 * TC_BK * 2) + 1024;
+            R2D2_CUDA_OK(cudaFuncSetAttribute(tc_gemm_x3_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            R2D2_LAUNCH("tc_gemm_kernel_x3", as_stream(stream),
+                        tc_gemm_x3_kernel<128><<<grid, 192, smem, as_stream(stream)>>>(ta, tb, ta_lo, tb_lo, ep, M, N, K));
+        }
+        return R2D2_OK;
+    }
     constexpr int BN = 128;
     CUtensorMap ta, tb, ta_lo, tb_lo;
     int rc = make_tmap(&ta, x_hi, M, K, TC_BM);

@@ -389,14 +389,17 @@ class Learner:
             main, side = torch.cuda.current_stream(), ws["side_stream"]
             overlap_bwd = self.overlap_streams
 
-            def beside(fn):
-                """Run fn() on the side stream after everything enqueued so far on main."""
+            aux = ws["aux_stream"]
+
+            def beside(fn, stream=None):
+                """Run fn() on a side stream after everything enqueued so far on main."""
                 if not overlap_bwd:
                     return fn()
+                stream = stream or side
                 e = next(ev)
                 e.record(main)
-                side.wait_event(e)
-                with torch.cuda.stream(side):
+                stream.wait_event(e)
+                with torch.cuda.stream(stream):
                     fn()
 
             def priorities():
@@ -429,7 +432,7 @@ class Learner:
                 engine.transpose_cast_bf16(feat_l, ws["featT16"])
                 engine.tc_linear(ws["dgT16"], ws["featT16"], None, None, y32=g.w_ih)
 
-            beside(lstm_wgrad)
+            beside(lstm_wgrad, aux)       # the longest consumer chain gets a stream of its own
             engine.cast_bf16(ws["dgates"], ws["dg16"])
             engine.transpose_cast_bf16(w.w_ih, ws["w_ihT16"])
             engine.tc_linear(ws["dg16"], ws["w_ihT16"], None, None, y32=ws["dfeat"])
@@ -459,9 +462,10 @@ class Learner:
             _lib.call("r2d2_tc_conv_wgrad_layer", 1, P(slab, "u8"), B, T + n, BI, L, P(dz1, "f32"), P(g.w1),
                       P(ws["wpart"][0], "f32"), st())
             if overlap_bwd:
-                e = next(ev)
-                e.record(side)
-                main.wait_event(e)
+                for st_ in (side, aux):
+                    e = next(ev)
+                    e.record(st_)
+                    main.wait_event(e)
         else:
             engine.head_bwd(td["dq"], ws["hid_on"], w, ws["dhid"], g.head_w2, g.head_b2)
             engine.linear_wgrad(ws["dhid"], hs_learn, g.head_w1, g.head_b1, scratch)

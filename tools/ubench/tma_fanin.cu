@@ -41,6 +41,7 @@ __device__ __forceinline__ void bulk_1d_mc(void* dst, const void* src, uint32_t 
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)), "h"(mask) : "memory");
 }
 __device__ __forceinline__ int ld_acq(const int* p) { int v; asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v; }
+__device__ __forceinline__ int ld_rlx(const int* p) { int v; asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v; }
 __device__ __forceinline__ void red_rel(int* p, int v) { asm volatile("red.release.gpu.global.add.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
 __device__ __forceinline__ uint32_t cluster_rank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
 
@@ -52,7 +53,7 @@ fanin(const __grid_constant__ CUtensorMap tm, uint8_t* buf, int* counter, long l
     __shared__ uint64_t bar, pbar[PIECES], ebar[PIECES];
     uint8_t* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     const int G = gridDim.x, c = blockIdx.x;
-    const bool own = mode == 1 || mode == 3, rewrite = mode >= 5;
+    const bool own = mode == 1 || mode == 3, rewrite = (mode >= 5 && mode <= 7) || mode >= 10;
     const bool mc = mode == 7;
     uint8_t* src = buf + (own ? (size_t)c * TILE : 0);
     if (threadIdx.x == 0) { for (int p = 0; p < PIECES; ++p) { mbar_init(&pbar[p], 1); mbar_init(&ebar[p], 1); } mbar_init(&bar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
@@ -70,10 +71,26 @@ fanin(const __grid_constant__ CUtensorMap tm, uint8_t* buf, int* counter, long l
         __syncthreads();
         if (threadIdx.x == 0) {
             red_rel(counter, 1);
-            while (ld_acq(counter) < G * (s + 1)) {}
+            if (mode == 11 || mode == 12) {
+                // several relaxed polls in flight, staggered, then one acquire fence
+                const int target = G * (s + 1);
+                int v[4];
+                const int NP = mode == 11 ? 4 : 2;
+                for (int i = 0; i < NP; ++i) { v[i] = ld_rlx(counter); if (i + 1 < NP) __nanosleep(600 / NP); }
+                bool done = false;
+                while (!done) {
+                    for (int i = 0; i < NP; ++i) {
+                        if (v[i] >= target) { done = true; break; }
+                        v[i] = ld_rlx(counter);
+                    }
+                }
+                asm volatile("fence.acq_rel.gpu;" ::: "memory");
+            } else {
+                while (ld_acq(counter) < G * (s + 1)) {}
+            }
             asm volatile("fence.proxy.async;" ::: "memory");
             const long long t0 = gtimer();
-            if (mode >= 8) {
+            if (mode == 8 || mode == 9) {
                 for (int p = 0; p < PIECES; ++p) {
                     if (mode == 9) mbar_wait(&ebar[p], 1);
                     mbar_expect_tx(&pbar[p], PIECE);
@@ -89,7 +106,7 @@ fanin(const __grid_constant__ CUtensorMap tm, uint8_t* buf, int* counter, long l
             if (mode == 0 || mode == 1 || mode == 5) {
                 const int row0 = (own ? c * PIECES * 32 : 0) + (rewrite ? (s & 1) * PIECES * 32 : 0);
                 for (int p = 0; p < PIECES; ++p) tma_2d(base + p * PIECE, &tm, 0, row0 + p * 32, &bar);
-            } else if (mode == 4) {
+            } else if (mode == 4 || mode >= 10) {
                 for (int p = 0; p < 4; ++p) bulk_1d(base + p * 32768, src + p * 32768, 32768, &bar);
             } else if (mc) {
                 const uint32_t r = cluster_rank();
@@ -134,9 +151,11 @@ int main(int argc, char** argv) {
     const char* names[] = {"2-D boxes, same tile", "2-D boxes, own tile", "1-D 4 KB, same", "1-D 4 KB, own", "1-D 32 KB, same",
                            "2-D boxes, same, rewritten each step", "1-D 4 KB, same, rewritten each step",
                            "1-D 4 KB multicast x4, rewritten each step", "2-D boxes, same, barrier per piece",
-                           "2-D boxes, same, barrier per piece + stage-free try_wait"};
+                           "2-D boxes, same, barrier per piece + stage-free try_wait",
+                           "1-D 32 KB, rewritten, acquire poll", "1-D 32 KB, rewritten, 4 staggered relaxed polls + fence",
+                           "1-D 32 KB, rewritten, 2 staggered relaxed polls + fence"};
     for (int G : {64}) {
-        for (int mode = 0; mode < 10; ++mode) {
+        for (int mode = 0; mode < 13; ++mode) {
             CK(cudaMemset(counter, 0, 256));
             cudaLaunchConfig_t cfg = {};
             cfg.gridDim = dim3(G); cfg.blockDim = dim3(128); cfg.dynamicSmemBytes = smem;
@@ -157,7 +176,7 @@ int main(int argc, char** argv) {
             double mean = 0, mx = 0;
             for (int i = 0; i < G; ++i) { mean += h[i]; if (h[i] > mx) mx = h[i]; }
             mean /= G;
-            if (mode >= 8) { long long ti; CK(cudaMemcpy(&ti, out + G, 8, cudaMemcpyDeviceToHost)); printf("        (issue loop of the last step: %lld ns)\n", ti); }
+            if (mode == 8 || mode == 9) { long long ti; CK(cudaMemcpy(&ti, out + G, 8, cudaMemcpyDeviceToHost)); printf("        (issue loop of the last step: %lld ns)\n", ti); }
             printf("G=%3d  %-44s load %6.0f ns mean / %6.0f ns max per step (%.1f GB/s per SM), step %6.0f ns\n", G, names[mode],
                    mean / steps, mx / steps, TILE / (mean / steps), ms * 1e6 / steps);
         }
