@@ -224,12 +224,15 @@ int r2d2_tc_torso_fwd_u8(const uint8_t* slab, int B, int S, int s0, int nt, cons
  * and target nets, learner.py:71-72,79: both read the sampled frames; the pass is bound by
  * gathering the receptive fields, which is done once).  Net a covers frames 0..nt of every
  * sequence -> a1_a [nt*B,32,20,20]; net b covers frames s0_b..nt -> a1_b [(nt-s0_b)*B,32,20,20].
- * r2d2_tc_torso_fwd_tail runs the remaining two layers of one network from its a1. */
+ * r2d2_tc_torso_fwd_tail runs the remaining two layers of one network from its a1; with feat_hi /
+ * feat_lo (bf16 [R,1568], optional, together) the last layer also writes the r2d2_split_bf16 image
+ * of feat that the input projection consumes. */
 int r2d2_tc_conv1_fwd_dual_u8(const uint8_t* slab, int B, int S, int nt, const float* w1_a,
                               const float* b1_a, float* a1_a, const float* w1_b, const float* b1_b,
                               float* a1_b, int s0_b, void* stream);
 int r2d2_tc_torso_fwd_tail(const float* a1, int R, const float* w2, const float* b2, const float* w3,
-                           const float* b3, float* a2, float* feat, void* stream);
+                           const float* b3, float* a2, float* feat, void* feat_hi, void* feat_lo,
+                           void* stream);
 int r2d2_tc_torso_fwd_f32(const float* frames, int R, const float* w1, const float* b1,
                           const float* w2, const float* b2, const float* w3, const float* b3,
                           float* a1, float* a2, float* feat, void* stream);

@@ -95,7 +95,8 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
                    const float* __restrict__ bias, float* __restrict__ out, const int R,
                    const float in_scale, const float* __restrict__ w1 = nullptr,
                    const float* __restrict__ bias1 = nullptr, float* __restrict__ out1 = nullptr,
-                   const int skip1 = 0) {
+                   const int skip1 = 0, __nv_bfloat16* __restrict__ out_hi = nullptr,
+                   __nv_bfloat16* __restrict__ out_lo = nullptr) {
     constexpr int K = CIN * KH * KH, NKB = (K + 63) / 64, KP = NKB * 64;
     constexpr int P = HOUT * HOUT, COUT = 32;
     constexpr bool NEED_LO = sizeof(T) != 1;                 // u8 pixels are exact in bf16
@@ -337,11 +338,24 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
                 }
                 const int fo = net == 0 ? fr : fr - skip1;         // net 1 starts skip1 frames later
                 if (m < Mtot && fo >= 0) {
-                    float* o = (net == 0 ? out : out1) + (long long)fo * COUT * P + p;
+                    const long long oo = (long long)fo * COUT * P + p;
+                    float* o = (net == 0 ? out : out1) + oo;
                     const float* bs = net == 0 ? bias : bias1;
+                    if (NW == 1 && out_hi) {
+                        // also emit the bf16 (hi, lo) split the next contraction consumes
 #pragma unroll
-                    for (int co = 0; co < COUT; ++co)
-                        o[(long long)co * P] = fmaxf(fmaf(__uint_as_float(r[co]), in_scale, __ldg(bs + co)), 0.f);
+                        for (int co = 0; co < COUT; ++co) {
+                            const float x = fmaxf(fmaf(__uint_as_float(r[co]), in_scale, __ldg(bs + co)), 0.f);
+                            const __nv_bfloat16 h = __float2bfloat16_rn(x);
+                            o[(long long)co * P] = x;
+                            out_hi[oo + (long long)co * P] = h;
+                            out_lo[oo + (long long)co * P] = __float2bfloat16_rn(x - __bfloat162float(h));
+                        }
+                    } else {
+#pragma unroll
+                        for (int co = 0; co < COUT; ++co)
+                            o[(long long)co * P] = fmaxf(fmaf(__uint_as_float(r[co]), in_scale, __ldg(bs + co)), 0.f);
+                    }
                 }
             }
         }
@@ -353,7 +367,8 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
 
 template <class T, int CIN, int KH, int HIN, int HOUT, int STRIDE>
 static int launch_tc_conv(const char* name, const T* in, FrameMap fm, const float* w, const float* b,
-                          float* out, int R, float in_scale, cudaStream_t st) {
+                          float* out, int R, float in_scale, cudaStream_t st,
+                          __nv_bfloat16* out_hi = nullptr, __nv_bfloat16* out_lo = nullptr) {
     constexpr int K = CIN * KH * KH, NKB = (K + 63) / 64;
     constexpr bool NEED_LO = sizeof(T) != 1;
     constexpr int NPW = (sizeof(T) == 1 && KH == 8) ? 8 : 16;
@@ -364,7 +379,7 @@ static int launch_tc_conv(const char* name, const T* in, FrameMap fm, const floa
     const int ntiles = (int)((Mtot + 127) / 128);
     int grid = sm_count();
     if (grid > ntiles) grid = ntiles;
-    R2D2_LAUNCH(name, st, kern<<<grid, NPW * 32 + 160, smem, st>>>(in, fm, w, b, out, R, in_scale, nullptr, nullptr, nullptr, 0));
+    R2D2_LAUNCH(name, st, kern<<<grid, NPW * 32 + 160, smem, st>>>(in, fm, w, b, out, R, in_scale, nullptr, nullptr, nullptr, 0, out_hi, out_lo));
     return R2D2_OK;
 }
 
@@ -380,7 +395,7 @@ static int launch_tc_conv1_dual(const uint8_t* in, FrameMap fm, const float* wa,
     const int ntiles = (int)((Mtot + 127) / 128);
     int grid = sm_count();
     if (grid > ntiles) grid = ntiles;
-    R2D2_LAUNCH("tc_conv1_fwd_dual", st, kern<<<grid, 416, smem, st>>>(in, fm, wa, ba, outa, R, 1.f / 255.f, wb, bb, outb, skip_b));
+    R2D2_LAUNCH("tc_conv1_fwd_dual", st, kern<<<grid, 416, smem, st>>>(in, fm, wa, ba, outa, R, 1.f / 255.f, wb, bb, outb, skip_b, nullptr, nullptr));
     return R2D2_OK;
 }
 
@@ -1046,13 +1061,17 @@ int r2d2_tc_conv1_fwd_dual_u8(const uint8_t* slab, int B, int S, int nt, const f
 }
 
 int r2d2_tc_torso_fwd_tail(const float* a1, int R, const float* w2, const float* b2, const float* w3,
-                           const float* b3, float* a2, float* feat, void* stream) {
+                           const float* b3, float* a2, float* feat, void* feat_hi, void* feat_lo,
+                           void* stream) {
     R2D2_REQUIRE(a1 && w2 && b2 && w3 && b3 && a2 && feat && R > 0, "tc_torso_fwd_tail: bad args");
+    R2D2_REQUIRE((feat_hi == nullptr) == (feat_lo == nullptr), "tc_torso_fwd_tail: feat_hi and feat_lo go together");
     int rc = launch_tc_conv<float, 32, 4, 20, 9, 2>("tc_conv2_fwd", a1, FrameMap{0, 0, 0, 12800}, w2, b2, a2,
                                                     R, 1.f, as_stream(stream));
     if (rc) return rc;
     return launch_tc_conv<float, 32, 3, 9, 7, 1>("tc_conv3_fwd", a2, FrameMap{0, 0, 0, 2592}, w3, b3, feat,
-                                                 R, 1.f, as_stream(stream));
+                                                 R, 1.f, as_stream(stream),
+                                                 static_cast<__nv_bfloat16*>(feat_hi),
+                                                 static_cast<__nv_bfloat16*>(feat_lo));
 }
 
 // data gradients of conv3 (into the 9x9 layer) and conv2 (into the 20x20 layer), ReLU' fused

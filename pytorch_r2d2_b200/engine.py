@@ -49,10 +49,12 @@ def conv1_fwd_dual_u8(slab, nt, wa: Weights, a1_a, wb: Weights, a1_b, s0_b):
               P(wb.w1), P(wb.b1), P(a1_b, "f32"), s0_b, S())
 
 
-def torso_fwd_tail(a1, w: Weights, a2, feat):
-    """conv2 + conv3 of one net from its first-layer activations."""
+def torso_fwd_tail(a1, w: Weights, a2, feat, feat16=None):
+    """conv2 + conv3 of one net from its first-layer activations; feat16 = (hi, lo) bf16 buffers
+    that also receive the split image of feat."""
+    hi, lo = (P(feat16[0], "bf16"), P(feat16[1], "bf16")) if feat16 is not None else (None, None)
     _lib.call("r2d2_tc_torso_fwd_tail", P(a1, "f32"), a1.shape[0], P(w.w2), P(w.b2), P(w.w3), P(w.b3),
-              P(a2, "f32"), P(feat, "f32"), S())
+              P(a2, "f32"), P(feat, "f32"), hi, lo, S())
 
 
 def torso_fwd_f32(frames, w: Weights, a1, a2, feat, tc=False):

@@ -287,7 +287,7 @@ class Learner:
             next_state[0:BI], evaluation on next_state[BI:T].  Independent of the online net
             until the TD target, so in bf16 mode it runs on the side stream."""
             if fused_conv1:
-                engine.torso_fwd_tail(ws["a1_tg"], wt, ws["a2_tg"], ws["feat_tg"])
+                engine.torso_fwd_tail(ws["a1_tg"], wt, ws["a2_tg"], ws["feat_tg"], ws["feat16_tg"])
             else:
                 engine.torso_fwd_u8(slab, n, T, wt, ws["a1_tg"], ws["a2_tg"], ws["feat_tg"], tc=bf16)
             ws["hs_tg"][0].copy_(batch["target_hs"])
@@ -295,7 +295,8 @@ class Learner:
             if bf16:
                 split(wt.w_ih, ws["w_ih16_t"])
                 split(wt.head_w1, ws["hw1_16_t"])
-                split(ws["feat_tg"], ws["feat16_tg"])
+                if not fused_conv1:
+                    split(ws["feat_tg"], ws["feat16_tg"])
                 engine.tc_linear_x3(ws["w_ih16_t"][0], ws["w_ih16_t"][1], ws["feat16_tg"][0],
                                     ws["feat16_tg"][1], wt.b_ih, wt.b_hh, y32=ws["xpT_tg"], bias_row=True)
                 engine.tc_lstm_seq_fwd(ws["xpT_tg"], 0, wt.w_hh, ws["hs_tg"], ws["cs_tg"], None, T, B, H,
@@ -327,7 +328,7 @@ class Learner:
         #      from the state left after state[T-1] (the reference never resets it:
         #      learner.py:86,91)
         if fused_conv1:
-            engine.torso_fwd_tail(ws["a1_on"], w, ws["a2_on"], ws["feat_on"])
+            engine.torso_fwd_tail(ws["a1_on"], w, ws["a2_on"], ws["feat_on"], ws["feat16_on"])
         else:
             engine.torso_fwd_u8(slab, 0, T + n, w, ws["a1_on"], ws["a2_on"], ws["feat_on"], tc=bf16)
         ws["hs_on"][0].copy_(batch["hs"])
@@ -337,7 +338,8 @@ class Learner:
             # xproj^T[4H, frames*B] = W_ih . feat^T + (b_ih + b_hh) per row
             split(w.w_ih, ws["w_ih16"])
             split(w.head_w1, ws["hw1_16"])
-            split(ws["feat_on"], ws["feat16_on"])
+            if not fused_conv1:
+                split(ws["feat_on"], ws["feat16_on"])
             engine.tc_linear_x3(ws["w_ih16"][0], ws["w_ih16"][1], ws["feat16_on"][0], ws["feat16_on"][1],
                                 w.b_ih, w.b_hh, y32=ws["xpT_on"], bias_row=True)
             sc = ws["lstm_scratch"]

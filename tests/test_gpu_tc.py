@@ -123,9 +123,13 @@ def test_tc_conv1_dual_matches_single(cuda_device):
         d1.fill_(float("nan"))
         engine.conv1_fwd_dual_u8(slab, S, wa, c1, wb, d1, s0)
         assert torch.equal(c1, a1) and torch.equal(d1, b1)
-        engine.torso_fwd_tail(c1, wa, c2, fc)
+        f16 = torch.zeros(2, B * S, 1568, dtype=torch.bfloat16, device="cuda")
+        engine.torso_fwd_tail(c1, wa, c2, fc, f16)
         engine.torso_fwd_tail(d1, wb, d2, fd)
         assert torch.equal(fc, fa) and torch.equal(fd, fb)
+        # the fused (hi, lo) image of feat == r2d2_split_bf16(feat)
+        hi = fa.bfloat16()
+        assert torch.equal(f16[0], hi) and torch.equal(f16[1], (fa - hi.float()).bfloat16())
 
 
 @pytest.mark.parametrize("H,B,T", [(256, 4, 5), (512, 64, 6), (512, 8, 3), (256, 100, 2)])
