@@ -214,6 +214,10 @@ int r2d2_torso_bwd_f32(const float* frames, int R, const float* a1, const float*
  * and - on transposed bf16 copies - the data and weight gradients of both. */
 int r2d2_tc_linear(const void* x_bf16, const void* w_bf16, const float* bias1, const float* bias2,
                    float* y_f32, void* y_bf16, int M, int N, int K, int relu, void* stream);
+/* y[M,N] = mask[M,N] > 0 ? x.w^T : 0 -- a data gradient with the ReLU' of the layer it flows
+ * into fused (mask = that layer's forward output), e.g. dL/dfeat masked by feat. */
+int r2d2_tc_linear_masked(const void* x_bf16, const void* w_bf16, const float* mask, float* y_f32,
+                          int M, int N, int K, void* stream);
 /* conv torso forward on tensor cores (same contract as r2d2_torso_fwd_{u8,f32}): implicit GEMM,
  * patches gathered by producer warps into swizzled shared memory, bf16x3 compensation, weights
  * resident, two TMEM accumulators */
@@ -251,11 +255,12 @@ int r2d2_tc_lstm_seq_fwd(const float* xprojT, int64_t ldx, int64_t col0, const f
                          float* hs_ext, float* cs_ext, float* gates, int T, int B, int H,
                          void* scratch, void* stream);
 /* Persistent BPTT on tensor cores (same contract as r2d2_lstm_seq_bwd, plain bf16 operands):
- * dG_{t+1} streamed by TMA, W_hh^T slice resident, dL/dc in registers, grid-wide counter. */
+ * dG_{t+1} pulled in by bulk copies, W_hh^T slice resident, dL/dc in registers, grid-wide counter.
+ * dgates_bf16 (optional, [T,B,4H] bf16): a rounded copy of dgates for the gradient GEMMs. */
 int64_t r2d2_tc_lstm_bwd_scratch_bytes(int B, int H);
 int r2d2_tc_lstm_seq_bwd(const float* dhs, const float* w_hh, const float* gates,
-                         const float* cs_ext, float* dgates, int T, int B, int H, void* scratch,
-                         void* stream);
+                         const float* cs_ext, float* dgates, void* dgates_bf16, int T, int B, int H,
+                         void* scratch, void* stream);
 /* conv torso backward split for the tensor-core path: r2d2_torso_bwd_dgrad_u8 runs the ReLU
  * masks, data gradients and bias gradients (scratch as r2d2_torso_bwd_u8: [dz2 | dz1 | partials])
  * and r2d2_tc_torso_wgrad_u8 the three weight gradients on tcgen05 (plain bf16, the forward's

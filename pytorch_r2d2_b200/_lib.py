@@ -59,7 +59,7 @@ PROTOTYPES = {
     "r2d2_tc_lstm_scratch_bytes": (_L, [_I, _I]),
     "r2d2_tc_lstm_seq_fwd": (_I, [_P, _L, _L, _P, _P, _P, _P, _I, _I, _I, _P, _P]),
     "r2d2_tc_lstm_bwd_scratch_bytes": (_L, [_I, _I]),
-    "r2d2_tc_lstm_seq_bwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _P, _P]),
+    "r2d2_tc_lstm_seq_bwd": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P]),
     "r2d2_torso_bwd_dgrad_u8": (_I, [_P, _I, _I, _I, _I] + [_P] * 10 + [_P]),
     "r2d2_tc_torso_wgrad_u8": (_I, [_P, _I, _I, _I, _I] + [_P] * 9 + [_P]),
     "r2d2_reduce_partials": (_I, [_P, _P, _L, _I, _P]),
@@ -69,6 +69,7 @@ PROTOTYPES = {
     "r2d2_chansum": (_I, [_P, _P, _I, _I, _P, _P]),
     "r2d2_tc_conv_wgrad_layer": (_I, [_I, _P, _I, _I, _I, _I, _P, _P, _P, _P]),
     "r2d2_tc_linear": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
+    "r2d2_tc_linear_masked": (_I, [_P, _P, _P, _P, _I, _I, _I, _P]),
     "r2d2_tc_linear_x3": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "r2d2_split_bf16": (_I, [_P, _P, _P, _L, _P]),
     "r2d2_cast_bf16": (_I, [_P, _P, _L, _P]),

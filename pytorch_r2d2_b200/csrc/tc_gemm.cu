@@ -26,6 +26,7 @@ struct TcEpilogue {
     const float* bias2;
     int relu;
     int bias_row;           // biases indexed by output row m instead of column n
+    const float* mask;      // optional [M, ldc]: outputs where mask <= 0 are written as 0 (ReLU')
 };
 
 __device__ __forceinline__ uint32_t pack2_bf16(float a, float b) {
@@ -128,6 +129,13 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                         if (ep.bias2) x += __ldg(ep.bias2 + (ep.bias_row ? m : n + e));
                         if (ep.relu) x = fmaxf(x, 0.f);
                         v[e] = x;
+                    }
+                    if (ep.mask) {
+                        const float4 mk = __ldg(reinterpret_cast<const float4*>(ep.mask + (long long)m * ep.ldc + n));
+                        if (!(mk.x > 0.f)) v[0] = 0.f;
+                        if (!(mk.y > 0.f)) v[1] = 0.f;
+                        if (!(mk.z > 0.f)) v[2] = 0.f;
+                        if (!(mk.w > 0.f)) v[3] = 0.f;
                     }
                     if (ep.c32)
                         *reinterpret_cast<float4*>(ep.c32 + (long long)m * ep.ldc + n) =
@@ -389,7 +397,8 @@ extern "C" {
 
 static int tc_linear_impl(const void* x_hi, const void* x_lo, const void* w_hi, const void* w_lo,
                           const float* bias1, const float* bias2, float* y_f32, void* y_bf16, int M,
-                          int N, int K, int relu, void* stream) {
+                          int N, int K, int relu, void* stream, const float* mask = nullptr) {
+    R2D2_REQUIRE(!mask || (!x_lo && ((uintptr_t)mask % 16) == 0), "tc_linear: mask is for the plain bf16 form, 16-byte aligned");
     R2D2_REQUIRE(x_hi && w_hi && (y_f32 || y_bf16) && M > 0 && N > 0 && K > 0, "tc_linear: bad args");
     R2D2_REQUIRE((x_lo == nullptr) == (w_lo == nullptr), "tc_linear: give both lo parts or neither");
     R2D2_REQUIRE(N % 4 == 0, "tc_linear: N must be a multiple of 4 (N=%d)", N);
@@ -409,7 +418,7 @@ static int tc_linear_impl(const void* x_hi, const void* x_lo, const void* w_hi, 
         if (rc) return rc;
         rc = make_tmap(&tb_lo, w_lo, N, K, BNx);
         if (rc) return rc;
-        TcEpilogue ep{y_f32, reinterpret_cast<__nv_bfloat16*>(y_bf16), N, bias1, bias2, relu & 1, (relu >> 1) & 1};
+        TcEpilogue ep{y_f32, reinterpret_cast<__nv_bfloat16*>(y_bf16), N, bias1, bias2, relu & 1, (relu >> 1) & 1, nullptr};
         dim3 grid((M + TC_BM - 1) / TC_BM, (N + BNx - 1) / BNx);
         if (wide) {
             const int smem = 2 * (2 * TC_BM * TC_BK * 2 + 2 * 256 * TC_BK * 2) + 1024;
@@ -441,7 +450,7 @@ static int tc_linear_impl(const void* x_hi, const void* x_lo, const void* w_hi, 
         attr_set = true;
     }
     TcEpilogue ep{y_f32, reinterpret_cast<__nv_bfloat16*>(y_bf16), N, bias1, bias2, relu & 1,
-                  (relu >> 1) & 1};
+                  (relu >> 1) & 1, mask};
     dim3 grid((M + TC_BM - 1) / TC_BM, (N + BN - 1) / BN);
     const int nseg = x_lo ? 3 : 1;
     R2D2_LAUNCH(nseg == 3 ? "tc_gemm_kernel_x3" : "tc_gemm_kernel", as_stream(stream),
@@ -454,6 +463,13 @@ int r2d2_tc_linear(const void* x_bf16, const void* w_bf16, const float* bias1, c
                    float* y_f32, void* y_bf16, int M, int N, int K, int relu, void* stream) {
     return tc_linear_impl(x_bf16, nullptr, w_bf16, nullptr, bias1, bias2, y_f32, y_bf16, M, N, K, relu,
                           stream);
+}
+
+int r2d2_tc_linear_masked(const void* x_bf16, const void* w_bf16, const float* mask, float* y_f32,
+                          int M, int N, int K, void* stream) {
+    R2D2_REQUIRE(mask && y_f32, "tc_linear_masked: mask and y_f32 required");
+    return tc_linear_impl(x_bf16, nullptr, w_bf16, nullptr, nullptr, nullptr, y_f32, nullptr, M, N, K, 0,
+                          stream, mask);
 }
 
 int r2d2_tc_linear_x3(const void* x_hi, const void* x_lo, const void* w_hi, const void* w_lo,

@@ -391,6 +391,7 @@ struct LstmBwdArgs {
     const float* gates;    // [T, B, 4H] post-activation i,f,g,o
     const float* cs_ext;   // [(T+1), B, H], slot t = c_{t-1}, slot t+1 = c_t
     float* dgates;         // [T, B, 4H] out: pre-activation gradients
+    __nv_bfloat16* dgates16;   // optional [T, B, 4H] bf16 copy (operand of the gradient GEMMs)
     __nv_bfloat16* dg16;   // [2, 4H/64, B, 64] ping-pong, k-block-major (contiguous TMA boxes)
     int* counter;
     int T, B, H;
@@ -628,6 +629,16 @@ tc_lstm_bwd_kernel(const LstmBwdArgs a) {
                     *reinterpret_cast<float4*>(dgp + 2 * H + j) = make_float4(dg[j], dg[j + 1], dg[j + 2], dg[j + 3]);
                     *reinterpret_cast<float4*>(dgp + 3 * H + j) = make_float4(dov[j], dov[j + 1], dov[j + 2], dov[j + 3]);
                 }
+                if (a.dgates16) {
+                    __nv_bfloat16* d16r = a.dgates16 + ((long long)t * B + rb) * K4 + u0 + mu;
+#pragma unroll
+                    for (int j = 0; j < EPT; j += 4) {
+                        *reinterpret_cast<uint2*>(d16r + j) = make_uint2(ls_pack(di[j], di[j + 1]), ls_pack(di[j + 2], di[j + 3]));
+                        *reinterpret_cast<uint2*>(d16r + H + j) = make_uint2(ls_pack(df[j], df[j + 1]), ls_pack(df[j + 2], df[j + 3]));
+                        *reinterpret_cast<uint2*>(d16r + 2 * H + j) = make_uint2(ls_pack(dg[j], dg[j + 1]), ls_pack(dg[j + 2], dg[j + 3]));
+                        *reinterpret_cast<uint2*>(d16r + 3 * H + j) = make_uint2(ls_pack(dov[j], dov[j + 1]), ls_pack(dov[j + 2], dov[j + 3]));
+                    }
+                }
             }
         }
     }
@@ -712,8 +723,8 @@ int64_t r2d2_tc_lstm_bwd_scratch_bytes(int B, int H) {
 }
 
 int r2d2_tc_lstm_seq_bwd(const float* dhs, const float* w_hh, const float* gates,
-                         const float* cs_ext, float* dgates, int T, int B, int H, void* scratch,
-                         void* stream) {
+                         const float* cs_ext, float* dgates, void* dgates_bf16, int T, int B, int H,
+                         void* scratch, void* stream) {
     R2D2_REQUIRE(dhs && w_hh && gates && cs_ext && dgates && scratch, "tc_lstm_seq_bwd: null pointer");
     R2D2_REQUIRE(T > 0 && B > 0 && H > 0 && H % 64 == 0 && H <= 512,
                  "tc_lstm_seq_bwd: H must be a multiple of 64 and <= 512 (H=%d)", H);
@@ -725,6 +736,8 @@ int r2d2_tc_lstm_seq_bwd(const float* dhs, const float* w_hh, const float* gates
     uint8_t* sc = static_cast<uint8_t*>(scratch);
     LstmBwdArgs a;
     a.dhs = dhs; a.w_hh = w_hh; a.gates = gates; a.cs_ext = cs_ext; a.dgates = dgates;
+    a.dgates16 = static_cast<__nv_bfloat16*>(dgates_bf16);
+    R2D2_REQUIRE(((uintptr_t)dgates_bf16 % 8) == 0, "tc_lstm_seq_bwd: misaligned dgates_bf16");
     a.dg16 = reinterpret_cast<__nv_bfloat16*>(sc);
     a.counter = reinterpret_cast<int*>(sc + dg16);
     a.T = T; a.B = B; a.H = H;

@@ -183,6 +183,13 @@ def tc_linear(x16, w16, b1, b2, y32=None, y16=None, relu=False):
               P(y32, "f32", True), P(y16, "bf16", True), M, N, K, int(relu), S())
 
 
+def tc_linear_masked(x16, w16, mask, y32):
+    """y = (mask > 0) * (x . w^T): data gradient with the downstream ReLU' fused."""
+    M, K = x16.shape
+    N = w16.shape[0]
+    _lib.call("r2d2_tc_linear_masked", P(x16, "bf16"), P(w16, "bf16"), P(mask, "f32"), P(y32, "f32"), M, N, K, S())
+
+
 def tc_linear_x3(x_hi, x_lo, w_hi, w_lo, b1, b2, y32=None, y16=None, relu=False, bias_row=False):
     M, K = x_hi.shape
     N = w_hi.shape[0]
@@ -195,9 +202,9 @@ def tc_lstm_bwd_scratch_bytes(B, H):
     return int(_lib.load().r2d2_tc_lstm_bwd_scratch_bytes(B, H))
 
 
-def tc_lstm_seq_bwd(dhs, w_hh, gates, cs_ext, dgates, T, B, H, scratch):
+def tc_lstm_seq_bwd(dhs, w_hh, gates, cs_ext, dgates, T, B, H, scratch, dgates16=None):
     _lib.call("r2d2_tc_lstm_seq_bwd", P(dhs, "f32"), P(w_hh, "f32"), P(gates, "f32"), P(cs_ext, "f32"),
-              P(dgates, "f32"), T, B, H, P(scratch), S())
+              P(dgates, "f32"), P(dgates16, "bf16", True), T, B, H, P(scratch), S())
 
 
 def tc_lstm_scratch_bytes(B, H):

@@ -14,6 +14,7 @@ the data-parallel gradient allreduce.
 """
 from __future__ import annotations
 
+import contextlib
 import os
 from copy import deepcopy
 
@@ -208,7 +209,7 @@ class Learner:
             ws["cpart"] = [f(296 * 32), f(296 * 32), f(296 * 32)]   # R2D2_CHANSUM_PART_FLOATS
             ws["side_stream"] = torch.cuda.Stream(device=dev)
             ws["aux_stream"] = torch.cuda.Stream(device=dev)
-            ws["ev_aux"] = [torch.cuda.Event() for _ in range(2)]
+            ws["ev_aux"] = [torch.cuda.Event() for _ in range(3)]
             ws["events"] = [torch.cuda.Event() for _ in range(16)]
             ws["ev_fork"], ws["ev_join"] = torch.cuda.Event(), torch.cuda.Event()
             ws["dhid16"], ws["dhidT16"], ws["hsT16"] = h(M, 2 * H), h(2 * H, M), h(H, M)
@@ -338,6 +339,14 @@ class Learner:
             # xproj^T[4H, frames*B] = W_ih . feat^T + (b_ih + b_hh) per row
             split(w.w_ih, ws["w_ih16"])
             split(w.head_w1, ws["hw1_16"])
+            # transposed bf16 weights for the backward data gradients: weight-only work, done now
+            # on the idle third stream instead of between the gradient kernels on the critical path
+            if overlap:
+                ws["ev_aux"][2].record(main)
+                ws["aux_stream"].wait_event(ws["ev_aux"][2])
+            with torch.cuda.stream(ws["aux_stream"]) if overlap else contextlib.nullcontext():
+                engine.transpose_cast_bf16(w.head_w1, ws["hw1T16"])
+                engine.transpose_cast_bf16(w.w_ih, ws["w_ihT16"])
             if not fused_conv1:
                 split(ws["feat_on"], ws["feat16_on"])
             engine.tc_linear_x3(ws["w_ih16"][0], ws["w_ih16"][1], ws["feat16_on"][0], ws["feat16_on"][1],
@@ -420,10 +429,9 @@ class Learner:
 
             beside(head_wgrad)
             engine.cast_bf16(ws["dhid"], ws["dhid16"])
-            engine.transpose_cast_bf16(w.head_w1, ws["hw1T16"])
             engine.tc_linear(ws["dhid16"], ws["hw1T16"], None, None, y32=ws["dhs"])
             engine.tc_lstm_seq_bwd(ws["dhs"], w.w_hh, ws["gates"][BI:], ws["cs_on"][BI:], ws["dgates"],
-                                   L, B, H, ws["lstm_bwd_scratch"])
+                                   L, B, H, ws["lstm_bwd_scratch"], dgates16=ws["dg16"])
 
             def lstm_wgrad():
                 engine.transpose_cast_bf16(ws["dgates"], ws["dgT16"])
@@ -435,8 +443,6 @@ class Learner:
                 engine.tc_linear(ws["dgT16"], ws["featT16"], None, None, y32=g.w_ih)
 
             beside(lstm_wgrad, aux)       # the longest consumer chain gets a stream of its own
-            engine.cast_bf16(ws["dgates"], ws["dg16"])
-            engine.transpose_cast_bf16(w.w_ih, ws["w_ihT16"])
             engine.tc_linear(ws["dg16"], ws["w_ihT16"], None, None, y32=ws["dfeat"])
             # conv torso: scratch = [dz2 | dz1 | ...]; dz3 = dfeat masked in place
             sc32 = scratch.view(torch.float32)

@@ -28,6 +28,12 @@ def test_tc_linear_vs_fp64(cuda_device, M, N, K):
     y32r = torch.empty(M, N, device="cuda")
     engine.tc_linear(x, w, None, None, y32=y32r, relu=True)
     assert rel_err(y32r, torch.relu(x.double() @ w.double().T)) < 1e-4
+    # masked form: outputs where mask <= 0 are exactly zero, the others equal the plain product
+    mask = torch.randn(M, N, generator=g).cuda()
+    y32p, y32m = torch.empty(M, N, device="cuda"), torch.full((M, N), float("nan"), device="cuda")
+    engine.tc_linear(x, w, None, None, y32=y32p)
+    engine.tc_linear_masked(x, w, mask, y32m)
+    assert torch.equal(y32m, torch.where(mask > 0, y32p, torch.zeros_like(y32p)))
 
 
 @pytest.mark.parametrize("M,N,K", [(256, 128, 64), (5440, 2048, 1568), (2560, 1024, 512), (100, 132, 72)])
@@ -187,11 +193,13 @@ def test_tc_lstm_bwd_vs_autograd(cuda_device, H, B, T):
     cs_ext = torch.stack(cs).detach().cuda().contiguous()
     dgates = torch.full((T, B, 4 * H), float("nan"), device="cuda")
     scratch = torch.empty(engine.tc_lstm_bwd_scratch_bytes(B, H), dtype=torch.uint8, device="cuda")
+    dg16 = torch.zeros(T, B, 4 * H, dtype=torch.bfloat16, device="cuda")
     for _ in range(2):
-        engine.tc_lstm_seq_bwd(dhs.cuda(), w_hh.cuda(), gates_d, cs_ext, dgates, T, B, H, scratch)
+        engine.tc_lstm_seq_bwd(dhs.cuda(), w_hh.cuda(), gates_d, cs_ext, dgates, T, B, H, scratch, dgates16=dg16)
     torch.cuda.synchronize()
     err = rel_err(dgates, xproj.grad)
     assert err < 1e-2, err
+    assert torch.equal(dg16, dgates.bfloat16())              # the fused bf16 copy
     assert rel_err(dgates[-1], xproj.grad[-1]) < 1e-5        # last step has no recurrent term
 
 
