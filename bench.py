@@ -43,6 +43,9 @@ def parse():
                     help="e2e leg: fresh transitions uploaded from pinned host memory per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--tma-gather", action="store_true")
+    ap.add_argument("--dp-exchange", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: gradient exchange + optimiser as one kernel over NVLink peer memory "
+                         "(csrc/dp_peer.cu), or NCCL all-reduce followed by the per-rank optimiser kernel")
     ap.add_argument("--no-cuda-graph", action="store_true",
                     help="enqueue every kernel from Python instead of replaying the captured step")
     ap.add_argument("--precision", default="bf16", choices=["fp32", "bf16"],
@@ -121,7 +124,8 @@ def work_model(B, BI, L, n, H, nparams):
         "conv1_wgrad": ("flop", c1 * M), "conv2_wgrad": ("flop", c2 * M), "conv3_wgrad": ("flop", c3 * M),
         "conv_dgrad_kernel<4,20,9,2>": ("flop", c2 * M), "conv_dgrad_kernel<3,9,7,1>": ("flop", c3 * M),
         # tensor-core path
-        "tc_conv1_fwd": ("flop", c1 * fr_fwd), "tc_conv2_fwd": ("flop", c2 * fr_fwd),
+        "tc_conv1_fwd": ("flop", c1 * fr_fwd), "tc_conv1_fwd_dual": ("flop", c1 * fr_fwd),
+        "tc_conv2_fwd": ("flop", c2 * fr_fwd),
         "tc_conv3_fwd": ("flop", c3 * fr_fwd),
         "tc_gemm_kernel_x3": ("flop", lin_fwd), "tc_gemm_kernel": ("flop", lin_bwd),
         "tc_lstm_fwd_kernel": ("flop", lstm * steps_fwd), "tc_lstm_bwd_kernel": ("flop", lstm * (L - 1)),
@@ -130,7 +134,10 @@ def work_model(B, BI, L, n, H, nparams):
         # HBM-bound
         "gather_rows_kernel": ("byte", 2 * B * S * FRAME), "gather_rows_tma_kernel": ("byte", 2 * B * S * FRAME),
         "rmsprop_kernel": ("byte", 28 * nparams),
-        "split_bf16_kernel": ("byte", 8 * ((S + T) * B * FEAT + 2 * (4 * H * FEAT + 2 * H * H) + 3 * M * H)),
+        # (the feature split is fused into the conv3 epilogue; what is left: both nets' W_ih and
+        #  head weights, and the three head inputs)
+        "split_bf16_kernel": ("byte", 8 * (2 * (4 * H * FEAT + 2 * H * H) + 3 * M * H)),
+        "dp_reduce_rmsprop_kernel": ("byte", 4 * nparams * 3),   # per rank: grads in, params out, shard state
         "chansum_partial_kernel": ("byte", 4 * M * (1568 + 2592 + 12800)),
     }
     total = fr_fwd * (c1 + c2 + c3 + proj) + steps_fwd * lstm + 3 * M * 2 * (2 * H * H + 7 * H) \
@@ -284,9 +291,11 @@ def run_ours(args):
     L.batch_size, L.burn_in_length, L.learning_length, L.bootstrap_steps = B, BI, Ln, n
     L.sequence_length = BI + Ln
     L.replay_memory.use_tma_gather = args.tma_gather
-    # world > 1: the step is enqueued eagerly (capturing the NCCL all-reduce together with the
-    # cooperative LSTM launches hung in testing; the eager step time is the same)
-    L.use_cuda_graph = not args.no_cuda_graph and world == 1
+    # world > 1: gradient exchange + optimiser in one NVLink peer-memory kernel; with it the whole
+    # step is again a CUDA graph (capturing the NCCL all-reduce together with the cooperative LSTM
+    # launches hung in testing, so the NCCL variant is enqueued eagerly)
+    peer = world > 1 and args.dp_exchange == "peer" and L.enable_peer_exchange()
+    L.use_cuda_graph = not args.no_cuda_graph and (world == 1 or peer)
     fill_synthetic(L, args, rank)
     torch.manual_seed(1234 + rank)
 
@@ -449,6 +458,9 @@ def run_ours(args):
             "replay_slots_per_gpu": args.memory_size, "l2_policy": "inputs larger than L2 "
             "(replay ring >> 126 MB; each step gathers a fresh 154 MB slab)",
             "parallelism": f"dp{world}", "global_batch": world * B,
+            "dp_exchange": ("none" if world == 1 else
+                            "fused reduce+rmsprop kernel over NVLink peer memory" if peer else
+                            "nccl all-reduce + per-rank rmsprop"),
             "algorithmic_gflop_per_step_per_gpu": total_flops / 1e9,
             "e2e_ingest_rows_per_step": rows}),
         "e2e": {"value": e2e_value, "unit": "seq/s", "h2d_bytes_per_step": h2d,

@@ -43,13 +43,30 @@ class FusedCenteredRMSprop:
         self.square_avg = torch.zeros_like(flat)
         self.grad_avg = torch.zeros_like(flat)
         self.grad_scale = 1.0
+        self.peer = None
 
     def zero_grad(self):
         self.grad.zero_()
 
     def step(self):
+        if self.peer is not None:
+            # gradient sum over the ranks + optimiser + parameter all-gather in one kernel
+            self.peer.reduce_rmsprop(self.square_avg, self.grad_avg, self.lr, self.alpha, self.eps)
+            return
         engine.rmsprop_centered(self.net.flat_parameters(), self.grad, self.square_avg,
                                 self.grad_avg, self.lr, self.alpha, self.eps, self.grad_scale)
+
+    def attach_peer_exchange(self, peer):
+        """Switch to the fused NVLink reduce + RMSprop path: parameters and gradients move into the
+        IPC-mapped buffers, the optimiser state shrinks to this rank's shard."""
+        if self.square_avg.abs().max().item() != 0 or self.grad_avg.abs().max().item() != 0:
+            raise RuntimeError("attach_peer_exchange must be called before the first optimiser step")
+        self.net.rebase(peer.param)
+        self.grad = peer.grad
+        n_shard = parallel.shard_elems(peer.n, peer.world)
+        self.square_avg = torch.zeros(n_shard, dtype=torch.float32, device=peer.device)
+        self.grad_avg = torch.zeros(n_shard, dtype=torch.float32, device=peer.device)
+        self.peer = peer
 
     def state_dict(self):
         return {"square_avg": self.square_avg.clone(), "grad_avg": self.grad_avg.clone(),
@@ -217,13 +234,25 @@ class Learner:
         self._ws = ws
         return ws
 
+    def enable_peer_exchange(self) -> bool:
+        """Data-parallel on one node (one process per GPU): replace the NCCL all-reduce + per-rank
+        RMSprop by the fused NVLink reduce + optimiser kernel (csrc/dp_peer.cu).  Call on every
+        rank before the first train(); returns False (and changes nothing) for a single process."""
+        if parallel.active_world(self.process_group) < 2:
+            return False
+        peer = parallel.PeerExchange(self.net.layout.total, self.device, self.process_group)
+        self.optim.attach_peer_exchange(peer)
+        self._graph = None
+        return True
+
     # ------------------------------------------------------------------ the hot path
     def train(self, u=None, seq_index=None, next_action_override=None):
         """One learner step (learner.py:68-104).  `u` optionally supplies the B float64
         uniforms (default: drawn from torch's global CPU generator like the reference's
         multinomial); `seq_index` bypasses the draw (parity tests)."""
         if (self.use_cuda_graph and u is None and seq_index is None and next_action_override is None
-                and (parallel.active_world(self.process_group) == 1 or self.graph_collectives)):
+                and (parallel.active_world(self.process_group) == 1 or self.graph_collectives
+                     or self.optim.peer is not None)):
             return self._train_graphed()
         return self._train_eager(u, seq_index, next_action_override)
 
@@ -487,7 +516,8 @@ class Learner:
             engine.torso_bwd_u8(slab, BI, L, a1_l, a2_l, feat_l, ws["dfeat"], w, g, scratch)
 
         # ---- optimiser (data-parallel: sum gradients over ranks, 1/world folded into K10)
-        self.optim.grad_scale = parallel.allreduce_flat_grad(self.optim.grad, self.process_group)
+        if self.optim.peer is None:
+            self.optim.grad_scale = parallel.allreduce_flat_grad(self.optim.grad, self.process_group)
         self.optim.step()
 
         # ---- priorities (learner.py:102-104); the bf16 path already ran them beside the backward

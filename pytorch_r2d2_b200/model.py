@@ -207,17 +207,25 @@ class QNet(nn.Module):
         return all(p.data_ptr() == base + 4 * self.layout.offset(k) and p.device == self._flat.device
                    for k, p in zip(MODULE_ORDER, self._named()))
 
-    def _reflatten(self):
-        """Re-point the parameters into one flat buffer (after .to()/deepcopy broke the views)."""
+    def _reflatten(self, flat=None):
+        """Re-point the parameters into one flat buffer (after .to()/deepcopy broke the views), or
+        into a caller-supplied one (`flat`: e.g. the IPC-mapped buffer of the peer exchange)."""
         ps = self._named()
         dev = ps[0].device
         if dev.type != "cuda":
             raise RuntimeError("QNet parameters were moved off the GPU; there is no CPU path")
-        flat = torch.empty(self.layout.total, dtype=torch.float32, device=dev)
+        if flat is None:
+            flat = torch.empty(self.layout.total, dtype=torch.float32, device=dev)
+        elif flat.numel() != self.layout.total or flat.dtype != torch.float32 or flat.device != dev:
+            raise ValueError("rebase: need a contiguous f32 buffer of layout.total elements on the net's device")
         for k, p in zip(MODULE_ORDER, ps):
             self.layout.view(flat, k).copy_(p.data)
             p.data = self.layout.view(flat, k)
         self._flat, self._w, self.device = flat, None, dev
+
+    def rebase(self, flat: torch.Tensor) -> None:
+        """Move the parameters (values kept) into the given flat f32 buffer."""
+        self._reflatten(flat)
 
     def _weights(self) -> Weights:
         if not self._flat_ok():

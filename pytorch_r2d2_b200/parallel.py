@@ -55,3 +55,69 @@ def broadcast_flat_params(flat: torch.Tensor, src: int = 0, group=None) -> None:
     DP analogue of `target_net.load_state_dict(net.state_dict())`, learner.py:49)."""
     if active_world(group) > 1:
         dist.broadcast(flat, src=src, group=group)
+
+
+def shard_elems(n: int, world: int) -> int:
+    """Optimiser-state floats rank r keeps for its shard of an n-element parameter vector
+    (mirror of r2d2_dp_shard_elems: float4-granular shards + room for the scalar tail)."""
+    per = (n // 4 + world - 1) // world
+    return per * 4 + 4
+
+
+class _DevBuf:
+    """A raw device allocation exposed to torch through __cuda_array_interface__."""
+
+    def __init__(self, ptr: int, n: int, typestr: str):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
+
+
+class PeerExchange:
+    """Gradient / parameter / flag buffers of every rank mapped into this process over CUDA IPC,
+    for the fused NVLink reduce + RMSprop kernel (csrc/dp_peer.cu).  One process per GPU on one
+    node; the handles travel through torch.distributed (any backend)."""
+
+    def __init__(self, n: int, device, group=None):
+        import ctypes
+        from . import _lib
+        self.n, self.group = n, group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self.device = torch.device(device)
+        torch.cuda.set_device(self.device)
+        sizes = {"grad": n * 4, "param": n * 4, "flags": 1024}
+        own, handles = {}, {}
+        for name, nbytes in sizes.items():
+            p, h = ctypes.c_void_p(), ctypes.create_string_buffer(64)
+            _lib.call("r2d2_peer_alloc", nbytes, ctypes.byref(p), h)
+            own[name], handles[name] = p.value, bytes(h.raw)
+        torch.cuda.synchronize()
+        gathered = [None] * self.world
+        dist.all_gather_object(gathered, handles, group=group)
+        self._own, self._opened = own, []
+        self.ptrs = {name: [0] * self.world for name in sizes}
+        for r in range(self.world):
+            for name in sizes:
+                if r == self.rank:
+                    self.ptrs[name][r] = own[name]
+                else:
+                    p = ctypes.c_void_p()
+                    _lib.call("r2d2_peer_open", ctypes.create_string_buffer(gathered[r][name], 64), ctypes.byref(p))
+                    self.ptrs[name][r] = p.value
+                    self._opened.append(p.value)
+        arr = ctypes.c_void_p * self.world
+        self.c_ptrs = {name: arr(*self.ptrs[name]) for name in sizes}
+        self.grad = torch.as_tensor(_DevBuf(own["grad"], n, "<f4"), device=self.device)
+        self.param = torch.as_tensor(_DevBuf(own["param"], n, "<f4"), device=self.device)
+        dist.barrier(group=group)
+
+    def reduce_rmsprop(self, square_avg_shard, grad_avg_shard, lr, alpha, eps):
+        from . import _lib
+        _lib.call("r2d2_dp_reduce_rmsprop", self.rank, self.world, self.c_ptrs["grad"], self.c_ptrs["param"],
+                  self.c_ptrs["flags"], _lib.ptr(square_avg_shard, "f32"), _lib.ptr(grad_avg_shard, "f32"),
+                  self.n, float(lr), float(alpha), float(eps), 1.0 / self.world, _lib.stream_ptr())
+
+    def close(self):
+        from . import _lib
+        torch.cuda.synchronize()
+        for p in self._opened:
+            _lib.call("r2d2_peer_close", p)
+        self._opened = []

@@ -83,3 +83,15 @@ def test_no_product_import_of_oracle():
     for f in os.listdir(pkg):
         if f.endswith(".py"):
             assert "oracle" not in open(os.path.join(pkg, f)).read(), f
+
+
+def test_dp_shard_elems_matches_library():
+    """Host mirror of the optimiser-state shard size == the C entry point (no GPU work)."""
+    from pytorch_r2d2_b200 import _lib, parallel
+    lib = _lib.load()
+    for n in (1, 4, 7, 100_003, 4_737_000):
+        for world in (1, 2, 3, 8, 16):
+            assert parallel.shard_elems(n, world) == lib.r2d2_dp_shard_elems(n, world)
+            # the shards cover the float4 part and the tail fits behind the last one
+            per = (n // 4 + world - 1) // world
+            assert per * world >= n // 4 and parallel.shard_elems(n, world) >= per * 4 + n % 4
