@@ -315,8 +315,10 @@ int r2d2_rmsprop_centered(float* param, const float* grad, float* square_avg, fl
  * the optimiser step (learner.py:51,99-100) in one kernel over NVLink peer memory.
  * r2d2_peer_alloc: cudaMalloc (zero-filled) + CUDA IPC export (handle64: 64 bytes) of a buffer the
  * other ranks map with r2d2_peer_open.  r2d2_dp_reduce_rmsprop: grads/params/flags are arrays of
- * `world` device pointers (index = rank; the local rank's own buffers included; flags: >= 1 KiB,
- * zero at start).  Rank r reduces shard r of all gradients in rank order, applies centered RMSprop
+ * `world` device pointers (index = rank; the local rank's own buffers included; flags: 4 KiB,
+ * zero at start).  One call handles the slice [offset, offset+n) of the flat vectors ("bucket",
+ * 0..7, each with its own flags and its own state shards), so that slices whose gradients are
+ * complete early can be exchanged while the rest of the backward pass still runs.  Rank r reduces shard r of all gradients in rank order, applies centered RMSprop
  * (state only for its shard: r2d2_dp_shard_elems floats each) and writes the new parameters of its
  * shard into every rank's parameter buffer; the call returns (on the stream) when every rank's
  * shard has arrived.  All ranks must call it once per step; a missing rank traps after ~15 s. */
@@ -327,8 +329,8 @@ int r2d2_peer_free(void* ptr);
 int64_t r2d2_dp_shard_elems(int64_t n, int world);
 int r2d2_dp_reduce_rmsprop(int rank, int world, void* const* grads, void* const* params,
                            void* const* flags, float* square_avg_shard, float* grad_avg_shard,
-                           int64_t n, double lr, double alpha, double eps, double grad_scale,
-                           void* stream);
+                           int64_t offset, int bucket, int64_t n, double lr, double alpha, double eps,
+                           double grad_scale, void* stream);
 
 #ifdef __cplusplus
 }

@@ -51,9 +51,18 @@ __device__ __forceinline__ void wait_flag(const int* p, int want) {
 }
 
 __global__ void __launch_bounds__(256)
-dp_reduce_rmsprop_kernel(const DpPeers pe, const int rank, const int world, float* __restrict__ v,
-                         float* __restrict__ mavg, const long long n, const float lr,
-                         const float alpha, const float oma, const float eps, const float gscale) {
+dp_reduce_rmsprop_kernel(DpPeers pe, const int rank, const int world, float* __restrict__ v,
+                         float* __restrict__ mavg, const long long offset, const int bucket,
+                         const long long n, const float lr, const float alpha, const float oma,
+                         const float eps, const float gscale) {
+    // a bucket = the slice [offset, offset + n) of the flat vectors with its own flag block, so
+    // that slices whose gradients are complete early can be exchanged while the rest of the
+    // backward pass is still running
+    for (int r = 0; r < world; ++r) {
+        pe.grad[r] += offset;
+        pe.param[r] += offset;
+        pe.flags[r] += bucket * 128;
+    }
     int* my = pe.flags[rank];
     const int step = my[64] + 1;               // written only by this kernel's last CTA (below)
     // 1. my gradient is complete (every earlier kernel of this stream has finished)
@@ -185,8 +194,10 @@ int64_t r2d2_dp_shard_elems(int64_t n, int world) {
 
 int r2d2_dp_reduce_rmsprop(int rank, int world, void* const* grads, void* const* params,
                            void* const* flags, float* square_avg_shard, float* grad_avg_shard,
-                           int64_t n, double lr, double alpha, double eps, double grad_scale,
-                           void* stream) {
+                           int64_t offset, int bucket, int64_t n, double lr, double alpha, double eps,
+                           double grad_scale, void* stream) {
+    R2D2_REQUIRE(offset >= 0 && offset % 4 == 0 && bucket >= 0 && bucket < 8,
+                 "dp_reduce_rmsprop: offset must be a multiple of 4 elements, bucket in 0..7");
     R2D2_REQUIRE(world >= 1 && world <= DP_MAX_WORLD && rank >= 0 && rank < world,
                  "dp_reduce_rmsprop: world must be 1..%d (rank %d of %d)", DP_MAX_WORLD, rank, world);
     R2D2_REQUIRE(grads && params && flags && square_avg_shard && grad_avg_shard && n > 0,
@@ -208,7 +219,8 @@ int r2d2_dp_reduce_rmsprop(int rank, int world, void* const* grads, void* const*
     cudaStream_t st = as_stream(stream);
     R2D2_LAUNCH("dp_reduce_rmsprop_kernel", st,
                 dp_reduce_rmsprop_kernel<<<(unsigned)blocks, 256, 0, st>>>(
-                    pe, rank, world, square_avg_shard, grad_avg_shard, (long long)n, (float)lr,
+                    pe, rank, world, square_avg_shard, grad_avg_shard, (long long)offset, bucket,
+                    (long long)n, (float)lr,
                     (float)alpha, (float)(1.0 - alpha), (float)eps, (float)grad_scale));
     return R2D2_OK;
 }

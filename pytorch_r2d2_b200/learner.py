@@ -50,29 +50,54 @@ class FusedCenteredRMSprop:
 
     def step(self):
         if self.peer is not None:
-            # gradient sum over the ranks + optimiser + parameter all-gather in one kernel
-            self.peer.reduce_rmsprop(self.square_avg, self.grad_avg, self.lr, self.alpha, self.eps)
+            # gradient sum over the ranks + optimiser + parameter all-gather in one kernel per
+            # bucket; buckets already exchanged during the backward pass are skipped
+            for k in range(len(self.buckets)):
+                if k not in self._done:
+                    self.step_bucket(k)
+            self._done.clear()
             return
         engine.rmsprop_centered(self.net.flat_parameters(), self.grad, self.square_avg,
                                 self.grad_avg, self.lr, self.alpha, self.eps, self.grad_scale)
 
+    def step_bucket(self, k):
+        """Exchange + update bucket k now, on the current stream (its gradients must be complete)."""
+        off, n = self.buckets[k]
+        self.peer.reduce_rmsprop(self.square_avg[k], self.grad_avg[k], self.lr, self.alpha, self.eps,
+                                 offset=off, n=n, bucket=k)
+        self._done.add(k)
+
     def attach_peer_exchange(self, peer):
         """Switch to the fused NVLink reduce + RMSprop path: parameters and gradients move into the
         IPC-mapped buffers, the optimiser state shrinks to this rank's shard."""
-        if self.square_avg.abs().max().item() != 0 or self.grad_avg.abs().max().item() != 0:
-            raise RuntimeError("attach_peer_exchange must be called before the first optimiser step")
+        if self.peer is not None or self.square_avg.abs().max().item() != 0 or self.grad_avg.abs().max().item() != 0:
+            raise RuntimeError("attach_peer_exchange must be called once, before the first optimiser step")
         self.net.rebase(peer.param)
         self.grad = peer.grad
-        n_shard = parallel.shard_elems(peer.n, peer.world)
-        self.square_avg = torch.zeros(n_shard, dtype=torch.float32, device=peer.device)
-        self.grad_avg = torch.zeros(n_shard, dtype=torch.float32, device=peer.device)
+        # two buckets: [0] the conv torso (its gradients are the last to complete), [1] LSTM + head
+        # (complete half-way through the backward pass: exchanged beside the conv backward)
+        split = self.net.layout.offset("lstm.weight_ih")
+        assert split % 4 == 0
+        self.buckets = [(0, split), (split, peer.n - split)]
+        z = lambda n: torch.zeros(parallel.shard_elems(n, peer.world), dtype=torch.float32, device=peer.device)  # noqa: E731
+        self.square_avg = [z(n) for _, n in self.buckets]
+        self.grad_avg = [z(n) for _, n in self.buckets]
+        self._done = set()
         self.peer = peer
 
     def state_dict(self):
+        if self.peer is not None:     # sharded: this rank's shards of every bucket
+            return {"square_avg": [t.clone() for t in self.square_avg], "grad_avg": [t.clone() for t in self.grad_avg],
+                    "lr": self.lr, "alpha": self.alpha, "eps": self.eps, "rank": self.peer.rank, "world": self.peer.world}
         return {"square_avg": self.square_avg.clone(), "grad_avg": self.grad_avg.clone(),
                 "lr": self.lr, "alpha": self.alpha, "eps": self.eps}
 
     def load_state_dict(self, sd):
+        if self.peer is not None:
+            for dst, src in zip(self.square_avg + self.grad_avg, sd["square_avg"] + sd["grad_avg"]):
+                dst.copy_(src)
+            self.lr, self.alpha, self.eps = sd["lr"], sd["alpha"], sd["eps"]
+            return
         self.square_avg.copy_(sd["square_avg"])
         self.grad_avg.copy_(sd["grad_avg"])
         self.lr, self.alpha, self.eps = sd["lr"], sd["alpha"], sd["eps"]
@@ -472,6 +497,14 @@ class Learner:
                 engine.tc_linear(ws["dgT16"], ws["featT16"], None, None, y32=g.w_ih)
 
             beside(lstm_wgrad, aux)       # the longest consumer chain gets a stream of its own
+            if overlap_bwd and self.optim.peer is not None:
+                # LSTM + head gradients are complete once head_wgrad (side) and lstm_wgrad (aux) are:
+                # their exchange + update crosses NVLink beside the conv backward
+                e = next(ev)
+                e.record(side)
+                aux.wait_event(e)
+                with torch.cuda.stream(aux):
+                    self.optim.step_bucket(1)
             engine.tc_linear(ws["dg16"], ws["w_ihT16"], None, None, y32=ws["dfeat"])
             # conv torso: scratch = [dz2 | dz1 | ...]; dz3 = dfeat masked in place
             sc32 = scratch.view(torch.float32)

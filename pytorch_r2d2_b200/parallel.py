@@ -83,7 +83,7 @@ class PeerExchange:
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
         self.device = torch.device(device)
         torch.cuda.set_device(self.device)
-        sizes = {"grad": n * 4, "param": n * 4, "flags": 1024}
+        sizes = {"grad": n * 4, "param": n * 4, "flags": 4096}
         own, handles = {}, {}
         for name, nbytes in sizes.items():
             p, h = ctypes.c_void_p(), ctypes.create_string_buffer(64)
@@ -109,11 +109,14 @@ class PeerExchange:
         self.param = torch.as_tensor(_DevBuf(own["param"], n, "<f4"), device=self.device)
         dist.barrier(group=group)
 
-    def reduce_rmsprop(self, square_avg_shard, grad_avg_shard, lr, alpha, eps):
+    def reduce_rmsprop(self, square_avg_shard, grad_avg_shard, lr, alpha, eps, offset=0, n=None, bucket=0):
+        """Exchange + optimiser step for the slice [offset, offset+n) of the flat vectors (default:
+        all of it); every slice needs its own `bucket` id and its own state shards."""
         from . import _lib
+        n = self.n - offset if n is None else n
         _lib.call("r2d2_dp_reduce_rmsprop", self.rank, self.world, self.c_ptrs["grad"], self.c_ptrs["param"],
                   self.c_ptrs["flags"], _lib.ptr(square_avg_shard, "f32"), _lib.ptr(grad_avg_shard, "f32"),
-                  self.n, float(lr), float(alpha), float(eps), 1.0 / self.world, _lib.stream_ptr())
+                  offset, bucket, n, float(lr), float(alpha), float(eps), 1.0 / self.world, _lib.stream_ptr())
 
     def close(self):
         from . import _lib

@@ -23,19 +23,21 @@ def _worker(rank, world, port, out):
     # ---- kernel level: three steps against a local torch restatement (every rank can rebuild
     #      every rank's gradient from its seed)
     n, lr, alpha, eps = 100_003, 1e-3, 0.95, 1.5e-7
+    split = 40_000                      # two buckets, exchanged separately (bucket 1 first)
     pe = parallel.PeerExchange(n, dev)
     g0 = torch.Generator().manual_seed(7)
     p_ref = torch.randn(n, generator=g0).double()
     pe.param.copy_(p_ref.float())
-    v = torch.zeros(parallel.shard_elems(n, world), device=dev)
-    m = torch.zeros_like(v)
+    v = [torch.zeros(parallel.shard_elems(k, world), device=dev) for k in (split, n - split)]
+    m = [torch.zeros_like(x) for x in v]
     v_ref, m_ref = torch.zeros(n).double(), torch.zeros(n).double()
     p_ref = p_ref.float().double()
     dist.barrier()
     for step in range(3):
         grads = [torch.randn(n, generator=torch.Generator().manual_seed(100 * step + r)) for r in range(world)]
         pe.grad.copy_(grads[rank])
-        pe.reduce_rmsprop(v, m, lr, alpha, eps)
+        pe.reduce_rmsprop(v[1], m[1], lr, alpha, eps, offset=split, n=n - split, bucket=1)
+        pe.reduce_rmsprop(v[0], m[0], lr, alpha, eps, offset=0, n=split, bucket=0)
         torch.cuda.synchronize()
         g = sum(x.double() for x in grads) / world
         v_ref = alpha * v_ref + (1 - alpha) * g * g
