@@ -126,6 +126,9 @@ class Learner:
         # bf16 mode: run the target net's branch on a side stream next to the online net's
         # (False = one stream, e.g. to time kernels in isolation)
         self.overlap_streams = True
+        # run the step's critical chain (online net, data gradients) on a high-priority stream:
+        # when its kernels and the side streams' are ready together, its CTAs get the SMs first
+        self.prioritize_critical = True
         # capture the whole step (both streams) in a CUDA graph and replay it: removes ~110
         # launches worth of host work per step.  Only the default path (u drawn from the global
         # CPU generator, no overrides) is graphed; anything else runs eagerly.
@@ -250,6 +253,7 @@ class Learner:
             ws["wpart"] = [f(nsm * 32 * 256), f(nsm * 32 * 512), f(nsm * 32 * 288)]
             ws["cpart"] = [f(296 * 32), f(296 * 32), f(296 * 32)]   # R2D2_CHANSUM_PART_FLOATS
             ws["side_stream"] = torch.cuda.Stream(device=dev)
+            ws["crit_stream"] = torch.cuda.Stream(device=dev, priority=-1)
             ws["aux_stream"] = torch.cuda.Stream(device=dev)
             ws["ev_aux"] = [torch.cuda.Event() for _ in range(3)]
             ws["events"] = [torch.cuda.Event() for _ in range(16)]
@@ -308,6 +312,17 @@ class Learner:
         return self._graph_loss
 
     def _train_eager(self, u=None, seq_index=None, next_action_override=None):
+        if self.precision == "bf16" and self.overlap_streams and self.prioritize_critical:
+            ws = self._workspace()
+            outer, crit = torch.cuda.current_stream(), ws["crit_stream"]
+            crit.wait_stream(outer)
+            with torch.cuda.stream(crit):
+                loss = self._train_step(u, seq_index, next_action_override)
+            outer.wait_stream(crit)
+            return loss
+        return self._train_step(u, seq_index, next_action_override)
+
+    def _train_step(self, u=None, seq_index=None, next_action_override=None):
         rm = self.replay_memory
         B, BI, L, n, H = (self.batch_size, self.burn_in_length, self.learning_length,
                           self.bootstrap_steps, self.cell_size)
