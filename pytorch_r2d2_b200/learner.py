@@ -254,6 +254,7 @@ class Learner:
             ws["cpart"] = [f(296 * 32), f(296 * 32), f(296 * 32)]   # R2D2_CHANSUM_PART_FLOATS
             ws["side_stream"] = torch.cuda.Stream(device=dev)
             ws["crit_stream"] = torch.cuda.Stream(device=dev, priority=-1)
+            ws["aux2_stream"] = torch.cuda.Stream(device=dev)
             ws["aux_stream"] = torch.cuda.Stream(device=dev)
             ws["ev_aux"] = [torch.cuda.Event() for _ in range(3)]
             ws["events"] = [torch.cuda.Event() for _ in range(16)]
@@ -541,13 +542,13 @@ class Learner:
                 _lib.call("r2d2_tc_conv_wgrad_layer", 2, P(a1_l, "f32"), B, 0, 0, L, P(dz2, "f32"), P(g.w2),
                           P(ws["wpart"][1], "f32"), st())
 
-            beside(conv2_grads)
+            beside(conv2_grads, ws["aux2_stream"])
             _lib.call("r2d2_tc_conv_dgrad2", P(dz2, "f32"), P(w.w2), P(a1_l, "f32"), P(dz1, "f32"), M, st())
             _lib.call("r2d2_chansum", P(dz1, "f32"), P(g.b1), M, 400, P(ws["cpart"][0], "f32"), st())
             _lib.call("r2d2_tc_conv_wgrad_layer", 1, P(slab, "u8"), B, T + n, BI, L, P(dz1, "f32"), P(g.w1),
                       P(ws["wpart"][0], "f32"), st())
             if overlap_bwd:
-                for st_ in (side, aux):
+                for st_ in (side, aux, ws["aux2_stream"]):
                     e = next(ev)
                     e.record(st_)
                     main.wait_event(e)
