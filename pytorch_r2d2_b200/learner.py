@@ -255,6 +255,7 @@ class Learner:
             ws["side_stream"] = torch.cuda.Stream(device=dev)
             ws["crit_stream"] = torch.cuda.Stream(device=dev, priority=-1)
             ws["aux2_stream"] = torch.cuda.Stream(device=dev)
+            ws["xchg_stream"] = torch.cuda.Stream(device=dev, priority=-1)   # multi-GPU exchange: peers wait on it
             ws["aux_stream"] = torch.cuda.Stream(device=dev)
             ws["ev_aux"] = [torch.cuda.Event() for _ in range(3)]
             ws["events"] = [torch.cuda.Event() for _ in range(16)]
@@ -516,10 +517,12 @@ class Learner:
             if overlap_bwd and self.optim.peer is not None:
                 # LSTM + head gradients are complete once head_wgrad (side) and lstm_wgrad (aux) are:
                 # their exchange + update crosses NVLink beside the conv backward
-                e = next(ev)
-                e.record(side)
-                aux.wait_event(e)
-                with torch.cuda.stream(aux):
+                xs = ws["xchg_stream"]
+                for st_ in (side, aux):
+                    e = next(ev)
+                    e.record(st_)
+                    xs.wait_event(e)
+                with torch.cuda.stream(xs):
                     self.optim.step_bucket(1)
             engine.tc_linear(ws["dg16"], ws["w_ihT16"], None, None, y32=ws["dfeat"])
             # conv torso: scratch = [dz2 | dz1 | ...]; dz3 = dfeat masked in place
@@ -548,7 +551,7 @@ class Learner:
             _lib.call("r2d2_tc_conv_wgrad_layer", 1, P(slab, "u8"), B, T + n, BI, L, P(dz1, "f32"), P(g.w1),
                       P(ws["wpart"][0], "f32"), st())
             if overlap_bwd:
-                for st_ in (side, aux, ws["aux2_stream"]):
+                for st_ in (side, aux, ws["aux2_stream"]) + ((ws["xchg_stream"],) if self.optim.peer is not None else ()):
                     e = next(ev)
                     e.record(st_)
                     main.wait_event(e)
