@@ -304,6 +304,7 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    barrier()      # ranks enter the first (peer-synchronised) step together
     for _ in range(max(args.warmup, 3)):
         L.train()
     barrier()

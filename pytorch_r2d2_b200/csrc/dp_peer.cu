@@ -16,7 +16,8 @@
 //
 // Buffers that peers touch (gradient, parameters, flags) are cudaMalloc'ed by this library and
 // exported with CUDA IPC handles (one process per GPU); step numbers only grow, so flags never
-// need resetting.  Every wait is bounded: a lost peer traps instead of hanging the GPU.
+// need resetting.  Every wait is bounded: a lost peer traps (after about a minute) instead of
+// hanging the GPU.
 #include <cuda_runtime.h>
 
 #include <cstring>
@@ -43,11 +44,11 @@ __device__ __forceinline__ int ld_acquire_sys(const int* p) {
     return v;
 }
 __device__ __forceinline__ void wait_flag(const int* p, int want) {
-    for (unsigned it = 0; it < (1u << 27); ++it) {
+    for (unsigned it = 0; it < (1u << 29); ++it) {
         if (ld_acquire_sys(p) >= want) return;
         __nanosleep(100);
     }
-    __trap();   // ~15 s: a peer died or never reached this step
+    __trap();   // about a minute: a peer died or never reached this step
 }
 
 __global__ void __launch_bounds__(256)

@@ -271,7 +271,12 @@ class Learner:
         rank before the first train(); returns False (and changes nothing) for a single process."""
         if parallel.active_world(self.process_group) < 2:
             return False
-        peer = parallel.PeerExchange(self.net.layout.total, self.device, self.process_group)
+        try:
+            peer = parallel.PeerExchange(self.net.layout.total, self.device, self.process_group)
+        except parallel.PeerUnavailable as e:       # raised on every rank together: NCCL path stays
+            import warnings
+            warnings.warn(f"peer exchange unavailable, keeping the NCCL all-reduce: {e}")
+            return False
         self.optim.attach_peer_exchange(peer)
         self._graph = None
         return True

@@ -71,6 +71,10 @@ class _DevBuf:
         self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
 
 
+class PeerUnavailable(RuntimeError):
+    """CUDA IPC / peer access could not be set up on every rank (raised on ALL ranks together)."""
+
+
 class PeerExchange:
     """Gradient / parameter / flag buffers of every rank mapped into this process over CUDA IPC,
     for the fused NVLink reduce + RMSprop kernel (csrc/dp_peer.cu).  One process per GPU on one
@@ -85,29 +89,49 @@ class PeerExchange:
         torch.cuda.set_device(self.device)
         sizes = {"grad": n * 4, "param": n * 4, "flags": 4096}
         own, handles = {}, {}
-        for name, nbytes in sizes.items():
-            p, h = ctypes.c_void_p(), ctypes.create_string_buffer(64)
-            _lib.call("r2d2_peer_alloc", nbytes, ctypes.byref(p), h)
-            own[name], handles[name] = p.value, bytes(h.raw)
-        torch.cuda.synchronize()
+        try:
+            for name, nbytes in sizes.items():
+                p, h = ctypes.c_void_p(), ctypes.create_string_buffer(64)
+                _lib.call("r2d2_peer_alloc", nbytes, ctypes.byref(p), h)
+                own[name], handles[name] = p.value, bytes(h.raw)
+            torch.cuda.synchronize()
+            ok = True
+        except Exception as e:          # noqa: BLE001 -- the decision below must be collective
+            ok, why = False, repr(e)
+        # every rank must take the same branch: agree before anybody waits for anybody
+        if not self._all_ok(ok):
+            raise PeerUnavailable(f"rank {self.rank}: IPC export failed on some rank" + ("" if ok else f" ({why})"))
         gathered = [None] * self.world
         dist.all_gather_object(gathered, handles, group=group)
         self._own, self._opened = own, []
         self.ptrs = {name: [0] * self.world for name in sizes}
-        for r in range(self.world):
-            for name in sizes:
-                if r == self.rank:
-                    self.ptrs[name][r] = own[name]
-                else:
-                    p = ctypes.c_void_p()
-                    _lib.call("r2d2_peer_open", ctypes.create_string_buffer(gathered[r][name], 64), ctypes.byref(p))
-                    self.ptrs[name][r] = p.value
-                    self._opened.append(p.value)
+        try:
+            for r in range(self.world):
+                for name in sizes:
+                    if r == self.rank:
+                        self.ptrs[name][r] = own[name]
+                    else:
+                        p = ctypes.c_void_p()
+                        _lib.call("r2d2_peer_open", ctypes.create_string_buffer(gathered[r][name], 64), ctypes.byref(p))
+                        self.ptrs[name][r] = p.value
+                        self._opened.append(p.value)
+            ok = True
+        except Exception as e:          # noqa: BLE001
+            ok, why = False, repr(e)
+        if not self._all_ok(ok):
+            raise PeerUnavailable(f"rank {self.rank}: mapping a peer's buffers failed on some rank (no P2P / IPC "
+                                  "between these devices?)" + ("" if ok else f" ({why})"))
         arr = ctypes.c_void_p * self.world
         self.c_ptrs = {name: arr(*self.ptrs[name]) for name in sizes}
         self.grad = torch.as_tensor(_DevBuf(own["grad"], n, "<f4"), device=self.device)
         self.param = torch.as_tensor(_DevBuf(own["param"], n, "<f4"), device=self.device)
         dist.barrier(group=group)
+
+    def _all_ok(self, ok: bool) -> bool:
+        t = torch.tensor([1 if ok else 0], dtype=torch.int32,
+                         device=self.device if dist.get_backend(self.group) == "nccl" else "cpu")
+        dist.all_reduce(t, op=dist.ReduceOp.MIN, group=self.group)
+        return bool(t.item())
 
     def reduce_rmsprop(self, square_avg_shard, grad_avg_shard, lr, alpha, eps, offset=0, n=None, bucket=0):
         """Exchange + optimiser step for the slice [offset, offset+n) of the flat vectors (default:
