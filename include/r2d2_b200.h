@@ -251,9 +251,11 @@ int64_t r2d2_tc_lstm_scratch_bytes(int B, int H);
  * (barrier passed, proxy fence, MMAs issued, accumulator ready, gates staged, stores issued,
  * fence done, arrive done); null switches it off */
 int r2d2_tc_lstm_set_trace(void* trace);
+/* h16_hi / h16_lo (optional, together; bf16 [T - hist_t0, B, H]): the r2d2_split_bf16 image of
+ * h_t for t >= hist_t0, written by the kernel itself for the dueling-head GEMM. */
 int r2d2_tc_lstm_seq_fwd(const float* xprojT, int64_t ldx, int64_t col0, const float* w_hh,
-                         float* hs_ext, float* cs_ext, float* gates, int T, int B, int H,
-                         void* scratch, void* stream);
+                         float* hs_ext, float* cs_ext, float* gates, void* h16_hi, void* h16_lo,
+                         int hist_t0, int T, int B, int H, void* scratch, void* stream);
 /* Persistent BPTT on tensor cores (same contract as r2d2_lstm_seq_bwd, plain bf16 operands):
  * dG_{t+1} pulled in by bulk copies, W_hh^T slice resident, dL/dc in registers, grid-wide counter.
  * dgates_bf16 (optional, [T,B,4H] bf16): a rounded copy of dgates for the gradient GEMMs. */

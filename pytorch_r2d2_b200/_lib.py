@@ -57,7 +57,7 @@ PROTOTYPES = {
     "r2d2_tc_torso_fwd_f32": (_I, [_P, _I] + [_P] * 9 + [_P]),
     "r2d2_tc_lstm_set_trace": (_I, [_P]),
     "r2d2_tc_lstm_scratch_bytes": (_L, [_I, _I]),
-    "r2d2_tc_lstm_seq_fwd": (_I, [_P, _L, _L, _P, _P, _P, _P, _I, _I, _I, _P, _P]),
+    "r2d2_tc_lstm_seq_fwd": (_I, [_P, _L, _L, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _P]),
     "r2d2_tc_lstm_bwd_scratch_bytes": (_L, [_I, _I]),
     "r2d2_tc_lstm_seq_bwd": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P]),
     "r2d2_torso_bwd_dgrad_u8": (_I, [_P, _I, _I, _I, _I] + [_P] * 10 + [_P]),

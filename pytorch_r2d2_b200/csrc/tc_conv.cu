@@ -109,7 +109,6 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
     constexpr int MMA_WARP = NPW;
     constexpr int NCH = 32 / NPW;                            // 16-byte chunks of a row per producer thread
     static_assert(NPW == 8 || NPW == 16, "8 or 16 producer warps");
-    static_assert(NPW == 8 || !(sizeof(T) == 1 && KH == 8), "the u8 first-layer path is written for 8 producer warps");
     extern __shared__ uint8_t smem_raw[];
     __shared__ uint64_t full_bar[CV_STAGES], empty_bar[CV_STAGES], acc_full[2], acc_empty[2];
     __shared__ uint32_t tmem_slot;
@@ -173,7 +172,7 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
             // a tile row (4 input channels x this thread's 4 patch rows x 8 pixels) are issued
             // together, and the NEXT tile's loads are issued before the current tile is converted
             // and stored, so that DRAM latency overlaps the ring traffic of the current tile.
-            auto issue = [&](int tile, uint32_t (&dst)[NKB][4][2]) {
+            auto issue = [&](int tile, uint32_t (&dst)[NKB][NCH][2]) {
                 const long long m = (long long)tile * 128 + row;
                 const bool valid = tile < ntiles && m < Mtot;
                 const T* src = in;
@@ -185,14 +184,14 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
 #pragma unroll
                 for (int kb = 0; kb < NKB; ++kb)
 #pragma unroll
-                    for (int cc = 0; cc < 4; ++cc) {
+                    for (int cc = 0; cc < NCH; ++cc) {
                         const uint32_t* q = reinterpret_cast<const uint32_t*>(
-                            src + kb * (HIN * HIN) + (half * 4 + cc) * HIN);
+                            src + kb * (HIN * HIN) + (half * NCH + cc) * HIN);
                         dst[kb][cc][0] = valid ? __ldg(q) : 0u;
                         dst[kb][cc][1] = valid ? __ldg(q + 1) : 0u;
                     }
             };
-            uint32_t cur[NKB][4][2], nxt[NKB][4][2];
+            uint32_t cur[NKB][NCH][2], nxt[NKB][NCH][2];
             issue(blockIdx.x, cur);
             for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
                 issue(tile + gridDim.x, nxt);
@@ -202,14 +201,14 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
                     mbar_wait(&empty_bar[s], ((it / CV_STAGES) & 1) ^ 1);
                     uint8_t* a_hi = a_s + (size_t)s * STAGE_BYTES;
 #pragma unroll
-                    for (int cc = 0; cc < 4; ++cc) {
+                    for (int cc = 0; cc < NCH; ++cc) {
                         float v[8];
 #pragma unroll
                         for (int e = 0; e < 4; ++e) {
                             v[e] = __uint_as_float(__byte_perm(cur[kb][cc][0], 0x4B000000u, 0x7650u | e)) - 8388608.f;
                             v[4 + e] = __uint_as_float(__byte_perm(cur[kb][cc][1], 0x4B000000u, 0x7650u | e)) - 8388608.f;
                         }
-                        *reinterpret_cast<uint4*>(a_hi + sw128_off(row, half * 4 + cc)) =
+                        *reinterpret_cast<uint4*>(a_hi + sw128_off(row, half * NCH + cc)) =
                             make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
                                        pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
                     }
@@ -219,7 +218,7 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
 #pragma unroll
                 for (int kb = 0; kb < NKB; ++kb)
 #pragma unroll
-                    for (int cc = 0; cc < 4; ++cc) {
+                    for (int cc = 0; cc < NCH; ++cc) {
                         cur[kb][cc][0] = nxt[kb][cc][0];
                         cur[kb][cc][1] = nxt[kb][cc][1];
                     }
@@ -389,13 +388,14 @@ static int launch_tc_conv1_dual(const uint8_t* in, FrameMap fm, const float* wa,
                                 cudaStream_t st) {
     constexpr int NKB = 4;
     const int smem = 2 * 2 * NKB * 32 * 128 + CV_STAGES * 128 * 128 + 1024;
-    auto kern = tc_conv_fwd_kernel<uint8_t, 4, 8, 84, 20, 4, 2>;
+    constexpr int NPW = 16;
+    auto kern = tc_conv_fwd_kernel<uint8_t, 4, 8, 84, 20, 4, 2, NPW>;
     R2D2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     const long long Mtot = (long long)R * 400;
     const int ntiles = (int)((Mtot + 127) / 128);
     int grid = sm_count();
     if (grid > ntiles) grid = ntiles;
-    R2D2_LAUNCH("tc_conv1_fwd_dual", st, kern<<<grid, 416, smem, st>>>(in, fm, wa, ba, outa, R, 1.f / 255.f, wb, bb, outb, skip_b, nullptr, nullptr));
+    R2D2_LAUNCH("tc_conv1_fwd_dual", st, kern<<<grid, NPW * 32 + 160, smem, st>>>(in, fm, wa, ba, outa, R, 1.f / 255.f, wb, bb, outb, skip_b, nullptr, nullptr));
     return R2D2_OK;
 }
 

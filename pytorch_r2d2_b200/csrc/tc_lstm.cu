@@ -61,6 +61,9 @@ struct LstmArgs {
     int* counter;          // [gridDim.y] grid barrier counters, zero on entry
     int T, B, H;
     long long* trace;      // optional [T, 8] globaltimer stamps of CTA (0,0) (diagnostics), or null
+    __nv_bfloat16* hist_hi;   // optional [T - hist_t0, B, H] bf16 (hi, lo) split of h_t for t >= hist_t0:
+    __nv_bfloat16* hist_lo;   //   the operand image the dueling-head GEMM consumes (no split pass)
+    int hist_t0;
 };
 
 __device__ __forceinline__ long long gtimer() {
@@ -360,6 +363,10 @@ tc_lstm_fwd_kernel(const LstmArgs a) {
                 const long long o = (long long)(b0 + pb) * H + u0 + pu;
                 st_f32<UPT>(a.hs_ext + (long long)(t + 1) * BH + o, hv);
                 st_f32<UPT>(a.cs_ext + (long long)(t + 1) * BH + o, cv);
+                if (a.hist_hi && t >= a.hist_t0) {
+                    const long long oh = (long long)(t - a.hist_t0) * BH + o;
+                    st_bf16_hilo<UPT>(a.hist_hi + oh, a.hist_lo + oh, hv);
+                }
                 if (a.gates) {
                     float* gp = a.gates + ((long long)t * B + b0 + pb) * 4 * H + u0 + pu;
                     st_f32<UPT>(gp, gi);
@@ -670,8 +677,11 @@ int64_t r2d2_tc_lstm_scratch_bytes(int B, int H) {
 }
 
 int r2d2_tc_lstm_seq_fwd(const float* xprojT, int64_t ldx, int64_t col0, const float* w_hh,
-                         float* hs_ext, float* cs_ext, float* gates, int T, int B, int H,
-                         void* scratch, void* stream) {
+                         float* hs_ext, float* cs_ext, float* gates, void* h16_hi, void* h16_lo,
+                         int hist_t0, int T, int B, int H, void* scratch, void* stream) {
+    R2D2_REQUIRE((h16_hi == nullptr) == (h16_lo == nullptr) && hist_t0 >= 0 && hist_t0 <= T &&
+                     ((uintptr_t)h16_hi % 8) == 0 && ((uintptr_t)h16_lo % 8) == 0,
+                 "tc_lstm_seq_fwd: h16_hi/h16_lo go together (8-byte aligned), 0 <= hist_t0 <= T");
     R2D2_REQUIRE(xprojT && w_hh && hs_ext && cs_ext && scratch, "tc_lstm_seq_fwd: null pointer");
     R2D2_REQUIRE(T > 0 && B > 0 && H > 0 && H % 64 == 0 && H <= 512,
                  "tc_lstm_seq_fwd: H must be a multiple of 64 and <= 512 (H=%d)", H);
@@ -689,6 +699,9 @@ int r2d2_tc_lstm_seq_fwd(const float* xprojT, int64_t ldx, int64_t col0, const f
     a.counter = reinterpret_cast<int*>(sc + h16);
     a.T = T; a.B = B; a.H = H;
     a.trace = g_lstm_trace;
+    a.hist_hi = static_cast<__nv_bfloat16*>(h16_hi);
+    a.hist_lo = static_cast<__nv_bfloat16*>(h16_lo);
+    a.hist_t0 = hist_t0;
     // batch tile: 32 columns spreads a chain over twice the SMs; fall back to 64 when that many
     // CTAs (two chains may run side by side) would not be co-resident
     const int NKB = H / 64;

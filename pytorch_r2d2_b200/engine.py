@@ -211,10 +211,13 @@ def tc_lstm_scratch_bytes(B, H):
     return int(_lib.load().r2d2_tc_lstm_scratch_bytes(B, H))
 
 
-def tc_lstm_seq_fwd(xprojT, col0, w_hh, hs_ext, cs_ext, gates, T, B, H, scratch):
-    """xprojT: [4H, ldx] f32 (transposed input projection, biases included)."""
+def tc_lstm_seq_fwd(xprojT, col0, w_hh, hs_ext, cs_ext, gates, T, B, H, scratch, h16=None, hist_t0=0):
+    """xprojT: [4H, ldx] f32 (transposed input projection, biases included).  h16 = (hi, lo) bf16
+    [T - hist_t0, B, H] buffers that receive the split image of h_t for t >= hist_t0."""
+    hi, lo = (P(h16[0], "bf16"), P(h16[1], "bf16")) if h16 is not None else (None, None)
     _lib.call("r2d2_tc_lstm_seq_fwd", P(xprojT, "f32"), xprojT.shape[1], col0, P(w_hh, "f32"),
-              P(hs_ext, "f32"), P(cs_ext, "f32"), P(gates, "f32", True), T, B, H, P(scratch), S())
+              P(hs_ext, "f32"), P(cs_ext, "f32"), P(gates, "f32", True), hi, lo, hist_t0, T, B, H,
+              P(scratch), S())
 
 
 def split_bf16(x, hi, lo):

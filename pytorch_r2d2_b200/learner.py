@@ -219,8 +219,11 @@ class Learner:
         ws["a1_on"], ws["a2_on"], ws["feat_on"] = f(S * B, 32, 20, 20), f(S * B, 32, 9, 9), f(S * B, FEAT)
         ws["a1_tg"], ws["a2_tg"], ws["feat_tg"] = f(T * B, 32, 20, 20), f(T * B, 32, 9, 9), f(T * B, FEAT)
         ws["xp_on"], ws["xp_tg"] = f(S * B, 4 * H), f(T * B, 4 * H)
-        ws["hs_on"], ws["cs_on"] = f(T + 1, B, H), f(T + 1, B, H)
-        ws["hs_dq"], ws["cs_dq"] = f(L + 1, B, H), f(L + 1, B, H)
+        # one history for both online passes: the double-Q pass continues from the state after
+        # state[T-1] (learner.py:86,91), so its slot 0 IS slot T of the first pass -- no copy
+        hs_all, cs_all = f(T + 1 + L, B, H), f(T + 1 + L, B, H)
+        ws["hs_on"], ws["cs_on"] = hs_all[:T + 1], cs_all[:T + 1]
+        ws["hs_dq"], ws["cs_dq"] = hs_all[T:], cs_all[T:]
         ws["hs_tg"], ws["cs_tg"] = f(T + 1, B, H), f(T + 1, B, H)
         ws["gates"] = f(T, B, 4 * H)
         ws["hid_on"], ws["hid_tmp"], ws["hid_tg"] = f(M, 2 * H), f(M, 2 * H), f(M, 2 * H)
@@ -349,10 +352,12 @@ class Learner:
         def split(x, pair):
             engine.split_bf16(x, pair[0], pair[1])
 
-        def head(hs, wts, w1_16, hs16, hid, q):
-            """Dueling head on [M,H] hidden states (bf16: compensated tcgen05 hidden layer)."""
+        def head(hs, wts, w1_16, hs16, hid, q, presplit=False):
+            """Dueling head on [M,H] hidden states (bf16: compensated tcgen05 hidden layer; the
+            recurrence kernel has already written the (hi, lo) image when `presplit`)."""
             if bf16:
-                split(hs, hs16)
+                if not presplit:
+                    split(hs, hs16)
                 engine.tc_linear_x3(hs16[0], hs16[1], w1_16[0], w1_16[1], wts.head_b1, None, y32=hid,
                                     relu=True)
                 engine.head_out(hid, wts, q)
@@ -377,12 +382,12 @@ class Learner:
                 engine.tc_linear_x3(ws["w_ih16_t"][0], ws["w_ih16_t"][1], ws["feat16_tg"][0],
                                     ws["feat16_tg"][1], wt.b_ih, wt.b_hh, y32=ws["xpT_tg"], bias_row=True)
                 engine.tc_lstm_seq_fwd(ws["xpT_tg"], 0, wt.w_hh, ws["hs_tg"], ws["cs_tg"], None, T, B, H,
-                                       ws["lstm_scratch_tg"])
+                                       ws["lstm_scratch_tg"], h16=ws["hs16_t"], hist_t0=BI)
             else:
                 engine.linear_fwd(ws["feat_tg"], wt.w_ih, wt.b_ih, wt.b_hh, ws["xp_tg"])
                 engine.lstm_seq_fwd(ws["xp_tg"], wt.w_hh, ws["hs_tg"], ws["cs_tg"], None, T, B, H)
             head(ws["hs_tg"][1 + BI:].reshape(M, H), wt, ws.get("hw1_16_t"), ws.get("hs16_t"),
-                 ws["hid_tg"], ws["qn_tg"])
+                 ws["hid_tg"], ws["qn_tg"], presplit=bf16)
 
         overlap = bf16 and self.overlap_streams
         # both nets read the same frames and the first layer is bound by gathering them: one pass
@@ -428,32 +433,31 @@ class Learner:
             engine.tc_linear_x3(ws["w_ih16"][0], ws["w_ih16"][1], ws["feat16_on"][0], ws["feat16_on"][1],
                                 w.b_ih, w.b_hh, y32=ws["xpT_on"], bias_row=True)
             sc = ws["lstm_scratch"]
-            engine.tc_lstm_seq_fwd(ws["xpT_on"], 0, w.w_hh, ws["hs_on"], ws["cs_on"], ws["gates"], T, B, H, sc)
+            engine.tc_lstm_seq_fwd(ws["xpT_on"], 0, w.w_hh, ws["hs_on"], ws["cs_on"], ws["gates"], T, B, H, sc,
+                                   h16=ws["hs16_l"], hist_t0=BI)
             if overlap:
                 # the learn-window head only needs hs_on: it runs on a third stream beside the
                 # double-Q pass of the recurrence (which occupies 64 of the 148 SMs)
                 ws["ev_aux"][0].record(main)
                 ws["aux_stream"].wait_event(ws["ev_aux"][0])
                 with torch.cuda.stream(ws["aux_stream"]):
-                    head(hs_learn, w, ws["hw1_16"], ws["hs16_l"], ws["hid_on"], ws["q_all"])
+                    head(hs_learn, w, ws["hw1_16"], ws["hs16_l"], ws["hid_on"], ws["q_all"], presplit=True)
                     ws["ev_aux"][1].record(ws["aux_stream"])
-            ws["hs_dq"][0].copy_(ws["hs_on"][T])
-            ws["cs_dq"][0].copy_(ws["cs_on"][T])
-            engine.tc_lstm_seq_fwd(ws["xpT_on"], (BI + n) * B, w.w_hh, ws["hs_dq"], ws["cs_dq"], None, L, B, H, sc)
+            engine.tc_lstm_seq_fwd(ws["xpT_on"], (BI + n) * B, w.w_hh, ws["hs_dq"], ws["cs_dq"], None, L, B, H, sc,
+                                   h16=ws["hs16"], hist_t0=0)
         else:
             engine.linear_fwd(ws["feat_on"], w.w_ih, w.b_ih, w.b_hh, ws["xp_on"])
             engine.lstm_seq_fwd(ws["xp_on"], w.w_hh, ws["hs_on"], ws["cs_on"], ws["gates"], T, B, H)
-            ws["hs_dq"][0].copy_(ws["hs_on"][T])
-            ws["cs_dq"][0].copy_(ws["cs_on"][T])
             engine.lstm_seq_fwd(ws["xp_on"][(BI + n) * B:], w.w_hh, ws["hs_dq"], ws["cs_dq"], None, L, B, H)
 
         # ---- dueling heads on the learn window only
-        head(ws["hs_dq"][1:].reshape(M, H), w, ws.get("hw1_16"), ws.get("hs16"), ws["hid_tmp"], ws["qn_on"])
+        head(ws["hs_dq"][1:].reshape(M, H), w, ws.get("hw1_16"), ws.get("hs16"), ws["hid_tmp"], ws["qn_on"],
+             presplit=bf16)
         if overlap:
             main.wait_event(ws["ev_aux"][1])
             main.wait_event(ws["ev_join"])
         else:
-            head(hs_learn, w, ws.get("hw1_16"), ws.get("hs16"), ws["hid_on"], ws["q_all"])
+            head(hs_learn, w, ws.get("hw1_16"), ws.get("hs16_l"), ws["hid_on"], ws["q_all"], presplit=bf16)
 
         # ---- n-step double-Q target, TD error, loss gradient, per-step priorities
         td = ws["td"]

@@ -162,9 +162,14 @@ def test_tc_lstm_vs_torch(cuda_device, H, B, T):
     hs_ext[0], cs_ext[0] = h0.cuda(), c0.cuda()
     gates_d = torch.empty(T, B, 4 * H, device="cuda")
     scratch = torch.empty(engine.tc_lstm_scratch_bytes(B, H), dtype=torch.uint8, device="cuda")
+    t0 = 1                                                                # split image from step 1 on
+    h16 = torch.zeros(2, T - t0, B, H, dtype=torch.bfloat16, device="cuda")
     for _ in range(2):                                                    # twice: scratch reuse
-        engine.tc_lstm_seq_fwd(xprojT, 3 * B, w_hh.cuda(), hs_ext, cs_ext, gates_d, T, B, H, scratch)
+        engine.tc_lstm_seq_fwd(xprojT, 3 * B, w_hh.cuda(), hs_ext, cs_ext, gates_d, T, B, H, scratch,
+                               h16=(h16[0], h16[1]), hist_t0=t0)
     torch.cuda.synchronize()
+    hi = hs_ext[1 + t0:].bfloat16()
+    assert torch.equal(h16[0], hi) and torch.equal(h16[1], (hs_ext[1 + t0:] - hi.float()).bfloat16())
     assert rel_err(hs_ext[1:], torch.stack(hs)) < 1e-5, rel_err(hs_ext[1:], torch.stack(hs))
     assert rel_err(cs_ext[1:], torch.stack(cs)) < 1e-5
     assert rel_err(gates_d, torch.stack(gs)) < 1e-5
