@@ -226,7 +226,9 @@ tc_lstm_fwd_kernel(const LstmArgs a) {
                 while (ld_acquire(counter) < target)
                     if (++spins > (1u << 28)) __trap();
                 LS_STAMP(0);                                        // barrier passed
-                asm volatile("fence.proxy.async;" ::: "memory");   // generic writes -> TMA reads
+                // generic-proxy global writes of the other CTAs -> async-proxy (bulk copy) reads; the
+                // .global form is enough (and 0.35 us/step cheaper than the all-spaces fence)
+                asm volatile("fence.proxy.async.global;" ::: "memory");
                 LS_STAMP(1);
                 const uint8_t* img = reinterpret_cast<const uint8_t*>(a.h16 + (long long)p * IMG + (long long)blockIdx.y * GRP);
                 for (int kb = 0; kb < NKB; kb += KBG, ++it) {
@@ -496,7 +498,7 @@ tc_lstm_bwd_kernel(const LstmBwdArgs a) {
                 while (ld_acquire(counter) < target)
                     if (++spins > (1u << 28)) __trap();
                 LB_STAMP(0);                                    // barrier passed
-                asm volatile("fence.proxy.async;" ::: "memory");
+                asm volatile("fence.proxy.async.global;" ::: "memory");
                 const int p = (s - 1) & 1;
                 const uint8_t* img = reinterpret_cast<const uint8_t*>(a.dg16 + (long long)p * IMG + (long long)blockIdx.y * GRP);
                 for (int g = 0; g < ngrp; ++g, ++it) {

@@ -88,7 +88,8 @@ fanin(const __grid_constant__ CUtensorMap tm, uint8_t* buf, int* counter, long l
             } else {
                 while (ld_acq(counter) < G * (s + 1)) {}
             }
-            asm volatile("fence.proxy.async;" ::: "memory");
+            if (mode == 13) asm volatile("fence.proxy.async.global;" ::: "memory");
+            else if (mode != 14) asm volatile("fence.proxy.async;" ::: "memory");
             const long long t0 = gtimer();
             if (mode == 8 || mode == 9) {
                 for (int p = 0; p < PIECES; ++p) {
@@ -153,9 +154,10 @@ int main(int argc, char** argv) {
                            "1-D 4 KB multicast x4, rewritten each step", "2-D boxes, same, barrier per piece",
                            "2-D boxes, same, barrier per piece + stage-free try_wait",
                            "1-D 32 KB, rewritten, acquire poll", "1-D 32 KB, rewritten, 4 staggered relaxed polls + fence",
-                           "1-D 32 KB, rewritten, 2 staggered relaxed polls + fence"};
+                           "1-D 32 KB, rewritten, 2 staggered relaxed polls + fence",
+                           "1-D 32 KB, rewritten, acquire poll, fence.proxy.async.global", "1-D 32 KB, rewritten, acquire poll, NO proxy fence (timing only)"};
     for (int G : {64}) {
-        for (int mode = 0; mode < 13; ++mode) {
+        for (int mode = 0; mode < 15; ++mode) {
             CK(cudaMemset(counter, 0, 256));
             cudaLaunchConfig_t cfg = {};
             cfg.gridDim = dim3(G); cfg.blockDim = dim3(128); cfg.dynamicSmemBytes = smem;
