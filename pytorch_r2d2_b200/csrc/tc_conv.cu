@@ -388,7 +388,7 @@ static int launch_tc_conv1_dual(const uint8_t* in, FrameMap fm, const float* wa,
                                 cudaStream_t st) {
     constexpr int NKB = 4;
     const int smem = 2 * 2 * NKB * 32 * 128 + CV_STAGES * 128 * 128 + 1024;
-    constexpr int NPW = 16;
+    constexpr int NPW = 8;     // measured: 16 producer warps are no faster here (0.260 vs 0.245 ms)
     auto kern = tc_conv_fwd_kernel<uint8_t, 4, 8, 84, 20, 4, 2, NPW>;
     R2D2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     const long long Mtot = (long long)R * 400;

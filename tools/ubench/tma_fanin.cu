@@ -69,6 +69,30 @@ fanin(const __grid_constant__ CUtensorMap tm, uint8_t* buf, int* counter, long l
             src = img;
         }
         __syncthreads();
+        if (mode >= 15) {
+            // several acquire pollers in different warps, staggered in time; the first to see the
+            // barrier complete claims the step and issues the loads
+            __shared__ int claimed;
+            __shared__ long long tshared;
+            const int NP = mode == 15 ? 2 : 4;
+            const int w = threadIdx.x >> 5;
+            if ((threadIdx.x & 31) == 0 && w < NP) {
+                if (w == 0) red_rel(counter, 1);
+                else __nanosleep(w * (600 / NP));
+                while (ld_acq(counter) < G * (s + 1)) {}
+                if (atomicExch(&claimed, s + 1) != s + 1) {
+                    asm volatile("fence.proxy.async.global;" ::: "memory");
+                    const long long t0 = gtimer();
+                    mbar_expect_tx(&bar, TILE);
+                    for (int p = 0; p < 4; ++p) bulk_1d(base + p * 32768, src + p * 32768, 32768, &bar);
+                    mbar_wait(&bar, s & 1);
+                    tshared = gtimer() - t0;
+                }
+            }
+            __syncthreads();
+            if (threadIdx.x == 0) tsum += tshared;
+            continue;
+        }
         if (threadIdx.x == 0) {
             red_rel(counter, 1);
             if (mode == 11 || mode == 12) {
@@ -155,9 +179,10 @@ int main(int argc, char** argv) {
                            "2-D boxes, same, barrier per piece + stage-free try_wait",
                            "1-D 32 KB, rewritten, acquire poll", "1-D 32 KB, rewritten, 4 staggered relaxed polls + fence",
                            "1-D 32 KB, rewritten, 2 staggered relaxed polls + fence",
-                           "1-D 32 KB, rewritten, acquire poll, fence.proxy.async.global", "1-D 32 KB, rewritten, acquire poll, NO proxy fence (timing only)"};
+                           "1-D 32 KB, rewritten, acquire poll, fence.proxy.async.global", "1-D 32 KB, rewritten, acquire poll, NO proxy fence (timing only)",
+                           "1-D 32 KB, rewritten, .global fence, 2 staggered acquire pollers", "1-D 32 KB, rewritten, .global fence, 4 staggered acquire pollers"};
     for (int G : {64}) {
-        for (int mode = 0; mode < 15; ++mode) {
+        for (int mode = 0; mode < 17; ++mode) {
             CK(cudaMemset(counter, 0, 256));
             cudaLaunchConfig_t cfg = {};
             cfg.gridDim = dim3(G); cfg.blockDim = dim3(128); cfg.dynamicSmemBytes = smem;
