@@ -420,3 +420,51 @@ def test_batched_actor_inference_vs_oracle(cuda_device, precision, tol):
     prio = act.calc_priority(q.cpu().numpy(), action.cpu().numpy(), rng.randn(N).astype(np.float32),
                              q.cpu().numpy(), tq.cpu().numpy(), rng.rand(N) < 0.2)
     assert prio.shape == (N,) and np.all(prio > 0)
+
+
+def test_hundred_step_drift_vs_oracle(cuda_device):
+    """100 consecutive learner steps (sample -> train -> RMSprop -> priority update)
+    against the oracle doing the same 100 steps on the CPU.  Both sides draw from the same
+    uniforms; the GPU is fed the oracle's indices (one ulp of priority difference must not fork
+    the two trajectories) and its own tree must agree with them on the way."""
+    M, B, BI, LN, NS, H = 64, 4, 2, 3, 2, 256
+    rep, _ = make_oracle_replay(M, H, NS, BI, LN, seed=33)
+    L = _learner(H, M, B, BI, LN, NS, seed=3)
+    L.replay_memory = mirror_to_gpu(rep, B)
+    p = {k: v.cpu().clone() for k, v in L.net.state_dict().items()}
+    pt = {k: v.cpu().clone() for k, v in L.target_net.state_dict().items()}
+    sq = {k: torch.zeros_like(v) for k, v in p.items()}
+    ga = {k: torch.zeros_like(v) for k, v in p.items()}
+    rng = np.random.RandomState(5)
+    agree = 0
+    for step in range(100):
+        u = rng.rand(B)
+        si = rep.sample_indices(u)
+        res = NO.train_step(p, pt, NO.to_torch_batch(rep.gather(si)["batch"]), burn_in=BI, n_step=NS)
+        for k in NO.PARAM_KEYS:
+            NO.rmsprop_centered(p[k], res["grads"][k], sq[k], ga[k])
+        T = BI + LN
+        idx = (si[None, :] + np.arange(BI, T)[:, None]) % M          # index[BI:] time-major
+        rep.update_priority(idx.reshape(-1), np.asarray(res["priority"]).reshape(-1))
+        rep.update_sequence_priority(si, True)
+        own = L.replay_memory.sample_indices(torch.from_numpy(u)).cpu().numpy()
+        agree += int(np.array_equal(own, si))
+        L.train(seq_index=torch.from_numpy(si).cuda(), next_action_override=res["next_action"].cuda())
+    # Centered RMSprop moves every weight by ~lr/0.22 per step whatever the size of its gradient
+    # (v - m^2 = a(1-a) g^2 after one step), so weights whose gradient is at rounding-noise level
+    # legitimately random-walk apart between two fp32 implementations.  What must agree: the bulk
+    # of every tensor, and the function the network computes.
+    sd = L.net.state_dict()
+    stats = {}
+    for k in NO.PARAM_KEYS:
+        d = (sd[k].cpu() - p[k]).abs().reshape(-1) / float(p[k].abs().max())
+        stats[k] = (float(d.median()), float(d.quantile(0.99)) if d.numel() > 1 else float(d.max()), float(d.max()))
+        assert stats[k][0] < 2e-3, (k, stats[k])
+        assert stats[k][2] < 0.1, (k, stats[k])
+    probe = NO.to_torch_batch(rep.gather(rep.sample_indices(np.random.RandomState(9).rand(B)))["batch"])
+    want = NO.train_step(p, pt, probe, burn_in=BI, n_step=NS)
+    mine = NO.train_step({k: v.cpu() for k, v in sd.items()}, pt, probe, burn_in=BI, n_step=NS)
+    qerr = rel_err(mine["q_all"], want["q_all"])
+    assert qerr < 2e-2, (qerr, stats)
+    assert np.allclose(gpu_mem_np(L.replay_memory, "priority"), rep.memory["priority"], rtol=0.2, atol=1e-3), stats
+    assert agree >= 95, agree       # the GPU tree draws the same sequences on (almost) every step
