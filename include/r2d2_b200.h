@@ -234,6 +234,15 @@ int r2d2_tc_torso_fwd_u8(const uint8_t* slab, int B, int S, int s0, int nt, cons
 int r2d2_tc_conv1_fwd_dual_u8(const uint8_t* slab, int B, int S, int nt, const float* w1_a,
                               const float* b1_a, float* a1_a, const float* w1_b, const float* b1_b,
                               float* a1_b, int s0_b, void* stream);
+/* Ring forms: the sampled sequences are read IN PLACE from the replay ring (frame (t,b) = ring row
+ * (seq_index[b] + s0 + t) mod M, seq_index on the device = r2d2_tree_sample's output), so the
+ * frames are never copied into a slab (r2d2_replay_gather with slab = NULL still fills the small
+ * per-sequence fields).  Same results as the slab forms. */
+int r2d2_tc_conv1_fwd_dual_ring(const uint8_t* ring_state, int64_t M, const int64_t* seq_index, int B,
+                                int nt, const float* w1_a, const float* b1_a, float* a1_a,
+                                const float* w1_b, const float* b1_b, float* a1_b, int s0_b, void* stream);
+int r2d2_tc_conv1_wgrad_ring(const uint8_t* ring_state, int64_t M, const int64_t* seq_index, int B, int s0,
+                             int nt, const float* dz, float* dw, float* part, void* stream);
 int r2d2_tc_torso_fwd_tail(const float* a1, int R, const float* w2, const float* b2, const float* w3,
                            const float* b3, float* a2, float* feat, void* feat_hi, void* feat_lo,
                            void* stream);

@@ -52,6 +52,8 @@ PROTOTYPES = {
     "r2d2_torso_bwd_u8": (_I, [_P, _I, _I, _I, _I] + [_P] * 13 + [_P]),
     "r2d2_torso_bwd_f32": (_I, [_P, _I] + [_P] * 13 + [_P]),
     "r2d2_tc_conv1_fwd_dual_u8": (_I, [_P, _I, _I, _I, _P, _P, _P, _P, _P, _P, _I, _P]),
+    "r2d2_tc_conv1_fwd_dual_ring": (_I, [_P, _L, _P, _I, _I, _P, _P, _P, _P, _P, _P, _I, _P]),
+    "r2d2_tc_conv1_wgrad_ring": (_I, [_P, _L, _P, _I, _I, _I, _P, _P, _P, _P]),
     "r2d2_tc_torso_fwd_tail": (_I, [_P, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "r2d2_tc_torso_fwd_u8": (_I, [_P, _I, _I, _I, _I] + [_P] * 9 + [_P]),
     "r2d2_tc_torso_fwd_f32": (_I, [_P, _I] + [_P] * 9 + [_P]),

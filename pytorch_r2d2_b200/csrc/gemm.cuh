@@ -168,9 +168,18 @@ struct DenseLoad {
 struct FrameMap {
     int B, S, s0;
     long long frame_elems;
+    // ring mode (seq != null): frame (t, b) is ring row (seq[b] + s0 + t) mod M -- the sampled
+    // sequences are read in place from the replay ring, no gathered slab
+    const long long* seq = nullptr;
+    long long M = 0;
     __device__ __forceinline__ long long base(int r) const {
         if (B == 0) return (long long)r * frame_elems;
         const int t = r / B, b = r - t * B;
+        if (seq) {
+            long long row = __ldg(seq + b) + s0 + t;
+            row %= M;
+            return row * frame_elems;
+        }
         return ((long long)b * S + s0 + t) * frame_elems;
     }
 };

@@ -640,7 +640,7 @@ int r2d2_replay_gather(const uint8_t* state, const float* hs_cs, const float* ta
                        int burn_in, uint8_t* slab, float* hs, float* cs, float* ths, float* tcs,
                        int64_t* action_out, float* reward_out, float* done_out,
                        int64_t* index_out, int use_tma, void* stream) {
-    R2D2_REQUIRE(state && hs_cs && target_hs_cs && action && reward && done && seq_index && slab &&
+    R2D2_REQUIRE(state && hs_cs && target_hs_cs && action && reward && done && seq_index &&
                      hs && cs && ths && tcs && action_out && reward_out && done_out && index_out,
                  "replay_gather: null pointer");
     R2D2_REQUIRE(B > 0 && T > 0 && n_step >= 0 && burn_in >= 0 && burn_in < T && cell > 0 && M > 0,
@@ -648,7 +648,10 @@ int r2d2_replay_gather(const uint8_t* state, const float* hs_cs, const float* ta
     R2D2_REQUIRE(((uintptr_t)state % 16) == 0 && ((uintptr_t)slab % 16) == 0,
                  "replay_gather: state/slab must be 16-byte aligned");
     const int S = T + n_step;
-    if (use_tma) {
+    if (!slab) {
+        // frames stay in the ring: the consumer reads them in place through seq_index
+        // (r2d2_tc_conv1_fwd_dual_ring / r2d2_tc_conv1_wgrad_ring)
+    } else if (use_tma) {
         const int smem = TMA_STAGES * R2D2_FRAME_BYTES;
         R2D2_CUDA_OK(cudaFuncSetAttribute(gather_rows_tma_kernel,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, smem));

@@ -1060,6 +1060,30 @@ int r2d2_tc_conv1_fwd_dual_u8(const uint8_t* slab, int B, int S, int nt, const f
                                 B * nt, s0_b * B, as_stream(stream));
 }
 
+int r2d2_tc_conv1_fwd_dual_ring(const uint8_t* ring_state, int64_t M, const int64_t* seq_index, int B,
+                                int nt, const float* w1_a, const float* b1_a, float* a1_a,
+                                const float* w1_b, const float* b1_b, float* a1_b, int s0_b, void* stream) {
+    R2D2_REQUIRE(ring_state && seq_index && w1_a && b1_a && a1_a && w1_b && b1_b && a1_b,
+                 "tc_conv1_fwd_dual_ring: null pointer");
+    R2D2_REQUIRE(B > 0 && nt > 0 && M > 0 && s0_b >= 0 && s0_b < nt, "tc_conv1_fwd_dual_ring: bad frame window");
+    R2D2_REQUIRE((long long)B * nt * 400 < (1ll << 31), "tc_conv1_fwd_dual_ring: too many frames");
+    FrameMap fm{B, nt, 0, R2D2_FRAME_BYTES, reinterpret_cast<const long long*>(seq_index), (long long)M};
+    return launch_tc_conv1_dual(ring_state, fm, w1_a, b1_a, a1_a, w1_b, b1_b, a1_b, B * nt, s0_b * B,
+                                as_stream(stream));
+}
+
+int r2d2_tc_conv1_wgrad_ring(const uint8_t* ring_state, int64_t M, const int64_t* seq_index, int B, int s0,
+                             int nt, const float* dz, float* dw, float* part, void* stream) {
+    R2D2_REQUIRE(ring_state && seq_index && dz && dw && part && nt > 0 && B > 0 && M > 0 && s0 >= 0,
+                 "tc_conv1_wgrad_ring: bad args");
+    int grid = 0;
+    FrameMap fm{B, s0 + nt, s0, R2D2_FRAME_BYTES, reinterpret_cast<const long long*>(seq_index), (long long)M};
+    int rc = launch_tc_wgrad<uint8_t, 4, 8, 84, 20, 4, 4>("tc_conv1_wgrad", ring_state, fm, dz, part, B * nt,
+                                                          1.f / 255.f, &grid, as_stream(stream));
+    if (rc) return rc;
+    return r2d2_reduce_partials(part, dw, 32 * 256, grid, stream);
+}
+
 int r2d2_tc_torso_fwd_tail(const float* a1, int R, const float* w2, const float* b2, const float* w3,
                            const float* b3, float* a2, float* feat, void* feat_hi, void* feat_lo,
                            void* stream) {

@@ -340,7 +340,10 @@ class Learner:
         rm.batch_size, rm.n_step = B, n
         rm.burn_in_length, rm.learning_length, rm.sequence_length = BI, L, T
         ws = self._workspace()
-        batch = rm.sample_slab(u=u, seq_index=seq_index)
+        bf16 = self.precision == "bf16"
+        # tensor-core path: the first conv layer (forward and weight gradient) reads the sampled
+        # frames in place from the ring, so the 154 MB slab copy never happens
+        batch = rm.sample_slab(u=u, seq_index=seq_index, frames=not bf16)
         slab = batch["slab"]
         w, wt = self.net._weights(), self.target_net._weights()
         g = Weights(self.optim.grad, self.net.layout)
@@ -394,7 +397,7 @@ class Learner:
         # builds each receptive field once and multiplies it against both nets' filters
         fused_conv1 = bf16
         if fused_conv1:
-            engine.conv1_fwd_dual_u8(slab, T + n, w, ws["a1_on"], wt, ws["a1_tg"], n)
+            engine.conv1_fwd_dual_ring(batch["ring"], batch["seq_index"], T + n, w, ws["a1_on"], wt, ws["a1_tg"], n)
         if overlap:
             main, side = torch.cuda.current_stream(), ws["side_stream"]
             ws["ev_fork"].record(main)
@@ -557,8 +560,7 @@ class Learner:
             beside(conv2_grads, ws["aux2_stream"])
             _lib.call("r2d2_tc_conv_dgrad2", P(dz2, "f32"), P(w.w2), P(a1_l, "f32"), P(dz1, "f32"), M, st())
             _lib.call("r2d2_chansum", P(dz1, "f32"), P(g.b1), M, 400, P(ws["cpart"][0], "f32"), st())
-            _lib.call("r2d2_tc_conv_wgrad_layer", 1, P(slab, "u8"), B, T + n, BI, L, P(dz1, "f32"), P(g.w1),
-                      P(ws["wpart"][0], "f32"), st())
+            engine.conv1_wgrad_ring(batch["ring"], batch["seq_index"], BI, L, dz1, g.w1, ws["wpart"][0])
             if overlap_bwd:
                 for st_ in (side, aux, ws["aux2_stream"]) + ((ws["xchg_stream"],) if self.optim.peer is not None else ()):
                     e = next(ev)

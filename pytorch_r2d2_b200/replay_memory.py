@@ -342,10 +342,11 @@ class ReplayMemory:
                   _lib.stream_ptr())
         return out
 
-    def sample_slab(self, u=None, seq_index=None):
+    def sample_slab(self, u=None, seq_index=None, frames=True):
         """Device-resident fast path: draw, then gather one contiguous (T+n)-frame u8 slab per
         sequence plus hidden/action/reward/done/index.  Returns the workspace dict (tensors are
-        reused by the next call)."""
+        reused by the next call).  frames=False leaves the frames in the ring (``ws["ring"]``,
+        read in place through ``ws["seq_index"]`` by the ring forms of the first conv layer)."""
         B, T, n, H = self.batch_size, self.sequence_length, self.n_step, self.cell_size
         ws = self._workspace(B, T, n, H)
         self._wait_ingest()
@@ -365,11 +366,12 @@ class ReplayMemory:
                   _lib.ptr(self._raw("action"), "i8"), _lib.ptr(self._raw("reward"), "f32"),
                   _lib.ptr(self._raw("done"), "f32"), self.memory_size, H,
                   _lib.ptr(ws["seq_index"], "i64"), B, T, n, self.burn_in_length,
-                  _lib.ptr(ws["slab"], "u8"), _lib.ptr(ws["hs"], "f32"), _lib.ptr(ws["cs"], "f32"),
+                  _lib.ptr(ws["slab"], "u8") if frames else None, _lib.ptr(ws["hs"], "f32"), _lib.ptr(ws["cs"], "f32"),
                   _lib.ptr(ws["target_hs"], "f32"), _lib.ptr(ws["target_cs"], "f32"),
                   _lib.ptr(ws["action"], "i64"), _lib.ptr(ws["reward"], "f32"),
                   _lib.ptr(ws["done"], "f32"), _lib.ptr(ws["index"], "i64"),
                   int(self.use_tma_gather), _lib.stream_ptr())
+        ws["ring"] = self._raw("state")
         return ws
 
     def sample(self, device=None):

@@ -236,3 +236,35 @@ def test_tc_conv_backward_vs_fp32(cuda_device):
         assert err < 1e-2, (name, err)
     for name in ("b1", "b2", "b3"):   # data gradients now also run in bf16 on tensor cores
         assert rel_err(getattr(tc, name), getattr(ref, name)) < 1e-2, name
+
+
+def test_conv1_ring_forms_match_slab_forms(cuda_device):
+    """First conv layer reading the sampled frames in place from the replay ring (incl. sequences
+    that wrap around the end of the ring) == the same kernels on the gathered slab, bit for bit."""
+    import numpy as np
+    from pytorch_r2d2_b200 import QNet, _lib, engine
+    torch.manual_seed(6)
+    na, nb = QNet("cuda:0", 256), QNet("cuda:0", 256)
+    wa, wb = na._weights(), nb._weights()
+    rng = np.random.RandomState(8)
+    Mring, B, S, s0 = 50, 5, 9, 2
+    ring = torch.from_numpy(rng.randint(0, 256, (Mring, 4, 84, 84)).astype(np.uint8)).cuda()
+    seq = torch.tensor([0, 13, 44, 49, 13], dtype=torch.int64, device="cuda")     # two wrap, one duplicate
+    rows = (seq[:, None] + torch.arange(S, device="cuda")[None, :]) % Mring
+    slab = ring[rows].contiguous()                                                # [B,S,4,84,84]
+    a1, _, _ = engine.alloc_torso(B * S, "cuda")
+    b1, _, _ = engine.alloc_torso(B * (S - s0), "cuda")
+    c1, _, _ = engine.alloc_torso(B * S, "cuda")
+    d1, _, _ = engine.alloc_torso(B * (S - s0), "cuda")
+    engine.conv1_fwd_dual_u8(slab, S, wa, a1, wb, b1, s0)
+    engine.conv1_fwd_dual_ring(ring, seq, S, wa, c1, wb, d1, s0)
+    assert torch.equal(a1, c1) and torch.equal(b1, d1)
+    # weight gradient of the first layer over the window [s0, S)
+    nt = S - s0
+    dz = torch.randn(B * nt, 32, 20, 20, device="cuda")
+    part = torch.empty(_lib.load().r2d2_sm_count() * 32 * 256, device="cuda")
+    g_slab, g_ring = torch.empty(32, 4, 8, 8, device="cuda"), torch.empty(32, 4, 8, 8, device="cuda")
+    _lib.call("r2d2_tc_conv_wgrad_layer", 1, _lib.ptr(slab, "u8"), B, S, s0, nt, _lib.ptr(dz, "f32"),
+              _lib.ptr(g_slab, "f32"), _lib.ptr(part, "f32"), _lib.stream_ptr())
+    engine.conv1_wgrad_ring(ring, seq, s0, nt, dz, g_ring, part)
+    assert torch.equal(g_slab, g_ring)
