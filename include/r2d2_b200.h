@@ -242,7 +242,7 @@ int r2d2_tc_conv1_fwd_dual_ring(const uint8_t* ring_state, int64_t M, const int6
                                 int nt, const float* w1_a, const float* b1_a, float* a1_a,
                                 const float* w1_b, const float* b1_b, float* a1_b, int s0_b, void* stream);
 int r2d2_tc_conv1_wgrad_ring(const uint8_t* ring_state, int64_t M, const int64_t* seq_index, int B, int s0,
-                             int nt, const float* dz, float* dw, float* part, void* stream);
+                             int nt, const float* dz, float* dw, float* db, float* part, void* stream);
 int r2d2_tc_torso_fwd_tail(const float* a1, int R, const float* w2, const float* b2, const float* w3,
                            const float* b3, float* a2, float* feat, void* feat_hi, void* feat_lo,
                            void* stream);
@@ -285,10 +285,12 @@ int r2d2_tc_torso_wgrad_u8(const uint8_t* slab, int B, int S, int s0, int nt, co
                            float* dw1, float* dw2, float* dw3, void* scratch, void* stream);
 int r2d2_reduce_partials(const float* part, float* out, int64_t n, int splits, void* stream);
 /* one conv layer's weight gradient (layer 1: `in` = u8 slab, B/S/s0/nt as r2d2_torso_fwd_u8;
- * layers 2/3: `in` = that layer's fp32 NCHW input activations, S/s0 ignored), private partial
- * buffer of r2d2_sm_count()*32*K floats (K = 256/512/288) so layers can run on separate streams */
+ * layers 2/3: `in` = that layer's fp32 NCHW input activations, S/s0 ignored) and, when db is given,
+ * its bias gradient db[co] = sum over frames and pixels of dz (accumulated by the producer threads
+ * while they build the dZ operand).  Private partial buffer of r2d2_sm_count()*(32*K + 32) floats
+ * (K = 256/512/288) so layers can run on separate streams. */
 int r2d2_tc_conv_wgrad_layer(int layer, const void* in, int B, int S, int s0, int nt,
-                             const float* dz, float* dw, float* part, void* stream);
+                             const float* dz, float* dw, float* db, float* part, void* stream);
 /* conv data gradients on tcgen05 (plain bf16, ReLU' of the layer input fused): dz3 [R,32,7,7]
  * -> dz2 [R,32,9,9] (a2 = that layer's activations), dz2 -> dz1 [R,32,20,20]; the stride-2 layer
  * runs as four output-parity classes.  Plus the two small pieces of the conv backward that stay

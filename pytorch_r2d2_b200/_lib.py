@@ -53,7 +53,7 @@ PROTOTYPES = {
     "r2d2_torso_bwd_f32": (_I, [_P, _I] + [_P] * 13 + [_P]),
     "r2d2_tc_conv1_fwd_dual_u8": (_I, [_P, _I, _I, _I, _P, _P, _P, _P, _P, _P, _I, _P]),
     "r2d2_tc_conv1_fwd_dual_ring": (_I, [_P, _L, _P, _I, _I, _P, _P, _P, _P, _P, _P, _I, _P]),
-    "r2d2_tc_conv1_wgrad_ring": (_I, [_P, _L, _P, _I, _I, _I, _P, _P, _P, _P]),
+    "r2d2_tc_conv1_wgrad_ring": (_I, [_P, _L, _P, _I, _I, _I, _P, _P, _P, _P, _P]),
     "r2d2_tc_torso_fwd_tail": (_I, [_P, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "r2d2_tc_torso_fwd_u8": (_I, [_P, _I, _I, _I, _I] + [_P] * 9 + [_P]),
     "r2d2_tc_torso_fwd_f32": (_I, [_P, _I] + [_P] * 9 + [_P]),
@@ -69,7 +69,7 @@ PROTOTYPES = {
     "r2d2_tc_conv_dgrad2": (_I, [_P, _P, _P, _P, _I, _P]),
     "r2d2_relu_mask": (_I, [_P, _P, _L, _P]),
     "r2d2_chansum": (_I, [_P, _P, _I, _I, _P, _P]),
-    "r2d2_tc_conv_wgrad_layer": (_I, [_I, _P, _I, _I, _I, _I, _P, _P, _P, _P]),
+    "r2d2_tc_conv_wgrad_layer": (_I, [_I, _P, _I, _I, _I, _I, _P, _P, _P, _P, _P]),
     "r2d2_tc_linear": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "r2d2_tc_linear_masked": (_I, [_P, _P, _P, _P, _I, _I, _I, _P]),
     "r2d2_peer_alloc": (_I, [_L, _P, _P]),

@@ -440,7 +440,8 @@ __device__ __forceinline__ void wgrad_gather(const T* __restrict__ src, const bo
 template <class T, int CIN, int KH, int HIN, int HOUT, int STRIDE, int STAGES>
 __global__ void __launch_bounds__(416, 1)
 tc_conv_wgrad_kernel(const T* __restrict__ in, const FrameMap fm, const float* __restrict__ dz,
-                     float* __restrict__ part, const int R, const float in_scale) {
+                     float* __restrict__ part, const int R, const float in_scale,
+                     float* __restrict__ bias_part) {
     constexpr int K = CIN * KH * KH, NKB = (K + 63) / 64;
     constexpr int MT = (NKB + 1) / 2, KPM = MT * 128;           // M tiles of 128 patch elements
     constexpr int P = HOUT * HOUT, COUT = 32;
@@ -485,6 +486,9 @@ tc_conv_wgrad_kernel(const T* __restrict__ in, const FrameMap fm, const float* _
         const int prow = tid & 63, sub = tid >> 6;
         const int bco = tid >> 3, bch = tid & 7;
         uint32_t it = 0;
+        // the producers see every dZ value of their channel anyway: the bias gradient (sum over
+        // frames and pixels, in fp32 before the bf16 rounding) falls out of the operand build
+        float bsum = 0.f;
         if constexpr (sizeof(T) == 1 && KH == 8 && P % 8 == 0) {
             // first layer on the u8 slab: the gather is memory-latency bound, so the loads of block
             // blk+1 (16 words of patch + 8 gradient values per thread) are issued before block blk
@@ -544,6 +548,8 @@ tc_conv_wgrad_kernel(const T* __restrict__ in, const FrameMap fm, const float* _
                 *reinterpret_cast<uint4*>(a_stage + A_STAGE + sw128_off(bco, bch)) =
                     make_uint4(pack_bf16x2(gcur[0].x, gcur[0].y), pack_bf16x2(gcur[0].z, gcur[0].w),
                                pack_bf16x2(gcur[1].x, gcur[1].y), pack_bf16x2(gcur[1].z, gcur[1].w));
+                bsum += ((gcur[0].x + gcur[0].y) + (gcur[0].z + gcur[0].w)) +
+                        ((gcur[1].x + gcur[1].y) + (gcur[1].z + gcur[1].w));
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 mbar_arrive(&full_bar[s]);
 #pragma unroll
@@ -592,10 +598,17 @@ tc_conv_wgrad_kernel(const T* __restrict__ in, const FrameMap fm, const float* _
                 *reinterpret_cast<uint4*>(a_stage + A_STAGE + sw128_off(bco, bch)) =
                     make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
                                pack_bf16x2(v[6], v[7]));
+                bsum += ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             mbar_arrive(&full_bar[s]);
         }
+        }
+        if (bias_part) {   // the 8 chunk-threads of a channel are neighbouring lanes
+            bsum += __shfl_xor_sync(FULL, bsum, 1);
+            bsum += __shfl_xor_sync(FULL, bsum, 2);
+            bsum += __shfl_xor_sync(FULL, bsum, 4);
+            if (bch == 0) bias_part[blockIdx.x * COUT + bco] = bsum;
         }
     } else if (warp == MMA_WARP) {
         if (lane == 0) {
@@ -651,7 +664,8 @@ tc_conv_wgrad_kernel(const T* __restrict__ in, const FrameMap fm, const float* _
 
 template <class T, int CIN, int KH, int HIN, int HOUT, int STRIDE, int STAGES>
 static int launch_tc_wgrad(const char* name, const T* in, FrameMap fm, const float* dz, float* part,
-                           int R, float in_scale, int* grid_out, cudaStream_t st) {
+                           int R, float in_scale, int* grid_out, cudaStream_t st,
+                           float* bias_part = nullptr) {
     constexpr int K = CIN * KH * KH, NKB = (K + 63) / 64, MT = (NKB + 1) / 2;
     const int smem = STAGES * (2 * MT * 8192 + 32 * 128) + 1024;
     auto kern = tc_conv_wgrad_kernel<T, CIN, KH, HIN, HOUT, STRIDE, STAGES>;
@@ -661,7 +675,29 @@ static int launch_tc_wgrad(const char* name, const T* in, FrameMap fm, const flo
     int grid = sm_count();
     if (grid > nblk) grid = nblk;
     *grid_out = grid;
-    R2D2_LAUNCH(name, st, kern<<<grid, 416, smem, st>>>(in, fm, dz, part, R, in_scale));
+    R2D2_LAUNCH(name, st, kern<<<grid, 416, smem, st>>>(in, fm, dz, part, R, in_scale, bias_part));
+    return R2D2_OK;
+}
+
+// dw[i] = sum_z part[z*nw + i]  and  db[c] = sum_z bias_part[z*32 + c]  in one launch, fixed order
+__global__ void reduce_wgrad_partials_kernel(const float* __restrict__ part, float* __restrict__ dw, int nw,
+                                             const float* __restrict__ bias_part, float* __restrict__ db,
+                                             int splits) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < nw) {
+        float s = 0.f;
+        for (int z = 0; z < splits; ++z) s += part[(long long)z * nw + i];
+        dw[i] = s;
+    } else if (i < nw + 32) {
+        float s = 0.f;
+        for (int z = 0; z < splits; ++z) s += bias_part[z * 32 + (i - nw)];
+        db[i - nw] = s;
+    }
+}
+static int reduce_wgrad(const float* part, float* dw, int nw, float* db, int grid, cudaStream_t st) {
+    // bias partials live behind the weight partials of all CTAs
+    R2D2_LAUNCH("reduce_partials_kernel", st, reduce_wgrad_partials_kernel<<<(nw + 32 + 255) / 256, 256, 0, st>>>(
+        part, dw, nw, part + (long long)grid * nw, db, grid));
     return R2D2_OK;
 }
 
@@ -1072,15 +1108,24 @@ int r2d2_tc_conv1_fwd_dual_ring(const uint8_t* ring_state, int64_t M, const int6
                                 as_stream(stream));
 }
 
+// grid the weight-gradient kernels run with (one CTA per SM, at most one per 64-pixel block)
+static int wgrad_grid(int R, int P) {
+    const long long nblk = ((long long)R * P + 63) / 64;
+    const int g = sm_count();
+    return nblk < g ? (int)nblk : g;
+}
+
 int r2d2_tc_conv1_wgrad_ring(const uint8_t* ring_state, int64_t M, const int64_t* seq_index, int B, int s0,
-                             int nt, const float* dz, float* dw, float* part, void* stream) {
+                             int nt, const float* dz, float* dw, float* db, float* part, void* stream) {
     R2D2_REQUIRE(ring_state && seq_index && dz && dw && part && nt > 0 && B > 0 && M > 0 && s0 >= 0,
                  "tc_conv1_wgrad_ring: bad args");
-    int grid = 0;
+    int grid = wgrad_grid(B * nt, 400);
     FrameMap fm{B, s0 + nt, s0, R2D2_FRAME_BYTES, reinterpret_cast<const long long*>(seq_index), (long long)M};
     int rc = launch_tc_wgrad<uint8_t, 4, 8, 84, 20, 4, 4>("tc_conv1_wgrad", ring_state, fm, dz, part, B * nt,
-                                                          1.f / 255.f, &grid, as_stream(stream));
+                                                          1.f / 255.f, &grid, as_stream(stream),
+                                                          db ? part + (long long)grid * 32 * 256 : nullptr);
     if (rc) return rc;
+    if (db) return reduce_wgrad(part, dw, 32 * 256, db, grid, as_stream(stream));
     return r2d2_reduce_partials(part, dw, 32 * 256, grid, stream);
 }
 
@@ -1152,29 +1197,34 @@ int r2d2_tc_torso_wgrad_u8(const uint8_t* slab, int B, int S, int s0, int nt, co
 // one layer at a time (layer = 1, 2, 3), with its own partial buffer, so that the three weight
 // gradients can run on different streams: part needs sm_count * 32 * K floats (K = 256/512/288)
 int r2d2_tc_conv_wgrad_layer(int layer, const void* in, int B, int S, int s0, int nt,
-                             const float* dz, float* dw, float* part, void* stream) {
+                             const float* dz, float* dw, float* db, float* part, void* stream) {
     R2D2_REQUIRE(in && dz && dw && part && nt > 0 && B > 0, "tc_conv_wgrad_layer: bad args");
     cudaStream_t st = as_stream(stream);
     const int R = B * nt;
     int grid = 0, rc = 0, K = 0;
+    const int pix = layer == 1 ? 400 : layer == 2 ? 81 : 49, kk = layer == 1 ? 256 : layer == 2 ? 512 : 288;
+    float* bias_part = db ? part + (long long)wgrad_grid(R, pix) * 32 * kk : nullptr;
     if (layer == 1) {
         R2D2_REQUIRE(s0 >= 0 && s0 + nt <= S, "tc_conv_wgrad_layer: bad frame window");
         K = 256;
         rc = launch_tc_wgrad<uint8_t, 4, 8, 84, 20, 4, 4>("tc_conv1_wgrad", static_cast<const uint8_t*>(in),
                                                           FrameMap{B, S, s0, R2D2_FRAME_BYTES}, dz, part, R,
-                                                          1.f / 255.f, &grid, st);
+                                                          1.f / 255.f, &grid, st, bias_part);
     } else if (layer == 2) {
         K = 512;
         rc = launch_tc_wgrad<float, 32, 4, 20, 9, 2, 3>("tc_conv2_wgrad", static_cast<const float*>(in),
-                                                        FrameMap{0, 0, 0, 12800}, dz, part, R, 1.f, &grid, st);
+                                                        FrameMap{0, 0, 0, 12800}, dz, part, R, 1.f, &grid, st,
+                                                        bias_part);
     } else if (layer == 3) {
         K = 288;
         rc = launch_tc_wgrad<float, 32, 3, 9, 7, 1, 3>("tc_conv3_wgrad", static_cast<const float*>(in),
-                                                       FrameMap{0, 0, 0, 2592}, dz, part, R, 1.f, &grid, st);
+                                                       FrameMap{0, 0, 0, 2592}, dz, part, R, 1.f, &grid, st,
+                                                       bias_part);
     } else {
         return set_err(R2D2_EINVAL, "tc_conv_wgrad_layer: layer must be 1, 2 or 3");
     }
     if (rc) return rc;
+    if (db) return reduce_wgrad(part, dw, 32 * K, db, grid, st);
     return r2d2_reduce_partials(part, dw, 32 * K, grid, stream);
 }
 

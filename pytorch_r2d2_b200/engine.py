@@ -56,9 +56,11 @@ def conv1_fwd_dual_ring(ring, seq_index, nt, wa: Weights, a1_a, wb: Weights, a1_
               P(wa.w1), P(wa.b1), P(a1_a, "f32"), P(wb.w1), P(wb.b1), P(a1_b, "f32"), s0_b, S())
 
 
-def conv1_wgrad_ring(ring, seq_index, s0, nt, dz1, dw1, part):
+def conv1_wgrad_ring(ring, seq_index, s0, nt, dz1, dw1, part, db1=None):
+    """First-layer weight gradient (and, with db1, bias gradient) over frames s0..s0+nt of the
+    sampled sequences read in place from the ring; part: sm_count*(32*256+32) floats."""
     _lib.call("r2d2_tc_conv1_wgrad_ring", P(ring, "u8"), ring.shape[0], P(seq_index, "i64"), seq_index.numel(), s0, nt,
-              P(dz1, "f32"), P(dw1), P(part, "f32"), S())
+              P(dz1, "f32"), P(dw1), P(db1, None, True), P(part, "f32"), S())
 
 
 def torso_fwd_tail(a1, w: Weights, a2, feat, feat16=None):

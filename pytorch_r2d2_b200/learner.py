@@ -253,7 +253,7 @@ class Learner:
             ws["lstm_scratch_tg"] = torch.empty_like(ws["lstm_scratch"])
             ws["lstm_bwd_scratch"] = torch.empty(engine.tc_lstm_bwd_scratch_bytes(B, H), dtype=torch.uint8, device=dev)
             nsm = int(_lib.load().r2d2_sm_count())
-            ws["wpart"] = [f(nsm * 32 * 256), f(nsm * 32 * 512), f(nsm * 32 * 288)]
+            ws["wpart"] = [f(nsm * (32 * 256 + 32)), f(nsm * (32 * 512 + 32)), f(nsm * (32 * 288 + 32))]
             ws["cpart"] = [f(296 * 32), f(296 * 32), f(296 * 32)]   # R2D2_CHANSUM_PART_FLOATS
             ws["side_stream"] = torch.cuda.Stream(device=dev)
             ws["crit_stream"] = torch.cuda.Stream(device=dev, priority=-1)
@@ -545,22 +545,20 @@ class Learner:
             _lib.call("r2d2_relu_mask", P(dz3, "f32"), P(feat_l, "f32"), dz3.numel(), st())
 
             def conv3_grads():
-                _lib.call("r2d2_chansum", P(dz3, "f32"), P(g.b3), M, 49, P(ws["cpart"][2], "f32"), st())
+                # weight AND bias gradient (the bias sums fall out of the operand build)
                 _lib.call("r2d2_tc_conv_wgrad_layer", 3, P(a2_l, "f32"), B, 0, 0, L, P(dz3, "f32"), P(g.w3),
-                          P(ws["wpart"][2], "f32"), st())
+                          P(g.b3), P(ws["wpart"][2], "f32"), st())
 
             beside(conv3_grads)
             _lib.call("r2d2_tc_conv_dgrad3", P(dz3, "f32"), P(w.w3), P(a2_l, "f32"), P(dz2, "f32"), M, st())
 
             def conv2_grads():
-                _lib.call("r2d2_chansum", P(dz2, "f32"), P(g.b2), M, 81, P(ws["cpart"][1], "f32"), st())
                 _lib.call("r2d2_tc_conv_wgrad_layer", 2, P(a1_l, "f32"), B, 0, 0, L, P(dz2, "f32"), P(g.w2),
-                          P(ws["wpart"][1], "f32"), st())
+                          P(g.b2), P(ws["wpart"][1], "f32"), st())
 
             beside(conv2_grads, ws["aux2_stream"])
             _lib.call("r2d2_tc_conv_dgrad2", P(dz2, "f32"), P(w.w2), P(a1_l, "f32"), P(dz1, "f32"), M, st())
-            _lib.call("r2d2_chansum", P(dz1, "f32"), P(g.b1), M, 400, P(ws["cpart"][0], "f32"), st())
-            engine.conv1_wgrad_ring(batch["ring"], batch["seq_index"], BI, L, dz1, g.w1, ws["wpart"][0])
+            engine.conv1_wgrad_ring(batch["ring"], batch["seq_index"], BI, L, dz1, g.w1, ws["wpart"][0], db1=g.b1)
             if overlap_bwd:
                 for st_ in (side, aux, ws["aux2_stream"]) + ((ws["xchg_stream"],) if self.optim.peer is not None else ()):
                     e = next(ev)

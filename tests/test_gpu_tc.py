@@ -262,9 +262,13 @@ def test_conv1_ring_forms_match_slab_forms(cuda_device):
     # weight gradient of the first layer over the window [s0, S)
     nt = S - s0
     dz = torch.randn(B * nt, 32, 20, 20, device="cuda")
-    part = torch.empty(_lib.load().r2d2_sm_count() * 32 * 256, device="cuda")
+    part = torch.empty(_lib.load().r2d2_sm_count() * (32 * 256 + 32), device="cuda")
     g_slab, g_ring = torch.empty(32, 4, 8, 8, device="cuda"), torch.empty(32, 4, 8, 8, device="cuda")
+    b_slab, b_ring = torch.empty(32, device="cuda"), torch.empty(32, device="cuda")
     _lib.call("r2d2_tc_conv_wgrad_layer", 1, _lib.ptr(slab, "u8"), B, S, s0, nt, _lib.ptr(dz, "f32"),
-              _lib.ptr(g_slab, "f32"), _lib.ptr(part, "f32"), _lib.stream_ptr())
-    engine.conv1_wgrad_ring(ring, seq, s0, nt, dz, g_ring, part)
-    assert torch.equal(g_slab, g_ring)
+              _lib.ptr(g_slab, "f32"), _lib.ptr(b_slab, "f32"), _lib.ptr(part, "f32"), _lib.stream_ptr())
+    engine.conv1_wgrad_ring(ring, seq, s0, nt, dz, g_ring, part, db1=b_ring)
+    assert torch.equal(g_slab, g_ring) and torch.equal(b_slab, b_ring)
+    # the fused bias gradient == the per-channel sum of dz
+    want = dz.double().sum(dim=(0, 2, 3))
+    assert rel_err(b_ring, want) < 1e-5
