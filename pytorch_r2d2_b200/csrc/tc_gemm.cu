@@ -16,7 +16,9 @@
 
 namespace r2d2 {
 
-constexpr int TC_BM = 128, TC_BK = 64, TC_STAGES = 6;
+// 3 stages (96 KB): a plain-GEMM CTA then fits on an SM beside a persistent conv-gradient CTA
+// (87-99 KB), so the weight-gradient GEMMs of the backward pass fill in instead of queueing
+constexpr int TC_BM = 128, TC_BK = 64, TC_STAGES = 3;
 
 struct TcEpilogue {
     float* c32;             // may be null

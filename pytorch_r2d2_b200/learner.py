@@ -259,7 +259,7 @@ class Learner:
             ws["crit_stream"] = torch.cuda.Stream(device=dev, priority=-1)
             ws["aux2_stream"] = torch.cuda.Stream(device=dev)
             ws["xchg_stream"] = torch.cuda.Stream(device=dev, priority=-1)   # multi-GPU exchange: peers wait on it
-            ws["aux_stream"] = torch.cuda.Stream(device=dev)
+            ws["aux_stream"] = torch.cuda.Stream(device=dev, priority=-1)   # LSTM weight gradients: short CTAs, gate the exchange
             ws["ev_aux"] = [torch.cuda.Event() for _ in range(3)]
             ws["events"] = [torch.cuda.Event() for _ in range(16)]
             ws["ev_fork"], ws["ev_join"] = torch.cuda.Event(), torch.cuda.Event()
