@@ -185,6 +185,8 @@ int r2d2_linear_wgrad_static(const float* dy, const float* x, float* dw, float* 
                              int K, void* stream);
 /* db[N] = column sums of dy[M,N] (bias gradients when the weight gradient runs on tensor cores) */
 int r2d2_colsum(const float* dy, float* db, int M, int N, void* stream);
+/* same, the sums also written to db_copy (LSTMCell's bias_ih and bias_hh receive one gradient) */
+int r2d2_colsum2(const float* dy, float* db, float* db_copy, int M, int N, void* stream);
 /* BPTT over the learn window: dhs [T,B,H] is dL/dh_t from the head; gates/cs_ext from
  * r2d2_lstm_seq_fwd.  Writes dgates [T,B,4H] (pre-activation grads).  dc_work [B,H] carries
  * dL/dc between steps (caller-owned, contents undefined on entry). */

@@ -41,6 +41,7 @@ PROTOTYPES = {
     "r2d2_head_fwd": (_I, [_P] * 7 + [_I, _I, _P]),
     "r2d2_head_out": (_I, [_P, _P, _P, _P, _I, _I, _P]),
     "r2d2_colsum": (_I, [_P, _P, _I, _I, _P]),
+    "r2d2_colsum2": (_I, [_P, _P, _P, _I, _I, _P]),
     "r2d2_td_target": (_I, [_P] * 6 + [_I, _F, _I, _F, _F, _F] + [_P] * 7 + [_P]),
     "r2d2_head_bwd": (_I, [_P] * 6 + [_I, _I, _P]),
     "r2d2_linear_dgrad": (_I, [_P, _P, _P, _I, _I, _I, _I, _P]),

@@ -45,7 +45,8 @@ __global__ void reduce_partials_kernel(const float* __restrict__ part, float* __
 // db[n] = sum_m dy[m*N + n]: 8 columns (one 32-byte sector per row) per CTA, 128 row lanes
 // stride over the rows with four independent accumulators, then a fixed-order reduction
 __global__ void __launch_bounds__(1024)
-colsum_kernel(const float* __restrict__ dy, float* __restrict__ db, int M, int N) {
+colsum_kernel(const float* __restrict__ dy, float* __restrict__ db, int M, int N,
+              float* __restrict__ db_copy = nullptr) {
     __shared__ float red[128][9];
     const int col = threadIdx.x & 7, rl = threadIdx.x >> 3;
     const int n = blockIdx.x * 8 + col;
@@ -67,7 +68,10 @@ colsum_kernel(const float* __restrict__ dy, float* __restrict__ db, int M, int N
         if (rl < h) red[rl][col] += red[rl + h][col];
         __syncthreads();
     }
-    if (rl == 0 && n < N) db[n] = red[0][col];
+    if (rl == 0 && n < N) {
+        db[n] = red[0][col];
+        if (db_copy) db_copy[n] = red[0][col];   // e.g. bias_ih and bias_hh share one gradient
+    }
 }
 
 // per-channel sum over frames and pixels of an NCHW gradient: db[c] = sum_{r,p} dz[r,c,p], C = 32.
@@ -808,6 +812,12 @@ int r2d2_head_out(const float* hid, const float* w2, const float* b2, float* q, 
 int r2d2_colsum(const float* dy, float* db, int M, int N, void* stream) {
     R2D2_REQUIRE(dy && db && M > 0 && N > 0, "colsum: bad args");
     R2D2_LAUNCH("colsum_kernel", as_stream(stream), colsum_kernel<<<(N + 7) / 8, 1024, 0, as_stream(stream)>>>(dy, db, M, N));
+    return R2D2_OK;
+}
+
+int r2d2_colsum2(const float* dy, float* db, float* db_copy, int M, int N, void* stream) {
+    R2D2_REQUIRE(dy && db && db_copy && M > 0 && N > 0, "colsum2: bad args");
+    R2D2_LAUNCH("colsum_kernel", as_stream(stream), colsum_kernel<<<(N + 7) / 8, 1024, 0, as_stream(stream)>>>(dy, db, M, N, db_copy));
     return R2D2_OK;
 }
 

@@ -101,9 +101,12 @@ def head_out(hid, w: Weights, q):
     _lib.call("r2d2_head_out", P(hid, "f32"), P(w.head_w2), P(w.head_b2), P(q, "f32"), M, H2 // 2, S())
 
 
-def colsum(dy, db):
+def colsum(dy, db, db_copy=None):
     M, N = dy.shape
-    _lib.call("r2d2_colsum", P(dy, "f32"), P(db, "f32"), M, N, S())
+    if db_copy is not None:
+        _lib.call("r2d2_colsum2", P(dy, "f32"), P(db, "f32"), P(db_copy, "f32"), M, N, S())
+    else:
+        _lib.call("r2d2_colsum", P(dy, "f32"), P(db, "f32"), M, N, S())
 
 
 def td_target(q_all, qn_on, qn_tg, action, reward, done, gamma_n, out, *, rescale=False,

@@ -513,17 +513,20 @@ class Learner:
             beside(head_wgrad)
             engine.cast_bf16(ws["dhid"], ws["dhid16"])
             engine.tc_linear(ws["dhid16"], ws["hw1T16"], None, None, y32=ws["dhs"])
+
+            def lstm_wgrad_operands():   # forward-only operands: transposed while the BPTT runs
+                engine.transpose_cast_bf16(hprev, ws["hprevT16"])
+                engine.transpose_cast_bf16(feat_l, ws["featT16"])
+
+            beside(lstm_wgrad_operands, aux)
             engine.tc_lstm_seq_bwd(ws["dhs"], w.w_hh, ws["gates"][BI:], ws["cs_on"][BI:], ws["dgates"],
                                    L, B, H, ws["lstm_bwd_scratch"], dgates16=ws["dg16"])
 
             def lstm_wgrad():
                 engine.transpose_cast_bf16(ws["dgates"], ws["dgT16"])
-                engine.transpose_cast_bf16(hprev, ws["hprevT16"])
                 engine.tc_linear(ws["dgT16"], ws["hprevT16"], None, None, y32=g.w_hh)
-                engine.colsum(ws["dgates"], g.b_hh)
-                g.b_ih.copy_(g.b_hh)
-                engine.transpose_cast_bf16(feat_l, ws["featT16"])
                 engine.tc_linear(ws["dgT16"], ws["featT16"], None, None, y32=g.w_ih)
+                engine.colsum(ws["dgates"], g.b_hh, g.b_ih)
 
             beside(lstm_wgrad, aux)       # the longest consumer chain gets a stream of its own
             if overlap_bwd and self.optim.peer is not None:
