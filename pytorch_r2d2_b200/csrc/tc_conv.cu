@@ -16,6 +16,7 @@
 // The weights (both halves, all K) stay resident in shared memory; two TMEM accumulator
 // buffers let the epilogue of tile i overlap the MMAs of tile i+1.
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 
 #include "common.cuh"
 #include "gemm.cuh"   // FrameMap
@@ -28,6 +29,18 @@ constexpr int CV_STAGES = 4;
 __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
     __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
     return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ uint32_t pack_f16x2(float a, float b) {
+    __half2 v = __floats2half2_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&v);
+}
+// two u8 pixels (bytes 2*PAIR, 2*PAIR+1 of w) -> packed fp16x2, exact, two instructions: splice each
+// byte under the exponent of 1024.0h (0x64xx = 1024 + x) with one PRMT, subtract (1024, 1024)
+template <int PAIR>
+__device__ __forceinline__ uint32_t u8x2_to_f16x2(uint32_t w) {
+    const uint32_t m = __byte_perm(w, 0x64646464u, PAIR == 0 ? 0x4140u : 0x4342u);
+    const __half2 r = __hsub2(*reinterpret_cast<const __half2*>(&m), __half2half2(__ushort_as_half(0x6400)));
+    return *reinterpret_cast<const uint32_t*>(&r);
 }
 __device__ __forceinline__ float bf16_round(float x) {
     return __bfloat162float(__float2bfloat16_rn(x));
@@ -106,6 +119,10 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
     constexpr uint32_t W_KB = COUT * 128;                    // 32 rows x 64 bf16 per k-block and half
     constexpr uint32_t W_BYTES = NW * 2 * NKB * W_KB;        // per k-block: NW x [hi rows | lo rows]
     constexpr uint32_t ACC_COLS = NW * 2 * COUT;             // accumulator columns per buffer
+    // u8 frames: operands in fp16 instead of bf16 -- pixels 0..255 are exact in both, but a byte
+    // becomes fp16 with ONE PRMT + half an HSUB2 (bf16 needs PRMT + FADD + half an F2FP), and the
+    // weights' (hi, lo) split keeps 22 mantissa bits instead of 16
+    constexpr bool U8F16 = sizeof(T) == 1 && KH == 8;
     constexpr int MMA_WARP = NPW;
     constexpr int NCH = 32 / NPW;                            // 16-byte chunks of a row per producer thread
     static_assert(NPW == 8 || NPW == 16, "8 or 16 producer warps");
@@ -145,16 +162,24 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
             const int k = ch * 8 + e;
             const float x = k < K ? __ldg(wsrc + (long long)co * K + k) : 0.f;
             v[e] = x;
-            l[e] = x - bf16_round(x);
+            l[e] = x - (U8F16 ? __half2float(__float2half_rn(x)) : bf16_round(x));
         }
         // rows 0..31 of a net's k-block tile = W_hi, rows 32..63 = W_lo: ONE K-major operand of
         // 64*NW rows (1 KB swizzle atoms of 8 rows, so the per-net 8 KB offset keeps the pattern)
         const uint32_t off = (uint32_t)(kb * NW + net) * 2 * W_KB + sw128_off(co, c);
+        if constexpr (U8F16) {
+            *reinterpret_cast<uint4*>(w_s + off) = make_uint4(pack_f16x2(v[0], v[1]), pack_f16x2(v[2], v[3]),
+                                                             pack_f16x2(v[4], v[5]), pack_f16x2(v[6], v[7]));
+            *reinterpret_cast<uint4*>(w_s + off + W_KB) =
+                make_uint4(pack_f16x2(l[0], l[1]), pack_f16x2(l[2], l[3]), pack_f16x2(l[4], l[5]),
+                           pack_f16x2(l[6], l[7]));
+        } else {
         *reinterpret_cast<uint4*>(w_s + off) = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
                                                          pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
         *reinterpret_cast<uint4*>(w_s + off + W_KB) =
             make_uint4(pack_bf16x2(l[0], l[1]), pack_bf16x2(l[2], l[3]), pack_bf16x2(l[4], l[5]),
                        pack_bf16x2(l[6], l[7]));
+        }
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // weights -> tensor-core proxy
     if (warp == MMA_WARP) tmem_alloc(&tmem_slot, 2 * ACC_COLS);            // 2 buffers x NW x (32 + 32) columns
@@ -202,15 +227,9 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
                     uint8_t* a_hi = a_s + (size_t)s * STAGE_BYTES;
 #pragma unroll
                     for (int cc = 0; cc < NCH; ++cc) {
-                        float v[8];
-#pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            v[e] = __uint_as_float(__byte_perm(cur[kb][cc][0], 0x4B000000u, 0x7650u | e)) - 8388608.f;
-                            v[4 + e] = __uint_as_float(__byte_perm(cur[kb][cc][1], 0x4B000000u, 0x7650u | e)) - 8388608.f;
-                        }
                         *reinterpret_cast<uint4*>(a_hi + sw128_off(row, half * NCH + cc)) =
-                            make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
-                                       pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+                            make_uint4(u8x2_to_f16x2<0>(cur[kb][cc][0]), u8x2_to_f16x2<1>(cur[kb][cc][0]),
+                                       u8x2_to_f16x2<0>(cur[kb][cc][1]), u8x2_to_f16x2<1>(cur[kb][cc][1]));
                     }
                     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                     mbar_arrive(&full_bar[s]);
@@ -286,7 +305,8 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
             // issues one every ~37 ns, so the count matters: A_hi multiplies both W_hi and W_lo,
             // hence ONE MMA with N = 64 against the stacked [W_hi ; W_lo] rows (columns 0-31 and
             // 32-63 of the accumulator, added in the epilogue) instead of two with N = 32.
-            constexpr uint32_t idesc64 = umma_idesc_bf16(128, ACC_COLS), idesc32 = umma_idesc_bf16(128, COUT);
+            constexpr uint32_t idesc64 = U8F16 ? umma_idesc_f16(128, ACC_COLS) : umma_idesc_bf16(128, ACC_COLS),
+                               idesc32 = umma_idesc_bf16(128, COUT);
             const uint32_t wb = smem_u32(w_s);
             uint32_t it = 0, tcount = 0;
             for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++tcount) {
