@@ -172,7 +172,10 @@ __global__ void __launch_bounds__(192, 1)
 tc_gemm_x3_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                   const __grid_constant__ CUtensorMap tma_a_lo,
                   const __grid_constant__ CUtensorMap tma_b_lo, const TcEpilogue ep, const int M,
-                  const int N, const int K) {
+                  const int N, const int K, const int bn_rt) {
+    // wide form: the tile is bn <= 256 columns wide (multiple of 16, chosen by the host so that the
+    // number of tiles fills whole waves of SMs); the stage layout keeps room for 256
+    const int bn = BN == 128 ? BN : bn_rt;
     constexpr uint32_t A_BYTES = TC_BM * TC_BK * 2, B_BYTES = BN * TC_BK * 2;
     constexpr uint32_t STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;
     constexpr int STAGES = BN == 128 ? 3 : 2;
@@ -183,7 +186,7 @@ tc_gemm_x3_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
     const uint32_t raw = smem_u32(smem_raw);
     uint8_t* tiles = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int m0 = blockIdx.x * TC_BM, n0 = blockIdx.y * BN;
+    const int m0 = blockIdx.x * TC_BM, n0 = blockIdx.y * bn;
     const int num_kb = (K + TC_BK - 1) / TC_BK;
 
     if (warp == 0 && lane == 0) {
@@ -209,7 +212,7 @@ tc_gemm_x3_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
             for (int kb = 0; kb < num_kb; ++kb) {
                 const int s = kb % STAGES;
                 mbar_wait(&empty_bar[s], ((kb / STAGES) & 1) ^ 1);
-                mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+                mbar_expect_tx(&full_bar[s], 2 * A_BYTES + 2 * (uint32_t)bn * TC_BK * 2);
                 uint8_t* dst = tiles + (size_t)s * STAGE_BYTES;
                 const int kk = kb * TC_BK;
                 tma_load_2d(dst, &tma_a, kk, m0, &full_bar[s]);
@@ -220,7 +223,8 @@ tc_gemm_x3_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_bf16(TC_BM, BN), idesc_cat = umma_idesc_bf16(TC_BM, 256);
+            const uint32_t idesc = umma_idesc_bf16(TC_BM, bn);
+            constexpr uint32_t idesc_cat = umma_idesc_bf16(TC_BM, 256);
             for (int kb = 0; kb < num_kb; ++kb) {
                 const int s = kb % STAGES;
                 mbar_wait(&full_bar[s], (kb / STAGES) & 1);
@@ -249,7 +253,7 @@ tc_gemm_x3_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
         const int q = warp & 3;
         const int m = m0 + q * 32 + lane;
 #pragma unroll 1
-        for (int c = 0; c < BN; c += 32) {
+        for (int c = 0; c < bn; c += 32) {
             uint32_t r[32];
             tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c, r);
             if constexpr (CAT) {
@@ -265,7 +269,7 @@ tc_gemm_x3_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
 #pragma unroll
                 for (int j = 0; j < 32; j += 4) {
                     const int n = n0 + c + j;
-                    if (n >= N) break;
+                    if (n >= N || c + j >= bn) break;
                     float v[4];
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
@@ -410,7 +414,16 @@ static int tc_linear_impl(const void* x_hi, const void* x_lo, const void* w_hi, 
         // bf16x3: BN = 256 halves the operand traffic per output; the small problems (heads) keep
         // 128-wide tiles so that they still spread over the SMs
         const bool wide = (long long)((M + TC_BM - 1) / TC_BM) * ((N + 255) / 256) >= 2 * sm_count();
-        const int BNx = wide ? 256 : 128;
+        int BNx = 128;
+        if (wide) {
+            // tile width that wastes the least in the last wave: cost = waves x width
+            const long long mt = (M + TC_BM - 1) / TC_BM, sms = sm_count();
+            long long best = -1;
+            for (int bn = 256; bn >= 144; bn -= 16) {
+                const long long tiles = mt * ((N + bn - 1) / bn), cost = (tiles + sms - 1) / sms * bn;
+                if (best < 0 || cost < best) { best = cost; BNx = bn; }
+            }
+        }
         CUtensorMap ta, tb, ta_lo, tb_lo;
         int rc = make_tmap(&ta, x_hi, M, K, TC_BM);
         if (rc) return rc;
@@ -426,12 +439,12 @@ static int tc_linear_impl(const void* x_hi, const void* x_lo, const void* w_hi, 
             const int smem = 2 * (2 * TC_BM * TC_BK * 2 + 2 * 256 * TC_BK * 2) + 1024;
             R2D2_CUDA_OK(cudaFuncSetAttribute(tc_gemm_x3_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
             R2D2_LAUNCH("tc_gemm_kernel_x3", as_stream(stream),
-                        tc_gemm_x3_kernel<256><<<grid, 192, smem, as_stream(stream)>>>(ta, tb, ta_lo, tb_lo, ep, M, N, K));
+                        tc_gemm_x3_kernel<256><<<grid, 192, smem, as_stream(stream)>>>(ta, tb, ta_lo, tb_lo, ep, M, N, K, BNx));
         } else {
             const int smem = 3 * (2 * TC_BM * TC_BK * 2 + 2 * 128 * TC_BK * 2) + 1024;
             R2D2_CUDA_OK(cudaFuncSetAttribute(tc_gemm_x3_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
             R2D2_LAUNCH("tc_gemm_kernel_x3", as_stream(stream),
-                        tc_gemm_x3_kernel<128><<<grid, 192, smem, as_stream(stream)>>>(ta, tb, ta_lo, tb_lo, ep, M, N, K));
+                        tc_gemm_x3_kernel<128><<<grid, 192, smem, as_stream(stream)>>>(ta, tb, ta_lo, tb_lo, ep, M, N, K, 128));
         }
         return R2D2_OK;
     }
