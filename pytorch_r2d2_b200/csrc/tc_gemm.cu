@@ -41,7 +41,9 @@ __global__ void __launch_bounds__(192, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                const __grid_constant__ CUtensorMap tma_a_lo,
                const __grid_constant__ CUtensorMap tma_b_lo, const int nseg, const TcEpilogue ep,
-               const int M, const int N, const int K) {
+               const int M, const int N, const int K, const int bn) {
+    // bn <= BN (multiple of 16): tile width chosen by the host to fill whole waves of SMs; the
+    // stage layout keeps room for BN columns
     constexpr uint32_t A_BYTES = TC_BM * TC_BK * 2, B_BYTES = BN * TC_BK * 2;
     constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
     extern __shared__ uint8_t smem_raw[];
@@ -53,7 +55,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     uint8_t* tiles = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int m0 = blockIdx.x * TC_BM, n0 = blockIdx.y * BN;
+    const int m0 = blockIdx.x * TC_BM, n0 = blockIdx.y * bn;
     // nseg == 1: C = A.B^T in plain bf16.  nseg == 3: error-compensated "bf16x3" -- A = A_hi+A_lo,
     // B = B_hi+B_lo (each the bf16 rounding of the remainder) and C = A_hi.B_hi + A_hi.B_lo +
     // A_lo.B_hi accumulated in fp32 in TMEM: ~2^-16 relative operand error instead of 2^-9.
@@ -82,7 +84,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                 const int s = kb % TC_STAGES;
                 const uint32_t ph = (kb / TC_STAGES) & 1;
                 mbar_wait(&empty_bar[s], ph ^ 1);            // slot free (first pass: immediate)
-                mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+                mbar_expect_tx(&full_bar[s], A_BYTES + (uint32_t)bn * TC_BK * 2);
                 uint8_t* a_dst = tiles + (size_t)s * STAGE_BYTES;
                 const int seg = kb / kb_per_seg, kk = (kb - seg * kb_per_seg) * TC_BK;
                 tma_load_2d(a_dst, seg == 2 ? &tma_a_lo : &tma_a, kk, m0, &full_bar[s]);
@@ -91,7 +93,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_bf16(TC_BM, BN);
+            const uint32_t idesc = umma_idesc_bf16(TC_BM, bn);
             for (int kb = 0; kb < num_kb; ++kb) {
                 const int s = kb % TC_STAGES;
                 const uint32_t ph = (kb / TC_STAGES) & 1;
@@ -114,7 +116,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
         const int q = warp & 3;                              // TMEM lane quarter of this warp
         const int m = m0 + q * 32 + lane;
 #pragma unroll 1
-        for (int c = 0; c < BN; c += 32) {
+        for (int c = 0; c < bn; c += 32) {
             uint32_t r[32];
             tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c, r);
             tmem_ld_wait();
@@ -122,7 +124,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
 #pragma unroll
                 for (int j = 0; j < 32; j += 4) {
                     const int n = n0 + c + j;
-                    if (n >= N) break;
+                    if (n >= N || c + j >= bn) break;
                     float v[4];
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
@@ -449,14 +451,23 @@ static int tc_linear_impl(const void* x_hi, const void* x_lo, const void* w_hi, 
         return R2D2_OK;
     }
     constexpr int BN = 128;
+    int bn = BN;
+    {   // tile width that wastes the least in the last wave (cost = waves x width); ties -> wider
+        const long long mt = (M + TC_BM - 1) / TC_BM, sms = sm_count();
+        long long best = -1;
+        for (int w = BN; w >= 64; w -= 16) {
+            const long long tiles = mt * ((N + w - 1) / w), cost = (tiles + sms - 1) / sms * w;
+            if (best < 0 || cost < best) { best = cost; bn = w; }
+        }
+    }
     CUtensorMap ta, tb, ta_lo, tb_lo;
     int rc = make_tmap(&ta, x_hi, M, K, TC_BM);
     if (rc) return rc;
-    rc = make_tmap(&tb, w_hi, N, K, BN);
+    rc = make_tmap(&tb, w_hi, N, K, bn);
     if (rc) return rc;
     rc = make_tmap(&ta_lo, x_lo ? x_lo : x_hi, M, K, TC_BM);
     if (rc) return rc;
-    rc = make_tmap(&tb_lo, w_lo ? w_lo : w_hi, N, K, BN);
+    rc = make_tmap(&tb_lo, w_lo ? w_lo : w_hi, N, K, bn);
     if (rc) return rc;
     const int smem = TC_STAGES * (TC_BM * TC_BK * 2 + BN * TC_BK * 2) + 1024;
     static bool attr_set = false;
@@ -466,11 +477,11 @@ static int tc_linear_impl(const void* x_hi, const void* x_lo, const void* w_hi, 
     }
     TcEpilogue ep{y_f32, reinterpret_cast<__nv_bfloat16*>(y_bf16), N, bias1, bias2, relu & 1,
                   (relu >> 1) & 1, mask};
-    dim3 grid((M + TC_BM - 1) / TC_BM, (N + BN - 1) / BN);
+    dim3 grid((M + TC_BM - 1) / TC_BM, (N + bn - 1) / bn);
     const int nseg = x_lo ? 3 : 1;
     R2D2_LAUNCH(nseg == 3 ? "tc_gemm_kernel_x3" : "tc_gemm_kernel", as_stream(stream),
                 tc_gemm_kernel<BN><<<grid, 192, smem, as_stream(stream)>>>(ta, tb, ta_lo, tb_lo, nseg,
-                                                                         ep, M, N, K));
+                                                                         ep, M, N, K, bn));
     return R2D2_OK;
 }
 
