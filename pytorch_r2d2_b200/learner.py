@@ -261,6 +261,7 @@ class Learner:
             ws["xchg_stream"] = torch.cuda.Stream(device=dev, priority=-1)   # multi-GPU exchange: peers wait on it
             ws["aux_stream"] = torch.cuda.Stream(device=dev, priority=-1)   # LSTM weight gradients: short CTAs, gate the exchange
             ws["ev_aux"] = [torch.cuda.Event() for _ in range(3)]
+            ws["ev_wprep"] = torch.cuda.Event()
             ws["events"] = [torch.cuda.Event() for _ in range(16)]
             ws["ev_fork"], ws["ev_join"] = torch.cuda.Event(), torch.cuda.Event()
             ws["dhid16"], ws["dhidT16"], ws["hsT16"] = h(M, 2 * H), h(2 * H, M), h(H, M)
@@ -343,9 +344,31 @@ class Learner:
         bf16 = self.precision == "bf16"
         # tensor-core path: the first conv layer (forward and weight gradient) reads the sampled
         # frames in place from the ring, so the 154 MB slab copy never happens
-        batch = rm.sample_slab(u=u, seq_index=seq_index, frames=not bf16)
-        slab = batch["slab"]
         w, wt = self.net._weights(), self.target_net._weights()
+        if bf16:
+            # weight-only operand preparation (bf16 hi/lo splits for the forward GEMMs, transposed
+            # bf16 copies for the backward data gradients): nothing here depends on the batch, so it
+            # runs on the third stream from the very start of the step
+            def weight_prep():
+                engine.split_bf16(w.w_ih, ws["w_ih16"][0], ws["w_ih16"][1])
+                engine.split_bf16(w.head_w1, ws["hw1_16"][0], ws["hw1_16"][1])
+                engine.split_bf16(wt.w_ih, ws["w_ih16_t"][0], ws["w_ih16_t"][1])
+                engine.split_bf16(wt.head_w1, ws["hw1_16_t"][0], ws["hw1_16_t"][1])
+                engine.transpose_cast_bf16(w.head_w1, ws["hw1T16"])
+                engine.transpose_cast_bf16(w.w_ih, ws["w_ihT16"])
+
+            if self.overlap_streams:
+                ws["ev_aux"][2].record(torch.cuda.current_stream())
+                ws["aux_stream"].wait_event(ws["ev_aux"][2])
+                with torch.cuda.stream(ws["aux_stream"]):
+                    weight_prep()
+                    ws["ev_wprep"].record(ws["aux_stream"])
+            else:
+                weight_prep()
+        # the gather writes the initial recurrent states straight into slot 0 of the histories
+        batch = rm.sample_slab(u=u, seq_index=seq_index, frames=not bf16,
+                               hidden_out=(ws["hs_on"][0], ws["cs_on"][0], ws["hs_tg"][0], ws["cs_tg"][0]))
+        slab = batch["slab"]
         g = Weights(self.optim.grad, self.net.layout)
         M = L * B
 
@@ -375,11 +398,9 @@ class Learner:
                 engine.torso_fwd_tail(ws["a1_tg"], wt, ws["a2_tg"], ws["feat_tg"], ws["feat16_tg"])
             else:
                 engine.torso_fwd_u8(slab, n, T, wt, ws["a1_tg"], ws["a2_tg"], ws["feat_tg"], tc=bf16)
-            ws["hs_tg"][0].copy_(batch["target_hs"])
-            ws["cs_tg"][0].copy_(batch["target_cs"])
             if bf16:
-                split(wt.w_ih, ws["w_ih16_t"])
-                split(wt.head_w1, ws["hw1_16_t"])
+                if overlap:
+                    torch.cuda.current_stream().wait_event(ws["ev_wprep"])
                 if not fused_conv1:
                     split(ws["feat_tg"], ws["feat16_tg"])
                 engine.tc_linear_x3(ws["w_ih16_t"][0], ws["w_ih16_t"][1], ws["feat16_tg"][0],
@@ -416,21 +437,11 @@ class Learner:
             engine.torso_fwd_tail(ws["a1_on"], w, ws["a2_on"], ws["feat_on"], ws["feat16_on"])
         else:
             engine.torso_fwd_u8(slab, 0, T + n, w, ws["a1_on"], ws["a2_on"], ws["feat_on"], tc=bf16)
-        ws["hs_on"][0].copy_(batch["hs"])
-        ws["cs_on"][0].copy_(batch["cs"])
         if bf16:
             # forward contractions: error-compensated bf16x3;
             # xproj^T[4H, frames*B] = W_ih . feat^T + (b_ih + b_hh) per row
-            split(w.w_ih, ws["w_ih16"])
-            split(w.head_w1, ws["hw1_16"])
-            # transposed bf16 weights for the backward data gradients: weight-only work, done now
-            # on the idle third stream instead of between the gradient kernels on the critical path
             if overlap:
-                ws["ev_aux"][2].record(main)
-                ws["aux_stream"].wait_event(ws["ev_aux"][2])
-            with torch.cuda.stream(ws["aux_stream"]) if overlap else contextlib.nullcontext():
-                engine.transpose_cast_bf16(w.head_w1, ws["hw1T16"])
-                engine.transpose_cast_bf16(w.w_ih, ws["w_ihT16"])
+                main.wait_event(ws["ev_wprep"])
             if not fused_conv1:
                 split(ws["feat_on"], ws["feat16_on"])
             engine.tc_linear_x3(ws["w_ih16"][0], ws["w_ih16"][1], ws["feat16_on"][0], ws["feat16_on"][1],

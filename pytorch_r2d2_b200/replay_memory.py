@@ -342,11 +342,13 @@ class ReplayMemory:
                   _lib.stream_ptr())
         return out
 
-    def sample_slab(self, u=None, seq_index=None, frames=True):
+    def sample_slab(self, u=None, seq_index=None, frames=True, hidden_out=None):
         """Device-resident fast path: draw, then gather one contiguous (T+n)-frame u8 slab per
         sequence plus hidden/action/reward/done/index.  Returns the workspace dict (tensors are
         reused by the next call).  frames=False leaves the frames in the ring (``ws["ring"]``,
-        read in place through ``ws["seq_index"]`` by the ring forms of the first conv layer)."""
+        read in place through ``ws["seq_index"]`` by the ring forms of the first conv layer).
+        hidden_out = (hs, cs, target_hs, target_cs) [B,H] f32 tensors that receive the initial
+        recurrent states directly (e.g. slot 0 of the caller's history buffers)."""
         B, T, n, H = self.batch_size, self.sequence_length, self.n_step, self.cell_size
         ws = self._workspace(B, T, n, H)
         self._wait_ingest()
@@ -361,13 +363,14 @@ class ReplayMemory:
                       _lib.ptr(ws["seq_index"], "i64"), _lib.stream_ptr())
         else:
             ws["seq_index"].copy_(self._dev(seq_index, torch.int64).reshape(-1))
+        ho = hidden_out if hidden_out is not None else (ws["hs"], ws["cs"], ws["target_hs"], ws["target_cs"])
         _lib.call("r2d2_replay_gather", _lib.ptr(self._raw("state"), "u8"),
                   _lib.ptr(self._raw("hs_cs"), "f32"), _lib.ptr(self._raw("target_hs_cs"), "f32"),
                   _lib.ptr(self._raw("action"), "i8"), _lib.ptr(self._raw("reward"), "f32"),
                   _lib.ptr(self._raw("done"), "f32"), self.memory_size, H,
                   _lib.ptr(ws["seq_index"], "i64"), B, T, n, self.burn_in_length,
-                  _lib.ptr(ws["slab"], "u8") if frames else None, _lib.ptr(ws["hs"], "f32"), _lib.ptr(ws["cs"], "f32"),
-                  _lib.ptr(ws["target_hs"], "f32"), _lib.ptr(ws["target_cs"], "f32"),
+                  _lib.ptr(ws["slab"], "u8") if frames else None, _lib.ptr(ho[0], "f32"), _lib.ptr(ho[1], "f32"),
+                  _lib.ptr(ho[2], "f32"), _lib.ptr(ho[3], "f32"),
                   _lib.ptr(ws["action"], "i64"), _lib.ptr(ws["reward"], "f32"),
                   _lib.ptr(ws["done"], "f32"), _lib.ptr(ws["index"], "i64"),
                   int(self.use_tma_gather), _lib.stream_ptr())
