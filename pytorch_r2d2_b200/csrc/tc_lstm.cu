@@ -315,13 +315,16 @@ tc_lstm_fwd_kernel(const LstmArgs a) {
 #pragma unroll
                 for (int i = 0; i < LS_ISSUERS; ++i) {
                     if (i < nslices) {
+                        // both halves of the slice in flight before the one wait
+                        static_assert(SW == 64, "two 32-column loads per slice");
+                        uint32_t r0[32], r1[32];
+                        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + i * SW, r0);
+                        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + i * SW + 32, r1);
+                        tmem_ld_wait();
 #pragma unroll
-                        for (int c = 0; c < SW; c += 32) {
-                            uint32_t r[32];
-                            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + i * SW + c, r);
-                            tmem_ld_wait();
-#pragma unroll
-                            for (int j = 0; j < 32; ++j) acc[(c + j) % NB] += __uint_as_float(r[j]);
+                        for (int j = 0; j < 32; ++j) {
+                            acc[j % NB] += __uint_as_float(r0[j]);
+                            acc[(32 + j) % NB] += __uint_as_float(r1[j]);
                         }
                     }
                 }
