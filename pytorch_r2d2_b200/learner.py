@@ -14,7 +14,6 @@ the data-parallel gradient allreduce.
 """
 from __future__ import annotations
 
-import contextlib
 import os
 from copy import deepcopy
 

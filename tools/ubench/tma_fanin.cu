@@ -125,7 +125,6 @@ fanin(const __grid_constant__ CUtensorMap tm, uint8_t* buf, int* counter, long l
                 for (int p = 0; p < PIECES; ++p) mbar_wait(&pbar[p], s & 1);
                 tsum += gtimer() - t0;
                 if (c == 0 && s == steps - 1) out[gridDim.x] = t1 - t0;
-                continue_step:;
             } else {
             mbar_expect_tx(&bar, TILE);
             if (mode == 0 || mode == 1 || mode == 5) {
