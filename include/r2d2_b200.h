@@ -242,7 +242,12 @@ int r2d2_tc_conv1_fwd_dual_u8(const uint8_t* slab, int B, int S, int nt, const f
  * per-sequence fields).  Same results as the slab forms. */
 int r2d2_tc_conv1_fwd_dual_ring(const uint8_t* ring_state, int64_t M, const int64_t* seq_index, int B,
                                 int nt, const float* w1_a, const float* b1_a, float* a1_a,
-                                const float* w1_b, const float* b1_b, float* a1_b, int s0_b, void* stream);
+                                const float* w1_b, const float* b1_b, float* a1_b, int s0_b,
+                                uint32_t* relu_bits_a, void* stream);
+/* relu_bits_a (optional, u32 [nt*B, 20*20]): bit co of word (frame, pixel) = (a1_a[frame, co, pixel] > 0);
+ * r2d2_tc_conv_dgrad2_masked takes ReLU' from it instead of reading the fp32 activations back. */
+int r2d2_tc_conv_dgrad2_masked(const float* dz2, const float* w2, const uint32_t* relu_bits, float* dz1,
+                               int R, void* stream);
 int r2d2_tc_conv1_wgrad_ring(const uint8_t* ring_state, int64_t M, const int64_t* seq_index, int B, int s0,
                              int nt, const float* dz, float* dw, float* db, float* part, void* stream);
 int r2d2_tc_torso_fwd_tail(const float* a1, int R, const float* w2, const float* b2, const float* w3,

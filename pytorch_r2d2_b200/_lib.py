@@ -53,7 +53,8 @@ PROTOTYPES = {
     "r2d2_torso_bwd_u8": (_I, [_P, _I, _I, _I, _I] + [_P] * 13 + [_P]),
     "r2d2_torso_bwd_f32": (_I, [_P, _I] + [_P] * 13 + [_P]),
     "r2d2_tc_conv1_fwd_dual_u8": (_I, [_P, _I, _I, _I, _P, _P, _P, _P, _P, _P, _I, _P]),
-    "r2d2_tc_conv1_fwd_dual_ring": (_I, [_P, _L, _P, _I, _I, _P, _P, _P, _P, _P, _P, _I, _P]),
+    "r2d2_tc_conv1_fwd_dual_ring": (_I, [_P, _L, _P, _I, _I, _P, _P, _P, _P, _P, _P, _I, _P, _P]),
+    "r2d2_tc_conv_dgrad2_masked": (_I, [_P, _P, _P, _P, _I, _P]),
     "r2d2_tc_conv1_wgrad_ring": (_I, [_P, _L, _P, _I, _I, _I, _P, _P, _P, _P, _P]),
     "r2d2_tc_torso_fwd_tail": (_I, [_P, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "r2d2_tc_torso_fwd_u8": (_I, [_P, _I, _I, _I, _I] + [_P] * 9 + [_P]),
@@ -121,7 +122,7 @@ def stream_ptr() -> ctypes.c_void_p:
 
 
 _DT = {"bf16": torch.bfloat16, "f32": torch.float32, "f64": torch.float64, "u8": torch.uint8, "i8": torch.int8,
-       "i64": torch.int64}
+       "i64": torch.int64, "i32": torch.int32}
 
 
 def ptr(t, dtype: str | None = None, allow_none: bool = False) -> ctypes.c_void_p:

@@ -109,7 +109,7 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
                    const float in_scale, const float* __restrict__ w1 = nullptr,
                    const float* __restrict__ bias1 = nullptr, float* __restrict__ out1 = nullptr,
                    const int skip1 = 0, __nv_bfloat16* __restrict__ out_hi = nullptr,
-                   __nv_bfloat16* __restrict__ out_lo = nullptr) {
+                   __nv_bfloat16* __restrict__ out_lo = nullptr, uint32_t* __restrict__ relu_bits = nullptr) {
     constexpr int K = CIN * KH * KH, NKB = (K + 63) / 64, KP = NKB * 64;
     constexpr int P = HOUT * HOUT, COUT = 32;
     constexpr bool NEED_LO = sizeof(T) != 1;                 // u8 pixels are exact in bf16
@@ -371,9 +371,16 @@ tc_conv_fwd_kernel(const T* __restrict__ in, const FrameMap fm, const float* __r
                             out_lo[oo + (long long)co * P] = __float2bfloat16_rn(x - __bfloat162float(h));
                         }
                     } else {
+                        uint32_t bits = 0u;
 #pragma unroll
-                        for (int co = 0; co < COUT; ++co)
-                            o[(long long)co * P] = fmaxf(fmaf(__uint_as_float(r[co]), in_scale, __ldg(bs + co)), 0.f);
+                        for (int co = 0; co < COUT; ++co) {
+                            const float x = fmaxf(fmaf(__uint_as_float(r[co]), in_scale, __ldg(bs + co)), 0.f);
+                            o[(long long)co * P] = x;
+                            bits |= (x > 0.f ? 1u : 0u) << co;
+                        }
+                        // ReLU' of net 0 as one word per frame and pixel (bit co), for the data
+                        // gradient that flows back into this layer's output
+                        if (net == 0 && relu_bits) relu_bits[(long long)fo * P + p] = bits;
                     }
                 }
             }
@@ -398,14 +405,14 @@ static int launch_tc_conv(const char* name, const T* in, FrameMap fm, const floa
     const int ntiles = (int)((Mtot + 127) / 128);
     int grid = sm_count();
     if (grid > ntiles) grid = ntiles;
-    R2D2_LAUNCH(name, st, kern<<<grid, NPW * 32 + 160, smem, st>>>(in, fm, w, b, out, R, in_scale, nullptr, nullptr, nullptr, 0, out_hi, out_lo));
+    R2D2_LAUNCH(name, st, kern<<<grid, NPW * 32 + 160, smem, st>>>(in, fm, w, b, out, R, in_scale, nullptr, nullptr, nullptr, 0, out_hi, out_lo, nullptr));
     return R2D2_OK;
 }
 
 // first conv layer of two networks over the same u8 frames (see the kernel's NW parameter)
 static int launch_tc_conv1_dual(const uint8_t* in, FrameMap fm, const float* wa, const float* ba, float* outa,
                                 const float* wb, const float* bb, float* outb, int R, int skip_b,
-                                cudaStream_t st) {
+                                cudaStream_t st, uint32_t* relu_bits_a = nullptr) {
     constexpr int NKB = 4;
     const int smem = 2 * 2 * NKB * 32 * 128 + CV_STAGES * 128 * 128 + 1024;
     constexpr int NPW = 8;     // measured: 16 producer warps are no faster here (0.260 vs 0.245 ms)
@@ -415,7 +422,7 @@ static int launch_tc_conv1_dual(const uint8_t* in, FrameMap fm, const float* wa,
     const int ntiles = (int)((Mtot + 127) / 128);
     int grid = sm_count();
     if (grid > ntiles) grid = ntiles;
-    R2D2_LAUNCH("tc_conv1_fwd_dual", st, kern<<<grid, NPW * 32 + 160, smem, st>>>(in, fm, wa, ba, outa, R, 1.f / 255.f, wb, bb, outb, skip_b, nullptr, nullptr));
+    R2D2_LAUNCH("tc_conv1_fwd_dual", st, kern<<<grid, NPW * 32 + 160, smem, st>>>(in, fm, wa, ba, outa, R, 1.f / 255.f, wb, bb, outb, skip_b, nullptr, nullptr, relu_bits_a));
     return R2D2_OK;
 }
 
@@ -895,9 +902,14 @@ tc_conv_dgrad_kernel(const float* __restrict__ dz, const float* __restrict__ w,
 // class, only the weights do, so the classes are concatenated along N: D[(r,yy,xx), (py,px,ci)],
 // N = 128.  One pass over dZ and over the layer's activations (ReLU'), 2x2 output blocks written
 // as float2 -- the per-class version re-read the activations four times (ncu: 226 MB per class).
+// MASKBITS: ReLU' comes from a bit mask (one u32 per frame and pixel, bit ci = activation > 0,
+// written by the first layer's forward epilogue) instead of the fp32 activations themselves:
+// 16 bytes per thread instead of 512, and the kernel is HBM-bound.
+template <bool MASKBITS>
 __global__ void __launch_bounds__(416, 1)
 tc_conv_dgrad2_kernel(const float* __restrict__ dz, const float* __restrict__ w,
-                      const float* __restrict__ act, float* __restrict__ din, const int R) {
+                      const float* __restrict__ act, const uint32_t* __restrict__ maskbits,
+                      float* __restrict__ din, const int R) {
     constexpr int KH = 4, HIN = 20, HOUT = 9, TAPS = 2, C = 32, NCOL = 128;
     constexpr int K = C * TAPS * TAPS, NKB = K / 64;             // 128, 2
     constexpr int G = 10, P = G * G;                              // (yy, xx) grid per frame
@@ -1026,12 +1038,14 @@ tc_conv_dgrad2_kernel(const float* __restrict__ dz, const float* __restrict__ w,
             tc_fence_after();
             const long long m = (long long)tile * 128 + q * 32 + lane;
             const bool valid = m < Mtot;
-            long long o = 0;
+            long long o = 0, mo = 0;
             if (valid) {
                 const int fr = (int)(m / P), p = (int)(m - (long long)fr * P);
                 const int yy = p / G, xx = p - yy * G;
                 o = (long long)fr * C * HIN * HIN + (2 * yy) * HIN + 2 * xx;
+                mo = (long long)fr * HIN * HIN + (2 * yy) * HIN + 2 * xx;
             }
+            (void)mo;
 #pragma unroll
             for (int py = 0; py < 2; ++py) {
                 uint32_t r0[32], r1[32];                       // px = 0, 1
@@ -1043,13 +1057,25 @@ tc_conv_dgrad2_kernel(const float* __restrict__ dz, const float* __restrict__ w,
                     mbar_arrive(&acc_empty[buf]);
                 }
                 if (valid) {
+                    if constexpr (MASKBITS) {
+                        // the two pixels (2yy+py, 2xx) and (2yy+py, 2xx+1) of this frame
+                        const uint2 mk = __ldg(reinterpret_cast<const uint2*>(maskbits + mo + py * HIN));
 #pragma unroll
-                    for (int ci = 0; ci < C; ++ci) {
-                        const long long oo = o + (long long)ci * HIN * HIN + py * HIN;
-                        const float2 a = *reinterpret_cast<const float2*>(act + oo);
-                        *reinterpret_cast<float2*>(din + oo) =
-                            make_float2(a.x > 0.f ? __uint_as_float(r0[ci]) : 0.f,
-                                        a.y > 0.f ? __uint_as_float(r1[ci]) : 0.f);
+                        for (int ci = 0; ci < C; ++ci) {
+                            const long long oo = o + (long long)ci * HIN * HIN + py * HIN;
+                            *reinterpret_cast<float2*>(din + oo) =
+                                make_float2((mk.x >> ci) & 1u ? __uint_as_float(r0[ci]) : 0.f,
+                                            (mk.y >> ci) & 1u ? __uint_as_float(r1[ci]) : 0.f);
+                        }
+                    } else {
+#pragma unroll
+                        for (int ci = 0; ci < C; ++ci) {
+                            const long long oo = o + (long long)ci * HIN * HIN + py * HIN;
+                            const float2 a = *reinterpret_cast<const float2*>(act + oo);
+                            *reinterpret_cast<float2*>(din + oo) =
+                                make_float2(a.x > 0.f ? __uint_as_float(r0[ci]) : 0.f,
+                                            a.y > 0.f ? __uint_as_float(r1[ci]) : 0.f);
+                        }
                     }
                 }
             }
@@ -1118,14 +1144,15 @@ int r2d2_tc_conv1_fwd_dual_u8(const uint8_t* slab, int B, int S, int nt, const f
 
 int r2d2_tc_conv1_fwd_dual_ring(const uint8_t* ring_state, int64_t M, const int64_t* seq_index, int B,
                                 int nt, const float* w1_a, const float* b1_a, float* a1_a,
-                                const float* w1_b, const float* b1_b, float* a1_b, int s0_b, void* stream) {
+                                const float* w1_b, const float* b1_b, float* a1_b, int s0_b,
+                                uint32_t* relu_bits_a, void* stream) {
     R2D2_REQUIRE(ring_state && seq_index && w1_a && b1_a && a1_a && w1_b && b1_b && a1_b,
                  "tc_conv1_fwd_dual_ring: null pointer");
     R2D2_REQUIRE(B > 0 && nt > 0 && M > 0 && s0_b >= 0 && s0_b < nt, "tc_conv1_fwd_dual_ring: bad frame window");
     R2D2_REQUIRE((long long)B * nt * 400 < (1ll << 31), "tc_conv1_fwd_dual_ring: too many frames");
     FrameMap fm{B, nt, 0, R2D2_FRAME_BYTES, reinterpret_cast<const long long*>(seq_index), (long long)M};
     return launch_tc_conv1_dual(ring_state, fm, w1_a, b1_a, a1_a, w1_b, b1_b, a1_b, B * nt, s0_b * B,
-                                as_stream(stream));
+                                as_stream(stream), relu_bits_a);
 }
 
 // grid the weight-gradient kernels run with (one CTA per SM, at most one per 64-pixel block)
@@ -1169,17 +1196,31 @@ int r2d2_tc_conv_dgrad3(const float* dz3, const float* w3, const float* a2, floa
     R2D2_REQUIRE(dz3 && w3 && a2 && dz2 && R > 0, "tc_conv_dgrad3: bad args");
     return launch_tc_dgrad<3, 9, 7, 1, 0, 0>("tc_conv3_dgrad", dz3, w3, a2, dz2, R, as_stream(stream));
 }
-int r2d2_tc_conv_dgrad2(const float* dz2, const float* w2, const float* a1, float* dz1, int R,
-                        void* stream) {
-    R2D2_REQUIRE(dz2 && w2 && a1 && dz1 && R > 0, "tc_conv_dgrad2: bad args");
-    cudaStream_t st = as_stream(stream);
+static int dgrad2_launch(const float* dz2, const float* w2, const float* a1, const uint32_t* maskbits,
+                         float* dz1, int R, cudaStream_t st) {
     const int smem = 2 * 128 * 128 + CV_STAGES * 128 * 128 + 1024;
-    R2D2_CUDA_OK(cudaFuncSetAttribute(tc_conv_dgrad2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     const int ntiles = (int)(((long long)R * 100 + 127) / 128);
     int grid = sm_count();
     if (grid > ntiles) grid = ntiles;
-    R2D2_LAUNCH("tc_conv2_dgrad", st, tc_conv_dgrad2_kernel<<<grid, 416, smem, st>>>(dz2, w2, a1, dz1, R));
+    if (maskbits) {
+        R2D2_CUDA_OK(cudaFuncSetAttribute(tc_conv_dgrad2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        R2D2_LAUNCH("tc_conv2_dgrad", st, tc_conv_dgrad2_kernel<true><<<grid, 416, smem, st>>>(dz2, w2, nullptr, maskbits, dz1, R));
+    } else {
+        R2D2_CUDA_OK(cudaFuncSetAttribute(tc_conv_dgrad2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        R2D2_LAUNCH("tc_conv2_dgrad", st, tc_conv_dgrad2_kernel<false><<<grid, 416, smem, st>>>(dz2, w2, a1, nullptr, dz1, R));
+    }
     return R2D2_OK;
+}
+int r2d2_tc_conv_dgrad2(const float* dz2, const float* w2, const float* a1, float* dz1, int R,
+                        void* stream) {
+    R2D2_REQUIRE(dz2 && w2 && a1 && dz1 && R > 0, "tc_conv_dgrad2: bad args");
+    return dgrad2_launch(dz2, w2, a1, nullptr, dz1, R, as_stream(stream));
+}
+int r2d2_tc_conv_dgrad2_masked(const float* dz2, const float* w2, const uint32_t* relu_bits, float* dz1,
+                               int R, void* stream) {
+    R2D2_REQUIRE(dz2 && w2 && relu_bits && dz1 && R > 0 && ((uintptr_t)relu_bits % 8) == 0,
+                 "tc_conv_dgrad2_masked: bad args");
+    return dgrad2_launch(dz2, w2, nullptr, relu_bits, dz1, R, as_stream(stream));
 }
 
 // partial-sum reduction shared with the fp32 path (nn_kernels.cu)

@@ -49,11 +49,12 @@ def conv1_fwd_dual_u8(slab, nt, wa: Weights, a1_a, wb: Weights, a1_b, s0_b):
               P(wb.w1), P(wb.b1), P(a1_b, "f32"), s0_b, S())
 
 
-def conv1_fwd_dual_ring(ring, seq_index, nt, wa: Weights, a1_a, wb: Weights, a1_b, s0_b):
+def conv1_fwd_dual_ring(ring, seq_index, nt, wa: Weights, a1_a, wb: Weights, a1_b, s0_b, relu_bits_a=None):
     """As conv1_fwd_dual_u8, the frames read in place from the replay ring [M,4,84,84] u8 through
     the sampled start slots seq_index (i64 [B], device)."""
     _lib.call("r2d2_tc_conv1_fwd_dual_ring", P(ring, "u8"), ring.shape[0], P(seq_index, "i64"), seq_index.numel(), nt,
-              P(wa.w1), P(wa.b1), P(a1_a, "f32"), P(wb.w1), P(wb.b1), P(a1_b, "f32"), s0_b, S())
+              P(wa.w1), P(wa.b1), P(a1_a, "f32"), P(wb.w1), P(wb.b1), P(a1_b, "f32"), s0_b,
+              P(relu_bits_a, "i32", True), S())
 
 
 def conv1_wgrad_ring(ring, seq_index, s0, nt, dz1, dw1, part, db1=None):

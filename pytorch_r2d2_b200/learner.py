@@ -252,6 +252,7 @@ class Learner:
             ws["lstm_scratch_tg"] = torch.empty_like(ws["lstm_scratch"])
             ws["lstm_bwd_scratch"] = torch.empty(engine.tc_lstm_bwd_scratch_bytes(B, H), dtype=torch.uint8, device=dev)
             nsm = int(_lib.load().r2d2_sm_count())
+            ws["relu1_bits"] = torch.empty((S * B, 400), dtype=torch.int32, device=dev)
             ws["wpart"] = [f(nsm * (32 * 256 + 32)), f(nsm * (32 * 512 + 32)), f(nsm * (32 * 288 + 32))]
             ws["cpart"] = [f(296 * 32), f(296 * 32), f(296 * 32)]   # R2D2_CHANSUM_PART_FLOATS
             ws["side_stream"] = torch.cuda.Stream(device=dev)
@@ -417,7 +418,8 @@ class Learner:
         # builds each receptive field once and multiplies it against both nets' filters
         fused_conv1 = bf16
         if fused_conv1:
-            engine.conv1_fwd_dual_ring(batch["ring"], batch["seq_index"], T + n, w, ws["a1_on"], wt, ws["a1_tg"], n)
+            engine.conv1_fwd_dual_ring(batch["ring"], batch["seq_index"], T + n, w, ws["a1_on"], wt, ws["a1_tg"], n,
+                                       relu_bits_a=ws["relu1_bits"])
         if overlap:
             main, side = torch.cuda.current_stream(), ws["side_stream"]
             ws["ev_fork"].record(main)
@@ -570,7 +572,9 @@ class Learner:
                           P(g.b2), P(ws["wpart"][1], "f32"), st())
 
             beside(conv2_grads, ws["aux2_stream"])
-            _lib.call("r2d2_tc_conv_dgrad2", P(dz2, "f32"), P(w.w2), P(a1_l, "f32"), P(dz1, "f32"), M, st())
+            # ReLU' of the first layer from the bit mask its forward epilogue wrote (learn window)
+            _lib.call("r2d2_tc_conv_dgrad2_masked", P(dz2, "f32"), P(w.w2),
+                      P(ws["relu1_bits"][BI * B:], "i32"), P(dz1, "f32"), M, st())
             engine.conv1_wgrad_ring(batch["ring"], batch["seq_index"], BI, L, dz1, g.w1, ws["wpart"][0], db1=g.b1)
             if overlap_bwd:
                 for st_ in (side, aux, ws["aux2_stream"]) + ((ws["xchg_stream"],) if self.optim.peer is not None else ()):

@@ -257,8 +257,21 @@ def test_conv1_ring_forms_match_slab_forms(cuda_device):
     c1, _, _ = engine.alloc_torso(B * S, "cuda")
     d1, _, _ = engine.alloc_torso(B * (S - s0), "cuda")
     engine.conv1_fwd_dual_u8(slab, S, wa, a1, wb, b1, s0)
-    engine.conv1_fwd_dual_ring(ring, seq, S, wa, c1, wb, d1, s0)
+    bits = torch.zeros(B * S, 400, dtype=torch.int32, device="cuda")
+    engine.conv1_fwd_dual_ring(ring, seq, S, wa, c1, wb, d1, s0, relu_bits_a=bits)
     assert torch.equal(a1, c1) and torch.equal(b1, d1)
+    # ReLU bit mask of net a: bit co of word (frame, pixel) == (a1[frame, co, pixel] > 0)
+    want_bits = ((c1.reshape(B * S, 32, 400) > 0).long() << torch.arange(32, device="cuda").view(1, 32, 1)).sum(1)
+    assert torch.equal(bits.long() & 0xFFFFFFFF, want_bits)
+    # conv2 data gradient with ReLU' from the bit mask == from the activations
+    R = B * S
+    dz2 = torch.randn(R, 32, 9, 9, device="cuda")
+    g_act, g_bits = torch.empty(R, 32, 20, 20, device="cuda"), torch.full((R, 32, 20, 20), float("nan"), device="cuda")
+    _lib.call("r2d2_tc_conv_dgrad2", _lib.ptr(dz2, "f32"), _lib.ptr(wa.w2), _lib.ptr(c1, "f32"), _lib.ptr(g_act, "f32"),
+              R, _lib.stream_ptr())
+    _lib.call("r2d2_tc_conv_dgrad2_masked", _lib.ptr(dz2, "f32"), _lib.ptr(wa.w2), _lib.ptr(bits, "i32"),
+              _lib.ptr(g_bits, "f32"), R, _lib.stream_ptr())
+    assert torch.equal(g_act, g_bits)
     # weight gradient of the first layer over the window [s0, S)
     nt = S - s0
     dz = torch.randn(B * nt, 32, 20, 20, device="cuda")
