@@ -178,8 +178,9 @@ int r2d2_linear_wgrad(const float* dy, const float* x, float* dw, float* db, int
  * every stream on the device.  The split-K partial sums go to an array built into the library
  * (R2D2_STATIC_WGRAD_SCRATCH_BYTES per GPU, resident until exit).  Problems whose scratch
  * need exceeds it are refused with R2D2_EINVAL.  The first call on each device resolves the
- * array's address (do it at set-up, before any stream capture); all calls share the array, so
- * calls that may overlap on the GPU must be serialised by the caller.  Never allocates. */
+ * array's address (do it at set-up, before any stream capture: a first call on a capturing
+ * stream is refused); `stream` must belong to the current device (checked); all calls share the
+ * array, so calls that may overlap on the GPU must be serialised by the caller.  Never allocates. */
 #define R2D2_STATIC_WGRAD_SCRATCH_BYTES (32 << 20)
 int r2d2_linear_wgrad_static(const float* dy, const float* x, float* dw, float* db, int M, int N,
                              int K, void* stream);

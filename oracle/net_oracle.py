@@ -189,12 +189,15 @@ def _train_step(p_online, p_target, batch, burn_in, n_step, gamma, alpha, prio_e
         _, _, _, (th, tc) = qnet_forward(p_target, next_state[:BI], th, tc)
     q_all, hs_seq, cs_seq, (h, c) = qnet_forward(po, state[BI:], h, c)
     q = q_all.gather(1, batch["action"].view(-1, 1))
+    ends = {"h_learn_end": h.detach(), "c_learn_end": c.detach()}
     with torch.no_grad():
-        q_next_online, _, _, _ = qnet_forward(po, next_state[BI:], h.detach(), c.detach())
+        q_next_online, _, _, (hd, cd) = qnet_forward(po, next_state[BI:], h.detach(), c.detach())
+        ends["h_dq_end"], ends["c_dq_end"] = hd, cd
         next_action = torch.argmax(q_next_online, 1).view(-1, 1)
         if next_action_override is not None:
             next_action = next_action_override.view(-1, 1)
-        q_next_target, _, _, _ = qnet_forward(p_target, next_state[BI:], th, tc)
+        q_next_target, _, _, (th, tc) = qnet_forward(p_target, next_state[BI:], th, tc)
+        ends["h_tg_end"], ends["c_tg_end"] = th, tc
         nq = q_next_target.gather(1, next_action)
         r = batch["reward"].view(-1, 1)
         d = batch["done"].view(-1, 1)
@@ -210,7 +213,7 @@ def _train_step(p_online, p_target, batch, burn_in, n_step, gamma, alpha, prio_e
                 q_next_target=q_next_target, next_action=next_action.view(-1),
                 y=y, delta=delta, loss=loss.detach(), priority=prio.astype(np.float32),
                 grads={k: g for k, g in zip(PARAM_KEYS, grads)},
-                hs_seq=hs_seq.detach(), cs_seq=cs_seq.detach())
+                hs_seq=hs_seq.detach(), cs_seq=cs_seq.detach(), **ends)
 
 
 def to_torch_batch(b: dict) -> dict:

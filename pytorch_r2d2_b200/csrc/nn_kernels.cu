@@ -867,7 +867,8 @@ int r2d2_td_target(const float* q_all, const float* q_next_online, const float* 
 //   * The first call on each device looks up the array's device address (the name below is
 //     only a host-side handle, never a pointer a kernel may dereference) with
 //     cudaGetSymbolAddress while that device is current, and caches it.  Make that first
-//     call during set-up, before any stream capture begins.
+//     call during set-up, before any stream capture begins (a first call on a capturing
+//     stream is refused).  `stream` must belong to the current device (checked).
 //   * One array per device, shared by every call and every stream.  It still holds the
 //     previous call's partial sums; that is harmless because each call overwrites every
 //     element it later reads (all splits of all tiles are written, empty splits write
@@ -877,14 +878,26 @@ int r2d2_td_target(const float* q_all, const float* q_next_online, const float* 
 // ------------------------------------------------------------------------------------------
 static __device__ __align__(256) float g_static_wgrad_scratch[R2D2_STATIC_WGRAD_SCRATCH_BYTES / 4];
 
-static int static_wgrad_scratch_ptr(float** out) {
+static int static_wgrad_scratch_ptr(float** out, cudaStream_t st) {
     static std::mutex mu;
     static float* ptrs[64] = {nullptr};
     int dev = -1;
     R2D2_CUDA_OK(cudaGetDevice(&dev));
     R2D2_REQUIRE(dev >= 0 && dev < 64, "linear_wgrad_static: device ordinal %d out of range", dev);
+    // the array that gets used is the CURRENT device's copy: a stream of another device would run
+    // the kernels there with this device's address
+    int sdev = dev;
+    R2D2_CUDA_OK(cudaStreamGetDevice(st, &sdev));
+    R2D2_REQUIRE(sdev == dev, "linear_wgrad_static: the stream belongs to device %d but device %d is "
+                 "current; make the stream's device current before the call", sdev, dev);
     std::lock_guard<std::mutex> lk(mu);
     if (!ptrs[dev]) {
+        // first call on this device: the address look-up is not a capturable operation
+        cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+        R2D2_CUDA_OK(cudaStreamIsCapturing(st, &cap));
+        R2D2_REQUIRE(cap == cudaStreamCaptureStatusNone,
+                     "linear_wgrad_static: the first call on device %d looks up the built-in scratch "
+                     "array and must be made before stream capture begins", dev);
         void* p = nullptr;
         R2D2_CUDA_OK(cudaGetSymbolAddress(&p, g_static_wgrad_scratch));
         R2D2_REQUIRE(p != nullptr, "linear_wgrad_static: cudaGetSymbolAddress returned null");
@@ -911,23 +924,20 @@ int r2d2_linear_wgrad_static(const float* dy, const float* x, float* dw, float* 
     const dim3 grid((N + 127) / 128, (K + 127) / 128, splits);
     if (splits > 1) {
         float* part = nullptr;
-        int rc = static_wgrad_scratch_ptr(&part);
+        int rc = static_wgrad_scratch_ptr(&part, st);
         if (rc) return rc;
         EpiPartial ep{part, K, (long long)N * K};
-        gemm_kernel<128, 128, 8, 8, AL, AL, EpiPartial><<<grid, 256, 0, st>>>(al, bl, ep, N, K, M, kps);
-        R2D2_LAUNCH_OK();
+        R2D2_LAUNCH("linear_wgrad", st,
+                    gemm_kernel<128, 128, 8, 8, AL, AL, EpiPartial><<<grid, 256, 0, st>>>(al, bl, ep, N, K, M, kps));
         const int64_t n = (int64_t)N * K;
-        reduce_partials_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(part, dw, n, splits);
-        R2D2_LAUNCH_OK();
+        R2D2_LAUNCH("reduce_partials_kernel", st,
+                    reduce_partials_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(part, dw, n, splits));
     } else {
         EpiDense ep{dw, K, nullptr, nullptr, 0, 0};
-        gemm_kernel<128, 128, 8, 8, AL, AL, EpiDense><<<grid, 256, 0, st>>>(al, bl, ep, N, K, M, kps);
-        R2D2_LAUNCH_OK();
+        R2D2_LAUNCH("linear_wgrad", st,
+                    gemm_kernel<128, 128, 8, 8, AL, AL, EpiDense><<<grid, 256, 0, st>>>(al, bl, ep, N, K, M, kps));
     }
-    if (db) {
-        colsum_kernel<<<(N + 7) / 8, 1024, 0, st>>>(dy, db, M, N);
-        R2D2_LAUNCH_OK();
-    }
+    if (db) R2D2_LAUNCH("colsum_kernel", st, colsum_kernel<<<(N + 7) / 8, 1024, 0, st>>>(dy, db, M, N));
     return R2D2_OK;
 }
 

@@ -300,19 +300,23 @@ class Learner:
         rm = self.replay_memory
         key = (self.batch_size, self.burn_in_length, self.learning_length, self.bootstrap_steps,
                self.cell_size, self.precision, self.overlap_streams, id(rm))
-        u_host = rm.draw_uniforms(self.batch_size)          # host RNG + pinned buffer, every step
+        rm.configure(self.batch_size, self.bootstrap_steps, self.burn_in_length, self.learning_length)
+        # host RNG -> pinned slot -> device, every step, OUTSIDE the graph: a memcpy node would read
+        # one fixed host address that the host (running many replays ahead) keeps overwriting
+        u_dev = rm._workspace(rm.batch_size, rm.sequence_length, rm.n_step, rm.cell_size)["u"]
+        rm.upload_uniforms(self.batch_size, u_dev)
         rm._wait_ingest()                                    # cross-stream waits stay outside the graph
         if self._graph is None or self._graph_key != key:
             # the captured step always rebuilds the sum-tree first (cheap: M*5 bytes), so that
             # replays are valid whether or not rows were ingested / poked since the last step
             rm._tree_dirty = True
-            self._train_eager(u_host, None, None)            # warm-up: allocates every workspace
+            self._train_eager(u_dev, None, None)             # warm-up: allocates every workspace
             torch.cuda.synchronize()
             rm._tree_dirty = True
             g = torch.cuda.CUDAGraph()
             n0 = _lib.launch_count()
             with torch.cuda.graph(g):
-                loss = self._train_eager(u_host, None, None)
+                loss = self._train_eager(u_dev, None, None)
             self.graph_kernel_nodes = _lib.launch_count() - n0
             self._graph, self._graph_key, self._graph_loss = g, key, loss
             rm._tree_dirty = False
@@ -338,8 +342,7 @@ class Learner:
         B, BI, L, n, H = (self.batch_size, self.burn_in_length, self.learning_length,
                           self.bootstrap_steps, self.cell_size)
         T = BI + L
-        rm.batch_size, rm.n_step = B, n
-        rm.burn_in_length, rm.learning_length, rm.sequence_length = BI, L, T
+        rm.configure(B, n, BI, L)
         ws = self._workspace()
         bf16 = self.precision == "bf16"
         # tensor-core path: the first conv layer (forward and weight gradient) reads the sampled

@@ -95,7 +95,7 @@ class ReplayMemory:
         self._nodes = torch.zeros(total, dtype=torch.float64, device=dev)
         self._tree_dirty = True
         self._ingest_stream, self._pending, self._stage, self._stage_turn = None, [], {}, 0
-        self._u_host = None      # pinned staging for the uniforms
+        self._u_ring, self._u_turn = None, 0   # pinned staging slots for the uniforms
         self._ws = {}            # sample workspaces keyed by shape
         self._touched = None
 
@@ -175,6 +175,10 @@ class ReplayMemory:
                 self._ingest_stream = torch.cuda.Stream(device=self.device)
             st = self._staging(rows, self._stage_turn)
             self._stage_turn ^= 1
+            if any(p[0] is st for p in self._pending):
+                # a third dump of this size before the next draw: the set still holds rows whose
+                # scatter has not been enqueued -- land everything staged so far first
+                self._wait_ingest()
             with torch.cuda.stream(self._ingest_stream):
                 self._ingest_stream.wait_event(st["free"])     # previous scatter out of this set done
                 for k in KEYS:
@@ -306,13 +310,36 @@ class ReplayMemory:
         self._raw("target_hs_cs")[idx, H:] = self._dev(target_cs, torch.float32)
 
     # ------------------------------------------------------------------ sampling
-    def draw_uniforms(self, B):
-        """The B float64 uniforms ``torch.multinomial`` would consume from the global CPU
-        generator (replay_memory.py:227-231), staged through pinned memory."""
-        if self._u_host is None or self._u_host.numel() != B:
-            self._u_host = torch.empty(B, dtype=torch.float64).pin_memory()
-        torch.rand(B, dtype=torch.float64, out=self._u_host)
-        return self._u_host
+    U_SLOTS = 8
+
+    def upload_uniforms(self, B, u_dev):
+        """Draw the B float64 uniforms ``torch.multinomial`` would consume from the global CPU
+        generator (replay_memory.py:227-231) and enqueue their copy into `u_dev` on the current
+        stream.  The host may run many steps ahead of the device (CUDA-graph replays cost it
+        ~30 us against ~2 ms of device work), so the uniforms of every step get a pinned slot
+        of their own out of a ring of U_SLOTS, and a slot is only redrawn once the copy that
+        read it has completed (event recorded behind the copy; the wait only blocks when the
+        host is more than U_SLOTS steps ahead).  Returns the pinned slot (valid until the ring
+        wraps)."""
+        if self._u_ring is None or self._u_ring[0][0].numel() != B:
+            self._u_ring = [[torch.empty(B, dtype=torch.float64).pin_memory(), None]
+                            for _ in range(self.U_SLOTS)]
+        slot = self._u_ring[self._u_turn % self.U_SLOTS]
+        self._u_turn += 1
+        if slot[1] is None:
+            slot[1] = torch.cuda.Event()
+        else:
+            slot[1].synchronize()
+        torch.rand(B, dtype=torch.float64, out=slot[0])
+        u_dev.copy_(slot[0], non_blocking=True)
+        slot[1].record(torch.cuda.current_stream())
+        return slot[0]
+
+    def configure(self, batch_size, n_step, burn_in_length, learning_length):
+        """Set the sampling shape (plain attributes in the reference: replay_memory.py:63-74)."""
+        self.batch_size, self.n_step = batch_size, n_step
+        self.burn_in_length, self.learning_length = burn_in_length, learning_length
+        self.sequence_length = burn_in_length + learning_length
 
     def _workspace(self, B, T, n, H):
         key = (B, T, n, H, self.burn_in_length)
@@ -354,8 +381,11 @@ class ReplayMemory:
         self._wait_ingest()
         if seq_index is None:
             if u is None:
-                u = self.draw_uniforms(B)
-            ws["u"].copy_(u if torch.is_tensor(u) else torch.as_tensor(u), non_blocking=True)
+                self.upload_uniforms(B, ws["u"])
+            elif not (torch.is_tensor(u) and u.is_cuda and u.data_ptr() == ws["u"].data_ptr()):
+                # caller-supplied uniforms (a device tensor that IS the workspace buffer was
+                # uploaded by the caller already: the graphed learner step does that)
+                ws["u"].copy_(u if torch.is_tensor(u) else torch.as_tensor(u), non_blocking=True)
             self._ensure_tree()
             _lib.call("r2d2_tree_sample", _lib.ptr(self._raw("sequence_priority"), "f32"),
                       _lib.ptr(self._raw("is_seq_start"), "u8"), self.memory_size,

@@ -1,0 +1,221 @@
+"""GPU parity at the configuration bench.py measures (BASELINE.json configs[1]): B=64, burn-in 40 +
+learn 40, n=5, LSTM 512 -- one full ``Learner.train()`` against the oracle's ``train_step`` on
+the same sampled batch, in both precisions, with the recurrent state compared at the END of the
+unrolls (120 dependent steps for the online net, 80 for the target net: rounding error compounds
+along the chain, SURVEY.md section 7 hard part 2), the 40-step BPTT gradients of all 18 tensors,
+and the priority bookkeeping after the step.  Plus the persistent recurrence kernels alone at
+(H,B,T) = (512,64,80) forward and (512,64,40) backward, and the async sampling path: K graph
+replays with NO host synchronisation must consume their own uniforms.
+
+Tolerances (max|a-b| / max|b| per tensor): fp32 mode 1e-5, bf16 mode 2e-2 (BASELINE.json
+north_star); sampled indices and everything downstream of the per-step priorities bit-exact.
+Where a tighter bound holds it is asserted (bf16 forward is error-compensated: 2e-4).
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import net_oracle as NO
+from oracle import replay_oracle as RO
+from util import gpu_mem_np, make_oracle_replay, mirror_to_gpu, rel_err
+
+pytestmark = pytest.mark.gpu
+
+FULL = dict(M=1400, H=512, B=64, BI=40, LN=40, NS=5)
+
+
+@pytest.fixture(scope="module")
+def full_case():
+    """Oracle replay + one oracle train step at the full shape (computed once, ~10 s of CPU)."""
+    c = FULL
+    rep, _ = make_oracle_replay(c["M"], c["H"], c["NS"], c["BI"], c["LN"], seed=77, start_stride=7)
+    p = NO.init_params(11, c["H"])
+    pt = NO.init_params(12, c["H"])            # a target net that differs from the online net
+    u = np.random.RandomState(5).rand(c["B"])
+    si = rep.sample_indices(u)
+    g = rep.gather(si)
+    res = NO.train_step(p, pt, NO.to_torch_batch(g["batch"]), burn_in=c["BI"], n_step=c["NS"])
+    # priority bookkeeping after the step (learner.py:102-104)
+    rep2_prio = rep.memory["priority"].copy()
+    rep2_seq = rep.memory["sequence_priority"].copy()
+    rep.update_priority(g["index"][c["BI"]:].reshape(-1), res["priority"])
+    rep.update_sequence_priority(si, True)
+    after = (rep.memory["priority"].copy(), rep.memory["sequence_priority"].copy())
+    rep.memory["priority"][:] = rep2_prio
+    rep.memory["sequence_priority"][:] = rep2_seq
+    return dict(rep=rep, p=p, pt=pt, u=u, si=si, res=res, after=after)
+
+
+def _full_learner(case, precision):
+    from pytorch_r2d2_b200 import Learner
+    c = FULL
+    L = Learner(1, {}, device="cuda:0", cell_size=c["H"], memory_size=c["M"], precision=precision)
+    L.batch_size, L.burn_in_length, L.learning_length, L.bootstrap_steps = c["B"], c["BI"], c["LN"], c["NS"]
+    L.sequence_length = c["BI"] + c["LN"]
+    L.replay_memory = mirror_to_gpu(case["rep"], c["B"])
+    L.net.load_state_dict({k: v.cuda() for k, v in case["p"].items()})
+    L.target_net.load_state_dict({k: v.cuda() for k, v in case["pt"].items()})
+    return L
+
+
+@pytest.mark.parametrize("precision,fwd_tol,grad_tol", [("fp32", 1e-5, 1e-5), ("bf16", 2e-4, 2e-2)])
+def test_full_shape_train_step_vs_oracle(cuda_device, full_case, precision, fwd_tol, grad_tol):
+    c, res = FULL, full_case["res"]
+    T, Ln, B = c["BI"] + c["LN"], c["LN"], c["B"]
+    # 1) free-running double-Q: argmax decisions that differ from the oracle's are reported
+    L = _full_learner(full_case, precision)
+    L.train(u=torch.from_numpy(full_case["u"]))
+    torch.cuda.synchronize()
+    assert np.array_equal(L.last["seq_index"].cpu().numpy(), full_case["si"])        # bit-exact draw
+    flips = int((L.last["next_action"].cpu() != res["next_action"]).sum())
+    print(f"[{precision}] argmax flips {flips} of {Ln * B}")
+    assert flips <= (0 if precision == "fp32" else 2), flips
+    # 2) given the oracle's a*: every tensor
+    L = _full_learner(full_case, precision)
+    L.train(u=torch.from_numpy(full_case["u"]), next_action_override=res["next_action"].cuda())
+    torch.cuda.synchronize()
+    out, ws = L.last, L._ws
+    errs = {k: rel_err(out[k], res[k]) for k in ("q_all", "q_next_online", "q_next_target", "y", "delta")}
+    errs["loss"] = rel_err(out["loss"], res["loss"])
+    # end-of-unroll recurrent state: online after 80 (learn end) and 120 (double-Q end) dependent
+    # steps, target after 80
+    ends = {"h_learn_end": ws["hs_on"][T], "c_learn_end": ws["cs_on"][T],
+            "h_dq_end": ws["hs_dq"][Ln], "c_dq_end": ws["cs_dq"][Ln],
+            "h_tg_end": ws["hs_tg"][T], "c_tg_end": ws["cs_tg"][T]}
+    for k, v in ends.items():
+        errs[k] = rel_err(v, res[k])
+    errs["hs_learn_window"] = rel_err(ws["hs_on"][1 + c["BI"]:].reshape(-1, c["H"]), res["hs_seq"])
+    print(f"[{precision}] forward errors", {k: f"{v:.2e}" for k, v in errs.items()})
+    bad = {k: v for k, v in errs.items() if v >= fwd_tol}
+    assert not bad, bad
+    gerr = {k: rel_err(L.net.layout.view(L.optim.grad, k), res["grads"][k]) for k in NO.PARAM_KEYS}
+    print(f"[{precision}] gradient errors", {k: f"{v:.2e}" for k, v in gerr.items()})
+    bad = {k: v for k, v in gerr.items() if v >= grad_tol}
+    assert not bad, bad
+    # per-step priorities: powf class; the scatter and everything downstream follow the oracle
+    assert rel_err(out["priority"], res["priority"]) < (1e-4 if precision == "fp32" else 2e-3)
+    prio_after, seq_after = full_case["after"]
+    rt = 1e-4 if precision == "fp32" else 5e-3
+    assert np.allclose(gpu_mem_np(L.replay_memory, "priority"), prio_after, rtol=rt, atol=1e-7)
+    assert np.allclose(gpu_mem_np(L.replay_memory, "sequence_priority"), seq_after, rtol=rt, atol=1e-7)
+    # sequence priorities are bit-exact GIVEN the per-step priorities the GPU wrote
+    rep = full_case["rep"]
+    chk = RO.ReplayOracle(rep.M, rep.cell, rep.n_step, rep.burn_in, rep.learn)
+    for k in rep.memory:
+        chk.memory[k][:] = rep.memory[k]
+    chk.index = rep.index
+    chk.memory["priority"][:] = gpu_mem_np(L.replay_memory, "priority")
+    chk.update_sequence_priority(full_case["si"], True)
+    assert np.array_equal(chk.memory["sequence_priority"].view(np.uint32),
+                          gpu_mem_np(L.replay_memory, "sequence_priority").view(np.uint32))
+
+
+def _recurrence_reference(xproj, w_hh, h0, c0):
+    T = xproj.shape[0]
+    h, c, hs, cs, gs = h0, c0, [], [c0], []
+    for t in range(T):
+        gates = xproj[t] + h @ w_hh.T
+        i, f, gg, o = gates.chunk(4, 1)
+        i, f, gg, o = torch.sigmoid(i), torch.sigmoid(f), torch.tanh(gg), torch.sigmoid(o)
+        c = f * c + i * gg
+        h = o * torch.tanh(c)
+        hs.append(h); cs.append(c); gs.append(torch.cat([i, f, gg, o], 1))
+    return hs, cs, gs
+
+
+def test_tc_lstm_fwd_full_unroll(cuda_device):
+    """Persistent tensor-core recurrence at (H,B,T) = (512,64,80) == the fp32 recurrence; the
+    error is taken over the whole history AND at the last step alone (end of the unroll)."""
+    from pytorch_r2d2_b200 import engine
+    H, B, T = 512, 64, 80
+    g = torch.Generator().manual_seed(1)
+    xproj = torch.randn(T, B, 4 * H, generator=g) * 0.5
+    w_hh = (torch.rand(4 * H, H, generator=g) * 2 - 1) / H ** 0.5        # LSTMCell default init range
+    h0, c0 = torch.randn(B, H, generator=g) * 0.1, torch.randn(B, H, generator=g) * 0.1
+    hs, cs, gs = _recurrence_reference(xproj.double(), w_hh.double(), h0.double(), c0.double())
+    xprojT = xproj.reshape(T * B, 4 * H).T.contiguous().cuda()
+    hs_ext = torch.empty(T + 1, B, H, device="cuda"); cs_ext = torch.empty(T + 1, B, H, device="cuda")
+    hs_ext[0], cs_ext[0] = h0.cuda(), c0.cuda()
+    gates_d = torch.empty(T, B, 4 * H, device="cuda")
+    scratch = torch.empty(engine.tc_lstm_scratch_bytes(B, H), dtype=torch.uint8, device="cuda")
+    engine.tc_lstm_seq_fwd(xprojT, 0, w_hh.cuda(), hs_ext, cs_ext, gates_d, T, B, H, scratch)
+    torch.cuda.synchronize()
+    e_all = rel_err(hs_ext[1:], torch.stack(hs))
+    e_end_h, e_end_c = rel_err(hs_ext[T], hs[-1]), rel_err(cs_ext[T], cs[-1])
+    print(f"tc_lstm fwd T=80: all {e_all:.2e}, h_end {e_end_h:.2e}, c_end {e_end_c:.2e}")
+    assert e_all < 1e-5 and e_end_h < 1e-5 and e_end_c < 1e-5
+    assert rel_err(gates_d, torch.stack(gs)) < 1e-5
+
+
+def test_tc_lstm_bwd_full_unroll(cuda_device):
+    """Persistent tensor-core BPTT at (H,B,T) = (512,64,40) vs autograd of the fp32 recurrence:
+    bf16 class (plain bf16 operands in the backward contraction), checked over all steps and at
+    step 0 alone (the far end of the 40-step chain)."""
+    from pytorch_r2d2_b200 import engine
+    H, B, T = 512, 64, 40
+    g = torch.Generator().manual_seed(2)
+    xproj = (torch.randn(T, B, 4 * H, generator=g) * 0.5).requires_grad_(True)
+    w_hh = (torch.rand(4 * H, H, generator=g) * 2 - 1) / H ** 0.5
+    h0, c0 = torch.randn(B, H, generator=g) * 0.1, torch.randn(B, H, generator=g) * 0.1
+    dhs = torch.randn(T, B, H, generator=g)
+    hs, cs, gs = _recurrence_reference(xproj, w_hh, h0, c0)
+    (torch.stack(hs) * dhs).sum().backward()
+    gates_d = torch.stack(gs).detach().cuda().contiguous()
+    cs_ext = torch.stack(cs).detach().cuda().contiguous()
+    dgates = torch.full((T, B, 4 * H), float("nan"), device="cuda")
+    scratch = torch.empty(engine.tc_lstm_bwd_scratch_bytes(B, H), dtype=torch.uint8, device="cuda")
+    dg16 = torch.zeros(T, B, 4 * H, dtype=torch.bfloat16, device="cuda")
+    engine.tc_lstm_seq_bwd(dhs.cuda(), w_hh.cuda(), gates_d, cs_ext, dgates, T, B, H, scratch, dgates16=dg16)
+    torch.cuda.synchronize()
+    e_all, e_first = rel_err(dgates, xproj.grad), rel_err(dgates[0], xproj.grad[0])
+    print(f"tc_lstm bwd T=40: all {e_all:.2e}, step0 {e_first:.2e}")
+    assert e_all < 2e-2 and e_first < 2e-2
+    assert torch.equal(dg16, dgates.bfloat16())
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_graph_replays_without_host_sync_consume_their_own_uniforms(cuda_device, precision):
+    """The async product path (how bench.py drives it): K CUDA-graph replays enqueued back to
+    back with no host synchronisation.  The host is made to run far ahead of the device, and K
+    exceeds the number of pinned uniform slots, so a step that read the host's LATEST uniforms
+    instead of its own would be caught.  Every step's sampled indices must equal (a) those of
+    an eager run that synchronises after every step from the same generator state, and through
+    it (b) ``oracle.sample_indices(u_k)`` for the k-th uniform vector the global generator
+    produced, evaluated on the priorities in force at step k."""
+    from pytorch_r2d2_b200 import Learner, ReplayMemory
+    M, B, BI, LN, NS, H, K = 96, 8, 3, 4, 2, 256, 20
+    assert K > 2 * ReplayMemory.U_SLOTS
+    torch.manual_seed(77)
+    want_u = [torch.rand(B, dtype=torch.float64).numpy() for _ in range(K)]   # what the K draws produce
+    runs = {}
+    for mode in ("eager_sync", "graph_nosync"):
+        rep, _ = make_oracle_replay(M, H, NS, BI, LN, seed=5)
+        torch.manual_seed(3)
+        L = Learner(1, {}, device="cuda:0", cell_size=H, memory_size=M, precision=precision)
+        L.batch_size, L.burn_in_length, L.learning_length, L.bootstrap_steps = B, BI, LN, NS
+        L.replay_memory = mirror_to_gpu(rep, B)
+        L.use_cuda_graph = mode == "graph_nosync"
+        hist = torch.zeros(K, B, dtype=torch.int64, device="cuda")
+        torch.manual_seed(77)
+        for k in range(K):
+            if mode == "eager_sync":
+                # tier (i) of the sampling contract on the priorities in
+                # force now: the 32-ary f64 tree restated on the CPU, same uniforms
+                tree = RO.SumTree(RO.masked_leaves(gpu_mem_np(L.replay_memory, "sequence_priority"),
+                                                   gpu_mem_np(L.replay_memory, "is_seq_start")))
+                want_si = tree.sample(want_u[k])
+            L.train()
+            hist[k].copy_(L.last["seq_index"])            # device-side copy, no host sync
+            if mode == "eager_sync":
+                torch.cuda.synchronize()
+                assert np.array_equal(hist[k].cpu().numpy(), want_si), k
+            elif k == 0:
+                torch.cuda._sleep(200_000_000)            # ~0.1 s: the host is now far ahead
+        torch.cuda.synchronize()
+        runs[mode] = (hist.cpu(), L.net.flat_parameters().clone(),
+                      gpu_mem_np(L.replay_memory, "sequence_priority"))
+    a, b = runs["eager_sync"], runs["graph_nosync"]
+    assert torch.equal(a[0], b[0]), (a[0] != b[0]).any(1).nonzero().reshape(-1).tolist()
+    assert len({tuple(r.tolist()) for r in a[0]}) > K // 2        # the draws do differ step to step
+    assert torch.equal(a[1], b[1])
+    assert np.array_equal(a[2], b[2])
