@@ -45,12 +45,28 @@ def init_params(seed: int, cell: int = 256) -> dict:
     return p
 
 
-def torso(p: dict, frames: torch.Tensor) -> torch.Tensor:
-    """[N,4,84,84] f32 in [0,1] -> [N,1568], channel-major flatten (model.py:13-21,46)."""
-    x = F.relu(F.conv2d(frames, p["vis_layers.0.weight"], p["vis_layers.0.bias"], stride=4))
-    x = F.relu(F.conv2d(x, p["vis_layers.2.weight"], p["vis_layers.2.bias"], stride=2))
-    x = F.relu(F.conv2d(x, p["vis_layers.4.weight"], p["vis_layers.4.bias"], stride=1))
+def torso(p: dict, frames: torch.Tensor, masks=None) -> torch.Tensor:
+    """[N,4,84,84] f32 in [0,1] -> [N,1568], channel-major flatten (model.py:13-21,46).
+
+    masks = (m1, m2, m3): 0/1 tensors shaped like the three conv outputs.  When given, each
+    ReLU is evaluated as ``z * m`` -- the network with its activation pattern pinned.  Tests use
+    it to compare gradients across two fp32 implementations whose pre-activations straddle a
+    ReLU kink at a handful of positions (|z| ~ 1e-8): with the pattern of the implementation
+    under test pinned, the remaining difference is pure rounding."""
+    act = (lambda z, i: z * masks[i]) if masks is not None else (lambda z, i: F.relu(z))
+    x = act(F.conv2d(frames, p["vis_layers.0.weight"], p["vis_layers.0.bias"], stride=4), 0)
+    x = act(F.conv2d(x, p["vis_layers.2.weight"], p["vis_layers.2.bias"], stride=2), 1)
+    x = act(F.conv2d(x, p["vis_layers.4.weight"], p["vis_layers.4.bias"], stride=1), 2)
     return x.reshape(x.shape[0], FEAT)
+
+
+def torso_preacts(p: dict, frames: torch.Tensor):
+    """(z1, z2, z3): the three conv pre-activations (no grad)."""
+    with torch.no_grad():
+        z1 = F.conv2d(frames, p["vis_layers.0.weight"], p["vis_layers.0.bias"], stride=4)
+        z2 = F.conv2d(F.relu(z1), p["vis_layers.2.weight"], p["vis_layers.2.bias"], stride=2)
+        z3 = F.conv2d(F.relu(z2), p["vis_layers.4.weight"], p["vis_layers.4.bias"], stride=1)
+    return z1, z2, z3
 
 
 def torso_kink_margin(p: dict, frames: torch.Tensor) -> float:
@@ -110,7 +126,7 @@ def head(p: dict, hs: torch.Tensor) -> torch.Tensor:
     return val + adv - adv.mean(1, keepdim=True)
 
 
-def qnet_forward(p: dict, state: torch.Tensor, h, c):
+def qnet_forward(p: dict, state: torch.Tensor, h, c, masks=None):
     """``QNet.forward`` with the module-held hidden state made explicit (model.py:38-72).
 
     state: [T,B,4,84,84] or [B,4,84,84] f32.  h,c: [B,H] or None (-> zeros, model.py:48-50).
@@ -121,7 +137,7 @@ def qnet_forward(p: dict, state: torch.Tensor, h, c):
     else:
         T, B = 1, state.shape[0]
     H = p["lstm.weight_hh"].shape[1]
-    feats = torso(p, state.reshape(-1, 4, 84, 84)).reshape(T, B, FEAT)
+    feats = torso(p, state.reshape(-1, 4, 84, 84), masks).reshape(T, B, FEAT)
     if h is None:
         h = torch.zeros(B, H)
         c = torch.zeros(B, H)
@@ -159,7 +175,8 @@ def rmsprop_centered(param, grad, square_avg, grad_avg, lr=0.00025 / 4.0, alpha=
 
 def train_step(p_online: dict, p_target: dict, batch: dict, *, burn_in: int, n_step: int,
                gamma: float = 0.99, alpha: float = 0.6, prio_eps: float = 1e-6,
-               rescale: bool = False, next_action_override=None, tc_emulation=()) -> dict:
+               rescale: bool = False, next_action_override=None, tc_emulation=(),
+               learn_masks=None) -> dict:
     """``Learner.train`` from the sampled batch to the per-step priorities
     (learner.py:71-102), without the optimiser step (see ``rmsprop_centered``).
 
@@ -171,14 +188,14 @@ def train_step(p_online: dict, p_target: dict, batch: dict, *, burn_in: int, n_s
         _TC[k] = k in tc_emulation
     try:
         return _train_step(p_online, p_target, batch, burn_in, n_step, gamma, alpha, prio_eps,
-                           rescale, next_action_override)
+                           rescale, next_action_override, learn_masks)
     finally:
         for k in _TC:
             _TC[k] = False
 
 
 def _train_step(p_online, p_target, batch, burn_in, n_step, gamma, alpha, prio_eps, rescale,
-                next_action_override):
+                next_action_override, learn_masks=None):
     po = {k: v.detach().clone().requires_grad_(True) for k, v in p_online.items()}
     BI = burn_in
     state, next_state = batch["state"], batch["next_state"]
@@ -187,7 +204,8 @@ def _train_step(p_online, p_target, batch, burn_in, n_step, gamma, alpha, prio_e
     with torch.no_grad():
         _, _, _, (h, c) = qnet_forward(po, state[:BI], h, c)
         _, _, _, (th, tc) = qnet_forward(p_target, next_state[:BI], th, tc)
-    q_all, hs_seq, cs_seq, (h, c) = qnet_forward(po, state[BI:], h, c)
+    # learn_masks: ReLU pattern of the grad-enabled pass pinned (see torso)
+    q_all, hs_seq, cs_seq, (h, c) = qnet_forward(po, state[BI:], h, c, learn_masks)
     q = q_all.gather(1, batch["action"].view(-1, 1))
     ends = {"h_learn_end": h.detach(), "c_learn_end": c.detach()}
     with torch.no_grad():

@@ -34,7 +34,8 @@ def full_case():
     u = np.random.RandomState(5).rand(c["B"])
     si = rep.sample_indices(u)
     g = rep.gather(si)
-    res = NO.train_step(p, pt, NO.to_torch_batch(g["batch"]), burn_in=c["BI"], n_step=c["NS"])
+    tb = NO.to_torch_batch(g["batch"])
+    res = NO.train_step(p, pt, tb, burn_in=c["BI"], n_step=c["NS"])
     # priority bookkeeping after the step (learner.py:102-104)
     rep2_prio = rep.memory["priority"].copy()
     rep2_seq = rep.memory["sequence_priority"].copy()
@@ -43,7 +44,7 @@ def full_case():
     after = (rep.memory["priority"].copy(), rep.memory["sequence_priority"].copy())
     rep.memory["priority"][:] = rep2_prio
     rep.memory["sequence_priority"][:] = rep2_seq
-    return dict(rep=rep, p=p, pt=pt, u=u, si=si, res=res, after=after)
+    return dict(rep=rep, p=p, pt=pt, u=u, si=si, res=res, after=after, tb=tb)
 
 
 def _full_learner(case, precision):
@@ -90,7 +91,36 @@ def test_full_shape_train_step_vs_oracle(cuda_device, full_case, precision, fwd_
     assert not bad, bad
     gerr = {k: rel_err(L.net.layout.view(L.optim.grad, k), res["grads"][k]) for k in NO.PARAM_KEYS}
     print(f"[{precision}] gradient errors", {k: f"{v:.2e}" for k, v in gerr.items()})
-    bad = {k: v for k, v in gerr.items() if v >= grad_tol}
+    # ReLU' is discontinuous.  The learn window holds 43 M conv pre-activations; a few of them sit
+    # within rounding distance of 0 (|z| ~ 1e-8) and legitimately come out on the other side of
+    # the kink in another fp32 implementation, which moves the conv gradients (heavily cancelling
+    # sums) by ~1e-3.  So: (a) every ReLU decision that differs from the oracle's must be such a
+    # near-zero pre-activation, (b) against the oracle evaluated with the GPU's activation
+    # pattern pinned, every gradient is inside the tolerance of the class.
+    BI, H = c["BI"], c["H"]
+    lo, hi = BI * B, T * B
+    masks_gpu = [(ws[k][lo:hi] > 0).cpu() for k in ("a1_on", "a2_on", "feat_on")]
+    masks_gpu[2] = masks_gpu[2].reshape(-1, 32, 7, 7)
+    zs = NO.torso_preacts(full_case["p"], full_case["tb"]["state"][BI:].reshape(-1, 4, 84, 84))
+    n_flip, worst_z = 0, 0.0
+    for m, z in zip(masks_gpu, zs):
+        diff = m != (z > 0)
+        n_flip += int(diff.sum())
+        if diff.any():
+            worst_z = max(worst_z, float(z[diff].abs().max()))
+    print(f"[{precision}] ReLU decisions differing from the oracle: {n_flip} of "
+          f"{sum(z.numel() for z in zs)}, largest |z| among them {worst_z:.2e}")
+    assert n_flip < 200 and worst_z < (1e-5 if precision == "fp32" else 1e-4), (n_flip, worst_z)
+    res_m = NO.train_step(full_case["p"], full_case["pt"], full_case["tb"], burn_in=BI, n_step=c["NS"],
+                          next_action_override=res["next_action"],
+                          learn_masks=[m.float() for m in masks_gpu])
+    gerr_m = {k: rel_err(L.net.layout.view(L.optim.grad, k), res_m["grads"][k]) for k in NO.PARAM_KEYS}
+    print(f"[{precision}] gradient errors, activation pattern pinned", {k: f"{v:.2e}" for k, v in gerr_m.items()})
+    bad = {k: v for k, v in gerr_m.items() if v >= grad_tol}
+    assert not bad, bad
+    # un-pinned: everything above the torso is unaffected by the kinks and stays in the class; the
+    # conv tensors stay within the bf16 class even in fp32 mode
+    bad = {k: v for k, v in gerr.items() if v >= (grad_tol if not k.startswith("vis_layers") else 2e-2)}
     assert not bad, bad
     # per-step priorities: powf class; the scatter and everything downstream follow the oracle
     assert rel_err(out["priority"], res["priority"]) < (1e-4 if precision == "fp32" else 2e-3)

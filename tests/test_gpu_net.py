@@ -12,6 +12,17 @@ from util import gpu_mem_np, make_oracle_replay, mirror_to_gpu, rel_err
 
 pytestmark = pytest.mark.gpu
 TOL = 1e-5
+# stored priorities after 100 optimiser steps, max |gpu - oracle| / (|oracle| + 1e-3)
+# (measured: fp32 0.077, bf16 0.29 -- (|delta|+eps)^0.6 of small TD errors is ill-conditioned)
+PRIO_DRIFT = {"fp32": 0.1, "bf16": 0.4}
+# median / max over a tensor of |w_gpu - w_oracle| / max|w| after 100 optimiser steps, and the
+# Q-values of the two final networks on a probe batch.  Measured: fp32 1.8e-3 / 0.077 / 9.5e-3,
+# bf16 5.2e-3 / 0.13 / 6.2e-2: per-step gradients are within 2e-2 (4e-3 measured) but centered
+# RMSprop divides by sqrt(v - m^2), which is ~0.22 |g| whatever the size of g, so every weight
+# moves ~lr/0.22 per step in the direction of a gradient SIGN that rounding can flip.
+MEDIAN_DRIFT = {"fp32": 2.5e-3, "bf16": 8e-3}
+MAX_DRIFT = {"fp32": 0.1, "bf16": 0.2}
+Q_DRIFT = {"fp32": 2e-2, "bf16": 1e-1}
 
 
 @pytest.fixture(scope="module")
@@ -220,10 +231,10 @@ def test_qnet_autograd_vs_oracle(cuda_device):
         assert rel_err(got[k].grad, pr[k].grad) < TOL, k
 
 
-def _learner(H, M, B, BI, LN, NS, seed=0):
+def _learner(H, M, B, BI, LN, NS, seed=0, precision="fp32"):
     from pytorch_r2d2_b200 import Learner
     torch.manual_seed(seed)
-    L = Learner(1, {}, device="cuda:0", cell_size=H, memory_size=M)
+    L = Learner(1, {}, device="cuda:0", cell_size=H, memory_size=M, precision=precision)
     L.batch_size, L.burn_in_length, L.learning_length, L.bootstrap_steps = B, BI, LN, NS
     L.sequence_length = BI + LN
     return L
@@ -422,14 +433,15 @@ def test_batched_actor_inference_vs_oracle(cuda_device, precision, tol):
     assert prio.shape == (N,) and np.all(prio > 0)
 
 
-def test_hundred_step_drift_vs_oracle(cuda_device):
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_hundred_step_drift_vs_oracle(cuda_device, precision):
     """100 consecutive learner steps (sample -> train -> RMSprop -> priority update)
     against the oracle doing the same 100 steps on the CPU.  Both sides draw from the same
     uniforms; the GPU is fed the oracle's indices (one ulp of priority difference must not fork
     the two trajectories) and its own tree must agree with them on the way."""
-    M, B, BI, LN, NS, H = 64, 4, 2, 3, 2, 256
+    M, B, BI, LN, NS, H = 64, (4 if precision == "fp32" else 8), 2, 3, 2, 256   # bf16: L*B % 8 == 0
     rep, _ = make_oracle_replay(M, H, NS, BI, LN, seed=33)
-    L = _learner(H, M, B, BI, LN, NS, seed=3)
+    L = _learner(H, M, B, BI, LN, NS, seed=3, precision=precision)
     L.replay_memory = mirror_to_gpu(rep, B)
     p = {k: v.cpu().clone() for k, v in L.net.state_dict().items()}
     pt = {k: v.cpu().clone() for k, v in L.target_net.state_dict().items()}
@@ -459,12 +471,17 @@ def test_hundred_step_drift_vs_oracle(cuda_device):
     for k in NO.PARAM_KEYS:
         d = (sd[k].cpu() - p[k]).abs().reshape(-1) / float(p[k].abs().max())
         stats[k] = (float(d.median()), float(d.quantile(0.99)) if d.numel() > 1 else float(d.max()), float(d.max()))
-        assert stats[k][0] < 2e-3, (k, stats[k])
-        assert stats[k][2] < 0.1, (k, stats[k])
     probe = NO.to_torch_batch(rep.gather(rep.sample_indices(np.random.RandomState(9).rand(B)))["batch"])
     want = NO.train_step(p, pt, probe, burn_in=BI, n_step=NS)
     mine = NO.train_step({k: v.cpu() for k, v in sd.items()}, pt, probe, burn_in=BI, n_step=NS)
     qerr = rel_err(mine["q_all"], want["q_all"])
-    assert qerr < 2e-2, (qerr, stats)
-    assert np.allclose(gpu_mem_np(L.replay_memory, "priority"), rep.memory["priority"], rtol=0.2, atol=1e-3), stats
+    gp, op = gpu_mem_np(L.replay_memory, "priority"), rep.memory["priority"]
+    pdev = float(np.max(np.abs(gp - op) / (np.abs(op) + 1e-3)))
+    print(f"[{precision}] drift after 100 steps: q {qerr:.2e}, priority {pdev:.2e}, tree agreement {agree}/100, "
+          f"worst tensor median {max(v[0] for v in stats.values()):.2e} max {max(v[2] for v in stats.values()):.2e}")
+    for k in NO.PARAM_KEYS:
+        assert stats[k][0] < MEDIAN_DRIFT[precision], (k, stats[k])
+        assert stats[k][2] < MAX_DRIFT[precision], (k, stats[k])
+    assert qerr < Q_DRIFT[precision], (qerr, stats)
+    assert pdev < PRIO_DRIFT[precision], (pdev, stats)
     assert agree >= 95, agree       # the GPU tree draws the same sequences on (almost) every step

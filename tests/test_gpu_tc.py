@@ -209,9 +209,11 @@ def test_tc_lstm_bwd_vs_autograd(cuda_device, H, B, T):
 
 
 def test_tc_conv_backward_vs_fp32(cuda_device):
-    """Tensor-core conv backward (data + weight gradients in plain bf16) vs the fp32 kernels on
-    the same inputs: 1e-2 relative to max|grad| (bf16 operand rounding)."""
+    """Tensor-core conv backward (data + weight gradients in plain bf16) vs torch autograd of the
+    fp32 convs AND vs the fp32 kernels on the same inputs: 1e-2 relative to max|grad| (bf16
+    operand rounding)."""
     import numpy as np
+    from oracle import net_oracle as NO
     from pytorch_r2d2_b200 import QNet, engine
     torch.manual_seed(4)
     net = QNet("cuda:0", 256)
@@ -231,6 +233,15 @@ def test_tc_conv_backward_vs_fp32(cuda_device):
         fn(slab, s0, nt, a1, a2, feat, dfeat.clone(), w, gw, scratch)
         outs.append(gw)
     ref, tc = outs
+    # directly against autograd (the oracle's torso on the same frames)
+    p = {k: v.cpu().clone().requires_grad_(True) for k, v in net.state_dict().items()}
+    frames = slab[:, s0:s0 + nt].permute(1, 0, 2, 3, 4).reshape(R, 4, 84, 84).cpu().float() / 255.
+    (NO.torso(p, frames) * dfeat.cpu()).sum().backward()
+    for name, key in (("w1", "vis_layers.0.weight"), ("b1", "vis_layers.0.bias"), ("w2", "vis_layers.2.weight"),
+                      ("b2", "vis_layers.2.bias"), ("w3", "vis_layers.4.weight"), ("b3", "vis_layers.4.bias")):
+        err = rel_err(getattr(tc, name), p[key].grad)
+        assert err < 1e-2, (name, err)
+        assert rel_err(getattr(ref, name), p[key].grad) < 1e-5, name
     for name in ("w1", "w2", "w3"):
         err = rel_err(getattr(tc, name), getattr(ref, name))
         assert err < 1e-2, (name, err)
