@@ -26,6 +26,16 @@ for r in rows[2:]:
             a[2] += float(r[it])
             break
 res = {k: {"launches": n, "dram_bytes_per_launch": b / n, "avg_duration_" + units[it]: t / n} for k, (n, b, t) in agg.items()}
-res["_source"] = sys.argv[1] + " (ncu --set full --clock-control none, one learner step, B=64 T=40+40 n=5 H=512)"
+# provenance: bench.py reports `roofline.traffic` from this file only while csrc/ is unchanged
+import os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from bench import csrc_sha16
+try:
+    commit = subprocess.run(["git", "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip()
+except OSError:
+    commit = ""
+res["_meta"] = {"csrc_sha16": csrc_sha16(), "commit": commit or (sys.argv[3] if len(sys.argv) > 3 else None),
+                "source": sys.argv[1] + " (ncu --set full --clock-control none, one learner step, "
+                          "B=64 T=40+40 n=5 H=512)"}
 json.dump(res, open(sys.argv[2], "w"), indent=1)
 print(json.dumps(res, indent=1))
