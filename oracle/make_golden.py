@@ -328,13 +328,59 @@ def make_network(ref_replay, ref_model, ref_learner):
     np.savez_compressed(os.path.join(GOLD, "network.npz"), **out)
 
 
+# ------------------------------------------------------------------ hand-off dump golden
+class _NoLock:
+    """Stand-in for fasteners.InterProcessLock (not installed): single process, always free."""
+
+    def __init__(self, path):
+        self.path = path
+
+    def acquire(self, blocking=True):
+        return True
+
+    def release(self):
+        pass
+
+
+def make_dump(ref_replay):
+    """A dump file written by the REFERENCE's own ``ReplayMemory.save`` (fit + torch.save,
+    replay_memory.py:121-152), rows appended through its ``add`` (float frames -> u8
+    truncation): the wire format the learner's ``load`` must read."""
+    sys.modules["fasteners"].InterProcessLock = _NoLock
+    rows, H = 7, 256
+    r = ref_replay.ReplayMemory(16, 4, 2)
+    rng = np.random.RandomState(31)
+    for i in range(rows):
+        frame = rng.randint(0, 256, (4, 84, 84)).astype(np.float32) / np.float32(255)
+        r.add(frame, (rng.randn(1, H) * 0.1).astype(np.float32), (rng.randn(1, H) * 0.1).astype(np.float32),
+              (rng.randn(1, H) * 0.1).astype(np.float32), (rng.randn(1, H) * 0.1).astype(np.float32),
+              int(rng.randint(6)), float(rng.randn()), bool(i == 4), 1, float(rng.rand() + 0.01))
+    r.burn_in_length, r.learning_length, r.sequence_length = 2, 2, 4
+    starts = np.array([0, 2, 3])
+    r.update_sequence_priority(starts)
+    r.memory["is_seq_start"][starts] = 1
+    path = os.path.join(GOLD, "memory7.pt")
+    if os.path.exists(path):
+        os.remove(path)
+    r.save(GOLD, 7)
+    d = torch.load(path, weights_only=False)
+    assert d["state"].shape == (rows, 4, 84, 84) and d["state"].dtype == np.uint8
+    print("[dump] reference-written hand-off file:", {k: (v.dtype.name, v.shape) for k, v in d.items()})
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     ref_replay, ref_model, ref_learner = import_reference()
     torch.set_num_threads(8)
-    make_priority(ref_replay)
-    make_sampling(ref_replay)
-    make_network(ref_replay, ref_model, ref_learner)
+    only = set(sys.argv[1:])
+    if not only or "priority" in only:
+        make_priority(ref_replay)
+    if not only or "sampling" in only:
+        make_sampling(ref_replay)
+    if not only or "network" in only:
+        make_network(ref_replay, ref_model, ref_learner)
+    if not only or "dump" in only:
+        make_dump(ref_replay)
     print("golden fixtures written to", GOLD)
 
 

@@ -15,7 +15,6 @@ the data-parallel gradient allreduce.
 from __future__ import annotations
 
 import os
-from copy import deepcopy
 
 import numpy as np
 import torch
@@ -166,8 +165,11 @@ class Learner:
         self.last = None  # tensors of the last step (q, y, delta, loss, ...) for inspection
 
     # ------------------------------------------------------------------ control loop
-    def run(self):
-        while True:
+    def run(self, max_steps=None):
+        """learner.py:53-66: train once the replay holds more than ``initial_exploration``
+        transitions, ingest actor dumps until then.  ``max_steps`` (not in the reference, which
+        loops forever) returns after that many training steps."""
+        while max_steps is None or self.n_epochs < max_steps:
             if self.replay_memory.size > self.initial_exploration:
                 self.train()
                 self.n_epochs += 1
@@ -178,6 +180,7 @@ class Learner:
                 self._ingest()
 
     def _ingest(self):
+        """Pull every actor's waiting dump into the ring (learner.py:62-66,111-116)."""
         for i in range(self.n_actors):
             try:
                 self.replay_memory.load(self.memory_path, i)
@@ -185,6 +188,8 @@ class Learner:
                 pass
 
     def interval(self):
+        """learner.py:106-120: target sync every 1000 steps, weight publish every 100, replay
+        ingest every 20, weight file every 10000."""
         if self.n_epochs % self.target_update_interval == 0:
             self.sync_target()
         if self.n_epochs % self.net_save_interval == 0:
@@ -193,15 +198,80 @@ class Learner:
             self._ingest()
         if self.n_epochs % 10000 == 0:
             os.makedirs("save", exist_ok=True)
-            torch.save(self.net.cpu().state_dict(), "save/" + str(self.n_epochs) + "_save.pt")
+            torch.save(self.net.cpu_state_dict(), "save/" + str(self.n_epochs) + "_save.pt")
 
     def sync_target(self):
         """target_net.load_state_dict(net.state_dict()) (learner.py:108) = one D2D copy."""
         self.target_net.flat_parameters().copy_(self.net.flat_parameters())
 
     def save_model(self):
-        self.shared_dict["net_state"] = self.net.cpu().state_dict()
-        self.shared_dict["target_net_state"] = self.target_net.cpu().state_dict()
+        """Publish both nets to the actors as CPU state dicts (learner.py:122-124)."""
+        self.shared_dict["net_state"] = self.net.cpu_state_dict()
+        self.shared_dict["target_net_state"] = self.target_net.cpu_state_dict()
+
+    # ------------------------------------------------------------------ checkpoint / resume
+    def _ckpt_path(self, path):
+        world = parallel.active_world(self.process_group)
+        if world == 1:
+            return path
+        import torch.distributed as dist
+        return f"{path}.rank{dist.get_rank(self.process_group)}"
+
+    def save_checkpoint(self, path, include_replay=True):
+        """Everything a resumed run needs to continue bit-identically (the reference only ever
+        saves the online weights, learner.py:117-120): both nets, the centered-RMSprop state
+        (this rank's shards under the peer exchange), the step counter, the host RNG states the
+        sampler draws from, and -- with `include_replay` -- the replay shard (its ten arrays up
+        to ``size`` plus the write counter; the sum-tree is rebuilt from them on load).  One file
+        per rank (``path.rank<r>``) when data-parallel: every rank owns a replay shard."""
+        rm = self.replay_memory
+        rm._wait_ingest()
+        ck = {"format": 1, "n_epochs": self.n_epochs, "cell_size": self.cell_size,
+              "net": self.net.cpu_state_dict(), "target_net": self.target_net.cpu_state_dict(),
+              "optim": {k: ([t.cpu() for t in v] if isinstance(v, list) else v.cpu() if torch.is_tensor(v) else v)
+                        for k, v in self.optim.state_dict().items()},
+              "shape": {"batch_size": self.batch_size, "burn_in_length": self.burn_in_length,
+                        "learning_length": self.learning_length, "bootstrap_steps": self.bootstrap_steps},
+              "torch_rng": torch.get_rng_state(), "numpy_rng": np.random.get_state()}
+        if include_replay:
+            ck["replay"] = {"index": rm.index, "memory_size": rm.memory_size, "memory": rm.dump()}
+        path = self._ckpt_path(path)
+        tmp = path + ".tmp"
+        torch.save(ck, tmp)
+        os.replace(tmp, path)
+        return path
+
+    def load_checkpoint(self, path):
+        """Inverse of ``save_checkpoint`` into an already constructed learner of the same width
+        (and, under the peer exchange, the same world size)."""
+        ck = torch.load(self._ckpt_path(path), weights_only=False)
+        if ck.get("format") != 1 or ck["cell_size"] != self.cell_size:
+            raise ValueError("checkpoint does not match this learner (format / cell_size)")
+        dev = self.net.flat_parameters().device
+        self.net.load_state_dict({k: v.to(dev) for k, v in ck["net"].items()})
+        self.target_net.load_state_dict({k: v.to(dev) for k, v in ck["target_net"].items()})
+        od = ck["optim"]
+        if self.optim.peer is not None and (od.get("world") != self.optim.peer.world or od.get("rank") != self.optim.peer.rank):
+            raise ValueError("sharded optimiser state was saved by another rank / world size")
+        self.optim.load_state_dict({k: ([t.to(dev) for t in v] if isinstance(v, list) else v.to(dev) if torch.is_tensor(v) else v)
+                                    for k, v in od.items()})
+        self.n_epochs = ck["n_epochs"]
+        for k, v in ck["shape"].items():
+            setattr(self, k, v)
+        self.sequence_length = self.burn_in_length + self.learning_length
+        torch.set_rng_state(ck["torch_rng"])
+        np.random.set_state(ck["numpy_rng"])
+        if "replay" in ck:
+            rm, rp = self.replay_memory, ck["replay"]
+            if rp["memory_size"] != rm.memory_size:
+                raise ValueError("replay shard was saved with another memory_size")
+            rm._wait_ingest()
+            n = rp["memory"]["state"].shape[0]
+            for k, v in rp["memory"].items():
+                rm._raw(k)[:n].copy_(torch.from_numpy(v).to(dev).reshape(rm._raw(k)[:n].shape))
+            rm.index = rp["index"]
+            rm._tree_dirty = True
+        self._graph = None
 
     # ------------------------------------------------------------------ workspace
     def _workspace(self):

@@ -261,13 +261,13 @@ class QNet(nn.Module):
                 md[parts[1]].register_parameter(parts[2], p)
         return new
 
-    def cpu(self):
-        """``deepcopy(net).cpu().state_dict()`` is how the reference publishes weights
-        (learner.py:119,123-124): return a plain holder with CPU copies."""
-        holder = _Group()
-        sd = {k: v.detach().cpu() for k, v in self.state_dict().items()}
-        holder.state_dict = lambda *a, **kw: sd  # type: ignore[assignment]
-        return holder
+    def cpu_state_dict(self):
+        """CPU copy of ``state_dict()``: what the reference publishes to its actors and saves
+        (``deepcopy(net).cpu().state_dict()``, learner.py:119,123-124) without cloning the
+        network on the device first.  The reference's own idiom keeps working as it is:
+        ``deepcopy(net)`` is a detached device copy and ``nn.Module.cpu()`` on that copy moves
+        its parameters to the host (such a copy can be read, not run: there is no CPU path)."""
+        return {k: v.detach().cpu() for k, v in self.state_dict().items()}
 
     # ------------------------------------------------------------------ reference API
     def reset(self):

@@ -232,31 +232,100 @@ class ReplayMemory:
     push = add
 
     def fit(self):
-        """Reference truncates the arrays to ``size`` before a dump (replay_memory.py:121-123);
-        the device ring keeps its capacity, ``dump()`` applies the truncation."""
+        """The reference truncates its arrays to ``size`` before a dump (replay_memory.py:121-123).
+        The device ring keeps its capacity; ``dump()`` applies the truncation to what it returns."""
         return None
 
     def dump(self):
+        """``{key: ndarray[:size]}`` with the reference's ten keys, dtypes and shapes: the payload
+        of the file hand-off and of ``extend``."""
         n = self.size
+        self._wait_ingest()
         return {k: self._raw(k)[:n].cpu().numpy() for k in KEYS}
 
-    def save(self, path, actor_id):
-        """File hand-off wire format of replay_memory.py:125-152: ``torch.save`` of
-        ``{key: ndarray[:size]}``, merged with an existing dump."""
+    @staticmethod
+    def _lock_file(path, timeout):
+        """The reference guards each dump file with ``fasteners.InterProcessLock(path)``
+        (replay_memory.py:127,157): an fcntl lock on the DATA FILE itself, opened 'a+' (which
+        creates it empty -- hence the size checks), polled without blocking.  Same protocol here
+        (``fcntl.lockf``, what fasteners uses on POSIX), so this learner and the reference's
+        actors can share a directory.  Returns the locked file object, or None on time-out.
+        A file that was removed and recreated while we waited is a different inode: retry."""
+        import fcntl
+        import time
+        deadline = time.monotonic() + timeout
+        while True:
+            f = open(path, "a+b")
+            try:
+                fcntl.lockf(f, fcntl.LOCK_EX | fcntl.LOCK_NB)
+                try:
+                    if os.fstat(f.fileno()).st_ino == os.stat(path).st_ino:
+                        return f
+                except FileNotFoundError:
+                    pass
+                fcntl.lockf(f, fcntl.LOCK_UN)
+            except OSError:
+                pass
+            f.close()
+            if time.monotonic() >= deadline:
+                return None
+            time.sleep(0.05)
+
+    def save(self, path, actor_id, timeout=30.0):
+        """File hand-off, writer side (replay_memory.py:125-152): under the per-file lock, merge
+        with a dump that is still waiting there (own rows first, then the waiting ones, as
+        ``extend`` + ``fit`` give), and write ``torch.save({key: ndarray[:size]})``.  The bytes are
+        serialised in memory first and written in place under the lock, so a reader that honours
+        the lock never sees a torn file.  An unreadable waiting dump is replaced, not merged."""
+        import io
+        os.makedirs(path, exist_ok=True)
         path = os.path.join(path, f"memory{actor_id}.pt")
         new = self.dump()
-        if os.path.isfile(path) and os.path.getsize(path) > 0:
-            old = torch.load(path, weights_only=False)
-            new = {k: np.concatenate([new[k], old[k]]) for k in KEYS}
-        torch.save(new, path)
+        f = self._lock_file(path, timeout)
+        if f is None:
+            raise TimeoutError(f"could not lock {path}")
+        try:
+            f.seek(0)
+            raw = f.read()
+            if raw:
+                try:
+                    old = torch.load(io.BytesIO(raw), weights_only=False)
+                    new = {k: np.concatenate([new[k], old[k]]) for k in KEYS}
+                except Exception:      # noqa: BLE001 -- a corrupt leftover must not block the hand-off
+                    pass
+            buf = io.BytesIO()
+            torch.save(new, buf)
+            f.seek(0)
+            f.truncate()
+            f.write(buf.getvalue())
+            f.flush()
+            os.fsync(f.fileno())
+        finally:
+            f.close()                  # closing releases the lock
 
-    def load(self, path, actor_id):
+    def load(self, path, actor_id, timeout=0.0):
+        """File hand-off, reader side (replay_memory.py:155-173): if a non-empty dump is waiting
+        and its lock is free, ``extend`` with it and delete the file.  Like the reference a busy
+        lock means "try again later" (returns False).  Unlike the reference an unreadable file is
+        NOT deleted: the error is raised and the file stays for inspection."""
+        import io
         path = os.path.join(path, f"memory{actor_id}.pt")
-        if os.path.isfile(path) and os.path.getsize(path) > 0:
-            try:
-                self.extend(torch.load(path, weights_only=False))
-            finally:
-                os.remove(path)
+        if not (os.path.isfile(path) and os.path.getsize(path) > 0):
+            return False
+        f = self._lock_file(path, timeout)
+        if f is None:
+            return False
+        try:
+            f.seek(0)
+            raw = f.read()
+            if not raw:
+                return False
+            memory = torch.load(io.BytesIO(raw), weights_only=False)
+            self.extend(memory)
+            os.remove(path)            # only after a successful read, still under the lock
+            return True
+        finally:
+            f.close()
 
     # ------------------------------------------------------------------ priorities
     def update_priority(self, index, priority):
