@@ -187,6 +187,30 @@ __global__ void tree_update_kernel(const float* __restrict__ sp, const uint8_t* 
     }
 }
 
+// one level of the same refresh, grid-wide: one warp per touched leaf recomputes that leaf's
+// ancestor at level `lvl` from its 32 children (duplicates recompute the same value).  Levels
+// are separate launches (level l+1 reads what level l wrote).  Used for large batches of
+// touched leaves, where a single CTA would serialise thousands of warp-scans.
+__global__ void tree_update_level_kernel(const float* __restrict__ sp, const uint8_t* __restrict__ st,
+                                         int64_t M, double* __restrict__ nodes, TreeLayout L,
+                                         const int64_t* __restrict__ slots, int n, int lvl) {
+    const int lane = threadIdx.x & 31;
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (int i = warp; i < n; i += nwarps) {
+        int64_t s = slots[i];
+        if (s < 0 || s >= M) continue;  // warp-uniform
+        int64_t node = s;
+        for (int k = 0; k <= lvl; ++k) node /= FAN;
+        const int64_t c = node * FAN + lane;
+        double v;
+        if (lvl == 0) v = leaf_value(sp, st, c, M);
+        else v = c < L.size[lvl - 1] ? nodes[L.off[lvl - 1] + c] : 0.0;
+        v = hs_scan(v, lane);
+        if (lane == 31) nodes[L.off[lvl] + node] = v;
+    }
+}
+
 // ======================================================================== gather
 constexpr int FRAME_U4 = R2D2_FRAME_BYTES / 16;  // 1764 x 16 B per transition row
 
@@ -416,6 +440,49 @@ __global__ void update_priority_seq_kernel(float* __restrict__ priority, int64_t
     }
 }
 
+// Last-writer-wins in O(n) without scratch, for large batches (the scans above are O(n*B)):
+//   claim : atomicMax(bits(priority[slot]), OWNER | k)   OWNER = 0xFFC00000 (quiet-NaN space:
+//           above the bit pattern of every finite float and of +-inf, so the largest flat
+//           position k among the writers of a slot survives, whatever the slot held before)
+//   commit: atomicCAS(bits(priority[slot]), OWNER | k, bits(p[k]))  -- only the owner's succeeds
+// Two launches; max is order-independent, so the result is deterministic.  k < 2^22.
+constexpr unsigned OWNER_TAG = 0xFFC00000u;
+constexpr int64_t OWNER_MAX_N = 1 << 22;
+
+__device__ __forceinline__ int64_t seq_slot(const int64_t* __restrict__ seq_index, int B, int burn_in,
+                                            int64_t M, int64_t k) {
+    const int t = (int)(k / B), b = (int)(k % B);
+    return (seq_index[b] + burn_in + t) % M;
+}
+
+// seq_index != nullptr: learner form (slot from the sampled starts); else generic index list
+__global__ void priority_claim_kernel(float* __restrict__ priority, int64_t M,
+                                      const int64_t* __restrict__ seq_index, int B, int burn_in,
+                                      const int64_t* __restrict__ index, int64_t n, int64_t k0) {
+    unsigned* bits = reinterpret_cast<unsigned*>(priority);
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n;
+         k += (int64_t)gridDim.x * blockDim.x) {
+        int64_t s;
+        if (seq_index) s = seq_slot(seq_index, B, burn_in, M, k0 + k);
+        else { s = index[k0 + k]; if (s < 0) s += M; if (s < 0 || s >= M) continue; }
+        atomicMax(bits + s, OWNER_TAG | (unsigned)k);
+    }
+}
+
+__global__ void priority_commit_kernel(float* __restrict__ priority, int64_t M,
+                                       const int64_t* __restrict__ seq_index, int B, int burn_in,
+                                       const int64_t* __restrict__ index, const float* __restrict__ p,
+                                       int64_t n, int64_t k0) {
+    unsigned* bits = reinterpret_cast<unsigned*>(priority);
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n;
+         k += (int64_t)gridDim.x * blockDim.x) {
+        int64_t s;
+        if (seq_index) s = seq_slot(seq_index, B, burn_in, M, k0 + k);
+        else { s = index[k0 + k]; if (s < 0) s += M; if (s < 0 || s >= M) continue; }
+        atomicCAS(bits + s, OWNER_TAG | (unsigned)k, __float_as_uint(p[k0 + k]));
+    }
+}
+
 // numpy float32 pairwise sum over a window of `n` priorities starting at `start`
 // (wrap: element i is priority[(start+i) mod M]); association as numpy's add.reduce.
 __device__ float pw_sum(const float* __restrict__ pr, int64_t start, int n, int64_t M,
@@ -509,6 +576,91 @@ __global__ void update_seq_priority_kernel(const float* __restrict__ pr, float* 
             v = seq_priority_value(pr, slot, T, M, true, eta, ometa);
         }
         sp[slot] = v;
+    }
+}
+
+// ---- the same refresh, grid-wide (large batches): phase 1 = one thread per op, phase 2 = one
+// warp per op.  Lanes 0..7 carry numpy's eight strided partial sums, all lanes share the max.
+__device__ float seq_priority_value_warp(const float* __restrict__ pr, int64_t start, int n,
+                                         int64_t M, bool wrap, float eta, float ometa, int lane) {
+    if (n < 8 || n > 128) {
+        float v = 0.f;
+        if (lane == 0) v = seq_priority_value(pr, start, n, M, wrap, eta, ometa);
+        return __shfl_sync(FULL, v, 0);
+    }
+    auto at = [&](int i) -> float {
+        int64_t s = start + i;
+        if (wrap) s = mod_pos(s, M);
+        return pr[s];
+    };
+    float mx = -INFINITY;
+    for (int i = lane; i < n; i += 32) mx = fmaxf(mx, at(i));
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) mx = fmaxf(mx, __shfl_xor_sync(FULL, mx, d));
+    const int nfull = n - (n % 8);
+    float r = 0.f;
+    if (lane < 8) {
+        r = at(lane);
+        for (int i = 8 + lane; i < nfull; i += 8) r = __fadd_rn(r, at(i));
+    }
+    float s1 = __fadd_rn(r, __shfl_down_sync(FULL, r, 1));      // lanes 0,2,4,6: r0+r1, r2+r3, ...
+    float s2 = __fadd_rn(s1, __shfl_down_sync(FULL, s1, 2));    // lanes 0,4
+    float res = __fadd_rn(s2, __shfl_down_sync(FULL, s2, 4));   // lane 0
+    float v = 0.f;
+    if (lane == 0) {
+        for (int i = nfull; i < n; ++i) res = __fadd_rn(res, at(i));
+        const float mean = __fdiv_rn(res, (float)n);
+        v = __fadd_rn(__fmul_rn(eta, mx), __fmul_rn(ometa, mean));
+    }
+    return __shfl_sync(FULL, v, 0);
+}
+
+__global__ void seq_priority_targets_kernel(const uint8_t* __restrict__ st, int64_t M,
+                                            const int64_t* __restrict__ seq_index, int n, int T,
+                                            int flag, int64_t* __restrict__ touched) {
+    const int nops = 3 * n;
+    for (int op = blockIdx.x * blockDim.x + threadIdx.x; op < nops; op += gridDim.x * blockDim.x) {
+        const int i = op / 3, j = op % 3;
+        const int64_t idx = seq_index[i];
+        int64_t hit = -1;
+        bool valid = false;
+        if (j == 0) { hit = idx; valid = true; }
+        else if (flag) {
+            const int dir = j == 1 ? -1 : 1;
+            for (int k = 1; k <= T; ++k) {
+                if (st[mod_pos(idx + (int64_t)dir * k, M)] == 1) { hit = idx - k; valid = true; break; }
+            }
+        }
+        touched[op] = valid ? mod_pos(hit, M) : -1;
+    }
+}
+
+__global__ void seq_priority_values_kernel(const float* __restrict__ pr, float* __restrict__ sp,
+                                           int64_t M, const int64_t* __restrict__ seq_index, int n,
+                                           int T, float eta, float ometa,
+                                           const int64_t* __restrict__ touched) {
+    const int nops = 3 * n;
+    const int lane = threadIdx.x & 31;
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (int op = warp; op < nops; op += nwarps) {
+        const int64_t slot = touched[op];
+        if (slot < 0) continue;                       // warp-uniform
+        const int i = op / 3, j = op % 3;
+        if (slot + T > M) {                           // formulas differ only near the array end
+            bool later = false;
+            for (int o2 = op + 1 + lane; o2 < nops; o2 += 32) later |= (touched[o2] == slot);
+            if (__any_sync(FULL, later)) continue;
+        }
+        float v;
+        if (j == 0) {
+            const int64_t idx = seq_index[i];
+            const int len = (int)((idx + T <= M) ? T : (M - idx));
+            v = seq_priority_value_warp(pr, idx, len, M, false, eta, ometa, lane);
+        } else {
+            v = seq_priority_value_warp(pr, slot, T, M, true, eta, ometa, lane);
+        }
+        if (lane == 0) sp[slot] = v;
     }
 }
 
@@ -629,8 +781,16 @@ int r2d2_tree_update(const float* seq_prio, const uint8_t* is_start, int64_t M, 
     R2D2_REQUIRE(seq_prio && is_start && nodes && slots, "tree_update: null pointer");
     if (n <= 0) return R2D2_OK;
     TreeLayout L = make_layout(M);
-    R2D2_LAUNCH("tree_update_kernel", as_stream(stream), tree_update_kernel<<<1, 1024, 0, as_stream(stream)>>>(seq_prio, is_start, M, nodes, L, slots,
-                                                           n));
+    if (n <= 96) {      // one launch, levels synchronised inside the CTA
+        R2D2_LAUNCH("tree_update_kernel", as_stream(stream), tree_update_kernel<<<1, 1024, 0, as_stream(stream)>>>(seq_prio, is_start, M, nodes, L, slots,
+                                                               n));
+        return R2D2_OK;
+    }
+    int blocks = (n + 7) / 8;                          // 8 warps per CTA, one warp per touched leaf
+    blocks = blocks > sm_count() * 8 ? sm_count() * 8 : blocks;
+    for (int l = 0; l < L.n_levels; ++l)
+        R2D2_LAUNCH("tree_update_level_kernel", as_stream(stream),
+                    tree_update_level_kernel<<<blocks, 256, 0, as_stream(stream)>>>(seq_prio, is_start, M, nodes, L, slots, n, l));
     return R2D2_OK;
 }
 
@@ -720,8 +880,21 @@ int r2d2_update_priority(float* priority, int64_t M, const int64_t* index, const
     if (n <= 0) return R2D2_OK;
     int64_t blocks = (n + 127) / 128;
     if (blocks > 148 * 16) blocks = 148 * 16;
-    R2D2_LAUNCH("update_priority_kernel", as_stream(stream), update_priority_kernel<<<(unsigned)blocks, 128, 0, as_stream(stream)>>>(priority, M, index, p,
-                                                                            n));
+    if (n <= 2048) {     // few indices: one launch, each index scans the ones behind it
+        R2D2_LAUNCH("update_priority_kernel", as_stream(stream), update_priority_kernel<<<(unsigned)blocks, 128, 0, as_stream(stream)>>>(priority, M, index, p,
+                                                                                n));
+        return R2D2_OK;
+    }
+    // many: claim/commit in O(n), in chunks the owner tag can number (later chunks overwrite earlier ones)
+    for (int64_t k0 = 0; k0 < n; k0 += OWNER_MAX_N) {
+        const int64_t nn = n - k0 < OWNER_MAX_N ? n - k0 : OWNER_MAX_N;
+        int64_t bl = (nn + 255) / 256;
+        if (bl > 148 * 16) bl = 148 * 16;
+        R2D2_LAUNCH("priority_claim_kernel", as_stream(stream),
+                    priority_claim_kernel<<<(unsigned)bl, 256, 0, as_stream(stream)>>>(priority, M, nullptr, 0, 0, index, nn, k0));
+        R2D2_LAUNCH("priority_commit_kernel", as_stream(stream),
+                    priority_commit_kernel<<<(unsigned)bl, 256, 0, as_stream(stream)>>>(priority, M, nullptr, 0, 0, index, p, nn, k0));
+    }
     return R2D2_OK;
 }
 
@@ -729,8 +902,18 @@ int r2d2_update_priority_seq(float* priority, int64_t M, const int64_t* seq_inde
                              int burn_in, int L, const float* p, void* stream) {
     R2D2_REQUIRE(priority && seq_index && p && M > 0 && B > 0 && L > 0 && burn_in >= 0,
                  "update_priority_seq: bad args");
-    R2D2_REQUIRE(B <= 4096, "update_priority_seq: B=%d exceeds 4096", B);
     const int64_t n = (int64_t)L * B;
+    if (B > 32) {       // larger batches: claim/commit in O(n) instead of an O(B) scan per element
+        R2D2_REQUIRE(n <= OWNER_MAX_N && M >= L, "update_priority_seq: L*B=%lld exceeds %lld (or M < L)",
+                     (long long)n, (long long)OWNER_MAX_N);
+        int64_t bl = (n + 255) / 256;
+        if (bl > 148 * 16) bl = 148 * 16;
+        R2D2_LAUNCH("priority_claim_kernel", as_stream(stream),
+                    priority_claim_kernel<<<(unsigned)bl, 256, 0, as_stream(stream)>>>(priority, M, seq_index, B, burn_in, nullptr, n, 0));
+        R2D2_LAUNCH("priority_commit_kernel", as_stream(stream),
+                    priority_commit_kernel<<<(unsigned)bl, 256, 0, as_stream(stream)>>>(priority, M, seq_index, B, burn_in, nullptr, p, n, 0));
+        return R2D2_OK;
+    }
     int64_t blocks = (n + 127) / 128;
     if (blocks > 148 * 16) blocks = 148 * 16;
     R2D2_LAUNCH("update_priority_seq_kernel", as_stream(stream), update_priority_seq_kernel<<<(unsigned)blocks, 128, B * sizeof(int64_t), as_stream(stream)>>>(
@@ -746,9 +929,22 @@ int r2d2_update_sequence_priority(const float* priority, float* seq_prio,
                  "update_sequence_priority: null pointer");
     R2D2_REQUIRE(M > 0 && T > 0 && T <= M, "update_sequence_priority: need 0 < T <= M");
     if (n <= 0) return R2D2_OK;
-    R2D2_LAUNCH("update_seq_priority_kernel", as_stream(stream), update_seq_priority_kernel<<<1, 1024, 0, as_stream(stream)>>>(
-        priority, seq_prio, is_start, M, seq_index, n, T, eta_f32, one_minus_eta_f32,
-        update_pre_next, touched));
+    if (n <= 32) {      // small batches: one launch, phases synchronised inside the CTA
+        R2D2_LAUNCH("update_seq_priority_kernel", as_stream(stream), update_seq_priority_kernel<<<1, 1024, 0, as_stream(stream)>>>(
+            priority, seq_prio, is_start, M, seq_index, n, T, eta_f32, one_minus_eta_f32,
+            update_pre_next, touched));
+        return R2D2_OK;
+    }
+    const int nops = 3 * n;
+    int b1 = (nops + 127) / 128, b2 = (nops + 7) / 8;
+    const int cap = sm_count() * 8;
+    b1 = b1 > cap ? cap : b1;
+    b2 = b2 > cap ? cap : b2;
+    R2D2_LAUNCH("seq_priority_targets_kernel", as_stream(stream),
+                seq_priority_targets_kernel<<<b1, 128, 0, as_stream(stream)>>>(is_start, M, seq_index, n, T, update_pre_next, touched));
+    R2D2_LAUNCH("seq_priority_values_kernel", as_stream(stream),
+                seq_priority_values_kernel<<<b2, 256, 0, as_stream(stream)>>>(priority, seq_prio, M, seq_index, n, T, eta_f32,
+                                                                              one_minus_eta_f32, touched));
     return R2D2_OK;
 }
 

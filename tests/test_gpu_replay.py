@@ -273,3 +273,45 @@ def test_overlapped_extend_is_visible_to_next_draw(cuda_device):
         assert np.array_equal(ws["seq_index"].cpu().numpy(), si)
         rows_idx = (si[:, None] + np.arange(9)[None]) % M
         assert np.array_equal(ws["slab"].cpu().numpy(), rep.memory["state"][rows_idx])
+
+
+@pytest.mark.parametrize("B", [300, 1024, 4096])
+def test_large_batch_priority_path_vs_oracle(cuda_device, B):
+    """BASELINE config 3 batch sizes take the grid-wide kernels (O(n) claim/commit scatter, one
+    warp per sequence refresh, per-level tree update): same arrays as the oracle, bit for bit,
+    with duplicate and overlapping sequences, starts near the ring end, and a generic
+    update_priority call large enough for the claim/commit form."""
+    from pytorch_r2d2_b200 import ReplayMemory
+    M, BI, LN = 20000, 6, 14
+    T = BI + LN
+    rng = np.random.RandomState(B)
+    rep = RO.ReplayOracle(M, 32, 1, BI, LN)
+    rep.memory["priority"][:] = rng.rand(M).astype(np.float32) + 0.01
+    starts = np.unique(np.concatenate([np.arange(0, M, 7), [M - 1, M - 5, M - T, M - T + 1]]))
+    rep.memory["is_seq_start"][starts] = 1
+    rep.memory["sequence_priority"][:] = rng.rand(M).astype(np.float32)
+    rep.index = M
+    g = ReplayMemory(M, 4, 1, cell_size=32)
+    g.burn_in_length, g.learning_length, g.sequence_length = BI, LN, T
+    g.extend({k: v.copy() for k, v in rep.memory.items()})
+    g._ensure_tree()
+    seq = rng.choice(starts, B).astype(np.int64)                  # duplicates and overlaps
+    seq[:4] = [M - 1, M - 5, M - T + 1, M - 1]
+    p = rng.rand(LN, B).astype(np.float32)
+    index = np.stack([(seq + s) % M for s in range(T)])
+    rep.update_priority(index[BI:].reshape(-1), p.reshape(-1))
+    rep.update_sequence_priority(seq, True)
+    g.update_priority_learn_window(torch.from_numpy(seq).cuda(), torch.from_numpy(p).cuda())
+    g.update_sequence_priority(torch.from_numpy(seq).cuda(), True)
+    assert np.array_equal(gpu_mem_np(g, "priority").view(np.uint32), rep.memory["priority"].view(np.uint32))
+    assert np.array_equal(gpu_mem_np(g, "sequence_priority").view(np.uint32),
+                          rep.memory["sequence_priority"].view(np.uint32))
+    nodes = g._nodes.clone()
+    g.rebuild_tree()
+    assert torch.equal(nodes, g._nodes)
+    # generic scatter, n > 2048 -> claim/commit; negative (numpy-style) indices included
+    idx = rng.randint(-M, M, 5000).astype(np.int64)
+    val = rng.rand(5000).astype(np.float32)
+    rep.update_priority(idx, val)
+    g.update_priority(idx, val)
+    assert np.array_equal(gpu_mem_np(g, "priority").view(np.uint32), rep.memory["priority"].view(np.uint32))
