@@ -81,17 +81,20 @@ class NStepOracle:
 
 def calc_priority(q_value, action, reward, next_q_value, target_next_q_value, done,
                   gamma=0.99, n=3, eps=1e-6, alpha=0.6):
-    """actor.py:144-157.  q arrays are float32; under numpy 2 the Python-float constants are
-    weak scalars, so every operation rounds to float32."""
+    """actor.py:144-157.  q arrays are float32 ([1,6]); under numpy 2 the Python-float constants
+    are weak scalars, so every operation rounds to float32.  Shapes are kept as the reference
+    has them (a (1,)-array when bootstrapping, a scalar when done): numpy's array and scalar
+    ``power`` paths need not agree in the last bit."""
     q = np.asarray(q_value, np.float32).reshape(-1)[action]
     tn = np.asarray(target_next_q_value, np.float32).reshape(-1)
     if done:
         target = reward
     else:
-        na = np.asarray(next_q_value, np.float32).argmax(-1)
-        target = reward + (gamma ** n) * tn[na].reshape(-1)[0] if np.ndim(na) else reward + (gamma ** n) * tn[na]
+        na = np.asarray(next_q_value, np.float32).reshape(1, -1).argmax(-1)     # array([k])
+        target = reward + (gamma ** n) * tn[na]
     p = np.abs(q - target) + eps
-    return np.float32(p ** alpha)
+    p = p ** alpha
+    return np.float32(np.asarray(p).reshape(-1)[0])
 
 
 class ActorOracle:

@@ -368,6 +368,95 @@ def make_dump(ref_replay):
     print("[dump] reference-written hand-off file:", {k: (v.dtype.name, v.shape) for k, v in d.items()})
 
 
+# ------------------------------------------------------------------ actor goldens
+def make_actor(ref_replay, ref_model):
+    """The UNMODIFIED reference ``Actor`` (actor.py) stepped on the scripted environment of
+    oracle/actor_oracle.py (``env`` is stubbed: gym/ALE are not installed).  Stores what the
+    actor fed its replay (per step: action, reward, done, both nets' Q/h/c) and the replay it
+    ended up with; asserts the oracle restatement reproduces that replay."""
+    import contextlib
+    import io
+    from oracle import actor_oracle as AO
+    env_mod = types.ModuleType("env")
+    env_mod.PongEnv = None
+    sys.modules["env"] = env_mod
+    import actor as ref_actor  # noqa
+    out = {}
+    BI, LN, OV, NS = 3, 3, 3, 3
+    cases = {"a": (1, 3, 11, (11, 9, 13)), "b": (2, 3, 12, (8, 2, 15, 7))}
+    for name, (actor_id, n_actors, seed, lengths) in cases.items():
+        ref_actor.PongEnv = lambda action_repeat, n_stacks, _s=seed, _l=lengths: AO.ScriptedEnv(_s, _l)
+        torch.manual_seed(0)
+        np.random.seed(100 + seed)
+        A = ref_actor.Actor(actor_id, n_actors, {}, "cpu")
+        A.burn_in_length, A.learning_length, A.overlap_length = BI, LN, OV
+        A.sequence_length = BI + LN
+        A.memory_save_interval = A.net_load_interval = 10 ** 9
+        M = 64
+        A.memory_size = M
+        A.replay_memory = ref_replay.ReplayMemory(M, 4, NS)
+        A.replay_memory.burn_in_length, A.replay_memory.learning_length = BI, LN
+        A.replay_memory.sequence_length = BI + LN
+        # make the two nets differ (the reference starts them equal): target = online * 1.01
+        with torch.no_grad():
+            for v in A.target_net.parameters():
+                v.mul_(1.01)
+        rec = []
+        orig = A.select_action
+
+        def spy(state, _o=orig, _rec=rec):
+            r = _o(state)
+            _rec.append(dict(state=np.array(state, copy=True), action=r[0], q=r[1].numpy().copy(), h=np.array(r[2]),
+                             c=np.array(r[3]), tq=r[4].numpy().copy(), th=np.array(r[5]), tc=np.array(r[6])))
+            return r
+        A.select_action = spy
+        orig_step = A.env.step
+
+        def env_spy(action, _o=orig_step, _rec=rec):
+            r = _o(action)
+            _rec[-1]["reward"], _rec[-1]["done"] = r[1], r[2]
+            return r
+        A.env.step = env_spy
+        n_steps = sum(lengths)
+        with contextlib.redirect_stdout(io.StringIO()):
+            for _ in range(n_steps):
+                A.step()
+        rm = A.replay_memory
+        rows = rm.index
+        # oracle restatement fed with the same per-step network outputs
+        O = AO.ActorOracle(M, 256, NS, BI, LN, OV)
+        for r in rec:
+            O.observe(r["state"], r["action"], r["q"], r["h"], r["c"], r["tq"], r["th"], r["tc"], r["reward"], r["done"])
+        assert O.replay.index == rows, (O.replay.index, rows)
+        for k in RO.KEYS:
+            a, b = O.replay.memory[k][:rows], rm.memory[k][:rows]
+            if k in ("priority", "sequence_priority"):
+                assert np.array_equal(a.view(np.uint32), b.view(np.uint32)), (name, k)
+            else:
+                assert np.array_equal(a, b), (name, k)
+        print(f"[actor] case {name}: {n_steps} steps, {rows} rows stored; oracle restatement == reference replay (bit-exact)")
+        # which step's frame each stored row holds (frames are regenerated from the env seed)
+        src = []
+        for i in range(rows):
+            hit = [j for j, r in enumerate(rec) if np.array_equal((r["state"] * 255).astype(np.uint8), rm.memory["state"][i])]
+            assert len(hit) == 1
+            src.append(hit[0])
+        out.update({f"{name}/config": np.array([actor_id, n_actors, seed, M, BI, LN, OV, NS]),
+                    f"{name}/lengths": np.array(lengths), f"{name}/np_seed": 100 + seed,
+                    f"{name}/action": np.array([r["action"] for r in rec]),
+                    f"{name}/reward": np.array([r["reward"] for r in rec]),
+                    f"{name}/done": np.array([r["done"] for r in rec]),
+                    f"{name}/q": np.stack([r["q"].reshape(6) for r in rec]),
+                    f"{name}/tq": np.stack([r["tq"].reshape(6) for r in rec]),
+                    f"{name}/h_last": rec[-1]["h"].reshape(-1), f"{name}/c_last": rec[-1]["c"].reshape(-1),
+                    f"{name}/rows": rows, f"{name}/state_src_step": np.array(src),
+                    f"{name}/epsilon": A.epsilon})
+        for k in RO.KEYS:
+            if k != "state":
+                out[f"{name}/mem/{k}"] = rm.memory[k][:rows].copy()
+    np.savez_compressed(os.path.join(GOLD, "actor.npz"), **out)
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     ref_replay, ref_model, ref_learner = import_reference()
@@ -381,6 +470,8 @@ def main():
         make_network(ref_replay, ref_model, ref_learner)
     if not only or "dump" in only:
         make_dump(ref_replay)
+    if not only or "actor" in only:
+        make_actor(ref_replay, ref_model)
     print("golden fixtures written to", GOLD)
 
 

@@ -156,3 +156,36 @@ def test_train_step_restatement(gold):
 def test_value_rescale_inverse():
     x = torch.linspace(-50, 50, 1001)
     assert torch.allclose(NO.value_rescale_inv(NO.value_rescale(x)), x, atol=2e-3)
+
+
+def test_actor_oracle_vs_reference_actor_golden(golden_dir):
+    """oracle.actor_oracle (NStepMemory quirks, calc_priority, sequence starts) replays the
+    per-step record of the UNMODIFIED reference Actor and must rebuild its replay bit for bit
+    (hidden states are not in the record: zeros are fed, those two keys are skipped)."""
+    import os
+    import numpy as np
+    from oracle import actor_oracle as AO
+    g = np.load(os.path.join(golden_dir, "actor.npz"))
+    for name in ("a", "b"):
+        actor_id, n_actors, seed, M, BI, LN, OV, NS = [int(v) for v in g[f"{name}/config"]]
+        env = AO.ScriptedEnv(seed, tuple(int(x) for x in g[f"{name}/lengths"]))
+        O = AO.ActorOracle(M, 256, NS, BI, LN, OV)
+        z = np.zeros((1, 256), np.float32)
+        state = env.reset()
+        frames = []
+        for t in range(len(g[f"{name}/action"])):
+            frames.append(state)
+            nxt, reward, done, _ = env.step(int(g[f"{name}/action"][t]))
+            assert reward == float(g[f"{name}/reward"][t]) and done == bool(g[f"{name}/done"][t])
+            O.observe(state, int(g[f"{name}/action"][t]), g[f"{name}/q"][t][None], z, z, g[f"{name}/tq"][t][None],
+                      z, z, reward, done)
+            state = env.reset() if done else nxt
+        rows = int(g[f"{name}/rows"])
+        assert O.replay.index == rows
+        for k in ("action", "reward", "done", "stack_count", "is_seq_start"):
+            assert np.array_equal(O.replay.memory[k][:rows], g[f"{name}/mem/{k}"]), (name, k)
+        for k in ("priority", "sequence_priority"):
+            assert np.array_equal(O.replay.memory[k][:rows].view(np.uint32), g[f"{name}/mem/{k}"].view(np.uint32)), (name, k)
+        src = g[f"{name}/state_src_step"]
+        for i in range(rows):
+            assert np.array_equal(O.replay.memory["state"][i], (frames[src[i]] * 255).astype(np.uint8))
