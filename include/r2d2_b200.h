@@ -353,6 +353,45 @@ int r2d2_dp_reduce_rmsprop(int rank, int world, void* const* grads, void* const*
                            int64_t offset, int bucket, int64_t n, double lr, double alpha, double eps,
                            double grad_scale, void* stream);
 
+/* ------------------------------------------------------------------ actor-side experience (section 8f)
+ * Replaces, for N actors stepped together, what /root/reference actor.py:74-94 does per actor
+ * after env.step returned: NStepMemory.add / get (replay_memory.py:27-52, deques of maxlen n --
+ * so the first transition of an episode is pushed out before the first get, and the reward
+ * deque, never popped, gives every transition flushed at the end of an episode the same
+ * discounted sum), calc_priority (actor.py:144-157: the CURRENT step's Q-values stand in for
+ * the next state's, `done` is the current step's), ReplayMemory.add into the actor's local ring
+ * (replay_memory.py:93-105: frames stored as state*255 truncated to u8), and at the end of an
+ * episode set_seq_start_index (actor.py:159-167: a start every `overlap` rows from the
+ * episode's first row while < last-T, plus a forced start at last-T; their sequence
+ * priorities eta*max + (1-eta)*mean in numpy's order, replay_memory.py:187-188).  If fewer than
+ * T rows are in the ring at the end of an episode the reference indexes a negative slot (and
+ * raises on the empty slice); here that forced start is skipped.
+ *
+ * All pointers are device memory owned by the caller; leading dimension N (actor) everywhere.
+ *   n-step ring : ns_state u8[N,n,28224], ns_hc / ns_thc f32[N,n,2H] (h|c of the online / target
+ *                 net), ns_q f32[N,n,6], ns_action i32[N,n], ns_reward f64[N,n],
+ *                 counters i32[N,2] = {steps in this episode, entries waiting}
+ *   local rings : the ten replay keys with shapes [N,C,...] (same dtypes as the replay ring),
+ *                 index i64[N] (rows written), ep_start i64[N]; the caller hands the rows to
+ *                 the learner's replay (r2d2_replay_ingest) before C rows are reached.
+ *   per call    : obs f32[N,28224] in [0,1], action i64[N], q / tq f32[N,6], h c th tc
+ *                 f32[N,H], reward f64[N], done u8[N]; gamma_pow f64[n] = gamma^0..gamma^(n-1)
+ *                 as the host computes them (the reference sums gamma**i * r in Python floats),
+ *                 gamma_n = gamma^n rounded to f32. */
+typedef struct {
+    uint8_t* ns_state; float* ns_hc; float* ns_thc; float* ns_q; int32_t* ns_action;
+    double* ns_reward; int32_t* counters;
+    uint8_t* state; float* hs_cs; float* target_hs_cs; int8_t* action; float* reward; float* done;
+    int8_t* stack_count; float* priority; float* sequence_priority; uint8_t* is_seq_start;
+    int64_t* index; int64_t* ep_start;
+} r2d2_actor_buffers;
+int r2d2_actor_observe(const r2d2_actor_buffers* buf, int N, int n, int H, int64_t C, int T,
+                       int overlap, const float* obs, const int64_t* action, const float* q,
+                       const float* h, const float* c, const float* tq, const float* th,
+                       const float* tc, const double* reward, const uint8_t* done,
+                       const double* gamma_pow, float gamma_n, float prio_eps, float alpha,
+                       float eta_f32, float one_minus_eta_f32, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -18,7 +18,7 @@ def __getattr__(name):
     if name in ("Learner", "learner_process"):
         from . import learner
         return getattr(learner, name)
-    if name == "BatchedActor":
-        from .actor import BatchedActor
-        return BatchedActor
+    if name in ("BatchedActor", "ActorExperience", "Actor", "actor_process"):
+        from . import actor
+        return getattr(actor, name)
     raise AttributeError(name)

@@ -85,6 +85,7 @@ PROTOTYPES = {
     "r2d2_cast_bf16": (_I, [_P, _P, _L, _P]),
     "r2d2_transpose_cast_bf16": (_I, [_P, _P, _I, _I, _P]),
     "r2d2_rmsprop_centered": (_I, [_P, _P, _P, _P, _L, _D, _D, _D, _D, _P]),
+    "r2d2_actor_observe": (_I, [_P, _I, _I, _I, _L, _I, _I] + [_P] * 11 + [_F, _F, _F, _F, _F, _P]),
 }
 
 _lib = None

@@ -2,6 +2,7 @@
 // priority scatter and sequence-priority refresh (K8).  Integer/byte work: HBM- or
 // latency-bound; no tensor cores.  Reference semantics: replay_memory.py:93-119,175-262.
 #include "common.cuh"
+#include "priority.cuh"
 #include "ptx.cuh"
 
 #include <atomic>
@@ -481,51 +482,6 @@ __global__ void priority_commit_kernel(float* __restrict__ priority, int64_t M,
         else { s = index[k0 + k]; if (s < 0) s += M; if (s < 0 || s >= M) continue; }
         atomicCAS(bits + s, OWNER_TAG | (unsigned)k, __float_as_uint(p[k0 + k]));
     }
-}
-
-// numpy float32 pairwise sum over a window of `n` priorities starting at `start`
-// (wrap: element i is priority[(start+i) mod M]); association as numpy's add.reduce.
-__device__ float pw_sum(const float* __restrict__ pr, int64_t start, int n, int64_t M,
-                        bool wrap) {
-    auto at = [&](int i) -> float {
-        int64_t s = start + i;
-        if (wrap) s = mod_pos(s, M);
-        return pr[s];
-    };
-    if (n < 8) {
-        float res = 0.f;
-        for (int i = 0; i < n; ++i) res = __fadd_rn(res, at(i));
-        return res;
-    }
-    if (n <= 128) {
-        float r[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) r[j] = at(j);
-        int i = 8;
-        for (; i < n - (n % 8); i += 8) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) r[j] = __fadd_rn(r[j], at(i + j));
-        }
-        float res = __fadd_rn(__fadd_rn(__fadd_rn(r[0], r[1]), __fadd_rn(r[2], r[3])),
-                              __fadd_rn(__fadd_rn(r[4], r[5]), __fadd_rn(r[6], r[7])));
-        for (; i < n; ++i) res = __fadd_rn(res, at(i));
-        return res;
-    }
-    int n2 = n / 2;
-    n2 -= n2 % 8;
-    return __fadd_rn(pw_sum(pr, start, n2, M, wrap), pw_sum(pr, start + n2, n - n2, M, wrap));
-}
-
-__device__ float seq_priority_value(const float* __restrict__ pr, int64_t start, int n,
-                                    int64_t M, bool wrap, float eta, float ometa) {
-    float mx = -INFINITY;
-    for (int i = 0; i < n; ++i) {
-        int64_t s = start + i;
-        if (wrap) s = mod_pos(s, M);
-        mx = fmaxf(mx, pr[s]);
-    }
-    const float mean = __fdiv_rn(pw_sum(pr, start, n, M, wrap), (float)n);
-    return __fadd_rn(__fmul_rn(eta, mx), __fmul_rn(ometa, mean));
 }
 
 // Single CTA.  op = 3*i + j: j=0 own slot (non-wrapping, truncated window), j=1 "previous",

@@ -423,7 +423,7 @@ def test_batched_actor_inference_vs_oracle(cuda_device, precision, tol):
         with torch.no_grad():
             q_ref, _, _, (h, c) = NO.qnet_forward(p, x, h, c)
             tq_ref, _, _, (th, tc) = NO.qnet_forward(p, x, th, tc)
-        action, q, tq = act.select_action(x.cuda(), rng=np.random.RandomState(step))
+        action, q, _, _, tq, _, _ = act.select_action(x.cuda(), rng=np.random.RandomState(step))
         assert rel_err(q, q_ref) < tol and rel_err(tq, tq_ref) < tol, (step, rel_err(q, q_ref))
         assert action.shape == (N,) and int(action.min()) >= 0 and int(action.max()) < 6
     hh, cc = act.net.get_state()
