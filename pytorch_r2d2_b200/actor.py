@@ -48,6 +48,71 @@ class BatchedActor:
         self.target_net = target_net if target_net is not None else QNet(device, cell_size, precision)
         if target_net is None:
             self.target_net.load_state_dict(self.net.state_dict())
+        # One step of both nets is ~50 small kernels: replayed from a CUDA graph over a fixed
+        # workspace (nothing allocated per step, the weights' bf16 operand images refreshed inside
+        # the graph, so weight updates need no invalidation).  False = enqueue kernel by kernel.
+        self.use_cuda_graph = True
+        self._g = None
+
+    def _build_graph(self):
+        from .model import alloc_forward_ws, net_forward
+        N, dev = self.n_actors, self.device
+        g = {"obs": torch.empty((N, 4, 84, 84), dtype=torch.float32, device=dev), "ws": [], "last": [None, None]}
+        nets = (self.net, self.target_net)
+        for net in nets:
+            ws = alloc_forward_ws(net._weights(), 1, N, dev, want_gates=False, tc=net.precision == "bf16")
+            ws["hs_ext"].zero_()
+            ws["cs_ext"].zero_()
+            g["ws"].append(ws)
+        side = torch.cuda.Stream(device=dev)
+
+        def both():
+            main = torch.cuda.current_stream()
+            side.wait_stream(main)
+            for net, ws, stream in zip(nets, g["ws"], (main, side)):
+                with torch.cuda.stream(stream):
+                    net_forward(net._weights(), 1, N, ws["hs_ext"][0], ws["cs_ext"][0], frames=g["obs"],
+                                want_gates=False, ws=ws, tc=net.precision == "bf16")
+            main.wait_stream(side)
+
+        g["obs"].zero_()
+        saved = [(ws["hs_ext"].clone(), ws["cs_ext"].clone()) for ws in g["ws"]]
+        s = torch.cuda.Stream(device=dev)
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            both()                               # warm-up outside capture
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            both()
+        for ws, (hs, cs) in zip(g["ws"], saved):
+            ws["hs_ext"].copy_(hs)
+            ws["cs_ext"].copy_(cs)
+        g["graph"] = graph
+        self._g = g
+        return g
+
+    def _graph_step(self, state):
+        g = self._g or self._build_graph()
+        for i, (net, ws) in enumerate(zip((self.net, self.target_net), g["ws"])):
+            # module-held state (model.py:48-57): None -> zeros; anything the caller put there
+            # (set_state, a partial reset) -> copied in; our own previous output -> carried over
+            if net.hs is None:
+                ws["hs_ext"][0].zero_()
+                ws["cs_ext"][0].zero_()
+            elif net.hs is g["last"][i]:
+                ws["hs_ext"][0].copy_(ws["hs_ext"][1])
+                ws["cs_ext"][0].copy_(ws["cs_ext"][1])
+            else:
+                ws["hs_ext"][0].copy_(torch.as_tensor(net.hs).to(self.device))
+                ws["cs_ext"][0].copy_(torch.as_tensor(net.cs).to(self.device))
+        g["obs"].copy_(state.reshape(g["obs"].shape), non_blocking=True)
+        g["graph"].replay()
+        for i, (net, ws) in enumerate(zip((self.net, self.target_net), g["ws"])):
+            net.hs, net.cs = ws["hs_ext"][1], ws["cs_ext"][1]
+            g["last"][i] = net.hs
+        return g["ws"][0]["q"], g["ws"][1]["q"]
 
     def reset(self, actors=None):
         """Zero recurrent state (actor.py:112-113) for all actors, or for the given ones."""
@@ -64,7 +129,10 @@ class BatchedActor:
     @torch.no_grad()
     def forward_both(self, state):
         """state: [N,4,84,84] f32 in [0,1] on the device.  Returns (q, tq) [N,6]; hidden states
-        advance inside the modules (model.py:48-57)."""
+        advance inside the modules (model.py:48-57).  With ``use_cuda_graph`` the returned tensors
+        (and ``net.hs`` / ``net.cs``) live in the fixed workspace: valid until the next step."""
+        if self.use_cuda_graph and state.shape[0] == self.n_actors:
+            return self._graph_step(state)
         q = self.net(state)
         tq = self.target_net(state)
         return q, tq

@@ -48,10 +48,31 @@ class NetStash:
                  "cs_ext", "gates", "hid", "q")
 
 
-def _split(x):
-    pair = torch.empty((2, *x.shape), dtype=torch.bfloat16, device=x.device)
-    engine.split_bf16(x, pair[0], pair[1])
-    return pair
+def alloc_forward_ws(w: Weights, T, B, device, *, want_gates=True, head_from=0, tc=False):
+    """Every buffer one ``net_forward`` call writes (activations, LSTM histories, head, and for
+    the tensor-core path the bf16 operand images and the recurrence scratch).  Callers that run
+    the same shape repeatedly (actors) allocate it once and pass it as ``ws``; nothing is then
+    allocated per call, which also makes the call capturable in a CUDA graph."""
+    H, R = w.H, T * B
+    dev = device
+    f = lambda *shape: torch.empty(shape, dtype=torch.float32, device=dev)  # noqa: E731
+    h16 = lambda *shape: torch.empty(shape, dtype=torch.bfloat16, device=dev)  # noqa: E731
+    Mh = (T - head_from) * B
+    ws = dict(key=(T, B, H, want_gates, head_from, tc))
+    ws["a1"], ws["a2"], ws["feat"] = engine.alloc_torso(R, dev)
+    ws["hs_ext"], ws["cs_ext"] = f(T + 1, B, H), f(T + 1, B, H)
+    ws["gates"] = f(T, B, 4 * H) if want_gates else None
+    ws["hid"], ws["q"] = f(Mh, 2 * H), f(Mh, N_ACTIONS)
+    if tc:
+        Rp = (R + 3) // 4 * 4                      # tc_linear needs N % 4 == 0 (N = frames here)
+        ws["xproj"] = f(4 * H, Rp)                                   # transposed projection
+        ws["w16"], ws["hw16"] = h16(2, 4 * H, FEAT), h16(2, 2 * H, H)
+        ws["f16"] = torch.zeros((2, Rp, FEAT), dtype=torch.bfloat16, device=dev)   # pad rows stay zero
+        ws["hd16"] = h16(2, Mh, H)
+        ws["scratch"] = torch.empty(engine.tc_lstm_scratch_bytes(B, H), dtype=torch.uint8, device=dev)
+    else:
+        ws["xproj"] = f(R, 4 * H)
+    return ws
 
 
 def net_forward(w: Weights, T, B, h0, c0, *, slab=None, s0=0, frames=None, want_gates=True,
@@ -60,41 +81,44 @@ def net_forward(w: Weights, T, B, h0, c0, *, slab=None, s0=0, frames=None, want_
 
     Frames come either from a u8 slab [B,S,4,84,84] (steps s0..s0+T, /255 fused) or from an f32
     tensor [T*B,4,84,84].  tc=True runs every contraction on tcgen05 tensor cores (compensated
-    bf16x3, fp32-accurate forward).  Returns a NetStash; q covers rows head_from*B .. T*B."""
+    bf16x3, fp32-accurate forward).  ``ws`` = a workspace from ``alloc_forward_ws`` for this shape
+    (default: allocated here).  Returns a NetStash whose tensors live in the workspace; q covers
+    rows head_from*B .. T*B."""
     dev, H = h0.device, w.H
     R = T * B
+    key = (T, B, H, want_gates, head_from, tc)
+    if ws is None:
+        ws = alloc_forward_ws(w, T, B, dev, want_gates=want_gates, head_from=head_from, tc=tc)
+    elif ws["key"] != key:
+        raise ValueError(f"workspace was allocated for {ws['key']}, this call is {key}")
     st = NetStash()
     st.frames_u8, st.frames_f32, st.s0, st.T, st.B = slab, frames, s0, T, B
-    st.a1, st.a2, st.feat = engine.alloc_torso(R, dev)
+    st.a1, st.a2, st.feat = ws["a1"], ws["a2"], ws["feat"]
     if slab is not None:
         engine.torso_fwd_u8(slab, s0, T, w, st.a1, st.a2, st.feat, tc=tc)
     else:
         engine.torso_fwd_f32(frames, w, st.a1, st.a2, st.feat, tc=tc)
-    st.hs_ext = torch.empty((T + 1, B, H), device=dev)
-    st.cs_ext = torch.empty((T + 1, B, H), device=dev)
-    st.hs_ext[0].copy_(h0)
-    st.cs_ext[0].copy_(c0)
-    st.gates = torch.empty((T, B, 4 * H), device=dev) if want_gates else None
+    st.hs_ext, st.cs_ext = ws["hs_ext"], ws["cs_ext"]
+    if h0.data_ptr() != st.hs_ext[0].data_ptr():
+        st.hs_ext[0].copy_(h0)
+    if c0.data_ptr() != st.cs_ext[0].data_ptr():
+        st.cs_ext[0].copy_(c0)
+    st.gates = ws["gates"]
     Mh = (T - head_from) * B
-    st.hid = torch.empty((Mh, 2 * H), device=dev)
-    st.q = torch.empty((Mh, N_ACTIONS), device=dev)
+    st.hid, st.q = ws["hid"], ws["q"]
     hs_head = st.hs_ext[1 + head_from:].reshape(Mh, H)
+    st.xproj = ws["xproj"]
     if tc:
-        Rp = (R + 3) // 4 * 4                      # tc_linear needs N % 4 == 0 (N = frames here)
-        w16, f16 = _split(w.w_ih), _split(st.feat)
-        st.xproj = torch.empty((4 * H, Rp), device=dev)          # transposed projection
-        if Rp != R:
-            fpad = torch.zeros((2, Rp, f16.shape[2]), dtype=torch.bfloat16, device=dev)
-            fpad[:, :R] = f16
-            f16 = fpad
+        w16, f16, hd16, hw16 = ws["w16"], ws["f16"], ws["hd16"], ws["hw16"]
+        engine.split_bf16(w.w_ih, w16[0], w16[1])
+        engine.split_bf16(st.feat, f16[0, :R], f16[1, :R])
         engine.tc_linear_x3(w16[0], w16[1], f16[0], f16[1], w.b_ih, w.b_hh, y32=st.xproj, bias_row=True)
-        scratch = torch.empty(engine.tc_lstm_scratch_bytes(B, H), dtype=torch.uint8, device=dev)
-        engine.tc_lstm_seq_fwd(st.xproj, 0, w.w_hh, st.hs_ext, st.cs_ext, st.gates, T, B, H, scratch)
-        h16, hw16 = _split(hs_head), _split(w.head_w1)
-        engine.tc_linear_x3(h16[0], h16[1], hw16[0], hw16[1], w.head_b1, None, y32=st.hid, relu=True)
+        engine.tc_lstm_seq_fwd(st.xproj, 0, w.w_hh, st.hs_ext, st.cs_ext, st.gates, T, B, H, ws["scratch"])
+        engine.split_bf16(hs_head, hd16[0], hd16[1])
+        engine.split_bf16(w.head_w1, hw16[0], hw16[1])
+        engine.tc_linear_x3(hd16[0], hd16[1], hw16[0], hw16[1], w.head_b1, None, y32=st.hid, relu=True)
         engine.head_out(st.hid, w, st.q)
     else:
-        st.xproj = torch.empty((R, 4 * H), device=dev)
         engine.linear_fwd(st.feat, w.w_ih, w.b_ih, w.b_hh, st.xproj)
         engine.lstm_seq_fwd(st.xproj, w.w_hh, st.hs_ext, st.cs_ext, st.gates, T, B, H)
         engine.head_fwd(hs_head, w, st.hid, st.q)
