@@ -1,0 +1,328 @@
+// conv2 / conv3 forward (model.py:16-21,46) on tcgen05 tensor cores, "shifted window" form.
+//
+// The gather form in tc_conv.cu builds every A-tile row (a pixel's receptive field) from global
+// memory, so each activation is loaded and stored once per kernel offset that touches it (4x in
+// conv2, 9x in conv3) and the L1/shared data pipe, not the tensor pipe, bounds the kernel.  Here a
+// frame's activations go to shared memory ONCE, as an image whose row p is one input position
+// and whose 128-byte row holds that position's channels (bf16, hi and lo planes):
+//   conv2 (4x4, stride 2, 20x20x32): space-to-depth by 2 -> 10x10 positions x 128 channels
+//          (dy,dx,ci); the convolution becomes 2x2, stride 1: offsets (ky2,kx2) = row shifts
+//          {0, 1, 10, 11}; two planes of 64 channels (dy = 0 | dy = 1);
+//   conv3 (3x3, stride 1, 9x9x32): row p = [channels of position p | channels of position p+1];
+//          offsets (ky, kx in {0,1}) = row shift 9*ky over the whole row, (ky, 2) = shift 9*ky+2
+//          over its first half.
+// The A operand of every kernel offset is then THE SAME shared-memory image read through a UMMA
+// descriptor whose start address is advanced by `shift` rows (the descriptor's base-offset field
+// carries the row phase inside the 8-row swizzle atom).  One M = 128 tile per frame (rows past the
+// last position, and positions whose window leaves the frame, produce values nobody stores).
+// Arithmetic as in tc_conv.cu: error-compensated bf16x3, A_hi x [W_hi ; W_lo] as one N = 64 MMA
+// plus A_lo x W_hi, fp32 accumulation in TMEM (two buffers), bias + ReLU epilogue to NCHW fp32
+// (and for conv3 the bf16 (hi, lo) image of the features for the projection GEMM).
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace r2d2 {
+
+namespace {
+
+constexpr int SWC_PROD = 416;            // producer threads (13 warps)
+constexpr int SWC_ISSUERS = 1;           // MMA-issuing warps, each with its own accumulator slice (2: measured slower)
+constexpr int SWC_THREADS = SWC_PROD + 32 * SWC_ISSUERS + 128;
+
+__device__ __forceinline__ uint32_t swc_pack(float a, float b) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ float swc_round(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
+__device__ __forceinline__ uint32_t swc_off(int row, int chunk) {
+    return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((chunk ^ (row & 7)) << 4));
+}
+// K-major SWIZZLE_128B descriptor whose start may sit on any 128-byte row of a 1024-byte atom
+__device__ __forceinline__ uint64_t swc_desc(uint32_t smem_addr) {
+    return umma_desc_k_sw128(smem_addr);
+}
+
+template <int L> struct SwCfg;
+template <> struct SwCfg<2> {            // conv2
+    static constexpr int HIN = 20, GRID = 10, HOUT = 9, NPOS = 100, PLANES = 2, NKB = 8;
+    static constexpr int ROWS = 144, STAGES = 2, KTOT = 512, NITEMS = 800;
+    __device__ static constexpr int shift(int kb) { return ((kb >> 1) >> 1) * 10 + ((kb >> 1) & 1); }
+    __device__ static constexpr int plane(int kb) { return kb & 1; }
+    __device__ static constexpr int nk(int) { return 4; }
+    // element e of k-block kb  ->  index into W[co][ci][ky][kx] (row of 512), or -1
+    __host__ __device__ static constexpr int widx(int kb, int e) {
+        const int o = kb >> 1, dy = kb & 1, dx = e >> 5, ci = e & 31;
+        const int ky = 2 * (o >> 1) + dy, kx = 2 * (o & 1) + dx;
+        return ci * 16 + ky * 4 + kx;
+    }
+};
+template <> struct SwCfg<3> {            // conv3
+    static constexpr int HIN = 9, GRID = 9, HOUT = 7, NPOS = 81, PLANES = 1, NKB = 6;
+    static constexpr int ROWS = 152, STAGES = 3, KTOT = 288, NITEMS = 324;
+    __device__ static constexpr int shift(int kb) { return (kb >> 1) * 9 + 2 * (kb & 1); }
+    __device__ static constexpr int plane(int) { return 0; }
+    __device__ static constexpr int nk(int kb) { return (kb & 1) ? 2 : 4; }
+    __host__ __device__ static constexpr int widx(int kb, int e) {
+        const int ky = kb >> 1, part = kb & 1;
+        const int kx = part ? 2 : (e >> 5), ci = e & 31;
+        return (part && e >= 32) ? -1 : ci * 9 + ky * 3 + kx;
+    }
+};
+
+template <int L>
+__global__ void __launch_bounds__(SWC_THREADS, 1)
+tc_conv_sw_fwd_kernel(const float* __restrict__ in, const float* __restrict__ w,
+                      const float* __restrict__ bias, float* __restrict__ out, const int R,
+                      __nv_bfloat16* __restrict__ out_hi, __nv_bfloat16* __restrict__ out_lo) {
+    using C = SwCfg<L>;
+    constexpr int COUT = 32, P = C::HOUT * C::HOUT, NKB = C::NKB, STAGES = C::STAGES;
+    constexpr uint32_t PLANE = C::ROWS * 128;                    // one (hi or lo) plane of 64 channels
+    constexpr uint32_t STAGE_BYTES = C::PLANES * 2 * PLANE;      // [plane][hi|lo][ROWS x 128 B]
+    constexpr uint32_t W_KB = 2 * COUT * 128;                    // [W_hi rows ; W_lo rows] x 64 k
+    constexpr uint32_t SLICE = 2 * COUT;                         // [A_hi.W_hi + A_lo.W_hi | A_hi.W_lo]
+    constexpr uint32_t ACC_COLS = SWC_ISSUERS * SLICE;           // per buffer
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], acc_full[2], acc_empty[2];
+    __shared__ uint32_t tmem_slot;
+
+    const uint32_t raw = smem_u32(smem_raw);
+    uint8_t* base = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
+    uint8_t* w_s = base;
+    uint8_t* a_s = base + NKB * W_KB;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    constexpr int MMA_WARP = SWC_PROD / 32;
+
+    if (tid == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full_bar[s], SWC_PROD);
+            mbar_init(&empty_bar[s], SWC_ISSUERS);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&acc_full[b], SWC_ISSUERS);
+            mbar_init(&acc_empty[b], 128);
+        }
+        mbar_fence_init();
+    }
+    // resident weights, K permuted to the image's channel order, split into (hi, lo), swizzled
+    for (int i = tid; i < NKB * COUT * 8; i += blockDim.x) {
+        const int kb = i / (COUT * 8), i2 = i - kb * (COUT * 8);
+        const int co = i2 >> 3, c = i2 & 7;
+        float v[8], l[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const int wi = C::widx(kb, c * 8 + e);
+            const float x = wi >= 0 ? __ldg(w + (long long)co * C::KTOT + wi) : 0.f;
+            v[e] = x;
+            l[e] = x - swc_round(x);
+        }
+        const uint32_t off = (uint32_t)kb * W_KB + swc_off(co, c);
+        *reinterpret_cast<uint4*>(w_s + off) =
+            make_uint4(swc_pack(v[0], v[1]), swc_pack(v[2], v[3]), swc_pack(v[4], v[5]), swc_pack(v[6], v[7]));
+        *reinterpret_cast<uint4*>(w_s + off + COUT * 128) =
+            make_uint4(swc_pack(l[0], l[1]), swc_pack(l[2], l[3]), swc_pack(l[4], l[5]), swc_pack(l[6], l[7]));
+    }
+    // rows the producers never write must not hold NaN patterns that could trip nothing but
+    // debuggers; zero the whole ring once
+    for (uint32_t i = tid * 16; i < STAGES * STAGE_BYTES; i += blockDim.x * 16)
+        *reinterpret_cast<uint4*>(a_s + i) = make_uint4(0, 0, 0, 0);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    if (warp == MMA_WARP) tmem_alloc(&tmem_slot, 2 * ACC_COLS);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+
+    if (warp < MMA_WARP) {
+        // ================= producers: the frame's image, every activation loaded and stored once.
+        // The loads of frame f+1 are issued (into registers) before frame f is converted and
+        // stored, and before the wait for a free stage: the gather is memory-latency bound.
+        constexpr int NIT = (C::NITEMS + SWC_PROD - 1) / SWC_PROD;      // items per thread
+        constexpr int NV = L == 2 ? 16 : 8;                              // floats per item
+        float cur[NIT][NV], nxt[NIT][NV];
+        auto issue = [&](int fr, float (&dst)[NIT][NV]) {
+            if (fr >= R) return;
+            const float* src = in + (long long)fr * (32 * C::HIN * C::HIN);
+#pragma unroll
+            for (int j = 0; j < NIT; ++j) {
+                const int i = tid + j * SWC_PROD;
+                if (i < C::NITEMS) {
+                    if constexpr (L == 2) {
+                        // item = (dy, ci-chunk cc, position Y, X): 8 channels x (dx = 0, 1)
+                        const int X = i % 10, Y = (i / 10) % 10, cc = (i / 100) & 3, dy = i / 400;
+                        const float* q = src + (cc * 8) * 400 + (2 * Y + dy) * 20 + 2 * X;
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) {
+                            const float2 v = __ldg(reinterpret_cast<const float2*>(q + e * 400));
+                            dst[j][e] = v.x;
+                            dst[j][8 + e] = v.y;
+                        }
+                    } else {
+                        const int p = i % 81, cc = i / 81;
+                        const float* q = src + (cc * 8) * 81 + p;
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) dst[j][e] = __ldg(q + e * 81);
+                    }
+                }
+            }
+        };
+        auto chunk = [](const float* v, uint4& h, uint4& l) {
+            split_bf16x2(v[0], v[1], h.x, l.x); split_bf16x2(v[2], v[3], h.y, l.y);
+            split_bf16x2(v[4], v[5], h.z, l.z); split_bf16x2(v[6], v[7], h.w, l.w);
+        };
+        uint32_t it = 0;
+        issue(blockIdx.x, cur);
+        for (int fr = blockIdx.x; fr < R; fr += gridDim.x, ++it) {
+            const int s = it % STAGES;
+            issue(fr + gridDim.x, nxt);
+            mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
+            uint8_t* st = a_s + (size_t)s * STAGE_BYTES;
+#pragma unroll
+            for (int j = 0; j < NIT; ++j) {
+                const int i = tid + j * SWC_PROD;
+                if (i < C::NITEMS) {
+                    uint4 h, l;
+                    if constexpr (L == 2) {
+                        const int X = i % 10, Y = (i / 10) % 10, cc = (i / 100) & 3, dy = i / 400;
+                        const int row = Y * 10 + X;
+                        uint8_t* pl = st + (size_t)dy * 2 * PLANE;
+                        const uint32_t o0 = swc_off(row, cc), o1 = swc_off(row, 4 + cc);   // dx = 0 | dx = 1
+                        chunk(cur[j], h, l);
+                        *reinterpret_cast<uint4*>(pl + o0) = h;
+                        *reinterpret_cast<uint4*>(pl + PLANE + o0) = l;
+                        chunk(cur[j] + 8, h, l);
+                        *reinterpret_cast<uint4*>(pl + o1) = h;
+                        *reinterpret_cast<uint4*>(pl + PLANE + o1) = l;
+                    } else {
+                        // own row's first half, previous row's second half
+                        const int p = i % 81, cc = i / 81;
+                        chunk(cur[j], h, l);
+                        const uint32_t o0 = swc_off(p, cc);
+                        *reinterpret_cast<uint4*>(st + o0) = h;
+                        *reinterpret_cast<uint4*>(st + PLANE + o0) = l;
+                        if (p > 0) {
+                            const uint32_t o1 = swc_off(p - 1, 4 + cc);
+                            *reinterpret_cast<uint4*>(st + o1) = h;
+                            *reinterpret_cast<uint4*>(st + PLANE + o1) = l;
+                        }
+                    }
+                }
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            mbar_arrive(&full_bar[s]);
+#pragma unroll
+            for (int j = 0; j < NIT; ++j)
+#pragma unroll
+                for (int e = 0; e < NV; ++e) cur[j][e] = nxt[j][e];
+        }
+    } else if (warp < MMA_WARP + SWC_ISSUERS) {
+        // The k-blocks can be split between SWC_ISSUERS issuing warps, each accumulating into its
+        // own TMEM slice (the epilogue adds the slices).  Measured: two issuers are SLOWER (0.138
+        // vs 0.121 ms per conv2 launch) -- the bound is not the issue rate but the tensor core's
+        // operand fetch: every M=128 x K=16 MMA re-reads 4 KB of A from shared memory (~32 clk)
+        // for 16 clk of math at N = 64.
+        if (lane == 0) {
+            const int issuer = warp - MMA_WARP;
+            constexpr uint32_t idesc64 = umma_idesc_bf16(128, SLICE), idesc32 = umma_idesc_bf16(128, COUT);
+            constexpr int KB_PER = NKB / SWC_ISSUERS;
+            static_assert(NKB % SWC_ISSUERS == 0, "k-blocks split evenly between the issuers");
+            const uint32_t wb = smem_u32(w_s);
+            uint32_t it = 0;
+            for (int fr = blockIdx.x; fr < R; fr += gridDim.x, ++it) {
+                const uint32_t buf = it & 1, use = it >> 1;
+                const int s = it % STAGES;
+                mbar_wait(&acc_empty[buf], (use & 1) ^ 1);
+                mbar_wait(&full_bar[s], (it / STAGES) & 1);
+                tc_fence_after();
+                const uint32_t d = tmem_base + buf * ACC_COLS + issuer * SLICE;
+                const uint32_t st = smem_u32(a_s + (size_t)s * STAGE_BYTES);
+#pragma unroll
+                for (int kk = 0; kk < KB_PER; ++kk) {
+                    const int kb = issuer * KB_PER + kk;
+                    const uint32_t a_hi = st + C::plane(kb) * 2 * PLANE + C::shift(kb) * 128, a_lo = a_hi + PLANE;
+                    const uint32_t b_hl = wb + kb * W_KB;
+                    for (int k = 0; k < C::nk(kb); ++k) {
+                        umma_f16(d, swc_desc(a_hi + k * 32), umma_desc_k_sw128(b_hl + k * 32), idesc64, (kk | k) != 0);
+                        umma_f16(d, swc_desc(a_lo + k * 32), umma_desc_k_sw128(b_hl + k * 32), idesc32, 1);
+                    }
+                }
+                umma_commit(&empty_bar[s]);
+                umma_commit(&acc_full[buf]);
+            }
+        }
+    } else {
+        // ================= epilogue: one image row (TMEM lane) per thread, 32 channels
+        const int q = warp & 3;
+        const int m = q * 32 + lane;
+        const int Y = m / C::GRID, X = m - Y * C::GRID;
+        const bool valid = m < C::NPOS && Y < C::HOUT && X < C::HOUT;
+        const int p = Y * C::HOUT + X;
+        float bs[COUT];
+#pragma unroll
+        for (int co = 0; co < COUT; ++co) bs[co] = __ldg(bias + co);
+        uint32_t it = 0;
+        for (int fr = blockIdx.x; fr < R; fr += gridDim.x, ++it) {
+            const uint32_t buf = it & 1, use = it >> 1;
+            mbar_wait(&acc_full[buf], use & 1);
+            tc_fence_after();
+            uint32_t r[32], r2[32];
+            float acc[32];
+#pragma unroll
+            for (int i = 0; i < SWC_ISSUERS; ++i) {
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + buf * ACC_COLS + i * SLICE, r);
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + buf * ACC_COLS + i * SLICE + COUT, r2);
+                tmem_ld_wait();
+#pragma unroll
+                for (int co = 0; co < COUT; ++co) {
+                    const float v = __uint_as_float(r[co]) + __uint_as_float(r2[co]);
+                    acc[co] = i == 0 ? v : acc[co] + v;
+                }
+            }
+            tc_fence_before();
+            mbar_arrive(&acc_empty[buf]);
+            if (valid) {
+                const long long oo = (long long)fr * COUT * P + p;
+                if (out_hi) {
+#pragma unroll
+                    for (int co = 0; co < COUT; ++co) {
+                        const float x = fmaxf(acc[co] + bs[co], 0.f);
+                        const __nv_bfloat16 h = __float2bfloat16_rn(x);
+                        out[oo + (long long)co * P] = x;
+                        out_hi[oo + (long long)co * P] = h;
+                        out_lo[oo + (long long)co * P] = __float2bfloat16_rn(x - __bfloat162float(h));
+                    }
+                } else {
+#pragma unroll
+                    for (int co = 0; co < COUT; ++co)
+                        out[oo + (long long)co * P] = fmaxf(acc[co] + bs[co], 0.f);
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == MMA_WARP) tmem_dealloc(tmem_base, 2 * ACC_COLS);
+}
+
+}  // namespace
+
+template <int L>
+int launch_tc_conv_sw(const char* name, const float* in, const float* w, const float* b, float* out, int R,
+                      cudaStream_t st, __nv_bfloat16* out_hi, __nv_bfloat16* out_lo) {
+    using C = SwCfg<L>;
+    const int smem = C::NKB * 2 * 32 * 128 + C::STAGES * C::PLANES * 2 * C::ROWS * 128 + 1024;
+    auto kern = tc_conv_sw_fwd_kernel<L>;
+    R2D2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    int grid = sm_count();
+    if (grid > R) grid = R;
+    R2D2_LAUNCH(name, st, kern<<<grid, SWC_THREADS, smem, st>>>(in, w, b, out, R, out_hi, out_lo));
+    return R2D2_OK;
+}
+
+template int launch_tc_conv_sw<2>(const char*, const float*, const float*, const float*, float*, int, cudaStream_t,
+                                  __nv_bfloat16*, __nv_bfloat16*);
+template int launch_tc_conv_sw<3>(const char*, const float*, const float*, const float*, float*, int, cudaStream_t,
+                                  __nv_bfloat16*, __nv_bfloat16*);
+
+}  // namespace r2d2
