@@ -342,7 +342,8 @@ int r2d2_rmsprop_centered(float* param, const float* grad, float* square_avg, fl
  * complete early can be exchanged while the rest of the backward pass still runs.  Rank r reduces shard r of all gradients in rank order, applies centered RMSprop
  * (state only for its shard: r2d2_dp_shard_elems floats each) and writes the new parameters of its
  * shard into every rank's parameter buffer; the call returns (on the stream) when every rank's
- * shard has arrived.  All ranks must call it once per step; a missing rank traps after about a minute. */
+ * shard has arrived.  All ranks must call it once per step; a missing rank traps after
+ * R2D2_PEER_TIMEOUT_S seconds (environment, default 600). */
 int r2d2_peer_alloc(int64_t bytes, void** ptr, void* handle64);
 int r2d2_peer_open(const void* handle64, void** ptr);
 int r2d2_peer_close(void* ptr);

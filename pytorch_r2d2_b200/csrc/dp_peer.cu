@@ -16,10 +16,11 @@
 //
 // Buffers that peers touch (gradient, parameters, flags) are cudaMalloc'ed by this library and
 // exported with CUDA IPC handles (one process per GPU); step numbers only grow, so flags never
-// need resetting.  Every wait is bounded: a lost peer traps (after about a minute) instead of
-// hanging the GPU.
+// need resetting.  Every wait is bounded: a lost peer traps (after R2D2_PEER_TIMEOUT_S seconds,
+// default 600) instead of hanging the GPU.
 #include <cuda_runtime.h>
 
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -43,19 +44,23 @@ __device__ __forceinline__ int ld_acquire_sys(const int* p) {
     asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
-__device__ __forceinline__ void wait_flag(const int* p, int want) {
-    for (unsigned it = 0; it < (1u << 29); ++it) {
+// Bounded wait: `budget` polls of ~0.1-0.2 us each.  The bound exists so that a dead peer ends in
+// an error the host sees (the kernel traps) instead of a hung GPU; it is generous by default
+// (R2D2_PEER_TIMEOUT_S, default 600 s) because a healthy peer may legitimately be late -- a long
+// replay ingest, a checkpoint, a debugger.
+__device__ __forceinline__ void wait_flag(const int* p, int want, unsigned long long budget) {
+    for (unsigned long long it = 0; it < budget; ++it) {
         if (ld_acquire_sys(p) >= want) return;
         __nanosleep(100);
     }
-    __trap();   // about a minute: a peer died or never reached this step
+    __trap();
 }
 
 __global__ void __launch_bounds__(256)
 dp_reduce_rmsprop_kernel(DpPeers pe, const int rank, const int world, float* __restrict__ v,
                          float* __restrict__ mavg, const long long offset, const int bucket,
                          const long long n, const float lr, const float alpha, const float oma,
-                         const float eps, const float gscale) {
+                         const float eps, const float gscale, const unsigned long long wait_budget) {
     // a bucket = the slice [offset, offset + n) of the flat vectors with its own flag block, so
     // that slices whose gradients are complete early can be exchanged while the rest of the
     // backward pass is still running
@@ -72,7 +77,7 @@ dp_reduce_rmsprop_kernel(DpPeers pe, const int rank, const int world, float* __r
         st_release_sys(pe.flags[threadIdx.x] + rank, step);
     }
     // 2. wait for everybody's gradient
-    if (threadIdx.x < world) wait_flag(my + threadIdx.x, step);
+    if (threadIdx.x < world) wait_flag(my + threadIdx.x, step, wait_budget);
     __syncthreads();
 
     // 3. my shard: [lo, hi) in float4 units; the tail (n % 4) belongs to the last rank
@@ -146,7 +151,7 @@ dp_reduce_rmsprop_kernel(DpPeers pe, const int rank, const int world, float* __r
         if (threadIdx.x < world) {
             __threadfence_system();
             st_release_sys(pe.flags[threadIdx.x] + 32 + rank, step);
-            wait_flag(my + 32 + threadIdx.x, step);
+            wait_flag(my + 32 + threadIdx.x, step, wait_budget);
         }
         __syncthreads();
         if (threadIdx.x == 0) {
@@ -217,12 +222,19 @@ int r2d2_dp_reduce_rmsprop(int rank, int world, void* const* grads, void* const*
     const int cap = 2 * sm_count();          // every CTA must be resident while it waits for the peers
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
+    // polls cost ~0.15 us each (100 ns sleep + a system-scope load)
+    static const unsigned long long wait_budget = [] {
+        const char* e = getenv("R2D2_PEER_TIMEOUT_S");
+        double sec = e ? atof(e) : 600.0;
+        if (!(sec > 0)) sec = 600.0;
+        return (unsigned long long)(sec / 0.15e-6);
+    }();
     cudaStream_t st = as_stream(stream);
     R2D2_LAUNCH("dp_reduce_rmsprop_kernel", st,
                 dp_reduce_rmsprop_kernel<<<(unsigned)blocks, 256, 0, st>>>(
                     pe, rank, world, square_avg_shard, grad_avg_shard, (long long)offset, bucket,
                     (long long)n, (float)lr,
-                    (float)alpha, (float)(1.0 - alpha), (float)eps, (float)grad_scale));
+                    (float)alpha, (float)(1.0 - alpha), (float)eps, (float)grad_scale, wait_budget));
     return R2D2_OK;
 }
 
