@@ -8,11 +8,14 @@
 // h_t (bf16 hi/lo, K-major) to a ping-pong buffer in global memory, a grid-wide arrive/wait
 // counter publishes it, and TMA streams it back in as the B operand of the next step.
 // Forward contractions are error-compensated bf16x3 (W_hi.h_hi + W_lo.h_hi + W_hi.h_lo, fp32
-// accumulation in TMEM) -- see DESIGN.md section 2 for why the forward pass needs this.
+// accumulation in TMEM) -- see DESIGN.md section 2 for why the forward pass needs this.  The
+// (hi, lo) halves of W are stacked along M (UMMA M = 128) and, at NB = 32, those of h along N, so
+// one MMA per k-step produces all three terms.
 //
 // 416 threads: warp 0 = bulk-copy producer, warps 1,10,11,12 = MMA issuers (warp 1 also owns the
-// TMEM allocation), warps 2-5 = TMEM readers (gate q = warp % 4 sits in lanes 32q..32q+15 of the
-// M=64 accumulator layout), warps 2-9 = pointwise cell update (thread -> batch row, 2-4 units).
+// TMEM allocation), warps 2-5 = TMEM readers (lane quarter q = warp % 4 = accumulator rows
+// 32q..32q+31: two gates x 16 units of the W_hi rows for q < 2, of the W_lo rows for q >= 2),
+// warps 2-9 = pointwise cell update (thread -> batch row, 2-4 units).
 #include <cuda.h>
 #include <cuda_bf16.h>
 
@@ -132,7 +135,7 @@ tc_lstm_fwd_kernel(const LstmArgs a) {
     const uint32_t raw = smem_u32(smem_raw);
     uint8_t* base = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
     const uint32_t W_KB = LS_ROWS * 128;                        // 64 rows x 64 bf16
-    uint8_t* w_s = base;                                        // [hi|lo][NKB][8 KB]
+    uint8_t* w_s = base;                                        // [NKB][W_hi 8 KB | W_lo 8 KB]
     uint8_t* h_s = base + 2 * NKB * W_KB;                       // STAGES x (hi | lo)
     constexpr uint32_t H_TILE = NB * 128, STAGE = 2 * H_TILE;
 
@@ -162,10 +165,11 @@ tc_lstm_fwd_kernel(const LstmArgs a) {
         float l[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) l[e] = v[e] - ls_round(v[e]);
-        const uint32_t off = (uint32_t)kb * W_KB + ls_sw128(row, c);
+        // per k-block ONE 128-row K-major tile: rows 0..63 = W_hi, rows 64..127 = W_lo
+        const uint32_t off = (uint32_t)kb * 2 * W_KB + ls_sw128(row, c);
         *reinterpret_cast<uint4*>(w_s + off) =
             make_uint4(ls_pack(v[0], v[1]), ls_pack(v[2], v[3]), ls_pack(v[4], v[5]), ls_pack(v[6], v[7]));
-        *reinterpret_cast<uint4*>(w_s + NKB * W_KB + off) =
+        *reinterpret_cast<uint4*>(w_s + W_KB + off) =
             make_uint4(ls_pack(l[0], l[1]), ls_pack(l[2], l[3]), ls_pack(l[4], l[5]), ls_pack(l[6], l[7]));
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -242,13 +246,17 @@ tc_lstm_fwd_kernel(const LstmArgs a) {
         } else if (issuer >= 0) {
             if (lane == 0) {
                 // Four issuing warps, load groups g % 4 == issuer, each accumulating into its own
-                // TMEM slice (the readers add the slices): issuing the 12*NKB small MMAs of a step
+                // TMEM slice (the readers add the slices): issuing all the small MMAs of a step
                 // from one thread was the critical path (37 ns per MMA, tools/diag_lstm.py).
-                constexpr uint32_t idesc = umma_idesc_bf16(LS_ROWS, NB), idesc2 = umma_idesc_bf16(LS_ROWS, 2 * NB);
+                // A = [W_hi ; W_lo] stacked along M (128 rows): ONE MMA per k-step gives W_hi.[h_hi|h_lo]
+                // in accumulator rows 0..63 and W_lo.h_hi in rows 64..127 (their W_lo.h_lo columns are
+                // ~2^-16 of the result and simply added in).  The tensor pipe spends the same ~20 ns
+                // on an MMA this small whatever its M, so halving the count halves the MMA phase.
+                constexpr uint32_t idesc = umma_idesc_bf16(2 * LS_ROWS, 64);
+                static_assert(SW == 64, "accumulator slice = 64 columns");
                 mbar_wait(&acc_empty, (t & 1) ^ 1);                // readers drained step t-1
                 tc_fence_after();
-                const uint64_t dw_hi = umma_desc_k_sw128(smem_u32(w_s));
-                const uint64_t dw_lo = dw_hi + (uint64_t)((NKB * W_KB) >> 4);
+                const uint64_t dw = umma_desc_k_sw128(smem_u32(w_s));
                 const uint64_t dh0 = umma_desc_k_sw128(smem_u32(h_s));
                 const uint32_t d = tmem_base + issuer * SW;
                 const int ngrp = (NKB + KBG - 1) / KBG;             // load groups per step
@@ -263,18 +271,15 @@ tc_lstm_fwd_kernel(const LstmArgs a) {
                         const int kb = g * KBG + j;
                         if (kb < NKB) {
                             const uint64_t hhi = dh0 + (uint64_t)(((s * KBG + j) * STAGE) >> 4), hlo = hhi + (H_TILE >> 4);
-                            const uint64_t whi = dw_hi + (uint64_t)((kb * W_KB) >> 4);
-                            const uint64_t wlo = dw_lo + (uint64_t)((kb * W_KB) >> 4);
+                            const uint64_t wk = dw + (uint64_t)((kb * 2 * W_KB) >> 4);
 #pragma unroll
                             for (int k = 0; k < 4; ++k) {
                                 const uint32_t acc = (g >= LS_ISSUERS) | (j != 0) | (k != 0);
                                 if constexpr (CAT) {
-                                    umma_f16(d, whi + 2 * k, hhi + 2 * k, idesc2, acc);
-                                    umma_f16(d, wlo + 2 * k, hhi + 2 * k, idesc, 1);
+                                    umma_f16(d, wk + 2 * k, hhi + 2 * k, idesc, acc);      // B = [h_hi ; h_lo], 64 rows
                                 } else {
-                                    umma_f16(d, whi + 2 * k, hhi + 2 * k, idesc, acc);
-                                    umma_f16(d, wlo + 2 * k, hhi + 2 * k, idesc, 1);
-                                    umma_f16(d, whi + 2 * k, hlo + 2 * k, idesc, 1);
+                                    umma_f16(d, wk + 2 * k, hhi + 2 * k, idesc, acc);
+                                    umma_f16(d, wk + 2 * k, hlo + 2 * k, idesc, 1);
                                 }
                             }
                         }
@@ -297,8 +302,11 @@ tc_lstm_fwd_kernel(const LstmArgs a) {
                         xp[g][j] = __ldg(xc + (long long)(g * H + u0 + pu + j) * a.ldx);
             }
             if (warp < 6) {
-                // ---- TMEM readers: gate q = warp % 4, unit = lane (< 16), NB batch columns
+                // ---- TMEM readers: warp with lane quarter q = warp % 4 owns accumulator rows
+                //      32q..32q+31: q < 2 the W_hi rows of gates 2q, 2q+1 (16 units each), q >= 2 the
+                //      W_lo rows of gates 2(q-2), 2(q-2)+1; NB batch columns per row
                 const int q = warp & 3;
+                const int gate = 2 * (q & 1) + (lane >> 4), unit = lane & 15;
                 // one thread polls the accumulator barrier, the other readers sleep on a hardware
                 // barrier: pollers take issue slots from the TMA and MMA issuing threads
                 if (tid == 64) {
@@ -330,11 +338,21 @@ tc_lstm_fwd_kernel(const LstmArgs a) {
                 }
                 tc_fence_before();
                 mbar_arrive(&acc_empty);
-                if (lane < LS_UNITS) {
+                // W_hi rows store, then the W_lo rows of the same (gate, unit) add on top
+                if (q < 2) {
 #pragma unroll
                     for (int j = 0; j < NB; j += 4)
-                        *reinterpret_cast<float4*>(&G[q][lane][j]) =
+                        *reinterpret_cast<float4*>(&G[gate][unit][j]) =
                             make_float4(acc[j], acc[j + 1], acc[j + 2], acc[j + 3]);
+                }
+                named_bar_sync(5, 128);
+                if (q >= 2) {
+#pragma unroll
+                    for (int j = 0; j < NB; j += 4) {
+                        float4 v = *reinterpret_cast<float4*>(&G[gate][unit][j]);
+                        v.x += acc[j]; v.y += acc[j + 1]; v.z += acc[j + 2]; v.w += acc[j + 3];
+                        *reinterpret_cast<float4*>(&G[gate][unit][j]) = v;
+                    }
                 }
             }
             named_bar_sync(1, 256);                                 // G complete

@@ -21,7 +21,7 @@ PRIO_DRIFT = {"fp32": 0.1, "bf16": 0.4}
 # RMSprop divides by sqrt(v - m^2), which is ~0.22 |g| whatever the size of g, so every weight
 # moves ~lr/0.22 per step in the direction of a gradient SIGN that rounding can flip.
 MEDIAN_DRIFT = {"fp32": 2.5e-3, "bf16": 8e-3}
-MAX_DRIFT = {"fp32": 0.1, "bf16": 0.2}
+MAX_DRIFT = {"fp32": 0.1, "bf16": 0.3}      # bf16: 0.13 / 0.20 measured with two summation orders
 Q_DRIFT = {"fp32": 2e-2, "bf16": 1e-1}
 
 
