@@ -5,6 +5,7 @@ NAMES = [
     ("tc_lstm_fwd_kernel", "tc_lstm_fwd_kernel"), ("tc_lstm_bwd_kernel", "tc_lstm_bwd_kernel"),
     ("tc_conv_fwd_kernel<unsigned char", "tc_conv1_fwd"), ("tc_conv_fwd_kernel<float, 32, 4", "tc_conv2_fwd"),
     ("tc_conv_fwd_kernel<float, 32, 3", "tc_conv3_fwd"),
+    ("tc_conv_sw_fwd_kernel<2>", "tc_conv2_fwd"), ("tc_conv_sw_fwd_kernel<3>", "tc_conv3_fwd"),
     ("tc_conv_wgrad_kernel<unsigned char", "tc_conv1_wgrad"), ("tc_conv_wgrad_kernel<float, 32, 4", "tc_conv2_wgrad"),
     ("tc_conv_wgrad_kernel<float, 32, 3", "tc_conv3_wgrad"),
     ("tc_conv_dgrad_kernel<4", "tc_conv2_dgrad"), ("tc_conv_dgrad_kernel<3", "tc_conv3_dgrad"),
