@@ -1187,24 +1187,18 @@ int r2d2_tc_torso_fwd_tail(const float* a1, int R, const float* w2, const float*
                            void* stream) {
     R2D2_REQUIRE(a1 && w2 && b2 && w3 && b3 && a2 && feat && R > 0, "tc_torso_fwd_tail: bad args");
     R2D2_REQUIRE((feat_hi == nullptr) == (feat_lo == nullptr), "tc_torso_fwd_tail: feat_hi and feat_lo go together");
-    // conv2: shifted-window kernel (tc_conv_sw.cu: every activation staged once instead of once per
-    // kernel offset; 0.121 vs 0.149 ms per launch at 5440 frames).  conv3 (9 offsets of K = 32
-    // each) gains nothing from it (0.069 vs 0.065 ms) and keeps the gather kernel.
-    // R2D2_CONV_TAIL = "gather" | "sw" forces one form for both layers (A/B measurements).
-    static const int form = [] {
+    // shifted-window kernels (tc_conv_sw.cu): every activation staged once instead of once per
+    // kernel offset (per launch at 5440 frames: conv2 0.118 vs 0.149 ms, conv3 0.057 vs 0.065 ms).
+    // R2D2_CONV_TAIL=gather selects the gather kernels above (A/B measurements).
+    static const bool gather_form = [] {
         const char* e = getenv("R2D2_CONV_TAIL");
-        return !e ? 0 : e[0] == 'g' ? 1 : 2;
+        return e && e[0] == 'g';
     }();
-    if (form != 1) {
+    if (!gather_form) {
         int rc = launch_tc_conv_sw<2>("tc_conv2_fwd", a1, w2, b2, a2, R, as_stream(stream), nullptr, nullptr);
         if (rc) return rc;
-        if (form == 2)
-            return launch_tc_conv_sw<3>("tc_conv3_fwd", a2, w3, b3, feat, R, as_stream(stream),
-                                        static_cast<__nv_bfloat16*>(feat_hi), static_cast<__nv_bfloat16*>(feat_lo));
-        return launch_tc_conv<float, 32, 3, 9, 7, 1>("tc_conv3_fwd", a2, FrameMap{0, 0, 0, 2592}, w3, b3, feat,
-                                                     R, 1.f, as_stream(stream),
-                                                     static_cast<__nv_bfloat16*>(feat_hi),
-                                                     static_cast<__nv_bfloat16*>(feat_lo));
+        return launch_tc_conv_sw<3>("tc_conv3_fwd", a2, w3, b3, feat, R, as_stream(stream),
+                                    static_cast<__nv_bfloat16*>(feat_hi), static_cast<__nv_bfloat16*>(feat_lo));
     }
     int rc = launch_tc_conv<float, 32, 4, 20, 9, 2>("tc_conv2_fwd", a1, FrameMap{0, 0, 0, 12800}, w2, b2, a2,
                                                     R, 1.f, as_stream(stream));

@@ -27,8 +27,26 @@ namespace r2d2 {
 
 namespace {
 
+// diagnostics: build with -DSWC_TRACE to record globaltimer stamps of CTA 0's first 32 frames
+// (slot: 0 stage free seen by producer thread 0, 1 producer arrived, 2 issuer 0 starts, 3 issuer 0
+// done issuing, 4 issuer 1 done issuing, 5 epilogue sees the accumulator, 6 epilogue stores done)
+#ifdef SWC_TRACE
+__device__ long long g_swc_trace[32 * 8];
+#define SWC_STAMP(slot)                                                                      \
+    do {                                                                                     \
+        if (blockIdx.x == 0 && it < 32 && (threadIdx.x & 31) == 0 &&                          \
+            (threadIdx.x == 0 || threadIdx.x >= SWC_PROD)) {                                 \
+            long long t__;                                                                   \
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t__));                          \
+            g_swc_trace[it * 8 + (slot)] = t__;                                              \
+        }                                                                                    \
+    } while (0)
+#else
+#define SWC_STAMP(slot) do { } while (0)
+#endif
+
 constexpr int SWC_PROD = 416;            // producer threads (13 warps)
-constexpr int SWC_ISSUERS = 1;           // MMA-issuing warps, each with its own accumulator slice (2: measured slower)
+constexpr int SWC_ISSUERS = 2;           // MMA-issuing warps: warp 0 the A_hi MMAs, warp 1 the A_lo MMAs
 constexpr int SWC_THREADS = SWC_PROD + 32 * SWC_ISSUERS + 128;
 
 __device__ __forceinline__ uint32_t swc_pack(float a, float b) {
@@ -81,8 +99,8 @@ tc_conv_sw_fwd_kernel(const float* __restrict__ in, const float* __restrict__ w,
     constexpr uint32_t PLANE = C::ROWS * 128;                    // one (hi or lo) plane of 64 channels
     constexpr uint32_t STAGE_BYTES = C::PLANES * 2 * PLANE;      // [plane][hi|lo][ROWS x 128 B]
     constexpr uint32_t W_KB = 2 * COUT * 128;                    // [W_hi rows ; W_lo rows] x 64 k
-    constexpr uint32_t SLICE = 2 * COUT;                         // [A_hi.W_hi + A_lo.W_hi | A_hi.W_lo]
-    constexpr uint32_t ACC_COLS = SWC_ISSUERS * SLICE;           // per buffer
+    // accumulator columns of one buffer: [A_hi.W_hi | A_hi.W_lo | A_lo.W_hi] (the epilogue adds them)
+    constexpr uint32_t SLICE = 2 * COUT, ACC_COLS = 128;
     extern __shared__ uint8_t smem_raw[];
     __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], acc_full[2], acc_empty[2];
     __shared__ uint32_t tmem_slot;
@@ -177,6 +195,7 @@ tc_conv_sw_fwd_kernel(const float* __restrict__ in, const float* __restrict__ w,
             const int s = it % STAGES;
             issue(fr + gridDim.x, nxt);
             mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
+            SWC_STAMP(0);
             uint8_t* st = a_s + (size_t)s * STAGE_BYTES;
 #pragma unroll
             for (int j = 0; j < NIT; ++j) {
@@ -211,22 +230,20 @@ tc_conv_sw_fwd_kernel(const float* __restrict__ in, const float* __restrict__ w,
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             mbar_arrive(&full_bar[s]);
+            SWC_STAMP(1);
 #pragma unroll
             for (int j = 0; j < NIT; ++j)
 #pragma unroll
                 for (int e = 0; e < NV; ++e) cur[j][e] = nxt[j][e];
         }
     } else if (warp < MMA_WARP + SWC_ISSUERS) {
-        // The k-blocks can be split between SWC_ISSUERS issuing warps, each accumulating into its
-        // own TMEM slice (the epilogue adds the slices).  Measured: two issuers are SLOWER (0.138
-        // vs 0.121 ms per conv2 launch) -- the bound is not the issue rate but the tensor core's
-        // operand fetch: every M=128 x K=16 MMA re-reads 4 KB of A from shared memory (~32 clk)
-        // for 16 clk of math at N = 64.
+        // One thread issues a tcgen05.mma every ~74 clk whatever its shape (tools/ubench/mma_rate.cu)
+        // and a frame takes 64 of them, so the issue is split between two warps: warp 0 issues the
+        // A_hi MMAs (N = 64 against [W_hi ; W_lo]), warp 1 the A_lo MMAs (N = 32 against W_hi), each
+        // into its own accumulator columns.
         if (lane == 0) {
             const int issuer = warp - MMA_WARP;
             constexpr uint32_t idesc64 = umma_idesc_bf16(128, SLICE), idesc32 = umma_idesc_bf16(128, COUT);
-            constexpr int KB_PER = NKB / SWC_ISSUERS;
-            static_assert(NKB % SWC_ISSUERS == 0, "k-blocks split evenly between the issuers");
             const uint32_t wb = smem_u32(w_s);
             uint32_t it = 0;
             for (int fr = blockIdx.x; fr < R; fr += gridDim.x, ++it) {
@@ -235,20 +252,32 @@ tc_conv_sw_fwd_kernel(const float* __restrict__ in, const float* __restrict__ w,
                 mbar_wait(&acc_empty[buf], (use & 1) ^ 1);
                 mbar_wait(&full_bar[s], (it / STAGES) & 1);
                 tc_fence_after();
-                const uint32_t d = tmem_base + buf * ACC_COLS + issuer * SLICE;
+                if (issuer == 0) SWC_STAMP(2);
                 const uint32_t st = smem_u32(a_s + (size_t)s * STAGE_BYTES);
+                if (issuer == 0) {
+                    const uint32_t d = tmem_base + buf * ACC_COLS;
 #pragma unroll
-                for (int kk = 0; kk < KB_PER; ++kk) {
-                    const int kb = issuer * KB_PER + kk;
-                    const uint32_t a_hi = st + C::plane(kb) * 2 * PLANE + C::shift(kb) * 128, a_lo = a_hi + PLANE;
-                    const uint32_t b_hl = wb + kb * W_KB;
-                    for (int k = 0; k < C::nk(kb); ++k) {
-                        umma_f16(d, swc_desc(a_hi + k * 32), umma_desc_k_sw128(b_hl + k * 32), idesc64, (kk | k) != 0);
-                        umma_f16(d, swc_desc(a_lo + k * 32), umma_desc_k_sw128(b_hl + k * 32), idesc32, 1);
+                    for (int kb = 0; kb < NKB; ++kb) {
+                        const uint32_t a_hi = st + C::plane(kb) * 2 * PLANE + C::shift(kb) * 128;
+                        const uint32_t b_hl = wb + kb * W_KB;
+#pragma unroll
+                        for (int k = 0; k < C::nk(kb); ++k)
+                            umma_f16(d, swc_desc(a_hi + k * 32), umma_desc_k_sw128(b_hl + k * 32), idesc64, (kb | k) != 0);
+                    }
+                } else {
+                    const uint32_t d = tmem_base + buf * ACC_COLS + SLICE;
+#pragma unroll
+                    for (int kb = 0; kb < NKB; ++kb) {
+                        const uint32_t a_lo = st + C::plane(kb) * 2 * PLANE + C::shift(kb) * 128 + PLANE;
+                        const uint32_t b_hl = wb + kb * W_KB;
+#pragma unroll
+                        for (int k = 0; k < C::nk(kb); ++k)
+                            umma_f16(d, swc_desc(a_lo + k * 32), umma_desc_k_sw128(b_hl + k * 32), idesc32, (kb | k) != 0);
                     }
                 }
                 umma_commit(&empty_bar[s]);
                 umma_commit(&acc_full[buf]);
+                if (issuer == 0) SWC_STAMP(3); else SWC_STAMP(4);
             }
         }
     } else {
@@ -265,20 +294,17 @@ tc_conv_sw_fwd_kernel(const float* __restrict__ in, const float* __restrict__ w,
         for (int fr = blockIdx.x; fr < R; fr += gridDim.x, ++it) {
             const uint32_t buf = it & 1, use = it >> 1;
             mbar_wait(&acc_full[buf], use & 1);
+            SWC_STAMP(5);
             tc_fence_after();
-            uint32_t r[32], r2[32];
+            uint32_t r[32], r2[32], r3[32];
             float acc[32];
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + buf * ACC_COLS, r);
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + buf * ACC_COLS + COUT, r2);
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + buf * ACC_COLS + SLICE, r3);
+            tmem_ld_wait();
 #pragma unroll
-            for (int i = 0; i < SWC_ISSUERS; ++i) {
-                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + buf * ACC_COLS + i * SLICE, r);
-                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + buf * ACC_COLS + i * SLICE + COUT, r2);
-                tmem_ld_wait();
-#pragma unroll
-                for (int co = 0; co < COUT; ++co) {
-                    const float v = __uint_as_float(r[co]) + __uint_as_float(r2[co]);
-                    acc[co] = i == 0 ? v : acc[co] + v;
-                }
-            }
+            for (int co = 0; co < COUT; ++co)
+                acc[co] = (__uint_as_float(r[co]) + __uint_as_float(r2[co])) + __uint_as_float(r3[co]);
             tc_fence_before();
             mbar_arrive(&acc_empty[buf]);
             if (valid) {
@@ -298,6 +324,7 @@ tc_conv_sw_fwd_kernel(const float* __restrict__ in, const float* __restrict__ w,
                         out[oo + (long long)co * P] = fmaxf(acc[co] + bs[co], 0.f);
                 }
             }
+            if (q == 3) SWC_STAMP(6);
         }
     }
     tc_fence_before();
@@ -326,3 +353,9 @@ template int launch_tc_conv_sw<3>(const char*, const float*, const float*, const
                                   __nv_bfloat16*, __nv_bfloat16*);
 
 }  // namespace r2d2
+
+#ifdef SWC_TRACE
+extern "C" int r2d2_dbg_swc_trace(long long* host) {
+    return (int)cudaMemcpyFromSymbol(host, r2d2::g_swc_trace, sizeof(long long) * 32 * 8);
+}
+#endif
