@@ -12,9 +12,10 @@
 //          offsets (ky, kx in {0,1}) = row shift 9*ky over the whole row, (ky, 2) = shift 9*ky+2
 //          over its first half.
 // The A operand of every kernel offset is then THE SAME shared-memory image read through a UMMA
-// descriptor whose start address is advanced by `shift` rows (the descriptor's base-offset field
-// carries the row phase inside the 8-row swizzle atom).  One M = 128 tile per frame (rows past the
-// last position, and positions whose window leaves the frame, produce values nobody stores).
+// descriptor whose start address is advanced by `shift` rows (no base-offset field needed: the
+// swizzle is a function of the absolute shared-memory address).  One
+// M = 128 tile per frame (rows past the last position, and positions whose window leaves the
+// frame, produce values nobody stores).
 // Arithmetic as in tc_conv.cu: error-compensated bf16x3, A_hi x [W_hi ; W_lo] as one N = 64 MMA
 // plus A_lo x W_hi, fp32 accumulation in TMEM (two buffers), bias + ReLU epilogue to NCHW fp32
 // (and for conv3 the bf16 (hi, lo) image of the features for the projection GEMM).
@@ -31,14 +32,14 @@ namespace {
 // (slot: 0 stage free seen by producer thread 0, 1 producer arrived, 2 issuer 0 starts, 3 issuer 0
 // done issuing, 4 issuer 1 done issuing, 5 epilogue sees the accumulator, 6 epilogue stores done)
 #ifdef SWC_TRACE
-__device__ long long g_swc_trace[32 * 8];
+__device__ long long g_swc_trace[2 * 32 * 8];     // [layer - 2][frame][slot]
 #define SWC_STAMP(slot)                                                                      \
     do {                                                                                     \
         if (blockIdx.x == 0 && it < 32 && (threadIdx.x & 31) == 0 &&                          \
             (threadIdx.x == 0 || threadIdx.x >= SWC_PROD)) {                                 \
             long long t__;                                                                   \
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t__));                          \
-            g_swc_trace[it * 8 + (slot)] = t__;                                              \
+            g_swc_trace[(L - 2) * 256 + it * 8 + (slot)] = t__;                                              \
         }                                                                                    \
     } while (0)
 #else
@@ -65,7 +66,7 @@ __device__ __forceinline__ uint64_t swc_desc(uint32_t smem_addr) {
 template <int L> struct SwCfg;
 template <> struct SwCfg<2> {            // conv2
     static constexpr int HIN = 20, GRID = 10, HOUT = 9, NPOS = 100, PLANES = 2, NKB = 8;
-    static constexpr int ROWS = 144, STAGES = 2, KTOT = 512, NITEMS = 800;
+    static constexpr int ROWS = 104, STAGES = 3, KTOT = 512, NITEMS = 800;
     __device__ static constexpr int shift(int kb) { return ((kb >> 1) >> 1) * 10 + ((kb >> 1) & 1); }
     __device__ static constexpr int plane(int kb) { return kb & 1; }
     __device__ static constexpr int nk(int) { return 4; }
@@ -78,7 +79,7 @@ template <> struct SwCfg<2> {            // conv2
 };
 template <> struct SwCfg<3> {            // conv3
     static constexpr int HIN = 9, GRID = 9, HOUT = 7, NPOS = 81, PLANES = 1, NKB = 6;
-    static constexpr int ROWS = 152, STAGES = 3, KTOT = 288, NITEMS = 324;
+    static constexpr int ROWS = 88, STAGES = 4, KTOT = 288, NITEMS = 324;
     __device__ static constexpr int shift(int kb) { return (kb >> 1) * 9 + 2 * (kb & 1); }
     __device__ static constexpr int plane(int) { return 0; }
     __device__ static constexpr int nk(int kb) { return (kb & 1) ? 2 : 4; }
@@ -96,7 +97,12 @@ tc_conv_sw_fwd_kernel(const float* __restrict__ in, const float* __restrict__ w,
                       __nv_bfloat16* __restrict__ out_hi, __nv_bfloat16* __restrict__ out_lo) {
     using C = SwCfg<L>;
     constexpr int COUT = 32, P = C::HOUT * C::HOUT, NKB = C::NKB, STAGES = C::STAGES;
-    constexpr uint32_t PLANE = C::ROWS * 128;                    // one (hi or lo) plane of 64 channels
+    // One (hi or lo) plane of 64 channels: ROWS = the positions rounded up to whole 8-row swizzle
+    // atoms.  An M = 128 tile read at a row shift runs past the plane's end into whatever follows
+    // (the next plane, the next stage, and behind the ring the resident weights): initialised,
+    // finite bf16 data that only feed accumulator rows nobody stores -- so the planes carry no
+    // padding and a third stage fits.
+    constexpr uint32_t PLANE = C::ROWS * 128;
     constexpr uint32_t STAGE_BYTES = C::PLANES * 2 * PLANE;      // [plane][hi|lo][ROWS x 128 B]
     constexpr uint32_t W_KB = 2 * COUT * 128;                    // [W_hi rows ; W_lo rows] x 64 k
     // accumulator columns of one buffer: [A_hi.W_hi | A_hi.W_lo | A_lo.W_hi] (the epilogue adds them)
@@ -107,8 +113,8 @@ tc_conv_sw_fwd_kernel(const float* __restrict__ in, const float* __restrict__ w,
 
     const uint32_t raw = smem_u32(smem_raw);
     uint8_t* base = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
-    uint8_t* w_s = base;
-    uint8_t* a_s = base + NKB * W_KB;
+    uint8_t* a_s = base;                                         // ring first, weights behind it (see PLANE)
+    uint8_t* w_s = base + STAGES * STAGE_BYTES;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     constexpr int MMA_WARP = SWC_PROD / 32;
 
@@ -189,13 +195,11 @@ tc_conv_sw_fwd_kernel(const float* __restrict__ in, const float* __restrict__ w,
             split_bf16x2(v[0], v[1], h.x, l.x); split_bf16x2(v[2], v[3], h.y, l.y);
             split_bf16x2(v[4], v[5], h.z, l.z); split_bf16x2(v[6], v[7], h.w, l.w);
         };
+        // convert + store one frame's registers into stage s (a lambda so that the two register
+        // sets of the ping-pong below are used in place: a copy `cur = nxt` would wait for the
+        // loads it copies, i.e. put the whole memory latency back inside every iteration)
         uint32_t it = 0;
-        issue(blockIdx.x, cur);
-        for (int fr = blockIdx.x; fr < R; fr += gridDim.x, ++it) {
-            const int s = it % STAGES;
-            issue(fr + gridDim.x, nxt);
-            mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
-            SWC_STAMP(0);
+        auto store = [&](const float (&cur)[NIT][NV], int s) {
             uint8_t* st = a_s + (size_t)s * STAGE_BYTES;
 #pragma unroll
             for (int j = 0; j < NIT; ++j) {
@@ -228,19 +232,33 @@ tc_conv_sw_fwd_kernel(const float* __restrict__ in, const float* __restrict__ w,
                     }
                 }
             }
+            SWC_STAMP(7);
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             mbar_arrive(&full_bar[s]);
+        };
+        issue(blockIdx.x, cur);
+        for (int fr = blockIdx.x; fr < R; fr += 2 * gridDim.x) {
+            issue(fr + gridDim.x, nxt);
+            mbar_wait(&empty_bar[it % STAGES], ((it / STAGES) & 1) ^ 1);
+            SWC_STAMP(0);
+            store(cur, it % STAGES);
             SWC_STAMP(1);
-#pragma unroll
-            for (int j = 0; j < NIT; ++j)
-#pragma unroll
-                for (int e = 0; e < NV; ++e) cur[j][e] = nxt[j][e];
+            ++it;
+            if (fr + gridDim.x >= R) break;
+            issue(fr + 2 * gridDim.x, cur);
+            mbar_wait(&empty_bar[it % STAGES], ((it / STAGES) & 1) ^ 1);
+            SWC_STAMP(0);
+            store(nxt, it % STAGES);
+            SWC_STAMP(1);
+            ++it;
         }
     } else if (warp < MMA_WARP + SWC_ISSUERS) {
-        // One thread issues a tcgen05.mma every ~74 clk whatever its shape (tools/ubench/mma_rate.cu)
-        // and a frame takes 64 of them, so the issue is split between two warps: warp 0 issues the
-        // A_hi MMAs (N = 64 against [W_hi ; W_lo]), warp 1 the A_lo MMAs (N = 32 against W_hi), each
-        // into its own accumulator columns.
+        // One thread issues a tcgen05.mma every ~74 clk whatever its shape and a frame takes 64 of
+        // them, so the issue is split between two warps: warp 0 issues the A_hi MMAs (N = 64 against
+        // [W_hi ; W_lo]), warp 1 the A_lo MMAs (N = 32 against W_hi), each into its own accumulator
+        // columns.  With two issuers the tensor pipe itself is the limit: ~45 clk per M=128 MMA at
+        // N <= 64 (tools/ubench/mma_rate.cu), i.e. ~1.5 us of MMA time per frame; the traced phases
+        // (tools/diag_conv_sw.py) show the producers' 51 KB of loads per frame taking about as long.
         if (lane == 0) {
             const int issuer = warp - MMA_WARP;
             constexpr uint32_t idesc64 = umma_idesc_bf16(128, SLICE), idesc32 = umma_idesc_bf16(128, COUT);
@@ -339,6 +357,7 @@ int launch_tc_conv_sw(const char* name, const float* in, const float* w, const f
                       cudaStream_t st, __nv_bfloat16* out_hi, __nv_bfloat16* out_lo) {
     using C = SwCfg<L>;
     const int smem = C::NKB * 2 * 32 * 128 + C::STAGES * C::PLANES * 2 * C::ROWS * 128 + 1024;
+    static_assert(C::NKB * 2 * 32 * 128 >= 48 * 128, "the weights behind the ring absorb the over-read");
     auto kern = tc_conv_sw_fwd_kernel<L>;
     R2D2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     int grid = sm_count();
@@ -356,6 +375,6 @@ template int launch_tc_conv_sw<3>(const char*, const float*, const float*, const
 
 #ifdef SWC_TRACE
 extern "C" int r2d2_dbg_swc_trace(long long* host) {
-    return (int)cudaMemcpyFromSymbol(host, r2d2::g_swc_trace, sizeof(long long) * 32 * 8);
+    return (int)cudaMemcpyFromSymbol(host, r2d2::g_swc_trace, sizeof(long long) * 2 * 32 * 8);
 }
 #endif

@@ -15,12 +15,13 @@ for _ in range(3):
     engine.torso_fwd_tail(a1, w, a2, feat)
 torch.cuda.synchronize()
 lib = _lib.load()
-buf = (ctypes.c_longlong * 256)()
+buf = (ctypes.c_longlong * 512)()
 rc = lib.r2d2_dbg_swc_trace(buf)
-t = torch.tensor(list(buf), dtype=torch.float64).reshape(32, 8)
-names = ["stage free (producer)", "producer arrived", "issuer0 start", "issuer0 issued", "issuer1 issued", "epilogue sees acc", "epilogue done"]
-print("NOTE: the trace holds the LAST launch that wrote it (conv3 overwrites conv2 when the tail runs both sw kernels)")
-base = t[4:28, 0]
-print(f"frame period {float((t[5:28,0]-t[4:27,0]).mean()):.0f} ns")
-for i, n in enumerate(names):
-    print(f"  {n:>24s}  +{float((t[4:28, i] - base).mean()):8.0f} ns after 'stage free' of the same frame")
+names = ["stage free (producer)", "producer arrived", "issuer0 start", "issuer0 issued", "issuer1 issued", "epilogue sees acc", "epilogue done", "producer stores issued"]
+for layer in (2, 3):
+    t = torch.tensor(list(buf), dtype=torch.float64).reshape(2, 32, 8)[layer - 2]
+    print(f"conv{layer}: frame period {float((t[5:28,0]-t[4:27,0]).mean()):.0f} ns (CTA 0, frames 4..27)")
+    for i, n in enumerate(names):
+        # stamps of frame f relative to the moment ITS stage was seen free by the producer
+        print(f"  {n:>24s}  +{float((t[4:28, i] - t[4:28, 0]).mean()):8.0f} ns")
+    print(f"  issuer0: start -> issued {float((t[4:28,3]-t[4:28,2]).mean()):.0f} ns; acc seen -> epilogue done {float((t[4:28,6]-t[4:28,5]).mean()):.0f} ns")
