@@ -66,7 +66,7 @@ __device__ __forceinline__ uint64_t swc_desc(uint32_t smem_addr) {
 template <int L> struct SwCfg;
 template <> struct SwCfg<2> {            // conv2
     static constexpr int HIN = 20, GRID = 10, HOUT = 9, NPOS = 100, PLANES = 2, NKB = 8;
-    static constexpr int ROWS = 104, STAGES = 3, KTOT = 512, NITEMS = 800;
+    static constexpr int ROWS = 104, STAGES = 2, KTOT = 512, NITEMS = 800, NRAW = 1;
     __device__ static constexpr int shift(int kb) { return ((kb >> 1) >> 1) * 10 + ((kb >> 1) & 1); }
     __device__ static constexpr int plane(int kb) { return kb & 1; }
     __device__ static constexpr int nk(int) { return 4; }
@@ -79,7 +79,7 @@ template <> struct SwCfg<2> {            // conv2
 };
 template <> struct SwCfg<3> {            // conv3
     static constexpr int HIN = 9, GRID = 9, HOUT = 7, NPOS = 81, PLANES = 1, NKB = 6;
-    static constexpr int ROWS = 88, STAGES = 4, KTOT = 288, NITEMS = 324;
+    static constexpr int ROWS = 88, STAGES = 4, KTOT = 288, NITEMS = 324, NRAW = 4;
     __device__ static constexpr int shift(int kb) { return (kb >> 1) * 9 + 2 * (kb & 1); }
     __device__ static constexpr int plane(int) { return 0; }
     __device__ static constexpr int nk(int kb) { return (kb & 1) ? 2 : 4; }
@@ -108,13 +108,19 @@ tc_conv_sw_fwd_kernel(const float* __restrict__ in, const float* __restrict__ w,
     // accumulator columns of one buffer: [A_hi.W_hi | A_hi.W_lo | A_lo.W_hi] (the epilogue adds them)
     constexpr uint32_t SLICE = 2 * COUT, ACC_COLS = 128;
     extern __shared__ uint8_t smem_raw[];
-    __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], acc_full[2], acc_empty[2];
+    __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], acc_full[2], acc_empty[2], raw_full[C::NRAW], raw_empty[C::NRAW];
     __shared__ uint32_t tmem_slot;
+    constexpr uint32_t FRAME_BYTES = 32 * C::HIN * C::HIN * 4;   // one frame of fp32 NCHW activations
 
     const uint32_t raw = smem_u32(smem_raw);
     uint8_t* base = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
     uint8_t* a_s = base;                                         // ring first, weights behind it (see PLANE)
     uint8_t* w_s = base + STAGES * STAGE_BYTES;
+    // raw fp32 frames, each brought in by ONE bulk copy issued NRAW frames ahead: the producers read
+    // shared memory instead of waiting for global loads (conv2: 51 KB per frame, room for one
+    // buffer only, so its fetch overlaps the MMAs of the previous frame but not its conversion)
+    constexpr int NRAW = C::NRAW;
+    const float* raw_s = reinterpret_cast<const float*>(w_s + NKB * W_KB);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     constexpr int MMA_WARP = SWC_PROD / 32;
 
@@ -126,6 +132,10 @@ tc_conv_sw_fwd_kernel(const float* __restrict__ in, const float* __restrict__ w,
         for (int b = 0; b < 2; ++b) {
             mbar_init(&acc_full[b], SWC_ISSUERS);
             mbar_init(&acc_empty[b], 128);
+        }
+        for (int r = 0; r < NRAW; ++r) {
+            mbar_init(&raw_full[r], 1);
+            mbar_init(&raw_empty[r], SWC_PROD);
         }
         mbar_fence_init();
     }
@@ -159,47 +169,33 @@ tc_conv_sw_fwd_kernel(const float* __restrict__ in, const float* __restrict__ w,
     const uint32_t tmem_base = tmem_slot;
 
     if (warp < MMA_WARP) {
-        // ================= producers: the frame's image, every activation loaded and stored once.
-        // The loads of frame f+1 are issued (into registers) before frame f is converted and
-        // stored, and before the wait for a free stage: the gather is memory-latency bound.
-        constexpr int NIT = (C::NITEMS + SWC_PROD - 1) / SWC_PROD;      // items per thread
-        constexpr int NV = L == 2 ? 16 : 8;                              // floats per item
-        float cur[NIT][NV], nxt[NIT][NV];
-        auto issue = [&](int fr, float (&dst)[NIT][NV]) {
-            if (fr >= R) return;
-            const float* src = in + (long long)fr * (32 * C::HIN * C::HIN);
-#pragma unroll
-            for (int j = 0; j < NIT; ++j) {
-                const int i = tid + j * SWC_PROD;
-                if (i < C::NITEMS) {
-                    if constexpr (L == 2) {
-                        // item = (dy, ci-chunk cc, position Y, X): 8 channels x (dx = 0, 1)
-                        const int X = i % 10, Y = (i / 10) % 10, cc = (i / 100) & 3, dy = i / 400;
-                        const float* q = src + (cc * 8) * 400 + (2 * Y + dy) * 20 + 2 * X;
-#pragma unroll
-                        for (int e = 0; e < 8; ++e) {
-                            const float2 v = __ldg(reinterpret_cast<const float2*>(q + e * 400));
-                            dst[j][e] = v.x;
-                            dst[j][8 + e] = v.y;
-                        }
-                    } else {
-                        const int p = i % 81, cc = i / 81;
-                        const float* q = src + (cc * 8) * 81 + p;
-#pragma unroll
-                        for (int e = 0; e < 8; ++e) dst[j][e] = __ldg(q + e * 81);
-                    }
-                }
-            }
+        // ================= producers: raw frame (shared memory, via bulk copy) -> the frame's image;
+        // every activation is read and stored once.  Thread 0 also drives the bulk copies: frame
+        // f+1 is requested as soon as every producer has finished reading frame f.
+        uint32_t it = 0;
+        // one frame = one bulk copy (splitting it into 8 requests changed nothing)
+        auto fetch = [&](long long f, int r) {
+            mbar_expect_tx(&raw_full[r], FRAME_BYTES);
+            bulk_g2s(const_cast<float*>(raw_s) + (size_t)r * (FRAME_BYTES / 4), in + f * (FRAME_BYTES / 4), FRAME_BYTES,
+                     &raw_full[r]);
         };
+        if (tid == 0) {
+            for (int r = 0; r < NRAW; ++r) {
+                const long long f = (long long)blockIdx.x + (long long)r * gridDim.x;
+                if (f < R) fetch(f, r);
+            }
+        }
         auto chunk = [](const float* v, uint4& h, uint4& l) {
             split_bf16x2(v[0], v[1], h.x, l.x); split_bf16x2(v[2], v[3], h.y, l.y);
             split_bf16x2(v[4], v[5], h.z, l.z); split_bf16x2(v[6], v[7], h.w, l.w);
         };
-        // convert + store one frame's registers into stage s (a lambda so that the two register
-        // sets of the ping-pong below are used in place: a copy `cur = nxt` would wait for the
-        // loads it copies, i.e. put the whole memory latency back inside every iteration)
-        uint32_t it = 0;
-        auto store = [&](const float (&cur)[NIT][NV], int s) {
+        constexpr int NIT = (C::NITEMS + SWC_PROD - 1) / SWC_PROD;      // items per thread
+        for (int fr = blockIdx.x; fr < R; fr += gridDim.x, ++it) {
+            const int s = it % STAGES, rb = it % NRAW;
+            const float* raw_f = raw_s + rb * (FRAME_BYTES / 4);
+            mbar_wait(&raw_full[rb], (it / NRAW) & 1);                   // frame landed in shared memory
+            mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);           // image stage free
+            SWC_STAMP(0);
             uint8_t* st = a_s + (size_t)s * STAGE_BYTES;
 #pragma unroll
             for (int j = 0; j < NIT; ++j) {
@@ -207,20 +203,33 @@ tc_conv_sw_fwd_kernel(const float* __restrict__ in, const float* __restrict__ w,
                 if (i < C::NITEMS) {
                     uint4 h, l;
                     if constexpr (L == 2) {
+                        // item = (dy, ci-chunk cc, position Y, X): 8 channels x (dx = 0, 1) -> 2 chunks
                         const int X = i % 10, Y = (i / 10) % 10, cc = (i / 100) & 3, dy = i / 400;
+                        const float* q = raw_f + (cc * 8) * 400 + (2 * Y + dy) * 20 + 2 * X;
+                        float v0[8], v1[8];
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) {
+                            const float2 v = *reinterpret_cast<const float2*>(q + e * 400);
+                            v0[e] = v.x;
+                            v1[e] = v.y;
+                        }
                         const int row = Y * 10 + X;
                         uint8_t* pl = st + (size_t)dy * 2 * PLANE;
                         const uint32_t o0 = swc_off(row, cc), o1 = swc_off(row, 4 + cc);   // dx = 0 | dx = 1
-                        chunk(cur[j], h, l);
+                        chunk(v0, h, l);
                         *reinterpret_cast<uint4*>(pl + o0) = h;
                         *reinterpret_cast<uint4*>(pl + PLANE + o0) = l;
-                        chunk(cur[j] + 8, h, l);
+                        chunk(v1, h, l);
                         *reinterpret_cast<uint4*>(pl + o1) = h;
                         *reinterpret_cast<uint4*>(pl + PLANE + o1) = l;
                     } else {
-                        // own row's first half, previous row's second half
+                        // item = (ci-chunk cc, position p): own row's first half, previous row's second half
                         const int p = i % 81, cc = i / 81;
-                        chunk(cur[j], h, l);
+                        const float* q = raw_f + (cc * 8) * 81 + p;
+                        float v[8];
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) v[e] = q[e * 81];
+                        chunk(v, h, l);
                         const uint32_t o0 = swc_off(p, cc);
                         *reinterpret_cast<uint4*>(st + o0) = h;
                         *reinterpret_cast<uint4*>(st + PLANE + o0) = l;
@@ -232,25 +241,15 @@ tc_conv_sw_fwd_kernel(const float* __restrict__ in, const float* __restrict__ w,
                     }
                 }
             }
+            mbar_arrive(&raw_empty[rb]);                                 // done reading the raw frame
             SWC_STAMP(7);
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             mbar_arrive(&full_bar[s]);
-        };
-        issue(blockIdx.x, cur);
-        for (int fr = blockIdx.x; fr < R; fr += 2 * gridDim.x) {
-            issue(fr + gridDim.x, nxt);
-            mbar_wait(&empty_bar[it % STAGES], ((it / STAGES) & 1) ^ 1);
-            SWC_STAMP(0);
-            store(cur, it % STAGES);
             SWC_STAMP(1);
-            ++it;
-            if (fr + gridDim.x >= R) break;
-            issue(fr + 2 * gridDim.x, cur);
-            mbar_wait(&empty_bar[it % STAGES], ((it / STAGES) & 1) ^ 1);
-            SWC_STAMP(0);
-            store(nxt, it % STAGES);
-            SWC_STAMP(1);
-            ++it;
+            if (tid == 0 && (long long)fr + (long long)NRAW * gridDim.x < R) {
+                mbar_wait(&raw_empty[rb], (it / NRAW) & 1);              // every producer has read it
+                fetch((long long)fr + (long long)NRAW * gridDim.x, rb);
+            }
         }
     } else if (warp < MMA_WARP + SWC_ISSUERS) {
         // One thread issues a tcgen05.mma every ~74 clk whatever its shape and a frame takes 64 of
@@ -356,7 +355,7 @@ template <int L>
 int launch_tc_conv_sw(const char* name, const float* in, const float* w, const float* b, float* out, int R,
                       cudaStream_t st, __nv_bfloat16* out_hi, __nv_bfloat16* out_lo) {
     using C = SwCfg<L>;
-    const int smem = C::NKB * 2 * 32 * 128 + C::STAGES * C::PLANES * 2 * C::ROWS * 128 + 1024;
+    const int smem = C::NKB * 2 * 32 * 128 + C::STAGES * C::PLANES * 2 * C::ROWS * 128 + C::NRAW * 32 * C::HIN * C::HIN * 4 + 1024;
     static_assert(C::NKB * 2 * 32 * 128 >= 48 * 128, "the weights behind the ring absorb the over-read");
     auto kern = tc_conv_sw_fwd_kernel<L>;
     R2D2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
