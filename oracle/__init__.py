@@ -11,3 +11,18 @@ the unmodified reference imported from ``/root/reference`` (see ``oracle/make_go
 the outputs of that run are committed as fixtures under ``tests/golden/`` and re-checked
 against the oracle by the ``-m "not gpu"`` tests.
 """
+
+
+def warm_up():
+    """Run one tiny forward of the network oracle and throw it away.
+
+    Measured on the GPU boxes' hosts (tools/cpu_oracle_first_call.py): in about 1 process of 20
+    the FIRST torch-CPU forward of the process differs from every later identical call by ~3.5e-5
+    (the later calls agree with float64 to 5e-7); after any earlier forward it never did (0 of
+    40).  The checker must not be the noisy side of a 1e-5 comparison, so everything that uses
+    the oracle as a checker calls this first."""
+    import torch
+    from . import net_oracle as NO
+    with torch.no_grad():
+        p = NO.init_params(1, 64)
+        NO.qnet_forward(p, torch.rand(8, 4, 84, 84), None, None)

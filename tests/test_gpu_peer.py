@@ -57,6 +57,8 @@ def _worker(rank, world, port, out):
     #      the IPC buffers after the step), averaged over the ranks -- within the bf16 class -- and
     #      the parameters every replica ends up with == centered RMSprop of that average.
     import numpy as np
+    import oracle
+    oracle.warm_up()                    # spawned process: see oracle.warm_up
     from oracle import net_oracle as NO
     from util import make_oracle_replay, mirror_to_gpu, rel_err
     torch.manual_seed(0)
