@@ -20,6 +20,8 @@ def _worker(rank, world, port, out_dir):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank),
                       WORLD_SIZE=str(world), LOCAL_RANK=str(rank))
     torch.set_num_threads(2)
+    import oracle
+    oracle.warm_up()                    # spawned process: see oracle.warm_up
     from oracle import net_oracle as NO
     from pytorch_r2d2_b200 import parallel
     from pytorch_r2d2_b200.params import MODULE_ORDER, ParamLayout
