@@ -25,6 +25,10 @@
 
 namespace r2d2 {
 
+// tc_conv1_sw.cu
+int launch_tc_conv1_sw_dual(const uint8_t* in, FrameMap fm, const float* wa, const float* ba, float* outa,
+                            const float* wb, const float* bb, float* outb, int R, int skip_b, cudaStream_t st,
+                            uint32_t* relu_bits_a);
 // tc_conv_sw.cu
 template <int L>
 int launch_tc_conv_sw(const char* name, const float* in, const float* w, const float* b, float* out, int R,
@@ -419,6 +423,12 @@ static int launch_tc_conv(const char* name, const T* in, FrameMap fm, const floa
 static int launch_tc_conv1_dual(const uint8_t* in, FrameMap fm, const float* wa, const float* ba, float* outa,
                                 const float* wb, const float* bb, float* outb, int R, int skip_b,
                                 cudaStream_t st, uint32_t* relu_bits_a = nullptr) {
+    // shifted-window kernel (tc_conv1_sw.cu) unless R2D2_CONV1=gather (A/B measurements)
+    static const bool gather_form = [] {
+        const char* e = getenv("R2D2_CONV1");
+        return e && e[0] == 'g';
+    }();
+    if (!gather_form) return launch_tc_conv1_sw_dual(in, fm, wa, ba, outa, wb, bb, outb, R, skip_b, st, relu_bits_a);
     constexpr int NKB = 4;
     const int smem = 2 * 2 * NKB * 32 * 128 + CV_STAGES * 128 * 128 + 1024;
     constexpr int NPW = 8;     // measured: 16 producer warps are no faster here (0.260 vs 0.245 ms)
