@@ -153,6 +153,16 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N) {
     return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) |
            ((uint32_t)(M >> 4) << 24);
 }
+// bf16 with the A operand MN-major (M contiguous in shared memory)
+__host__ __device__ constexpr uint32_t umma_idesc_bf16_amn(int M, int N) {
+    return umma_idesc_bf16(M, N) | (1u << 15);
+}
+// MN-major SWIZZLE_128B operand: 64-element (128 B) MN groups `lbo` bytes apart, 8-row K groups
+// 1024 bytes apart
+__device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t smem_addr, uint32_t lbo_bytes) {
+    return (uint64_t)((smem_addr & 0x3FFFF) >> 4) | ((uint64_t)(lbo_bytes >> 4) << 16) |
+           (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
 // same with A = B = fp16 (format field 0): exact for small integers (u8 pixels), 11-bit mantissa
 __host__ __device__ constexpr uint32_t umma_idesc_f16(int M, int N) {
     return (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);

@@ -29,6 +29,9 @@ namespace r2d2 {
 int launch_tc_conv1_sw_dual(const uint8_t* in, FrameMap fm, const float* wa, const float* ba, float* outa,
                             const float* wb, const float* bb, float* outb, int R, int skip_b, cudaStream_t st,
                             uint32_t* relu_bits_a);
+// tc_wgrad_sw.cu
+int launch_tc_conv1_wgrad_sw(const uint8_t* in, FrameMap fm, const float* dz, float* part, int R, float in_scale,
+                             int grid, cudaStream_t st, float* bias_part);
 // tc_conv_sw.cu
 template <int L>
 int launch_tc_conv_sw(const char* name, const float* in, const float* w, const float* b, float* out, int R,
@@ -451,16 +454,6 @@ static int launch_tc_conv1_dual(const uint8_t* in, FrameMap fm, const float* wa,
 // B is a K-major [32 co x 64 pixels] tile of dZ.  Each persistent CTA owns a contiguous range of
 // 64-pixel blocks, accumulates its partial dW in TMEM (KP/128 accumulators of 32 columns) and
 // writes it out once; the partials are then summed in fixed order (reduce_partials_kernel).
-__host__ __device__ constexpr uint32_t umma_idesc_bf16_amn(int M, int N) {
-    return umma_idesc_bf16(M, N) | (1u << 15);               // A operand MN-major
-}
-// MN-major SWIZZLE_128B operand: 64-element (128 B) MN groups `lbo` bytes apart, 8-row K groups
-// 1024 bytes apart
-__device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t smem_addr, uint32_t lbo_bytes) {
-    return (uint64_t)((smem_addr & 0x3FFFF) >> 4) | ((uint64_t)(lbo_bytes >> 4) << 16) |
-           (64ull << 32) | (1ull << 46) | (2ull << 61);
-}
-
 template <class T, int CIN, int KH, int HIN, int SUB>
 __device__ __forceinline__ void wgrad_gather(const T* __restrict__ src, const bool valid, const int prow,
                                              uint8_t* __restrict__ a_stage) {
@@ -1178,15 +1171,28 @@ static int wgrad_grid(int R, int P) {
     return nblk < g ? (int)nblk : g;
 }
 
+// first-layer weight gradient: shifted-window kernel (tc_wgrad_sw.cu) unless R2D2_WGRAD=gather
+static int launch_conv1_wgrad(const uint8_t* in, FrameMap fm, const float* dz, float* part, int R, int* grid_out,
+                              cudaStream_t st, float* bias_part = nullptr) {
+    static const bool gather_form = [] {
+        const char* e = getenv("R2D2_WGRAD");
+        return e && e[0] == 'g';
+    }();
+    if (gather_form)
+        return launch_tc_wgrad<uint8_t, 4, 8, 84, 20, 4, 4>("tc_conv1_wgrad", in, fm, dz, part, R, 1.f / 255.f, grid_out,
+                                                            st, bias_part);
+    *grid_out = wgrad_grid(R, 400);
+    return launch_tc_conv1_wgrad_sw(in, fm, dz, part, R, 1.f / 255.f, *grid_out, st, bias_part);
+}
+
 int r2d2_tc_conv1_wgrad_ring(const uint8_t* ring_state, int64_t M, const int64_t* seq_index, int B, int s0,
                              int nt, const float* dz, float* dw, float* db, float* part, void* stream) {
     R2D2_REQUIRE(ring_state && seq_index && dz && dw && part && nt > 0 && B > 0 && M > 0 && s0 >= 0,
                  "tc_conv1_wgrad_ring: bad args");
     int grid = wgrad_grid(B * nt, 400);
     FrameMap fm{B, s0 + nt, s0, R2D2_FRAME_BYTES, reinterpret_cast<const long long*>(seq_index), (long long)M};
-    int rc = launch_tc_wgrad<uint8_t, 4, 8, 84, 20, 4, 4>("tc_conv1_wgrad", ring_state, fm, dz, part, B * nt,
-                                                          1.f / 255.f, &grid, as_stream(stream),
-                                                          db ? part + (long long)grid * 32 * 256 : nullptr);
+    int rc = launch_conv1_wgrad(ring_state, fm, dz, part, B * nt, &grid, as_stream(stream),
+                                db ? part + (long long)grid * 32 * 256 : nullptr);
     if (rc) return rc;
     if (db) return reduce_wgrad(part, dw, 32 * 256, db, grid, as_stream(stream));
     return r2d2_reduce_partials(part, dw, 32 * 256, grid, stream);
@@ -1277,9 +1283,7 @@ int r2d2_tc_torso_wgrad_u8(const uint8_t* slab, int B, int S, int s0, int nt, co
     if (rc) return rc;
     rc = r2d2_reduce_partials(part, dw2, 32 * 512, grid, stream);
     if (rc) return rc;
-    rc = launch_tc_wgrad<uint8_t, 4, 8, 84, 20, 4, 4>("tc_conv1_wgrad", slab,
-                                                      FrameMap{B, S, s0, R2D2_FRAME_BYTES}, dz1, part, R,
-                                                      1.f / 255.f, &grid, st);
+    rc = launch_conv1_wgrad(slab, FrameMap{B, S, s0, R2D2_FRAME_BYTES}, dz1, part, R, &grid, st);
     if (rc) return rc;
     return r2d2_reduce_partials(part, dw1, 32 * 256, grid, stream);
 }
@@ -1297,9 +1301,8 @@ int r2d2_tc_conv_wgrad_layer(int layer, const void* in, int B, int S, int s0, in
     if (layer == 1) {
         R2D2_REQUIRE(s0 >= 0 && s0 + nt <= S, "tc_conv_wgrad_layer: bad frame window");
         K = 256;
-        rc = launch_tc_wgrad<uint8_t, 4, 8, 84, 20, 4, 4>("tc_conv1_wgrad", static_cast<const uint8_t*>(in),
-                                                          FrameMap{B, S, s0, R2D2_FRAME_BYTES}, dz, part, R,
-                                                          1.f / 255.f, &grid, st, bias_part);
+        rc = launch_conv1_wgrad(static_cast<const uint8_t*>(in), FrameMap{B, S, s0, R2D2_FRAME_BYTES}, dz, part, R,
+                                &grid, st, bias_part);
     } else if (layer == 2) {
         K = 512;
         rc = launch_tc_wgrad<float, 32, 4, 20, 9, 2, 3>("tc_conv2_wgrad", static_cast<const float*>(in),

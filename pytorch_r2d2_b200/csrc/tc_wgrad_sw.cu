@@ -1,0 +1,245 @@
+// Conv weight gradients in "shifted window" form (plain bf16; see tc_conv.cu for the gather form).
+//
+//   dW[co][ci][ky][kx] = sum over frames and output positions of dZ[co][oy][ox] * X[ci][S oy + ky][S ox + kx]
+//
+// With the input in space-to-depth layout (row = position, 128-byte row = 64 channels (ci, dy, dx),
+// exactly the image the forward shifted-window kernels build) the sum over positions is a GEMM whose
+// K dimension is the position:   D_shift[chan][co] = sum_m Img[m + shift][chan] * dZ'[co][m]
+// -- Img is consumed as an MN-major A operand (M = channel), one kernel offset (ky2, kx2) is a ROW
+// SHIFT of the same image, and two shifts that differ by one row are the two 64-element MN groups
+// of one M = 128 tile (leading-dimension offset 128 bytes).  dZ' is dZ laid out on the image's
+// position grid (the column the s2d grid has and the output grid lacks holds zeros), a K-major
+// B operand of N = 32 channels.  Every input pixel and every gradient value is loaded and
+// converted once per frame; the gather form builds 64 patch elements per output pixel.
+// Each persistent CTA accumulates its frames in TMEM and writes one partial; partials are summed
+// in fixed order by reduce_wgrad_partials_kernel (tc_conv.cu).
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+#include "gemm.cuh"   // FrameMap
+#include "ptx.cuh"
+
+namespace r2d2 {
+
+namespace {
+
+__device__ __forceinline__ uint32_t ws_off(int row, int chunk) {
+    return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((chunk ^ (row & 7)) << 4));
+}
+__device__ __forceinline__ uint32_t ws_pack(float a, float b) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&v);
+}
+// four u8 pixels of w -> two packed bf16x2 (exact: 8 significant bits)
+__device__ __forceinline__ void ws_u8x4(uint32_t w, uint32_t& lo, uint32_t& hi) {
+    const float f0 = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7650u)) - 8388608.f;
+    const float f1 = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7651u)) - 8388608.f;
+    const float f2 = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7652u)) - 8388608.f;
+    const float f3 = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7653u)) - 8388608.f;
+    // the upper halves of the fp32 patterns ARE the bf16 values
+    lo = __byte_perm(__float_as_uint(f0), __float_as_uint(f1), 0x7632u);
+    hi = __byte_perm(__float_as_uint(f2), __float_as_uint(f3), 0x7632u);
+}
+__device__ __forceinline__ void ws_bar(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// ---------------------------------------------------------------------------------------------
+// first layer: 8x8 / stride 4 on u8 84x84x4 -> s2d by 4: 21x21 positions x 64 channels, shifts
+// {0, 1, 21, 22}; dZ [32][20][20] -> dZ' [32][441 (+7)]
+constexpr int W1_PROD = 320;                        // producers: 882 image items = 3 rounds; 320 = 32 co x 10 row pairs
+constexpr int W1_THREADS = W1_PROD + 32 + 128;
+constexpr int W1_ROWS = 448, W1_STAGES = 2, W1_NKB = 7, W1_KSTEPS = 28;
+constexpr uint32_t W1_IMG = W1_ROWS * 128;          // 448 positions x 64 bf16
+constexpr uint32_t W1_DZ = W1_NKB * 32 * 128;       // 7 k-blocks of [32 co x 64 positions]
+constexpr int W1_SMEM = W1_STAGES * (W1_IMG + W1_DZ) + 1024;
+
+__global__ void __launch_bounds__(W1_THREADS, 1)
+tc_conv1_wgrad_sw_kernel(const uint8_t* __restrict__ in, const FrameMap fm, const float* __restrict__ dz,
+                         float* __restrict__ part, const int R, const float in_scale,
+                         float* __restrict__ bias_part) {
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t full_bar[W1_STAGES], empty_bar[W1_STAGES], acc_full;
+    __shared__ uint32_t tmem_slot;
+    __shared__ float bias_s[W1_PROD];
+    const uint32_t raw = smem_u32(smem_raw);
+    uint8_t* base = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
+    // images first, gradient tiles behind them: a shifted tile's over-read (rows 448..469, always
+    // multiplied by zero gradients) must still hold finite values
+    uint8_t* a_s = base;
+    uint8_t* g_s = base + W1_STAGES * W1_IMG;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    constexpr int MMA_WARP = W1_PROD / 32;
+    const bool has_work = (int)blockIdx.x < R;
+
+    if (tid == 0) {
+        for (int s = 0; s < W1_STAGES; ++s) {
+            mbar_init(&full_bar[s], W1_PROD);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(&acc_full, 1);
+        mbar_fence_init();
+    }
+    for (uint32_t i = tid * 16; i < W1_STAGES * (W1_IMG + W1_DZ); i += blockDim.x * 16)
+        *reinterpret_cast<uint4*>(base + i) = make_uint4(0, 0, 0, 0);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    if (warp == MMA_WARP) tmem_alloc(&tmem_slot, 64);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+
+    if (warp < MMA_WARP) {
+        // ================= producers
+        // image item = (input channel, position): 4 raw rows x 4 bytes -> two 16-byte chunks
+        constexpr int NIT = 6;                                           // 2 channel pairs x 3 rounds of 320
+        int soff[NIT];
+        uint32_t doff[NIT];
+        bool act[NIT];
+#pragma unroll
+        for (int k = 0; k < NIT; ++k) {
+            const int i = tid + (k % 3) * W1_PROD;
+            act[k] = i < 2 * 441;
+            const int c2 = i / 441, p = i - c2 * 441;
+            const int Y = p / 21, X = p - Y * 21;
+            const int ci = (k / 3) * 2 + c2;
+            soff[k] = act[k] ? ci * 7056 + (4 * Y) * 84 + 4 * X : 0;
+            doff[k] = ws_off(act[k] ? p : 0, ci * 2);
+        }
+        // gradient item = (channel co, output rows 2 yp and 2 yp + 1): 40 consecutive floats ->
+        // image positions 42 yp .. 42 yp + 41 (each output row followed by one zero)
+        const int co = tid / 10, yp = tid - co * 10;
+        // register prefetch in two halves: the next frame's pixels are in flight while this
+        // frame's gradients are converted, and the other way round
+        uint32_t nx[NIT][4];
+        float4 ng[10];
+        auto load_img = [&](int f) {
+            const uint8_t* fb = in + fm.base(f);
+#pragma unroll
+            for (int k = 0; k < NIT; ++k) {
+                const uint32_t* q = reinterpret_cast<const uint32_t*>(fb + soff[k]);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) nx[k][j] = act[k] ? __ldg(q + 21 * j) : 0u;
+            }
+        };
+        auto load_dz = [&](int f) {
+            const float4* gp = reinterpret_cast<const float4*>(dz + ((long long)f * 32 + co) * 400 + 40 * yp);
+#pragma unroll
+            for (int j = 0; j < 10; ++j) ng[j] = __ldg(gp + j);
+        };
+        if (has_work) {
+            load_img(blockIdx.x);
+            load_dz(blockIdx.x);
+        }
+        float bsum = 0.f;
+        uint32_t it = 0;
+        for (int fr = blockIdx.x; fr < R; fr += gridDim.x, ++it) {
+            const int s = it % W1_STAGES;
+            const bool more = fr + (int)gridDim.x < R;
+            mbar_wait(&empty_bar[s], ((it / W1_STAGES) & 1) ^ 1);
+            uint8_t* img = a_s + (size_t)s * W1_IMG;
+            uint8_t* gt = g_s + (size_t)s * W1_DZ;
+#pragma unroll
+            for (int k = 0; k < NIT; ++k)
+                if (act[k]) {
+                    uint4 c0, c1;
+                    ws_u8x4(nx[k][0], c0.x, c0.y);
+                    ws_u8x4(nx[k][1], c0.z, c0.w);
+                    ws_u8x4(nx[k][2], c1.x, c1.y);
+                    ws_u8x4(nx[k][3], c1.z, c1.w);
+                    *reinterpret_cast<uint4*>(img + doff[k]) = c0;
+                    *reinterpret_cast<uint4*>(img + (doff[k] ^ 16u)) = c1;
+                }
+            if (more) load_img(fr + gridDim.x);
+            float g[40];
+#pragma unroll
+            for (int j = 0; j < 10; ++j) g[4 * j] = ng[j].x, g[4 * j + 1] = ng[j].y, g[4 * j + 2] = ng[j].z, g[4 * j + 3] = ng[j].w;
+            // 42 positions = 21 bf16 pairs: j < 20 -> g[j], j = 20 -> 0, 21 <= j < 41 -> g[j-1], j = 41 -> 0
+            float bs = 0.f;
+#pragma unroll
+            for (int jp = 0; jp < 21; ++jp) {
+                const int j0 = 2 * jp, j1 = 2 * jp + 1;
+                const float v0 = j0 < 20 ? g[j0] : j0 == 20 ? 0.f : g[j0 - 1];
+                const float v1 = j1 < 20 ? g[j1] : j1 == 41 ? 0.f : g[j1 - 1];
+                const int m = 42 * yp + j0;
+                *reinterpret_cast<uint32_t*>(gt + (m >> 6) * 4096 + ws_off(co, (m & 63) >> 3) + (m & 7) * 2) = ws_pack(v0, v1);
+                bs += v0 + v1;
+            }
+            bsum += bs;
+            if (more) load_dz(fr + gridDim.x);
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            mbar_arrive(&full_bar[s]);
+        }
+        if (bias_part) {                                                 // fixed order: thread, then row pairs
+            bias_s[tid] = bsum;
+            ws_bar(1, W1_PROD);
+            if (tid < 32) {
+                float t = 0.f;
+#pragma unroll
+                for (int j = 0; j < 10; ++j) t += bias_s[tid * 10 + j];
+                bias_part[blockIdx.x * 32 + tid] = t;
+            }
+        }
+    } else if (warp == MMA_WARP) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16_amn(128, 32);
+            uint32_t it = 0;
+            for (int fr = blockIdx.x; fr < R; fr += gridDim.x, ++it) {
+                const int s = it % W1_STAGES;
+                mbar_wait(&full_bar[s], (it / W1_STAGES) & 1);
+                tc_fence_after();
+                const uint32_t img = smem_u32(a_s + (size_t)s * W1_IMG), gt = smem_u32(g_s + (size_t)s * W1_DZ);
+#pragma unroll 4
+                for (int ks = 0; ks < W1_KSTEPS; ++ks) {                 // 16 positions per MMA
+                    const uint64_t b = umma_desc_k_sw128(gt + (ks >> 2) * 4096 + (ks & 3) * 32);
+#pragma unroll
+                    for (int pair = 0; pair < 2; ++pair)                 // shifts (21 pair, 21 pair + 1)
+                        umma_f16(tmem_base + pair * 32, umma_desc_mn_sw128(img + (ks * 16 + pair * 21) * 128, 128), b,
+                                 idesc, (it | ks) != 0);
+                }
+                umma_commit(&empty_bar[s]);
+            }
+            umma_commit(&acc_full);
+        }
+    } else {
+        // ================= epilogue (once): TMEM lane = (shift kx2, channel), 32 columns = co
+        const int q = warp & 3;
+        if (has_work) {
+            mbar_wait(&acc_full, 0);
+            tc_fence_after();
+        }
+        float* out = part + (long long)blockIdx.x * 32 * 256;
+        const int l = q * 32 + lane, kx2 = l >> 6, chan = l & 63;
+        const int ci = chan >> 4, dy = (chan >> 2) & 3, dx = chan & 3;
+#pragma unroll 1
+        for (int ky2 = 0; ky2 < 2; ++ky2) {
+            uint32_t r[32];
+            if (has_work) {
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + ky2 * 32, r);
+                tmem_ld_wait();
+            } else {
+#pragma unroll
+                for (int c = 0; c < 32; ++c) r[c] = 0u;
+            }
+            const int k = ci * 64 + (4 * ky2 + dy) * 8 + 4 * kx2 + dx;
+#pragma unroll
+            for (int c = 0; c < 32; ++c) out[c * 256 + k] = __uint_as_float(r[c]) * in_scale;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == MMA_WARP) tmem_dealloc(tmem_base, 64);
+}
+
+}  // namespace
+
+// part: [grid][32][256] weight partials; bias_part (may be null): [grid][32]
+int launch_tc_conv1_wgrad_sw(const uint8_t* in, FrameMap fm, const float* dz, float* part, int R, float in_scale,
+                             int grid, cudaStream_t st, float* bias_part) {
+    R2D2_CUDA_OK(cudaFuncSetAttribute(tc_conv1_wgrad_sw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, W1_SMEM));
+    R2D2_LAUNCH("tc_conv1_wgrad", st,
+                tc_conv1_wgrad_sw_kernel<<<grid, W1_THREADS, W1_SMEM, st>>>(in, fm, dz, part, R, in_scale, bias_part));
+    return R2D2_OK;
+}
+
+}  // namespace r2d2
