@@ -32,6 +32,8 @@ int launch_tc_conv1_sw_dual(const uint8_t* in, FrameMap fm, const float* wa, con
 // tc_wgrad_sw.cu
 int launch_tc_conv1_wgrad_sw(const uint8_t* in, FrameMap fm, const float* dz, float* part, int R, float in_scale,
                              int grid, cudaStream_t st, float* bias_part);
+int launch_tc_conv2_wgrad_sw(const float* in, const float* dz, float* part, int R, int grid, cudaStream_t st,
+                             float* bias_part);
 // tc_conv_sw.cu
 template <int L>
 int launch_tc_conv_sw(const char* name, const float* in, const float* w, const float* b, float* out, int R,
@@ -1171,14 +1173,25 @@ static int wgrad_grid(int R, int P) {
     return nblk < g ? (int)nblk : g;
 }
 
-// first-layer weight gradient: shifted-window kernel (tc_wgrad_sw.cu) unless R2D2_WGRAD=gather
-static int launch_conv1_wgrad(const uint8_t* in, FrameMap fm, const float* dz, float* part, int R, int* grid_out,
-                              cudaStream_t st, float* bias_part = nullptr) {
-    static const bool gather_form = [] {
+static bool wgrad_gather_form() {
+    static const bool v = [] {
         const char* e = getenv("R2D2_WGRAD");
         return e && e[0] == 'g';
     }();
-    if (gather_form)
+    return v;
+}
+static int launch_conv2_wgrad(const float* a1, const float* dz, float* part, int R, int* grid_out, cudaStream_t st,
+                              float* bias_part = nullptr) {
+    if (wgrad_gather_form())
+        return launch_tc_wgrad<float, 32, 4, 20, 9, 2, 3>("tc_conv2_wgrad", a1, FrameMap{0, 0, 0, 12800}, dz, part, R, 1.f,
+                                                          grid_out, st, bias_part);
+    *grid_out = wgrad_grid(R, 81);
+    return launch_tc_conv2_wgrad_sw(a1, dz, part, R, *grid_out, st, bias_part);
+}
+// first-layer weight gradient: shifted-window kernel (tc_wgrad_sw.cu) unless R2D2_WGRAD=gather
+static int launch_conv1_wgrad(const uint8_t* in, FrameMap fm, const float* dz, float* part, int R, int* grid_out,
+                              cudaStream_t st, float* bias_part = nullptr) {
+    if (wgrad_gather_form())
         return launch_tc_wgrad<uint8_t, 4, 8, 84, 20, 4, 4>("tc_conv1_wgrad", in, fm, dz, part, R, 1.f / 255.f, grid_out,
                                                             st, bias_part);
     *grid_out = wgrad_grid(R, 400);
@@ -1278,8 +1291,7 @@ int r2d2_tc_torso_wgrad_u8(const uint8_t* slab, int B, int S, int s0, int nt, co
     if (rc) return rc;
     rc = r2d2_reduce_partials(part, dw3, 32 * 288, grid, stream);
     if (rc) return rc;
-    rc = launch_tc_wgrad<float, 32, 4, 20, 9, 2, 3>("tc_conv2_wgrad", a1, FrameMap{0, 0, 0, 12800}, dz2,
-                                                    part, R, 1.f, &grid, st);
+    rc = launch_conv2_wgrad(a1, dz2, part, R, &grid, st);
     if (rc) return rc;
     rc = r2d2_reduce_partials(part, dw2, 32 * 512, grid, stream);
     if (rc) return rc;
@@ -1305,9 +1317,7 @@ int r2d2_tc_conv_wgrad_layer(int layer, const void* in, int B, int S, int s0, in
                                 &grid, st, bias_part);
     } else if (layer == 2) {
         K = 512;
-        rc = launch_tc_wgrad<float, 32, 4, 20, 9, 2, 3>("tc_conv2_wgrad", static_cast<const float*>(in),
-                                                        FrameMap{0, 0, 0, 12800}, dz, part, R, 1.f, &grid, st,
-                                                        bias_part);
+        rc = launch_conv2_wgrad(static_cast<const float*>(in), dz, part, R, &grid, st, bias_part);
     } else if (layer == 3) {
         K = 288;
         rc = launch_tc_wgrad<float, 32, 3, 9, 7, 1, 3>("tc_conv3_wgrad", static_cast<const float*>(in),

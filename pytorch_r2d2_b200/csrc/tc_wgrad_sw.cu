@@ -231,6 +231,180 @@ tc_conv1_wgrad_sw_kernel(const uint8_t* __restrict__ in, const FrameMap fm, cons
     if (warp == MMA_WARP) tmem_dealloc(tmem_base, 64);
 }
 
+// ---------------------------------------------------------------------------------------------
+// second layer: 4x4 / stride 2 on fp32 [32][20][20] -> s2d by 2: 10x10 positions x 128 channels
+// (ci, dy, dx) = two 64-channel planes (the two MN groups of an M = 128 tile), shifts
+// {0, 1, 10, 11}; dZ [32][9][9] -> dZ' [32][100 (+28)]
+constexpr int W2_PROD = 416;                        // 400 image items x 2 + 288 gradient items
+constexpr int W2_THREADS = W2_PROD + 32 + 128;
+constexpr int W2_STAGES = 4, W2_KSTEPS = 7;
+constexpr uint32_t W2_PLANE = 128 * 128;            // 128 position rows x 64 bf16
+constexpr uint32_t W2_IMG = 2 * W2_PLANE, W2_DZ = 2 * 32 * 128;
+constexpr int W2_SMEM = W2_STAGES * (W2_IMG + W2_DZ) + 1024;
+
+__global__ void __launch_bounds__(W2_THREADS, 1)
+tc_conv2_wgrad_sw_kernel(const float* __restrict__ in, const float* __restrict__ dz, float* __restrict__ part,
+                         const int R, float* __restrict__ bias_part) {
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t full_bar[W2_STAGES], empty_bar[W2_STAGES], acc_full;
+    __shared__ uint32_t tmem_slot;
+    __shared__ float bias_s[288];
+    const uint32_t raw = smem_u32(smem_raw);
+    uint8_t* base = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    constexpr int MMA_WARP = W2_PROD / 32;
+    const bool has_work = (int)blockIdx.x < R;
+
+    if (tid == 0) {
+        for (int s = 0; s < W2_STAGES; ++s) {
+            mbar_init(&full_bar[s], W2_PROD);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(&acc_full, 1);
+        mbar_fence_init();
+    }
+    // rows 100..127 of every plane and gradient positions 9, 19, .., 99..127 stay zero for good
+    for (uint32_t i = tid * 16; i < W2_STAGES * (W2_IMG + W2_DZ); i += blockDim.x * 16)
+        *reinterpret_cast<uint4*>(base + i) = make_uint4(0, 0, 0, 0);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    if (warp == MMA_WARP) tmem_alloc(&tmem_slot, 128);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+
+    if (warp < MMA_WARP) {
+        // ================= producers
+        // image item = (channel pair cp, row Y, column pair xp): 2 ci x 2 dy float4 -> the 16-byte
+        // chunks of positions (Y, 2 xp) and (Y, 2 xp + 1); threads 0..399 take items tid, tid + 400
+        const bool img_t = tid < 400;
+        const int xp = tid % 5, Y = (tid / 5) % 10, cp0 = tid / 50;      // cp0 0..7, second item cp0 + 8
+        const int m0 = Y * 10 + 2 * xp;
+        const float* src0 = in + (long long)(2 * cp0) * 400 + (2 * Y) * 20 + 4 * xp;
+        const uint32_t d0 = ws_off(m0, cp0), d1 = ws_off(m0 + 1, cp0);
+        // gradient item = (co, oy): 9 floats -> positions 10 oy .. 10 oy + 8; threads 0..287
+        const bool dz_t = tid < 288;
+        const int co = tid / 9, oy = tid - co * 9;
+        float4 nx[2][4];
+        float ng[9];
+        auto load_img = [&](int f) {
+            if (img_t) {
+                const float* fb = src0 + (long long)f * 12800;
+#pragma unroll
+                for (int it2 = 0; it2 < 2; ++it2)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)                          // j = (ci & 1) * 2 + dy
+                        nx[it2][j] = __ldg(reinterpret_cast<const float4*>(fb + it2 * 16 * 400 + (j >> 1) * 400 + (j & 1) * 20));
+            }
+        };
+        auto load_dz = [&](int f) {
+            if (dz_t) {
+                const float* gp = dz + ((long long)f * 32 + co) * 81 + 9 * oy;
+#pragma unroll
+                for (int j = 0; j < 9; ++j) ng[j] = __ldg(gp + j);
+            }
+        };
+        if (has_work) {
+            load_img(blockIdx.x);
+            load_dz(blockIdx.x);
+        }
+        float bsum = 0.f;
+        uint32_t it = 0;
+        for (int fr = blockIdx.x; fr < R; fr += gridDim.x, ++it) {
+            const int s = it % W2_STAGES;
+            const bool more = fr + (int)gridDim.x < R;
+            mbar_wait(&empty_bar[s], ((it / W2_STAGES) & 1) ^ 1);
+            uint8_t* img = base + (size_t)s * (W2_IMG + W2_DZ);
+            uint8_t* gt = img + W2_IMG;
+            if (img_t) {
+#pragma unroll
+                for (int it2 = 0; it2 < 2; ++it2) {                      // plane it2 (ci 0..15 | 16..31)
+                    uint8_t* pl = img + it2 * W2_PLANE;
+                    *reinterpret_cast<uint4*>(pl + d0) =
+                        make_uint4(ws_pack(nx[it2][0].x, nx[it2][0].y), ws_pack(nx[it2][1].x, nx[it2][1].y),
+                                   ws_pack(nx[it2][2].x, nx[it2][2].y), ws_pack(nx[it2][3].x, nx[it2][3].y));
+                    *reinterpret_cast<uint4*>(pl + d1) =
+                        make_uint4(ws_pack(nx[it2][0].z, nx[it2][0].w), ws_pack(nx[it2][1].z, nx[it2][1].w),
+                                   ws_pack(nx[it2][2].z, nx[it2][2].w), ws_pack(nx[it2][3].z, nx[it2][3].w));
+                }
+            }
+            if (more) load_img(fr + gridDim.x);
+            if (dz_t) {
+                float bs = 0.f;
+#pragma unroll
+                for (int jp = 0; jp < 5; ++jp) {
+                    const float v0 = ng[2 * jp], v1 = jp < 4 ? ng[2 * jp + 1] : 0.f;
+                    const int m = 10 * oy + 2 * jp;
+                    *reinterpret_cast<uint32_t*>(gt + (m >> 6) * 4096 + ws_off(co, (m & 63) >> 3) + (m & 7) * 2) = ws_pack(v0, v1);
+                    bs += v0 + v1;
+                }
+                bsum += bs;
+            }
+            if (more) load_dz(fr + gridDim.x);
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            mbar_arrive(&full_bar[s]);
+        }
+        if (bias_part) {                                                 // fixed order: thread, then rows
+            if (dz_t) bias_s[tid] = bsum;
+            ws_bar(1, W2_PROD);
+            if (tid < 32) {
+                float t = 0.f;
+#pragma unroll
+                for (int j = 0; j < 9; ++j) t += bias_s[tid * 9 + j];
+                bias_part[blockIdx.x * 32 + tid] = t;
+            }
+        }
+    } else if (warp == MMA_WARP) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16_amn(128, 32);
+            uint32_t it = 0;
+            for (int fr = blockIdx.x; fr < R; fr += gridDim.x, ++it) {
+                const int s = it % W2_STAGES;
+                mbar_wait(&full_bar[s], (it / W2_STAGES) & 1);
+                tc_fence_after();
+                const uint32_t img = smem_u32(base + (size_t)s * (W2_IMG + W2_DZ)), gt = img + W2_IMG;
+#pragma unroll
+                for (int ks = 0; ks < W2_KSTEPS; ++ks) {                 // 16 positions per MMA
+                    const uint64_t b = umma_desc_k_sw128(gt + (ks >> 2) * 4096 + (ks & 3) * 32);
+#pragma unroll
+                    for (int sh = 0; sh < 4; ++sh)                       // shift (ky2, kx2) = (sh >> 1, sh & 1)
+                        umma_f16(tmem_base + sh * 32,
+                                 umma_desc_mn_sw128(img + (ks * 16 + (sh >> 1) * 10 + (sh & 1)) * 128, W2_PLANE), b, idesc,
+                                 (it | ks) != 0);
+                }
+                umma_commit(&empty_bar[s]);
+            }
+            umma_commit(&acc_full);
+        }
+    } else {
+        // ================= epilogue (once): TMEM lane = channel (ci, dy, dx), 32 columns = co per shift
+        const int q = warp & 3;
+        if (has_work) {
+            mbar_wait(&acc_full, 0);
+            tc_fence_after();
+        }
+        float* out = part + (long long)blockIdx.x * 32 * 512;
+        const int l = q * 32 + lane, ci = l >> 2, dy = (l >> 1) & 1, dx = l & 1;
+#pragma unroll 1
+        for (int sh = 0; sh < 4; ++sh) {
+            uint32_t r[32];
+            if (has_work) {
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + sh * 32, r);
+                tmem_ld_wait();
+            } else {
+#pragma unroll
+                for (int c = 0; c < 32; ++c) r[c] = 0u;
+            }
+            const int k = ci * 16 + (2 * (sh >> 1) + dy) * 4 + 2 * (sh & 1) + dx;
+#pragma unroll
+            for (int c = 0; c < 32; ++c) out[c * 512 + k] = __uint_as_float(r[c]);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == MMA_WARP) tmem_dealloc(tmem_base, 128);
+}
+
 }  // namespace
 
 // part: [grid][32][256] weight partials; bias_part (may be null): [grid][32]
@@ -239,6 +413,15 @@ int launch_tc_conv1_wgrad_sw(const uint8_t* in, FrameMap fm, const float* dz, fl
     R2D2_CUDA_OK(cudaFuncSetAttribute(tc_conv1_wgrad_sw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, W1_SMEM));
     R2D2_LAUNCH("tc_conv1_wgrad", st,
                 tc_conv1_wgrad_sw_kernel<<<grid, W1_THREADS, W1_SMEM, st>>>(in, fm, dz, part, R, in_scale, bias_part));
+    return R2D2_OK;
+}
+
+// second layer: `in` = layer-1 activations [R][32][20][20] fp32 (contiguous frames), part: [grid][32][512]
+int launch_tc_conv2_wgrad_sw(const float* in, const float* dz, float* part, int R, int grid, cudaStream_t st,
+                             float* bias_part) {
+    R2D2_CUDA_OK(cudaFuncSetAttribute(tc_conv2_wgrad_sw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, W2_SMEM));
+    R2D2_LAUNCH("tc_conv2_wgrad", st,
+                tc_conv2_wgrad_sw_kernel<<<grid, W2_THREADS, W2_SMEM, st>>>(in, dz, part, R, bias_part));
     return R2D2_OK;
 }
 
