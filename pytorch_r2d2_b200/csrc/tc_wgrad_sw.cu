@@ -45,13 +45,15 @@ __device__ __forceinline__ void ws_bar(int id, int nthreads) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// first layer: 8x8 / stride 4 on u8 84x84x4 -> s2d by 4: 21x21 positions x 64 channels, shifts
-// {0, 1, 21, 22}; dZ [32][20][20] -> dZ' [32][441 (+7)]
+// first layer: 8x8 / stride 4 on u8 84x84x4 -> s2d by 4: 21x21 positions x 64 channels.  The
+// position grid is laid out with a row pitch of 24 (three pad columns): every output row of dZ
+// then starts on a 16-byte chunk of dZ' and is stored as three whole chunks (20 values + 4 zeros)
+// instead of 21 scalar pairs at run-time offsets.  Shifts {0, 1, 24, 25}; dZ [32][20][20] -> dZ' [32][504 (+8)]
 constexpr int W1_PROD = 320;                        // producers: 882 image items = 3 rounds; 320 = 32 co x 10 row pairs
-constexpr int W1_THREADS = W1_PROD + 32 + 128;
-constexpr int W1_ROWS = 448, W1_STAGES = 2, W1_NKB = 7, W1_KSTEPS = 28;
-constexpr uint32_t W1_IMG = W1_ROWS * 128;          // 448 positions x 64 bf16
-constexpr uint32_t W1_DZ = W1_NKB * 32 * 128;       // 7 k-blocks of [32 co x 64 positions]
+constexpr int W1_THREADS = W1_PROD + 64 + 128;       // + two MMA-issuing warps (one thread issues an MMA every ~74 clk)
+constexpr int W1_PITCH = 24, W1_ROWS = 512, W1_STAGES = 2, W1_NKB = 8, W1_KSTEPS = 32;
+constexpr uint32_t W1_IMG = W1_ROWS * 128;          // 21 x 24 (+8) positions x 64 bf16
+constexpr uint32_t W1_DZ = W1_NKB * 32 * 128;       // 8 k-blocks of [32 co x 64 positions]
 constexpr int W1_SMEM = W1_STAGES * (W1_IMG + W1_DZ) + 1024;
 
 __global__ void __launch_bounds__(W1_THREADS, 1)
@@ -64,7 +66,7 @@ tc_conv1_wgrad_sw_kernel(const uint8_t* __restrict__ in, const FrameMap fm, cons
     __shared__ float bias_s[W1_PROD];
     const uint32_t raw = smem_u32(smem_raw);
     uint8_t* base = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
-    // images first, gradient tiles behind them: a shifted tile's over-read (rows 448..469, always
+    // images first, gradient tiles behind them: a shifted tile's over-read (rows 512..536, always
     // multiplied by zero gradients) must still hold finite values
     uint8_t* a_s = base;
     uint8_t* g_s = base + W1_STAGES * W1_IMG;
@@ -75,9 +77,9 @@ tc_conv1_wgrad_sw_kernel(const uint8_t* __restrict__ in, const FrameMap fm, cons
     if (tid == 0) {
         for (int s = 0; s < W1_STAGES; ++s) {
             mbar_init(&full_bar[s], W1_PROD);
-            mbar_init(&empty_bar[s], 1);
+            mbar_init(&empty_bar[s], 2);
         }
-        mbar_init(&acc_full, 1);
+        mbar_init(&acc_full, 2);
         mbar_fence_init();
     }
     for (uint32_t i = tid * 16; i < W1_STAGES * (W1_IMG + W1_DZ); i += blockDim.x * 16)
@@ -104,17 +106,19 @@ tc_conv1_wgrad_sw_kernel(const uint8_t* __restrict__ in, const FrameMap fm, cons
             const int Y = p / 21, X = p - Y * 21;
             const int ci = (k / 3) * 2 + c2;
             soff[k] = act[k] ? ci * 7056 + (4 * Y) * 84 + 4 * X : 0;
-            doff[k] = ws_off(act[k] ? p : 0, ci * 2);
+            doff[k] = ws_off(act[k] ? Y * W1_PITCH + X : 0, ci * 2);
         }
         // gradient item = (channel co, output rows 2 yp and 2 yp + 1): 40 consecutive floats ->
-        // image positions 42 yp .. 42 yp + 41 (each output row followed by one zero)
+        // chunks 6 yp .. 6 yp + 5 of the channel's dZ' row (8 positions each; 20 values + 4 zeros per row)
         const int co = tid / 10, yp = tid - co * 10;
         // register prefetch in two halves: the next frame's pixels are in flight while this
         // frame's gradients are converted, and the other way round
         uint32_t nx[NIT][4];
         float4 ng[10];
-        auto load_img = [&](int f) {
-            const uint8_t* fb = in + fm.base(f);
+        // fm.base() of a ring frame is itself a dependent load (the sequence's start row) plus a
+        // 64-bit modulo: it is evaluated one frame ahead of the pixel loads that need it
+        auto load_img = [&](long long fbase) {
+            const uint8_t* fb = in + fbase;
 #pragma unroll
             for (int k = 0; k < NIT; ++k) {
                 const uint32_t* q = reinterpret_cast<const uint32_t*>(fb + soff[k]);
@@ -127,15 +131,31 @@ tc_conv1_wgrad_sw_kernel(const uint8_t* __restrict__ in, const FrameMap fm, cons
 #pragma unroll
             for (int j = 0; j < 10; ++j) ng[j] = __ldg(gp + j);
         };
+        // the register prefetch is half a frame deep; an L2 prefetch two frames ahead turns its
+        // loads into L2 hits (221 + 400 lines of 128 bytes per frame: two per thread)
+        auto prefetch_l2 = [&](int f, long long fbase) {
+            if (f < R) {
+                const uint8_t* fb = in + fbase;
+                const uint8_t* gb = reinterpret_cast<const uint8_t*>(dz + (long long)f * 12800);
+                if (tid < 221) asm volatile("prefetch.global.L2 [%0];" ::"l"(fb + tid * 128));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(gb + tid * 128));
+                if (tid < 80) asm volatile("prefetch.global.L2 [%0];" ::"l"(gb + (320 + tid) * 128));
+            }
+        };
+        long long b_next = 0;
         if (has_work) {
-            load_img(blockIdx.x);
+            load_img(fm.base(blockIdx.x));
             load_dz(blockIdx.x);
+            if ((int)(blockIdx.x + gridDim.x) < R) b_next = fm.base(blockIdx.x + gridDim.x);
+            prefetch_l2(blockIdx.x + gridDim.x, b_next);
         }
         float bsum = 0.f;
         uint32_t it = 0;
         for (int fr = blockIdx.x; fr < R; fr += gridDim.x, ++it) {
             const int s = it % W1_STAGES;
             const bool more = fr + (int)gridDim.x < R;
+            const int f2 = fr + 2 * gridDim.x;
+            const long long b_pref = f2 < R ? fm.base(f2) : 0;           // needed after this frame's conversions
             mbar_wait(&empty_bar[s], ((it / W1_STAGES) & 1) ^ 1);
             uint8_t* img = a_s + (size_t)s * W1_IMG;
             uint8_t* gt = g_s + (size_t)s * W1_DZ;
@@ -150,25 +170,30 @@ tc_conv1_wgrad_sw_kernel(const uint8_t* __restrict__ in, const FrameMap fm, cons
                     *reinterpret_cast<uint4*>(img + doff[k]) = c0;
                     *reinterpret_cast<uint4*>(img + (doff[k] ^ 16u)) = c1;
                 }
-            if (more) load_img(fr + gridDim.x);
+            if (more) load_img(b_next);
             float g[40];
 #pragma unroll
             for (int j = 0; j < 10; ++j) g[4 * j] = ng[j].x, g[4 * j + 1] = ng[j].y, g[4 * j + 2] = ng[j].z, g[4 * j + 3] = ng[j].w;
-            // 42 positions = 21 bf16 pairs: j < 20 -> g[j], j = 20 -> 0, 21 <= j < 41 -> g[j-1], j = 41 -> 0
             float bs = 0.f;
 #pragma unroll
-            for (int jp = 0; jp < 21; ++jp) {
-                const int j0 = 2 * jp, j1 = 2 * jp + 1;
-                const float v0 = j0 < 20 ? g[j0] : j0 == 20 ? 0.f : g[j0 - 1];
-                const float v1 = j1 < 20 ? g[j1] : j1 == 41 ? 0.f : g[j1 - 1];
-                const int m = 42 * yp + j0;
-                *reinterpret_cast<uint32_t*>(gt + (m >> 6) * 4096 + ws_off(co, (m & 63) >> 3) + (m & 7) * 2) = ws_pack(v0, v1);
-                bs += v0 + v1;
+            for (int j = 0; j < 40; ++j) bs += g[j];
+#pragma unroll
+            for (int c = 0; c < 6; ++c) {
+                const int C = 6 * yp + c;                                // chunk of the channel's 512-position row
+                const float* v = g + (c / 3) * 20 + (c % 3) * 8;
+                uint4 w;
+                w.x = ws_pack(v[0], v[1]);
+                w.y = ws_pack(v[2], v[3]);
+                w.z = c % 3 == 2 ? 0u : ws_pack(v[4], v[5]);
+                w.w = c % 3 == 2 ? 0u : ws_pack(v[6], v[7]);
+                *reinterpret_cast<uint4*>(gt + (C >> 3) * 4096 + ws_off(co, C & 7)) = w;
             }
             bsum += bs;
             if (more) load_dz(fr + gridDim.x);
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             mbar_arrive(&full_bar[s]);
+            prefetch_l2(f2, b_pref);
+            b_next = b_pref;
         }
         if (bias_part) {                                                 // fixed order: thread, then row pairs
             bias_s[tid] = bsum;
@@ -180,8 +205,9 @@ tc_conv1_wgrad_sw_kernel(const uint8_t* __restrict__ in, const FrameMap fm, cons
                 bias_part[blockIdx.x * 32 + tid] = t;
             }
         }
-    } else if (warp == MMA_WARP) {
-        if (lane == 0) {
+    } else if (warp < MMA_WARP + 2) {
+        if (lane == 0) {                                                 // issuer `pair`: shifts (24 pair, 24 pair + 1)
+            const int pair = warp - MMA_WARP;
             constexpr uint32_t idesc = umma_idesc_bf16_amn(128, 32);
             uint32_t it = 0;
             for (int fr = blockIdx.x; fr < R; fr += gridDim.x, ++it) {
@@ -190,13 +216,9 @@ tc_conv1_wgrad_sw_kernel(const uint8_t* __restrict__ in, const FrameMap fm, cons
                 tc_fence_after();
                 const uint32_t img = smem_u32(a_s + (size_t)s * W1_IMG), gt = smem_u32(g_s + (size_t)s * W1_DZ);
 #pragma unroll 4
-                for (int ks = 0; ks < W1_KSTEPS; ++ks) {                 // 16 positions per MMA
-                    const uint64_t b = umma_desc_k_sw128(gt + (ks >> 2) * 4096 + (ks & 3) * 32);
-#pragma unroll
-                    for (int pair = 0; pair < 2; ++pair)                 // shifts (21 pair, 21 pair + 1)
-                        umma_f16(tmem_base + pair * 32, umma_desc_mn_sw128(img + (ks * 16 + pair * 21) * 128, 128), b,
-                                 idesc, (it | ks) != 0);
-                }
+                for (int ks = 0; ks < W1_KSTEPS; ++ks)                   // 16 positions per MMA
+                    umma_f16(tmem_base + pair * 32, umma_desc_mn_sw128(img + (ks * 16 + pair * W1_PITCH) * 128, 128),
+                             umma_desc_k_sw128(gt + (ks >> 2) * 4096 + (ks & 3) * 32), idesc, (it | ks) != 0);
                 umma_commit(&empty_bar[s]);
             }
             umma_commit(&acc_full);
@@ -236,7 +258,7 @@ tc_conv1_wgrad_sw_kernel(const uint8_t* __restrict__ in, const FrameMap fm, cons
 // (ci, dy, dx) = two 64-channel planes (the two MN groups of an M = 128 tile), shifts
 // {0, 1, 10, 11}; dZ [32][9][9] -> dZ' [32][100 (+28)]
 constexpr int W2_PROD = 416;                        // 400 image items x 2 + 288 gradient items
-constexpr int W2_THREADS = W2_PROD + 32 + 128;
+constexpr int W2_THREADS = W2_PROD + 64 + 128;
 constexpr int W2_STAGES = 4, W2_KSTEPS = 7;
 constexpr uint32_t W2_PLANE = 128 * 128;            // 128 position rows x 64 bf16
 constexpr uint32_t W2_IMG = 2 * W2_PLANE, W2_DZ = 2 * 32 * 128;
@@ -258,9 +280,9 @@ tc_conv2_wgrad_sw_kernel(const float* __restrict__ in, const float* __restrict__
     if (tid == 0) {
         for (int s = 0; s < W2_STAGES; ++s) {
             mbar_init(&full_bar[s], W2_PROD);
-            mbar_init(&empty_bar[s], 1);
+            mbar_init(&empty_bar[s], 2);
         }
-        mbar_init(&acc_full, 1);
+        mbar_init(&acc_full, 2);
         mbar_fence_init();
     }
     // rows 100..127 of every plane and gradient positions 9, 19, .., 99..127 stay zero for good
@@ -354,8 +376,9 @@ tc_conv2_wgrad_sw_kernel(const float* __restrict__ in, const float* __restrict__
                 bias_part[blockIdx.x * 32 + tid] = t;
             }
         }
-    } else if (warp == MMA_WARP) {
-        if (lane == 0) {
+    } else if (warp < MMA_WARP + 2) {
+        if (lane == 0) {                                                 // issuer ky2: shifts (10 ky2, 10 ky2 + 1)
+            const int ky2 = warp - MMA_WARP;
             constexpr uint32_t idesc = umma_idesc_bf16_amn(128, 32);
             uint32_t it = 0;
             for (int fr = blockIdx.x; fr < R; fr += gridDim.x, ++it) {
@@ -367,9 +390,9 @@ tc_conv2_wgrad_sw_kernel(const float* __restrict__ in, const float* __restrict__
                 for (int ks = 0; ks < W2_KSTEPS; ++ks) {                 // 16 positions per MMA
                     const uint64_t b = umma_desc_k_sw128(gt + (ks >> 2) * 4096 + (ks & 3) * 32);
 #pragma unroll
-                    for (int sh = 0; sh < 4; ++sh)                       // shift (ky2, kx2) = (sh >> 1, sh & 1)
-                        umma_f16(tmem_base + sh * 32,
-                                 umma_desc_mn_sw128(img + (ks * 16 + (sh >> 1) * 10 + (sh & 1)) * 128, W2_PLANE), b, idesc,
+                    for (int kx2 = 0; kx2 < 2; ++kx2)
+                        umma_f16(tmem_base + (ky2 * 2 + kx2) * 32,
+                                 umma_desc_mn_sw128(img + (ks * 16 + ky2 * 10 + kx2) * 128, W2_PLANE), b, idesc,
                                  (it | ks) != 0);
                 }
                 umma_commit(&empty_bar[s]);
