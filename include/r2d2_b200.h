@@ -318,6 +318,12 @@ int r2d2_chansum(const float* dz, float* db, int R, int PIX, float* part, void* 
 int r2d2_tc_linear_x3(const void* x_hi, const void* x_lo, const void* w_hi, const void* w_lo,
                       const float* bias1, const float* bias2, float* y_f32, void* y_bf16, int M,
                       int N, int K, int relu, void* stream);
+/* Same, on at most max_ctas SMs (0 = all).  The kernel is persistent -- a CTA keeps its SM until all
+ * of its tiles are done -- so a caller that wants another kernel to START beside it (the learner:
+ * the online network's recurrence beside the target network's input projection) leaves SMs free. */
+int r2d2_tc_linear_x3_ctas(const void* x_hi, const void* x_lo, const void* w_hi, const void* w_lo,
+                           const float* bias1, const float* bias2, float* y_f32, void* y_bf16, int M,
+                           int N, int K, int relu, int max_ctas, void* stream);
 int r2d2_split_bf16(const float* in, void* hi_bf16, void* lo_bf16, int64_t n, void* stream);
 /* f32 -> bf16 copies feeding r2d2_tc_linear: flat cast, and out[c,r] = in[r,c] */
 int r2d2_cast_bf16(const float* in, void* out_bf16, int64_t n, void* stream);

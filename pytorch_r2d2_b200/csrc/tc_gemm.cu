@@ -176,19 +176,22 @@ tc_gemm_x3_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
                   const __grid_constant__ CUtensorMap tma_b_lo, const TcEpilogue ep, const int M,
                   const int N, const int K, const int bn_rt) {
     // wide form: the tile is bn <= 256 columns wide (multiple of 16, chosen by the host so that the
-    // number of tiles fills whole waves of SMs); the stage layout keeps room for 256
+    // number of tiles fills whole waves of SMs); the stage layout keeps room for 256.
+    // Persistent: CTA b works through tiles b, b + grid, ... (M-tile fastest, so that the CTAs of a
+    // wave share their B columns in L2) with TWO accumulators of 256 TMEM columns -- the epilogue of
+    // one tile (TMEM -> registers -> global) runs under the MMAs of the next.
     const int bn = BN == 128 ? BN : bn_rt;
     constexpr uint32_t A_BYTES = TC_BM * TC_BK * 2, B_BYTES = BN * TC_BK * 2;
     constexpr uint32_t STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;
     constexpr int STAGES = BN == 128 ? 3 : 2;
     constexpr bool CAT = BN == 128;
     extern __shared__ uint8_t smem_raw[];
-    __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], acc_bar;
+    __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], acc_full[2], acc_empty[2];
     __shared__ uint32_t tmem_slot;
     const uint32_t raw = smem_u32(smem_raw);
     uint8_t* tiles = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int m0 = blockIdx.x * TC_BM, n0 = blockIdx.y * bn;
+    const int mt = (M + TC_BM - 1) / TC_BM, ntiles = mt * ((N + bn - 1) / bn);
     const int num_kb = (K + TC_BK - 1) / TC_BK;
 
     if (warp == 0 && lane == 0) {
@@ -200,10 +203,13 @@ tc_gemm_x3_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
         }
-        mbar_init(&acc_bar, 1);
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&acc_full[b], 1);
+            mbar_init(&acc_empty[b], 128);
+        }
         mbar_fence_init();
     }
-    if (warp == 1) tmem_alloc(&tmem_slot, 256);
+    if (warp == 1) tmem_alloc(&tmem_slot, 512);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -211,84 +217,103 @@ tc_gemm_x3_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
 
     if (warp == 0) {
         if (lane == 0) {
-            for (int kb = 0; kb < num_kb; ++kb) {
-                const int s = kb % STAGES;
-                mbar_wait(&empty_bar[s], ((kb / STAGES) & 1) ^ 1);
-                mbar_expect_tx(&full_bar[s], 2 * A_BYTES + 2 * (uint32_t)bn * TC_BK * 2);
-                uint8_t* dst = tiles + (size_t)s * STAGE_BYTES;
-                const int kk = kb * TC_BK;
-                tma_load_2d(dst, &tma_a, kk, m0, &full_bar[s]);
-                tma_load_2d(dst + A_BYTES, &tma_a_lo, kk, m0, &full_bar[s]);
-                tma_load_2d(dst + 2 * A_BYTES, &tma_b, kk, n0, &full_bar[s]);
-                tma_load_2d(dst + 2 * A_BYTES + B_BYTES, &tma_b_lo, kk, n0, &full_bar[s]);
+            uint32_t it = 0;                                             // k-blocks issued so far (all tiles)
+            for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+                const int m0 = (t % mt) * TC_BM, n0 = (t / mt) * bn;
+                for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                    const int s = it % STAGES;
+                    mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
+                    mbar_expect_tx(&full_bar[s], 2 * A_BYTES + 2 * (uint32_t)bn * TC_BK * 2);
+                    uint8_t* dst = tiles + (size_t)s * STAGE_BYTES;
+                    const int kk = kb * TC_BK;
+                    tma_load_2d(dst, &tma_a, kk, m0, &full_bar[s]);
+                    tma_load_2d(dst + A_BYTES, &tma_a_lo, kk, m0, &full_bar[s]);
+                    tma_load_2d(dst + 2 * A_BYTES, &tma_b, kk, n0, &full_bar[s]);
+                    tma_load_2d(dst + 2 * A_BYTES + B_BYTES, &tma_b_lo, kk, n0, &full_bar[s]);
+                }
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {
             const uint32_t idesc = umma_idesc_bf16(TC_BM, bn);
             constexpr uint32_t idesc_cat = umma_idesc_bf16(TC_BM, 256);
-            for (int kb = 0; kb < num_kb; ++kb) {
-                const int s = kb % STAGES;
-                mbar_wait(&full_bar[s], (kb / STAGES) & 1);
+            uint32_t it = 0, ti = 0;
+            for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++ti) {
+                const uint32_t buf = ti & 1, d = tmem_base + buf * 256;
+                mbar_wait(&acc_empty[buf], ((ti >> 1) & 1) ^ 1);
                 tc_fence_after();
-                const uint32_t a_hi = smem_u32(tiles + (size_t)s * STAGE_BYTES), a_lo = a_hi + A_BYTES;
-                const uint32_t b_hi = a_hi + 2 * A_BYTES, b_lo = b_hi + B_BYTES;
+                for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                    const int s = it % STAGES;
+                    mbar_wait(&full_bar[s], (it / STAGES) & 1);
+                    tc_fence_after();
+                    const uint32_t a_hi = smem_u32(tiles + (size_t)s * STAGE_BYTES), a_lo = a_hi + A_BYTES;
+                    const uint32_t b_hi = a_hi + 2 * A_BYTES, b_lo = b_hi + B_BYTES;
 #pragma unroll
-                for (int k = 0; k < TC_BK / 16; ++k) {
-                    const uint32_t acc = (kb | k) != 0;
-                    if constexpr (CAT) {
-                        umma_f16(tmem_base, umma_desc_k_sw128(a_hi + k * 32), umma_desc_k_sw128(b_hi + k * 32), idesc_cat, acc);
-                        umma_f16(tmem_base, umma_desc_k_sw128(a_lo + k * 32), umma_desc_k_sw128(b_hi + k * 32), idesc, 1);
-                    } else {
-                        umma_f16(tmem_base, umma_desc_k_sw128(a_hi + k * 32), umma_desc_k_sw128(b_hi + k * 32), idesc, acc);
-                        umma_f16(tmem_base, umma_desc_k_sw128(a_hi + k * 32), umma_desc_k_sw128(b_lo + k * 32), idesc, 1);
-                        umma_f16(tmem_base, umma_desc_k_sw128(a_lo + k * 32), umma_desc_k_sw128(b_hi + k * 32), idesc, 1);
+                    for (int k = 0; k < TC_BK / 16; ++k) {
+                        const uint32_t acc = (kb | k) != 0;
+                        if constexpr (CAT) {
+                            umma_f16(d, umma_desc_k_sw128(a_hi + k * 32), umma_desc_k_sw128(b_hi + k * 32), idesc_cat, acc);
+                            umma_f16(d, umma_desc_k_sw128(a_lo + k * 32), umma_desc_k_sw128(b_hi + k * 32), idesc, 1);
+                        } else {
+                            umma_f16(d, umma_desc_k_sw128(a_hi + k * 32), umma_desc_k_sw128(b_hi + k * 32), idesc, acc);
+                            umma_f16(d, umma_desc_k_sw128(a_hi + k * 32), umma_desc_k_sw128(b_lo + k * 32), idesc, 1);
+                            umma_f16(d, umma_desc_k_sw128(a_lo + k * 32), umma_desc_k_sw128(b_hi + k * 32), idesc, 1);
+                        }
                     }
+                    umma_commit(&empty_bar[s]);
                 }
-                umma_commit(&empty_bar[s]);
+                umma_commit(&acc_full[buf]);
             }
-            umma_commit(&acc_bar);
         }
     } else {
-        mbar_wait(&acc_bar, 0);
-        tc_fence_after();
         const int q = warp & 3;
-        const int m = m0 + q * 32 + lane;
+        uint32_t ti = 0;
+        for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++ti) {
+            const uint32_t buf = ti & 1, d = tmem_base + buf * 256;
+            const int m0 = (t % mt) * TC_BM, n0 = (t / mt) * bn;
+            mbar_wait(&acc_full[buf], (ti >> 1) & 1);
+            tc_fence_after();
+            const int m = m0 + q * 32 + lane;
 #pragma unroll 1
-        for (int c = 0; c < bn; c += 32) {
-            uint32_t r[32];
-            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c, r);
-            if constexpr (CAT) {
-                uint32_t r2[32];
-                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(128 + c), r2);
-                tmem_ld_wait();
+            for (int c = 0; c < bn; c += 32) {
+                uint32_t r[32];
+                tmem_ld32(d + ((uint32_t)(q * 32) << 16) + (uint32_t)c, r);
+                if constexpr (CAT) {
+                    uint32_t r2[32];
+                    tmem_ld32(d + ((uint32_t)(q * 32) << 16) + (uint32_t)(128 + c), r2);
+                    tmem_ld_wait();
 #pragma unroll
-                for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(__uint_as_float(r[j]) + __uint_as_float(r2[j]));
-            } else {
-                tmem_ld_wait();
-            }
-            if (m < M) {
+                    for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(__uint_as_float(r[j]) + __uint_as_float(r2[j]));
+                } else {
+                    tmem_ld_wait();
+                }
+                if (c + 32 >= bn) {                                      // last read of this accumulator
+                    tc_fence_before();
+                    mbar_arrive(&acc_empty[buf]);
+                }
+                if (m < M) {
 #pragma unroll
-                for (int j = 0; j < 32; j += 4) {
-                    const int n = n0 + c + j;
-                    if (n >= N || c + j >= bn) break;
-                    float v[4];
+                    for (int j = 0; j < 32; j += 4) {
+                        const int n = n0 + c + j;
+                        if (n >= N || c + j >= bn) break;
+                        float v[4];
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        float x = __uint_as_float(r[j + e]);
-                        if (ep.bias1) x += __ldg(ep.bias1 + (ep.bias_row ? m : n + e));
-                        if (ep.bias2) x += __ldg(ep.bias2 + (ep.bias_row ? m : n + e));
-                        if (ep.relu) x = fmaxf(x, 0.f);
-                        v[e] = x;
-                    }
-                    if (ep.c32)
-                        *reinterpret_cast<float4*>(ep.c32 + (long long)m * ep.ldc + n) =
-                            make_float4(v[0], v[1], v[2], v[3]);
-                    if (ep.c16) {
-                        uint2 pk;
-                        pk.x = pack2_bf16(v[0], v[1]);
-                        pk.y = pack2_bf16(v[2], v[3]);
-                        *reinterpret_cast<uint2*>(ep.c16 + (long long)m * ep.ldc + n) = pk;
+                        for (int e = 0; e < 4; ++e) {
+                            float x = __uint_as_float(r[j + e]);
+                            if (ep.bias1) x += __ldg(ep.bias1 + (ep.bias_row ? m : n + e));
+                            if (ep.bias2) x += __ldg(ep.bias2 + (ep.bias_row ? m : n + e));
+                            if (ep.relu) x = fmaxf(x, 0.f);
+                            v[e] = x;
+                        }
+                        if (ep.c32)
+                            *reinterpret_cast<float4*>(ep.c32 + (long long)m * ep.ldc + n) =
+                                make_float4(v[0], v[1], v[2], v[3]);
+                        if (ep.c16) {
+                            uint2 pk;
+                            pk.x = pack2_bf16(v[0], v[1]);
+                            pk.y = pack2_bf16(v[2], v[3]);
+                            *reinterpret_cast<uint2*>(ep.c16 + (long long)m * ep.ldc + n) = pk;
+                        }
                     }
                 }
             }
@@ -296,7 +321,7 @@ tc_gemm_x3_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 1) tmem_dealloc(tmem_base, 256);
+    if (warp == 1) tmem_dealloc(tmem_base, 512);
 }
 
 // ---------------------------------------------------------------- host: tensor maps
@@ -405,7 +430,8 @@ extern "C" {
 
 static int tc_linear_impl(const void* x_hi, const void* x_lo, const void* w_hi, const void* w_lo,
                           const float* bias1, const float* bias2, float* y_f32, void* y_bf16, int M,
-                          int N, int K, int relu, void* stream, const float* mask = nullptr) {
+                          int N, int K, int relu, void* stream, const float* mask = nullptr,
+                          int max_ctas = 0) {
     R2D2_REQUIRE(!mask || (!x_lo && ((uintptr_t)mask % 16) == 0), "tc_linear: mask is for the plain bf16 form, 16-byte aligned");
     R2D2_REQUIRE(x_hi && w_hi && (y_f32 || y_bf16) && M > 0 && N > 0 && K > 0, "tc_linear: bad args");
     R2D2_REQUIRE((x_lo == nullptr) == (w_lo == nullptr), "tc_linear: give both lo parts or neither");
@@ -419,7 +445,8 @@ static int tc_linear_impl(const void* x_hi, const void* x_lo, const void* w_hi, 
         int BNx = 128;
         if (wide) {
             // tile width that wastes the least in the last wave: cost = waves x width
-            const long long mt = (M + TC_BM - 1) / TC_BM, sms = sm_count();
+            const long long mt = (M + TC_BM - 1) / TC_BM;
+            const long long sms = max_ctas > 0 && max_ctas < sm_count() ? max_ctas : sm_count();
             long long best = -1;
             for (int bn = 256; bn >= 144; bn -= 16) {
                 const long long tiles = mt * ((N + bn - 1) / bn), cost = (tiles + sms - 1) / sms * bn;
@@ -436,7 +463,11 @@ static int tc_linear_impl(const void* x_hi, const void* x_lo, const void* w_hi, 
         rc = make_tmap(&tb_lo, w_lo, N, K, BNx);
         if (rc) return rc;
         TcEpilogue ep{y_f32, reinterpret_cast<__nv_bfloat16*>(y_bf16), N, bias1, bias2, relu & 1, (relu >> 1) & 1, nullptr};
-        dim3 grid((M + TC_BM - 1) / TC_BM, (N + BNx - 1) / BNx);
+        const long long tiles_ll = (long long)((M + TC_BM - 1) / TC_BM) * ((N + BNx - 1) / BNx);
+        // persistent: at most one CTA per SM; the caller may leave SMs free for a kernel that
+        // must start beside this one (a CTA keeps its SM until all its tiles are done)
+        const int cta_cap = max_ctas > 0 && max_ctas < sm_count() ? max_ctas : sm_count();
+        const int grid = tiles_ll < cta_cap ? (int)tiles_ll : cta_cap;
         if (wide) {
             const int smem = 2 * (2 * TC_BM * TC_BK * 2 + 2 * 256 * TC_BK * 2) + 1024;
             R2D2_CUDA_OK(cudaFuncSetAttribute(tc_gemm_x3_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -503,6 +534,14 @@ int r2d2_tc_linear_x3(const void* x_hi, const void* x_lo, const void* w_hi, cons
                       int N, int K, int relu, void* stream) {
     R2D2_REQUIRE(x_lo && w_lo, "tc_linear_x3: lo parts required");
     return tc_linear_impl(x_hi, x_lo, w_hi, w_lo, bias1, bias2, y_f32, y_bf16, M, N, K, relu, stream);
+}
+
+int r2d2_tc_linear_x3_ctas(const void* x_hi, const void* x_lo, const void* w_hi, const void* w_lo,
+                           const float* bias1, const float* bias2, float* y_f32, void* y_bf16, int M,
+                           int N, int K, int relu, int max_ctas, void* stream) {
+    R2D2_REQUIRE(x_lo && w_lo && max_ctas >= 0, "tc_linear_x3_ctas: lo parts required, max_ctas >= 0");
+    return tc_linear_impl(x_hi, x_lo, w_hi, w_lo, bias1, bias2, y_f32, y_bf16, M, N, K, relu, stream, nullptr,
+                          max_ctas);
 }
 
 int r2d2_split_bf16(const float* in, void* hi_bf16, void* lo_bf16, int64_t n, void* stream) {

@@ -208,12 +208,13 @@ def tc_linear_masked(x16, w16, mask, y32):
     _lib.call("r2d2_tc_linear_masked", P(x16, "bf16"), P(w16, "bf16"), P(mask, "f32"), P(y32, "f32"), M, N, K, S())
 
 
-def tc_linear_x3(x_hi, x_lo, w_hi, w_lo, b1, b2, y32=None, y16=None, relu=False, bias_row=False):
+def tc_linear_x3(x_hi, x_lo, w_hi, w_lo, b1, b2, y32=None, y16=None, relu=False, bias_row=False, max_ctas=0):
+    """max_ctas > 0: run on at most that many SMs (the kernel is persistent; see the header)."""
     M, K = x_hi.shape
     N = w_hi.shape[0]
-    _lib.call("r2d2_tc_linear_x3", P(x_hi, "bf16"), P(x_lo, "bf16"), P(w_hi, "bf16"), P(w_lo, "bf16"),
+    _lib.call("r2d2_tc_linear_x3_ctas", P(x_hi, "bf16"), P(x_lo, "bf16"), P(w_hi, "bf16"), P(w_lo, "bf16"),
               P(b1, "f32", True), P(b2, "f32", True), P(y32, "f32", True), P(y16, "bf16", True),
-              M, N, K, int(relu) | (2 if bias_row else 0), S())
+              M, N, K, int(relu) | (2 if bias_row else 0), int(max_ctas), S())
 
 
 def tc_lstm_bwd_scratch_bytes(B, H):

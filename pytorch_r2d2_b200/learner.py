@@ -476,8 +476,13 @@ class Learner:
                     torch.cuda.current_stream().wait_event(ws["ev_wprep"])
                 if not fused_conv1:
                     split(ws["feat_tg"], ws["feat16_tg"])
+                # the projection kernel is persistent: it leaves the SMs the online net's recurrence
+                # (a cooperative launch that is ready while this one runs) needs to start
+                free = (H // 16) * ((B + 31) // 32) if overlap else 0
+                sms = ws.setdefault("sm_count", int(_lib.load().r2d2_sm_count()))
                 engine.tc_linear_x3(ws["w_ih16_t"][0], ws["w_ih16_t"][1], ws["feat16_tg"][0],
-                                    ws["feat16_tg"][1], wt.b_ih, wt.b_hh, y32=ws["xpT_tg"], bias_row=True)
+                                    ws["feat16_tg"][1], wt.b_ih, wt.b_hh, y32=ws["xpT_tg"], bias_row=True,
+                                    max_ctas=sms - free if 0 < free < sms - 32 else 0)
                 engine.tc_lstm_seq_fwd(ws["xpT_tg"], 0, wt.w_hh, ws["hs_tg"], ws["cs_tg"], None, T, B, H,
                                        ws["lstm_scratch_tg"], h16=ws["hs16_t"], hist_t0=BI)
             else:
