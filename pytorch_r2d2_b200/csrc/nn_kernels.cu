@@ -47,24 +47,25 @@ __global__ void reduce_partials_kernel(const float* __restrict__ part, float* __
 __global__ void __launch_bounds__(1024)
 colsum_kernel(const float* __restrict__ dy, float* __restrict__ db, int M, int N,
               float* __restrict__ db_copy = nullptr) {
-    __shared__ float red[128][9];
-    const int col = threadIdx.x & 7, rl = threadIdx.x >> 3;
-    const int n = blockIdx.x * 8 + col;
+    // 32 columns x 32 row lanes per block: a warp reads 128 contiguous bytes of one row
+    __shared__ float red[32][33];
+    const int col = threadIdx.x & 31, rl = threadIdx.x >> 5;
+    const int n = blockIdx.x * 32 + col;
     float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
     if (n < N) {
         const float* p = dy + n;
         int m = rl;
-        for (; m + 384 < M; m += 512) {
+        for (; m + 96 < M; m += 128) {
             s0 += p[(int64_t)m * N];
-            s1 += p[(int64_t)(m + 128) * N];
-            s2 += p[(int64_t)(m + 256) * N];
-            s3 += p[(int64_t)(m + 384) * N];
+            s1 += p[(int64_t)(m + 32) * N];
+            s2 += p[(int64_t)(m + 64) * N];
+            s3 += p[(int64_t)(m + 96) * N];
         }
-        for (; m < M; m += 128) s0 += p[(int64_t)m * N];
+        for (; m < M; m += 32) s0 += p[(int64_t)m * N];
     }
     red[rl][col] = (s0 + s1) + (s2 + s3);
     __syncthreads();
-    for (int h = 64; h >= 1; h >>= 1) {
+    for (int h = 16; h >= 1; h >>= 1) {
         if (rl < h) red[rl][col] += red[rl + h][col];
         __syncthreads();
     }
@@ -749,7 +750,7 @@ int r2d2_linear_wgrad(const float* dy, const float* x, float* dw, float* db, int
         R2D2_CUDA_OK((launch_gemm<128, 128, 8, 8>("linear_wgrad", al, bl, ep, N, K, M, 1, st)));
     }
     if (db) {
-        R2D2_LAUNCH("colsum_kernel", st, colsum_kernel<<<(N + 7) / 8, 1024, 0, st>>>(dy, db, M, N));
+        R2D2_LAUNCH("colsum_kernel", st, colsum_kernel<<<(N + 31) / 32, 1024, 0, st>>>(dy, db, M, N));
     }
     return R2D2_OK;
 }
@@ -811,13 +812,13 @@ int r2d2_head_out(const float* hid, const float* w2, const float* b2, float* q, 
 
 int r2d2_colsum(const float* dy, float* db, int M, int N, void* stream) {
     R2D2_REQUIRE(dy && db && M > 0 && N > 0, "colsum: bad args");
-    R2D2_LAUNCH("colsum_kernel", as_stream(stream), colsum_kernel<<<(N + 7) / 8, 1024, 0, as_stream(stream)>>>(dy, db, M, N));
+    R2D2_LAUNCH("colsum_kernel", as_stream(stream), colsum_kernel<<<(N + 31) / 32, 1024, 0, as_stream(stream)>>>(dy, db, M, N));
     return R2D2_OK;
 }
 
 int r2d2_colsum2(const float* dy, float* db, float* db_copy, int M, int N, void* stream) {
     R2D2_REQUIRE(dy && db && db_copy && M > 0 && N > 0, "colsum2: bad args");
-    R2D2_LAUNCH("colsum_kernel", as_stream(stream), colsum_kernel<<<(N + 7) / 8, 1024, 0, as_stream(stream)>>>(dy, db, M, N, db_copy));
+    R2D2_LAUNCH("colsum_kernel", as_stream(stream), colsum_kernel<<<(N + 31) / 32, 1024, 0, as_stream(stream)>>>(dy, db, M, N, db_copy));
     return R2D2_OK;
 }
 
@@ -937,7 +938,7 @@ int r2d2_linear_wgrad_static(const float* dy, const float* x, float* dw, float* 
         R2D2_LAUNCH("linear_wgrad", st,
                     gemm_kernel<128, 128, 8, 8, AL, AL, EpiDense><<<grid, 256, 0, st>>>(al, bl, ep, N, K, M, kps));
     }
-    if (db) R2D2_LAUNCH("colsum_kernel", st, colsum_kernel<<<(N + 7) / 8, 1024, 0, st>>>(dy, db, M, N));
+    if (db) R2D2_LAUNCH("colsum_kernel", st, colsum_kernel<<<(N + 31) / 32, 1024, 0, st>>>(dy, db, M, N));
     return R2D2_OK;
 }
 

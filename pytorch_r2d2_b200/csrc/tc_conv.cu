@@ -717,24 +717,34 @@ static int launch_tc_wgrad(const char* name, const T* in, FrameMap fm, const flo
     return R2D2_OK;
 }
 
-// dw[i] = sum_z part[z*nw + i]  and  db[c] = sum_z bias_part[z*32 + c]  in one launch, fixed order
-__global__ void reduce_wgrad_partials_kernel(const float* __restrict__ part, float* __restrict__ dw, int nw,
-                                             const float* __restrict__ bias_part, float* __restrict__ db,
-                                             int splits) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+// dw[i] = sum_z part[z*nw + i]  and  db[c] = sum_z bias_part[z*32 + c]  in one launch.  Fixed order:
+// four interleaved chains (z = j, j + 4, ...) per output, each summed in order, then
+// (c0 + c1) + (c2 + c3).  64 outputs x 4 chains per block: 148 partials of a 16K-element gradient
+// are 256 blocks of short loops instead of 64 blocks of long ones.
+__global__ void __launch_bounds__(256)
+reduce_wgrad_partials_kernel(const float* __restrict__ part, float* __restrict__ dw, int nw,
+                             const float* __restrict__ bias_part, float* __restrict__ db,
+                             int splits) {
+    __shared__ float sh[4][64];
+    const int o = threadIdx.x & 63, chain = threadIdx.x >> 6;
+    const int i = blockIdx.x * 64 + o;
+    float s = 0.f;
     if (i < nw) {
-        float s = 0.f;
-        for (int z = 0; z < splits; ++z) s += part[(long long)z * nw + i];
-        dw[i] = s;
+        for (int z = chain; z < splits; z += 4) s += part[(long long)z * nw + i];
     } else if (i < nw + 32) {
-        float s = 0.f;
-        for (int z = 0; z < splits; ++z) s += bias_part[z * 32 + (i - nw)];
-        db[i - nw] = s;
+        for (int z = chain; z < splits; z += 4) s += bias_part[z * 32 + (i - nw)];
+    }
+    sh[chain][o] = s;
+    __syncthreads();
+    if (chain == 0) {
+        const float t = (sh[0][o] + sh[1][o]) + (sh[2][o] + sh[3][o]);
+        if (i < nw) dw[i] = t;
+        else if (i < nw + 32) db[i - nw] = t;
     }
 }
 static int reduce_wgrad(const float* part, float* dw, int nw, float* db, int grid, cudaStream_t st) {
     // bias partials live behind the weight partials of all CTAs
-    R2D2_LAUNCH("reduce_partials_kernel", st, reduce_wgrad_partials_kernel<<<(nw + 32 + 255) / 256, 256, 0, st>>>(
+    R2D2_LAUNCH("reduce_partials_kernel", st, reduce_wgrad_partials_kernel<<<(nw + 32 + 63) / 64, 256, 0, st>>>(
         part, dw, nw, part + (long long)grid * nw, db, grid));
     return R2D2_OK;
 }
