@@ -318,6 +318,11 @@ int r2d2_chansum(const float* dz, float* db, int R, int PIX, float* part, void* 
 int r2d2_tc_linear_x3(const void* x_hi, const void* x_lo, const void* w_hi, const void* w_lo,
                       const float* bias1, const float* bias2, float* y_f32, void* y_bf16, int M,
                       int N, int K, int relu, void* stream);
+/* y[P, Q] = a^T . b for row-major bf16 a [Kc, P] and b [Kc, Q] (P, Q multiples of 8): the weight
+ * gradients dW = dY^T . X (learner.py:98, autograd of model.py:26-36,55) straight from the
+ * activations and gradients as they lie in memory -- both operands are read MN-major by the
+ * tensor cores, no transposed copies. */
+int r2d2_tc_linear_tn(const void* a_bf16, const void* b_bf16, float* y_f32, int Kc, int P, int Q, void* stream);
 /* Same, on at most max_ctas SMs (0 = all).  The kernel is persistent -- a CTA keeps its SM until all
  * of its tiles are done -- so a caller that wants another kernel to START beside it (the learner:
  * the online network's recurrence beside the target network's input projection) leaves SMs free. */

@@ -324,6 +324,102 @@ tc_gemm_x3_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
     if (warp == 1) tmem_dealloc(tmem_base, 512);
 }
 
+// ---------------------------------------------------------------- C = A^T . B, no transposed copies
+//   C[P, Q] = sum_k A[k, P] * B[k, Q]        A [Kc, P], B [Kc, Q] row-major bf16; C f32
+// The weight gradients dW = dY^T . X contract over the ROWS of two row-major matrices.  Both
+// operands are consumed MN-major: a TMA box of 64 elements x 64 rows lands as [k row][128 bytes]
+// (SWIZZLE_128B), which is one 64-element MN group of the UMMA operand; a 128-wide tile is two such
+// groups 8 KB apart, a k-step of 16 rows is 2 KB further down.  (The K-major form needs A^T and
+// B^T materialised first -- five transposing passes per step in the learner.)
+template <int BN>
+__global__ void __launch_bounds__(192, 1)
+tc_gemm_tn_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                  float* __restrict__ c, const int P, const int Q, const int Kc) {
+    constexpr uint32_t G_BYTES = 64 * 128;                               // one group: 64 k rows x 64 elements
+    constexpr uint32_t A_BYTES = 2 * G_BYTES, B_BYTES = (BN / 64) * G_BYTES;
+    constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t full_bar[TC_STAGES], empty_bar[TC_STAGES], acc_bar;
+    __shared__ uint32_t tmem_slot;
+    const uint32_t raw = smem_u32(smem_raw);
+    uint8_t* tiles = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = blockIdx.x * TC_BM, n0 = blockIdx.y * BN;
+    const int num_kb = (Kc + 63) / 64;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tma_a);
+        tma_prefetch_desc(&tma_b);
+        for (int s = 0; s < TC_STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(&acc_bar, 1);
+        mbar_fence_init();
+    }
+    if (warp == 1) tmem_alloc(&tmem_slot, BN);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % TC_STAGES;
+                mbar_wait(&empty_bar[s], ((kb / TC_STAGES) & 1) ^ 1);
+                mbar_expect_tx(&full_bar[s], STAGE_BYTES);               // out-of-range parts arrive as zeros
+                uint8_t* dst = tiles + (size_t)s * STAGE_BYTES;
+                tma_load_2d(dst, &tma_a, m0, kb * 64, &full_bar[s]);
+                tma_load_2d(dst + G_BYTES, &tma_a, m0 + 64, kb * 64, &full_bar[s]);
+#pragma unroll
+                for (int g = 0; g < BN / 64; ++g)
+                    tma_load_2d(dst + A_BYTES + g * G_BYTES, &tma_b, n0 + 64 * g, kb * 64, &full_bar[s]);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(TC_BM, BN) | (1u << 15) | (1u << 16);   // A and B MN-major
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % TC_STAGES;
+                mbar_wait(&full_bar[s], (kb / TC_STAGES) & 1);
+                tc_fence_after();
+                const uint32_t a_addr = smem_u32(tiles + (size_t)s * STAGE_BYTES), b_addr = a_addr + A_BYTES;
+#pragma unroll
+                for (int k = 0; k < 4; ++k)                              // 16 k rows per MMA
+                    umma_f16(tmem_base, umma_desc_mn_sw128(a_addr + k * 2048, G_BYTES),
+                             umma_desc_mn_sw128(b_addr + k * 2048, G_BYTES), idesc, (kb | k) != 0);
+                umma_commit(&empty_bar[s]);
+            }
+            umma_commit(&acc_bar);
+        }
+    } else {
+        mbar_wait(&acc_bar, 0);
+        tc_fence_after();
+        const int q = warp & 3;
+        const int m = m0 + q * 32 + lane;
+#pragma unroll 1
+        for (int cc = 0; cc < BN; cc += 32) {
+            uint32_t r[32];
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)cc, r);
+            tmem_ld_wait();
+            if (m < P) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) {
+                    const int n = n0 + cc + j;
+                    if (n >= Q) break;
+                    *reinterpret_cast<float4*>(c + (long long)m * Q + n) =
+                        make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
+                                    __uint_as_float(r[j + 3]));
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, BN);
+}
+
 // ---------------------------------------------------------------- host: tensor maps
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
@@ -353,6 +449,23 @@ static int make_tmap(CUtensorMap* tm, const void* base, long long rows, long lon
     cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
     cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
     cuuint32_t box[2] = {(cuuint32_t)TC_BK, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides,
+                    box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    R2D2_REQUIRE(r == CUDA_SUCCESS, "tc_gemm: cuTensorMapEncodeTiled failed with %d", (int)r);
+    return R2D2_OK;
+}
+
+// row-major bf16 [rows, cols]; box = 64 cols x 64 rows (one MN group of an MN-major operand)
+static int make_tmap_mn(CUtensorMap* tm, const void* base, long long rows, long long cols) {
+    EncodeTiledFn fn = encode_fn();
+    R2D2_REQUIRE(fn, "tc_gemm: cuTensorMapEncodeTiled is unavailable in this driver");
+    R2D2_REQUIRE(((uintptr_t)base % 16) == 0 && (cols * 2) % 16 == 0,
+                 "tc_gemm: operand base must be 16-byte aligned and its row a multiple of 8 elements (%lld)", cols);
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
+    cuuint32_t box[2] = {64, 64};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides,
                     box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
@@ -520,6 +633,28 @@ int r2d2_tc_linear(const void* x_bf16, const void* w_bf16, const float* bias1, c
                    float* y_f32, void* y_bf16, int M, int N, int K, int relu, void* stream) {
     return tc_linear_impl(x_bf16, nullptr, w_bf16, nullptr, bias1, bias2, y_f32, y_bf16, M, N, K, relu,
                           stream);
+}
+
+int r2d2_tc_linear_tn(const void* a_bf16, const void* b_bf16, float* y_f32, int Kc, int P, int Q, void* stream) {
+    R2D2_REQUIRE(a_bf16 && b_bf16 && y_f32 && Kc > 0 && P > 0 && Q > 0, "tc_linear_tn: bad args");
+    R2D2_REQUIRE(P % 8 == 0 && Q % 8 == 0 && ((uintptr_t)y_f32 % 16) == 0,
+                 "tc_linear_tn: P and Q must be multiples of 8, y 16-byte aligned (P=%d Q=%d)", P, Q);
+    CUtensorMap ta, tb;
+    int rc = make_tmap_mn(&ta, a_bf16, Kc, P);
+    if (rc) return rc;
+    rc = make_tmap_mn(&tb, b_bf16, Kc, Q);
+    if (rc) return rc;
+    constexpr int BN = 128;
+    const int smem = TC_STAGES * (2 + BN / 64) * 64 * 128 + 1024;
+    static bool attr_set = false;
+    if (!attr_set) {
+        R2D2_CUDA_OK(cudaFuncSetAttribute(tc_gemm_tn_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr_set = true;
+    }
+    dim3 grid((P + TC_BM - 1) / TC_BM, (Q + BN - 1) / BN);
+    R2D2_LAUNCH("tc_gemm_tn_kernel", as_stream(stream),
+                tc_gemm_tn_kernel<BN><<<grid, 192, smem, as_stream(stream)>>>(ta, tb, y_f32, P, Q, Kc));
+    return R2D2_OK;
 }
 
 int r2d2_tc_linear_masked(const void* x_bf16, const void* w_bf16, const float* mask, float* y_f32,

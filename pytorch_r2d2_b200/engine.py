@@ -208,6 +208,14 @@ def tc_linear_masked(x16, w16, mask, y32):
     _lib.call("r2d2_tc_linear_masked", P(x16, "bf16"), P(w16, "bf16"), P(mask, "f32"), P(y32, "f32"), M, N, K, S())
 
 
+def tc_linear_tn(a16, b16, y32):
+    """y [P, Q] = a^T . b for row-major bf16 a [K, P], b [K, Q] (weight gradients; no transposes)."""
+    Kc, Pn = a16.shape
+    Qn = b16.shape[1]
+    assert b16.shape[0] == Kc and y32.numel() == Pn * Qn
+    _lib.call("r2d2_tc_linear_tn", P(a16, "bf16"), P(b16, "bf16"), P(y32, "f32"), Kc, Pn, Qn, S())
+
+
 def tc_linear_x3(x_hi, x_lo, w_hi, w_lo, b1, b2, y32=None, y16=None, relu=False, bias_row=False, max_ctas=0):
     """max_ctas > 0: run on at most that many SMs (the kernel is persistent; see the header)."""
     M, K = x_hi.shape

@@ -334,8 +334,7 @@ class Learner:
             ws["ev_wprep"] = torch.cuda.Event()
             ws["events"] = [torch.cuda.Event() for _ in range(16)]
             ws["ev_fork"], ws["ev_join"] = torch.cuda.Event(), torch.cuda.Event()
-            ws["dhid16"], ws["dhidT16"], ws["hsT16"] = h(M, 2 * H), h(2 * H, M), h(H, M)
-            ws["dg16"], ws["dgT16"], ws["hprevT16"], ws["featT16"] = h(M, 4 * H), h(4 * H, M), h(H, M), h(FEAT, M)
+            ws["dhid16"], ws["dg16"], ws["hprev16"] = h(M, 2 * H), h(M, 4 * H), h(M, H)
         self._ws = ws
         return ws
 
@@ -593,29 +592,28 @@ class Learner:
             beside(priorities)
             engine.head_bwd(td["dq"], ws["hid_on"], w, ws["dhid"], None, None)
 
-            def head_wgrad():     # dW2, db2; dW1 = dhid^T . hs  (operands transposed to [*, M] bf16)
+            engine.cast_bf16(ws["dhid"], ws["dhid16"])
+
+            # weight gradients dW = dY^T . X straight from the row-major bf16 gradients and
+            # activations the step already holds (both operands MN-major: no transposed copies)
+            def head_wgrad():     # dW2, db2; dW1 = dhid^T . hs
                 engine.head_bwd(td["dq"], ws["hid_on"], w, None, g.head_w2, g.head_b2)
-                engine.transpose_cast_bf16(ws["dhid"], ws["dhidT16"])
-                engine.transpose_cast_bf16(hs_learn, ws["hsT16"])
-                engine.tc_linear(ws["dhidT16"], ws["hsT16"], None, None, y32=g.head_w1)
+                engine.tc_linear_tn(ws["dhid16"], ws["hs16_l"][0], g.head_w1)
                 engine.colsum(ws["dhid"], g.head_b1)
 
             beside(head_wgrad)
-            engine.cast_bf16(ws["dhid"], ws["dhid16"])
             engine.tc_linear(ws["dhid16"], ws["hw1T16"], None, None, y32=ws["dhs"])
 
-            def lstm_wgrad_operands():   # forward-only operands: transposed while the BPTT runs
-                engine.transpose_cast_bf16(hprev, ws["hprevT16"])
-                engine.transpose_cast_bf16(feat_l, ws["featT16"])
+            def lstm_wgrad_operands():   # forward-only operand: cast while the BPTT runs
+                engine.cast_bf16(hprev, ws["hprev16"])
 
             beside(lstm_wgrad_operands, aux)
             engine.tc_lstm_seq_bwd(ws["dhs"], w.w_hh, ws["gates"][BI:], ws["cs_on"][BI:], ws["dgates"],
                                    L, B, H, ws["lstm_bwd_scratch"], dgates16=ws["dg16"])
 
             def lstm_wgrad():
-                engine.transpose_cast_bf16(ws["dgates"], ws["dgT16"])
-                engine.tc_linear(ws["dgT16"], ws["hprevT16"], None, None, y32=g.w_hh)
-                engine.tc_linear(ws["dgT16"], ws["featT16"], None, None, y32=g.w_ih)
+                engine.tc_linear_tn(ws["dg16"], ws["hprev16"], g.w_hh)
+                engine.tc_linear_tn(ws["dg16"], ws["feat16_on"][0][BI * B: T * B], g.w_ih)
                 engine.colsum(ws["dgates"], g.b_hh, g.b_ih)
 
             beside(lstm_wgrad, aux)       # the longest consumer chain gets a stream of its own

@@ -60,6 +60,20 @@ def test_tc_linear_x3_is_fp32_accurate(cuda_device, M, N, K):
     assert rel_err(y1, want) > err          # the compensation is doing something
 
 
+@pytest.mark.parametrize("Kc,P,Q", [(2560, 2048, 512), (2560, 2048, 1568), (200, 72, 40), (64, 128, 128), (130, 8, 264)])
+def test_tc_linear_tn_vs_fp64(cuda_device, Kc, P, Q):
+    """y = a^T . b with both operands read MN-major (no transposed copies) == the fp64 product of
+    the same bf16 values to fp32-accumulation accuracy, incl. ragged K, P and Q."""
+    from pytorch_r2d2_b200 import engine
+    g = torch.Generator().manual_seed(Kc + P + Q)
+    a = torch.randn(Kc, P, generator=g).bfloat16().cuda()
+    b = torch.randn(Kc, Q, generator=g).bfloat16().cuda()
+    y = torch.full((P, Q), float("nan"), device="cuda")
+    engine.tc_linear_tn(a, b, y)
+    want = a.double().T @ b.double()
+    assert rel_err(y, want) < 1e-5, rel_err(y, want)     # fp32 accumulation over Kc terms
+
+
 def test_cast_and_transpose(cuda_device):
     from pytorch_r2d2_b200 import engine
     x = torch.randn(1000, 1568, device="cuda")
