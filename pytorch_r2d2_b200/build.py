@@ -8,7 +8,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libr2d2_b200.so")
-SOURCES = ("replay_kernels.cu", "nn_kernels.cu", "tc_gemm.cu", "tc_conv.cu", "tc_conv_sw.cu", "tc_conv1_sw.cu", "tc_wgrad_sw.cu", "tc_lstm.cu", "dp_peer.cu", "actor_kernels.cu")
+SOURCES = ("replay_kernels.cu", "nn_kernels.cu", "tc_gemm.cu", "tc_conv.cu", "tc_conv_sw.cu", "tc_conv1_sw.cu", "tc_wgrad_sw.cu", "tc_dgrad_sw.cu", "tc_lstm.cu", "dp_peer.cu", "actor_kernels.cu")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC"]
 

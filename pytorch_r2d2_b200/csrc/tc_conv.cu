@@ -34,6 +34,9 @@ int launch_tc_conv1_wgrad_sw(const uint8_t* in, FrameMap fm, const float* dz, fl
                              int grid, cudaStream_t st, float* bias_part);
 int launch_tc_conv2_wgrad_sw(const float* in, const float* dz, float* part, int R, int grid, cudaStream_t st,
                              float* bias_part);
+// tc_dgrad_sw.cu
+int launch_tc_conv2_dgrad_sw(const float* dz2, const float* w2, const uint32_t* maskbits, float* dz1, int R,
+                             cudaStream_t st);
 // tc_conv_sw.cu
 template <int L>
 int launch_tc_conv_sw(const char* name, const float* in, const float* w, const float* b, float* out, int R,
@@ -1260,6 +1263,11 @@ static int dgrad2_launch(const float* dz2, const float* w2, const float* a1, con
     const int ntiles = (int)(((long long)R * 100 + 127) / 128);
     int grid = sm_count();
     if (grid > ntiles) grid = ntiles;
+    static const bool gather_form = [] {                 // R2D2_DGRAD=gather: the previous kernels (A/B runs)
+        const char* e = getenv("R2D2_DGRAD");
+        return e && e[0] == 'g';
+    }();
+    if (maskbits && !gather_form) return launch_tc_conv2_dgrad_sw(dz2, w2, maskbits, dz1, R, st);
     if (maskbits) {
         R2D2_CUDA_OK(cudaFuncSetAttribute(tc_conv_dgrad2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         R2D2_LAUNCH("tc_conv2_dgrad", st, tc_conv_dgrad2_kernel<true><<<grid, 416, smem, st>>>(dz2, w2, nullptr, maskbits, dz1, R));
