@@ -37,6 +37,7 @@ int launch_tc_conv2_wgrad_sw(const float* in, const float* dz, float* part, int 
 // tc_dgrad_sw.cu
 int launch_tc_conv2_dgrad_sw(const float* dz2, const float* w2, const uint32_t* maskbits, float* dz1, int R,
                              cudaStream_t st);
+int launch_tc_conv3_dgrad_sw(const float* dz3, const float* w3, const float* a2, float* dz2, int R, cudaStream_t st);
 // tc_conv_sw.cu
 template <int L>
 int launch_tc_conv_sw(const char* name, const float* in, const float* w, const float* b, float* out, int R,
@@ -1255,6 +1256,11 @@ int r2d2_tc_torso_fwd_tail(const float* a1, int R, const float* w2, const float*
 int r2d2_tc_conv_dgrad3(const float* dz3, const float* w3, const float* a2, float* dz2, int R,
                         void* stream) {
     R2D2_REQUIRE(dz3 && w3 && a2 && dz2 && R > 0, "tc_conv_dgrad3: bad args");
+    static const bool gather_form = [] {                 // R2D2_DGRAD=gather: the previous kernel (A/B runs)
+        const char* e = getenv("R2D2_DGRAD");
+        return e && e[0] == 'g';
+    }();
+    if (!gather_form) return launch_tc_conv3_dgrad_sw(dz3, w3, a2, dz2, R, as_stream(stream));
     return launch_tc_dgrad<3, 9, 7, 1, 0, 0>("tc_conv3_dgrad", dz3, w3, a2, dz2, R, as_stream(stream));
 }
 static int dgrad2_launch(const float* dz2, const float* w2, const float* a1, const uint32_t* maskbits,
