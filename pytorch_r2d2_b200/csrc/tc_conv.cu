@@ -34,6 +34,8 @@ int launch_tc_conv1_wgrad_sw(const uint8_t* in, FrameMap fm, const float* dz, fl
                              int grid, cudaStream_t st, float* bias_part);
 int launch_tc_conv2_wgrad_sw(const float* in, const float* dz, float* part, int R, int grid, cudaStream_t st,
                              float* bias_part);
+int launch_tc_conv3_wgrad_sw(const float* in, const float* dz, float* part, int R, int grid, cudaStream_t st,
+                             float* bias_part);
 // tc_dgrad_sw.cu
 int launch_tc_conv2_dgrad_sw(const float* dz2, const float* w2, const uint32_t* maskbits, float* dz1, int R,
                              cudaStream_t st);
@@ -1194,6 +1196,14 @@ static bool wgrad_gather_form() {
     }();
     return v;
 }
+static int launch_conv3_wgrad(const float* a2, const float* dz, float* part, int R, int* grid_out, cudaStream_t st,
+                              float* bias_part = nullptr) {
+    if (wgrad_gather_form())
+        return launch_tc_wgrad<float, 32, 3, 9, 7, 1, 3>("tc_conv3_wgrad", a2, FrameMap{0, 0, 0, 2592}, dz, part, R, 1.f,
+                                                         grid_out, st, bias_part);
+    *grid_out = wgrad_grid(R, 49);
+    return launch_tc_conv3_wgrad_sw(a2, dz, part, R, *grid_out, st, bias_part);
+}
 static int launch_conv2_wgrad(const float* a1, const float* dz, float* part, int R, int* grid_out, cudaStream_t st,
                               float* bias_part = nullptr) {
     if (wgrad_gather_form())
@@ -1310,8 +1320,7 @@ int r2d2_tc_torso_wgrad_u8(const uint8_t* slab, int B, int S, int s0, int nt, co
     const int R = B * nt;
     float* part = static_cast<float*>(scratch);
     int grid = 0;
-    int rc = launch_tc_wgrad<float, 32, 3, 9, 7, 1, 3>("tc_conv3_wgrad", a2, FrameMap{0, 0, 0, 2592}, dz3,
-                                                       part, R, 1.f, &grid, st);
+    int rc = launch_conv3_wgrad(a2, dz3, part, R, &grid, st);
     if (rc) return rc;
     rc = r2d2_reduce_partials(part, dw3, 32 * 288, grid, stream);
     if (rc) return rc;
@@ -1344,9 +1353,7 @@ int r2d2_tc_conv_wgrad_layer(int layer, const void* in, int B, int S, int s0, in
         rc = launch_conv2_wgrad(static_cast<const float*>(in), dz, part, R, &grid, st, bias_part);
     } else if (layer == 3) {
         K = 288;
-        rc = launch_tc_wgrad<float, 32, 3, 9, 7, 1, 3>("tc_conv3_wgrad", static_cast<const float*>(in),
-                                                       FrameMap{0, 0, 0, 2592}, dz, part, R, 1.f, &grid, st,
-                                                       bias_part);
+        rc = launch_conv3_wgrad(static_cast<const float*>(in), dz, part, R, &grid, st, bias_part);
     } else {
         return set_err(R2D2_EINVAL, "tc_conv_wgrad_layer: layer must be 1, 2 or 3");
     }

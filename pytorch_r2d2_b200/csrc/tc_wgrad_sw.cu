@@ -428,6 +428,163 @@ tc_conv2_wgrad_sw_kernel(const float* __restrict__ in, const float* __restrict__
     if (warp == MMA_WARP) tmem_dealloc(tmem_base, 128);
 }
 
+// ---------------------------------------------------------------------------------------------
+// third layer: 3x3 / stride 1 on fp32 [32][9][9]: 81 positions x 32 channels.  A 128-byte row holds
+// TWO column shifts, row m = [a2[m][0..31] | a2[m+1][0..31]] (kx = 0, 1); the same image two rows
+// further down is kx = 2 (and a fourth, unused column) -- the second MN group of the M = 128 tile
+// (leading-dimension offset 256 bytes).  One MMA per k-step and ky; dZ [32][7][7] -> dZ' [32][64]
+// on the 9-wide grid, K = 64 positions.
+constexpr int W3_PROD = 352;                        // 81 positions x 4 channel octets = 324 image items
+constexpr int W3_THREADS = W3_PROD + 32 + 128;
+constexpr int W3_STAGES = 4;
+constexpr uint32_t W3_IMG = 96 * 128, W3_DZ = 32 * 128;
+constexpr int W3_SMEM = W3_STAGES * (W3_IMG + W3_DZ) + 1024;
+
+__global__ void __launch_bounds__(W3_THREADS, 1)
+tc_conv3_wgrad_sw_kernel(const float* __restrict__ in, const float* __restrict__ dz, float* __restrict__ part,
+                         const int R, float* __restrict__ bias_part) {
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t full_bar[W3_STAGES], empty_bar[W3_STAGES], acc_full;
+    __shared__ uint32_t tmem_slot;
+    __shared__ float bias_s[224];
+    const uint32_t raw = smem_u32(smem_raw);
+    uint8_t* base = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    constexpr int MMA_WARP = W3_PROD / 32;
+    const bool has_work = (int)blockIdx.x < R;
+
+    if (tid == 0) {
+        for (int s = 0; s < W3_STAGES; ++s) {
+            mbar_init(&full_bar[s], W3_PROD);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(&acc_full, 1);
+        mbar_fence_init();
+    }
+    for (uint32_t i = tid * 16; i < W3_STAGES * (W3_IMG + W3_DZ); i += blockDim.x * 16)
+        *reinterpret_cast<uint4*>(base + i) = make_uint4(0, 0, 0, 0);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    if (warp == MMA_WARP) tmem_alloc(&tmem_slot, 128);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+
+    if (warp < MMA_WARP) {
+        // image item = (position m, octet of ci): 8 loads -> chunk oc of row m and chunk 4 + oc of row m - 1
+        const bool img_t = tid < 324;
+        const int m = img_t ? tid % 81 : 0, oc = img_t ? tid / 81 : 0;
+        const uint32_t d0 = ws_off(m, oc), d1 = ws_off(m > 0 ? m - 1 : 0, 4 + oc);
+        const float* src = in + (long long)(oc * 8) * 81 + m;
+        // gradient item = (co, oy): 7 floats -> positions 9 oy .. 9 oy + 6 of row co
+        const bool dz_t = tid < 224;
+        const int co = tid / 7, oy = tid - co * 7;
+        float nx[8], ng[7];
+        auto load = [&](int f) {
+            if (img_t) {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) nx[e] = __ldg(src + (long long)f * 2592 + e * 81);
+            }
+            if (dz_t) {
+                const float* gp = dz + ((long long)f * 32 + co) * 49 + 7 * oy;
+#pragma unroll
+                for (int j = 0; j < 7; ++j) ng[j] = __ldg(gp + j);
+            }
+        };
+        if (has_work) load(blockIdx.x);
+        float bsum = 0.f;
+        uint32_t it = 0;
+        for (int fr = blockIdx.x; fr < R; fr += gridDim.x, ++it) {
+            const int s = it % W3_STAGES;
+            const uint4 c = make_uint4(ws_pack(nx[0], nx[1]), ws_pack(nx[2], nx[3]), ws_pack(nx[4], nx[5]), ws_pack(nx[6], nx[7]));
+            __nv_bfloat16 g16[7];
+            float bs = 0.f;
+#pragma unroll
+            for (int j = 0; j < 7; ++j) {
+                g16[j] = __float2bfloat16_rn(ng[j]);
+                bs += ng[j];
+            }
+            bsum += bs;
+            if (fr + (int)gridDim.x < R) load(fr + gridDim.x);
+            mbar_wait(&empty_bar[s], ((it / W3_STAGES) & 1) ^ 1);
+            uint8_t* img = base + (size_t)s * (W3_IMG + W3_DZ);
+            uint8_t* gt = img + W3_IMG;
+            if (img_t) {
+                *reinterpret_cast<uint4*>(img + d0) = c;
+                if (m > 0) *reinterpret_cast<uint4*>(img + d1) = c;
+            }
+            if (dz_t) {
+#pragma unroll
+                for (int j = 0; j < 7; ++j) {
+                    const int mm = 9 * oy + j;
+                    *reinterpret_cast<__nv_bfloat16*>(gt + ws_off(co, mm >> 3) + (mm & 7) * 2) = g16[j];
+                }
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            mbar_arrive(&full_bar[s]);
+        }
+        if (bias_part) {                                                 // fixed order: thread, then rows
+            if (dz_t) bias_s[tid] = bsum;
+            ws_bar(1, W3_PROD);
+            if (tid < 32) {
+                float t = 0.f;
+#pragma unroll
+                for (int j = 0; j < 7; ++j) t += bias_s[tid * 7 + j];
+                bias_part[blockIdx.x * 32 + tid] = t;
+            }
+        }
+    } else if (warp == MMA_WARP) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16_amn(128, 32);
+            uint32_t it = 0;
+            for (int fr = blockIdx.x; fr < R; fr += gridDim.x, ++it) {
+                const int s = it % W3_STAGES;
+                mbar_wait(&full_bar[s], (it / W3_STAGES) & 1);
+                tc_fence_after();
+                const uint32_t img = smem_u32(base + (size_t)s * (W3_IMG + W3_DZ)), gt = img + W3_IMG;
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks) {                         // 16 positions per MMA
+                    const uint64_t b = umma_desc_k_sw128(gt + ks * 32);
+#pragma unroll
+                    for (int ky = 0; ky < 3; ++ky)
+                        umma_f16(tmem_base + ky * 32, umma_desc_mn_sw128(img + (ks * 16 + 9 * ky) * 128, 256), b, idesc,
+                                 (it | ks) != 0);
+                }
+                umma_commit(&empty_bar[s]);
+            }
+            umma_commit(&acc_full);
+        }
+    } else {
+        // ================= epilogue (once): TMEM lane = (kx, ci) (kx = 3 unused), 32 columns = co per ky
+        const int q = warp & 3;
+        if (has_work) {
+            mbar_wait(&acc_full, 0);
+            tc_fence_after();
+        }
+        float* out = part + (long long)blockIdx.x * 32 * 288;
+        const int l = q * 32 + lane, kx = l >> 5, ci = l & 31;
+#pragma unroll 1
+        for (int ky = 0; ky < 3; ++ky) {
+            uint32_t r[32];
+            if (has_work) {
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + ky * 32, r);
+                tmem_ld_wait();
+            } else {
+#pragma unroll
+                for (int c = 0; c < 32; ++c) r[c] = 0u;
+            }
+            if (kx < 3) {
+                const int k = ci * 9 + ky * 3 + kx;
+#pragma unroll
+                for (int c = 0; c < 32; ++c) out[c * 288 + k] = __uint_as_float(r[c]);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == MMA_WARP) tmem_dealloc(tmem_base, 128);
+}
+
 }  // namespace
 
 // part: [grid][32][256] weight partials; bias_part (may be null): [grid][32]
@@ -445,6 +602,15 @@ int launch_tc_conv2_wgrad_sw(const float* in, const float* dz, float* part, int 
     R2D2_CUDA_OK(cudaFuncSetAttribute(tc_conv2_wgrad_sw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, W2_SMEM));
     R2D2_LAUNCH("tc_conv2_wgrad", st,
                 tc_conv2_wgrad_sw_kernel<<<grid, W2_THREADS, W2_SMEM, st>>>(in, dz, part, R, bias_part));
+    return R2D2_OK;
+}
+
+// third layer: `in` = layer-2 activations [R][32][9][9] fp32, part: [grid][32][288]
+int launch_tc_conv3_wgrad_sw(const float* in, const float* dz, float* part, int R, int grid, cudaStream_t st,
+                             float* bias_part) {
+    R2D2_CUDA_OK(cudaFuncSetAttribute(tc_conv3_wgrad_sw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, W3_SMEM));
+    R2D2_LAUNCH("tc_conv3_wgrad", st,
+                tc_conv3_wgrad_sw_kernel<<<grid, W3_THREADS, W3_SMEM, st>>>(in, dz, part, R, bias_part));
     return R2D2_OK;
 }
 
