@@ -312,31 +312,34 @@ def time_device(L, steps, barrier):
     return ev0.elapsed_time(ev1)
 
 
-def time_e2e(L, steps, dump, barrier):
+def time_e2e(L, steps, dump, barrier, warmup=5):
     """The public API with host buffers, wall clock: every step uploads `dump` (fresh experience)
     from pinned host memory through ReplayMemory.extend, runs Learner.train() (uniforms H2D
     inside) and copies the loss to pinned host memory; the host READS loss k-1 while step k runs,
-    the way a training loop logs.  Returns (seconds, last loss)."""
+    the way a training loop logs.  `warmup` untimed iterations of the same loop body come first
+    (pinned staging allocation, the copy stream's first use).  Returns (seconds, last loss)."""
     import torch
-    for _ in range(2):
-        float(L.train().item())
-        L.replay_memory.extend(dump, overlap=True)
-    barrier()
     loss_pin = [torch.empty(1).pin_memory() for _ in range(2)]
     loss_ev = [torch.cuda.Event() for _ in range(2)]
     losses = []
+
+    def loop(n):
+        for i in range(n):
+            loss = L.train()                                  # lands the dump staged during step i-1
+            L.replay_memory.extend(dump, overlap=True)        # H2D of the next dump overlaps step i
+            loss_pin[i & 1].copy_(loss, non_blocking=True)
+            loss_ev[i & 1].record()
+            if i > 0:
+                loss_ev[(i - 1) & 1].synchronize()
+                losses.append(float(loss_pin[(i - 1) & 1]))
+        loss_ev[(n - 1) & 1].synchronize()
+        losses.append(float(loss_pin[(n - 1) & 1]))
+        torch.cuda.synchronize()
+
+    loop(max(2, warmup))
+    barrier()
     t0 = time.perf_counter()
-    for i in range(steps):
-        loss = L.train()                                  # lands the dump staged during step i-1
-        L.replay_memory.extend(dump, overlap=True)        # H2D of the next dump overlaps step i
-        loss_pin[i & 1].copy_(loss, non_blocking=True)
-        loss_ev[i & 1].record()
-        if i > 0:
-            loss_ev[(i - 1) & 1].synchronize()
-            losses.append(float(loss_pin[(i - 1) & 1]))
-    loss_ev[(steps - 1) & 1].synchronize()
-    losses.append(float(loss_pin[(steps - 1) & 1]))
-    torch.cuda.synchronize()
+    loop(steps)
     return time.perf_counter() - t0, losses[-1]
 
 
@@ -563,7 +566,7 @@ def run_ours(args):
     rows = args.ingest_rows
     dump = make_host_dump(rows, H)
     h2d = sum(v.numel() * v.element_size() for v in dump.values()) + B * 8
-    e2e_s, loss_host = time_e2e(L, args.steps, dump, barrier)
+    e2e_s, loss_host = time_e2e(L, args.steps, dump, barrier, args.warmup)
     t = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
