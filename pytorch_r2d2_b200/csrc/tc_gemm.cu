@@ -324,6 +324,155 @@ tc_gemm_x3_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
     if (warp == 1) tmem_dealloc(tmem_base, 512);
 }
 
+// ---------------------------------------------------------------- bf16x3 GEMM, CTA pairs
+// The wide bf16x3 kernel moves (128 + bn) x 64 x 2 x 2 bytes from L2 into shared memory per k-block
+// and CTA, ~65 GB/s per SM at the measured speed: L2 bandwidth, not the tensor pipe, bounds it.
+// Here two CTAs of a cluster work on the two M-tiles 2j, 2j+1 of the SAME n-tile: each loads its
+// own A tiles and HALF of the B tiles, multicast into both CTAs' shared memory -- a third less L2
+// traffic per CTA.  A stage may be refilled once BOTH CTAs' MMAs have read it: the "stage free"
+// arrive (tcgen05.commit) is multicast to both CTAs' barriers.  Everything else as above
+// (persistent, two TMEM accumulators).  The tensor maps cover this GPU's memory only.
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(192, 1)
+tc_gemm_x3_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b_half,
+                       const __grid_constant__ CUtensorMap tma_a_lo,
+                       const __grid_constant__ CUtensorMap tma_b_lo_half, const TcEpilogue ep, const int M,
+                       const int N, const int K, const int bn) {
+    constexpr int BN = 256, STAGES = 2;
+    constexpr uint32_t A_BYTES = TC_BM * TC_BK * 2, B_BYTES = BN * TC_BK * 2;
+    constexpr uint32_t STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], acc_full[2], acc_empty[2];
+    __shared__ uint32_t tmem_slot;
+    const uint32_t raw = smem_u32(smem_raw);
+    uint8_t* tiles = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int rank = (int)cluster_ctarank();
+    const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+    const int mt2 = ((M + TC_BM - 1) / TC_BM) >> 1, ntiles = mt2 * ((N + bn - 1) / bn);   // tiles of a pair
+    const int num_kb = (K + TC_BK - 1) / TC_BK;
+    const uint32_t half_bytes = (uint32_t)(bn >> 1) * TC_BK * 2;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tma_a);
+        tma_prefetch_desc(&tma_b_half);
+        tma_prefetch_desc(&tma_a_lo);
+        tma_prefetch_desc(&tma_b_lo_half);
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 2);                                 // both CTAs' MMAs have read the stage
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&acc_full[b], 1);
+            mbar_init(&acc_empty[b], 128);
+        }
+        mbar_fence_init();
+    }
+    if (warp == 1) tmem_alloc(&tmem_slot, 512);
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();                                                  // the peer's barriers exist
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int t = pair; t < ntiles; t += npairs) {
+                const int m0 = (2 * (t % mt2) + rank) * TC_BM, n0 = (t / mt2) * bn;
+                for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                    const int s = it % STAGES;
+                    mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
+                    mbar_expect_tx(&full_bar[s], 2 * A_BYTES + 4 * half_bytes);
+                    uint8_t* dst = tiles + (size_t)s * STAGE_BYTES;
+                    const int kk = kb * TC_BK;
+                    tma_load_2d(dst, &tma_a, kk, m0, &full_bar[s]);
+                    tma_load_2d(dst + A_BYTES, &tma_a_lo, kk, m0, &full_bar[s]);
+                    // my half of the B rows, into both CTAs
+                    tma_load_2d_mc(dst + 2 * A_BYTES + rank * half_bytes, &tma_b_half, kk, n0 + rank * (bn >> 1),
+                                   &full_bar[s], 3);
+                    tma_load_2d_mc(dst + 2 * A_BYTES + B_BYTES + rank * half_bytes, &tma_b_lo_half, kk,
+                                   n0 + rank * (bn >> 1), &full_bar[s], 3);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = umma_idesc_bf16(TC_BM, bn);
+            uint32_t it = 0, ti = 0;
+            for (int t = pair; t < ntiles; t += npairs, ++ti) {
+                const uint32_t buf = ti & 1, d = tmem_base + buf * 256;
+                mbar_wait(&acc_empty[buf], ((ti >> 1) & 1) ^ 1);
+                tc_fence_after();
+                for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                    const int s = it % STAGES;
+                    mbar_wait(&full_bar[s], (it / STAGES) & 1);
+                    tc_fence_after();
+                    const uint32_t a_hi = smem_u32(tiles + (size_t)s * STAGE_BYTES), a_lo = a_hi + A_BYTES;
+                    const uint32_t b_hi = a_hi + 2 * A_BYTES, b_lo = b_hi + B_BYTES;
+#pragma unroll
+                    for (int k = 0; k < TC_BK / 16; ++k) {
+                        const uint32_t acc = (kb | k) != 0;
+                        umma_f16(d, umma_desc_k_sw128(a_hi + k * 32), umma_desc_k_sw128(b_hi + k * 32), idesc, acc);
+                        umma_f16(d, umma_desc_k_sw128(a_hi + k * 32), umma_desc_k_sw128(b_lo + k * 32), idesc, 1);
+                        umma_f16(d, umma_desc_k_sw128(a_lo + k * 32), umma_desc_k_sw128(b_hi + k * 32), idesc, 1);
+                    }
+                    umma_commit_mc(&empty_bar[s], 3);
+                }
+                umma_commit(&acc_full[buf]);
+            }
+        }
+    } else {
+        const int q = warp & 3;
+        uint32_t ti = 0;
+        for (int t = pair; t < ntiles; t += npairs, ++ti) {
+            const uint32_t buf = ti & 1, d = tmem_base + buf * 256;
+            const int m0 = (2 * (t % mt2) + rank) * TC_BM, n0 = (t / mt2) * bn;
+            mbar_wait(&acc_full[buf], (ti >> 1) & 1);
+            tc_fence_after();
+            const int m = m0 + q * 32 + lane;
+#pragma unroll 1
+            for (int c = 0; c < bn; c += 32) {
+                uint32_t r[32];
+                tmem_ld32(d + ((uint32_t)(q * 32) << 16) + (uint32_t)c, r);
+                tmem_ld_wait();
+                if (c + 32 >= bn) {
+                    tc_fence_before();
+                    mbar_arrive(&acc_empty[buf]);
+                }
+                if (m < M) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) {
+                        const int n = n0 + c + j;
+                        if (n >= N || c + j >= bn) break;
+                        float v[4];
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            float x = __uint_as_float(r[j + e]);
+                            if (ep.bias1) x += __ldg(ep.bias1 + (ep.bias_row ? m : n + e));
+                            if (ep.bias2) x += __ldg(ep.bias2 + (ep.bias_row ? m : n + e));
+                            if (ep.relu) x = fmaxf(x, 0.f);
+                            v[e] = x;
+                        }
+                        if (ep.c32)
+                            *reinterpret_cast<float4*>(ep.c32 + (long long)m * ep.ldc + n) =
+                                make_float4(v[0], v[1], v[2], v[3]);
+                        if (ep.c16) {
+                            uint2 pk;
+                            pk.x = pack2_bf16(v[0], v[1]);
+                            pk.y = pack2_bf16(v[2], v[3]);
+                            *reinterpret_cast<uint2*>(ep.c16 + (long long)m * ep.ldc + n) = pk;
+                        }
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();                                                  // nobody leaves while the peer still writes here
+    if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
 // ---------------------------------------------------------------- C = A^T . B, no transposed copies
 //   C[P, Q] = sum_k A[k, P] * B[k, Q]        A [Kc, P], B [Kc, Q] row-major bf16; C f32
 // The weight gradients dW = dY^T . X contract over the ROWS of two row-major matrices.  Both
@@ -581,7 +730,24 @@ static int tc_linear_impl(const void* x_hi, const void* x_lo, const void* w_hi, 
         // must start beside this one (a CTA keeps its SM until all its tiles are done)
         const int cta_cap = max_ctas > 0 && max_ctas < sm_count() ? max_ctas : sm_count();
         const int grid = tiles_ll < cta_cap ? (int)tiles_ll : cta_cap;
-        if (wide) {
+        static const bool no_pairs = [] {                // R2D2_GEMM_PAIRS=0: the single-CTA kernel (A/B runs)
+            const char* e = getenv("R2D2_GEMM_PAIRS");
+            return e && e[0] == '0';
+        }();
+        if (wide && !no_pairs && ((M + TC_BM - 1) / TC_BM) % 2 == 0 && M % TC_BM == 0) {
+            CUtensorMap tbh, tbh_lo;
+            rc = make_tmap(&tbh, w_hi, N, K, BNx / 2);
+            if (rc) return rc;
+            rc = make_tmap(&tbh_lo, w_lo, N, K, BNx / 2);
+            if (rc) return rc;
+            const int smem = 2 * (2 * TC_BM * TC_BK * 2 + 2 * 256 * TC_BK * 2) + 1024;
+            R2D2_CUDA_OK(cudaFuncSetAttribute(tc_gemm_x3_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            const long long pair_tiles = tiles_ll / 2;
+            int pairs = cta_cap / 2;
+            if (pairs > pair_tiles) pairs = (int)pair_tiles;
+            R2D2_LAUNCH("tc_gemm_kernel_x3", as_stream(stream),
+                        tc_gemm_x3_pair_kernel<<<2 * pairs, 192, smem, as_stream(stream)>>>(ta, tbh, ta_lo, tbh_lo, ep, M, N, K, BNx));
+        } else if (wide) {
             const int smem = 2 * (2 * TC_BM * TC_BK * 2 + 2 * 256 * TC_BK * 2) + 1024;
             R2D2_CUDA_OK(cudaFuncSetAttribute(tc_gemm_x3_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
             R2D2_LAUNCH("tc_gemm_kernel_x3", as_stream(stream),
