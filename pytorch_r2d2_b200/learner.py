@@ -72,11 +72,13 @@ class FusedCenteredRMSprop:
             raise RuntimeError("attach_peer_exchange must be called once, before the first optimiser step")
         self.net.rebase(peer.param)
         self.grad = peer.grad
-        # two buckets: [0] the conv torso (its gradients are the last to complete), [1] LSTM + head
-        # (complete half-way through the backward pass: exchanged beside the conv backward)
+        # three buckets in the order the backward pass completes them: [2] the dueling heads (done
+        # before the BPTT starts: exchanged beside it), [1] the LSTM (exchanged beside the conv
+        # backward), [0] the conv torso (its gradients are the last to complete)
         split = self.net.layout.offset("lstm.weight_ih")
-        assert split % 4 == 0
-        self.buckets = [(0, split), (split, peer.n - split)]
+        head = self.net.layout.offset("val.0.weight")
+        assert split % 4 == 0 and head % 4 == 0 and split < head < peer.n
+        self.buckets = [(0, split), (split, head - split), (head, peer.n - head)]
         z = lambda n: torch.zeros(parallel.shard_elems(n, peer.world), dtype=torch.float32, device=peer.device)  # noqa: E731
         self.square_avg = [z(n) for _, n in self.buckets]
         self.grad_avg = [z(n) for _, n in self.buckets]
@@ -602,6 +604,14 @@ class Learner:
                 engine.colsum(ws["dhid"], g.head_b1)
 
             beside(head_wgrad)
+            if overlap_bwd and self.optim.peer is not None:
+                # the heads' gradients are complete: exchanged beside the BPTT (most SMs idle)
+                xs = ws["xchg_stream"]
+                e = next(ev)
+                e.record(side)
+                xs.wait_event(e)
+                with torch.cuda.stream(xs):
+                    self.optim.step_bucket(2)
             engine.tc_linear(ws["dhid16"], ws["hw1T16"], None, None, y32=ws["dhs"])
 
             def lstm_wgrad_operands():   # forward-only operand: cast while the BPTT runs
@@ -618,13 +628,12 @@ class Learner:
 
             beside(lstm_wgrad, aux)       # the longest consumer chain gets a stream of its own
             if overlap_bwd and self.optim.peer is not None:
-                # LSTM + head gradients are complete once head_wgrad (side) and lstm_wgrad (aux) are:
-                # their exchange + update crosses NVLink beside the conv backward
+                # the LSTM gradients are complete once lstm_wgrad (aux) is: their exchange + update
+                # crosses NVLink beside the conv backward
                 xs = ws["xchg_stream"]
-                for st_ in (side, aux):
-                    e = next(ev)
-                    e.record(st_)
-                    xs.wait_event(e)
+                e = next(ev)
+                e.record(aux)
+                xs.wait_event(e)
                 with torch.cuda.stream(xs):
                     self.optim.step_bucket(1)
             engine.tc_linear(ws["dg16"], ws["w_ihT16"], None, None, y32=ws["dfeat"])
