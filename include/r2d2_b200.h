@@ -323,6 +323,9 @@ int r2d2_tc_linear_x3(const void* x_hi, const void* x_lo, const void* w_hi, cons
  * activations and gradients as they lie in memory -- both operands are read MN-major by the
  * tensor cores, no transposed copies. */
 int r2d2_tc_linear_tn(const void* a_bf16, const void* b_bf16, float* y_f32, int Kc, int P, int Q, void* stream);
+/* y[M, N] = a . b for row-major bf16 a [M, K] and b [K, N] (N, K multiples of 8): the data gradients
+ * dX = dY . W with the weight matrix as stored ([out, in]) -- b is read MN-major, no W^T copy. */
+int r2d2_tc_linear_nn(const void* a_bf16, const void* b_bf16, float* y_f32, int M, int N, int K, void* stream);
 /* Same, on at most max_ctas SMs (0 = all).  The kernel is persistent -- a CTA keeps its SM until all
  * of its tiles are done -- so a caller that wants another kernel to START beside it (the learner:
  * the online network's recurrence beside the target network's input projection) leaves SMs free. */

@@ -81,6 +81,7 @@ PROTOTYPES = {
     "r2d2_dp_shard_elems": (_L, [_L, _I]),
     "r2d2_dp_reduce_rmsprop": (_I, [_I, _I, _P, _P, _P, _P, _P, _L, _I, _L, _D, _D, _D, _D, _P]),
     "r2d2_tc_linear_x3": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
+    "r2d2_tc_linear_nn": (_I, [_P, _P, _P, _I, _I, _I, _P]),
     "r2d2_tc_linear_tn": (_I, [_P, _P, _P, _I, _I, _I, _P]),
     "r2d2_tc_linear_x3_ctas": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "r2d2_split_bf16": (_I, [_P, _P, _P, _L, _P]),

@@ -569,6 +569,99 @@ tc_gemm_tn_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
     if (warp == 1) tmem_dealloc(tmem_base, BN);
 }
 
+// ---------------------------------------------------------------- C = A . B, B as stored ([K, N] row-major)
+//   C[M, N] = sum_k A[m, k] * B[k, n]        A [M, K], B [K, N] row-major bf16; C f32
+// The data gradients dX = dY . W multiply by the weight matrix AS STORED ([out, in] = [K, N]):
+// A is K-major as in the plain kernel, B is read MN-major like the operands of tc_gemm_tn_kernel,
+// so the bf16 "hi" copy of W that the forward pass already made serves and no W^T is built.
+template <int BN>
+__global__ void __launch_bounds__(192, 1)
+tc_gemm_nn_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                  float* __restrict__ c, const int M, const int N, const int K) {
+    constexpr uint32_t G_BYTES = 64 * 128;
+    constexpr uint32_t A_BYTES = TC_BM * TC_BK * 2, B_BYTES = (BN / 64) * G_BYTES;
+    constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t full_bar[TC_STAGES], empty_bar[TC_STAGES], acc_bar;
+    __shared__ uint32_t tmem_slot;
+    const uint32_t raw = smem_u32(smem_raw);
+    uint8_t* tiles = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = blockIdx.x * TC_BM, n0 = blockIdx.y * BN;
+    const int num_kb = (K + TC_BK - 1) / TC_BK;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tma_a);
+        tma_prefetch_desc(&tma_b);
+        for (int s = 0; s < TC_STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(&acc_bar, 1);
+        mbar_fence_init();
+    }
+    if (warp == 1) tmem_alloc(&tmem_slot, BN);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % TC_STAGES;
+                mbar_wait(&empty_bar[s], ((kb / TC_STAGES) & 1) ^ 1);
+                mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+                uint8_t* dst = tiles + (size_t)s * STAGE_BYTES;
+                tma_load_2d(dst, &tma_a, kb * TC_BK, m0, &full_bar[s]);
+#pragma unroll
+                for (int g = 0; g < BN / 64; ++g)
+                    tma_load_2d(dst + A_BYTES + g * G_BYTES, &tma_b, n0 + 64 * g, kb * 64, &full_bar[s]);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(TC_BM, BN) | (1u << 16);                // B MN-major
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % TC_STAGES;
+                mbar_wait(&full_bar[s], (kb / TC_STAGES) & 1);
+                tc_fence_after();
+                const uint32_t a_addr = smem_u32(tiles + (size_t)s * STAGE_BYTES), b_addr = a_addr + A_BYTES;
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    umma_f16(tmem_base, umma_desc_k_sw128(a_addr + k * 32), umma_desc_mn_sw128(b_addr + k * 2048, G_BYTES),
+                             idesc, (kb | k) != 0);
+                umma_commit(&empty_bar[s]);
+            }
+            umma_commit(&acc_bar);
+        }
+    } else {
+        mbar_wait(&acc_bar, 0);
+        tc_fence_after();
+        const int q = warp & 3;
+        const int m = m0 + q * 32 + lane;
+#pragma unroll 1
+        for (int cc = 0; cc < BN; cc += 32) {
+            uint32_t r[32];
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)cc, r);
+            tmem_ld_wait();
+            if (m < M) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) {
+                    const int n = n0 + cc + j;
+                    if (n >= N) break;
+                    *reinterpret_cast<float4*>(c + (long long)m * N + n) =
+                        make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
+                                    __uint_as_float(r[j + 3]));
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, BN);
+}
+
 // ---------------------------------------------------------------- host: tensor maps
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
@@ -820,6 +913,28 @@ int r2d2_tc_linear_tn(const void* a_bf16, const void* b_bf16, float* y_f32, int 
     dim3 grid((P + TC_BM - 1) / TC_BM, (Q + BN - 1) / BN);
     R2D2_LAUNCH("tc_gemm_tn_kernel", as_stream(stream),
                 tc_gemm_tn_kernel<BN><<<grid, 192, smem, as_stream(stream)>>>(ta, tb, y_f32, P, Q, Kc));
+    return R2D2_OK;
+}
+
+int r2d2_tc_linear_nn(const void* a_bf16, const void* b_bf16, float* y_f32, int M, int N, int K, void* stream) {
+    R2D2_REQUIRE(a_bf16 && b_bf16 && y_f32 && M > 0 && N > 0 && K > 0, "tc_linear_nn: bad args");
+    R2D2_REQUIRE(N % 8 == 0 && K % 8 == 0 && ((uintptr_t)y_f32 % 16) == 0,
+                 "tc_linear_nn: N and K must be multiples of 8, y 16-byte aligned (N=%d K=%d)", N, K);
+    CUtensorMap ta, tb;
+    int rc = make_tmap(&ta, a_bf16, M, K, TC_BM);
+    if (rc) return rc;
+    rc = make_tmap_mn(&tb, b_bf16, K, N);
+    if (rc) return rc;
+    constexpr int BN = 128;
+    const int smem = TC_STAGES * (TC_BM * TC_BK * 2 + (BN / 64) * 64 * 128) + 1024;
+    static bool attr_set = false;
+    if (!attr_set) {
+        R2D2_CUDA_OK(cudaFuncSetAttribute(tc_gemm_nn_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr_set = true;
+    }
+    dim3 grid((M + TC_BM - 1) / TC_BM, (N + BN - 1) / BN);
+    R2D2_LAUNCH("tc_gemm_nn_kernel", as_stream(stream),
+                tc_gemm_nn_kernel<BN><<<grid, 192, smem, as_stream(stream)>>>(ta, tb, y_f32, M, N, K));
     return R2D2_OK;
 }
 

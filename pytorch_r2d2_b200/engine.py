@@ -208,6 +208,14 @@ def tc_linear_masked(x16, w16, mask, y32):
     _lib.call("r2d2_tc_linear_masked", P(x16, "bf16"), P(w16, "bf16"), P(mask, "f32"), P(y32, "f32"), M, N, K, S())
 
 
+def tc_linear_nn(a16, b16, y32):
+    """y [M, N] = a . b for row-major bf16 a [M, K], b [K, N] (data gradients; the weight as stored)."""
+    M, K = a16.shape
+    N = b16.shape[1]
+    assert b16.shape[0] == K and y32.numel() == M * N
+    _lib.call("r2d2_tc_linear_nn", P(a16, "bf16"), P(b16, "bf16"), P(y32, "f32"), M, N, K, S())
+
+
 def tc_linear_tn(a16, b16, y32):
     """y [P, Q] = a^T . b for row-major bf16 a [K, P], b [K, Q] (weight gradients; no transposes)."""
     Kc, Pn = a16.shape

@@ -315,8 +315,8 @@ class Learner:
             h = lambda *shape: torch.empty(shape, dtype=torch.bfloat16, device=dev)  # noqa: E731
             # forward operands as bf16 (hi, lo) pairs, stacked on a leading axis of 2
             ws["feat16_on"], ws["feat16_tg"] = h(2, S * B, FEAT), h(2, T * B, FEAT)
-            ws["w_ih16"], ws["w_ih16_t"], ws["w_ihT16"] = h(2, 4 * H, FEAT), h(2, 4 * H, FEAT), h(FEAT, 4 * H)
-            ws["hw1_16"], ws["hw1_16_t"], ws["hw1T16"] = h(2, 2 * H, H), h(2, 2 * H, H), h(H, 2 * H)
+            ws["w_ih16"], ws["w_ih16_t"] = h(2, 4 * H, FEAT), h(2, 4 * H, FEAT)
+            ws["hw1_16"], ws["hw1_16_t"] = h(2, 2 * H, H), h(2, 2 * H, H)
             ws["hs16"], ws["hs16_t"], ws["hs16_l"] = h(2, M, H), h(2, M, H), h(2, M, H)
             # transposed input projections [4H, frames*B] for the persistent LSTM kernel
             ws["xpT_on"], ws["xpT_tg"] = f(4 * H, S * B), f(4 * H, T * B)
@@ -420,16 +420,14 @@ class Learner:
         # frames in place from the ring, so the 154 MB slab copy never happens
         w, wt = self.net._weights(), self.target_net._weights()
         if bf16:
-            # weight-only operand preparation (bf16 hi/lo splits for the forward GEMMs, transposed
-            # bf16 copies for the backward data gradients): nothing here depends on the batch, so it
+            # weight-only operand preparation (bf16 hi/lo splits for the forward GEMMs; the "hi" parts
+            # also serve the backward data gradients): nothing here depends on the batch, so it
             # runs on the third stream from the very start of the step
             def weight_prep():
                 engine.split_bf16(w.w_ih, ws["w_ih16"][0], ws["w_ih16"][1])
                 engine.split_bf16(w.head_w1, ws["hw1_16"][0], ws["hw1_16"][1])
                 engine.split_bf16(wt.w_ih, ws["w_ih16_t"][0], ws["w_ih16_t"][1])
                 engine.split_bf16(wt.head_w1, ws["hw1_16_t"][0], ws["hw1_16_t"][1])
-                engine.transpose_cast_bf16(w.head_w1, ws["hw1T16"])
-                engine.transpose_cast_bf16(w.w_ih, ws["w_ihT16"])
 
             if self.overlap_streams:
                 ws["ev_aux"][2].record(torch.cuda.current_stream())
@@ -612,7 +610,8 @@ class Learner:
                 xs.wait_event(e)
                 with torch.cuda.stream(xs):
                     self.optim.step_bucket(2)
-            engine.tc_linear(ws["dhid16"], ws["hw1T16"], None, None, y32=ws["dhs"])
+            # data gradients multiply by the weights as stored: the bf16 "hi" copies of the forward pass
+            engine.tc_linear_nn(ws["dhid16"], ws["hw1_16"][0], ws["dhs"])
 
             def lstm_wgrad_operands():   # forward-only operand: cast while the BPTT runs
                 engine.cast_bf16(hprev, ws["hprev16"])
@@ -636,7 +635,7 @@ class Learner:
                 xs.wait_event(e)
                 with torch.cuda.stream(xs):
                     self.optim.step_bucket(1)
-            engine.tc_linear(ws["dg16"], ws["w_ihT16"], None, None, y32=ws["dfeat"])
+            engine.tc_linear_nn(ws["dg16"], ws["w_ih16"][0], ws["dfeat"])
             # conv torso: scratch = [dz2 | dz1 | ...]; dz3 = dfeat masked in place
             sc32 = scratch.view(torch.float32)
             dz2, dz1 = sc32[:M * 2592], sc32[M * 2592: M * (2592 + 12800)]

@@ -74,6 +74,19 @@ def test_tc_linear_tn_vs_fp64(cuda_device, Kc, P, Q):
     assert rel_err(y, want) < 1e-5, rel_err(y, want)     # fp32 accumulation over Kc terms
 
 
+@pytest.mark.parametrize("M,N,K", [(2560, 1568, 2048), (2560, 512, 1024), (100, 72, 40), (128, 128, 64), (130, 264, 8)])
+def test_tc_linear_nn_vs_fp64(cuda_device, M, N, K):
+    """y = a . b with b [K, N] as stored (read MN-major) == the fp64 product of the same bf16 values."""
+    from pytorch_r2d2_b200 import engine
+    g = torch.Generator().manual_seed(M + N + K)
+    a = torch.randn(M, K, generator=g).bfloat16().cuda()
+    b = torch.randn(K, N, generator=g).bfloat16().cuda()
+    y = torch.full((M, N), float("nan"), device="cuda")
+    engine.tc_linear_nn(a, b, y)
+    want = a.double() @ b.double()
+    assert rel_err(y, want) < 1e-5, rel_err(y, want)
+
+
 def test_cast_and_transpose(cuda_device):
     from pytorch_r2d2_b200 import engine
     x = torch.randn(1000, 1568, device="cuda")
