@@ -42,6 +42,12 @@ class FusedCenteredRMSprop:
         self.grad_avg = torch.zeros_like(flat)
         self.grad_scale = 1.0
         self.peer = None
+        self._done = set()
+        # the same three ranges the data-parallel exchange uses (see attach_peer_exchange): a single
+        # replica updates the heads and the LSTM as soon as their gradients are complete, too
+        lay, n = net.layout, flat.numel()
+        split, head = lay.offset("lstm.weight_ih"), lay.offset("val.0.weight")
+        self.buckets = [(0, split), (split, head - split), (head, n - head)]
 
     def zero_grad(self):
         self.grad.zero_()
@@ -55,14 +61,26 @@ class FusedCenteredRMSprop:
                     self.step_bucket(k)
             self._done.clear()
             return
+        if self._done:                       # some ranges were updated during the backward pass
+            for k in range(len(self.buckets)):
+                if k not in self._done:
+                    self.step_bucket(k)
+            self._done.clear()
+            return
         engine.rmsprop_centered(self.net.flat_parameters(), self.grad, self.square_avg,
                                 self.grad_avg, self.lr, self.alpha, self.eps, self.grad_scale)
 
     def step_bucket(self, k):
-        """Exchange + update bucket k now, on the current stream (its gradients must be complete)."""
+        """Exchange + update bucket k now, on the current stream (its gradients must be complete).
+        Single replica: the optimiser kernel on that range of the flat vectors."""
         off, n = self.buckets[k]
-        self.peer.reduce_rmsprop(self.square_avg[k], self.grad_avg[k], self.lr, self.alpha, self.eps,
-                                 offset=off, n=n, bucket=k)
+        if self.peer is None:
+            sl = slice(off, off + n)
+            engine.rmsprop_centered(self.net.flat_parameters()[sl], self.grad[sl], self.square_avg[sl],
+                                    self.grad_avg[sl], self.lr, self.alpha, self.eps, self.grad_scale)
+        else:
+            self.peer.reduce_rmsprop(self.square_avg[k], self.grad_avg[k], self.lr, self.alpha, self.eps,
+                                     offset=off, n=n, bucket=k)
         self._done.add(k)
 
     def attach_peer_exchange(self, peer):
@@ -602,8 +620,11 @@ class Learner:
                 engine.colsum(ws["dhid"], g.head_b1)
 
             beside(head_wgrad)
-            if overlap_bwd and self.optim.peer is not None:
-                # the heads' gradients are complete: exchanged beside the BPTT (most SMs idle)
+            # early optimiser ranges: with the peer exchange, or as a single replica (an NCCL
+            # all-reduce of the whole gradient, the fallback, has to wait for the end of the step)
+            early = overlap_bwd and (self.optim.peer is not None or parallel.active_world(self.process_group) == 1)
+            if early:
+                # the heads' gradients are complete: exchanged / applied beside the BPTT (most SMs idle)
                 xs = ws["xchg_stream"]
                 e = next(ev)
                 e.record(side)
@@ -626,9 +647,9 @@ class Learner:
                 engine.colsum(ws["dgates"], g.b_hh, g.b_ih)
 
             beside(lstm_wgrad, aux)       # the longest consumer chain gets a stream of its own
-            if overlap_bwd and self.optim.peer is not None:
+            if early:
                 # the LSTM gradients are complete once lstm_wgrad (aux) is: their exchange + update
-                # crosses NVLink beside the conv backward
+                # crosses NVLink (or, single replica, just runs) beside the conv backward
                 xs = ws["xchg_stream"]
                 e = next(ev)
                 e.record(aux)
@@ -661,7 +682,7 @@ class Learner:
                       P(ws["relu1_bits"][BI * B:], "i32"), P(dz1, "f32"), M, st())
             engine.conv1_wgrad_ring(batch["ring"], batch["seq_index"], BI, L, dz1, g.w1, ws["wpart"][0], db1=g.b1)
             if overlap_bwd:
-                for st_ in (side, aux, ws["aux2_stream"]) + ((ws["xchg_stream"],) if self.optim.peer is not None else ()):
+                for st_ in (side, aux, ws["aux2_stream"]) + ((ws["xchg_stream"],) if early else ()):
                     e = next(ev)
                     e.record(st_)
                     main.wait_event(e)
