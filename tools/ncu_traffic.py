@@ -3,6 +3,12 @@
 import csv, json, subprocess, sys, collections
 NAMES = [
     ("tc_lstm_fwd_kernel", "tc_lstm_fwd_kernel"), ("tc_lstm_bwd_kernel", "tc_lstm_bwd_kernel"),
+    ("tc_conv1_sw_dual_kernel", "tc_conv1_fwd_dual"), ("tc_conv1_wgrad_sw_kernel", "tc_conv1_wgrad"),
+    ("tc_conv2_wgrad_sw_kernel", "tc_conv2_wgrad"), ("tc_conv3_wgrad_sw_kernel", "tc_conv3_wgrad"),
+    ("tc_conv2_dgrad_sw_kernel", "tc_conv2_dgrad"), ("tc_conv3_dgrad_sw_kernel", "tc_conv3_dgrad"),
+    ("tc_gemm_x3_pair_kernel", "tc_gemm_kernel_x3"), ("tc_gemm_x3_kernel", "tc_gemm_kernel_x3"),
+    ("tc_gemm_tn_kernel", "tc_gemm_tn_kernel"), ("tc_gemm_nn_kernel", "tc_gemm_nn_kernel"),
+    ("rmsprop_kernel", "rmsprop_kernel"),
     ("tc_conv_fwd_kernel<unsigned char", "tc_conv1_fwd"), ("tc_conv_fwd_kernel<float, 32, 4", "tc_conv2_fwd"),
     ("tc_conv_fwd_kernel<float, 32, 3", "tc_conv3_fwd"),
     ("tc_conv_sw_fwd_kernel<2>", "tc_conv2_fwd"), ("tc_conv_sw_fwd_kernel<3>", "tc_conv3_fwd"),
