@@ -131,6 +131,9 @@ def work_model(B, BI, L, n, H, nparams):
         "tc_conv2_fwd": ("flop", c2 * fr_fwd),
         "tc_conv3_fwd": ("flop", c3 * fr_fwd),
         "tc_gemm_kernel_x3": ("flop", lin_fwd), "tc_gemm_kernel": ("flop", lin_bwd),
+        # weight gradients dW = dY^T.X (heads, W_hh, W_ih) and data gradients dX = dY.W (heads, W_ih)
+        "tc_gemm_tn_kernel": ("flop", M * 2 * (2 * H * H) + M * 2 * 4 * H * H + M * proj),
+        "tc_gemm_nn_kernel": ("flop", M * 2 * (2 * H * H) + M * proj),
         "tc_lstm_fwd_kernel": ("flop", lstm * steps_fwd), "tc_lstm_bwd_kernel": ("flop", lstm * (L - 1)),
         "tc_conv1_wgrad": ("flop", c1 * M), "tc_conv2_wgrad": ("flop", c2 * M), "tc_conv3_wgrad": ("flop", c3 * M),
         "tc_conv2_dgrad": ("flop", c2 * M), "tc_conv3_dgrad": ("flop", c3 * M),
