@@ -60,6 +60,31 @@ def test_tc_linear_x3_is_fp32_accurate(cuda_device, M, N, K):
     assert rel_err(y1, want) > err          # the compensation is doing something
 
 
+def test_tc_linear_x3_wide_forms_agree(cuda_device):
+    """The input-projection shape (wide tiles): the CTA-pair kernel with multicast B tiles, the
+    same with a CTA cap (max_ctas: the kernel is persistent, fewer CTAs walk more tiles each) and an
+    odd M-tile count (single-CTA kernel) give the fp32-accurate product; pair and capped runs are
+    bit-identical (same per-tile arithmetic)."""
+    from pytorch_r2d2_b200 import engine
+    g = torch.Generator().manual_seed(77)
+    for M, N, K in ((2048, 5440, 1568), (1920, 5000, 200)):      # 16 and 15 M-tiles
+        x = torch.randn(M, K, generator=g).cuda()
+        w = (torch.randn(N, K, generator=g) * 0.1).cuda()
+        b = torch.randn(M, generator=g).cuda()
+        xs = torch.empty(2, M, K, device="cuda", dtype=torch.bfloat16)
+        ws = torch.empty(2, N, K, device="cuda", dtype=torch.bfloat16)
+        engine.split_bf16(x, xs[0], xs[1])
+        engine.split_bf16(w, ws[0], ws[1])
+        want = x.double() @ w.double().T + b.double()[:, None]
+        ys = []
+        for cap in (0, 84, 2):
+            y = torch.full((M, N), float("nan"), device="cuda")
+            engine.tc_linear_x3(xs[0], xs[1], ws[0], ws[1], b, None, y32=y, bias_row=True, max_ctas=cap)
+            assert rel_err(y, want) < 1e-4, (M, cap, rel_err(y, want))
+            ys.append(y)
+        assert torch.equal(ys[0], ys[1]) and torch.equal(ys[0], ys[2])
+
+
 @pytest.mark.parametrize("Kc,P,Q", [(2560, 2048, 512), (2560, 2048, 1568), (200, 72, 40), (64, 128, 128), (130, 8, 264)])
 def test_tc_linear_tn_vs_fp64(cuda_device, Kc, P, Q):
     """y = a^T . b with both operands read MN-major (no transposed copies) == the fp64 product of
@@ -177,6 +202,35 @@ def test_tc_conv1_dual_matches_single(cuda_device):
         # the fused (hi, lo) image of feat == r2d2_split_bf16(feat)
         hi = fc.bfloat16()
         assert torch.equal(f16[0], hi) and torch.equal(f16[1], (fc - hi.float()).bfloat16())
+
+
+@pytest.mark.parametrize("B,nt", [(1, 1), (3, 1), (2, 5)])
+def test_tc_conv_backward_few_frames(cuda_device, B, nt):
+    """Shifted-window conv gradients with fewer frames than CTAs (persistent CTAs without work
+    write zero partials) and frame counts that are not a multiple of anything: == the fp32 kernels
+    to the bf16 class."""
+    import numpy as np
+    from pytorch_r2d2_b200 import QNet, engine
+    torch.manual_seed(9)
+    net = QNet("cuda:0", 256)
+    w = net._weights()
+    S, s0 = nt + 1, 1
+    slab = torch.from_numpy(np.random.RandomState(B * 10 + nt).randint(0, 256, (B, S, 4, 84, 84)).astype(np.uint8)).cuda()
+    R = B * nt
+    a1, a2, feat = engine.alloc_torso(R, "cuda")
+    engine.torso_fwd_u8(slab, s0, nt, w, a1, a2, feat)
+    dfeat = torch.randn(R, 1568, generator=torch.Generator().manual_seed(2)).cuda()
+    outs = []
+    for fn in (engine.torso_bwd_u8, engine.torso_bwd_tc_u8):
+        gflat = torch.full_like(net.flat_parameters(), float("nan"))
+        gw = engine.Weights(gflat, net.layout)
+        scratch = torch.empty(engine.torso_bwd_scratch_bytes(R), dtype=torch.uint8, device="cuda")
+        fn(slab, s0, nt, a1, a2, feat, dfeat.clone(), w, gw, scratch)
+        outs.append(gw)
+    ref, tc = outs
+    for name in ("w1", "b1", "w2", "b2", "w3", "b3"):
+        err = rel_err(getattr(tc, name), getattr(ref, name))
+        assert err < 1e-2, (name, err)
 
 
 @pytest.mark.parametrize("H,B,T", [(256, 4, 5), (512, 64, 6), (512, 8, 3), (256, 100, 2)])
