@@ -677,6 +677,294 @@ tc_lstm_bwd_kernel(const LstmBwdArgs a) {
     if (warp == 1) tmem_dealloc(tmem_base, 64);
 }
 
+// BPTT on CTA PAIRS: the contraction over the 4H gate rows is split between the two CTAs of a
+// cluster (same 16 units, same 32 batch rows, half of the k-blocks each): 64 instead of 128 small
+// MMAs and 64 instead of 128 KB of dG per CTA and step.  Each CTA finishes 8 of the 16 units: it keeps its
+// partial sums of those and PUSHES the partial sums of the other 8 into the peer's shared memory
+// (st.async, whose bytes complete a transaction barrier over there); the two partials are
+// summed in the order half 0 + half 1 on both sides.
+__device__ __forceinline__ uint32_t map_peer(const void* p, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_u32(p)), "r"(rank));
+    return r;
+}
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(288, 1)
+tc_lstm_bwd_pair_kernel(const LstmBwdArgs a) {
+    constexpr int NB = 32;
+    // A tile = NB rows x 128 B.  The UMMA reads 64 rows: with NB = 32 the upper half of a tile
+    // aliases the next tile (or the pad behind the ring) and only feeds ignored accumulator rows.
+    // Ring = 4 slots of 32 KB; a slot is a LOAD GROUP of kpg consecutive k-block tiles, contiguous
+    // and pre-swizzled in global memory: one bulk copy and one mbarrier per group (see the forward
+    // kernel).  NB = 32: 4 groups = the whole dG of a step (H <= 512), no "slot empty" barriers.
+    constexpr int LB_STAGES = 4;
+    constexpr uint32_t SLOT = LB_RING_BYTES / LB_STAGES;
+    constexpr bool WHOLE = NB == 32;
+    const int H = a.H, B = a.B, K4 = 4 * a.H, NKB_ALL = K4 / 64, NKB = NKB_ALL / 2;   // NKB: this CTA's k-blocks
+    const uint32_t half = cluster_ctarank();
+    const int kb0 = (int)half * NKB;
+    const int kpg = WHOLE ? NKB / 4 : (NKB >= 8 ? NKB / 8 : 1);   // tiles per load group (<= 32 KB)
+    const int ngrp = NKB / kpg;
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t full_bar[LB_STAGES], empty_bar[LB_STAGES], acc_full, acc_empty, xbar;
+    __shared__ uint32_t tmem_slot;
+    // partial recurrent terms of step parity s & 1: R = this CTA's k-half, P = the peer's (pushed by the peer),
+    // both only for the 8 units this CTA finishes
+    __shared__ __align__(16) float R[2][64][20], P[2][64][20];
+    const uint32_t raw = smem_u32(smem_raw);
+    uint8_t* base = smem_raw + ((1024u - (raw & 1023u)) & 1023u);
+    const uint32_t W_KB = LS_UNITS * 128;                       // 16 rows x 64 bf16 = 2 KB
+    uint8_t* w_s = base;                                        // [NKB][2 KB]
+    constexpr uint32_t A_TILE = NB * 128;                       // NB rows x 64 bf16
+    uint8_t* a_s = base + (size_t)NKB * W_KB;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int u0 = (blockIdx.x >> 1) * LS_UNITS, b0 = blockIdx.y * NB;
+    const int ncta = gridDim.x;
+    int* counter = a.counter + blockIdx.y;
+    const long long BH = (long long)B * H;
+    const long long GRP = (long long)NKB_ALL * NB * 64;         // dg16 image: [groups][4H/64][NB][64]
+    const long long IMG = GRP * gridDim.y;
+
+    if (tid == 0) {
+        for (int s = 0; s < LB_STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(&acc_full, LS_ISSUERS);
+        mbar_init(&acc_empty, 128);
+        mbar_init(&xbar, 1);
+        mbar_fence_init();
+    }
+    // resident B operand: row = unit u, K = gate index j: W_hh[j, u0+u]
+    for (int i = tid; i < LS_UNITS * NKB * 8; i += blockDim.x) {
+        const int u = i % LS_UNITS, chl = i / LS_UNITS;         // consecutive threads -> consecutive u
+        const int kb = chl >> 3, c = chl & 7, ch = kb0 * 8 + chl;
+        float v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] = __ldg(a.w_hh + (long long)(ch * 8 + e) * H + u0 + u);
+        *reinterpret_cast<uint4*>(w_s + (uint32_t)kb * W_KB + ls_sw128(u, c)) =
+            make_uint4(ls_pack(v[0], v[1]), ls_pack(v[2], v[3]), ls_pack(v[4], v[5]), ls_pack(v[6], v[7]));
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    if (warp == 1) tmem_alloc(&tmem_slot, 64);                   // LS_ISSUERS slices of 16 columns
+    const int issuer = warp == 1 ? 0 : (warp >= 6 ? warp - 5 : -1);   // MMA warps 1, 6, 7, 8
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();                                          // the peer's xbar exists
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+
+    // warps 2..5: TMEM readers (lane < 16 of warp q = warp % 4 owns accumulator row 16q + lane)
+    // hand the recurrent term over through shared memory, then all 128 threads do the gate-gradient
+    // math: thread -> batch row mr and EPT consecutive hidden units (dL/dc stays in registers)
+    const int q = warp & 3;
+    const bool treader = warp >= 2 && warp < 6 && q * 16 < NB;   // warp-uniform: tcgen05.ld is warp-wide
+    constexpr int EPT = 4, TPR = (LS_UNITS / 2) / EPT;          // this CTA finishes 8 of the 16 units: 64 threads
+    const int mi = tid - 64;
+    const int mr = (mi / TPR) & 31, mu = (int)half * (LS_UNITS / 2) + (mi % TPR) * EPT;
+    const int rb = b0 + mr;
+    const bool rvalid = warp >= 2 && warp < 6 && mi < NB * TPR && rb < B;
+    float dc_reg[EPT];
+#pragma unroll
+    for (int j = 0; j < EPT; ++j) dc_reg[j] = 0.f;
+
+    uint32_t it = 0;
+    for (int s = 0; s < a.T; ++s) {
+        const int t = a.T - 1 - s;
+        if (warp == 0) {
+            if (lane == 0 && s > 0) {
+                const int target = ncta * s;                    // every CTA finished iteration s-1
+                uint32_t spins = 0;
+                while (ld_acquire(counter) < target)
+                    if (++spins > (1u << 28)) __trap();
+                LB_STAMP(0);                                    // barrier passed
+                asm volatile("fence.proxy.async.global;" ::: "memory");
+                const int p = (s - 1) & 1;
+                const uint8_t* img = reinterpret_cast<const uint8_t*>(a.dg16 + (long long)p * IMG + (long long)blockIdx.y * GRP);
+                for (int g = 0; g < ngrp; ++g, ++it) {
+                    const int st = it % LB_STAGES;
+                    if constexpr (!WHOLE) mbar_wait(&empty_bar[st], ((it / LB_STAGES) & 1) ^ 1);
+                    mbar_expect_tx(&full_bar[st], kpg * A_TILE);
+                    bulk_g2s(a_s + (size_t)st * SLOT, img + (size_t)(kb0 + g * kpg) * A_TILE, kpg * A_TILE, &full_bar[st]);
+                }
+                LB_STAMP(1);                                    // all loads issued
+            }
+        } else if (issuer >= 0) {
+            if (lane == 0 && s > 0) {
+                // four issuing warps (k-blocks kb % 4 == issuer), private 16-column TMEM slices
+                constexpr uint32_t idesc = umma_idesc_bf16(LS_NB, LS_UNITS);
+                mbar_wait(&acc_empty, s & 1);   // readers drained iteration s-1 (s=1: passes at once)
+                tc_fence_after();
+                const uint64_t db0 = umma_desc_k_sw128(smem_u32(w_s));
+                const uint64_t da0 = umma_desc_k_sw128(smem_u32(a_s));
+                const uint32_t d = tmem_base + issuer * LS_UNITS;
+                const uint32_t it0 = (uint32_t)(s - 1) * ngrp;
+                for (int g = issuer; g < ngrp; g += LS_ISSUERS) {
+                    const uint32_t itk = it0 + g;
+                    const int st = itk % LB_STAGES;
+                    mbar_wait(&full_bar[st], (itk / LB_STAGES) & 1);
+                    tc_fence_after();
+                    if (g == 0) LB_STAMP(9);                    // first group landed
+                    if (g == ngrp - 1) LB_STAMP(10);            // last group landed
+                    for (int j = 0; j < kpg; ++j) {
+                        const int kb = g * kpg + j;
+                        const uint64_t aa = da0 + (uint64_t)((st * SLOT + j * A_TILE) >> 4);
+                        const uint64_t bb = db0 + (uint64_t)((kb * W_KB) >> 4);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            umma_f16(d, aa + 2 * k, bb + 2 * k, idesc, (g >= LS_ISSUERS) | (j != 0) | (k != 0));
+                    }
+                    if constexpr (!WHOLE) umma_commit(&empty_bar[st]);
+                }
+                umma_commit(&acc_full);
+                if (issuer == (ngrp - 1) % LS_ISSUERS) LB_STAMP(2);   // last MMA issued
+            }
+        } else if (warp >= 2 && warp < 6) {
+            // ---- everything that does not depend on the recurrent term is loaded BEFORE waiting
+            //      for the accumulator
+            float gi[EPT], gf[EPT], gg[EPT], go[EPT], ct[EPT], cp[EPT], dh[EPT];
+            const long long o = (long long)rb * H + u0 + mu;
+            if (rvalid) {
+                const float* gp = a.gates + ((long long)t * B + rb) * K4 + u0 + mu;
+#pragma unroll
+                for (int j = 0; j < EPT; j += 4) {
+                    *reinterpret_cast<float4*>(gi + j) = __ldg(reinterpret_cast<const float4*>(gp + j));
+                    *reinterpret_cast<float4*>(gf + j) = __ldg(reinterpret_cast<const float4*>(gp + H + j));
+                    *reinterpret_cast<float4*>(gg + j) = __ldg(reinterpret_cast<const float4*>(gp + 2 * H + j));
+                    *reinterpret_cast<float4*>(go + j) = __ldg(reinterpret_cast<const float4*>(gp + 3 * H + j));
+                    *reinterpret_cast<float4*>(ct + j) = __ldg(reinterpret_cast<const float4*>(a.cs_ext + (long long)(t + 1) * BH + o + j));
+                    *reinterpret_cast<float4*>(cp + j) = __ldg(reinterpret_cast<const float4*>(a.cs_ext + (long long)t * BH + o + j));
+                    *reinterpret_cast<float4*>(dh + j) = __ldg(reinterpret_cast<const float4*>(a.dhs + (long long)t * BH + o + j));
+                }
+            }
+            float rec[EPT];
+#pragma unroll
+            for (int j = 0; j < EPT; ++j) rec[j] = 0.f;
+            if (s > 0) {
+                if (tid == 64) {
+                    mbar_expect_tx(&xbar, NB * (LS_UNITS / 2) * 4);  // the peer's share of this step: 32 rows x 8 units
+                    mbar_wait_sleep(&acc_full, (s - 1) & 1, 32);
+                    LB_STAMP(3);                                // accumulators complete
+                }
+                named_bar_sync(3, 128);
+                tc_fence_after();
+                if (treader) {
+                    uint32_t ra[32], rb2[32];
+                    tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16), ra);
+                    tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + 32, rb2);
+                    tmem_ld_wait();
+                    // units 0-7 are finished by half 0, units 8-15 by half 1: the sums of MY units
+                    // stay here, the others are pushed into the peer's shared memory
+                    float* dst = &R[s & 1][q * 16 + (lane & 15)][0];
+                    const uint32_t rdst = map_peer(&P[s & 1][q * 16 + (lane & 15)][0], half ^ 1u);
+                    const uint32_t rbar = map_peer(&xbar, half ^ 1u);
+                    if (lane < 16)
+#pragma unroll
+                    for (int j = 0; j < LS_UNITS; j += 4) {
+                        const float4 v = make_float4(
+                            (__uint_as_float(ra[j]) + __uint_as_float(ra[16 + j])) + (__uint_as_float(rb2[j]) + __uint_as_float(rb2[16 + j])),
+                            (__uint_as_float(ra[j + 1]) + __uint_as_float(ra[17 + j])) + (__uint_as_float(rb2[j + 1]) + __uint_as_float(rb2[17 + j])),
+                            (__uint_as_float(ra[j + 2]) + __uint_as_float(ra[18 + j])) + (__uint_as_float(rb2[j + 2]) + __uint_as_float(rb2[18 + j])),
+                            (__uint_as_float(ra[j + 3]) + __uint_as_float(ra[19 + j])) + (__uint_as_float(rb2[j + 3]) + __uint_as_float(rb2[19 + j])));
+                        if ((uint32_t)(j >> 3) == half)
+                            *reinterpret_cast<float4*>(dst + j) = v;
+                        else
+                            // asynchronous remote store that counts its bytes on the peer's barrier
+                            asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.f32 [%0], {%1, %2, %3, %4}, [%5];" ::"r"(
+                                             rdst + j * 4),
+                                         "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "r"(rbar)
+                                         : "memory");
+                    }
+                }
+                tc_fence_before();
+                mbar_arrive(&acc_empty);
+                named_bar_sync(4, 128);                          // both partials are written (mine here, the peer's share over there)
+                {                                                // the peer's share has landed in P
+                    uint32_t ok = 0, spins = 0;
+                    while (!ok) {
+                        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+                                     "selp.u32 %0, 1, 0, p;\n}"
+                                     : "=r"(ok)
+                                     : "r"(smem_u32(&xbar)), "r"((uint32_t)((s - 1) & 1))
+                                     : "memory");
+                        if (!ok && ++spins > (1u << 26)) __trap();
+                    }
+                }
+                if (tid == 64) LB_STAMP(4);                     // TMEM read + hand-over
+                {
+                    const float4 own = *reinterpret_cast<const float4*>(&R[s & 1][mr][mu]);
+                    const float4 peer = *reinterpret_cast<const float4*>(&P[s & 1][mr][mu]);
+                    const float4 lo = half == 0 ? own : peer, hi = half == 0 ? peer : own;   // half 0 + half 1
+                    rec[0] = lo.x + hi.x, rec[1] = lo.y + hi.y, rec[2] = lo.z + hi.z, rec[3] = lo.w + hi.w;
+                }
+            }
+            float di[EPT], df[EPT], dg[EPT], dov[EPT];
+            if (rvalid) {
+#pragma unroll
+                for (int j = 0; j < EPT; ++j) {
+                    const float d = dh[j] + rec[j];
+                    const float tc = ls_tanh(ct[j]);
+                    const float dc = dc_reg[j] + d * go[j] * (1.f - tc * tc);
+                    di[j] = dc * gg[j] * gi[j] * (1.f - gi[j]);
+                    df[j] = dc * cp[j] * gf[j] * (1.f - gf[j]);
+                    dg[j] = dc * gi[j] * (1.f - gg[j] * gg[j]);
+                    dov[j] = d * tc * go[j] * (1.f - go[j]);
+                    dc_reg[j] = dc * gf[j];
+                }
+                // bf16 image the next step's bulk copies read: gate g, units u0.. = k-block
+                // g*H/64 + u0/64; 16-byte chunks in SWIZZLE_128B order (chunk ^ row%8)
+                const int col = (u0 & 63) + mu;
+                __nv_bfloat16* d16 = a.dg16 + (long long)(s & 1) * IMG + (long long)blockIdx.y * GRP +
+                                     ((long long)(u0 >> 6) * NB + mr) * 64 + ((((col >> 3) ^ (mr & 7)) << 3) | (col & 7));
+                const long long gstep = (long long)(H >> 6) * NB * 64;
+                if constexpr (EPT == 4) {
+                    *reinterpret_cast<uint2*>(d16) = make_uint2(ls_pack(di[0], di[1]), ls_pack(di[2], di[3]));
+                    *reinterpret_cast<uint2*>(d16 + gstep) = make_uint2(ls_pack(df[0], df[1]), ls_pack(df[2], df[3]));
+                    *reinterpret_cast<uint2*>(d16 + 2 * gstep) = make_uint2(ls_pack(dg[0], dg[1]), ls_pack(dg[2], dg[3]));
+                    *reinterpret_cast<uint2*>(d16 + 3 * gstep) = make_uint2(ls_pack(dov[0], dov[1]), ls_pack(dov[2], dov[3]));
+                } else {
+                    *reinterpret_cast<uint4*>(d16) = make_uint4(ls_pack(di[0], di[1]), ls_pack(di[2], di[3]), ls_pack(di[4], di[5]), ls_pack(di[6], di[7]));
+                    *reinterpret_cast<uint4*>(d16 + gstep) = make_uint4(ls_pack(df[0], df[1]), ls_pack(df[2], df[3]), ls_pack(df[4], df[5]), ls_pack(df[6], df[7]));
+                    *reinterpret_cast<uint4*>(d16 + 2 * gstep) = make_uint4(ls_pack(dg[0], dg[1]), ls_pack(dg[2], dg[3]), ls_pack(dg[4], dg[5]), ls_pack(dg[6], dg[7]));
+                    *reinterpret_cast<uint4*>(d16 + 3 * gstep) = make_uint4(ls_pack(dov[0], dov[1]), ls_pack(dov[2], dov[3]), ls_pack(dov[4], dov[5]), ls_pack(dov[6], dov[7]));
+                }
+            }
+            if (tid == 64) LB_STAMP(5);                         // gate math + bf16 stores issued
+            named_bar_sync(1, 128);
+            if (tid == 64) {
+                LB_STAMP(6);
+                red_release_add(counter, 1);
+                LB_STAMP(7);
+            }
+            // fp32 gradients for the kernels after the unroll, behind the releasing arrive
+            if (rvalid) {
+                float* dgp = a.dgates + ((long long)t * B + rb) * K4 + u0 + mu;
+#pragma unroll
+                for (int j = 0; j < EPT; j += 4) {
+                    *reinterpret_cast<float4*>(dgp + j) = make_float4(di[j], di[j + 1], di[j + 2], di[j + 3]);
+                    *reinterpret_cast<float4*>(dgp + H + j) = make_float4(df[j], df[j + 1], df[j + 2], df[j + 3]);
+                    *reinterpret_cast<float4*>(dgp + 2 * H + j) = make_float4(dg[j], dg[j + 1], dg[j + 2], dg[j + 3]);
+                    *reinterpret_cast<float4*>(dgp + 3 * H + j) = make_float4(dov[j], dov[j + 1], dov[j + 2], dov[j + 3]);
+                }
+                if (a.dgates16) {
+                    __nv_bfloat16* d16r = a.dgates16 + ((long long)t * B + rb) * K4 + u0 + mu;
+#pragma unroll
+                    for (int j = 0; j < EPT; j += 4) {
+                        *reinterpret_cast<uint2*>(d16r + j) = make_uint2(ls_pack(di[j], di[j + 1]), ls_pack(di[j + 2], di[j + 3]));
+                        *reinterpret_cast<uint2*>(d16r + H + j) = make_uint2(ls_pack(df[j], df[j + 1]), ls_pack(df[j + 2], df[j + 3]));
+                        *reinterpret_cast<uint2*>(d16r + 2 * H + j) = make_uint2(ls_pack(dg[j], dg[j + 1]), ls_pack(dg[j + 2], dg[j + 3]));
+                        *reinterpret_cast<uint2*>(d16r + 3 * H + j) = make_uint2(ls_pack(dov[j], dov[j + 1]), ls_pack(dov[j + 2], dov[j + 3]));
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();                                          // the peer may still be writing P
+    if (warp == 1) tmem_dealloc(tmem_base, 64);
+}
+
 }  // namespace r2d2
 
 using namespace r2d2;
@@ -784,6 +1072,29 @@ int r2d2_tc_lstm_seq_bwd(const float* dhs, const float* w_hh, const float* gates
     R2D2_REQUIRE(groups <= 64, "tc_lstm_seq_bwd: batch too large");
     R2D2_CUDA_OK(cudaMemsetAsync(a.counter, 0, 256, st));
     const int NKB = 4 * H / 64;
+    static const bool no_pairs = [] {                    // R2D2_BPTT_PAIRS=0: one CTA per unit block (A/B runs)
+        const char* e = getenv("R2D2_BPTT_PAIRS");
+        return e && e[0] == '0';
+    }();
+    if (!no_pairs && nb == 32 && NKB % 8 == 0 && 2 * (H / LS_UNITS) * groups <= sm_count()) {
+        const int smem2 = (NKB / 2) * LS_UNITS * 128 + LB_RING_BYTES + 4096 + 1024;
+        R2D2_CUDA_OK(cudaFuncSetAttribute(tc_lstm_bwd_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(2 * (H / LS_UNITS), groups);
+        cfg.blockDim = dim3(288);
+        cfg.dynamicSmemBytes = (size_t)smem2;
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeCooperative;     // all CTAs co-resident: they meet at a grid barrier every step
+        attr[0].val.cooperative = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        {
+            ProfScope ps("tc_lstm_bwd_kernel", st);
+            R2D2_CUDA_OK(cudaLaunchKernelEx(&cfg, tc_lstm_bwd_pair_kernel, a));
+        }
+        return R2D2_OK;
+    }
     const int smem = NKB * LS_UNITS * 128 + LB_RING_BYTES + 4096 + 1024;
     void* kern = nb == 32 ? (void*)tc_lstm_bwd_kernel<32> : (void*)tc_lstm_bwd_kernel<64>;
     R2D2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
