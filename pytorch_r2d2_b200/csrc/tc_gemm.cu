@@ -796,18 +796,22 @@ static int tc_linear_impl(const void* x_hi, const void* x_lo, const void* w_hi, 
     if (x_lo) {
         // bf16x3: BN = 256 halves the operand traffic per output; the small problems (heads) keep
         // 128-wide tiles so that they still spread over the SMs
-        const bool wide = (long long)((M + TC_BM - 1) / TC_BM) * ((N + 255) / 256) >= 2 * sm_count();
+        // Tile width: cost = waves x width, the kernels being persistent (a CTA walks its tiles one
+        // after the other).  128-wide tiles ([B_hi;B_lo] as one N = 256 operand, three stages) for
+        // small problems; up to 256 wide (half the operand traffic per output, two stages) for
+        // large ones and wherever a width between 144 and 256 saves a wave (the dueling heads:
+        // 20 x 8 tiles of 128 are two waves on 148 SMs, 20 x 7 tiles of 160 are one).
+        const long long mt = (M + TC_BM - 1) / TC_BM;
+        const long long sms = max_ctas > 0 && max_ctas < sm_count() ? max_ctas : sm_count();
+        const long long cost_cat = (mt * ((N + 127) / 128) + sms - 1) / sms * 128;
+        long long best = -1;
         int BNx = 128;
-        if (wide) {
-            // tile width that wastes the least in the last wave: cost = waves x width
-            const long long mt = (M + TC_BM - 1) / TC_BM;
-            const long long sms = max_ctas > 0 && max_ctas < sm_count() ? max_ctas : sm_count();
-            long long best = -1;
-            for (int bn = 256; bn >= 144; bn -= 16) {
-                const long long tiles = mt * ((N + bn - 1) / bn), cost = (tiles + sms - 1) / sms * bn;
-                if (best < 0 || cost < best) { best = cost; BNx = bn; }
-            }
+        for (int bn = 256; bn >= 144; bn -= 16) {
+            const long long tiles = mt * ((N + bn - 1) / bn), cost = (tiles + sms - 1) / sms * bn;
+            if (best < 0 || cost < best) { best = cost; BNx = bn; }
         }
+        const bool wide = mt * ((N + 255) / 256) >= 2 * sm_count() || best < cost_cat;
+        if (!wide) BNx = 128;
         CUtensorMap ta, tb, ta_lo, tb_lo;
         int rc = make_tmap(&ta, x_hi, M, K, TC_BM);
         if (rc) return rc;
