@@ -2,7 +2,7 @@
 `ncu --set full` report, keyed by bench.py's kernel names -> profiles/<round>_ncu_traffic.json."""
 import csv, json, subprocess, sys, collections
 NAMES = [
-    ("tc_lstm_fwd_kernel", "tc_lstm_fwd_kernel"), ("tc_lstm_bwd_kernel", "tc_lstm_bwd_kernel"),
+    ("tc_lstm_fwd_kernel", "tc_lstm_fwd_kernel"), ("tc_lstm_bwd_kernel", "tc_lstm_bwd_kernel"), ("tc_lstm_bwd_pair_kernel", "tc_lstm_bwd_kernel"),
     ("tc_conv1_sw_dual_kernel", "tc_conv1_fwd_dual"), ("tc_conv1_wgrad_sw_kernel", "tc_conv1_wgrad"),
     ("tc_conv2_wgrad_sw_kernel", "tc_conv2_wgrad"), ("tc_conv3_wgrad_sw_kernel", "tc_conv3_wgrad"),
     ("tc_conv2_dgrad_sw_kernel", "tc_conv2_dgrad"), ("tc_conv3_dgrad_sw_kernel", "tc_conv3_dgrad"),
